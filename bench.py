@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the scan-matching hot path (BASELINE.json).
+
+Metric M1 (headline `value`): scan-to-TSDF residual + Jacobian points/s on config C2 =
+"multi-resolution TSDF registration: 64-scan batch x 100k pts, high+low-res grids, 1 GPU":
+one step = one Evaluate of 64 two-pose interpolated multi-resolution TSDF residual blocks
+(InterpolatedMultiResolutionTSDFSpaceCostFunction3D) over 8 control poses, 6.4 M points,
+residuals + all four Jacobian blocks written in Ceres' layout.
+Metric M2 (reported in `correlative`): correlative candidates scored/s on config C4
+(MatchFullSubmap, lowest-resolution level), sharded by discrete scan over the ranks.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+`--impl reference` times the CPU restatement of the reference (oracle/, the reference itself
+cannot be compiled here — see DESIGN.md) on the host cores for the same metric and config.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NUM_SCANS = 64
+POINTS_PER_SCAN = 100000
+NUM_POSES = 8
+HI_RES, LO_RES = 0.10, 0.45
+REL_TRUNC, MAX_WEIGHT = 2.5, 1000.0
+# two-pose functor, fine level touched: 12 B point + 32 B (8 TSDFVoxel) + 120 B (r + 14 J).
+ALG_BYTES_PER_POINT = 164
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def build_workload(seed=2, num_scans=NUM_SCANS, points_per_scan=POINTS_PER_SCAN):
+    """C2 inputs: grids as voxel lists, 64 scans in their sensor frames, control poses, block table."""
+    from hectorgrapher_b200 import synth
+    rng = np.random.RandomState(seed)
+    sph = synth.spheres()
+    map_poses = [synth.corkscrew_pose(k, NUM_POSES) for k in range(NUM_POSES)]
+    hi = synth.build_tsdf(HI_RES, map_poses, 48, 1024, sph, REL_TRUNC, MAX_WEIGHT)
+    lo = synth.build_tsdf(LO_RES, map_poses, 48, 1024, sph, REL_TRUNC, MAX_WEIGHT)
+    clouds, i0, i1, ratios = [], [], [], []
+    rings, az = 128, 800
+    for s in range(num_scans):
+        u = s * (NUM_POSES - 1) / num_scans
+        a = int(np.floor(u))
+        f = rng.uniform(0.0, 1.0)
+        (oa, ya), (ob, yb) = map_poses[a], map_poses[a + 1]
+        origin = oa + (ob - oa) * f
+        yaw = ya + (yb - ya) * f
+        pts = synth.scan(origin, yaw, rings, az, sph, rng)
+        if len(pts) < points_per_scan:
+            pts = np.concatenate([pts, pts[: points_per_scan - len(pts)]])
+        clouds.append(pts[:points_per_scan])
+        i0.append(a)
+        i1.append(a + 1)
+        ratios.append(f)
+    poses = []
+    for k in range(NUM_POSES):
+        o, y = map_poses[k]
+        t = o + rng.uniform(-0.05, 0.05, 3)
+        q = synth.quat_mul(synth.quat_from_yaw(y), synth.small_rotation(rng, 0.02))
+        poses.append(np.concatenate([t, q]))
+    points = np.ascontiguousarray(np.concatenate(clouds), np.float32)
+    offsets = np.arange(num_scans + 1, dtype=np.int64) * points_per_scan
+    scales = np.full(num_scans, 1.0 / np.sqrt(points_per_scan))
+    return dict(hi=hi, lo=lo, points=points, offsets=offsets, scales=scales, ratios=np.array(ratios),
+                poses=np.array(poses), i0=np.array(i0, np.int32), i1=np.array(i1, np.int32), synth=synth,
+                sph=sph, map_poses=map_poses)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.samples = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(index), "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            p = [x.strip() for x in s.split(",")]
+            if len(p) < 6:
+                continue
+            try:
+                sm.append(float(p[0]))
+                mx.append(float(p[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, p[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(np.max(mx)) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline_points(w, seconds=12.0, threads=None):
+    """Times the CPU restatement (oracle/) of the same functor on a bounded sample: one 100k-point
+    block, all host threads evaluating it concurrently (how ConstraintBuilder3D's pool and a
+    multi-threaded Ceres evaluate blocks). Returns (points/s, description, threads)."""
+    from oracle import pyoracle as o
+    threads = threads or os.cpu_count() or 1
+    hi = o.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT)
+    hi.set_raw(*w["hi"])
+    lo = o.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT)
+    lo.set_raw(*w["lo"])
+    n = int(w["offsets"][1])
+    c = o.Cost("interpolated_multires_tsdf", w["scales"][0], w["points"][:n], [hi, lo], float(w["ratios"][0]))
+    p = np.concatenate([w["poses"][w["i0"][0]], w["poses"][w["i1"][0]]])
+    t1 = c.time(p, 1, 1)
+    one_thread = n / t1
+    reps = max(1, int(seconds / max(t1 * 1.3, 1e-3)))
+    tt = c.time(p, reps, threads)
+    rate = n * reps * threads / tt
+    desc = ("block 0 (%d pts, two-pose multi-res TSDF, residuals+Jacobians), %d threads x %d evaluations; "
+            "1 thread: %.3g pts/s" % (n, threads, reps, one_thread))
+    return rate, desc, threads, (c, p, n, hi, lo)
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    w = build_workload()
+    rate, desc, threads, (c, p, n, hi, lo) = cpu_baseline_points(w, seconds=2.0)
+    # steps: each a bounded sample (all threads x 1 evaluation of one 100k-point block)
+    for _ in range(args.warmup):
+        c.time(p, 1, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        c.time(p, 1, threads)
+    dt = time.perf_counter() - t0
+    value = n * threads * args.steps / dt
+    line = {
+        "impl": "reference", "metric": "scan-to-TSDF residual+Jacobian points/s", "value": value,
+        "unit": "points/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "C2 multi-resolution TSDF registration: 64 scans x 100k pts, 0.10 m + 0.45 m TSDF, "
+                               "two-pose interpolated multi-res functor",
+                   "sample_per_step": "%d threads x 1 Evaluate of one 100k-point block" % threads},
+        "cpu_baseline": {"value": value, "unit": "points/s", "cores": threads, "kind": "port",
+                         "sample": "CPU restatement (oracle/) of the reference functor; " + desc},
+        "e2e": {"value": value, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def correlative_bench(hg, torch, w, rank, world, dist):
+    """C4: MatchFullSubmap on the 0.10 m TSDF submap; lowest-resolution candidates sharded by discrete
+    scan over ranks. Returns a dict for the `correlative` key (rank 0) or None."""
+    synth = w["synth"]
+    g_hi = hg.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT, *w["hi"])
+    g_lo = hg.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT, *w["lo"])
+    origin, yaw = w["map_poses"][3]
+    rng = np.random.RandomState(4)
+    cloud = synth.scan(origin, yaw, 64, 512, w["sph"], rng)
+    high = synth.voxel_downsample(cloud, 0.2, 2048, seed=4)
+    low = synth.voxel_downsample(cloud, 0.9, 256, seed=5)
+    hist = synth.rotational_histogram(high, 120)
+    opts = dict(branch_and_bound_depth=7, full_resolution_depth=3, use_rotational_scan_matcher=False,
+                min_low_resolution_score=0.3, linear_xy_search_window=5.0, linear_z_search_window=1.0,
+                angular_search_window=float(np.deg2rad(15.0)))
+    m = hg.Fcsm(g_hi, g_lo, hist, **opts)
+    node = np.concatenate([[0, 0, 0], synth.quat_from_yaw(yaw + 0.4)])
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    # warm-up + timed full search on this rank's shard
+    m.match(node, submap, high[:256], low, hist, min_score=0.3, full=True, shard_index=rank, num_shards=world)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    r = m.match(node, submap, high, low, hist, min_score=0.3, full=True, shard_index=rank, num_shards=world)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    rec = torch.tensor([dt, float(r["num_scored"]), float(r["found"]), float(r["score"]), float(r["scan_index"]),
+                        r["ox"], r["oy"], r["oz"], float(r["num_scans"])], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        allrec = [torch.zeros_like(rec) for _ in range(world)]
+        dist.all_gather(allrec, rec)  # NCCL: best-candidate reduce (tens of bytes per rank)
+        allrec = torch.stack(allrec).cpu().numpy()
+    else:
+        allrec = rec.cpu().numpy()[None]
+    if rank != 0:
+        return None
+    tmax = float(allrec[:, 0].max())
+    scored = float(allrec[:, 1].sum())
+    found = allrec[allrec[:, 2] > 0]
+    best = found[np.argmax(found[:, 3])] if len(found) else None
+    n_pts = len(high)
+    peak, _ = measured_peak()
+    cps = scored / tmax
+    return {
+        "metric": "correlative candidates scored/s", "value": cps, "unit": "candidates/s",
+        "workload": "C4 MatchFullSubmap, 0.10 m TSDF submap, 7-level pyramid (full_resolution_depth 3), "
+                    "N=%d pts, sharded by discrete scan over %d rank(s)" % (n_pts, world),
+        "search_ms": 1e3 * tmax, "candidates_scored": scored, "discrete_scans": float(allrec[:, 8].sum()),
+        "best": None if best is None else {"score": float(best[3]), "scan": int(best[4]),
+                                           "offset": [int(best[5]), int(best[6]), int(best[7])]},
+        "roofline": {"bound": "hbm", "achieved": cps * (n_pts + 24) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": cps * (n_pts + 24) / 1e9 / peak, "traffic": None,
+                     "note": "whole search incl. host replay; algorithmic bytes N+24 per candidate"},
+    }
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import hectorgrapher_b200 as hg
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback "
+                         "(use --impl reference for the CPU arm)")
+    hg.lib()
+    torch.cuda.set_device(local_rank)
+    hg.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist = dist_mod
+    t_setup = time.time()
+    w = build_workload()
+    N = int(w["offsets"][-1])
+    g_hi = hg.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT, *w["hi"])
+    g_lo = hg.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT, *w["lo"])
+    batch = hg.Batch("interpolated_multires_tsdf", w["points"], w["offsets"], w["scales"], [g_hi, g_lo], w["ratios"])
+    log("[rank %d] setup %.1f s: %d pts, grids %d + %d voxels, %d + %d bricks" % (
+        rank, time.time() - t_setup, N, len(w["hi"][0]), len(w["lo"][0]), g_hi.num_bricks, g_lo.num_bricks))
+
+    dev = torch.device("cuda", local_rank)
+    d_r = torch.empty(N, dtype=torch.float64, device=dev)
+    d_jt0 = torch.empty(N * 3, dtype=torch.float64, device=dev)
+    d_jq0 = torch.empty(N * 4, dtype=torch.float64, device=dev)
+    d_jt1 = torch.empty(N * 3, dtype=torch.float64, device=dev)
+    d_jq1 = torch.empty(N * 4, dtype=torch.float64, device=dev)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    poses = np.ascontiguousarray(w["poses"])
+    i0, i1 = w["i0"], w["i1"]
+    stream = torch.cuda.current_stream()
+
+    def step_device():
+        batch.evaluate_raw(poses.ctypes.data, len(poses), i0.ctypes.data, i1.ctypes.data, True, d_r.data_ptr(),
+                           d_jt0.data_ptr(), d_jq0.data_ptr(), d_jt1.data_ptr(), d_jq1.data_ptr(),
+                           stream.cuda_stream)
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    launches0 = hg.kernel_launch_count()
+    times = []
+    torch.cuda.synchronize()
+    for _ in range(args.steps):
+        flush.fill_(1)  # evict L2 between timed iterations (256 MiB > 126 MB L2); not timed
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        step_device()
+        e1.record(stream)
+        e1.synchronize()
+        times.append(e0.elapsed_time(e1))
+    torch.cuda.synchronize()
+    launches = hg.kernel_launch_count() - launches0
+    if dist is not None:
+        dist.barrier()
+    total_ms = torch.tensor([float(np.sum(times))], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    clocks = sampler.stop() if sampler else None
+
+    # sanity: finite outputs, non-trivial Jacobian
+    chk = float(d_r.abs().sum().item())
+    jchk = float(d_jq1.abs().max().item())
+    assert np.isfinite(chk) and jchk > 0, "bench outputs are not plausible"
+
+    # end to end through the C-ABI with HOST buffers: this step's scans H2D from pinned memory,
+    # Evaluate, residuals + Jacobians D2H into pinned host arrays.
+    h_pts = torch.from_numpy(w["points"]).pin_memory()
+    h_out = [torch.empty(n, dtype=torch.float64).pin_memory() for n in (N, 3 * N, 4 * N, 3 * N, 4 * N)]
+    def step_e2e():
+        batch.update_points(h_pts.numpy())
+        batch.evaluate_raw(poses.ctypes.data, len(poses), i0.ctypes.data, i1.ctypes.data, False,
+                           h_out[0].data_ptr(), h_out[1].data_ptr(), h_out[2].data_ptr(), h_out[3].data_ptr(),
+                           h_out[4].data_ptr(), None)
+    step_e2e()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    e2e_steps = max(2, min(args.steps, 5))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_e2e()
+    torch.cuda.synchronize()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_s.item())
+    assert abs(float(h_out[0].abs().sum()) - chk) <= 1e-9 * max(1.0, chk)
+
+    # Gauss-Newton surface (no Jacobian materialised), for context
+    batch.normal_equations(poses, i0, i1)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        batch.normal_equations(poses, i0, i1)
+    ne_ms = 1e3 * (time.perf_counter() - t0) / 3
+
+    corr = None
+    try:
+        corr = correlative_bench(hg, torch, w, rank, world, dist)
+    except Exception as ex:  # the headline must not be lost to the secondary metric
+        log("[rank %d] correlative bench failed: %r" % (rank, ex))
+        corr = {"error": repr(ex)}
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        ms_per_step = total_ms / args.steps
+        value = world * N / (ms_per_step * 1e-3)
+        per_gpu = N / (ms_per_step * 1e-3)
+        achieved = per_gpu * ALG_BYTES_PER_POINT / 1e9
+        cpu_rate, cpu_desc, cpu_threads, _ = cpu_baseline_points(w)
+        line = {
+            "metric": "scan-to-TSDF residual+Jacobian points/s", "value": value, "unit": "points/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C2 multi-resolution TSDF registration: 64 scans x 100k pts, 0.10 m + 0.45 m "
+                                   "TSDF, two-pose interpolated multi-res functor, 8 control poses; one step = one "
+                                   "batched Evaluate (residuals + 4 Jacobian blocks, Ceres layout)",
+                       "points_per_step_per_gpu": N, "multi_gpu": "replicas only (one window per GPU)",
+                       "l2": "256 MiB flush write between timed steps; working set per step ~0.9 GB"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_point": ALG_BYTES_PER_POINT, "kernel": "CostKernel<2,true,false>"},
+            "cpu_baseline": {"value": cpu_rate, "unit": "points/s", "cores": cpu_threads, "kind": "port",
+                             "sample": cpu_desc},
+            "e2e": {"value": world * N * e2e_steps / e2e_s, "unit": "points/s",
+                    "h2d_bytes_per_step": int(w["points"].nbytes + poses.nbytes),
+                    "d2h_bytes_per_step": int(15 * N * 8), "ms_per_step": 1e3 * e2e_s / e2e_steps},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "normal_equations": {"ms_per_step": ne_ms, "points_per_s": N / (ne_ms * 1e-3),
+                                 "note": "hg_batch_normal_equations: host poses in, 64 x (14x14 JtJ, Jtr, cost) out"},
+            "correlative": corr,
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,538 @@
+"""ctypes bindings of include/hg_b200.h (libhg_b200.so). No compute happens here."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhg_b200.so")
+_LIB = None
+
+vp = C.c_void_p
+c_i = C.c_int
+c_i64 = C.c_int64
+c_f = C.c_float
+c_d = C.c_double
+
+KINDS = {
+    "occupied": 0, "interpolated_occupied": 1, "tsdf": 2, "interpolated_tsdf": 3,
+    "interpolated_tsdf_per_point": 4, "multires_tsdf": 5, "interpolated_multires_tsdf": 6,
+    "interpolated_multires_tsdf_per_point": 7,
+}
+
+
+class HgError(RuntimeError):
+    pass
+
+
+class FcsmOptions(C.Structure):
+    _fields_ = [("branch_and_bound_depth", C.c_int32), ("full_resolution_depth", C.c_int32),
+                ("use_rotational_scan_matcher", C.c_int32), ("min_rotational_score", c_d),
+                ("min_low_resolution_score", c_d), ("linear_xy_search_window", c_d),
+                ("linear_z_search_window", c_d), ("angular_search_window", c_d),
+                ("float_flavor", C.c_int32)]
+
+
+class NodeData(C.Structure):
+    _fields_ = [("high_resolution_point_cloud", vp), ("num_high_resolution_points", C.c_int32),
+                ("low_resolution_point_cloud", vp), ("num_low_resolution_points", C.c_int32),
+                ("rotational_scan_matcher_histogram", vp), ("histogram_size", C.c_int32),
+                ("gravity_alignment", c_d * 4)]
+
+
+class MatchResult(C.Structure):
+    _fields_ = [("found", C.c_int32), ("score", c_f), ("pose_translation", c_d * 3),
+                ("pose_rotation", c_d * 4), ("rotational_score", c_f), ("low_resolution_score", c_f),
+                ("best_scan_index", C.c_int32), ("best_offset", C.c_int32 * 3),
+                ("num_discrete_scans", C.c_int32), ("num_candidates_scored", c_i64),
+                ("num_candidates_visited", c_i64), ("num_score_launches", C.c_int32)]
+
+
+class ConstraintJob(C.Structure):
+    _fields_ = [("submap_index", C.c_int32), ("match_full_submap", C.c_int32),
+                ("global_node_pose", c_d * 7), ("global_submap_pose", c_d * 7), ("data", NodeData)]
+
+
+class ConstraintOptions(C.Structure):
+    _fields_ = [("min_score", c_f), ("global_localization_min_score", c_f),
+                ("occupied_space_weights", c_d * 2), ("translation_weight", c_d),
+                ("rotation_weight", c_d), ("only_optimize_yaw", C.c_int32),
+                ("max_num_iterations", C.c_int32), ("use_nonmonotonic_steps", C.c_int32)]
+
+
+class ConstraintResult(C.Structure):
+    _fields_ = [("found", C.c_int32), ("score", c_f), ("pose", c_d * 7), ("rotational_score", c_f),
+                ("low_resolution_score", c_f), ("num_candidates_scored", c_i64)]
+
+
+# Every symbol include/hg_b200.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "hg_last_error": (C.c_char_p, []),
+    "hg_version": (C.c_char_p, []),
+    "hg_kernel_launch_count": (C.c_uint64, []),
+    "hg_set_device": (c_i, [c_i]),
+    "hg_grid_upload_prob": (c_i, [c_f, c_i, c_i64, vp, vp, vp]),
+    "hg_grid_upload_tsdf": (c_i, [c_f, c_f, c_f, c_i, c_i64, vp, vp, vp, vp]),
+    "hg_grid_destroy": (None, [vp]),
+    "hg_grid_size": (c_i, [vp]),
+    "hg_grid_num_bricks": (c_i64, [vp]),
+    "hg_grid_lookup": (c_i, [vp, c_i, c_i64, vp, vp]),
+    "hg_get_cell_index": (c_i, [c_f, c_i64, vp, vp]),
+    "hg_cost_create": (c_i, [c_i, c_d, vp, c_i, c_i, vp, c_i, c_d, vp]),
+    "hg_cost_destroy": (None, [vp]),
+    "hg_cost_num_residuals": (c_i, [vp]),
+    "hg_cost_num_parameter_blocks": (c_i, [vp]),
+    "hg_cost_evaluate": (c_i, [vp, vp, vp, vp]),
+    "hg_cost_evaluate_device": (c_i, [vp, vp, vp, vp, vp]),
+    "hg_cost_normal_equations": (c_i, [vp, vp, vp, vp, vp]),
+    "hg_batch_create": (c_i, [c_i, c_i, vp, c_i, vp, vp, vp, vp, c_i, vp]),
+    "hg_batch_destroy": (None, [vp]),
+    "hg_batch_num_residuals": (c_i64, [vp]),
+    "hg_batch_update_points": (c_i, [vp, vp, c_i]),
+    "hg_batch_evaluate": (c_i, [vp, vp, c_i, vp, vp, c_i, vp, vp, vp, vp, vp, vp]),
+    "hg_batch_normal_equations": (c_i, [vp, vp, c_i, vp, vp, vp, vp, vp]),
+    "hg_scan_match": (c_i, [c_i, vp, vp, vp, vp, c_d, c_d, c_i, c_i, c_i, vp, vp, vp, vp]),
+    "hg_stack_build": (c_i, [vp, c_i, c_i, vp]),
+    "hg_stack_destroy": (None, [vp]),
+    "hg_stack_depth": (c_i, [vp]),
+    "hg_stack_lookup": (c_i, [vp, c_i, c_i64, vp, vp]),
+    "hg_stack_num_nonzero": (c_i64, [vp, c_i]),
+    "hg_stack_export": (c_i, [vp, c_i, c_i64, vp, vp, vp]),
+    "hg_fcsm_create": (c_i, [vp, vp, vp, c_i, vp, vp]),
+    "hg_fcsm_destroy": (None, [vp]),
+    "hg_fcsm_stack": (vp, [vp]),
+    "hg_fcsm_match": (c_i, [vp, vp, vp, vp, c_f, vp]),
+    "hg_fcsm_match_full_submap": (c_i, [vp, vp, vp, vp, c_f, c_i, c_i, vp]),
+    "hg_fcsm_discrete_scans": (c_i, [vp, c_i, c_i, c_d, vp, vp, vp, c_i, vp, vp, vp, vp]),
+    "hg_fcsm_score_candidates": (c_i, [vp, c_i, c_i, c_d, vp, vp, vp, c_i, c_i64, vp, vp, vp, vp]),
+    "hg_low_resolution_scores": (c_i, [vp, vp, c_i, c_i64, vp, vp]),
+    "hg_constraints_run_batch": (c_i, [vp, vp, vp, c_i, vp, c_i64, vp, c_i, c_i, vp]),
+}
+
+
+def build(verbose=False):
+    """Compiles libhg_b200.so in-tree (nvcc, sm_100a)."""
+    cmd = ["make", "-C", os.path.join(_HERE, "csrc"), "-j8"]
+    if not verbose:
+        cmd.append("-s")
+    subprocess.check_call(cmd)
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise HgError("libhg_b200.so is missing: run hectorgrapher_b200.build() / "
+                          "__graft_entry__.build(); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = L
+    return _LIB
+
+
+def _check(rc):
+    if rc != 0:
+        raise HgError("hg error %d: %s" % (rc, lib().hg_last_error().decode()))
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(vp)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def set_device(device):
+    _check(lib().hg_set_device(device))
+
+
+def kernel_launch_count():
+    return int(lib().hg_kernel_launch_count())
+
+
+class Grid:
+    def __init__(self, handle, tsdf):
+        self.h = handle
+        self.is_tsdf = tsdf
+
+    @staticmethod
+    def prob(resolution, xyz, values, grid_size=0):
+        xyz = _i32(xyz).reshape(-1, 3)
+        values = np.ascontiguousarray(values, dtype=np.uint16)
+        out = vp()
+        _check(lib().hg_grid_upload_prob(resolution, grid_size, len(xyz), _p(xyz), _p(values), C.byref(out)))
+        return Grid(out, False)
+
+    @staticmethod
+    def tsdf(resolution, relative_truncation_distance, max_weight, xyz, tsd, weight, grid_size=0):
+        xyz = _i32(xyz).reshape(-1, 3)
+        tsd = np.ascontiguousarray(tsd, dtype=np.uint16)
+        weight = np.ascontiguousarray(weight, dtype=np.uint16)
+        out = vp()
+        _check(lib().hg_grid_upload_tsdf(resolution, relative_truncation_distance, max_weight, grid_size,
+                                         len(xyz), _p(xyz), _p(tsd), _p(weight), C.byref(out)))
+        return Grid(out, True)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().hg_grid_destroy(self.h)
+            self.h = None
+
+    @property
+    def grid_size(self):
+        return lib().hg_grid_size(self.h)
+
+    @property
+    def num_bricks(self):
+        return lib().hg_grid_num_bricks(self.h)
+
+    def lookup(self, what, xyz):
+        xyz = _i32(xyz).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float32)
+        code = {"probability": 0, "tsd": 1, "weight": 2}[what]
+        _check(lib().hg_grid_lookup(self.h, code, len(xyz), _p(xyz), _p(out)))
+        return out
+
+
+def get_cell_index(resolution, pts):
+    pts = _f32(pts).reshape(-1, 3)
+    out = np.zeros((len(pts), 3), np.int32)
+    _check(lib().hg_get_cell_index(resolution, len(pts), _p(pts), _p(out)))
+    return out
+
+
+def _grid_array(grids):
+    return (vp * len(grids))(*[g.h for g in grids])
+
+
+class Cost:
+    """One residual block; evaluate() has ceres::CostFunction::Evaluate semantics."""
+
+    def __init__(self, kind, scaling, pts, grids, ratio=0.0, stride=3):
+        self.pts = _f32(pts).reshape(-1, stride)
+        self.grids = list(grids)
+        out = vp()
+        k = KINDS[kind] if isinstance(kind, str) else kind
+        _check(lib().hg_cost_create(k, scaling, _p(self.pts), stride, len(self.pts), _grid_array(grids),
+                                    len(grids), ratio, C.byref(out)))
+        self.h = out
+        self.n = lib().hg_cost_num_residuals(self.h)
+        self.nblocks = lib().hg_cost_num_parameter_blocks(self.h)
+        self.sizes = [3, 4] * (self.nblocks // 2)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().hg_cost_destroy(self.h)
+            self.h = None
+
+    def _blocks(self, params):
+        params = _f64(params).reshape(-1)
+        blocks, off = [], 0
+        for s in self.sizes:
+            blocks.append(np.ascontiguousarray(params[off:off + s]))
+            off += s
+        return blocks
+
+    def evaluate(self, params, jacobians=True, skip_blocks=()):
+        blocks = self._blocks(params)
+        parr = (vp * len(blocks))(*[b.ctypes.data for b in blocks])
+        r = np.zeros(self.n, np.float64)
+        if not jacobians:
+            _check(lib().hg_cost_evaluate(self.h, parr, _p(r), None))
+            return r, None
+        J = [np.zeros((self.n, s), np.float64) for s in self.sizes]
+        jarr = (vp * len(J))(*[None if i in skip_blocks else J[i].ctypes.data for i in range(len(J))])
+        _check(lib().hg_cost_evaluate(self.h, parr, _p(r), jarr))
+        return r, J
+
+    def normal_equations(self, params):
+        blocks = self._blocks(params)
+        parr = (vp * len(blocks))(*[b.ctypes.data for b in blocks])
+        n = sum(self.sizes)
+        JtJ = np.zeros((n, n))
+        Jtr = np.zeros(n)
+        cost = np.zeros(1)
+        _check(lib().hg_cost_normal_equations(self.h, parr, _p(JtJ), _p(Jtr), _p(cost)))
+        return JtJ, Jtr, float(cost[0])
+
+
+class Batch:
+    """Many residual blocks of one kind over the same grids, one launch."""
+
+    def __init__(self, kind, clouds_or_points, offsets, scales, grids, ratios=None, stride=3):
+        self.kind = KINDS[kind] if isinstance(kind, str) else kind
+        self.two_pose = self.kind in (1, 3, 4, 6, 7)
+        pts = _f32(clouds_or_points).reshape(-1, stride)
+        self.offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        self.num_blocks = len(self.offsets) - 1
+        self.N = int(self.offsets[-1])
+        self.stride = stride
+        scales = _f64(scales)
+        ratios = None if ratios is None else _f64(ratios)
+        self.grids = list(grids)
+        out = vp()
+        _check(lib().hg_batch_create(self.kind, self.num_blocks, _p(pts), stride, _p(self.offsets), _p(scales),
+                                     _p(ratios), _grid_array(grids), len(grids), C.byref(out)))
+        self.h = out
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().hg_batch_destroy(self.h)
+            self.h = None
+
+    def update_points(self, pts):
+        """pts: host array (pinned torch tensors are passed via .numpy())."""
+        pts = _f32(pts)
+        _check(lib().hg_batch_update_points(self.h, _p(pts), self.stride))
+
+    def evaluate_raw(self, poses_ptr, num_poses, i0_ptr, i1_ptr, device_outputs, r, jt0, jq0, jt1, jq1,
+                     stream=None):
+        """All arguments are raw addresses (ints) or None."""
+        _check(lib().hg_batch_evaluate(self.h, poses_ptr, num_poses, i0_ptr, i1_ptr, int(device_outputs), r,
+                                       jt0, jq0, jt1, jq1, stream))
+
+    def evaluate(self, poses, i0, i1=None):
+        """Host outputs as numpy arrays (parity tests)."""
+        poses = _f64(poses).reshape(-1, 7)
+        i0 = _i32(i0)
+        i1 = None if i1 is None else _i32(i1)
+        N = self.N
+        r = np.zeros(N)
+        jt0, jq0 = np.zeros((N, 3)), np.zeros((N, 4))
+        jt1 = np.zeros((N, 3)) if self.two_pose else None
+        jq1 = np.zeros((N, 4)) if self.two_pose else None
+        _check(lib().hg_batch_evaluate(self.h, _p(poses), len(poses), _p(i0), _p(i1), 0, _p(r), _p(jt0),
+                                       _p(jq0), _p(jt1), _p(jq1), None))
+        return r, [jt0, jq0] + ([jt1, jq1] if self.two_pose else [])
+
+    def normal_equations(self, poses, i0, i1=None):
+        poses = _f64(poses).reshape(-1, 7)
+        i0 = _i32(i0)
+        i1 = None if i1 is None else _i32(i1)
+        n = 14 if self.two_pose else 7
+        JtJ = np.zeros((self.num_blocks, n, n))
+        Jtr = np.zeros((self.num_blocks, n))
+        cost = np.zeros(self.num_blocks)
+        _check(lib().hg_batch_normal_equations(self.h, _p(poses), len(poses), _p(i0), _p(i1), _p(JtJ), _p(Jtr),
+                                               _p(cost)))
+        return JtJ, Jtr, cost
+
+
+def scan_match(clouds, grids, weights, translation_weight, rotation_weight, initial_pose,
+               target_translation=None, only_optimize_yaw=False, max_num_iterations=10,
+               use_nonmonotonic_steps=True):
+    clouds = [_f32(c).reshape(-1, 3) for c in clouds]
+    carr = (vp * len(clouds))(*[c.ctypes.data for c in clouds])
+    sizes = _i32([len(c) for c in clouds])
+    weights = _f64(weights)
+    initial_pose = _f64(initial_pose)
+    target = _f64(initial_pose[:3] if target_translation is None else target_translation)
+    pose = np.zeros(7)
+    summary = np.zeros(6)
+    _check(lib().hg_scan_match(len(clouds), carr, _p(sizes), _grid_array(grids), _p(weights),
+                               translation_weight, rotation_weight, int(only_optimize_yaw),
+                               max_num_iterations, int(use_nonmonotonic_steps), _p(target), _p(initial_pose),
+                               _p(pose), _p(summary)))
+    return pose, summary
+
+
+class Stack:
+    def __init__(self, grid, depth, full_resolution_depth, handle=None, owner=None):
+        self.grid = grid
+        self.owner = owner
+        if handle is None:
+            out = vp()
+            _check(lib().hg_stack_build(grid.h, depth, full_resolution_depth, C.byref(out)))
+            self.h = out
+            self.owned = True
+        else:
+            self.h = handle
+            self.owned = False
+        self.depth = lib().hg_stack_depth(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None) and self.owned:
+            lib().hg_stack_destroy(self.h)
+        self.h = None
+
+    def lookup(self, d, xyz):
+        xyz = _i32(xyz).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.uint8)
+        _check(lib().hg_stack_lookup(self.h, d, len(xyz), _p(xyz), _p(out)))
+        return out
+
+    def export(self, d):
+        n = lib().hg_stack_num_nonzero(self.h, d)
+        if n < 0:
+            raise HgError(lib().hg_last_error().decode())
+        xyz = np.zeros((n, 3), np.int32)
+        v = np.zeros(n, np.uint8)
+        written = c_i64(0)
+        _check(lib().hg_stack_export(self.h, d, n, _p(xyz), _p(v), C.byref(written)))
+        assert written.value == n
+        return xyz, v
+
+
+FCSM_DEFAULTS = dict(branch_and_bound_depth=8, full_resolution_depth=3, use_rotational_scan_matcher=True,
+                     min_rotational_score=0.77, min_low_resolution_score=0.55,
+                     linear_xy_search_window=5.0, linear_z_search_window=1.0,
+                     angular_search_window=float(np.deg2rad(15.0)), float_flavor=1)
+
+
+def make_node_data(high, low, hist, gravity=(1, 0, 0, 0)):
+    """Returns (NodeData, keepalive tuple)."""
+    high = _f32(high).reshape(-1, 3)
+    low = _f32(low).reshape(-1, 3)
+    hist = _f32(hist)
+    d = NodeData()
+    d.high_resolution_point_cloud = high.ctypes.data
+    d.num_high_resolution_points = len(high)
+    d.low_resolution_point_cloud = low.ctypes.data if len(low) else None
+    d.num_low_resolution_points = len(low)
+    d.rotational_scan_matcher_histogram = hist.ctypes.data if len(hist) else None
+    d.histogram_size = len(hist)
+    for k in range(4):
+        d.gravity_alignment[k] = float(gravity[k])
+    return d, (high, low, hist)
+
+
+def _result_dict(r):
+    return dict(found=float(r.found), score=float(r.score), tx=r.pose_translation[0], ty=r.pose_translation[1],
+                tz=r.pose_translation[2], qw=r.pose_rotation[0], qx=r.pose_rotation[1],
+                qy=r.pose_rotation[2], qz=r.pose_rotation[3], rotational_score=float(r.rotational_score),
+                low_resolution_score=float(r.low_resolution_score), scan_index=float(r.best_scan_index),
+                ox=float(r.best_offset[0]), oy=float(r.best_offset[1]), oz=float(r.best_offset[2]),
+                num_scans=float(r.num_discrete_scans), num_scored=int(r.num_candidates_scored),
+                num_visited=int(r.num_candidates_visited), num_launches=int(r.num_score_launches))
+
+
+class Fcsm:
+    def __init__(self, grid, low_grid, submap_hist, **options):
+        o = dict(FCSM_DEFAULTS)
+        o.update(options)
+        self.o = o
+        self.grid, self.low_grid = grid, low_grid
+        self.hist = _f32(submap_hist)
+        opt = FcsmOptions()
+        for k, v in o.items():
+            setattr(opt, k, int(v) if k in ("branch_and_bound_depth", "full_resolution_depth",
+                                            "use_rotational_scan_matcher", "float_flavor") else float(v))
+        self.opt = opt
+        out = vp()
+        _check(lib().hg_fcsm_create(grid.h, low_grid.h, _p(self.hist) if len(self.hist) else None,
+                                    len(self.hist), C.byref(opt), C.byref(out)))
+        self.h = out
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().hg_fcsm_destroy(self.h)
+            self.h = None
+
+    def stack(self):
+        return Stack(self.grid, 0, 0, handle=lib().hg_fcsm_stack(self.h), owner=self)
+
+    def match(self, node_pose, submap_pose, high, low, hist, gravity=(1, 0, 0, 0), min_score=0.55,
+              full=False, shard_index=0, num_shards=1):
+        node_pose, submap_pose = _f64(node_pose), _f64(submap_pose)
+        data, keep = make_node_data(high, low, hist, gravity)
+        res = MatchResult()
+        if full:
+            nq = np.ascontiguousarray(node_pose[3:])
+            sq = np.ascontiguousarray(submap_pose[3:])
+            _check(lib().hg_fcsm_match_full_submap(self.h, _p(nq), _p(sq), C.byref(data), min_score,
+                                                   shard_index, num_shards, C.byref(res)))
+        else:
+            _check(lib().hg_fcsm_match(self.h, _p(node_pose), _p(submap_pose), C.byref(data), min_score,
+                                       C.byref(res)))
+        del keep
+        return _result_dict(res)
+
+    def discrete_scans(self, wxy, wz, angular_window, node_pose, submap_pose, high, hist, gravity=(1, 0, 0, 0)):
+        node_pose, submap_pose = _f64(node_pose), _f64(submap_pose)
+        data, keep = make_node_data(high, np.zeros((0, 3)), hist, gravity)
+        S = C.c_int32(0)
+        _check(lib().hg_fcsm_discrete_scans(self.h, wxy, wz, angular_window, _p(node_pose), _p(submap_pose),
+                                            C.byref(data), 0, C.byref(S), None, None, None))
+        D = self.o["branch_and_bound_depth"]
+        n = data.num_high_resolution_points
+        poses = np.zeros((S.value, 7), np.float32)
+        rot = np.zeros(S.value, np.float32)
+        cells = np.zeros((S.value, D, n, 3), np.int32)
+        _check(lib().hg_fcsm_discrete_scans(self.h, wxy, wz, angular_window, _p(node_pose), _p(submap_pose),
+                                            C.byref(data), S.value, C.byref(S), _p(poses), _p(rot), _p(cells)))
+        del keep
+        return poses, rot, cells
+
+    def score_candidates(self, wxy, wz, angular_window, node_pose, submap_pose, high, hist, depth, cand,
+                         gravity=(1, 0, 0, 0)):
+        node_pose, submap_pose = _f64(node_pose), _f64(submap_pose)
+        data, keep = make_node_data(high, np.zeros((0, 3)), hist, gravity)
+        cand = _i32(cand).reshape(-1, 4)
+        sums = np.zeros(len(cand), np.int32)
+        scores = np.zeros(len(cand), np.float32)
+        ms = c_f(0)
+        _check(lib().hg_fcsm_score_candidates(self.h, wxy, wz, angular_window, _p(node_pose), _p(submap_pose),
+                                              C.byref(data), depth, len(cand), _p(cand), _p(sums), _p(scores),
+                                              C.byref(ms)))
+        del keep
+        return sums, scores, ms.value
+
+
+def low_resolution_scores(low_grid, pts, poses7):
+    pts = _f32(pts).reshape(-1, 3)
+    poses7 = _f32(poses7).reshape(-1, 7)
+    out = np.zeros(len(poses7), np.float32)
+    _check(lib().hg_low_resolution_scores(low_grid.h, _p(pts), len(pts), len(poses7), _p(poses7), _p(out)))
+    return out
+
+
+def constraints_run_batch(matchers, grids, low_grids, jobs, options, shard_index=0, num_shards=1):
+    """jobs: list of dicts(submap_index, full, node_pose, submap_pose, high, low, hist, gravity)."""
+    n = len(jobs)
+    arr = (ConstraintJob * n)()
+    keep = []
+    for i, j in enumerate(jobs):
+        arr[i].submap_index = j["submap_index"]
+        arr[i].match_full_submap = int(j.get("full", False))
+        for k in range(7):
+            arr[i].global_node_pose[k] = float(j["node_pose"][k])
+            arr[i].global_submap_pose[k] = float(j["submap_pose"][k])
+        d, ka = make_node_data(j["high"], j["low"], j["hist"], j.get("gravity", (1, 0, 0, 0)))
+        arr[i].data = d
+        keep.append(ka)
+    opt = ConstraintOptions()
+    opt.min_score = options.get("min_score", 0.55)
+    opt.global_localization_min_score = options.get("global_localization_min_score", 0.6)
+    w = options.get("occupied_space_weights", (5.0, 30.0))
+    opt.occupied_space_weights[0], opt.occupied_space_weights[1] = w
+    opt.translation_weight = options.get("translation_weight", 10.0)
+    opt.rotation_weight = options.get("rotation_weight", 1.0)
+    opt.only_optimize_yaw = int(options.get("only_optimize_yaw", False))
+    opt.max_num_iterations = options.get("max_num_iterations", 10)
+    opt.use_nonmonotonic_steps = int(options.get("use_nonmonotonic_steps", False))
+    res = (ConstraintResult * n)()
+    marr = (vp * len(matchers))(*[m.h for m in matchers])
+    _check(lib().hg_constraints_run_batch(marr, _grid_array(grids), _grid_array(low_grids), len(matchers), arr,
+                                          n, C.byref(opt), shard_index, num_shards, res))
+    out = []
+    for i in range(n):
+        r = res[i]
+        out.append(dict(found=int(r.found), score=float(r.score), pose=np.array(list(r.pose)),
+                        rotational_score=float(r.rotational_score),
+                        low_resolution_score=float(r.low_resolution_score),
+                        num_scored=int(r.num_candidates_scored)))
+    del keep
+    return out

@@ -1,0 +1,981 @@
+// Scan-to-grid residual + pose Jacobian kernels (the ceres::CostFunction::Evaluate
+// hot loop of CeresScanMatcher3D / OptimizingLocalTrajectoryBuilder).
+//
+// Reference behaviour reproduced (paths under
+// /root/reference/cartographer/mapping/internal/3d/scan_matching unless noted):
+//   tsdf_space_cost_function_3d.h:68-79 and the seven sibling functors  (hot loop)
+//   interpolated_grid.h:50-102            tricubic-Hermite occupancy lookup
+//   interpolated_tsdf.h:29-46, 71-116     weight-aware trilinear TSDF lookup
+//   interpolated_multi_resolution_tsdf.h:82-137  fine-to-coarse fall-through
+//   interpolated_tsdf.h:159-192           lower-voxel selection (float/double mix)
+//   transform/rigid_transform.h:191-196 + Eigen _transformVector  (point transform)
+//   transform/timestamped_transform.h:39-48  (two-pose interpolation; host side, pose_prep.h)
+//
+// Instead of carrying Jet<double,7|14> through every operation, each point
+// computes the value and its gradient with respect to the world point (three
+// partials), then applies the chain rule through d world / d q (3x4) and, for
+// two-pose functors, the per-block 4x4 matrices d q / d q0, d q / d q1. This is
+// the same derivative (forward mode is exact), evaluated with ~4x fewer FP64
+// operations. Interval / voxel selection replicates the reference's float steps
+// operation by operation (no FMA contraction) so that the same 2x2x2 stencil is
+// chosen.
+//
+// Layout: one thread per point, 256-thread CTAs, one CTA per tile of points of
+// one residual block. Voxels come from the brick table (hg_internal.cuh): one
+// 4-byte index load + up to eight voxel loads per pyramid level when the
+// stencil stays inside one 8^3 brick (67 % of points), eight index loads
+// otherwise. Outputs are written in Ceres' layout.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <memory>
+#include <mutex>
+
+#include "../../include/hg_dense_lm.h"
+#include "device_math.cuh"
+#include "host/pose_prep.h"
+
+namespace hg {
+
+struct BlockDev {
+  double t[3];
+  double q[4];
+  double ct0, ct1;
+  double m0[16];
+  double m1[16];
+  double scale;
+  long long point_offset;  // first point of the block in the concatenated cloud / outputs
+  int n;
+  int pad;
+};
+
+struct TileDev {
+  int block;
+  int start;  // first point of the tile inside its block
+};
+
+struct CostArgs {
+  GridDev grids[HG_MAX_PYRAMID_LEVELS];
+  int num_grids;
+  const float* points;
+  int stride;
+  const BlockDev* blocks;
+  const TileDev* tiles;
+  int tile_points;  // points per tile (multiple of 256)
+  double* r;
+  double* jt0;
+  double* jq0;
+  double* jt1;
+  double* jq1;
+  double* partials;  // normal-equation mode: [tile][P]
+};
+
+constexpr int kThreads = 256;
+
+// Lower-voxel selection for one axis (interpolated_tsdf.h:159-192).
+__device__ __forceinline__ void LowerVoxel(const float res, const double x, double* x1, double* x2,
+                                           int* index) {
+  const float xf = __double2float_rn(x);
+  const int i = CellIndex1(xf, res);
+  float c = __fmul_rn(static_cast<float>(i), res);
+  if (static_cast<double>(c) > x) c = __fsub_rn(c, res);
+  *x1 = static_cast<double>(c);
+  *x2 = static_cast<double>(__fadd_rn(c, res));
+  *index = CellIndex1(c, res);
+}
+
+// Fetches the 2x2x2 stencil at (ix..ix+1, iy..iy+1, iz..iz+1) in the reference's
+// corner order 111,112,121,122,211,212,221,222 (first digit x, last digit z).
+template <typename V, typename Load>
+__device__ __forceinline__ void FetchStencil(const BrickTable& t, const int ix, const int iy,
+                                             const int iz, V* v, Load load_default) {
+  if (((ix & 7) != 7) && ((iy & 7) != 7) && ((iz & 7) != 7)) {
+    const int id = BrickId(t, ix, iy, iz);
+    if (id < 0) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = load_default();
+      return;
+    }
+    const V* base = static_cast<const V*>(t.bricks) + static_cast<size_t>(id) * 512 + InBrick(ix, iy, iz);
+    v[0] = __ldg(base);
+    v[1] = __ldg(base + 64);
+    v[2] = __ldg(base + 8);
+    v[3] = __ldg(base + 72);
+    v[4] = __ldg(base + 1);
+    v[5] = __ldg(base + 65);
+    v[6] = __ldg(base + 9);
+    v[7] = __ldg(base + 73);
+    return;
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int x = ix + ((k >> 2) & 1), y = iy + ((k >> 1) & 1), z = iz + (k & 1);
+    const int id = BrickId(t, x, y, z);
+    v[k] = id < 0 ? load_default()
+                  : __ldg(static_cast<const V*>(t.bricks) + static_cast<size_t>(id) * 512 + InBrick(x, y, z));
+  }
+}
+
+struct ValueGrad {
+  double v, gx, gy, gz;  // value and gradient w.r.t. the world point
+};
+
+// interpolated_grid.h:50-102
+__device__ __forceinline__ ValueGrad LookupOccupancy(const GridDev& g, const double x, const double y,
+                                                     const double z) {
+  double x1, y1, z1, x2, y2, z2;
+  int ix, iy, iz;
+  LowerVoxel(g.resolution, x, &x1, &x2, &ix);
+  LowerVoxel(g.resolution, y, &y1, &y2, &iy);
+  LowerVoxel(g.resolution, z, &z1, &z2, &iz);
+  unsigned short raw[8];
+  FetchStencil<unsigned short>(g.table, ix, iy, iz, raw, [] { return static_cast<unsigned short>(0); });
+  double q[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) q[k] = static_cast<double>(Decode(g.a, raw[k]));
+  const double sx = 1.0 / (x2 - x1), sy = 1.0 / (y2 - y1), sz = 1.0 / (z2 - z1);
+  const double nx = (x - x1) / (x2 - x1), ny = (y - y1) / (y2 - y1), nz = (z - z1) / (z2 - z1);
+  const double nxx = nx * nx, nxxx = nx * nxx, nyy = ny * ny, nyyy = ny * nyy, nzz = nz * nz,
+               nzzz = nz * nzz;
+  // Derivatives of n^2, n^3 with respect to n.
+  const double dzz = 2.0 * nz, dzzz = 3.0 * nzz, dyy = 2.0 * ny, dyyy = 3.0 * nyy, dxx = 2.0 * nx,
+               dxxx = 3.0 * nxx;
+  // z stage: value and d/dnz.
+  double a[4], az[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const double qa = q[2 * k], qb = q[2 * k + 1];
+    a[k] = (qa - qb) * nzzz * 2. + (qb - qa) * nzz * 3. + qa;
+    az[k] = (qa - qb) * dzzz * 2. + (qb - qa) * dzz * 3.;
+  }
+  // y stage: pairs (a0, a1) -> x = 1 side, (a2, a3) -> x = 2 side.
+  double b[2], by[2], bz[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const double qa = a[2 * k], qb = a[2 * k + 1];
+    b[k] = (qa - qb) * nyyy * 2. + (qb - qa) * nyy * 3. + qa;
+    by[k] = (qa - qb) * dyyy * 2. + (qb - qa) * dyy * 3.;
+    const double za = az[2 * k], zb = az[2 * k + 1];
+    bz[k] = (za - zb) * nyyy * 2. + (zb - za) * nyy * 3. + za;
+  }
+  ValueGrad r;
+  r.v = (b[0] - b[1]) * nxxx * 2. + (b[1] - b[0]) * nxx * 3. + b[0];
+  r.gx = ((b[0] - b[1]) * dxxx * 2. + (b[1] - b[0]) * dxx * 3.) * sx;
+  r.gy = ((by[0] - by[1]) * nxxx * 2. + (by[1] - by[0]) * nxx * 3. + by[0]) * sy;
+  r.gz = ((bz[0] - bz[1]) * nxxx * 2. + (bz[1] - bz[0]) * nxx * 3. + bz[0]) * sz;
+  return r;
+}
+
+// interpolated_tsdf.h:29-46 on (value, partials) tuples. Copy branches pass the
+// upstream partials through; the both-unobserved branch is a constant.
+struct Q1 { double v, dz, w; };
+struct Q2 { double v, dy, dz, w; };
+
+__device__ __forceinline__ Q1 BlendZ(const double unknown, const double q1, const double q2,
+                                     const double w1, const double w2, const double n) {
+  Q1 r;
+  if (w1 == 0.0 && w2 == 0.0) {
+    r.v = unknown; r.dz = 0.0; r.w = 0.0;
+  } else if (w1 == 0.0) {
+    r.v = q2; r.dz = 0.0; r.w = w2;
+  } else if (w2 == 0.0) {
+    r.v = q1; r.dz = 0.0; r.w = w1;
+  } else {
+    r.v = (q2 - q1) * n + q1; r.dz = q2 - q1; r.w = w1 + w2;
+  }
+  return r;
+}
+__device__ __forceinline__ Q2 BlendY(const double unknown, const Q1& a, const Q1& b, const double n) {
+  Q2 r;
+  if (a.w == 0.0 && b.w == 0.0) {
+    r.v = unknown; r.dy = 0.0; r.dz = 0.0; r.w = 0.0;
+  } else if (a.w == 0.0) {
+    r.v = b.v; r.dy = 0.0; r.dz = b.dz; r.w = b.w;
+  } else if (b.w == 0.0) {
+    r.v = a.v; r.dy = 0.0; r.dz = a.dz; r.w = a.w;
+  } else {
+    r.v = (b.v - a.v) * n + a.v; r.dy = b.v - a.v; r.dz = (b.dz - a.dz) * n + a.dz; r.w = a.w + b.w;
+  }
+  return r;
+}
+
+// Shared tail of the TSDF lookups: 7 weight-aware blends, z then y then x.
+__device__ __forceinline__ ValueGrad BlendTsdf(const double unknown, const double* w, const double* q,
+                                               const double nx, const double ny, const double nz,
+                                               const double sx, const double sy, const double sz) {
+  const Q1 q11 = BlendZ(unknown, q[0], q[1], w[0], w[1], nz);
+  const Q1 q12 = BlendZ(unknown, q[2], q[3], w[2], w[3], nz);
+  const Q1 q21 = BlendZ(unknown, q[4], q[5], w[4], w[5], nz);
+  const Q1 q22 = BlendZ(unknown, q[6], q[7], w[6], w[7], nz);
+  const Q2 q1 = BlendY(unknown, q11, q12, ny);
+  const Q2 q2 = BlendY(unknown, q21, q22, ny);
+  ValueGrad r;
+  if (q1.w == 0.0 && q2.w == 0.0) {
+    r.v = unknown; r.gx = 0.0; r.gy = 0.0; r.gz = 0.0;
+  } else if (q1.w == 0.0) {
+    r.v = q2.v; r.gx = 0.0; r.gy = q2.dy * sy; r.gz = q2.dz * sz;
+  } else if (q2.w == 0.0) {
+    r.v = q1.v; r.gx = 0.0; r.gy = q1.dy * sy; r.gz = q1.dz * sz;
+  } else {
+    r.v = (q2.v - q1.v) * nx + q1.v;
+    r.gx = (q2.v - q1.v) * sx;
+    r.gy = ((q2.dy - q1.dy) * nx + q1.dy) * sy;
+    r.gz = ((q2.dz - q1.dz) * nx + q1.dz) * sz;
+  }
+  return r;
+}
+
+// One pyramid level. Returns false when the level must be skipped
+// (multi-resolution rule: any unobserved corner), true otherwise.
+template <bool MULTI>
+__device__ __forceinline__ bool LookupTsdfLevel(const GridDev& g, const double x, const double y,
+                                                const double z, ValueGrad* out) {
+  double x1, y1, z1, x2, y2, z2;
+  int ix, iy, iz;
+  LowerVoxel(g.resolution, x, &x1, &x2, &ix);
+  LowerVoxel(g.resolution, y, &y1, &y2, &iy);
+  LowerVoxel(g.resolution, z, &z1, &z2, &iz);
+  ushort2 raw[8];
+  FetchStencil<ushort2>(g.table, ix, iy, iz, raw, [] { return make_ushort2(0, 0); });
+  double w[8];
+  int zero = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    w[k] = static_cast<double>(Decode(g.b, raw[k].y));
+    zero += (w[k] == 0.0) ? 1 : 0;
+  }
+  if (MULTI) {
+    if (zero > 0) return false;  // interpolated_multi_resolution_tsdf.h:99-106
+  } else if (zero == 8) {       // interpolated_tsdf.h:87-90
+    out->v = static_cast<double>(g.min_tsd);
+    out->gx = out->gy = out->gz = 0.0;
+    return true;
+  }
+  double q[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) q[k] = static_cast<double>(Decode(g.a, raw[k].x));
+  const double sx = 1.0 / (x2 - x1), sy = 1.0 / (y2 - y1), sz = 1.0 / (z2 - z1);
+  const double nx = (x - x1) / (x2 - x1), ny = (y - y1) / (y2 - y1), nz = (z - z1) / (z2 - z1);
+  // interpolated_tsdf.h:34 hard-codes -0.3; the multi-resolution variant uses the level's minimum TSD.
+  const double unknown = MULTI ? static_cast<double>(g.min_tsd) : -0.3;
+  *out = BlendTsdf(unknown, w, q, nx, ny, nz, sx, sy, sz);
+  return true;
+}
+
+// LOOKUP: 0 occupancy, 1 TSDF, 2 multi-resolution TSDF. Returns the residual
+// and its gradient w.r.t. the world point, both already scaled.
+template <int LOOKUP>
+__device__ __forceinline__ ValueGrad Residual(const CostArgs& a, const double scale, const double x,
+                                              const double y, const double z) {
+  ValueGrad r;
+  if (LOOKUP == 0) {
+    const ValueGrad p = LookupOccupancy(a.grids[0], x, y, z);
+    r.v = scale * (1. - p.v);  // occupied_space_cost_function_3d.h:77
+    r.gx = -scale * p.gx;
+    r.gy = -scale * p.gy;
+    r.gz = -scale * p.gz;
+    return r;
+  }
+  ValueGrad t;
+  if (LOOKUP == 1) {
+    LookupTsdfLevel<false>(a.grids[0], x, y, z, &t);
+  } else {
+    bool found = false;
+    for (int l = 0; l < a.num_grids && !found; ++l) found = LookupTsdfLevel<true>(a.grids[l], x, y, z, &t);
+    if (!found) {  // interpolated_multi_resolution_tsdf.h:136
+      t.v = static_cast<double>(a.grids[0].min_tsd);
+      t.gx = t.gy = t.gz = 0.0;
+    }
+  }
+  r.v = scale * t.v;  // tsdf_space_cost_function_3d.h:76
+  r.gx = scale * t.gx;
+  r.gy = scale * t.gy;
+  r.gz = scale * t.gz;
+  return r;
+}
+
+// Number of Gauss-Newton outputs for n ambient parameters: upper triangle of
+// J'J, J'r, and sum r^2.
+__host__ __device__ constexpr int NumNormalTerms(int n) { return n * (n + 1) / 2 + n + 1; }
+
+template <int LOOKUP, bool TWO_POSE, bool NORMAL_EQ>
+__global__ void __launch_bounds__(kThreads) CostKernel(const CostArgs a) {
+  constexpr int NC = TWO_POSE ? 14 : 7;
+  constexpr int ROW = NC + 1;  // row of [J | r] staged for the normal-equation reduction
+  __shared__ BlockDev sb;
+  extern __shared__ double rows[];  // NORMAL_EQ only: kThreads x ROW
+
+  const TileDev tile = a.tiles[blockIdx.x];
+  {
+    // Cooperative copy of the block descriptor (352 bytes).
+    const int words = sizeof(BlockDev) / 8;
+    const double* src = reinterpret_cast<const double*>(a.blocks + tile.block);
+    double* dst = reinterpret_cast<double*>(&sb);
+    if (threadIdx.x < words) dst[threadIdx.x] = src[threadIdx.x];
+  }
+  __syncthreads();
+
+  constexpr int P = NumNormalTerms(NC);
+  double acc = 0.0;  // NORMAL_EQ: this thread's term (threadIdx.x < P), accumulated over sub-tiles
+
+  const int tile_end = min(sb.n, tile.start + a.tile_points);
+  for (int base = tile.start; base < tile_end; base += kThreads) {
+    const int i = base + threadIdx.x;
+    const bool active = i < tile_end;
+    double res = 0.0;
+    double J[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) J[c] = 0.0;
+    if (active) {
+      const long long gi = sb.point_offset + i;
+      const float* pp = a.points + gi * a.stride;
+      const double px = static_cast<double>(__ldg(pp)), py = static_cast<double>(__ldg(pp + 1)),
+                   pz = static_cast<double>(__ldg(pp + 2));
+      const double qw = sb.q[0], qx = sb.q[1], qy = sb.q[2], qz = sb.q[3];
+      // uv = 2 (u x p); world = p + w uv + u x uv + t
+      double uvx = qy * pz - qz * py, uvy = qz * px - qx * pz, uvz = qx * py - qy * px;
+      uvx += uvx; uvy += uvy; uvz += uvz;
+      const double wx = px + qw * uvx + (qy * uvz - qz * uvy) + sb.t[0];
+      const double wy = py + qw * uvy + (qz * uvx - qx * uvz) + sb.t[1];
+      const double wz = pz + qw * uvz + (qx * uvy - qy * uvx) + sb.t[2];
+
+      const ValueGrad v = Residual<LOOKUP>(a, sb.scale, wx, wy, wz);
+      res = v.v;
+
+      // a_k = grad . d world / d q_k
+      // d/dw = uv
+      const double aw = v.gx * uvx + v.gy * uvy + v.gz * uvz;
+      // d/du_k = w (2 e_k x p) + e_k x uv + u x (2 e_k x p)
+      // k = x: 2 e_x x p = (0, -2pz, 2py)
+      const double ex0 = 0.0, ex1 = -2.0 * pz, ex2 = 2.0 * py;
+      const double dxx_ = qw * ex0 + 0.0 + (qy * ex2 - qz * ex1);
+      const double dxy_ = qw * ex1 - uvz + (qz * ex0 - qx * ex2);
+      const double dxz_ = qw * ex2 + uvy + (qx * ex1 - qy * ex0);
+      const double ax = v.gx * dxx_ + v.gy * dxy_ + v.gz * dxz_;
+      // k = y: 2 e_y x p = (2pz, 0, -2px);  e_y x uv = (uvz, 0, -uvx)
+      const double ey0 = 2.0 * pz, ey1 = 0.0, ey2 = -2.0 * px;
+      const double dyx_ = qw * ey0 + uvz + (qy * ey2 - qz * ey1);
+      const double dyy_ = qw * ey1 + 0.0 + (qz * ey0 - qx * ey2);
+      const double dyz_ = qw * ey2 - uvx + (qx * ey1 - qy * ey0);
+      const double ay = v.gx * dyx_ + v.gy * dyy_ + v.gz * dyz_;
+      // k = z: 2 e_z x p = (-2py, 2px, 0);  e_z x uv = (-uvy, uvx, 0)
+      const double ez0 = -2.0 * py, ez1 = 2.0 * px, ez2 = 0.0;
+      const double dzx_ = qw * ez0 - uvy + (qy * ez2 - qz * ez1);
+      const double dzy_ = qw * ez1 + uvx + (qz * ez0 - qx * ez2);
+      const double dzz_ = qw * ez2 + 0.0 + (qx * ez1 - qy * ez0);
+      const double az = v.gx * dzx_ + v.gy * dzy_ + v.gz * dzz_;
+
+      if (!TWO_POSE) {
+        J[0] = v.gx; J[1] = v.gy; J[2] = v.gz;
+        J[3] = aw; J[4] = ax; J[5] = ay; J[6] = az;
+      } else {
+        J[0] = v.gx * sb.ct0; J[1] = v.gy * sb.ct0; J[2] = v.gz * sb.ct0;
+        J[7] = v.gx * sb.ct1; J[8] = v.gy * sb.ct1; J[9] = v.gz * sb.ct1;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          J[3 + j] = aw * sb.m0[j] + ax * sb.m0[4 + j] + ay * sb.m0[8 + j] + az * sb.m0[12 + j];
+          J[10 + j] = aw * sb.m1[j] + ax * sb.m1[4 + j] + ay * sb.m1[8 + j] + az * sb.m1[12 + j];
+        }
+      }
+
+      if (!NORMAL_EQ) {
+        if (a.r) a.r[gi] = res;
+        if (a.jt0) {
+          double* o = a.jt0 + gi * 3;
+          o[0] = J[0]; o[1] = J[1]; o[2] = J[2];
+        }
+        if (a.jq0) {
+          double2* o = reinterpret_cast<double2*>(a.jq0 + gi * 4);
+          o[0] = make_double2(J[3], J[4]);
+          o[1] = make_double2(J[5], J[6]);
+        }
+        if (TWO_POSE) {
+          if (a.jt1) {
+            double* o = a.jt1 + gi * 3;
+            o[0] = J[7]; o[1] = J[8]; o[2] = J[9];
+          }
+          if (a.jq1) {
+            double2* o = reinterpret_cast<double2*>(a.jq1 + gi * 4);
+            o[0] = make_double2(J[10], J[11]);
+            o[1] = make_double2(J[12], J[13]);
+          }
+        }
+      }
+    }
+    if (NORMAL_EQ) {
+      double* my = rows + threadIdx.x * ROW;
+#pragma unroll
+      for (int c = 0; c < NC; ++c) my[c] = J[c];
+      my[NC] = res;
+      __syncthreads();
+      if (threadIdx.x < P) {
+        // Term e: upper-triangle pairs (ca <= cb) first, then J'r, then r'r.
+        int ca, cb;
+        int e = threadIdx.x;
+        if (e < NC * (NC + 1) / 2) {
+          ca = 0;
+          while (e >= NC - ca) { e -= NC - ca; ++ca; }
+          cb = ca + e;
+        } else if (e < NC * (NC + 1) / 2 + NC) {
+          ca = e - NC * (NC + 1) / 2;
+          cb = NC;
+        } else {
+          ca = NC;
+          cb = NC;
+        }
+        double s = 0.0;
+        for (int rr = 0; rr < kThreads; ++rr) s += rows[rr * ROW + ca] * rows[rr * ROW + cb];
+        acc += s;
+      }
+      __syncthreads();
+    }
+  }
+  if (NORMAL_EQ && threadIdx.x < P) a.partials[static_cast<size_t>(blockIdx.x) * P + threadIdx.x] = acc;
+}
+
+// Sums the tile partials of each residual block in tile order (deterministic).
+__global__ void ReducePartialsKernel(const double* __restrict__ partials, const int* __restrict__ tile_begin,
+                                     const int P, double* __restrict__ out) {
+  const int b = blockIdx.x;
+  const int e = threadIdx.x;
+  if (e >= P) return;
+  double s = 0.0;
+  for (int t = tile_begin[b]; t < tile_begin[b + 1]; ++t) s += partials[static_cast<size_t>(t) * P + e];
+  out[static_cast<size_t>(b) * P + e] = s;
+}
+
+}  // namespace hg
+
+using namespace hg;
+
+// ---------------------------------------------------------------------------
+// Host side.
+
+struct hg_batch {
+  int device = 0;
+  int kind = 0;
+  int lookup = 0;  // 0 occupancy, 1 tsdf, 2 multires
+  bool two_pose = false;
+  int num_blocks = 0;
+  int stride = 3;
+  int64_t num_points = 0;
+  std::vector<int64_t> offsets;  // num_blocks + 1
+  std::vector<double> scales;
+  std::vector<double> ratios;
+  GridDev grids[HG_MAX_PYRAMID_LEVELS];
+  int num_grids = 0;
+  float* d_points = nullptr;
+  // Tile tables for 256-point (output) and 1024-point (normal equations) tiles.
+  TileDev* d_tiles_out = nullptr;
+  int num_tiles_out = 0;
+  TileDev* d_tiles_ne = nullptr;
+  int num_tiles_ne = 0;
+  int* d_ne_tile_begin = nullptr;  // num_blocks + 1
+  // Per-call scratch, guarded by 'mu' (calls on one handle serialise on it).
+  mutable std::mutex mu;
+  mutable BlockDev* d_blocks = nullptr;
+  mutable BlockDev* h_blocks = nullptr;  // pinned
+  mutable double* d_partials = nullptr;
+  mutable double* d_ne_out = nullptr;
+  mutable double* h_ne_out = nullptr;  // pinned
+  mutable double* d_out = nullptr;     // staging for host-pointer evaluate
+  mutable size_t d_out_doubles = 0;
+};
+
+struct hg_cost {
+  hg_batch* batch = nullptr;
+};
+
+namespace {
+
+constexpr int kTileOut = 256;
+constexpr int kTileNe = 1024;
+
+int LookupOfKind(int kind) {
+  if (kind == HG_COST_OCCUPIED_SPACE || kind == HG_COST_INTERPOLATED_OCCUPIED_SPACE) return 0;
+  if (kind == HG_COST_TSDF_SPACE || kind == HG_COST_INTERPOLATED_TSDF_SPACE ||
+      kind == HG_COST_INTERPOLATED_TSDF_PER_POINT_SPACE)
+    return 1;
+  return 2;
+}
+bool TwoPoseKind(int kind) {
+  return kind == HG_COST_INTERPOLATED_OCCUPIED_SPACE || kind == HG_COST_INTERPOLATED_TSDF_SPACE ||
+         kind == HG_COST_INTERPOLATED_TSDF_PER_POINT_SPACE ||
+         kind == HG_COST_INTERPOLATED_MULTI_RESOLUTION_TSDF_SPACE ||
+         kind == HG_COST_INTERPOLATED_MULTI_RESOLUTION_TSDF_PER_POINT_SPACE;
+}
+
+void BuildTiles(const std::vector<int64_t>& offsets, int tile_points, std::vector<TileDev>* tiles,
+                std::vector<int>* tile_begin) {
+  tiles->clear();
+  if (tile_begin) tile_begin->clear();
+  for (size_t b = 0; b + 1 < offsets.size(); ++b) {
+    if (tile_begin) tile_begin->push_back(static_cast<int>(tiles->size()));
+    const int64_t n = offsets[b + 1] - offsets[b];
+    for (int64_t s = 0; s < n; s += tile_points) tiles->push_back(TileDev{static_cast<int>(b), static_cast<int>(s)});
+  }
+  if (tile_begin) tile_begin->push_back(static_cast<int>(tiles->size()));
+}
+
+template <bool NE>
+int LaunchCost(const hg_batch* B, const CostArgs& args, int num_tiles, cudaStream_t stream) {
+  if (num_tiles == 0) return HG_OK;
+  const int NC = B->two_pose ? 14 : 7;
+  const size_t smem = NE ? static_cast<size_t>(kThreads) * (NC + 1) * sizeof(double) : 0;
+#define HG_LAUNCH(L, T)                                                                         \
+  do {                                                                                          \
+    if (NE && smem > 48 * 1024) {                                                               \
+      HG_CUDA(cudaFuncSetAttribute(CostKernel<L, T, NE>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                   static_cast<int>(smem)));                                    \
+    }                                                                                           \
+    CostKernel<L, T, NE><<<num_tiles, kThreads, smem, stream>>>(args);                          \
+  } while (0)
+  if (B->lookup == 0) {
+    if (B->two_pose) HG_LAUNCH(0, true); else HG_LAUNCH(0, false);
+  } else if (B->lookup == 1) {
+    if (B->two_pose) HG_LAUNCH(1, true); else HG_LAUNCH(1, false);
+  } else {
+    if (B->two_pose) HG_LAUNCH(2, true); else HG_LAUNCH(2, false);
+  }
+#undef HG_LAUNCH
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  return HG_OK;
+}
+
+// Fills the pinned block descriptors from host poses and copies them to the device.
+int PrepareBlocks(const hg_batch* B, const double* poses, int num_poses, const int32_t* i0,
+                  const int32_t* i1, cudaStream_t stream) {
+  for (int b = 0; b < B->num_blocks; ++b) {
+    const int a0 = i0 ? i0[b] : 0;
+    HG_REQUIRE(a0 >= 0 && a0 < num_poses, "pose_index0 out of range");
+    BlockPose p;
+    if (B->two_pose) {
+      HG_REQUIRE(i1 != nullptr, "pose_index1 is required for interpolated cost functions");
+      const int a1 = i1[b];
+      HG_REQUIRE(a1 >= 0 && a1 < num_poses, "pose_index1 out of range");
+      p = TwoPose(poses + 7 * a0, poses + 7 * a0 + 3, poses + 7 * a1, poses + 7 * a1 + 3, B->ratios[b]);
+    } else {
+      p = OnePose(poses + 7 * a0, poses + 7 * a0 + 3);
+    }
+    BlockDev& d = B->h_blocks[b];
+    std::memcpy(d.t, p.t, sizeof(d.t));
+    std::memcpy(d.q, p.q, sizeof(d.q));
+    d.ct0 = p.ct0;
+    d.ct1 = p.ct1;
+    std::memcpy(d.m0, p.m0, sizeof(d.m0));
+    std::memcpy(d.m1, p.m1, sizeof(d.m1));
+    d.scale = B->scales[b];
+    d.point_offset = B->offsets[b];
+    d.n = static_cast<int>(B->offsets[b + 1] - B->offsets[b]);
+    d.pad = 0;
+  }
+  HG_CUDA(cudaMemcpyAsync(B->d_blocks, B->h_blocks, sizeof(BlockDev) * B->num_blocks,
+                          cudaMemcpyHostToDevice, stream));
+  return HG_OK;
+}
+
+CostArgs BaseArgs(const hg_batch* B) {
+  CostArgs a;
+  std::memset(&a, 0, sizeof(a));
+  for (int i = 0; i < B->num_grids; ++i) a.grids[i] = B->grids[i];
+  a.num_grids = B->num_grids;
+  a.points = B->d_points;
+  a.stride = B->stride;
+  a.blocks = B->d_blocks;
+  return a;
+}
+
+}  // namespace
+
+extern "C" {
+
+int hg_batch_create(int kind, int num_blocks, const float* points, int stride_floats,
+                    const int64_t* cloud_offsets, const double* scaling_factors,
+                    const double* interpolation_ratios, const hg_grid* const* grids, int num_grids,
+                    hg_batch** out) {
+  HG_REQUIRE(out != nullptr && kind >= 0 && kind <= 7, "hg_batch_create: bad kind");
+  HG_REQUIRE(num_blocks >= 1 && cloud_offsets != nullptr && scaling_factors != nullptr,
+             "hg_batch_create: bad block arrays");
+  HG_REQUIRE(stride_floats >= 3, "hg_batch_create: stride must be >= 3 floats");
+  HG_REQUIRE(num_grids >= 1 && num_grids <= HG_MAX_PYRAMID_LEVELS && grids != nullptr,
+             "hg_batch_create: bad grid list");
+  const int lookup = LookupOfKind(kind);
+  HG_REQUIRE(lookup == 2 || num_grids == 1, "hg_batch_create: this functor takes exactly one grid");
+  float last_resolution = 0.f;
+  for (int i = 0; i < num_grids; ++i) {
+    HG_REQUIRE(grids[i] != nullptr, "hg_batch_create: null grid");
+    HG_REQUIRE((grids[i]->dev.kind == kGridProb) == (lookup == 0),
+               "hg_batch_create: grid type does not match the functor");
+    // interpolated_multi_resolution_tsdf.h:62-67 CHECKs ascending resolution.
+    HG_REQUIRE(last_resolution < grids[i]->dev.resolution,
+               "hg_batch_create: TSDF pyramid must be sorted by ascending resolution");
+    last_resolution = grids[i]->dev.resolution;
+  }
+  const bool two = TwoPoseKind(kind);
+  std::unique_ptr<hg_batch> B(new hg_batch);
+  HG_CUDA(cudaGetDevice(&B->device));
+  B->kind = kind;
+  B->lookup = lookup;
+  B->two_pose = two;
+  B->num_blocks = num_blocks;
+  B->stride = stride_floats;
+  B->offsets.assign(cloud_offsets, cloud_offsets + num_blocks + 1);
+  HG_REQUIRE(B->offsets[0] == 0, "hg_batch_create: cloud_offsets[0] must be 0");
+  for (int b = 0; b < num_blocks; ++b) {
+    HG_REQUIRE(B->offsets[b + 1] >= B->offsets[b], "hg_batch_create: cloud_offsets must be non-decreasing");
+    HG_REQUIRE(B->offsets[b + 1] - B->offsets[b] < (int64_t(1) << 31), "hg_batch_create: block too large");
+  }
+  B->num_points = B->offsets[num_blocks];
+  HG_REQUIRE(B->num_points == 0 || points != nullptr, "hg_batch_create: null points");
+  B->scales.assign(scaling_factors, scaling_factors + num_blocks);
+  if (two) {
+    HG_REQUIRE(interpolation_ratios != nullptr, "hg_batch_create: interpolation ratios required");
+    B->ratios.assign(interpolation_ratios, interpolation_ratios + num_blocks);
+  } else {
+    B->ratios.assign(num_blocks, 0.0);
+  }
+  for (int i = 0; i < num_grids; ++i) B->grids[i] = grids[i]->dev;
+  B->num_grids = num_grids;
+
+  const size_t point_bytes = static_cast<size_t>(std::max<int64_t>(B->num_points, 1)) * stride_floats * sizeof(float);
+  HG_CUDA(cudaMalloc(&B->d_points, point_bytes));
+  if (B->num_points > 0) {
+    HG_CUDA(cudaMemcpy(B->d_points, points, static_cast<size_t>(B->num_points) * stride_floats * sizeof(float),
+                       cudaMemcpyHostToDevice));
+  }
+  std::vector<TileDev> tiles;
+  std::vector<int> tile_begin;
+  BuildTiles(B->offsets, kTileOut, &tiles, nullptr);
+  B->num_tiles_out = static_cast<int>(tiles.size());
+  HG_CUDA(cudaMalloc(&B->d_tiles_out, sizeof(TileDev) * std::max<size_t>(tiles.size(), 1)));
+  if (!tiles.empty())
+    HG_CUDA(cudaMemcpy(B->d_tiles_out, tiles.data(), sizeof(TileDev) * tiles.size(), cudaMemcpyHostToDevice));
+  BuildTiles(B->offsets, kTileNe, &tiles, &tile_begin);
+  B->num_tiles_ne = static_cast<int>(tiles.size());
+  HG_CUDA(cudaMalloc(&B->d_tiles_ne, sizeof(TileDev) * std::max<size_t>(tiles.size(), 1)));
+  if (!tiles.empty())
+    HG_CUDA(cudaMemcpy(B->d_tiles_ne, tiles.data(), sizeof(TileDev) * tiles.size(), cudaMemcpyHostToDevice));
+  HG_CUDA(cudaMalloc(&B->d_ne_tile_begin, sizeof(int) * tile_begin.size()));
+  HG_CUDA(cudaMemcpy(B->d_ne_tile_begin, tile_begin.data(), sizeof(int) * tile_begin.size(), cudaMemcpyHostToDevice));
+
+  HG_CUDA(cudaMalloc(&B->d_blocks, sizeof(BlockDev) * num_blocks));
+  HG_CUDA(cudaMallocHost(&B->h_blocks, sizeof(BlockDev) * num_blocks));
+  const int P = NumNormalTerms(two ? 14 : 7);
+  HG_CUDA(cudaMalloc(&B->d_partials, sizeof(double) * P * std::max(B->num_tiles_ne, 1)));
+  HG_CUDA(cudaMalloc(&B->d_ne_out, sizeof(double) * P * num_blocks));
+  HG_CUDA(cudaMallocHost(&B->h_ne_out, sizeof(double) * P * num_blocks));
+  *out = B.release();
+  return HG_OK;
+}
+
+void hg_batch_destroy(hg_batch* B) {
+  if (B == nullptr) return;
+  cudaFree(B->d_points);
+  cudaFree(B->d_tiles_out);
+  cudaFree(B->d_tiles_ne);
+  cudaFree(B->d_ne_tile_begin);
+  cudaFree(B->d_blocks);
+  if (B->h_blocks) cudaFreeHost(B->h_blocks);
+  cudaFree(B->d_partials);
+  cudaFree(B->d_ne_out);
+  if (B->h_ne_out) cudaFreeHost(B->h_ne_out);
+  cudaFree(B->d_out);
+  delete B;
+}
+
+int64_t hg_batch_num_residuals(const hg_batch* B) { return B ? B->num_points : 0; }
+
+int hg_batch_update_points(hg_batch* B, const float* points, int stride_floats) {
+  HG_REQUIRE(B != nullptr && points != nullptr && stride_floats == B->stride,
+             "hg_batch_update_points: bad arguments");
+  std::lock_guard<std::mutex> lock(B->mu);
+  HG_CUDA(cudaMemcpy(B->d_points, points, static_cast<size_t>(B->num_points) * B->stride * sizeof(float),
+                     cudaMemcpyHostToDevice));
+  return HG_OK;
+}
+
+int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, const int32_t* pose_index0,
+                      const int32_t* pose_index1, int device_outputs, double* residuals, double* jt0,
+                      double* jq0, double* jt1, double* jq1, void* cuda_stream) {
+  HG_REQUIRE(B != nullptr && poses != nullptr && num_poses >= 1, "hg_batch_evaluate: bad arguments");
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  std::lock_guard<std::mutex> lock(B->mu);
+  int rc = PrepareBlocks(B, poses, num_poses, pose_index0, pose_index1, stream);
+  if (rc != HG_OK) return rc;
+  CostArgs a = BaseArgs(B);
+  a.tiles = B->d_tiles_out;
+  a.tile_points = kTileOut;
+  const int64_t N = B->num_points;
+  if (!B->two_pose) {
+    jt1 = nullptr;
+    jq1 = nullptr;
+  }
+  if (device_outputs) {
+    a.r = residuals; a.jt0 = jt0; a.jq0 = jq0; a.jt1 = jt1; a.jq1 = jq1;
+    return LaunchCost<false>(B, a, B->num_tiles_out, stream);
+  }
+  // Host outputs: stage in device memory, then one copy per requested array.
+  const size_t need = static_cast<size_t>(N) * 15;
+  if (B->d_out_doubles < need) {
+    if (B->d_out) cudaFree(B->d_out);
+    B->d_out = nullptr;
+    B->d_out_doubles = 0;
+    HG_CUDA(cudaMalloc(&B->d_out, std::max<size_t>(need, 1) * sizeof(double)));
+    B->d_out_doubles = need;
+  }
+  double* d = B->d_out;
+  a.r = residuals ? d : nullptr;
+  a.jt0 = jt0 ? d + N : nullptr;
+  a.jq0 = jq0 ? d + 4 * N : nullptr;
+  a.jt1 = jt1 ? d + 8 * N : nullptr;
+  a.jq1 = jq1 ? d + 11 * N : nullptr;
+  rc = LaunchCost<false>(B, a, B->num_tiles_out, stream);
+  if (rc != HG_OK) return rc;
+  if (residuals) HG_CUDA(cudaMemcpyAsync(residuals, a.r, sizeof(double) * N, cudaMemcpyDeviceToHost, stream));
+  if (jt0) HG_CUDA(cudaMemcpyAsync(jt0, a.jt0, sizeof(double) * N * 3, cudaMemcpyDeviceToHost, stream));
+  if (jq0) HG_CUDA(cudaMemcpyAsync(jq0, a.jq0, sizeof(double) * N * 4, cudaMemcpyDeviceToHost, stream));
+  if (jt1) HG_CUDA(cudaMemcpyAsync(jt1, a.jt1, sizeof(double) * N * 3, cudaMemcpyDeviceToHost, stream));
+  if (jq1) HG_CUDA(cudaMemcpyAsync(jq1, a.jq1, sizeof(double) * N * 4, cudaMemcpyDeviceToHost, stream));
+  HG_CUDA(cudaStreamSynchronize(stream));
+  return HG_OK;
+}
+
+int hg_batch_normal_equations(const hg_batch* B, const double* poses, int num_poses,
+                              const int32_t* pose_index0, const int32_t* pose_index1, double* JtJ,
+                              double* Jtr, double* cost_out) {
+  HG_REQUIRE(B != nullptr && poses != nullptr && num_poses >= 1, "hg_batch_normal_equations: bad arguments");
+  std::lock_guard<std::mutex> lock(B->mu);
+  cudaStream_t stream = nullptr;
+  int rc = PrepareBlocks(B, poses, num_poses, pose_index0, pose_index1, stream);
+  if (rc != HG_OK) return rc;
+  CostArgs a = BaseArgs(B);
+  a.tiles = B->d_tiles_ne;
+  a.tile_points = kTileNe;
+  a.partials = B->d_partials;
+  rc = LaunchCost<true>(B, a, B->num_tiles_ne, stream);
+  if (rc != HG_OK) return rc;
+  const int n = B->two_pose ? 14 : 7;
+  const int P = NumNormalTerms(n);
+  ReducePartialsKernel<<<B->num_blocks, 128, 0, stream>>>(B->d_partials, B->d_ne_tile_begin, P, B->d_ne_out);
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  HG_CUDA(cudaMemcpyAsync(B->h_ne_out, B->d_ne_out, sizeof(double) * P * B->num_blocks,
+                          cudaMemcpyDeviceToHost, stream));
+  HG_CUDA(cudaStreamSynchronize(stream));
+  for (int b = 0; b < B->num_blocks; ++b) {
+    const double* s = B->h_ne_out + static_cast<size_t>(b) * P;
+    int e = 0;
+    for (int ca = 0; ca < n; ++ca)
+      for (int cb = ca; cb < n; ++cb, ++e) {
+        if (JtJ) {
+          JtJ[(static_cast<size_t>(b) * n + ca) * n + cb] = s[e];
+          JtJ[(static_cast<size_t>(b) * n + cb) * n + ca] = s[e];
+        }
+      }
+    for (int c = 0; c < n; ++c, ++e)
+      if (Jtr) Jtr[static_cast<size_t>(b) * n + c] = s[e];
+    if (cost_out) cost_out[b] = 0.5 * s[e];
+  }
+  return HG_OK;
+}
+
+// ---- single residual block = batch of one ---------------------------------
+
+int hg_cost_create(int kind, double scaling_factor, const float* points, int stride_floats,
+                   int num_points, const hg_grid* const* grids, int num_grids,
+                   double interpolation_ratio, hg_cost** out) {
+  HG_REQUIRE(out != nullptr && num_points >= 0, "hg_cost_create: bad arguments");
+  const int64_t offsets[2] = {0, num_points};
+  hg_batch* B = nullptr;
+  const int rc = hg_batch_create(kind, 1, points, stride_floats, offsets, &scaling_factor,
+                                 &interpolation_ratio, grids, num_grids, &B);
+  if (rc != HG_OK) return rc;
+  hg_cost* c = new hg_cost;
+  c->batch = B;
+  *out = c;
+  return HG_OK;
+}
+
+void hg_cost_destroy(hg_cost* cost) {
+  if (cost == nullptr) return;
+  hg_batch_destroy(cost->batch);
+  delete cost;
+}
+
+int hg_cost_num_residuals(const hg_cost* cost) { return cost ? static_cast<int>(cost->batch->num_points) : 0; }
+int hg_cost_num_parameter_blocks(const hg_cost* cost) { return cost ? (cost->batch->two_pose ? 4 : 2) : 0; }
+
+static void GatherPoses(const hg_cost* cost, const double* const* parameters, double* poses) {
+  std::memcpy(poses, parameters[0], 3 * sizeof(double));
+  std::memcpy(poses + 3, parameters[1], 4 * sizeof(double));
+  if (cost->batch->two_pose) {
+    std::memcpy(poses + 7, parameters[2], 3 * sizeof(double));
+    std::memcpy(poses + 10, parameters[3], 4 * sizeof(double));
+  }
+}
+
+int hg_cost_evaluate(const hg_cost* cost, const double* const* parameters, double* residuals,
+                     double** jacobians) {
+  HG_REQUIRE(cost != nullptr && parameters != nullptr, "hg_cost_evaluate: bad arguments");
+  double poses[14];
+  GatherPoses(cost, parameters, poses);
+  const int32_t i0 = 0, i1 = 1;
+  const bool two = cost->batch->two_pose;
+  return hg_batch_evaluate(cost->batch, poses, two ? 2 : 1, &i0, &i1, 0, residuals,
+                           jacobians ? jacobians[0] : nullptr, jacobians ? jacobians[1] : nullptr,
+                           (jacobians && two) ? jacobians[2] : nullptr,
+                           (jacobians && two) ? jacobians[3] : nullptr, nullptr);
+}
+
+int hg_cost_evaluate_device(const hg_cost* cost, const double* const* parameters, double* d_residuals,
+                            double* const* d_jacobians, void* cuda_stream) {
+  HG_REQUIRE(cost != nullptr && parameters != nullptr, "hg_cost_evaluate_device: bad arguments");
+  double poses[14];
+  GatherPoses(cost, parameters, poses);
+  const int32_t i0 = 0, i1 = 1;
+  const bool two = cost->batch->two_pose;
+  return hg_batch_evaluate(cost->batch, poses, two ? 2 : 1, &i0, &i1, 1, d_residuals,
+                           d_jacobians ? d_jacobians[0] : nullptr, d_jacobians ? d_jacobians[1] : nullptr,
+                           (d_jacobians && two) ? d_jacobians[2] : nullptr,
+                           (d_jacobians && two) ? d_jacobians[3] : nullptr, cuda_stream);
+}
+
+int hg_cost_normal_equations(const hg_cost* cost, const double* const* parameters, double* JtJ,
+                             double* Jtr, double* cost_out) {
+  HG_REQUIRE(cost != nullptr && parameters != nullptr, "hg_cost_normal_equations: bad arguments");
+  double poses[14];
+  GatherPoses(cost, parameters, poses);
+  const int32_t i0 = 0, i1 = 1;
+  return hg_batch_normal_equations(cost->batch, poses, cost->batch->two_pose ? 2 : 1, &i0, &i1, JtJ, Jtr,
+                                   cost_out);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// CeresScanMatcher3D::Match on the dense LM.
+
+namespace {
+
+// Minimal cost-function shape for hg::DenseLmProblem.
+class LmCost {
+ public:
+  virtual ~LmCost() {}
+  virtual bool Evaluate(double const* const* parameters, double* residuals, double** jacobians) const = 0;
+  virtual int num_residuals() const = 0;
+};
+
+class GpuScanCost : public LmCost {
+ public:
+  explicit GpuScanCost(hg_cost* c) : c_(c) {}
+  ~GpuScanCost() override { hg_cost_destroy(c_); }
+  bool Evaluate(double const* const* p, double* r, double** J) const override {
+    return hg_cost_evaluate(c_, p, r, J) == HG_OK;
+  }
+  int num_residuals() const override { return hg_cost_num_residuals(c_); }
+
+ private:
+  hg_cost* c_;
+};
+
+// translation_delta_cost_functor_3d.h:31-45
+class TranslationDelta : public LmCost {
+ public:
+  TranslationDelta(double s, const double* target) : s_(s) { std::memcpy(t_, target, sizeof(t_)); }
+  bool Evaluate(double const* const* p, double* r, double** J) const override {
+    for (int k = 0; k < 3; ++k) r[k] = s_ * (p[0][k] - t_[k]);
+    if (J && J[0]) {
+      for (int k = 0; k < 9; ++k) J[0][k] = 0.0;
+      J[0][0] = J[0][4] = J[0][8] = s_;
+    }
+    return true;
+  }
+  int num_residuals() const override { return 3; }
+
+ private:
+  double s_, t_[3];
+};
+
+// rotation_delta_cost_functor_3d.h:35-54 with common/math.h:74-81: residual =
+// s * imag(target^-1 * q); linear in q, so the Jacobian is the constant matrix below.
+class RotationDelta : public LmCost {
+ public:
+  RotationDelta(double s, const double* target_wxyz) : s_(s) {
+    z_[0] = target_wxyz[0];
+    z_[1] = -target_wxyz[1];
+    z_[2] = -target_wxyz[2];
+    z_[3] = -target_wxyz[3];
+  }
+  bool Evaluate(double const* const* p, double* r, double** J) const override {
+    const double* w = p[0];
+    const double* z = z_;
+    r[0] = s_ * (z[0] * w[1] + z[1] * w[0] + z[2] * w[3] - z[3] * w[2]);
+    r[1] = s_ * (z[0] * w[2] - z[1] * w[3] + z[2] * w[0] + z[3] * w[1]);
+    r[2] = s_ * (z[0] * w[3] + z[1] * w[2] - z[2] * w[1] + z[3] * w[0]);
+    if (J && J[0]) {
+      const double M[12] = {z[1], z[0], -z[3], z[2], z[2], z[3], z[0], -z[1], z[3], -z[2], z[1], z[0]};
+      for (int k = 0; k < 12; ++k) J[0][k] = s_ * M[k];
+    }
+    return true;
+  }
+  int num_residuals() const override { return 3; }
+
+ private:
+  double s_, z_[4];
+};
+
+}  // namespace
+
+extern "C" int hg_scan_match(int num_clouds, const float* const* clouds, const int32_t* cloud_sizes,
+                             const hg_grid* const* grids, const double* occupied_space_weights,
+                             double translation_weight, double rotation_weight, int only_optimize_yaw,
+                             int max_num_iterations, int use_nonmonotonic_steps,
+                             const double* target_translation, const double* initial_pose,
+                             double* pose_out, double* summary_out) {
+  HG_REQUIRE(num_clouds >= 1 && clouds && cloud_sizes && grids && occupied_space_weights && initial_pose &&
+                 pose_out && target_translation,
+             "hg_scan_match: bad arguments");
+  double t[3] = {initial_pose[0], initial_pose[1], initial_pose[2]};
+  double q[4] = {initial_pose[3], initial_pose[4], initial_pose[5], initial_pose[6]};
+  hg::DenseLmProblem<LmCost> problem;
+  const int tb = problem.AddParameterBlock(t, 3, hg::LocalParameterization::kIdentity);
+  const int qb = problem.AddParameterBlock(q, 4, only_optimize_yaw ? hg::LocalParameterization::kYawOnlyQuaternion
+                                                                   : hg::LocalParameterization::kQuaternion);
+  std::vector<std::unique_ptr<LmCost>> owned;
+  for (int i = 0; i < num_clouds; ++i) {
+    HG_REQUIRE(occupied_space_weights[i] > 0., "hg_scan_match: occupied_space_weight must be > 0");
+    HG_REQUIRE(cloud_sizes[i] > 0, "hg_scan_match: empty point cloud");
+    // ceres_scan_matcher_3d.cc:138-139 / :149-150
+    const double scaling = occupied_space_weights[i] / std::sqrt(static_cast<double>(cloud_sizes[i]));
+    hg_cost* c = nullptr;
+    const int kind = grids[i]->dev.kind == kGridProb ? HG_COST_OCCUPIED_SPACE : HG_COST_TSDF_SPACE;
+    const int rc = hg_cost_create(kind, scaling, clouds[i], 3, cloud_sizes[i], &grids[i], 1, 0.0, &c);
+    if (rc != HG_OK) return rc;
+    owned.emplace_back(new GpuScanCost(c));
+    problem.AddResidualBlock(owned.back().get(), {tb, qb});
+  }
+  owned.emplace_back(new TranslationDelta(translation_weight, target_translation));
+  problem.AddResidualBlock(owned.back().get(), {tb});
+  owned.emplace_back(new RotationDelta(rotation_weight, initial_pose + 3));
+  problem.AddResidualBlock(owned.back().get(), {qb});
+  hg::LmOptions options;
+  options.max_num_iterations = max_num_iterations;
+  options.use_nonmonotonic_steps = use_nonmonotonic_steps != 0;
+  const hg::LmSummary s = problem.Solve(options);
+  if (s.termination == 4) {
+    SetError(std::string("hg_scan_match: evaluation failed: ") + hg_last_error());
+    return HG_ERR_CUDA;
+  }
+  for (int k = 0; k < 3; ++k) pose_out[k] = t[k];
+  for (int k = 0; k < 4; ++k) pose_out[3 + k] = q[k];
+  if (summary_out) {
+    summary_out[0] = s.initial_cost;
+    summary_out[1] = s.final_cost;
+    summary_out[2] = s.num_iterations;
+    summary_out[3] = s.num_successful_steps;
+    summary_out[4] = s.num_cost_evaluations;
+    summary_out[5] = s.num_jacobian_evaluations;
+  }
+  return HG_OK;
+}

@@ -1,0 +1,923 @@
+// FastCorrelativeScanMatcher3D on the device.
+//
+// Reference behaviour reproduced (paths under
+// /root/reference/cartographer/mapping/internal/3d/scan_matching unless noted):
+//   fast_correlative_scan_matcher_3d.cc:157-228  Match / MatchFullSubmap / MatchWithSearchParameters
+//   ... :230-274   DiscretizeScan (float point transform, GetCellIndex, low-resolution index fold)
+//   ... :276-326   GenerateDiscreteScans (angular step, yaw list, rotational prefilter, per-yaw pose)
+//   ... :328-398   lowest-resolution candidates, ScoreCandidates (integer gather sum, float score, sort)
+//   ... :400-471   GetPoseFromCandidate, BranchAndBound (DFS order, pruning, leaf gate)
+//   low_resolution_matcher.cc:24-69               leaf gate on the low-resolution grid
+//   rotational_scan_matcher.cc:121-185            RotateHistogram / MatchHistograms / Match
+//
+// Division of labour. The data-parallel parts run as CUDA kernels: rotating and
+// discretising every scan for every yaw (bit-exact float steps), scoring
+// candidates (integer gather sums over the uint8 pyramid), and the
+// low-resolution gate. The branch-and-bound itself is replayed on the host in
+// EXACTLY the reference's depth-first order over scores the GPU produced in
+// large speculative waves: whenever the replay needs the children of a node
+// that has not been scored yet, the pending part of the search frontier is
+// expanded level by level on the GPU (one launch per level over all pending
+// parents whose score still beats the current bound), so the replay consumes a
+// superset of what the reference's DFS scores and returns the same candidate,
+// including its tie-breaking. Integer sums are exact; float scores are computed
+// from them with the reference's expression, unfused.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <memory>
+
+#include "device_math.cuh"
+#include "host/float_geometry.h"
+
+namespace hg {
+namespace {
+
+using fgeom::Q4;
+using fgeom::Rigid;
+using fgeom::V3;
+
+// PrecomputationGrid3D::ToProbability (precomputation_grid_3d.h:33-36) applied to
+// sum / float(N) (fast_correlative_scan_matcher_3d.cc:380-382).
+inline float ScoreFromSum(const int sum, const int num_points) {
+  const float kMin = 0.1f;
+  const float kMax = 1.f - kMin;
+  const float value = sum / static_cast<float>(num_points);
+  return kMin + value * ((kMax - kMin) / 255.f);
+}
+
+// ---------------------------------------------------------------- kernels --
+
+// DiscretizeScan for every (scan, point): cells of the unique levels.
+// Layout: cells[(level * S + s) * N + i] as int3; level 0 = full resolution
+// (shared by depths 0..full_resolution_depth-1), level l >= 1 = reduction
+// exponent l.
+__global__ void __launch_bounds__(256) DiscretizeKernel(const float* __restrict__ points, const int N,
+                                                        const float* __restrict__ poses, const int S,
+                                                        const float resolution, const int num_low_levels,
+                                                        const int start_xy, const int start_z,
+                                                        int* __restrict__ cells) {
+  const int64_t gid = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (gid >= static_cast<int64_t>(S) * N) return;
+  const int s = static_cast<int>(gid / N);
+  const int i = static_cast<int>(gid - static_cast<int64_t>(s) * N);
+  const float* P = poses + 7 * s;
+  float wx, wy, wz;
+  RotateF(P[3], P[4], P[5], P[6], points[3 * i], points[3 * i + 1], points[3 * i + 2], &wx, &wy, &wz);
+  wx = __fadd_rn(wx, P[0]);
+  wy = __fadd_rn(wy, P[1]);
+  wz = __fadd_rn(wz, P[2]);
+  const int cx = CellIndex1(wx, resolution), cy = CellIndex1(wy, resolution), cz = CellIndex1(wz, resolution);
+  int* o = cells + gid * 3;
+  o[0] = cx; o[1] = cy; o[2] = cz;
+  const int64_t level_stride = static_cast<int64_t>(S) * N * 3;
+  for (int l = 1; l <= num_low_levels; ++l) {
+    o += level_stride;
+    o[0] = ((cx + start_xy) >> l) - (start_xy >> l);
+    o[1] = ((cy + start_xy) >> l) - (start_xy >> l);
+    o[2] = ((cz + start_z) >> l) - (start_z >> l);
+  }
+}
+
+// ScoreCandidates' inner loop: one warp per candidate, lanes stride over the
+// scan's points, integer gather from the uint8 level, warp-shuffle sum.
+__global__ void __launch_bounds__(256) ScoreKernel(const BrickTable level, const int* __restrict__ cells,
+                                                   const int N, const int reduction_exponent,
+                                                   const int4* __restrict__ candidates,
+                                                   const int64_t num_candidates, int* __restrict__ sums) {
+  const int64_t warp = (blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= num_candidates) return;
+  const int4 c = candidates[warp];
+  const int ox = c.y >> reduction_exponent, oy = c.z >> reduction_exponent, oz = c.w >> reduction_exponent;
+  const int* base = cells + static_cast<int64_t>(c.x) * N * 3;
+  int sum = 0;
+  for (int i = lane; i < N; i += 32) {
+    const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
+    sum += LoadU8(level, x + ox, y + oy, z + oz);
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+  if (lane == 0) sums[warp] = sum;
+}
+
+// LowResolutionMatcher closure: one thread per pose; the float accumulation is
+// sequential over the points in cloud order, exactly like the reference loop.
+__global__ void __launch_bounds__(128) LowResolutionKernel(const GridDev g, const float* __restrict__ points,
+                                                           const int N, const float* __restrict__ poses,
+                                                           const int64_t num_poses, float* __restrict__ scores) {
+  const int64_t p = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (p >= num_poses) return;
+  const float* P = poses + 7 * p;
+  const float tx = P[0], ty = P[1], tz = P[2], qw = P[3], qx = P[4], qy = P[5], qz = P[6];
+  float score = 0.f;
+  for (int i = 0; i < N; ++i) {
+    float wx, wy, wz;
+    RotateF(qw, qx, qy, qz, points[3 * i], points[3 * i + 1], points[3 * i + 2], &wx, &wy, &wz);
+    wx = __fadd_rn(wx, tx);
+    wy = __fadd_rn(wy, ty);
+    wz = __fadd_rn(wz, tz);
+    const int cx = CellIndex1(wx, g.resolution), cy = CellIndex1(wy, g.resolution),
+              cz = CellIndex1(wz, g.resolution);
+    if (g.kind == kGridProb) {
+      score = __fadd_rn(score, Decode(g.a, LoadU16(g.table, cx, cy, cz)));
+    } else {
+      const float tsd = Decode(g.a, LoadTsdf(g.table, cx, cy, cz).x);
+      score = __fadd_rn(score, __fsub_rn(1.f, fabsf(__fdiv_rn(tsd, g.max_tsd))));
+    }
+  }
+  scores[p] = __fdiv_rn(score, static_cast<float>(N));
+}
+
+// ------------------------------------------------------------- host parts --
+
+// rotational_scan_matcher.cc:121-143
+std::vector<float> RotateHistogram(const std::vector<float>& histogram, const float angle) {
+  const long size = static_cast<long>(histogram.size());
+  const float rotate_by_buckets = static_cast<float>((-angle * size) / M_PI);
+  int full_buckets = static_cast<int>(std::lround(rotate_by_buckets - 0.5f));
+  const float fraction = rotate_by_buckets - full_buckets;
+  while (full_buckets < 0) full_buckets += static_cast<int>(size);
+  std::vector<float> out(histogram.size());
+  for (long i = 0; i != size; ++i) {
+    const float h0 = histogram[(i + full_buckets) % size];
+    const float h1 = histogram[(i + 1 + full_buckets) % size];
+    out[i] = fraction * h1 + (1.f - fraction) * h0;
+  }
+  return out;
+}
+
+// rotational_scan_matcher.cc:106-117 (plain left-to-right float sums).
+float MatchHistograms(const std::vector<float>& submap, const std::vector<float>& scan) {
+  float scan_sq = 0.f, submap_sq = 0.f, dot = 0.f;
+  for (size_t i = 0; i < scan.size(); ++i) {
+    scan_sq += scan[i] * scan[i];
+    submap_sq += submap[i] * submap[i];
+    dot += submap[i] * scan[i];
+  }
+  const float normalization = std::sqrt(scan_sq) * std::sqrt(submap_sq);
+  if (normalization < 1e-3f) return 1.f;
+  return dot / normalization;
+}
+
+struct SearchParameters {
+  int wxy;
+  int wz;
+  double angular;
+};
+
+struct DeviceBuffer {
+  void* p = nullptr;
+  ~DeviceBuffer() {
+    if (p) cudaFree(p);
+  }
+  int Alloc(size_t bytes) {
+    if (p) cudaFree(p);
+    p = nullptr;
+    HG_CUDA(cudaMalloc(&p, std::max<size_t>(bytes, 16)));
+    return HG_OK;
+  }
+  template <typename T>
+  T* as() const { return static_cast<T*>(p); }
+};
+struct PinnedBuffer {
+  void* p = nullptr;
+  size_t cap = 0;
+  ~PinnedBuffer() {
+    if (p) cudaFreeHost(p);
+  }
+  int Reserve(size_t bytes) {
+    if (bytes <= cap) return HG_OK;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+    const size_t want = std::max<size_t>(bytes * 2, 1 << 16);
+    HG_CUDA(cudaMallocHost(&p, want));
+    cap = want;
+    return HG_OK;
+  }
+  template <typename T>
+  T* as() const { return static_cast<T*>(p); }
+};
+
+}  // namespace
+}  // namespace hg
+
+using namespace hg;
+
+struct hg_fcsm {
+  int device = 0;
+  hg_fcsm_options options;
+  const hg_grid* grid = nullptr;
+  const hg_grid* low_grid = nullptr;
+  hg_stack* stack = nullptr;
+  std::vector<float> histogram;
+  float resolution = 0.f;
+  int width_in_voxels = 0;
+};
+
+namespace {
+
+// The discrete scans of one search, resident on the device.
+struct ScanSet {
+  int S = 0;               // scans kept after the rotational prefilter
+  int N = 0;               // points per scan
+  int num_low_levels = 0;  // branch_and_bound_depth - full_resolution_depth (>= 0)
+  int frd = 0;             // min(full_resolution_depth, branch_and_bound_depth)
+  std::vector<Rigid> poses;
+  std::vector<float> rotational_scores;
+  std::vector<int> global_scan_index;  // index in the unsharded scan list
+  DeviceBuffer d_points, d_poses, d_cells;
+  // Cells of depth d live at level max(0, d - frd + 1).
+  const int* CellsOfDepth(int depth) const {
+    const int level = std::max(0, depth - frd + 1);
+    return d_cells.as<int>() + static_cast<int64_t>(level) * S * N * 3;
+  }
+};
+
+int GenerateDiscreteScans(const hg_fcsm* m, const SearchParameters& sp, const hg_node_data* data,
+                          const Rigid& node_pose, const Rigid& submap_pose, int shard_index, int num_shards,
+                          cudaStream_t stream, ScanSet* out) {
+  const int flavor = m->options.float_flavor;
+  const int N = data->num_high_resolution_points;
+  HG_REQUIRE(N > 0 && data->high_resolution_point_cloud != nullptr, "empty high resolution point cloud");
+  const float* pts = data->high_resolution_point_cloud;
+  const float resolution = m->resolution;
+  // :281-294
+  float max_scan_range = 3.f * resolution;
+  for (int i = 0; i < N; ++i) {
+    const float range = fgeom::Norm3(V3{pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]});
+    max_scan_range = std::max(range, max_scan_range);
+  }
+  const float kSafetyMargin = 1.f - 1e-2f;
+  const float angular_step_size =
+      kSafetyMargin * std::acos(1.f - (resolution * resolution) / (2.f * (max_scan_range * max_scan_range)));
+  const int angular_window_size = static_cast<int>(std::lround(sp.angular / angular_step_size));
+  std::vector<float> angles;
+  for (int rz = -angular_window_size; rz <= angular_window_size; ++rz) angles.push_back(rz * angular_step_size);
+  const Rigid node_to_submap = fgeom::RigidProduct(fgeom::RigidInverse(submap_pose), node_pose, flavor);
+  std::vector<float> scores;
+  if (m->options.use_rotational_scan_matcher) {
+    HG_REQUIRE(data->histogram_size == static_cast<int>(m->histogram.size()),
+               "rotational scan matcher histograms differ in size");
+    const double* ga = data->gravity_alignment;
+    const double n2 = (ga[1] * ga[1] + ga[2] * ga[2]) + (ga[3] * ga[3] + ga[0] * ga[0]);
+    const Q4 gravity_inverse{static_cast<float>(ga[0] / n2), static_cast<float>(-ga[1] / n2),
+                             static_cast<float>(-ga[2] / n2), static_cast<float>(-ga[3] / n2)};
+    const float initial_angle = fgeom::GetYaw(fgeom::Product(node_to_submap.q, gravity_inverse, flavor));
+    const std::vector<float> scan_hist(data->rotational_scan_matcher_histogram,
+                                       data->rotational_scan_matcher_histogram + data->histogram_size);
+    scores.reserve(angles.size());
+    for (const float angle : angles)
+      scores.push_back(MatchHistograms(m->histogram, RotateHistogram(scan_hist, initial_angle + angle)));
+  }
+  out->poses.clear();
+  out->rotational_scores.clear();
+  out->global_scan_index.clear();
+  int kept = 0;
+  for (size_t i = 0; i != angles.size(); ++i) {
+    if (m->options.use_rotational_scan_matcher &&
+        static_cast<double>(scores[i]) < m->options.min_rotational_score) {
+      continue;
+    }
+    const int global_index = kept++;
+    if (num_shards > 1 && (global_index % num_shards) != shard_index) continue;
+    const V3 angle_axis{0.f, 0.f, angles[i]};
+    const Q4 q = fgeom::Product(
+        fgeom::Product(fgeom::Inverse(submap_pose.q, flavor),
+                       fgeom::AngleAxisVectorToRotationQuaternion(angle_axis), flavor),
+        node_pose.q, flavor);
+    out->poses.push_back(Rigid{node_to_submap.t, q});
+    out->rotational_scores.push_back(m->options.use_rotational_scan_matcher ? scores[i] : 1.0f);
+    out->global_scan_index.push_back(global_index);
+  }
+  const int S = static_cast<int>(out->poses.size());
+  out->S = S;
+  out->N = N;
+  const int D = m->options.branch_and_bound_depth;
+  out->frd = std::min(m->options.full_resolution_depth, D);
+  out->num_low_levels = D - out->frd;
+  if (S == 0) return HG_OK;
+
+  int rc = out->d_points.Alloc(sizeof(float) * 3 * N);
+  if (rc != HG_OK) return rc;
+  rc = out->d_poses.Alloc(sizeof(float) * 7 * S);
+  if (rc != HG_OK) return rc;
+  const size_t cell_ints = static_cast<size_t>(1 + out->num_low_levels) * S * N * 3;
+  rc = out->d_cells.Alloc(sizeof(int) * cell_ints);
+  if (rc != HG_OK) return rc;
+  std::vector<float> flat(7 * static_cast<size_t>(S));
+  for (int s = 0; s < S; ++s) {
+    const Rigid& r = out->poses[s];
+    float* o = &flat[7 * s];
+    o[0] = r.t.x; o[1] = r.t.y; o[2] = r.t.z; o[3] = r.q.w; o[4] = r.q.x; o[5] = r.q.y; o[6] = r.q.z;
+  }
+  HG_CUDA(cudaMemcpyAsync(out->d_points.p, pts, sizeof(float) * 3 * N, cudaMemcpyHostToDevice, stream));
+  HG_CUDA(cudaMemcpyAsync(out->d_poses.p, flat.data(), sizeof(float) * flat.size(), cudaMemcpyHostToDevice, stream));
+  const int64_t total = static_cast<int64_t>(S) * N;
+  DiscretizeKernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
+      out->d_points.as<float>(), N, out->d_poses.as<float>(), S, resolution, out->num_low_levels, -sp.wxy,
+      -sp.wz, out->d_cells.as<int>());
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  HG_CUDA(cudaStreamSynchronize(stream));  // 'flat' goes out of scope
+  return HG_OK;
+}
+
+// Scores candidate records on the device; synchronous. 'kernel_ms' optional.
+struct Scorer {
+  const hg_fcsm* m;
+  const ScanSet* scans;
+  cudaStream_t stream;
+  DeviceBuffer d_cand, d_sums;
+  size_t cap = 0;
+  PinnedBuffer h_cand, h_sums;
+  int64_t total_scored = 0;
+  int launches = 0;
+
+  int Reserve(size_t n) {
+    int rc = h_cand.Reserve(n * sizeof(int4));
+    if (rc != HG_OK) return rc;
+    rc = h_sums.Reserve(n * sizeof(int));
+    if (rc != HG_OK) return rc;
+    if (n > cap) {
+      const size_t want = std::max<size_t>(n * 2, 4096);
+      rc = d_cand.Alloc(want * sizeof(int4));
+      if (rc != HG_OK) return rc;
+      rc = d_sums.Alloc(want * sizeof(int));
+      if (rc != HG_OK) return rc;
+      cap = want;
+    }
+    return HG_OK;
+  }
+  // Candidates must already be in h_cand (n records). Results land in h_sums.
+  int Run(int depth, size_t n, float* kernel_ms) {
+    if (n == 0) return HG_OK;
+    const int e = std::max(0, depth - m->options.full_resolution_depth + 1);
+    HG_CUDA(cudaMemcpyAsync(d_cand.p, h_cand.p, n * sizeof(int4), cudaMemcpyHostToDevice, stream));
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (kernel_ms) {
+      HG_CUDA(cudaEventCreate(&e0));
+      HG_CUDA(cudaEventCreate(&e1));
+      HG_CUDA(cudaEventRecord(e0, stream));
+    }
+    const int64_t threads = static_cast<int64_t>(n) * 32;
+    ScoreKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
+        m->stack->levels[depth].table, scans->CellsOfDepth(depth), scans->N, e, d_cand.as<int4>(),
+        static_cast<int64_t>(n), d_sums.as<int>());
+    CountLaunch();
+    HG_CUDA(cudaGetLastError());
+    if (kernel_ms) HG_CUDA(cudaEventRecord(e1, stream));
+    HG_CUDA(cudaMemcpyAsync(h_sums.p, d_sums.p, n * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    HG_CUDA(cudaStreamSynchronize(stream));
+    if (kernel_ms) {
+      float ms = 0.f;
+      HG_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+      *kernel_ms += ms;
+      cudaEventDestroy(e0);
+      cudaEventDestroy(e1);
+    }
+    total_scored += static_cast<int64_t>(n);
+    ++launches;
+    return HG_OK;
+  }
+};
+
+// ---- branch and bound --------------------------------------------------------
+
+struct Node {
+  int scan;
+  int ox, oy, oz;
+  float score;
+  float low_resolution_score;  // leaves only; NaN = not evaluated yet
+  int first_child;             // -1 = not expanded
+  int num_children;
+};
+
+struct BestCandidate {
+  int node = -1;
+  float score = -std::numeric_limits<float>::infinity();
+  float low_resolution_score = 0.f;
+};
+
+class BranchAndBoundSearch {
+ public:
+  BranchAndBoundSearch(const hg_fcsm* m, const SearchParameters& sp, const hg_node_data* data,
+                       const ScanSet* scans, cudaStream_t stream)
+      : m_(m), sp_(sp), data_(data), scans_(scans), stream_(stream) {
+    scorer_.m = m;
+    scorer_.scans = scans;
+    scorer_.stream = stream;
+  }
+
+  int Run(float min_score, BestCandidate* best_out) {
+    const int max_depth = m_->options.branch_and_bound_depth - 1;
+    int rc = ScoreLowestResolution(max_depth);
+    if (rc != HG_OK) return rc;
+    rc = UploadLowResolutionCloud();
+    if (rc != HG_OK) return rc;
+    failed_ = HG_OK;
+    const BestCandidate best = Search(0, static_cast<int>(top_count_), max_depth, min_score);
+    if (failed_ != HG_OK) return failed_;
+    *best_out = best;
+    return HG_OK;
+  }
+
+  const Node& node(int i) const { return nodes_[i]; }
+  int64_t scored() const { return scorer_.total_scored; }
+  int64_t visited() const { return visited_; }
+  int launches() const { return scorer_.launches + low_launches_; }
+
+  // GetPoseFromCandidate (:400-406): Translation(resolution * offset) * scan pose.
+  Rigid PoseOf(const Node& n) const {
+    const Rigid translation{V3{m_->resolution * static_cast<float>(n.ox), m_->resolution * static_cast<float>(n.oy),
+                               m_->resolution * static_cast<float>(n.oz)},
+                            Q4{1.f, 0.f, 0.f, 0.f}};
+    return fgeom::RigidProduct(translation, scans_->poses[n.scan], m_->options.float_flavor);
+  }
+
+ private:
+  // GenerateLowestResolutionCandidates + ScoreCandidates(max_depth) (:328-398).
+  int ScoreLowestResolution(int max_depth) {
+    const int step = 1 << max_depth;
+    std::vector<Node> generated;
+    for (int s = 0; s != scans_->S; ++s)
+      for (int z = -sp_.wz; z <= sp_.wz; z += step)
+        for (int y = -sp_.wxy; y <= sp_.wxy; y += step)
+          for (int x = -sp_.wxy; x <= sp_.wxy; x += step)
+            generated.push_back(Node{s, x, y, z, 0.f, std::numeric_limits<float>::quiet_NaN(), -1, 0});
+    const size_t n = generated.size();
+    int rc = scorer_.Reserve(n);
+    if (rc != HG_OK) return rc;
+    int4* hc = scorer_.h_cand.as<int4>();
+    for (size_t i = 0; i < n; ++i) hc[i] = make_int4(generated[i].scan, generated[i].ox, generated[i].oy, generated[i].oz);
+    rc = scorer_.Run(max_depth, n, nullptr);
+    if (rc != HG_OK) return rc;
+    const int* sums = scorer_.h_sums.as<int>();
+    for (size_t i = 0; i < n; ++i) generated[i].score = ScoreFromSum(sums[i], scans_->N);
+    visited_ += static_cast<int64_t>(n);
+    // std::sort(..., std::greater<Candidate3D>()) over the generation order: the
+    // comparator only looks at the score, so sorting (score, index) keys with
+    // the same algorithm yields the reference's permutation, ties included.
+    struct Key {
+      float score;
+      uint32_t index;
+    };
+    std::vector<Key> keys(n);
+    for (size_t i = 0; i < n; ++i) keys[i] = Key{generated[i].score, static_cast<uint32_t>(i)};
+    std::sort(keys.begin(), keys.end(), [](const Key& a, const Key& b) { return a.score > b.score; });
+    nodes_.resize(n);
+    for (size_t i = 0; i < n; ++i) nodes_[i] = generated[keys[i].index];
+    top_count_ = n;
+    return HG_OK;
+  }
+
+  int UploadLowResolutionCloud() {
+    const int n = data_->num_low_resolution_points;
+    if (n <= 0) return HG_OK;
+    int rc = d_low_points_.Alloc(sizeof(float) * 3 * n);
+    if (rc != HG_OK) return rc;
+    HG_CUDA(cudaMemcpyAsync(d_low_points_.p, data_->low_resolution_point_cloud, sizeof(float) * 3 * n,
+                            cudaMemcpyHostToDevice, stream_));
+    return HG_OK;
+  }
+
+  // BranchAndBound (:408-471) over nodes_[begin, begin + count) at 'depth'.
+  BestCandidate Search(int begin, int count, int depth, float min_score) {
+    BestCandidate unsuccessful;  // score -inf
+    if (failed_ != HG_OK) return unsuccessful;
+    if (depth == 0) {
+      for (int i = begin; i < begin + count; ++i) {
+        if (nodes_[i].score <= min_score) return unsuccessful;
+        if (std::isnan(nodes_[i].low_resolution_score)) {
+          failed_ = EvaluateLowResolution(begin, count, min_score);
+          if (failed_ != HG_OK) return unsuccessful;
+        }
+        const float low = nodes_[i].low_resolution_score;
+        if (static_cast<double>(low) >= m_->options.min_low_resolution_score) {
+          BestCandidate b;
+          b.node = i;
+          b.score = nodes_[i].score;
+          b.low_resolution_score = low;
+          return b;
+        }
+      }
+      return unsuccessful;
+    }
+    BestCandidate best;
+    best.score = min_score;
+    for (int i = begin; i < begin + count; ++i) {
+      if (nodes_[i].score <= min_score) break;
+      if (nodes_[i].first_child < 0) {
+        failed_ = Speculate(begin, count, i, depth, min_score, best.score);
+        if (failed_ != HG_OK) return unsuccessful;
+      }
+      visited_ += nodes_[i].num_children;
+      const BestCandidate sub = Search(nodes_[i].first_child, nodes_[i].num_children, depth - 1, best.score);
+      if (best.score < sub.score) best = sub;  // std::max(best, sub): the earlier one wins ties
+    }
+    return best;
+  }
+
+  // Children of a node in generation order (z outer, y, x inner; 'break' on the
+  // window edge, :441-461).
+  void AppendChildren(const Node& parent, int depth, std::vector<Node>* out) const {
+    const int half_width = 1 << (depth - 1);
+    for (int z : {0, half_width}) {
+      if (parent.oz + z > sp_.wz) break;
+      for (int y : {0, half_width}) {
+        if (parent.oy + y > sp_.wxy) break;
+        for (int x : {0, half_width}) {
+          if (parent.ox + x > sp_.wxy) break;
+          out->push_back(Node{parent.scan, parent.ox + x, parent.oy + y, parent.oz + z, 0.f,
+                              std::numeric_limits<float>::quiet_NaN(), -1, 0});
+        }
+      }
+    }
+  }
+
+  // Expands nodes_[trigger ..) of the sibling list [begin, begin+count) — every
+  // sibling the reference's loop will reach, i.e. with score > 'list_min_score'
+  // (the loop compares against its min_score argument, not the running best) —
+  // and then their descendants that still beat 'bound' (the running best),
+  // level by level, one scoring launch per level. The wave is truncated to a
+  // prefix in DFS order; the budget grows geometrically from call to call so
+  // that the first calls act as a quick dive that tightens the bound.
+  int Speculate(int begin, int count, int trigger, int depth, float list_min_score, float bound) {
+    std::vector<int> wave;
+    for (int i = trigger; i < begin + count; ++i) {
+      if (nodes_[i].score <= list_min_score) break;
+      if (nodes_[i].first_child < 0) wave.push_back(i);
+      if (static_cast<int64_t>(wave.size()) >= wave_budget_) break;
+    }
+    const int64_t budget = wave_budget_;
+    wave_budget_ = std::min<int64_t>(wave_budget_ * 8, int64_t(1) << 17);
+    std::vector<Node> children;
+    std::vector<int> child_begin;
+    for (int d = depth; d >= 1 && !wave.empty(); --d) {
+      children.clear();
+      child_begin.clear();
+      for (int p : wave) {
+        child_begin.push_back(static_cast<int>(children.size()));
+        AppendChildren(nodes_[p], d, &children);
+      }
+      child_begin.push_back(static_cast<int>(children.size()));
+      const size_t n = children.size();
+      int rc = scorer_.Reserve(n);
+      if (rc != HG_OK) return rc;
+      int4* hc = scorer_.h_cand.as<int4>();
+      for (size_t i = 0; i < n; ++i) hc[i] = make_int4(children[i].scan, children[i].ox, children[i].oy, children[i].oz);
+      rc = scorer_.Run(d - 1, n, nullptr);
+      if (rc != HG_OK) return rc;
+      const int* sums = scorer_.h_sums.as<int>();
+      for (size_t i = 0; i < n; ++i) children[i].score = ScoreFromSum(sums[i], scans_->N);
+      std::vector<int> next;
+      for (size_t w = 0; w < wave.size(); ++w) {
+        Node* first = children.data() + child_begin[w];
+        const int nc = child_begin[w + 1] - child_begin[w];
+        // std::sort on <= 16 elements is an insertion sort in libstdc++: stable
+        // in generation order for equal scores.
+        for (int a = 1; a < nc; ++a) {
+          const Node v = first[a];
+          int b = a - 1;
+          while (b >= 0 && v.score > first[b].score) {
+            first[b + 1] = first[b];
+            --b;
+          }
+          first[b + 1] = v;
+        }
+        const int at = static_cast<int>(nodes_.size());
+        nodes_.insert(nodes_.end(), first, first + nc);
+        nodes_[wave[w]].first_child = at;
+        nodes_[wave[w]].num_children = nc;
+        if (d - 1 >= 1) {
+          for (int c = 0; c < nc; ++c) {
+            if (nodes_[at + c].score <= bound) break;
+            if (static_cast<int64_t>(next.size()) < budget) next.push_back(at + c);
+          }
+        } else {
+          leaves_pending_.push_back(at);
+          leaves_pending_.push_back(nc);
+        }
+      }
+      wave.swap(next);
+    }
+    // Leaf gate for every freshly created leaf list.
+    int rc = HG_OK;
+    if (!leaves_pending_.empty()) {
+      std::vector<int> leaves;
+      for (size_t k = 0; k < leaves_pending_.size(); k += 2) {
+        for (int c = 0; c < leaves_pending_[k + 1]; ++c) {
+          const int idx = leaves_pending_[k] + c;
+          if (nodes_[idx].score <= bound) break;
+          leaves.push_back(idx);
+        }
+      }
+      leaves_pending_.clear();
+      rc = LowResolutionFor(leaves);
+    }
+    return rc;
+  }
+
+  int EvaluateLowResolution(int begin, int count, float min_score) {
+    std::vector<int> leaves;
+    for (int i = begin; i < begin + count; ++i) {
+      if (nodes_[i].score <= min_score) break;
+      if (std::isnan(nodes_[i].low_resolution_score)) leaves.push_back(i);
+    }
+    return LowResolutionFor(leaves);
+  }
+
+  int LowResolutionFor(const std::vector<int>& leaves) {
+    const size_t n = leaves.size();
+    if (n == 0) return HG_OK;
+    const int np = data_->num_low_resolution_points;
+    if (np <= 0) {
+      // score / points->size() with an empty cloud is 0 / 0 in the reference.
+      for (int idx : leaves) nodes_[idx].low_resolution_score = -std::numeric_limits<float>::infinity();
+      return HG_OK;
+    }
+    int rc = h_poses_.Reserve(n * 7 * sizeof(float));
+    if (rc != HG_OK) return rc;
+    rc = h_low_.Reserve(n * sizeof(float));
+    if (rc != HG_OK) return rc;
+    if (n > low_cap_) {
+      low_cap_ = std::max<size_t>(2 * n, 1024);
+      rc = d_low_poses_.Alloc(low_cap_ * 7 * sizeof(float));
+      if (rc != HG_OK) return rc;
+      rc = d_low_scores_.Alloc(low_cap_ * sizeof(float));
+      if (rc != HG_OK) return rc;
+    }
+    float* hp = h_poses_.as<float>();
+    for (size_t k = 0; k < n; ++k) {
+      const Rigid r = PoseOf(nodes_[leaves[k]]);
+      float* o = hp + 7 * k;
+      o[0] = r.t.x; o[1] = r.t.y; o[2] = r.t.z; o[3] = r.q.w; o[4] = r.q.x; o[5] = r.q.y; o[6] = r.q.z;
+    }
+    HG_CUDA(cudaMemcpyAsync(d_low_poses_.p, hp, n * 7 * sizeof(float), cudaMemcpyHostToDevice, stream_));
+    LowResolutionKernel<<<static_cast<unsigned>((n + 127) / 128), 128, 0, stream_>>>(
+        m_->low_grid->dev, d_low_points_.as<float>(), np, d_low_poses_.as<float>(), static_cast<int64_t>(n),
+        d_low_scores_.as<float>());
+    CountLaunch();
+    ++low_launches_;
+    HG_CUDA(cudaGetLastError());
+    HG_CUDA(cudaMemcpyAsync(h_low_.p, d_low_scores_.p, n * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+    HG_CUDA(cudaStreamSynchronize(stream_));
+    const float* hs = h_low_.as<float>();
+    for (size_t k = 0; k < n; ++k) nodes_[leaves[k]].low_resolution_score = hs[k];
+    return HG_OK;
+  }
+
+  const hg_fcsm* m_;
+  const SearchParameters sp_;
+  const hg_node_data* data_;
+  const ScanSet* scans_;
+  cudaStream_t stream_;
+  Scorer scorer_;
+  std::vector<Node> nodes_;
+  size_t top_count_ = 0;
+  int64_t visited_ = 0;
+  int64_t wave_budget_ = 8;
+  int failed_ = HG_OK;
+  int low_launches_ = 0;
+  std::vector<int> leaves_pending_;
+  DeviceBuffer d_low_points_, d_low_poses_, d_low_scores_;
+  size_t low_cap_ = 0;
+  PinnedBuffer h_poses_, h_low_;
+};
+
+Rigid ToRigidF(const double* t, const double* q) {
+  return Rigid{V3{static_cast<float>(t[0]), static_cast<float>(t[1]), static_cast<float>(t[2])},
+               Q4{static_cast<float>(q[0]), static_cast<float>(q[1]), static_cast<float>(q[2]),
+                  static_cast<float>(q[3])}};
+}
+
+// MatchWithSearchParameters (:202-228).
+int MatchWithSearchParameters(const hg_fcsm* m, const SearchParameters& sp, const Rigid& node_pose,
+                              const Rigid& submap_pose, const hg_node_data* data, float min_score,
+                              int shard_index, int num_shards, hg_match_result* result) {
+  std::memset(result, 0, sizeof(*result));
+  result->pose_rotation[0] = 1.0;
+  HG_CUDA(cudaSetDevice(m->device));
+  cudaStream_t stream = nullptr;
+  HG_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  struct StreamGuard {
+    cudaStream_t s;
+    ~StreamGuard() { cudaStreamDestroy(s); }
+  } guard{stream};
+  ScanSet scans;
+  int rc = GenerateDiscreteScans(m, sp, data, node_pose, submap_pose, shard_index, num_shards, stream, &scans);
+  if (rc != HG_OK) return rc;
+  result->num_discrete_scans = scans.S;
+  BranchAndBoundSearch search(m, sp, data, &scans, stream);
+  BestCandidate best;
+  rc = search.Run(min_score, &best);
+  if (rc != HG_OK) return rc;
+  result->num_candidates_scored = search.scored();
+  result->num_candidates_visited = search.visited();
+  result->num_score_launches = search.launches();
+  if (best.node >= 0 && best.score > min_score) {
+    const Node& n = search.node(best.node);
+    const Rigid pose = search.PoseOf(n);
+    result->found = 1;
+    result->score = best.score;
+    result->pose_translation[0] = pose.t.x;
+    result->pose_translation[1] = pose.t.y;
+    result->pose_translation[2] = pose.t.z;
+    result->pose_rotation[0] = pose.q.w;
+    result->pose_rotation[1] = pose.q.x;
+    result->pose_rotation[2] = pose.q.y;
+    result->pose_rotation[3] = pose.q.z;
+    result->rotational_score = scans.rotational_scores[n.scan];
+    result->low_resolution_score = best.low_resolution_score;
+    result->best_scan_index = scans.global_scan_index[n.scan];
+    result->best_offset[0] = n.ox;
+    result->best_offset[1] = n.oy;
+    result->best_offset[2] = n.oz;
+  }
+  return HG_OK;
+}
+
+int CheckNodeData(const hg_node_data* d) {
+  HG_REQUIRE(d != nullptr, "null node data");
+  HG_REQUIRE(d->num_high_resolution_points > 0 && d->high_resolution_point_cloud != nullptr,
+             "node data: empty high resolution point cloud");
+  HG_REQUIRE(d->num_low_resolution_points >= 0, "node data: negative low resolution point count");
+  HG_REQUIRE(d->num_low_resolution_points == 0 || d->low_resolution_point_cloud != nullptr,
+             "node data: null low resolution point cloud");
+  return HG_OK;
+}
+
+SearchParameters LocalWindow(const hg_fcsm* m) {
+  // :163-166 RoundToInt(double window / float resolution)
+  return SearchParameters{
+      static_cast<int>(std::lround(m->options.linear_xy_search_window / m->resolution)),
+      static_cast<int>(std::lround(m->options.linear_z_search_window / m->resolution)),
+      m->options.angular_search_window};
+}
+
+}  // namespace
+
+extern "C" {
+
+int hg_fcsm_create(const hg_grid* grid, const hg_grid* low_resolution_grid,
+                   const float* rotational_scan_matcher_histogram, int histogram_size,
+                   const hg_fcsm_options* options, hg_fcsm** out) {
+  HG_REQUIRE(grid && low_resolution_grid && options && out, "hg_fcsm_create: bad arguments");
+  HG_REQUIRE(histogram_size >= 0 && (histogram_size == 0 || rotational_scan_matcher_histogram != nullptr),
+             "hg_fcsm_create: bad histogram");
+  std::unique_ptr<hg_fcsm> m(new hg_fcsm);
+  m->device = grid->device;
+  m->options = *options;
+  m->grid = grid;
+  m->low_grid = low_resolution_grid;
+  m->resolution = grid->dev.resolution;
+  m->width_in_voxels = grid->grid_size;
+  if (histogram_size > 0)
+    m->histogram.assign(rotational_scan_matcher_histogram, rotational_scan_matcher_histogram + histogram_size);
+  const int rc = hg_stack_build(grid, options->branch_and_bound_depth, options->full_resolution_depth, &m->stack);
+  if (rc != HG_OK) return rc;
+  *out = m.release();
+  return HG_OK;
+}
+
+void hg_fcsm_destroy(hg_fcsm* m) {
+  if (m == nullptr) return;
+  hg_stack_destroy(m->stack);
+  delete m;
+}
+
+const hg_stack* hg_fcsm_stack(const hg_fcsm* m) { return m ? m->stack : nullptr; }
+
+int hg_fcsm_match(const hg_fcsm* m, const double* global_node_pose, const double* global_submap_pose,
+                  const hg_node_data* data, float min_score, hg_match_result* result) {
+  HG_REQUIRE(m && global_node_pose && global_submap_pose && result, "hg_fcsm_match: bad arguments");
+  const int rc = CheckNodeData(data);
+  if (rc != HG_OK) return rc;
+  return MatchWithSearchParameters(m, LocalWindow(m), ToRigidF(global_node_pose, global_node_pose + 3),
+                                   ToRigidF(global_submap_pose, global_submap_pose + 3), data, min_score, 0, 1,
+                                   result);
+}
+
+int hg_fcsm_match_full_submap(const hg_fcsm* m, const double* global_node_rotation,
+                              const double* global_submap_rotation, const hg_node_data* data, float min_score,
+                              int shard_index, int num_shards, hg_match_result* result) {
+  HG_REQUIRE(m && global_node_rotation && global_submap_rotation && result,
+             "hg_fcsm_match_full_submap: bad arguments");
+  HG_REQUIRE(num_shards >= 1 && shard_index >= 0 && shard_index < num_shards,
+             "hg_fcsm_match_full_submap: bad shard");
+  const int rc = CheckNodeData(data);
+  if (rc != HG_OK) return rc;
+  // :181-192
+  float max_point_distance = 0.f;
+  const float* pts = data->high_resolution_point_cloud;
+  for (int i = 0; i < data->num_high_resolution_points; ++i) {
+    max_point_distance = std::max(max_point_distance, fgeom::Norm3(V3{pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]}));
+  }
+  const int linear_window_size =
+      (m->width_in_voxels + 1) / 2 + static_cast<int>(std::lround(max_point_distance / m->resolution + 0.5f));
+  const SearchParameters sp{linear_window_size, linear_window_size, M_PI};
+  const double zero[3] = {0., 0., 0.};
+  return MatchWithSearchParameters(m, sp, ToRigidF(zero, global_node_rotation),
+                                   ToRigidF(zero, global_submap_rotation), data, min_score, shard_index,
+                                   num_shards, result);
+}
+
+int hg_fcsm_discrete_scans(const hg_fcsm* m, int wxy, int wz, double angular_search_window,
+                           const double* global_node_pose, const double* global_submap_pose,
+                           const hg_node_data* data, int max_scans, int32_t* num_scans, float* poses,
+                           float* rotational_scores, int32_t* cells) {
+  HG_REQUIRE(m && global_node_pose && global_submap_pose && num_scans, "hg_fcsm_discrete_scans: bad arguments");
+  int rc = CheckNodeData(data);
+  if (rc != HG_OK) return rc;
+  HG_CUDA(cudaSetDevice(m->device));
+  ScanSet scans;
+  const SearchParameters sp{wxy, wz, angular_search_window};
+  rc = GenerateDiscreteScans(m, sp, data, ToRigidF(global_node_pose, global_node_pose + 3),
+                             ToRigidF(global_submap_pose, global_submap_pose + 3), 0, 1, nullptr, &scans);
+  if (rc != HG_OK) return rc;
+  *num_scans = scans.S;
+  if (scans.S > max_scans || scans.S == 0) return HG_OK;
+  for (int s = 0; s < scans.S; ++s) {
+    if (poses) {
+      const Rigid& r = scans.poses[s];
+      float* o = poses + 7 * s;
+      o[0] = r.t.x; o[1] = r.t.y; o[2] = r.t.z; o[3] = r.q.w; o[4] = r.q.x; o[5] = r.q.y; o[6] = r.q.z;
+    }
+    if (rotational_scores) rotational_scores[s] = scans.rotational_scores[s];
+  }
+  if (cells) {
+    const int D = m->options.branch_and_bound_depth;
+    const size_t per = static_cast<size_t>(scans.N) * 3;
+    for (int d = 0; d < D; ++d) {
+      const int* src = scans.CellsOfDepth(d);
+      for (int s = 0; s < scans.S; ++s) {
+        HG_CUDA(cudaMemcpy(cells + (static_cast<size_t>(s) * D + d) * per, src + static_cast<size_t>(s) * per,
+                           per * sizeof(int), cudaMemcpyDeviceToHost));
+      }
+    }
+  }
+  return HG_OK;
+}
+
+int hg_fcsm_score_candidates(const hg_fcsm* m, int wxy, int wz, double angular_search_window,
+                             const double* global_node_pose, const double* global_submap_pose,
+                             const hg_node_data* data, int depth, int64_t num_candidates,
+                             const int32_t* candidates, int32_t* sums, float* scores, float* kernel_ms) {
+  HG_REQUIRE(m && global_node_pose && global_submap_pose && candidates && num_candidates >= 0,
+             "hg_fcsm_score_candidates: bad arguments");
+  HG_REQUIRE(depth >= 0 && depth < m->options.branch_and_bound_depth, "hg_fcsm_score_candidates: bad depth");
+  int rc = CheckNodeData(data);
+  if (rc != HG_OK) return rc;
+  HG_CUDA(cudaSetDevice(m->device));
+  ScanSet scans;
+  const SearchParameters sp{wxy, wz, angular_search_window};
+  rc = GenerateDiscreteScans(m, sp, data, ToRigidF(global_node_pose, global_node_pose + 3),
+                             ToRigidF(global_submap_pose, global_submap_pose + 3), 0, 1, nullptr, &scans);
+  if (rc != HG_OK) return rc;
+  for (int64_t i = 0; i < num_candidates; ++i) {
+    HG_REQUIRE(candidates[4 * i] >= 0 && candidates[4 * i] < scans.S, "hg_fcsm_score_candidates: scan index out of range");
+  }
+  Scorer scorer;
+  scorer.m = m;
+  scorer.scans = &scans;
+  scorer.stream = nullptr;
+  rc = scorer.Reserve(static_cast<size_t>(num_candidates));
+  if (rc != HG_OK) return rc;
+  std::memcpy(scorer.h_cand.p, candidates, static_cast<size_t>(num_candidates) * sizeof(int4));
+  if (kernel_ms) *kernel_ms = 0.f;
+  rc = scorer.Run(depth, static_cast<size_t>(num_candidates), kernel_ms);
+  if (rc != HG_OK) return rc;
+  const int* hs = scorer.h_sums.as<int>();
+  for (int64_t i = 0; i < num_candidates; ++i) {
+    if (sums) sums[i] = hs[i];
+    if (scores) scores[i] = ScoreFromSum(hs[i], scans.N);
+  }
+  return HG_OK;
+}
+
+int hg_low_resolution_scores(const hg_grid* low_resolution_grid, const float* points, int num_points,
+                             int64_t num_poses, const float* poses, float* scores) {
+  HG_REQUIRE(low_resolution_grid && points && num_points > 0 && num_poses >= 0 && poses && scores,
+             "hg_low_resolution_scores: bad arguments");
+  if (num_poses == 0) return HG_OK;
+  DeviceBuffer d_points, d_poses, d_scores;
+  int rc = d_points.Alloc(sizeof(float) * 3 * num_points);
+  if (rc != HG_OK) return rc;
+  rc = d_poses.Alloc(sizeof(float) * 7 * num_poses);
+  if (rc != HG_OK) return rc;
+  rc = d_scores.Alloc(sizeof(float) * num_poses);
+  if (rc != HG_OK) return rc;
+  HG_CUDA(cudaMemcpy(d_points.p, points, sizeof(float) * 3 * num_points, cudaMemcpyHostToDevice));
+  HG_CUDA(cudaMemcpy(d_poses.p, poses, sizeof(float) * 7 * num_poses, cudaMemcpyHostToDevice));
+  LowResolutionKernel<<<static_cast<unsigned>((num_poses + 127) / 128), 128>>>(
+      low_resolution_grid->dev, d_points.as<float>(), num_points, d_poses.as<float>(), num_poses,
+      d_scores.as<float>());
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  HG_CUDA(cudaMemcpy(scores, d_scores.p, sizeof(float) * num_poses, cudaMemcpyDeviceToHost));
+  return HG_OK;
+}
+
+}  // extern "C"

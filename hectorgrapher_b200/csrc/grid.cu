@@ -1,0 +1,274 @@
+// Submap storage on the device: HybridGrid / HybridGridTSDF flattened to a
+// brick table (see hg_internal.cuh), plus library-wide plumbing.
+//
+// Reference behaviour reproduced here:
+//   mapping/3d/hybrid_grid_base.h:263-279  value(): default outside the grid / absent bricks
+//   mapping/3d/hybrid_grid_base.h:40-43    z-major voxel order inside an 8^3 block
+//   mapping/3d/hybrid_grid.h:133-135, hybrid_grid_tsdf.h:105-113  value -> float
+//   mapping/value_conversion_tables.cc:29-51, 2d/tsd_value_converter.cc:22-32  decoding constants
+#include <algorithm>
+#include <cstring>
+#include <unordered_map>
+
+#include "device_math.cuh"
+
+namespace hg {
+
+static thread_local std::string t_error;
+std::atomic<uint64_t> g_kernel_launches{0};
+
+void SetError(const std::string& msg) { t_error = msg; }
+
+int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int voxel_bytes, BrickTable* table,
+                     void** d_index, void** d_bricks) {
+  const int64_t nb = static_cast<int64_t>(brick_coords.size() / 3);
+  int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+  for (int64_t i = 0; i < nb; ++i) {
+    for (int k = 0; k < 3; ++k) {
+      const int c = brick_coords[3 * i + k];
+      if (i == 0 || c < lo[k]) lo[k] = c;
+      if (i == 0 || c > hi[k]) hi[k] = c;
+    }
+  }
+  int64_t cells = 1;
+  for (int k = 0; k < 3; ++k) {
+    table->bmin[k] = lo[k];
+    table->bdim[k] = nb == 0 ? 1 : hi[k] - lo[k] + 1;
+    cells *= table->bdim[k];
+  }
+  if (cells > (int64_t(1) << 31)) {
+    SetError("brick index bounding box too large (" + std::to_string(cells) + " bricks)");
+    return HG_ERR_LIMIT;
+  }
+  std::vector<int32_t> index(static_cast<size_t>(cells), -1);
+  for (int64_t i = 0; i < nb; ++i) {
+    const int64_t bx = brick_coords[3 * i] - lo[0];
+    const int64_t by = brick_coords[3 * i + 1] - lo[1];
+    const int64_t bz = brick_coords[3 * i + 2] - lo[2];
+    index[(bz * table->bdim[1] + by) * table->bdim[0] + bx] = static_cast<int32_t>(i);
+  }
+  HG_CUDA(cudaMalloc(d_index, index.size() * sizeof(int32_t)));
+  HG_CUDA(cudaMemcpy(*d_index, index.data(), index.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  const size_t brick_bytes = static_cast<size_t>(std::max<int64_t>(nb, 1)) * 512 * voxel_bytes;
+  HG_CUDA(cudaMalloc(d_bricks, brick_bytes));
+  HG_CUDA(cudaMemset(*d_bricks, 0, brick_bytes));
+  table->index = static_cast<const int32_t*>(*d_index);
+  table->bricks = *d_bricks;
+  return HG_OK;
+}
+
+namespace {
+
+struct BrickKey {
+  int x, y, z;
+  bool operator==(const BrickKey& o) const { return x == o.x && y == o.y && z == o.z; }
+};
+struct BrickKeyHash {
+  size_t operator()(const BrickKey& k) const {
+    uint64_t h = static_cast<uint32_t>(k.x) * 0x9E3779B97F4A7C15ull;
+    h ^= (static_cast<uint64_t>(static_cast<uint32_t>(k.y)) + 0x7F4A7C15ull) * 0xC2B2AE3D27D4EB4Full;
+    h ^= (static_cast<uint64_t>(static_cast<uint32_t>(k.z)) + 0x165667B1ull) * 0xD6E8FEB86659FD93ull;
+    return static_cast<size_t>(h ^ (h >> 29));
+  }
+};
+
+// Smallest reference grid_size (64 << bits, bits >= 1) whose symmetric index
+// range contains every voxel (DynamicGrid::Grow, hybrid_grid_base.h:385-403).
+int DeriveGridSize(int64_t n, const int32_t* xyz) {
+  int bits = 1;
+  for (int64_t i = 0; i < 3 * n; ++i) {
+    while (bits < 8) {
+      const int half = (64 << bits) >> 1;
+      if (xyz[i] >= -half && xyz[i] < half) break;
+      ++bits;
+    }
+  }
+  return 64 << bits;
+}
+
+template <typename Voxel, typename MakeVoxel>
+int Flatten(int64_t n, const int32_t* xyz, MakeVoxel make, hg_grid* g) {
+  std::unordered_map<BrickKey, int32_t, BrickKeyHash> ids;
+  ids.reserve(static_cast<size_t>(n / 16 + 16));
+  std::vector<int32_t>& coords = g->brick_coords;
+  std::vector<int32_t> brick_of(static_cast<size_t>(n));
+  for (int64_t i = 0; i < n; ++i) {
+    const BrickKey k{xyz[3 * i] >> 3, xyz[3 * i + 1] >> 3, xyz[3 * i + 2] >> 3};
+    auto it = ids.find(k);
+    if (it == ids.end()) {
+      const int32_t id = static_cast<int32_t>(coords.size() / 3);
+      coords.push_back(k.x);
+      coords.push_back(k.y);
+      coords.push_back(k.z);
+      it = ids.emplace(k, id).first;
+    }
+    brick_of[static_cast<size_t>(i)] = it->second;
+  }
+  const int64_t nb = static_cast<int64_t>(coords.size() / 3);
+  std::vector<Voxel> bricks(static_cast<size_t>(std::max<int64_t>(nb, 1)) * 512);
+  std::memset(bricks.data(), 0, bricks.size() * sizeof(Voxel));
+  for (int64_t i = 0; i < n; ++i) {
+    const int x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+    bricks[static_cast<size_t>(brick_of[static_cast<size_t>(i)]) * 512 +
+           (((z & 7) << 6) | ((y & 7) << 3) | (x & 7))] = make(i);
+  }
+  const int rc = UploadBrickIndex(coords, sizeof(Voxel), &g->dev.table, &g->d_index, &g->d_bricks);
+  if (rc != HG_OK) return rc;
+  HG_CUDA(cudaMemcpy(g->d_bricks, bricks.data(), bricks.size() * sizeof(Voxel),
+                     cudaMemcpyHostToDevice));
+  g->num_bricks = nb;
+  g->num_voxels = n;
+  return HG_OK;
+}
+
+// Decoding constants computed exactly as SlowValueToBoundedFloat does.
+ValueDecode MakeDecode(float unknown, float lo, float hi) {
+  ValueDecode d;
+  const float scale = (hi - lo) / 32766.f;
+  d.scale = scale;
+  d.offset = lo - scale;
+  d.unknown = unknown;
+  return d;
+}
+
+__global__ void LookupKernel(const GridDev g, const int what, const int64_t n,
+                             const int32_t* __restrict__ xyz, float* __restrict__ out) {
+  const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (i >= n) return;
+  const int x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+  float v;
+  if (g.kind == kGridProb) {
+    v = Decode(g.a, LoadU16(g.table, x, y, z));
+  } else {
+    const ushort2 t = LoadTsdf(g.table, x, y, z);
+    v = what == 1 ? Decode(g.a, t.x) : Decode(g.b, t.y);
+  }
+  out[i] = v;
+}
+
+__global__ void CellIndexKernel(const float resolution, const int64_t n,
+                                const float* __restrict__ p, int32_t* __restrict__ out) {
+  const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (i >= 3 * n) return;
+  out[i] = CellIndex1(p[i], resolution);
+}
+
+}  // namespace
+}  // namespace hg
+
+using namespace hg;
+
+extern "C" {
+
+const char* hg_last_error(void) { return hg::t_error.c_str(); }
+const char* hg_version(void) { return "hectorgrapher_b200 0.1 (sm_100a)"; }
+uint64_t hg_kernel_launch_count(void) { return g_kernel_launches.load(); }
+
+int hg_set_device(int device) {
+  HG_CUDA(cudaSetDevice(device));
+  return HG_OK;
+}
+
+int hg_grid_upload_prob(float resolution, int grid_size, int64_t num_voxels, const int32_t* xyz,
+                        const uint16_t* values, hg_grid** out) {
+  HG_REQUIRE(out != nullptr && resolution > 0.f && num_voxels >= 0, "hg_grid_upload_prob: bad arguments");
+  HG_REQUIRE(num_voxels == 0 || (xyz != nullptr && values != nullptr), "hg_grid_upload_prob: null voxel arrays");
+  hg_grid* g = new hg_grid;
+  HG_CUDA(cudaGetDevice(&g->device));
+  g->dev.kind = kGridProb;
+  g->dev.resolution = resolution;
+  // probability_values.cc:56-60: unknown -> kMinProbability, range [0.1, 0.9].
+  const float kMin = 0.1f, kMax = 1.f - kMin;
+  g->dev.a = MakeDecode(kMin, kMin, kMax);
+  g->dev.b = MakeDecode(0.f, 0.f, 1.f);
+  g->dev.min_tsd = 0.f;
+  g->dev.max_tsd = 0.f;
+  g->grid_size = grid_size > 0 ? grid_size : DeriveGridSize(num_voxels, xyz);
+  const int rc = Flatten<uint16_t>(num_voxels, xyz, [values](int64_t i) { return values[i]; }, g);
+  if (rc != HG_OK) {
+    hg_grid_destroy(g);
+    return rc;
+  }
+  *out = g;
+  return HG_OK;
+}
+
+int hg_grid_upload_tsdf(float resolution, float relative_truncation_distance, float max_weight,
+                        int grid_size, int64_t num_voxels, const int32_t* xyz,
+                        const uint16_t* tsd_values, const uint16_t* weight_values, hg_grid** out) {
+  HG_REQUIRE(out != nullptr && resolution > 0.f && num_voxels >= 0 && max_weight > 0.f &&
+                 relative_truncation_distance > 0.f,
+             "hg_grid_upload_tsdf: bad arguments");
+  HG_REQUIRE(num_voxels == 0 || (xyz != nullptr && tsd_values != nullptr && weight_values != nullptr),
+             "hg_grid_upload_tsdf: null voxel arrays");
+  hg_grid* g = new hg_grid;
+  HG_CUDA(cudaGetDevice(&g->device));
+  g->dev.kind = kGridTsdf;
+  g->dev.resolution = resolution;
+  g->relative_truncation_distance = relative_truncation_distance;
+  g->max_weight = max_weight;
+  // hybrid_grid_tsdf.h:65-67, tsd_value_converter.cc:22-32.
+  const float max_tsd = relative_truncation_distance * resolution;
+  const float min_tsd = -max_tsd;
+  g->dev.max_tsd = max_tsd;
+  g->dev.min_tsd = min_tsd;
+  g->dev.a = MakeDecode(min_tsd, min_tsd, max_tsd);
+  g->dev.b = MakeDecode(0.f, 0.f, max_weight);
+  g->grid_size = grid_size > 0 ? grid_size : DeriveGridSize(num_voxels, xyz);
+  const int rc = Flatten<ushort2>(
+      num_voxels, xyz,
+      [tsd_values, weight_values](int64_t i) { return make_ushort2(tsd_values[i], weight_values[i]); }, g);
+  if (rc != HG_OK) {
+    hg_grid_destroy(g);
+    return rc;
+  }
+  *out = g;
+  return HG_OK;
+}
+
+void hg_grid_destroy(hg_grid* grid) {
+  if (grid == nullptr) return;
+  if (grid->d_index) cudaFree(grid->d_index);
+  if (grid->d_bricks) cudaFree(grid->d_bricks);
+  delete grid;
+}
+
+int hg_grid_size(const hg_grid* grid) { return grid ? grid->grid_size : 0; }
+int64_t hg_grid_num_bricks(const hg_grid* grid) { return grid ? grid->num_bricks : 0; }
+
+int hg_grid_lookup(const hg_grid* grid, int what, int64_t n, const int32_t* xyz, float* out) {
+  HG_REQUIRE(grid != nullptr && n >= 0 && what >= 0 && what <= 2, "hg_grid_lookup: bad arguments");
+  HG_REQUIRE((grid->dev.kind == kGridProb) == (what == 0), "hg_grid_lookup: 'what' does not match the grid type");
+  if (n == 0) return HG_OK;
+  int32_t* d_xyz = nullptr;
+  float* d_out = nullptr;
+  HG_CUDA(cudaMalloc(&d_xyz, n * 3 * sizeof(int32_t)));
+  HG_CUDA(cudaMalloc(&d_out, n * sizeof(float)));
+  HG_CUDA(cudaMemcpy(d_xyz, xyz, n * 3 * sizeof(int32_t), cudaMemcpyHostToDevice));
+  LookupKernel<<<static_cast<unsigned>((n + 255) / 256), 256>>>(grid->dev, what, n, d_xyz, d_out);
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  HG_CUDA(cudaMemcpy(out, d_out, n * sizeof(float), cudaMemcpyDeviceToHost));
+  cudaFree(d_xyz);
+  cudaFree(d_out);
+  return HG_OK;
+}
+
+int hg_get_cell_index(float resolution, int64_t n, const float* points_xyz, int32_t* out_xyz) {
+  HG_REQUIRE(n >= 0 && resolution > 0.f, "hg_get_cell_index: bad arguments");
+  if (n == 0) return HG_OK;
+  float* d_p = nullptr;
+  int32_t* d_o = nullptr;
+  HG_CUDA(cudaMalloc(&d_p, n * 3 * sizeof(float)));
+  HG_CUDA(cudaMalloc(&d_o, n * 3 * sizeof(int32_t)));
+  HG_CUDA(cudaMemcpy(d_p, points_xyz, n * 3 * sizeof(float), cudaMemcpyHostToDevice));
+  CellIndexKernel<<<static_cast<unsigned>((3 * n + 255) / 256), 256>>>(resolution, n, d_p, d_o);
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  HG_CUDA(cudaMemcpy(out_xyz, d_o, n * 3 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  cudaFree(d_p);
+  cudaFree(d_o);
+  return HG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,114 @@
+// Internal declarations shared by the .cu files of libhg_b200.so.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/hg_b200.h"
+
+namespace hg {
+
+// ---------------------------------------------------------------- errors --
+void SetError(const std::string& msg);
+extern std::atomic<uint64_t> g_kernel_launches;
+inline void CountLaunch(uint64_t n = 1) { g_kernel_launches.fetch_add(n, std::memory_order_relaxed); }
+
+#define HG_CUDA(expr)                                                                     \
+  do {                                                                                    \
+    cudaError_t _e = (expr);                                                              \
+    if (_e != cudaSuccess) {                                                              \
+      ::hg::SetError(std::string(#expr) + ": " + cudaGetErrorString(_e) + " (" + __FILE__ + \
+                     ":" + std::to_string(__LINE__) + ")");                               \
+      return HG_ERR_CUDA;                                                                 \
+    }                                                                                     \
+  } while (0)
+
+#define HG_REQUIRE(cond, msg)          \
+  do {                                 \
+    if (!(cond)) {                     \
+      ::hg::SetError(msg);             \
+      return HG_ERR_INVALID;           \
+    }                                  \
+  } while (0)
+
+// ----------------------------------------------------------- brick table --
+// A sparse voxel grid flattened for the device:
+//   * 'index' is a dense int32 array over the bounding box of occupied 8x8x8
+//     bricks (brick coordinates = voxel index >> 3, arithmetic shift), holding
+//     the brick id or -1;
+//   * 'bricks' holds brick id * 512 voxels, z-major inside a brick exactly like
+//     the reference's FlatGrid (hybrid_grid_base.h:40-43): ((z*8)+y)*8+x.
+// Voxel type: uint16 (probability), ushort2 {tsd, weight} (TSDF), uint8 (precomputation).
+struct BrickTable {
+  const int32_t* index;  // device
+  const void* bricks;    // device
+  int bmin[3];           // brick-coordinate origin of 'index'
+  int bdim[3];           // extent of 'index' in bricks
+};
+
+// Value decoding constants: value -> float is v' = v & 0x7FFF; v' == 0 ? unknown
+// : v' * scale + offset with offset = lo - scale (value_conversion_tables.cc:29-51),
+// evaluated with separate round-to-nearest multiply and add.
+struct ValueDecode {
+  float scale;
+  float offset;
+  float unknown;
+};
+
+enum GridKind { kGridProb = 0, kGridTsdf = 1 };
+
+struct GridDev {
+  BrickTable table;
+  float resolution;
+  ValueDecode a;  // probability, or tsd
+  ValueDecode b;  // weight (TSDF only)
+  float min_tsd;  // -max_tsd
+  float max_tsd;
+  int kind;
+};
+
+}  // namespace hg
+
+// Host-side handle definitions (opaque in the public header).
+struct hg_grid {
+  hg::GridDev dev;
+  int device = 0;
+  int grid_size = 0;
+  int64_t num_bricks = 0;
+  int64_t num_voxels = 0;
+  float relative_truncation_distance = 0.f;
+  float max_weight = 0.f;
+  void* d_index = nullptr;
+  void* d_bricks = nullptr;
+  // Host copy of the brick coordinates (brick id -> brick coords), used to
+  // derive the precomputation levels' brick sets.
+  std::vector<int32_t> brick_coords;
+};
+
+struct hg_stack_level {
+  hg::BrickTable table;
+  void* d_index = nullptr;
+  void* d_bricks = nullptr;
+  int64_t num_bricks = 0;
+  bool owns_index = true;
+};
+
+struct hg_stack {
+  int device = 0;
+  float resolution = 0.f;
+  int full_resolution_depth = 0;
+  std::vector<hg_stack_level> levels;
+  std::vector<std::vector<int32_t>> brick_coords;  // per level: brick id -> brick coordinates
+};
+
+namespace hg {
+// Builds a device brick table (index + zeroed bricks of 'voxel_bytes' each)
+// from a list of brick coordinates. Used by grid upload and the pyramid.
+int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int voxel_bytes, BrickTable* table,
+                     void** d_index, void** d_bricks);
+}  // namespace hg

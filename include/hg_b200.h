@@ -1,0 +1,338 @@
+/* hg_b200.h — C-ABI of libhg_b200.so: HectorGrapher's 3D scan-matching hot path on B200.
+ *
+ * Plain C: opaque handles, plain pointers and sizes, int status codes. No Eigen,
+ * Ceres, protobuf or torch types cross this boundary. Every entry point names
+ * the reference interface it stands in for (paths relative to
+ * /root/reference/cartographer). Host-side C++ adapters that present the
+ * reference's own class surfaces on top of these calls are in
+ * hectorgrapher_b200/csrc/host/ and INTEGRATION.md shows the reference-side glue.
+ *
+ * Conventions
+ *  - status: 0 = HG_OK; anything else is an error, hg_last_error() gives the text
+ *    (thread-local). The reference aborts on these conditions (CHECK / LOG(FATAL)).
+ *  - poses are double t[3], q[4] with q = (w, x, y, z)
+ *    (mapping/internal/optimization/ceres_pose.h:49-50).
+ *  - point clouds are float xyz with a stride in floats: 3 = sensor::PointCloud,
+ *    4 = sensor::TimedPointCloud (sensor/rangefinder_point.h:31-40).
+ *  - voxel lists are the content of the grid wire formats
+ *    (mapping/proto/3d/hybrid_grid.proto:19-29, hybrid_grid_tsdf.proto:19-32):
+ *    int32 xyz triples + raw uint16 values exactly as HybridGrid stores them.
+ *  - all handles may be used from several host threads for evaluate / match
+ *    calls (each call takes its own stream and scratch); create / destroy are
+ *    not to race with use of the same handle.
+ *  - there is no CPU fallback: without a CUDA device every compute entry point
+ *    fails with HG_ERR_CUDA.
+ */
+#ifndef HG_B200_H_
+#define HG_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HG_OK 0
+#define HG_ERR_INVALID 1
+#define HG_ERR_CUDA 2
+#define HG_ERR_LIMIT 3
+
+typedef struct hg_grid hg_grid;   /* HybridGrid or HybridGridTSDF as a device brick table */
+typedef struct hg_cost hg_cost;   /* one scan-to-grid residual block (a ceres::CostFunction) */
+typedef struct hg_batch hg_batch; /* many residual blocks evaluated in one launch */
+typedef struct hg_stack hg_stack; /* PrecomputationGridStack3D */
+typedef struct hg_fcsm hg_fcsm;   /* FastCorrelativeScanMatcher3D */
+
+/* Text of the last error on this thread ("" if none). */
+const char* hg_last_error(void);
+/* Library version string. */
+const char* hg_version(void);
+/* Number of kernels this library has launched in this process (all threads). */
+uint64_t hg_kernel_launch_count(void);
+/* Selects the CUDA device used by subsequent calls on this thread (cudaSetDevice). */
+int hg_set_device(int device);
+
+/* ---------------------------------------------------------------- grids -- */
+
+/* mapping/3d/hybrid_grid.h:46-140 (HybridGrid). 'grid_size' is the reference
+ * grid's current grid_size() (64 << bits, hybrid_grid_base.h:260); it only
+ * feeds MatchFullSubmap's window (fast_correlative_scan_matcher_3d.cc:186-188).
+ * Pass 0 to have it derived the way DynamicGrid grows (smallest 64<<bits, bits>=1,
+ * containing every voxel). Values may carry the update marker (bit 15). */
+int hg_grid_upload_prob(float resolution, int grid_size, int64_t num_voxels, const int32_t* xyz,
+                        const uint16_t* values, hg_grid** out);
+
+/* mapping/3d/hybrid_grid_tsdf.h:57-150 (HybridGridTSDF). max_tsd =
+ * relative_truncation_distance * resolution (hybrid_grid_tsdf.h:65-67). */
+int hg_grid_upload_tsdf(float resolution, float relative_truncation_distance, float max_weight,
+                        int grid_size, int64_t num_voxels, const int32_t* xyz,
+                        const uint16_t* tsd_values, const uint16_t* weight_values, hg_grid** out);
+
+void hg_grid_destroy(hg_grid* grid);
+int hg_grid_size(const hg_grid* grid);
+int64_t hg_grid_num_bricks(const hg_grid* grid);
+
+/* HybridGrid::GetProbability / HybridGridTSDF::GetTSD / GetWeight at integer
+ * cells (hybrid_grid.h:133-135, hybrid_grid_tsdf.h:105-113), evaluated on the
+ * device. what: 0 probability, 1 tsd, 2 weight. Host pointers. */
+int hg_grid_lookup(const hg_grid* grid, int what, int64_t n, const int32_t* xyz, float* out);
+
+/* HybridGridBase::GetCellIndex (hybrid_grid_base.h:428-433) on the device. */
+int hg_get_cell_index(float resolution, int64_t n, const float* points_xyz, int32_t* out_xyz);
+
+/* ------------------------------------------------------- cost functions -- */
+
+/* The eight functors of mapping/internal/3d/scan_matching/, numbered in the
+ * order SURVEY.md lists them. */
+#define HG_COST_OCCUPIED_SPACE 0                                   /* occupied_space_cost_function_3d.h:36-80 */
+#define HG_COST_INTERPOLATED_OCCUPIED_SPACE 1                      /* interpolated_occupied_space_cost_function_3d.h:37-92 */
+#define HG_COST_TSDF_SPACE 2                                       /* tsdf_space_cost_function_3d.h:37-79 */
+#define HG_COST_INTERPOLATED_TSDF_SPACE 3                          /* interpolated_tsdf_space_cost_function_3d.h:38-96 */
+#define HG_COST_INTERPOLATED_TSDF_PER_POINT_SPACE 4                /* interpolated_tsdf_per_point_space_cost_function_3d.h:38-74 */
+#define HG_COST_MULTI_RESOLUTION_TSDF_SPACE 5                      /* multi_resolution_tsdf_space_cost_function_3d.h:37-82 */
+#define HG_COST_INTERPOLATED_MULTI_RESOLUTION_TSDF_SPACE 6         /* interpolated_multi_resolution_tsdf_space_cost_function_3d.h:38-98 */
+#define HG_COST_INTERPOLATED_MULTI_RESOLUTION_TSDF_PER_POINT_SPACE 7 /* ..._per_point_space_cost_function_3d.h:38-74 */
+
+#define HG_MAX_PYRAMID_LEVELS 4
+
+/* XxxCostFunction3D::CreateAutoDiffCostFunction(scaling_factor, point_cloud,
+ * grid | grid pyramid [, interpolation_ratio]). The cloud is copied to the
+ * device. 'grids': one HybridGrid (kinds 0-1), one HybridGridTSDF (2-4) or an
+ * ascending-resolution TSDF pyramid (5-7; the handles are copied, unlike
+ * interpolated_multi_resolution_tsdf.h:218 which keeps a reference). One-pose
+ * kinds have parameter blocks {3,4}; interpolated kinds {3,4,3,4}. */
+int hg_cost_create(int kind, double scaling_factor, const float* points, int stride_floats,
+                   int num_points, const hg_grid* const* grids, int num_grids,
+                   double interpolation_ratio, hg_cost** out);
+void hg_cost_destroy(hg_cost* cost);
+int hg_cost_num_residuals(const hg_cost* cost);
+int hg_cost_num_parameter_blocks(const hg_cost* cost);
+
+/* ceres::CostFunction::Evaluate(parameters, residuals, jacobians) (Ceres 1.13
+ * cost_function.h; instantiations at tsdf_space_cost_function_3d.h:40-44 and
+ * interpolated_tsdf_space_cost_function_3d.h:45-51). All pointers are HOST
+ * memory. 'jacobians' may be NULL, and any jacobians[b] may be NULL (block held
+ * constant). jacobians[b] is row-major num_residuals x block_size. */
+int hg_cost_evaluate(const hg_cost* cost, const double* const* parameters, double* residuals,
+                     double** jacobians);
+
+/* Same evaluation with DEVICE output pointers (any may be NULL); parameters
+ * stay host pointers. Runs on 'cuda_stream' (a cudaStream_t, NULL = default
+ * stream) and does not synchronise. */
+int hg_cost_evaluate_device(const hg_cost* cost, const double* const* parameters,
+                            double* d_residuals, double* const* d_jacobians, void* cuda_stream);
+
+/* Gauss-Newton terms of one block without materialising the Jacobian:
+ * JtJ (n x n row-major, n = 7 or 14 ambient parameters in block order),
+ * Jtr (n) and cost = 1/2 sum r^2. Host outputs. */
+int hg_cost_normal_equations(const hg_cost* cost, const double* const* parameters, double* JtJ,
+                             double* Jtr, double* cost_out);
+
+/* ------------------------------------------------- batched cost blocks -- */
+
+/* Many residual blocks of one kind over the same grids, evaluated by one
+ * launch: the shape OptimizingLocalTrajectoryBuilder builds per optimisation
+ * (mapping/internal/3d/optimizing_local_trajectory_builder.cc:323-511: one
+ * block per scan of the window, each on one or two of the window's control
+ * poses). Block b uses points[cloud_offsets[b] .. cloud_offsets[b+1]). */
+int hg_batch_create(int kind, int num_blocks, const float* points, int stride_floats,
+                    const int64_t* cloud_offsets /* num_blocks + 1 */,
+                    const double* scaling_factors /* num_blocks */,
+                    const double* interpolation_ratios /* num_blocks, may be NULL for one-pose */,
+                    const hg_grid* const* grids, int num_grids, hg_batch** out);
+void hg_batch_destroy(hg_batch* batch);
+int64_t hg_batch_num_residuals(const hg_batch* batch);
+/* Replaces the point clouds (same offsets) from HOST memory: the next window of scans. */
+int hg_batch_update_points(hg_batch* batch, const float* points, int stride_floats);
+
+/* Evaluates every block. 'poses' = num_poses x 7 doubles (t3, q4) on the host;
+ * block b uses pose_index0[b] (and pose_index1[b] for interpolated kinds).
+ * Outputs are HOST pointers when device_outputs == 0, DEVICE pointers otherwise;
+ * any may be NULL. Layout: residuals[N]; jt0[N x 3], jq0[N x 4], jt1[N x 3],
+ * jq1[N x 4] row-major, so the slice of block b is exactly the jacobians[k]
+ * array Ceres would pass for it. */
+int hg_batch_evaluate(const hg_batch* batch, const double* poses, int num_poses,
+                      const int32_t* pose_index0, const int32_t* pose_index1, int device_outputs,
+                      double* residuals, double* jt0, double* jq0, double* jt1, double* jq1,
+                      void* cuda_stream);
+
+/* Per-block Gauss-Newton terms for the whole batch: JtJ[num_blocks x n x n],
+ * Jtr[num_blocks x n], cost[num_blocks]; n = 7 (one-pose) or 14. Host outputs. */
+int hg_batch_normal_equations(const hg_batch* batch, const double* poses, int num_poses,
+                              const int32_t* pose_index0, const int32_t* pose_index1, double* JtJ,
+                              double* Jtr, double* cost_out);
+
+/* CeresScanMatcher3D::Match (ceres_scan_matcher_3d.cc:72-95, problem set-up
+ * :120-172) for num_clouds (cloud, grid) pairs: occupied-space / TSDF blocks
+ * scaled by occupied_space_weights[i] / sqrt(N_i), plus the translation and
+ * rotation delta priors (translation_delta_cost_functor_3d.h:31-45,
+ * rotation_delta_cost_functor_3d.h:35-54). Solved with the dense LM of
+ * include/hg_dense_lm.h over the GPU cost blocks. pose arrays are t3 q4.
+ * summary_out (may be NULL): initial cost, final cost, iterations, successful
+ * steps, cost evaluations, jacobian evaluations. */
+int hg_scan_match(int num_clouds, const float* const* clouds, const int32_t* cloud_sizes,
+                  const hg_grid* const* grids, const double* occupied_space_weights,
+                  double translation_weight, double rotation_weight, int only_optimize_yaw,
+                  int max_num_iterations, int use_nonmonotonic_steps,
+                  const double* target_translation, const double* initial_pose, double* pose_out,
+                  double* summary_out);
+
+/* ------------------------------------------------ precomputation grids -- */
+
+/* PrecomputationGridStack3D(grid, options)
+ * (fast_correlative_scan_matcher_3d.cc:60-94; ConvertToPrecomputationGrid and
+ * PrecomputeGrid, precomputation_grid_3d.cc:49-97). */
+int hg_stack_build(const hg_grid* grid, int branch_and_bound_depth, int full_resolution_depth,
+                   hg_stack** out);
+void hg_stack_destroy(hg_stack* stack);
+int hg_stack_depth(const hg_stack* stack);
+/* PrecomputationGrid3D::value at integer cells of level 'depth' (host pointers). */
+int hg_stack_lookup(const hg_stack* stack, int depth, int64_t n, const int32_t* xyz, uint8_t* out);
+/* Number of non-zero voxels of a level, and their export (for parity checks). */
+int64_t hg_stack_num_nonzero(const hg_stack* stack, int depth);
+int hg_stack_export(const hg_stack* stack, int depth, int64_t capacity, int32_t* xyz,
+                    uint8_t* values, int64_t* num_written);
+
+/* ------------------------------------------ fast correlative scan matcher -- */
+
+/* proto::FastCorrelativeScanMatcherOptions3D
+ * (fast_correlative_scan_matcher_3d.cc:37-58, configuration_files/pose_graph.lua:40-49). */
+typedef struct hg_fcsm_options {
+  int32_t branch_and_bound_depth;
+  int32_t full_resolution_depth;
+  int32_t use_rotational_scan_matcher;
+  double min_rotational_score;
+  double min_low_resolution_score;
+  double linear_xy_search_window;
+  double linear_z_search_window;
+  double angular_search_window;
+  /* 1 = Eigen's SSE2 float summation orders (x86-64 reference build), 0 = Eigen's
+   * generic scalar code. See DESIGN.md "float flavors". */
+  int32_t float_flavor;
+} hg_fcsm_options;
+
+/* TrajectoryNode::Data fields the matcher reads (mapping/trajectory_node.h:45-62). */
+typedef struct hg_node_data {
+  const float* high_resolution_point_cloud; /* xyz, stride 3 */
+  int32_t num_high_resolution_points;
+  const float* low_resolution_point_cloud;
+  int32_t num_low_resolution_points;
+  const float* rotational_scan_matcher_histogram;
+  int32_t histogram_size;
+  double gravity_alignment[4]; /* (w, x, y, z) */
+} hg_node_data;
+
+/* FastCorrelativeScanMatcher3D::Result (fast_correlative_scan_matcher_3d.h:68-73)
+ * plus search statistics. found == 0 corresponds to a null result. */
+typedef struct hg_match_result {
+  int32_t found;
+  float score;
+  double pose_translation[3];
+  double pose_rotation[4]; /* (w, x, y, z) */
+  float rotational_score;
+  float low_resolution_score;
+  int32_t best_scan_index;
+  int32_t best_offset[3];
+  int32_t num_discrete_scans;
+  int64_t num_candidates_scored;     /* candidates the GPU scored (a superset of the DFS's) */
+  int64_t num_candidates_visited;    /* candidates the reference's DFS order consumed */
+  int32_t num_score_launches;
+} hg_match_result;
+
+/* FastCorrelativeScanMatcher3D(grid, low_resolution_grid, histogram, options)
+ * (fast_correlative_scan_matcher_3d.cc:129-153). The stack is built here. */
+int hg_fcsm_create(const hg_grid* grid, const hg_grid* low_resolution_grid,
+                   const float* rotational_scan_matcher_histogram, int histogram_size,
+                   const hg_fcsm_options* options, hg_fcsm** out);
+void hg_fcsm_destroy(hg_fcsm* matcher);
+const hg_stack* hg_fcsm_stack(const hg_fcsm* matcher);
+
+/* FastCorrelativeScanMatcher3D::Match (fast_correlative_scan_matcher_3d.cc:157-174).
+ * Poses are t3 q4 doubles. */
+int hg_fcsm_match(const hg_fcsm* matcher, const double* global_node_pose,
+                  const double* global_submap_pose, const hg_node_data* data, float min_score,
+                  hg_match_result* result);
+
+/* FastCorrelativeScanMatcher3D::MatchFullSubmap (:176-200). Rotations are (w,x,y,z).
+ * 'shard_index' / 'num_shards' restrict the search to the discrete scans
+ * s with s % num_shards == shard_index (multi-GPU sharding by yaw; 0 / 1 = all).
+ * best_scan_index is always the index in the unsharded scan list. */
+int hg_fcsm_match_full_submap(const hg_fcsm* matcher, const double* global_node_rotation,
+                              const double* global_submap_rotation, const hg_node_data* data,
+                              float min_score, int shard_index, int num_shards,
+                              hg_match_result* result);
+
+/* Stage-level entry points (parity tests and the candidates/s benchmark). */
+
+/* GenerateDiscreteScans (:276-326) for an explicit window. Host outputs, any
+ * may be NULL: poses [S x 7 float: t3, q wxyz], rotational scores [S], cells
+ * [S x depth x N x 3 int32]. *num_scans receives S; nothing is written if
+ * S > max_scans. */
+int hg_fcsm_discrete_scans(const hg_fcsm* matcher, int linear_xy_window_size,
+                           int linear_z_window_size, double angular_search_window,
+                           const double* global_node_pose, const double* global_submap_pose,
+                           const hg_node_data* data, int max_scans, int32_t* num_scans,
+                           float* poses, float* rotational_scores, int32_t* cells);
+
+/* ScoreCandidates (:363-386) without the sort: integer gather sums and float
+ * scores for explicit candidates (scan, ox, oy, oz) at 'depth'. Host pointers.
+ * kernel_ms (may be NULL) receives the device time of the scoring kernel(s). */
+int hg_fcsm_score_candidates(const hg_fcsm* matcher, int linear_xy_window_size,
+                             int linear_z_window_size, double angular_search_window,
+                             const double* global_node_pose, const double* global_submap_pose,
+                             const hg_node_data* data, int depth, int64_t num_candidates,
+                             const int32_t* candidates /* n x 4 */, int32_t* sums, float* scores,
+                             float* kernel_ms);
+
+/* CreateLowResolutionMatcher's closure (low_resolution_matcher.cc:24-69) for a
+ * batch of float poses [n x 7: t3, q wxyz]; host pointers. */
+int hg_low_resolution_scores(const hg_grid* low_resolution_grid, const float* points,
+                             int num_points, int64_t num_poses, const float* poses, float* scores);
+
+/* ------------------------------------------------- constraint batches -- */
+
+/* One (node, submap) pair of ConstraintBuilder3D::ComputeConstraint
+ * (mapping/internal/constraints/constraint_builder_3d.cc:192-295). */
+typedef struct hg_constraint_job {
+  int32_t submap_index;          /* which matcher / grids (index into the arrays below) */
+  int32_t match_full_submap;     /* 0 = MaybeAddConstraint path, 1 = MaybeAddGlobalConstraint */
+  double global_node_pose[7];    /* t3 q4 */
+  double global_submap_pose[7];
+  hg_node_data data;
+} hg_constraint_job;
+
+typedef struct hg_constraint_options {
+  float min_score;                    /* constraint_builder options: min_score / global_localization_min_score */
+  float global_localization_min_score;
+  double occupied_space_weights[2];   /* ceres_scan_matcher_options_3d: high- and low-resolution cloud */
+  double translation_weight;
+  double rotation_weight;
+  int32_t only_optimize_yaw;
+  int32_t max_num_iterations;
+  int32_t use_nonmonotonic_steps;
+} hg_constraint_options;
+
+typedef struct hg_constraint_result {
+  int32_t found;
+  float score;
+  double pose[7];          /* refined submap-local pose of the node, t3 q4 */
+  float rotational_score;
+  float low_resolution_score;
+  int64_t num_candidates_scored;
+} hg_constraint_result;
+
+/* Runs jobs [0, num_jobs): fast correlative match, then the Ceres-style refine
+ * on {high-res cloud + grid, low-res cloud + low-res grid}
+ * (constraint_builder_3d.cc:210-265). matchers[i], grids[i], low_grids[i]
+ * belong to submap i. Only jobs with job_index % num_shards == shard_index are
+ * computed (others are left untouched) — the multi-GPU partition. */
+int hg_constraints_run_batch(const hg_fcsm* const* matchers, const hg_grid* const* grids,
+                             const hg_grid* const* low_resolution_grids, int num_submaps,
+                             const hg_constraint_job* jobs, int64_t num_jobs,
+                             const hg_constraint_options* options, int shard_index, int num_shards,
+                             hg_constraint_result* results);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HG_B200_H_ */

@@ -1,0 +1,515 @@
+"""GPU parity tests: the CUDA path, called through the C-ABI, against the CPU oracle on the
+same seeded inputs. Bars (BASELINE.json north_star): bit-exact voxel indices, precomputation
+grids, integer candidate sums and selected candidate; residuals / Jacobians within 1e-5
+relative; solved pose within 1e-4 m / 1e-4 rad."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5   # north_star: residuals and Jacobians within 1e-5 relative of the double-precision Jets
+ATOL = 1e-9   # absolute floor for entries that cancel to ~0 (values are O(1e-2..1))
+
+
+@pytest.fixture(scope="module")
+def hg():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    import hectorgrapher_b200 as hg
+    hg.lib()
+    return hg
+
+
+@pytest.fixture(scope="module")
+def world(oracle, hg):
+    """Synthetic box+spheres world: TSDF high/low grids and an occupancy grid, in both libraries."""
+    from hectorgrapher_b200 import synth
+    sph = synth.spheres()
+    poses = [synth.corkscrew_pose(k, 4) for k in range(4)]
+    w = {"sph": sph, "poses": poses, "synth": synth}
+    xyz, tv, wv = synth.build_tsdf(0.10, poses, 32, 360, sph)
+    w["tsdf_hi"] = (xyz, tv, wv)
+    g = oracle.Grid.tsdf(0.10, 2.5, 1000.0)
+    g.set_raw(xyz, tv, wv)
+    w["o_tsdf_hi"] = g
+    w["g_tsdf_hi"] = hg.Grid.tsdf(0.10, 2.5, 1000.0, xyz, tv, wv, grid_size=g.grid_size)
+    xyz, tv, wv = synth.build_tsdf(0.45, poses, 32, 360, sph)
+    g = oracle.Grid.tsdf(0.45, 2.5, 1000.0)
+    g.set_raw(xyz, tv, wv)
+    w["o_tsdf_lo"] = g
+    w["g_tsdf_lo"] = hg.Grid.tsdf(0.45, 2.5, 1000.0, xyz, tv, wv, grid_size=g.grid_size)
+    xyz, pv = synth.build_occupancy(0.10, poses, 32, 360, sph)
+    g = oracle.Grid.prob(0.10)
+    g.set_raw(xyz, pv)
+    w["o_prob"] = g
+    w["g_prob"] = hg.Grid.prob(0.10, xyz, pv, grid_size=g.grid_size)
+    xyz, pv = synth.build_occupancy(0.45, poses, 32, 360, sph)
+    g = oracle.Grid.prob(0.45)
+    g.set_raw(xyz, pv)
+    w["o_prob_lo"] = g
+    w["g_prob_lo"] = hg.Grid.prob(0.45, xyz, pv, grid_size=g.grid_size)
+    rng = np.random.RandomState(3)
+    origin, yaw = poses[1]
+    cloud = synth.scan(origin, yaw, 16, 256, sph, rng)
+    w["cloud"] = cloud
+    w["truth"] = np.concatenate([origin, synth.quat_from_yaw(yaw)])
+    return w
+
+
+def perturbed(truth, rng, dt=0.1, da=0.05):
+    from hectorgrapher_b200 import synth
+    t = truth[:3] + rng.uniform(-dt, dt, 3)
+    q = synth.quat_mul(truth[3:], synth.small_rotation(rng, da))
+    return np.concatenate([t, q])
+
+
+def assert_close(a, b, what=""):
+    a, b = np.asarray(a), np.asarray(b)
+    assert a.shape == b.shape
+    err = np.abs(a - b)
+    tol = ATOL + RTOL * np.maximum(np.abs(a), np.abs(b))
+    bad = err > tol
+    assert not bad.any(), "%s: %d / %d entries differ, worst abs %.3e (values %.6e vs %.6e)" % (
+        what, bad.sum(), bad.size, err.max(), a.flat[err.argmax()], b.flat[err.argmax()])
+
+
+# ------------------------------------------------------------------ storage --
+
+def test_cell_index_bit_exact(oracle, hg):
+    rng = np.random.RandomState(0)
+    for res in [0.05, 0.1, 0.45, 2.0]:
+        pts = rng.uniform(-60, 60, size=(20000, 3)).astype(np.float32)
+        # exact half-cell cases (lround: half away from zero) on both sides of zero
+        k = rng.randint(-500, 500, size=(2000, 3))
+        halves = ((k + 0.5) * np.float32(res)).astype(np.float32)
+        pts = np.concatenate([pts, halves, -halves])
+        assert (hg.get_cell_index(res, pts) == oracle.get_cell_index(res, pts)).all()
+    want = np.array([[4, 6, 0], [4, 6, 1], [3, 7, 1], [3, 7, 2]])
+    got = hg.get_cell_index(2.0, [[8.5, 11.5, 0.5], [7.5, 12.5, 1.5], [6.5, 14.5, 2.5], [5.5, 13.5, 3.5]])
+    assert (got == want).all()  # hybrid_grid_test.cc:104-112
+
+
+def test_grid_lookup_bit_exact(oracle, hg, world):
+    rng = np.random.RandomState(1)
+    for name, kinds in [("tsdf_hi", ["tsd", "weight"]), ("tsdf_lo", ["tsd", "weight"]), ("prob", ["probability"])]:
+        og, gg = world["o_" + name], world["g_" + name]
+        ex = og.export()[0]
+        near = ex[rng.randint(0, len(ex), 30000)] + rng.randint(-2, 3, size=(30000, 3))
+        far = rng.randint(-9000, 9000, size=(2000, 3))
+        q = np.concatenate([near, far]).astype(np.int32)
+        for what in kinds:
+            a, b = gg.lookup(what, q), og.lookup(what, q)
+            assert (a.view(np.uint32) == b.view(np.uint32)).all(), (name, what)
+
+
+def test_grid_edge_cases(oracle, hg):
+    # empty grid: everything reads the default
+    g = hg.Grid.prob(0.1, np.zeros((0, 3), np.int32), np.zeros(0, np.uint16))
+    assert (g.lookup("probability", [[0, 0, 0], [5, -3, 9]]) == np.float32(0.1)).all()
+    t = hg.Grid.tsdf(1.0, 0.5, 10.0, np.zeros((0, 3), np.int32), np.zeros(0, np.uint16), np.zeros(0, np.uint16))
+    assert (t.lookup("tsd", [[1, 2, 3]]) == np.float32(-0.5)).all()   # hybrid_grid_tsdf_test.cc:45-52
+    assert (t.lookup("weight", [[1, 2, 3]]) == 0).all()
+    # single voxel at the extreme corner a reference grid can hold (+-8192)
+    og = oracle.Grid.tsdf(0.05, 2.5, 1000.0)
+    xyz = np.array([[-8192, -8192, -8192], [8191, 8191, 8191], [0, 0, 0]], np.int32)
+    og.set_cell(xyz, [0.01, -0.02, 0.1], [1.0, 2.0, 3.0])
+    ex, tv, wv = og.export()
+    gg = hg.Grid.tsdf(0.05, 2.5, 1000.0, ex, tv, wv)
+    assert gg.grid_size == og.grid_size == 16384
+    for what in ["tsd", "weight"]:
+        assert (gg.lookup(what, xyz).view(np.uint32) == og.lookup(what, xyz).view(np.uint32)).all()
+    # update marker on probability values is masked
+    g2 = hg.Grid.prob(0.1, [[1, 1, 1]], np.array([0x8000 | 20000], np.uint16))
+    o2 = oracle.Grid.prob(0.1)
+    o2.set_raw([[1, 1, 1]], np.array([0x8000 | 20000], np.uint16))
+    assert g2.lookup("probability", [[1, 1, 1]])[0] == o2.lookup("probability", [[1, 1, 1]])[0]
+
+
+# ------------------------------------------------------------ cost functions --
+
+KIND_GRIDS = {
+    "occupied": ["prob"], "interpolated_occupied": ["prob"],
+    "tsdf": ["tsdf_hi"], "interpolated_tsdf": ["tsdf_hi"], "interpolated_tsdf_per_point": ["tsdf_hi"],
+    "multires_tsdf": ["tsdf_hi", "tsdf_lo"], "interpolated_multires_tsdf": ["tsdf_hi", "tsdf_lo"],
+    "interpolated_multires_tsdf_per_point": ["tsdf_hi", "tsdf_lo"],
+}
+
+
+@pytest.mark.parametrize("kind", list(KIND_GRIDS.keys()))
+def test_cost_function_parity(oracle, hg, world, kind):
+    rng = np.random.RandomState(11)
+    cloud = world["cloud"]
+    if kind.endswith("per_point"):
+        cloud = cloud[777:778]
+    scale = 0.7 / np.sqrt(len(cloud))
+    og = [world["o_" + n] for n in KIND_GRIDS[kind]]
+    gg = [world["g_" + n] for n in KIND_GRIDS[kind]]
+    two = kind.startswith("interpolated")
+    ratio = 0.37 if two else 0.0
+    oc = oracle.Cost(kind, scale, cloud, og, ratio)
+    gc = hg.Cost(kind, scale, cloud, gg, ratio)
+    assert gc.n == oc.n == len(cloud) and gc.nblocks == oc.nblocks == (4 if two else 2)
+    for trial in range(3):
+        p = perturbed(world["truth"], rng)
+        if two:
+            p = np.concatenate([p, perturbed(world["truth"], rng, 0.3, 0.15)])
+        r0, J0 = oc.evaluate(p)
+        r1, J1 = gc.evaluate(p)
+        assert_close(r1, r0, kind + " residuals")
+        for b in range(len(J0)):
+            assert_close(J1[b], J0[b], "%s jacobian block %d" % (kind, b))
+        if len(cloud) > 1:
+            assert np.abs(np.hstack(J0)).max() > 1e-4  # the comparison is not vacuous
+        # jacobians == NULL, and one block held constant
+        r2, _ = gc.evaluate(p, jacobians=False)
+        assert_close(r2, r0, kind + " residuals (no jacobians)")
+        r3, J3 = gc.evaluate(p, skip_blocks=(1,))
+        assert_close(J3[0], J0[0], kind + " jacobian with block 1 skipped")
+        assert (J3[1] == 0).all()
+
+
+def test_cost_function_slerp_branches(oracle, hg, world):
+    """Two-pose functors: lerp branch (identical rotations) and the d < 0 sign flip."""
+    cloud = world["cloud"][:500]
+    oc = oracle.Cost("interpolated_tsdf", 0.1, cloud, [world["o_tsdf_hi"]], 0.25)
+    gc = hg.Cost("interpolated_tsdf", 0.1, cloud, [world["g_tsdf_hi"]], 0.25)
+    t = world["truth"]
+    same = np.concatenate([t, t[:3] + 0.05, t[3:]])
+    flipped = np.concatenate([t, t[:3] + 0.05, -t[3:] + np.array([0, 0.01, 0, 0])])
+    for p in [same, flipped]:
+        r0, J0 = oc.evaluate(p)
+        r1, J1 = gc.evaluate(p)
+        assert_close(r1, r0)
+        for b in range(4):
+            assert_close(J1[b], J0[b], "block %d" % b)
+
+
+def test_timed_point_cloud_stride(oracle, hg, world):
+    """sensor::TimedPointCloud: 16-byte points (xyz + time)."""
+    cloud = world["cloud"][:1000]
+    timed = np.concatenate([cloud, np.linspace(-0.1, 0, len(cloud), dtype=np.float32)[:, None]], axis=1)
+    oc = oracle.Cost("tsdf", 0.2, timed, [world["o_tsdf_hi"]], stride=4)
+    gc = hg.Cost("tsdf", 0.2, timed, [world["g_tsdf_hi"]], stride=4)
+    p = world["truth"]
+    r0, J0 = oc.evaluate(p)
+    r1, J1 = gc.evaluate(p)
+    assert_close(r1, r0)
+    assert_close(J1[1], J0[1])
+
+
+def test_cost_on_empty_grid(oracle, hg):
+    """interpolated_tsdf_space_cost_function_3d_test.cc: an empty TSDF yields constant residuals
+    (the minimum TSD) and zero Jacobians."""
+    og = oracle.Grid.tsdf(0.1, 2.5, 100.0)
+    gg = hg.Grid.tsdf(0.1, 2.5, 100.0, np.zeros((0, 3), np.int32), np.zeros(0, np.uint16), np.zeros(0, np.uint16))
+    pts = np.random.RandomState(0).uniform(-3, 3, (64, 3)).astype(np.float32)
+    p = np.array([0.1, 0.2, 0.3, 1, 0, 0, 0, 0.2, 0.1, 0.0, 1, 0, 0, 0], float)
+    r0, J0 = oracle.Cost("interpolated_tsdf", 0.5, pts, [og], 0.5).evaluate(p)
+    r1, J1 = hg.Cost("interpolated_tsdf", 0.5, pts, [gg], 0.5).evaluate(p)
+    assert (r1 == r0).all() and np.allclose(r1, 0.5 * np.float32(-0.25))
+    assert all((j == 0).all() for j in J1)
+
+
+@pytest.mark.parametrize("kind", ["tsdf", "interpolated_multires_tsdf", "occupied"])
+def test_normal_equations(oracle, hg, world, kind):
+    rng = np.random.RandomState(5)
+    cloud = world["cloud"]
+    og = [world["o_" + n] for n in KIND_GRIDS[kind]]
+    gg = [world["g_" + n] for n in KIND_GRIDS[kind]]
+    two = kind.startswith("interpolated")
+    oc = oracle.Cost(kind, 0.05, cloud, og, 0.6)
+    gc = hg.Cost(kind, 0.05, cloud, gg, 0.6)
+    p = perturbed(world["truth"], rng)
+    if two:
+        p = np.concatenate([p, perturbed(world["truth"], rng)])
+    r, J = oc.evaluate(p)
+    Jf = np.hstack(J)
+    JtJ, Jtr, cost = gc.normal_equations(p)
+    scale = np.abs(Jf.T @ Jf).max()
+    assert np.abs(JtJ - Jf.T @ Jf).max() < 1e-9 * scale
+    assert np.abs(Jtr - Jf.T @ r).max() < 1e-9 * max(1.0, np.abs(Jf.T @ r).max())
+    assert abs(cost - 0.5 * r @ r) < 1e-10 * max(1.0, 0.5 * r @ r)
+    # two calls in a row give identical bits (fixed-order reduction)
+    JtJ2, Jtr2, cost2 = gc.normal_equations(p)
+    assert (JtJ2 == JtJ).all() and (Jtr2 == Jtr).all() and cost2 == cost
+
+
+def test_batch_matches_per_block(oracle, hg, world):
+    """Ragged batch (one empty block, one 1-point block) against per-block oracle evaluation."""
+    rng = np.random.RandomState(8)
+    sizes = [700, 0, 1, 1300, 255, 257]
+    clouds = [world["cloud"][rng.choice(len(world["cloud"]), n, replace=False)] for n in sizes]
+    pts = np.concatenate(clouds)
+    offsets = np.concatenate([[0], np.cumsum(sizes)])
+    scales = rng.uniform(0.01, 0.2, len(sizes))
+    ratios = rng.uniform(0, 1, len(sizes))
+    poses = np.stack([perturbed(world["truth"], rng) for _ in range(4)])
+    i0 = rng.randint(0, 4, len(sizes))
+    i1 = rng.randint(0, 4, len(sizes))
+    kind = "interpolated_multires_tsdf"
+    gb = hg.Batch(kind, pts, offsets, scales, [world["g_tsdf_hi"], world["g_tsdf_lo"]], ratios)
+    r, J = gb.evaluate(poses, i0, i1)
+    JtJ, Jtr, cost = gb.normal_equations(poses, i0, i1)
+    for b, n in enumerate(sizes):
+        if n == 0:
+            assert (JtJ[b] == 0).all() and cost[b] == 0
+            continue
+        oc = oracle.Cost(kind, scales[b], clouds[b], [world["o_tsdf_hi"], world["o_tsdf_lo"]], ratios[b])
+        r0, J0 = oc.evaluate(np.concatenate([poses[i0[b]], poses[i1[b]]]))
+        sl = slice(offsets[b], offsets[b + 1])
+        assert_close(r[sl], r0, "block %d residuals" % b)
+        for k in range(4):
+            assert_close(J[k][sl], J0[k], "block %d jacobian %d" % (b, k))
+        Jf = np.hstack(J0)
+        assert np.abs(JtJ[b] - Jf.T @ Jf).max() < 1e-9 * max(1e-12, np.abs(Jf.T @ Jf).max())
+        assert abs(cost[b] - 0.5 * r0 @ r0) < 1e-10 * max(1.0, 0.5 * r0 @ r0)
+
+
+def test_scan_match_pose_parity(oracle, hg, world):
+    """CeresScanMatcher3D::Match: same optimiser over oracle vs GPU cost functions, final pose
+    within 1e-4 m / 1e-4 rad (north_star)."""
+    synth = world["synth"]
+    rng = np.random.RandomState(21)
+    hi = world["cloud"]
+    lo = synth.voxel_downsample(hi, 0.6)
+    for grids in [("tsdf_hi", "tsdf_lo"), ("prob", "prob_lo")]:
+        og = [world["o_" + g] for g in grids]
+        gg = [world["g_" + g] for g in grids]
+        for trial in range(2):
+            init = perturbed(world["truth"], rng, 0.08, 0.03)
+            p0, s0, _ = oracle.scan_match([hi, lo], og, [5.0, 30.0], 10.0, 1.0, init, max_num_iterations=12,
+                                          use_nonmonotonic_steps=False)
+            p1, s1 = hg.scan_match([hi, lo], gg, [5.0, 30.0], 10.0, 1.0, init, max_num_iterations=12,
+                                   use_nonmonotonic_steps=False)
+            assert np.abs(p1[:3] - p0[:3]).max() < 1e-4
+            q0, q1 = p0[3:] / np.linalg.norm(p0[3:]), p1[3:] / np.linalg.norm(p1[3:])
+            assert 2 * np.arccos(min(1.0, abs(float(q0 @ q1)))) < 1e-4
+            assert abs(s1[1] - s0[1]) <= 1e-6 * max(1.0, s0[1])
+            assert s1[1] < s1[0]
+
+
+# --------------------------------------------------------- precomputation grids --
+
+@pytest.mark.parametrize("name,depth,frd", [("prob", 7, 3), ("tsdf_hi", 7, 3), ("prob", 5, 5), ("tsdf_lo", 4, 1)])
+def test_precomputation_stack_bit_exact(oracle, hg, world, name, depth, frd):
+    os_ = oracle.Stack(world["o_" + name], depth, frd)
+    gs = hg.Stack(world["g_" + name], depth, frd)
+    assert gs.depth == depth
+    rng = np.random.RandomState(depth)
+    for d in range(depth):
+        xo, vo = os_.export(d)
+        xo, vo = xo[vo != 0], vo[vo != 0]
+        xg, vg = gs.export(d)
+        assert len(xo) == len(xg), "level %d: %d vs %d non-zero voxels" % (d, len(xo), len(xg))
+        a, b = np.lexsort(xo.T[::-1]), np.lexsort(xg.T[::-1])
+        assert (xo[a] == xg[b]).all() and (vo[a] == vg[b]).all(), "level %d differs" % d
+        q = np.concatenate([xo[rng.randint(0, len(xo), 4000)] + rng.randint(-9, 10, (4000, 3)),
+                            rng.randint(-4000, 4000, (500, 3))]).astype(np.int32)
+        assert (gs.lookup(d, q) == os_.lookup(d, q)).all()
+
+
+def test_precomputation_reference_known_answer(oracle, hg):
+    """precomputation_grid_3d_test.cc:30-77 on the GPU stack (full-resolution levels)."""
+    rng = np.random.RandomState(23847)
+    og = oracle.Grid.prob(2.0)
+    xyz = rng.randint(-50, 50, size=(1000, 3)).astype(np.int32)
+    p = rng.uniform(0.1, 0.9, size=1000).astype(np.float32)
+    for i in range(1000):
+        og.set_probability(xyz[i:i + 1], p[i:i + 1])
+    ex, ev = og.export()
+    gs = hg.Stack(hg.Grid.prob(2.0, ex, ev), 4, 4)
+    for depth in range(4):
+        width = 1 << depth
+        q = rng.randint(-50, 50, size=(100, 3)).astype(np.int32)
+        got = gs.lookup(depth, q)
+        d = np.arange(width)
+        off = np.stack(np.meshgrid(d, d, d, indexing="ij"), -1).reshape(-1, 3)
+        for i in range(100):
+            naive = float(og.lookup("probability", q[i] + off).max())
+            assert abs(naive - (0.1 + got[i] * (0.8 / 255.0))) < 1e-2
+
+
+# ------------------------------------------------------- correlative matcher --
+
+def node_inputs(world, n_high=600, n_low=150):
+    synth = world["synth"]
+    hi = synth.voxel_downsample(world["cloud"], 0.25, n_high, seed=1)
+    lo = synth.voxel_downsample(world["cloud"], 0.9, n_low, seed=2)
+    hist = synth.rotational_histogram(hi, 60)
+    return hi, lo, hist
+
+
+def world_matchers(oracle, hg, world, grid="tsdf", **opts):
+    names = ("tsdf_hi", "tsdf_lo") if grid == "tsdf" else ("prob", "prob_lo")
+    hi, lo, hist = node_inputs(world)
+    o = dict(branch_and_bound_depth=6, full_resolution_depth=3, min_rotational_score=0.5,
+             min_low_resolution_score=0.3, linear_xy_search_window=2.0, linear_z_search_window=0.6,
+             angular_search_window=0.12)
+    o.update(opts)
+    # the submap's histogram is the node's, rotated into the submap frame (mapping/3d/submap_3d.cc)
+    truth_yaw = 2 * np.arctan2(world["truth"][6], world["truth"][3])
+    submap_hist = oracle.rotate_histogram(hist, np.float32(truth_yaw))
+    om = oracle.Fcsm(world["o_" + names[0]], world["o_" + names[1]], submap_hist, **o)
+    gm = hg.Fcsm(world["g_" + names[0]], world["g_" + names[1]], submap_hist, **o)
+    return om, gm, hi, lo, hist
+
+
+@pytest.mark.parametrize("grid", ["tsdf", "prob"])
+def test_discrete_scans_bit_exact(oracle, hg, world, grid):
+    om, gm, hi, lo, hist = world_matchers(oracle, hg, world, grid)
+    rng = np.random.RandomState(4)
+    node = perturbed(world["truth"], rng, 0.5, 0.05)
+    submap = np.array([0.3, -0.2, 0.1, *world["synth"].small_rotation(rng, 0.2)])
+    for (wxy, wz, ang) in [(20, 6, 0.12), (7, 3, 0.05)]:
+        p0, r0, c0 = om.discrete_scans(wxy, wz, ang, node, submap, hi, hist)
+        p1, r1, c1 = gm.discrete_scans(wxy, wz, ang, node, submap, hi, hist)
+        assert p0.shape == p1.shape and len(p0) > 3
+        assert (p0.view(np.uint32) == p1.view(np.uint32)).all()      # poses bit-exact
+        assert (r0.view(np.uint32) == r1.view(np.uint32)).all()      # rotational scores bit-exact
+        assert (c0 == c1).all()                                      # rotated-scan voxel indices
+
+
+@pytest.mark.parametrize("grid", ["tsdf", "prob"])
+def test_candidate_scores_bit_exact(oracle, hg, world, grid):
+    om, gm, hi, lo, hist = world_matchers(oracle, hg, world, grid)
+    rng = np.random.RandomState(6)
+    node = perturbed(world["truth"], rng, 0.3, 0.03)
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    wxy, wz, ang = 20, 6, 0.12
+    S = len(om.discrete_scans(wxy, wz, ang, node, submap, hi, hist)[0])
+    for depth in range(6):
+        n = 3000
+        cand = np.stack([rng.randint(0, S, n), rng.randint(-wxy, wxy + 1, n), rng.randint(-wxy, wxy + 1, n),
+                         rng.randint(-wz, wz + 1, n)], 1).astype(np.int32)
+        s0, f0, _ = om.score_candidates(wxy, wz, ang, node, submap, hi, hist, depth, cand)
+        s1, f1, ms = gm.score_candidates(wxy, wz, ang, node, submap, hi, hist, depth, cand)
+        assert (s0 == s1).all(), "integer sums differ at depth %d" % depth
+        assert (f0.view(np.uint32) == f1.view(np.uint32)).all()
+        assert s0.max() > 0 and ms > 0
+
+
+@pytest.mark.parametrize("grid", ["tsdf", "prob"])
+def test_low_resolution_scores_bit_exact(oracle, hg, world, grid):
+    name = "tsdf_lo" if grid == "tsdf" else "prob_lo"
+    rng = np.random.RandomState(9)
+    lo = node_inputs(world)[1]
+    poses = np.stack([perturbed(world["truth"], rng, 1.0, 0.3) for _ in range(200)]).astype(np.float32)
+    got = hg.low_resolution_scores(world["g_" + name], lo, poses)
+    want = np.array([oracle.low_resolution_score(world["o_" + name], lo, p) for p in poses], np.float32)
+    assert (got.view(np.uint32) == want.view(np.uint32)).all()
+
+
+RESULT_KEYS = ["found", "score", "tx", "ty", "tz", "qw", "qx", "qy", "qz", "rotational_score",
+               "low_resolution_score", "scan_index", "ox", "oy", "oz", "num_scans"]
+
+
+def assert_same_match(r0, r1):
+    for k in RESULT_KEYS:
+        assert np.float64(r0[k]) == np.float64(r1[k]), (k, r0[k], r1[k])
+
+
+@pytest.mark.parametrize("grid", ["tsdf", "prob"])
+def test_match_selects_the_same_candidate(oracle, hg, world, grid):
+    om, gm, hi, lo, hist = world_matchers(oracle, hg, world, grid)
+    rng = np.random.RandomState(12)
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    found = 0
+    for trial in range(6):
+        node = perturbed(world["truth"], rng, 1.2, 0.08)
+        for min_score in [0.2, 0.32]:
+            r0 = om.match(node, submap, hi, lo, hist, min_score=min_score)
+            r1 = gm.match(node, submap, hi, lo, hist, min_score=min_score)
+            assert_same_match(r0, r1)
+            assert r1["num_scored"] >= r1["num_visited"] > 0
+            assert r1["num_visited"] == r0["num_scored"]  # the replay consumed exactly the DFS's candidates
+            found += int(r1["found"])
+    assert found >= 6
+    # a cloud that cannot pass the low-resolution gate gives a null result in both
+    far = np.array([[42., 42., 42.]], np.float32)
+    r0 = om.match(world["truth"], submap, hi, far, hist, min_score=0.2)
+    r1 = gm.match(world["truth"], submap, hi, far, hist, min_score=0.2)
+    assert r0["found"] == r1["found"] == 0.0
+
+
+def test_match_full_submap_selects_the_same_candidate(oracle, hg, world):
+    om, gm, hi, lo, hist = world_matchers(oracle, hg, world, "tsdf", branch_and_bound_depth=7,
+                                          use_rotational_scan_matcher=False)
+    hi = hi[:200]
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    node = world["truth"]
+    r0 = om.match(node, submap, hi, lo, hist, min_score=0.4, full=True)
+    r1 = gm.match(node, submap, hi, lo, hist, min_score=0.4, full=True)
+    assert_same_match(r0, r1)
+    assert r1["found"] == 1.0
+    # sharded by discrete scan: the best over shards equals the unsharded answer
+    shards = [gm.match(node, submap, hi, lo, hist, min_score=0.4, full=True, shard_index=s, num_shards=3)
+              for s in range(3)]
+    assert sum(int(s["num_scans"]) for s in shards) == int(r1["num_scans"])
+    best = max((s for s in shards if s["found"]), key=lambda s: s["score"])
+    assert best["score"] == r1["score"]
+    assert (best["scan_index"], best["ox"], best["oy"], best["oz"]) == (
+        r1["scan_index"], r1["ox"], r1["oy"], r1["oz"])
+
+
+def _rot_z(theta):
+    return np.array([np.cos(theta / 2), 0, 0, np.sin(theta / 2)])
+
+
+def test_reference_fcsm_fixture_on_gpu(oracle, hg):
+    """fast_correlative_scan_matcher_3d_test.cc:141-196 through the GPU matcher, and identical to
+    the oracle's result."""
+    from hectorgrapher_b200 import synth
+    cloud = np.array([[4, 0, 0], [4.5, 0, 0], [5, 0, 0], [5.5, 0, 0], [0, 4, 0], [0, 4.5, 0], [0, 5, 0],
+                      [0, 5.5, 0], [0, 0, 4], [0, 0, 4.5], [0, 0, 5], [0, 0, 5.5]], np.float32)
+    opts = dict(branch_and_bound_depth=6, full_resolution_depth=6, use_rotational_scan_matcher=True,
+                min_rotational_score=0.1, min_low_resolution_score=0.15, linear_xy_search_window=0.8,
+                linear_z_search_window=0.8, angular_search_window=0.3)
+    rng = np.random.RandomState(42)
+    ident = [0, 0, 0, 1, 0, 0, 0]
+    for trial in range(4):
+        t = (0.7 * rng.uniform(-1, 1, 3)).astype(np.float32)
+        q = _rot_z(np.float32(0.2 * rng.uniform(-1, 1))).astype(np.float32)
+        w = (synth.quat_rotate(q, cloud) + t).astype(np.float32)
+        og = oracle.Grid.prob(0.05)
+        og.insert_occupancy(t, w, 0.7, 0.4, 5)
+        ex, ev = og.export()
+        gg = hg.Grid.prob(0.05, ex, ev, grid_size=og.grid_size)
+        om = oracle.Fcsm(og, og, np.zeros(10, np.float32), **opts)
+        gm = hg.Fcsm(gg, gg, np.zeros(10, np.float32), **opts)
+        for full in ([False, True] if trial == 0 else [False]):
+            r0 = om.match(ident, ident, cloud, cloud, np.zeros(10), min_score=0.1, full=full)
+            r1 = gm.match(ident, ident, cloud, cloud, np.zeros(10), min_score=0.1, full=full)
+            assert_same_match(r0, r1)
+            assert r1["found"] == 1.0 and r1["score"] > 0.1
+            assert np.abs(np.array([r1["tx"], r1["ty"], r1["tz"]]) - t).max() < 0.05
+            far = gm.match(ident, ident, cloud, [[42., 42., 42.]], np.zeros(10), min_score=0.1, full=full)
+            assert far["found"] == 0.0
+
+
+def test_constraint_batch(oracle, hg, world):
+    """ConstraintBuilder3D::ComputeConstraint for a few pairs: correlative match + refine equals the
+    oracle's match followed by the oracle's refine (pose within 1e-4)."""
+    om, gm, hi, lo, hist = world_matchers(oracle, hg, world, "tsdf")
+    rng = np.random.RandomState(31)
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    jobs, nodes = [], []
+    for j in range(4):
+        node = perturbed(world["truth"], rng, 1.0, 0.06)
+        nodes.append(node)
+        jobs.append(dict(submap_index=0, full=False, node_pose=node, submap_pose=submap, high=hi, low=lo, hist=hist))
+    opts = dict(min_score=0.25, global_localization_min_score=0.4, occupied_space_weights=(5.0, 30.0),
+                translation_weight=10.0, rotation_weight=1.0, max_num_iterations=10)
+    res = hg.constraints_run_batch([gm], [world["g_tsdf_hi"]], [world["g_tsdf_lo"]], jobs, opts)
+    shard0 = hg.constraints_run_batch([gm], [world["g_tsdf_hi"]], [world["g_tsdf_lo"]], jobs, opts, 0, 2)
+    for j, node in enumerate(nodes):
+        r0 = om.match(node, submap, hi, lo, hist, min_score=0.25)
+        assert res[j]["found"] == int(r0["found"])
+        if not r0["found"]:
+            continue
+        init = np.array([r0[k] for k in ["tx", "ty", "tz", "qw", "qx", "qy", "qz"]])
+        p0, _, _ = oracle.scan_match([hi, lo], [world["o_tsdf_hi"], world["o_tsdf_lo"]], [5.0, 30.0], 10.0, 1.0,
+                                     init, max_num_iterations=10, use_nonmonotonic_steps=False)
+        assert res[j]["score"] == np.float32(r0["score"])
+        assert np.abs(res[j]["pose"][:3] - p0[:3]).max() < 1e-4
+        if j % 2 == 0:
+            assert np.abs(shard0[j]["pose"] - res[j]["pose"]).max() == 0
