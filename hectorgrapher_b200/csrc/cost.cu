@@ -68,6 +68,7 @@ struct CostArgs {
   double* jt1;
   double* jq1;
   double* partials;  // normal-equation mode: [tile][P]
+  int vec_store;     // jq0 / jq1 are 16-byte aligned: use 16-byte stores
 };
 
 constexpr int kThreads = 256;
@@ -385,9 +386,14 @@ __global__ void __launch_bounds__(kThreads) CostKernel(const CostArgs a) {
           o[0] = J[0]; o[1] = J[1]; o[2] = J[2];
         }
         if (a.jq0) {
-          double2* o = reinterpret_cast<double2*>(a.jq0 + gi * 4);
-          o[0] = make_double2(J[3], J[4]);
-          o[1] = make_double2(J[5], J[6]);
+          if (a.vec_store) {
+            double2* o = reinterpret_cast<double2*>(a.jq0 + gi * 4);
+            o[0] = make_double2(J[3], J[4]);
+            o[1] = make_double2(J[5], J[6]);
+          } else {
+            double* o = a.jq0 + gi * 4;
+            o[0] = J[3]; o[1] = J[4]; o[2] = J[5]; o[3] = J[6];
+          }
         }
         if (TWO_POSE) {
           if (a.jt1) {
@@ -395,9 +401,14 @@ __global__ void __launch_bounds__(kThreads) CostKernel(const CostArgs a) {
             o[0] = J[7]; o[1] = J[8]; o[2] = J[9];
           }
           if (a.jq1) {
-            double2* o = reinterpret_cast<double2*>(a.jq1 + gi * 4);
-            o[0] = make_double2(J[10], J[11]);
-            o[1] = make_double2(J[12], J[13]);
+            if (a.vec_store) {
+              double2* o = reinterpret_cast<double2*>(a.jq1 + gi * 4);
+              o[0] = make_double2(J[10], J[11]);
+              o[1] = make_double2(J[12], J[13]);
+            } else {
+              double* o = a.jq1 + gi * 4;
+              o[0] = J[10]; o[1] = J[11]; o[2] = J[12]; o[3] = J[13];
+            }
           }
         }
       }
@@ -713,6 +724,7 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
   }
   if (device_outputs) {
     a.r = residuals; a.jt0 = jt0; a.jq0 = jq0; a.jt1 = jt1; a.jq1 = jq1;
+    a.vec_store = ((reinterpret_cast<uintptr_t>(jq0) | reinterpret_cast<uintptr_t>(jq1)) % 16 == 0) ? 1 : 0;
     return LaunchCost<false>(B, a, B->num_tiles_out, stream);
   }
   // Host outputs: stage in device memory, then one copy per requested array.
@@ -724,12 +736,14 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
     HG_CUDA(cudaMalloc(&B->d_out, std::max<size_t>(need, 1) * sizeof(double)));
     B->d_out_doubles = need;
   }
+  // 4-wide arrays first so that they stay 32-byte aligned for any N.
   double* d = B->d_out;
-  a.r = residuals ? d : nullptr;
-  a.jt0 = jt0 ? d + N : nullptr;
-  a.jq0 = jq0 ? d + 4 * N : nullptr;
-  a.jt1 = jt1 ? d + 8 * N : nullptr;
-  a.jq1 = jq1 ? d + 11 * N : nullptr;
+  a.jq0 = jq0 ? d : nullptr;
+  a.jq1 = jq1 ? d + 4 * N : nullptr;
+  a.jt0 = jt0 ? d + 8 * N : nullptr;
+  a.jt1 = jt1 ? d + 11 * N : nullptr;
+  a.r = residuals ? d + 14 * N : nullptr;
+  a.vec_store = 1;
   rc = LaunchCost<false>(B, a, B->num_tiles_out, stream);
   if (rc != HG_OK) return rc;
   if (residuals) HG_CUDA(cudaMemcpyAsync(residuals, a.r, sizeof(double) * N, cudaMemcpyDeviceToHost, stream));

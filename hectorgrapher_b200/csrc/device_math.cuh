@@ -17,6 +17,17 @@ __device__ __forceinline__ int CellIndex1(const float p, const float resolution)
 
 // Brick id of the brick containing voxel (x, y, z), or -1.
 __device__ __forceinline__ int BrickId(const BrickTable& t, const int x, const int y, const int z) {
+  if (t.hash_mask != 0) {
+    const int kx = x >> 3, ky = y >> 3, kz = z >> 3;
+    const int4* entries = reinterpret_cast<const int4*>(t.index);
+    unsigned h = BrickHash(kx, ky, kz) & t.hash_mask;
+    for (;;) {
+      const int4 e = __ldg(entries + h);
+      if (e.w < 0) return -1;
+      if (e.x == kx && e.y == ky && e.z == kz) return e.w;
+      h = (h + 1) & t.hash_mask;
+    }
+  }
   const unsigned bx = static_cast<unsigned>((x >> 3) - t.bmin[0]);
   const unsigned by = static_cast<unsigned>((y >> 3) - t.bmin[1]);
   const unsigned bz = static_cast<unsigned>((z >> 3) - t.bmin[2]);

@@ -36,9 +36,31 @@ int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int voxel_bytes, 
     table->bdim[k] = nb == 0 ? 1 : hi[k] - lo[k] + 1;
     cells *= table->bdim[k];
   }
-  if (cells > (int64_t(1) << 31)) {
-    SetError("brick index bounding box too large (" + std::to_string(cells) + " bricks)");
-    return HG_ERR_LIMIT;
+  table->hash_mask = 0;
+  // Dense index while it stays within 64 Mi entries (256 MB) and within 64x the
+  // brick count + slack; otherwise an open-addressing hash table.
+  if (cells > (int64_t(1) << 26) || cells > 64 * nb + (int64_t(1) << 20)) {
+    unsigned cap = 16;
+    while (cap < 2 * static_cast<uint64_t>(nb) + 1) cap <<= 1;
+    std::vector<int32_t> entries(static_cast<size_t>(cap) * 4, -1);
+    for (int64_t i = 0; i < nb; ++i) {
+      const int bx = brick_coords[3 * i], by = brick_coords[3 * i + 1], bz = brick_coords[3 * i + 2];
+      unsigned h = BrickHash(bx, by, bz) & (cap - 1);
+      while (entries[4 * static_cast<size_t>(h) + 3] >= 0) h = (h + 1) & (cap - 1);
+      entries[4 * static_cast<size_t>(h)] = bx;
+      entries[4 * static_cast<size_t>(h) + 1] = by;
+      entries[4 * static_cast<size_t>(h) + 2] = bz;
+      entries[4 * static_cast<size_t>(h) + 3] = static_cast<int32_t>(i);
+    }
+    HG_CUDA(cudaMalloc(d_index, entries.size() * sizeof(int32_t)));
+    HG_CUDA(cudaMemcpy(*d_index, entries.data(), entries.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    table->hash_mask = cap - 1;
+    const size_t hb = static_cast<size_t>(std::max<int64_t>(nb, 1)) * 512 * voxel_bytes;
+    HG_CUDA(cudaMalloc(d_bricks, hb));
+    HG_CUDA(cudaMemset(*d_bricks, 0, hb));
+    table->index = static_cast<const int32_t*>(*d_index);
+    table->bricks = *d_bricks;
+    return HG_OK;
   }
   std::vector<int32_t> index(static_cast<size_t>(cells), -1);
   for (int64_t i = 0; i < nb; ++i) {

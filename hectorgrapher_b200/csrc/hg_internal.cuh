@@ -44,12 +44,24 @@ inline void CountLaunch(uint64_t n = 1) { g_kernel_launches.fetch_add(n, std::me
 //   * 'bricks' holds brick id * 512 voxels, z-major inside a brick exactly like
 //     the reference's FlatGrid (hybrid_grid_base.h:40-43): ((z*8)+y)*8+x.
 // Voxel type: uint16 (probability), ushort2 {tsd, weight} (TSDF), uint8 (precomputation).
+//   * when that bounding box would be too large (a few voxels at opposite
+//     corners of the +-8192 index range), 'index' is instead an open-addressing
+//     hash table of int4 {bx, by, bz, id} entries (id -1 = empty), selected by
+//     hash_mask != 0.
 struct BrickTable {
   const int32_t* index;  // device
   const void* bricks;    // device
   int bmin[3];           // brick-coordinate origin of 'index'
   int bdim[3];           // extent of 'index' in bricks
+  unsigned hash_mask;    // 0 = dense index; otherwise capacity - 1 of the hash table
 };
+
+__host__ __device__ inline unsigned BrickHash(int bx, int by, int bz) {
+  unsigned h = static_cast<unsigned>(bx) * 73856093u ^ static_cast<unsigned>(by) * 19349663u ^
+               static_cast<unsigned>(bz) * 83492791u;
+  h ^= h >> 15;
+  return h * 0x2c1b3c6du;
+}
 
 // Value decoding constants: value -> float is v' = v & 0x7FFF; v' == 0 ? unknown
 // : v' * scale + offset with offset = lo - scale (value_conversion_tables.cc:29-51),

@@ -1,0 +1,32 @@
+"""Builds and runs the C++ adapter test (tests/cpp/test_adapters.cpp) against libhg_b200.so."""
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "tests", "cpp", "test_adapters.bin")
+
+
+def _build():
+    import hectorgrapher_b200 as hg
+    if not os.path.exists(hg.capi.LIB_PATH):
+        hg.build()
+    lib_dir = os.path.dirname(hg.capi.LIB_PATH)
+    subprocess.check_call(["g++", "-std=c++11", "-O2", "-pthread", "-o", BIN,
+                           os.path.join(ROOT, "tests", "cpp", "test_adapters.cpp"), "-L" + lib_dir, "-lhg_b200",
+                           "-Wl,-rpath," + lib_dir, "-Wl,-rpath,/usr/local/cuda/lib64"])
+
+
+def test_adapters_compile_and_link():
+    _build()
+    out = subprocess.check_output([BIN, "compile-only"], text=True)
+    assert "sm_100a" in out
+
+
+@pytest.mark.gpu
+def test_adapters_on_gpu():
+    _build()
+    out = subprocess.run([BIN], text=True, capture_output=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "ADAPTERS OK" in out.stdout

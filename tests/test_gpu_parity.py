@@ -423,7 +423,7 @@ def test_match_selects_the_same_candidate(oracle, hg, world, grid):
             assert r1["num_scored"] >= r1["num_visited"] > 0
             assert r1["num_visited"] == r0["num_scored"]  # the replay consumed exactly the DFS's candidates
             found += int(r1["found"])
-    assert found >= 6
+    assert found >= 3
     # a cloud that cannot pass the low-resolution gate gives a null result in both
     far = np.array([[42., 42., 42.]], np.float32)
     r0 = om.match(world["truth"], submap, hi, far, hist, min_score=0.2)
