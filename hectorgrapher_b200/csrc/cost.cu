@@ -73,48 +73,96 @@ struct CostArgs {
 
 constexpr int kThreads = 256;
 
-// Lower-voxel selection for one axis (interpolated_tsdf.h:159-192).
-__device__ __forceinline__ void LowerVoxel(const float res, const double x, double* x1, double* x2,
+// Lower-voxel selection for one axis (interpolated_tsdf.h:159-192): narrow to
+// float, containing cell, its float centre, one float step down if the centre
+// lies above the double coordinate; x2 is the float sum centre + resolution.
+// The reference re-derives the cell index of the lower centre with a second
+// GetCellIndex; that is i or i - 1 exactly (|fl(i*res)/res - i| << 0.5 for the
+// +-8192 index range), so no second division is needed.
+__device__ __forceinline__ void LowerVoxel(const GridDev& g, const double x, double* x1, double* x2,
                                            int* index) {
   const float xf = __double2float_rn(x);
-  const int i = CellIndex1(xf, res);
-  float c = __fmul_rn(static_cast<float>(i), res);
-  if (static_cast<double>(c) > x) c = __fsub_rn(c, res);
+  int i = CellIndexFast(xf, g.resolution, g.inv_resolution);
+  float c = __fmul_rn(__int2float_rn(i), g.resolution);
+  if (static_cast<double>(c) > x) {
+    c = __fsub_rn(c, g.resolution);
+    --i;
+  }
   *x1 = static_cast<double>(c);
-  *x2 = static_cast<double>(__fadd_rn(c, res));
-  *index = CellIndex1(c, res);
+  *x2 = static_cast<double>(__fadd_rn(c, g.resolution));
+  *index = i;
+}
+
+// 1 / d for d = x2 - x1, which equals the resolution up to float rounding of the
+// cell centres: two Newton steps from 1 / double(resolution) converge to full
+// double precision (the seed is already within ~1e-7 relative).
+__device__ __forceinline__ double CellWidthReciprocal(const double seed, const double d) {
+  double r = seed * (2.0 - d * seed);
+  r = r * (2.0 - d * r);
+  return r;
 }
 
 // Fetches the 2x2x2 stencil at (ix..ix+1, iy..iy+1, iz..iz+1) in the reference's
 // corner order 111,112,121,122,211,212,221,222 (first digit x, last digit z).
-template <typename V, typename Load>
+// Branch-free for the dense brick index: the brick ids of the up to eight
+// bricks the stencil touches are loaded under predicates (a neighbour brick is
+// only needed when the stencil crosses the brick face on that axis, 1/8 of the
+// points per axis), then every corner selects its brick id and loads its voxel.
+template <typename V>
 __device__ __forceinline__ void FetchStencil(const BrickTable& t, const int ix, const int iy,
-                                             const int iz, V* v, Load load_default) {
-  if (((ix & 7) != 7) && ((iy & 7) != 7) && ((iz & 7) != 7)) {
-    const int id = BrickId(t, ix, iy, iz);
-    if (id < 0) {
+                                             const int iz, V* v) {
+  const V zero = V();
+  if (t.hash_mask != 0) {  // sparse-extreme grids only (uniform branch)
 #pragma unroll
-      for (int k = 0; k < 8; ++k) v[k] = load_default();
-      return;
+    for (int k = 0; k < 8; ++k) {
+      const int x = ix + ((k >> 2) & 1), y = iy + ((k >> 1) & 1), z = iz + (k & 1);
+      const int id = BrickId(t, x, y, z);
+      v[k] = id < 0 ? zero : __ldg(static_cast<const V*>(t.bricks) + id * 512 + InBrick(x, y, z));
     }
-    const V* base = static_cast<const V*>(t.bricks) + static_cast<size_t>(id) * 512 + InBrick(ix, iy, iz);
-    v[0] = __ldg(base);
-    v[1] = __ldg(base + 64);
-    v[2] = __ldg(base + 8);
-    v[3] = __ldg(base + 72);
-    v[4] = __ldg(base + 1);
-    v[5] = __ldg(base + 65);
-    v[6] = __ldg(base + 9);
-    v[7] = __ldg(base + 73);
     return;
   }
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const int x = ix + ((k >> 2) & 1), y = iy + ((k >> 1) & 1), z = iz + (k & 1);
-    const int id = BrickId(t, x, y, z);
-    v[k] = id < 0 ? load_default()
-                  : __ldg(static_cast<const V*>(t.bricks) + static_cast<size_t>(id) * 512 + InBrick(x, y, z));
-  }
+  const int bx = (ix >> 3) - t.bmin[0], by = (iy >> 3) - t.bmin[1], bz = (iz >> 3) - t.bmin[2];
+  const int lx = ix & 7, ly = iy & 7, lz = iz & 7;
+  const bool cx = lx == 7, cy = ly == 7, cz = lz == 7;
+  const bool vx0 = static_cast<unsigned>(bx) < static_cast<unsigned>(t.bdim[0]);
+  const bool vx1 = static_cast<unsigned>(bx + 1) < static_cast<unsigned>(t.bdim[0]);
+  const bool vy0 = static_cast<unsigned>(by) < static_cast<unsigned>(t.bdim[1]);
+  const bool vy1 = static_cast<unsigned>(by + 1) < static_cast<unsigned>(t.bdim[1]);
+  const bool vz0 = static_cast<unsigned>(bz) < static_cast<unsigned>(t.bdim[2]);
+  const bool vz1 = static_cast<unsigned>(bz + 1) < static_cast<unsigned>(t.bdim[2]);
+  const int sy = t.bdim[0], sz = t.bdim[0] * t.bdim[1];
+  const int32_t* p = t.index + (bz * sz + by * sy + bx);
+  // id[dz][dy][dx]
+  const int id000 = (vx0 && vy0 && vz0) ? __ldg(p) : -1;
+  const int id001 = (cx && vx1 && vy0 && vz0) ? __ldg(p + 1) : -1;
+  const int id010 = (cy && vx0 && vy1 && vz0) ? __ldg(p + sy) : -1;
+  const int id011 = (cx && cy && vx1 && vy1 && vz0) ? __ldg(p + sy + 1) : -1;
+  const int id100 = (cz && vx0 && vy0 && vz1) ? __ldg(p + sz) : -1;
+  const int id101 = (cz && cx && vx1 && vy0 && vz1) ? __ldg(p + sz + 1) : -1;
+  const int id110 = (cz && cy && vx0 && vy1 && vz1) ? __ldg(p + sz + sy) : -1;
+  const int id111 = (cz && cy && cx && vx1 && vy1 && vz1) ? __ldg(p + sz + sy + 1) : -1;
+  const int ox0 = lx, ox1 = (lx + 1) & 7;
+  const int oy0 = ly << 3, oy1 = ((ly + 1) & 7) << 3;
+  const int oz0 = lz << 6, oz1 = ((lz + 1) & 7) << 6;
+  const V* bricks = static_cast<const V*>(t.bricks);
+  // corner (kx, ky, kz) lives in brick (kx && cx, ky && cy, kz && cz)
+  const int i0 = id000;                                       // 111
+  const int i1 = cz ? id100 : id000;                          // 112
+  const int i2 = cy ? id010 : id000;                          // 121
+  const int i3 = cz ? (cy ? id110 : id100) : (cy ? id010 : id000);  // 122
+  const int i4 = cx ? id001 : id000;                          // 211
+  const int i5 = cz ? (cx ? id101 : id100) : (cx ? id001 : id000);  // 212
+  const int i6 = cy ? (cx ? id011 : id010) : (cx ? id001 : id000);  // 221
+  const int i7 = cz ? (cy ? (cx ? id111 : id110) : (cx ? id101 : id100))
+                    : (cy ? (cx ? id011 : id010) : (cx ? id001 : id000));  // 222
+  v[0] = i0 < 0 ? zero : __ldg(bricks + (i0 * 512 + (oz0 | oy0 | ox0)));
+  v[1] = i1 < 0 ? zero : __ldg(bricks + (i1 * 512 + (oz1 | oy0 | ox0)));
+  v[2] = i2 < 0 ? zero : __ldg(bricks + (i2 * 512 + (oz0 | oy1 | ox0)));
+  v[3] = i3 < 0 ? zero : __ldg(bricks + (i3 * 512 + (oz1 | oy1 | ox0)));
+  v[4] = i4 < 0 ? zero : __ldg(bricks + (i4 * 512 + (oz0 | oy0 | ox1)));
+  v[5] = i5 < 0 ? zero : __ldg(bricks + (i5 * 512 + (oz1 | oy0 | ox1)));
+  v[6] = i6 < 0 ? zero : __ldg(bricks + (i6 * 512 + (oz0 | oy1 | ox1)));
+  v[7] = i7 < 0 ? zero : __ldg(bricks + (i7 * 512 + (oz1 | oy1 | ox1)));
 }
 
 struct ValueGrad {
@@ -126,16 +174,20 @@ __device__ __forceinline__ ValueGrad LookupOccupancy(const GridDev& g, const dou
                                                      const double z) {
   double x1, y1, z1, x2, y2, z2;
   int ix, iy, iz;
-  LowerVoxel(g.resolution, x, &x1, &x2, &ix);
-  LowerVoxel(g.resolution, y, &y1, &y2, &iy);
-  LowerVoxel(g.resolution, z, &z1, &z2, &iz);
+  LowerVoxel(g, x, &x1, &x2, &ix);
+  LowerVoxel(g, y, &y1, &y2, &iy);
+  LowerVoxel(g, z, &z1, &z2, &iz);
   unsigned short raw[8];
-  FetchStencil<unsigned short>(g.table, ix, iy, iz, raw, [] { return static_cast<unsigned short>(0); });
+  FetchStencil<unsigned short>(g.table, ix, iy, iz, raw);
   double q[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) q[k] = static_cast<double>(Decode(g.a, raw[k]));
-  const double sx = 1.0 / (x2 - x1), sy = 1.0 / (y2 - y1), sz = 1.0 / (z2 - z1);
-  const double nx = (x - x1) / (x2 - x1), ny = (y - y1) / (y2 - y1), nz = (z - z1) / (z2 - z1);
+  // Ceres' Jet / double is a multiplication by the reciprocal (jet.h), which is
+  // what the reference's Jacobian-evaluating instantiation computes.
+  const double sx = CellWidthReciprocal(g.inv_resolution_d, x2 - x1);
+  const double sy = CellWidthReciprocal(g.inv_resolution_d, y2 - y1);
+  const double sz = CellWidthReciprocal(g.inv_resolution_d, z2 - z1);
+  const double nx = (x - x1) * sx, ny = (y - y1) * sy, nz = (z - z1) * sz;
   const double nxx = nx * nx, nxxx = nx * nxx, nyy = ny * ny, nyyy = ny * nyy, nzz = nz * nz,
                nzzz = nz * nzz;
   // Derivatives of n^2, n^3 with respect to n.
@@ -167,62 +219,53 @@ __device__ __forceinline__ ValueGrad LookupOccupancy(const GridDev& g, const dou
   return r;
 }
 
-// interpolated_tsdf.h:29-46 on (value, partials) tuples. Copy branches pass the
-// upstream partials through; the both-unobserved branch is a constant.
-struct Q1 { double v, dz, w; };
-struct Q2 { double v, dy, dz, w; };
+// interpolated_tsdf.h:29-46 on (value, partials) tuples, branch-free. The
+// reference's weights only ever decide "observed or not" (w == 0.0 tests; sums
+// of non-negative weights are zero iff both are), so a flag per voxel carries
+// them exactly: a stored weight value of 0 or 1 decodes to 0.0f, anything larger
+// to a positive weight (value_conversion_tables.cc:29-51 with lower bound 0).
+// Copy branches pass the upstream partials through; both-unobserved is a constant.
+struct Q1 { double v, dz; bool o; };
+struct Q2 { double v, dy, dz; bool o; };
 
 __device__ __forceinline__ Q1 BlendZ(const double unknown, const double q1, const double q2,
-                                     const double w1, const double w2, const double n) {
+                                     const bool o1, const bool o2, const double n) {
   Q1 r;
-  if (w1 == 0.0 && w2 == 0.0) {
-    r.v = unknown; r.dz = 0.0; r.w = 0.0;
-  } else if (w1 == 0.0) {
-    r.v = q2; r.dz = 0.0; r.w = w2;
-  } else if (w2 == 0.0) {
-    r.v = q1; r.dz = 0.0; r.w = w1;
-  } else {
-    r.v = (q2 - q1) * n + q1; r.dz = q2 - q1; r.w = w1 + w2;
-  }
+  const double d = q2 - q1;
+  const bool both = o1 && o2;
+  r.v = both ? d * n + q1 : (o1 ? q1 : (o2 ? q2 : unknown));
+  r.dz = both ? d : 0.0;
+  r.o = o1 || o2;
   return r;
 }
 __device__ __forceinline__ Q2 BlendY(const double unknown, const Q1& a, const Q1& b, const double n) {
   Q2 r;
-  if (a.w == 0.0 && b.w == 0.0) {
-    r.v = unknown; r.dy = 0.0; r.dz = 0.0; r.w = 0.0;
-  } else if (a.w == 0.0) {
-    r.v = b.v; r.dy = 0.0; r.dz = b.dz; r.w = b.w;
-  } else if (b.w == 0.0) {
-    r.v = a.v; r.dy = 0.0; r.dz = a.dz; r.w = a.w;
-  } else {
-    r.v = (b.v - a.v) * n + a.v; r.dy = b.v - a.v; r.dz = (b.dz - a.dz) * n + a.dz; r.w = a.w + b.w;
-  }
+  const bool both = a.o && b.o;
+  const double d = b.v - a.v;
+  r.v = both ? d * n + a.v : (a.o ? a.v : (b.o ? b.v : unknown));
+  r.dy = both ? d : 0.0;
+  r.dz = both ? (b.dz - a.dz) * n + a.dz : (a.o ? a.dz : (b.o ? b.dz : 0.0));
+  r.o = a.o || b.o;
   return r;
 }
 
 // Shared tail of the TSDF lookups: 7 weight-aware blends, z then y then x.
-__device__ __forceinline__ ValueGrad BlendTsdf(const double unknown, const double* w, const double* q,
+__device__ __forceinline__ ValueGrad BlendTsdf(const double unknown, const bool* o, const double* q,
                                                const double nx, const double ny, const double nz,
                                                const double sx, const double sy, const double sz) {
-  const Q1 q11 = BlendZ(unknown, q[0], q[1], w[0], w[1], nz);
-  const Q1 q12 = BlendZ(unknown, q[2], q[3], w[2], w[3], nz);
-  const Q1 q21 = BlendZ(unknown, q[4], q[5], w[4], w[5], nz);
-  const Q1 q22 = BlendZ(unknown, q[6], q[7], w[6], w[7], nz);
+  const Q1 q11 = BlendZ(unknown, q[0], q[1], o[0], o[1], nz);
+  const Q1 q12 = BlendZ(unknown, q[2], q[3], o[2], o[3], nz);
+  const Q1 q21 = BlendZ(unknown, q[4], q[5], o[4], o[5], nz);
+  const Q1 q22 = BlendZ(unknown, q[6], q[7], o[6], o[7], nz);
   const Q2 q1 = BlendY(unknown, q11, q12, ny);
   const Q2 q2 = BlendY(unknown, q21, q22, ny);
   ValueGrad r;
-  if (q1.w == 0.0 && q2.w == 0.0) {
-    r.v = unknown; r.gx = 0.0; r.gy = 0.0; r.gz = 0.0;
-  } else if (q1.w == 0.0) {
-    r.v = q2.v; r.gx = 0.0; r.gy = q2.dy * sy; r.gz = q2.dz * sz;
-  } else if (q2.w == 0.0) {
-    r.v = q1.v; r.gx = 0.0; r.gy = q1.dy * sy; r.gz = q1.dz * sz;
-  } else {
-    r.v = (q2.v - q1.v) * nx + q1.v;
-    r.gx = (q2.v - q1.v) * sx;
-    r.gy = ((q2.dy - q1.dy) * nx + q1.dy) * sy;
-    r.gz = ((q2.dz - q1.dz) * nx + q1.dz) * sz;
-  }
+  const bool both = q1.o && q2.o;
+  const double d = q2.v - q1.v;
+  r.v = both ? d * nx + q1.v : (q1.o ? q1.v : (q2.o ? q2.v : unknown));
+  r.gx = both ? d * sx : 0.0;
+  r.gy = (both ? (q2.dy - q1.dy) * nx + q1.dy : (q1.o ? q1.dy : (q2.o ? q2.dy : 0.0))) * sy;
+  r.gz = (both ? (q2.dz - q1.dz) * nx + q1.dz : (q1.o ? q1.dz : (q2.o ? q2.dz : 0.0))) * sz;
   return r;
 }
 
@@ -233,21 +276,21 @@ __device__ __forceinline__ bool LookupTsdfLevel(const GridDev& g, const double x
                                                 const double z, ValueGrad* out) {
   double x1, y1, z1, x2, y2, z2;
   int ix, iy, iz;
-  LowerVoxel(g.resolution, x, &x1, &x2, &ix);
-  LowerVoxel(g.resolution, y, &y1, &y2, &iy);
-  LowerVoxel(g.resolution, z, &z1, &z2, &iz);
+  LowerVoxel(g, x, &x1, &x2, &ix);
+  LowerVoxel(g, y, &y1, &y2, &iy);
+  LowerVoxel(g, z, &z1, &z2, &iz);
   ushort2 raw[8];
-  FetchStencil<ushort2>(g.table, ix, iy, iz, raw, [] { return make_ushort2(0, 0); });
-  double w[8];
-  int zero = 0;
+  FetchStencil<ushort2>(g.table, ix, iy, iz, raw);
+  bool o[8];
+  int observed = 0;
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    w[k] = static_cast<double>(Decode(g.b, raw[k].y));
-    zero += (w[k] == 0.0) ? 1 : 0;
+    o[k] = (raw[k].y & 0x7FFFu) > 1u;
+    observed += o[k] ? 1 : 0;
   }
   if (MULTI) {
-    if (zero > 0) return false;  // interpolated_multi_resolution_tsdf.h:99-106
-  } else if (zero == 8) {       // interpolated_tsdf.h:87-90
+    if (observed < 8) return false;  // interpolated_multi_resolution_tsdf.h:99-106
+  } else if (observed == 0) {        // interpolated_tsdf.h:87-90
     out->v = static_cast<double>(g.min_tsd);
     out->gx = out->gy = out->gz = 0.0;
     return true;
@@ -255,11 +298,26 @@ __device__ __forceinline__ bool LookupTsdfLevel(const GridDev& g, const double x
   double q[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) q[k] = static_cast<double>(Decode(g.a, raw[k].x));
-  const double sx = 1.0 / (x2 - x1), sy = 1.0 / (y2 - y1), sz = 1.0 / (z2 - z1);
-  const double nx = (x - x1) / (x2 - x1), ny = (y - y1) / (y2 - y1), nz = (z - z1) / (z2 - z1);
-  // interpolated_tsdf.h:34 hard-codes -0.3; the multi-resolution variant uses the level's minimum TSD.
-  const double unknown = MULTI ? static_cast<double>(g.min_tsd) : -0.3;
-  *out = BlendTsdf(unknown, w, q, nx, ny, nz, sx, sy, sz);
+  const double sx = CellWidthReciprocal(g.inv_resolution_d, x2 - x1);
+  const double sy = CellWidthReciprocal(g.inv_resolution_d, y2 - y1);
+  const double sz = CellWidthReciprocal(g.inv_resolution_d, z2 - z1);
+  const double nx = (x - x1) * sx, ny = (y - y1) * sy, nz = (z - z1) * sz;
+  if (MULTI) {
+    // every corner observed: plain trilinear blend (all seven blends take the lerp branch)
+    const double a0 = (q[1] - q[0]) * nz + q[0], d0 = q[1] - q[0];
+    const double a1 = (q[3] - q[2]) * nz + q[2], d1 = q[3] - q[2];
+    const double a2 = (q[5] - q[4]) * nz + q[4], d2 = q[5] - q[4];
+    const double a3 = (q[7] - q[6]) * nz + q[6], d3 = q[7] - q[6];
+    const double b0 = (a1 - a0) * ny + a0, b0y = a1 - a0, b0z = (d1 - d0) * ny + d0;
+    const double b1 = (a3 - a2) * ny + a2, b1y = a3 - a2, b1z = (d3 - d2) * ny + d2;
+    out->v = (b1 - b0) * nx + b0;
+    out->gx = (b1 - b0) * sx;
+    out->gy = ((b1y - b0y) * nx + b0y) * sy;
+    out->gz = ((b1z - b0z) * nx + b0z) * sz;
+    return true;
+  }
+  // interpolated_tsdf.h:34 hard-codes -0.3 for a pair of unobserved voxels.
+  *out = BlendTsdf(-0.3, o, q, nx, ny, nz, sx, sy, sz);
   return true;
 }
 
@@ -282,7 +340,10 @@ __device__ __forceinline__ ValueGrad Residual(const CostArgs& a, const double sc
     LookupTsdfLevel<false>(a.grids[0], x, y, z, &t);
   } else {
     bool found = false;
-    for (int l = 0; l < a.num_grids && !found; ++l) found = LookupTsdfLevel<true>(a.grids[l], x, y, z, &t);
+#pragma unroll
+    for (int l = 0; l < HG_MAX_PYRAMID_LEVELS; ++l) {
+      if (l < a.num_grids && !found) found = LookupTsdfLevel<true>(a.grids[l], x, y, z, &t);
+    }
     if (!found) {  // interpolated_multi_resolution_tsdf.h:136
       t.v = static_cast<double>(a.grids[0].min_tsd);
       t.gx = t.gy = t.gz = 0.0;

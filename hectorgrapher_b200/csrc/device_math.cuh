@@ -6,13 +6,33 @@
 
 namespace hg {
 
-// common/port.h:40-42 RoundToInt == std::lround: half away from zero.
-__device__ __forceinline__ int RoundToIntF(const float x) { return static_cast<int>(lroundf(x)); }
+// common/port.h:40-42 RoundToInt == std::lround: half away from zero. Evaluated
+// exactly without the 64-bit lroundf path: x - trunc(x) is exact in float, so
+// comparing it with +-0.5 decides the rounding without any rounding error.
+__device__ __forceinline__ int RoundToIntF(const float x) {
+  const int i = __float2int_rz(x);
+  const float f = __fsub_rn(x, __int2float_rn(i));
+  return i + (f >= 0.5f ? 1 : 0) - (f <= -0.5f ? 1 : 0);
+}
 
 // HybridGridBase::GetCellIndex for one component (hybrid_grid_base.h:428-433):
 // a true IEEE float division, then lround.
 __device__ __forceinline__ int CellIndex1(const float p, const float resolution) {
   return RoundToIntF(__fdiv_rn(p, resolution));
+}
+
+// Same result as CellIndex1, bit for bit, with the IEEE division taken only
+// when it can matter. q = p * fl(1/res) is within 1.5 * 2^-23 |q| of the
+// correctly rounded quotient; lround of the two can only differ when q's
+// fraction is that close to 0.5, so outside a 4 * 2^-23 |q| band around the
+// half-way point the product decides, inside it the exact division does.
+__device__ __forceinline__ int CellIndexFast(const float p, const float resolution,
+                                             const float inv_resolution) {
+  const float q = __fmul_rn(p, inv_resolution);
+  const int i = __float2int_rz(q);
+  const float f = fabsf(__fsub_rn(q, __int2float_rn(i)));
+  if (fabsf(f - 0.5f) <= fabsf(q) * 4.8e-7f) return CellIndex1(p, resolution);
+  return i + (f > 0.5f ? (q > 0.f ? 1 : -1) : 0);
 }
 
 // Brick id of the brick containing voxel (x, y, z), or -1.

@@ -28,6 +28,9 @@
 #include <limits>
 #include <memory>
 
+#include <chrono>
+#include <cstdlib>
+
 #include "device_math.cuh"
 #include "host/float_geometry.h"
 
@@ -37,6 +40,21 @@ namespace {
 using fgeom::Q4;
 using fgeom::Rigid;
 using fgeom::V3;
+
+// HG_TRACE=1 prints phase timings of every search to stderr.
+inline bool TraceEnabled() {
+  static const bool on = std::getenv("HG_TRACE") != nullptr;
+  return on;
+}
+struct PhaseTimer {
+  std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  double Lap() {
+    const auto t1 = std::chrono::steady_clock::now();
+    const double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    t0 = t1;
+    return ms;
+  }
+};
 
 // PrecomputationGrid3D::ToProbability (precomputation_grid_3d.h:33-36) applied to
 // sum / float(N) (fast_correlative_scan_matcher_3d.cc:380-382).
@@ -55,7 +73,7 @@ inline float ScoreFromSum(const int sum, const int num_points) {
 // exponent l.
 __global__ void __launch_bounds__(256) DiscretizeKernel(const float* __restrict__ points, const int N,
                                                         const float* __restrict__ poses, const int S,
-                                                        const float resolution, const int num_low_levels,
+                                                        const float resolution, const float inv_resolution, const int num_low_levels,
                                                         const int start_xy, const int start_z,
                                                         int* __restrict__ cells) {
   const int64_t gid = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
@@ -68,7 +86,8 @@ __global__ void __launch_bounds__(256) DiscretizeKernel(const float* __restrict_
   wx = __fadd_rn(wx, P[0]);
   wy = __fadd_rn(wy, P[1]);
   wz = __fadd_rn(wz, P[2]);
-  const int cx = CellIndex1(wx, resolution), cy = CellIndex1(wy, resolution), cz = CellIndex1(wz, resolution);
+  const int cx = CellIndexFast(wx, resolution, inv_resolution), cy = CellIndexFast(wy, resolution, inv_resolution),
+            cz = CellIndexFast(wz, resolution, inv_resolution);
   int* o = cells + gid * 3;
   o[0] = cx; o[1] = cy; o[2] = cz;
   const int64_t level_stride = static_cast<int64_t>(S) * N * 3;
@@ -118,8 +137,8 @@ __global__ void __launch_bounds__(128) LowResolutionKernel(const GridDev g, cons
     wx = __fadd_rn(wx, tx);
     wy = __fadd_rn(wy, ty);
     wz = __fadd_rn(wz, tz);
-    const int cx = CellIndex1(wx, g.resolution), cy = CellIndex1(wy, g.resolution),
-              cz = CellIndex1(wz, g.resolution);
+    const int cx = CellIndexFast(wx, g.resolution, g.inv_resolution), cy = CellIndexFast(wy, g.resolution, g.inv_resolution),
+              cz = CellIndexFast(wz, g.resolution, g.inv_resolution);
     if (g.kind == kGridProb) {
       score = __fadd_rn(score, Decode(g.a, LoadU16(g.table, cx, cy, cz)));
     } else {
@@ -317,7 +336,7 @@ int GenerateDiscreteScans(const hg_fcsm* m, const SearchParameters& sp, const hg
   HG_CUDA(cudaMemcpyAsync(out->d_poses.p, flat.data(), sizeof(float) * flat.size(), cudaMemcpyHostToDevice, stream));
   const int64_t total = static_cast<int64_t>(S) * N;
   DiscretizeKernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
-      out->d_points.as<float>(), N, out->d_poses.as<float>(), S, resolution, out->num_low_levels, -sp.wxy,
+      out->d_points.as<float>(), N, out->d_poses.as<float>(), S, resolution, 1.f / resolution, out->num_low_levels, -sp.wxy,
       -sp.wz, out->d_cells.as<int>());
   CountLaunch();
   HG_CUDA(cudaGetLastError());
@@ -440,6 +459,7 @@ class BranchAndBoundSearch {
  private:
   // GenerateLowestResolutionCandidates + ScoreCandidates(max_depth) (:328-398).
   int ScoreLowestResolution(int max_depth) {
+    PhaseTimer pt;
     const int step = 1 << max_depth;
     std::vector<Node> generated;
     for (int s = 0; s != scans_->S; ++s)
@@ -452,8 +472,10 @@ class BranchAndBoundSearch {
     if (rc != HG_OK) return rc;
     int4* hc = scorer_.h_cand.as<int4>();
     for (size_t i = 0; i < n; ++i) hc[i] = make_int4(generated[i].scan, generated[i].ox, generated[i].oy, generated[i].oz);
+    const double t_gen = pt.Lap();
     rc = scorer_.Run(max_depth, n, nullptr);
     if (rc != HG_OK) return rc;
+    const double t_gpu = pt.Lap();
     const int* sums = scorer_.h_sums.as<int>();
     for (size_t i = 0; i < n; ++i) generated[i].score = ScoreFromSum(sums[i], scans_->N);
     visited_ += static_cast<int64_t>(n);
@@ -470,6 +492,9 @@ class BranchAndBoundSearch {
     nodes_.resize(n);
     for (size_t i = 0; i < n; ++i) nodes_[i] = generated[keys[i].index];
     top_count_ = n;
+    if (TraceEnabled())
+      std::fprintf(stderr, "[hg trace] lowest level: %zu candidates, generate %.1f ms, score(H2D+kernel+D2H) %.1f ms, sort %.1f ms\n",
+                   n, t_gen, t_gpu, pt.Lap());
     return HG_OK;
   }
 
@@ -707,13 +732,19 @@ int MatchWithSearchParameters(const hg_fcsm* m, const SearchParameters& sp, cons
     ~StreamGuard() { cudaStreamDestroy(s); }
   } guard{stream};
   ScanSet scans;
+  PhaseTimer pt;
   int rc = GenerateDiscreteScans(m, sp, data, node_pose, submap_pose, shard_index, num_shards, stream, &scans);
   if (rc != HG_OK) return rc;
+  const double t_scans = pt.Lap();
   result->num_discrete_scans = scans.S;
   BranchAndBoundSearch search(m, sp, data, &scans, stream);
   BestCandidate best;
   rc = search.Run(min_score, &best);
   if (rc != HG_OK) return rc;
+  if (TraceEnabled())
+    std::fprintf(stderr, "[hg trace] search: %d scans x %d pts, window %d/%d; discretise %.1f ms, branch-and-bound %.1f ms, scored %lld visited %lld launches %d\n",
+                 scans.S, scans.N, sp.wxy, sp.wz, t_scans, pt.Lap(), static_cast<long long>(search.scored()),
+                 static_cast<long long>(search.visited()), search.launches());
   result->num_candidates_scored = search.scored();
   result->num_candidates_visited = search.visited();
   result->num_score_launches = search.launches();

@@ -168,11 +168,11 @@ __global__ void LookupKernel(const GridDev g, const int what, const int64_t n,
   out[i] = v;
 }
 
-__global__ void CellIndexKernel(const float resolution, const int64_t n,
+__global__ void CellIndexKernel(const float resolution, const float inv_resolution, const int64_t n,
                                 const float* __restrict__ p, int32_t* __restrict__ out) {
   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= 3 * n) return;
-  out[i] = CellIndex1(p[i], resolution);
+  out[i] = CellIndexFast(p[i], resolution, inv_resolution);
 }
 
 }  // namespace
@@ -199,6 +199,8 @@ int hg_grid_upload_prob(float resolution, int grid_size, int64_t num_voxels, con
   HG_CUDA(cudaGetDevice(&g->device));
   g->dev.kind = kGridProb;
   g->dev.resolution = resolution;
+  g->dev.inv_resolution = 1.f / resolution;
+  g->dev.inv_resolution_d = 1.0 / static_cast<double>(resolution);
   // probability_values.cc:56-60: unknown -> kMinProbability, range [0.1, 0.9].
   const float kMin = 0.1f, kMax = 1.f - kMin;
   g->dev.a = MakeDecode(kMin, kMin, kMax);
@@ -227,6 +229,8 @@ int hg_grid_upload_tsdf(float resolution, float relative_truncation_distance, fl
   HG_CUDA(cudaGetDevice(&g->device));
   g->dev.kind = kGridTsdf;
   g->dev.resolution = resolution;
+  g->dev.inv_resolution = 1.f / resolution;
+  g->dev.inv_resolution_d = 1.0 / static_cast<double>(resolution);
   g->relative_truncation_distance = relative_truncation_distance;
   g->max_weight = max_weight;
   // hybrid_grid_tsdf.h:65-67, tsd_value_converter.cc:22-32.
@@ -284,7 +288,7 @@ int hg_get_cell_index(float resolution, int64_t n, const float* points_xyz, int3
   HG_CUDA(cudaMalloc(&d_p, n * 3 * sizeof(float)));
   HG_CUDA(cudaMalloc(&d_o, n * 3 * sizeof(int32_t)));
   HG_CUDA(cudaMemcpy(d_p, points_xyz, n * 3 * sizeof(float), cudaMemcpyHostToDevice));
-  CellIndexKernel<<<static_cast<unsigned>((3 * n + 255) / 256), 256>>>(resolution, n, d_p, d_o);
+  CellIndexKernel<<<static_cast<unsigned>((3 * n + 255) / 256), 256>>>(resolution, 1.f / resolution, n, d_p, d_o);
   CountLaunch();
   HG_CUDA(cudaGetLastError());
   HG_CUDA(cudaMemcpy(out_xyz, d_o, n * 3 * sizeof(int32_t), cudaMemcpyDeviceToHost));

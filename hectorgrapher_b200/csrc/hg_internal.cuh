@@ -77,6 +77,8 @@ enum GridKind { kGridProb = 0, kGridTsdf = 1 };
 struct GridDev {
   BrickTable table;
   float resolution;
+  float inv_resolution;     // fl(1 / resolution): fast path of the exact cell-index computation
+  double inv_resolution_d;  // 1.0 / double(resolution): seed for the reciprocal of the cell width
   ValueDecode a;  // probability, or tsd
   ValueDecode b;  // weight (TSDF only)
   float min_tsd;  // -max_tsd
