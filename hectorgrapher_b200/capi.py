@@ -31,7 +31,7 @@ class FcsmOptions(C.Structure):
                 ("use_rotational_scan_matcher", C.c_int32), ("min_rotational_score", c_d),
                 ("min_low_resolution_score", c_d), ("linear_xy_search_window", c_d),
                 ("linear_z_search_window", c_d), ("angular_search_window", c_d),
-                ("float_flavor", C.c_int32)]
+                ("float_flavor", C.c_int32), ("strict_visit_order", C.c_int32)]
 
 
 class NodeData(C.Structure):
@@ -389,7 +389,7 @@ class Stack:
 FCSM_DEFAULTS = dict(branch_and_bound_depth=8, full_resolution_depth=3, use_rotational_scan_matcher=True,
                      min_rotational_score=0.77, min_low_resolution_score=0.55,
                      linear_xy_search_window=5.0, linear_z_search_window=1.0,
-                     angular_search_window=float(np.deg2rad(15.0)), float_flavor=1)
+                     angular_search_window=float(np.deg2rad(15.0)), float_flavor=1, strict_visit_order=0)
 
 
 def make_node_data(high, low, hist, gravity=(1, 0, 0, 0)):
@@ -429,7 +429,8 @@ class Fcsm:
         opt = FcsmOptions()
         for k, v in o.items():
             setattr(opt, k, int(v) if k in ("branch_and_bound_depth", "full_resolution_depth",
-                                            "use_rotational_scan_matcher", "float_flavor") else float(v))
+                                            "use_rotational_scan_matcher", "float_flavor",
+                                            "strict_visit_order") else float(v))
         self.opt = opt
         out = vp()
         _check(lib().hg_fcsm_create(grid.h, low_grid.h, _p(self.hist) if len(self.hist) else None,

@@ -26,6 +26,7 @@
 #include <cmath>
 #include <cstring>
 #include <limits>
+#include <map>
 #include <memory>
 
 #include <chrono>
@@ -121,6 +122,150 @@ __global__ void __launch_bounds__(256) ScoreKernel(const BrickTable level, const
   if (lane == 0) sums[warp] = sum;
 }
 
+// The lowest-resolution candidates of GenerateLowestResolutionCandidates
+// (:328-361) are a regular lattice (scan, z, y, x with step 2^max_depth), so the
+// kernel derives each candidate from its index in generation order instead of
+// reading a candidate list: nothing but the integer sums crosses PCIe.
+__global__ void __launch_bounds__(256) ScoreLatticeKernel(const BrickTable level, const int* __restrict__ cells,
+                                                          const int N, const int reduction_exponent,
+                                                          const int nxy, const int nz, const int wxy,
+                                                          const int wz, const int step,
+                                                          const int64_t num_candidates, int* __restrict__ sums) {
+  const int64_t warp = (blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= num_candidates) return;
+  const int per_scan = nxy * nxy * nz;
+  const int scan = static_cast<int>(warp / per_scan);
+  int rem = static_cast<int>(warp - static_cast<int64_t>(scan) * per_scan);
+  const int iz = rem / (nxy * nxy);
+  rem -= iz * nxy * nxy;
+  const int iy = rem / nxy;
+  const int ix = rem - iy * nxy;
+  const int ox = (-wxy + ix * step) >> reduction_exponent, oy = (-wxy + iy * step) >> reduction_exponent,
+            oz = (-wz + iz * step) >> reduction_exponent;
+  const int* base = cells + static_cast<int64_t>(scan) * N * 3;
+  int sum = 0;
+  for (int i = lane; i < N; i += 32) {
+    const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
+    sum += LoadU8(level, x + ox, y + oy, z + oz);
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+  if (lane == 0) sums[warp] = sum;
+}
+
+// Children of a wave of parents at 'depth' (the loop nest at :441-461): warp w
+// scores child slot w % 8 = (z, y, x) in {0, half}^3 of parent w / 8, so the
+// host uploads one record per parent and reads eight sums back. A child beyond
+// the search window (the reference's 'break') gets -1.
+__global__ void __launch_bounds__(256) ScoreChildrenKernel(const BrickTable level, const int* __restrict__ cells,
+                                                           const int N, const int reduction_exponent,
+                                                           const int4* __restrict__ parents,
+                                                           const int64_t num_parents, const int half,
+                                                           const int wxy, const int wz, int* __restrict__ sums) {
+  const int64_t warp = (blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= num_parents * 8) return;
+  const int4 p = parents[warp >> 3];
+  const int slot = static_cast<int>(warp & 7);
+  const int cx = p.y + ((slot & 1) ? half : 0), cy = p.z + ((slot & 2) ? half : 0), cz = p.w + ((slot & 4) ? half : 0);
+  if (cx > wxy || cy > wxy || cz > wz) {
+    if (lane == 0) sums[warp] = -1;
+    return;
+  }
+  const int ox = cx >> reduction_exponent, oy = cy >> reduction_exponent, oz = cz >> reduction_exponent;
+  const int* base = cells + static_cast<int64_t>(p.x) * N * 3;
+  int sum = 0;
+  for (int i = lane; i < N; i += 32) {
+    const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
+    sum += LoadU8(level, x + ox, y + oy, z + oz);
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+  if (lane == 0) sums[warp] = sum;
+}
+
+// Order-preserving compaction of the lattice sums that reach 'threshold':
+// count per 1024-element chunk, scan the chunk counts, then write (index, sum)
+// pairs — so only the candidates the reference's loop can reach cross PCIe.
+constexpr int kChunk = 1024;
+__global__ void __launch_bounds__(256) CountKeptKernel(const int* __restrict__ sums, const int64_t n,
+                                                       const int threshold, int* __restrict__ chunk_counts) {
+  const int64_t base = static_cast<int64_t>(blockIdx.x) * kChunk;
+  int c = 0;
+  for (int k = threadIdx.x; k < kChunk; k += 256) {
+    const int64_t i = base + k;
+    c += (i < n && sums[i] >= threshold) ? 1 : 0;
+  }
+  __shared__ int s[8];
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int w = 0; w < 8; ++w) t += s[w];
+    chunk_counts[blockIdx.x] = t;
+  }
+}
+// Single-CTA exclusive scan of the chunk counts; chunk_counts[num_chunks] receives the total.
+__global__ void __launch_bounds__(1024) ScanChunksKernel(int* __restrict__ chunk_counts, const int num_chunks) {
+  __shared__ int partial[1024];
+  const int per = (num_chunks + 1023) / 1024;
+  const int begin = threadIdx.x * per, end = min(num_chunks, begin + per);
+  int local = 0;
+  for (int i = begin; i < end; ++i) local += chunk_counts[i];
+  partial[threadIdx.x] = local;
+  __syncthreads();
+  for (int d = 1; d < 1024; d <<= 1) {
+    const int v = threadIdx.x >= d ? partial[threadIdx.x - d] : 0;
+    __syncthreads();
+    partial[threadIdx.x] += v;
+    __syncthreads();
+  }
+  int run = partial[threadIdx.x] - local;
+  for (int i = begin; i < end; ++i) {
+    const int c = chunk_counts[i];
+    chunk_counts[i] = run;
+    run += c;
+  }
+  if (threadIdx.x == 1023) chunk_counts[num_chunks] = partial[1023];
+}
+__global__ void __launch_bounds__(256) WriteKeptKernel(const int* __restrict__ sums, const int64_t n,
+                                                       const int threshold, const int* __restrict__ chunk_offsets,
+                                                       int2* __restrict__ kept) {
+  // One warp per 32 consecutive elements inside the chunk, chunks of 1024 = 32 warps' worth handled
+  // by 8 warps in 4 rounds; ballot + popc keep the order.
+  __shared__ int warp_counts[32];
+  const int64_t base = static_cast<int64_t>(blockIdx.x) * kChunk;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int my_flag[4];
+  int my_sum[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int seg = r * 8 + warp;  // segment of 32 elements, in order
+    const int64_t i = base + seg * 32 + lane;
+    const int v = i < n ? sums[i] : 0;
+    my_sum[r] = v;
+    my_flag[r] = (i < n && v >= threshold) ? 1 : 0;
+    const unsigned b = __ballot_sync(0xffffffffu, my_flag[r]);
+    if (lane == 0) warp_counts[seg] = __popc(b);
+  }
+  __syncthreads();
+  const int out_base = chunk_offsets[blockIdx.x];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int seg = r * 8 + warp;
+    int before = 0;
+    for (int k = 0; k < seg; ++k) before += warp_counts[k];
+    const unsigned b = __ballot_sync(0xffffffffu, my_flag[r]);
+    if (my_flag[r]) {
+      const int pos = out_base + before + __popc(b & ((1u << lane) - 1u));
+      kept[pos] = make_int2(static_cast<int>(base + seg * 32 + lane), my_sum[r]);
+    }
+  }
+}
+
 // LowResolutionMatcher closure: one thread per pose; the float accumulation is
 // sequential over the points in cloud order, exactly like the reference loop.
 __global__ void __launch_bounds__(128) LowResolutionKernel(const GridDev g, const float* __restrict__ points,
@@ -197,6 +342,15 @@ struct DeviceBuffer {
     HG_CUDA(cudaMalloc(&p, std::max<size_t>(bytes, 16)));
     return HG_OK;
   }
+  size_t cap = 0;
+  // Grow-only (with headroom); contents are not preserved.
+  int Reserve(size_t bytes) {
+    if (bytes <= cap) return HG_OK;
+    const size_t want = bytes + bytes / 2 + 4096;
+    const int rc = Alloc(want);
+    cap = rc == HG_OK ? want : 0;
+    return rc;
+  }
   template <typename T>
   T* as() const { return static_cast<T*>(p); }
 };
@@ -219,6 +373,23 @@ struct PinnedBuffer {
   template <typename T>
   T* as() const { return static_cast<T*>(p); }
 };
+
+// Scratch memory of the searches running on this host thread, per device.
+// Grow-only and reused from search to search: the allocations (pinned host
+// memory in particular) cost more than the kernels they serve.
+struct Workspace {
+  DeviceBuffer d_points, d_poses, d_cells;                     // discrete scans
+  DeviceBuffer d_cand, d_sums;                                 // waves
+  DeviceBuffer d_lattice, d_chunks, d_kept;                    // lowest-resolution lattice
+  DeviceBuffer d_low_points, d_low_poses, d_low_scores;        // leaf gate
+  PinnedBuffer h_cand, h_sums, h_kept, h_poses, h_low, h_count;
+};
+Workspace& GetWorkspace(int device) {
+  thread_local std::map<int, std::unique_ptr<Workspace>> spaces;
+  std::unique_ptr<Workspace>& w = spaces[device];
+  if (!w) w.reset(new Workspace);
+  return *w;
+}
 
 }  // namespace
 }  // namespace hg
@@ -247,11 +418,11 @@ struct ScanSet {
   std::vector<Rigid> poses;
   std::vector<float> rotational_scores;
   std::vector<int> global_scan_index;  // index in the unsharded scan list
-  DeviceBuffer d_points, d_poses, d_cells;
+  Workspace* ws = nullptr;  // owns d_points / d_poses / d_cells
   // Cells of depth d live at level max(0, d - frd + 1).
   const int* CellsOfDepth(int depth) const {
     const int level = std::max(0, depth - frd + 1);
-    return d_cells.as<int>() + static_cast<int64_t>(level) * S * N * 3;
+    return ws->d_cells.as<int>() + static_cast<int64_t>(level) * S * N * 3;
   }
 };
 
@@ -319,12 +490,14 @@ int GenerateDiscreteScans(const hg_fcsm* m, const SearchParameters& sp, const hg
   out->num_low_levels = D - out->frd;
   if (S == 0) return HG_OK;
 
-  int rc = out->d_points.Alloc(sizeof(float) * 3 * N);
+  Workspace& ws = GetWorkspace(m->device);
+  out->ws = &ws;
+  int rc = ws.d_points.Reserve(sizeof(float) * 3 * N);
   if (rc != HG_OK) return rc;
-  rc = out->d_poses.Alloc(sizeof(float) * 7 * S);
+  rc = ws.d_poses.Reserve(sizeof(float) * 7 * S);
   if (rc != HG_OK) return rc;
   const size_t cell_ints = static_cast<size_t>(1 + out->num_low_levels) * S * N * 3;
-  rc = out->d_cells.Alloc(sizeof(int) * cell_ints);
+  rc = ws.d_cells.Reserve(sizeof(int) * cell_ints);
   if (rc != HG_OK) return rc;
   std::vector<float> flat(7 * static_cast<size_t>(S));
   for (int s = 0; s < S; ++s) {
@@ -332,49 +505,45 @@ int GenerateDiscreteScans(const hg_fcsm* m, const SearchParameters& sp, const hg
     float* o = &flat[7 * s];
     o[0] = r.t.x; o[1] = r.t.y; o[2] = r.t.z; o[3] = r.q.w; o[4] = r.q.x; o[5] = r.q.y; o[6] = r.q.z;
   }
-  HG_CUDA(cudaMemcpyAsync(out->d_points.p, pts, sizeof(float) * 3 * N, cudaMemcpyHostToDevice, stream));
-  HG_CUDA(cudaMemcpyAsync(out->d_poses.p, flat.data(), sizeof(float) * flat.size(), cudaMemcpyHostToDevice, stream));
+  HG_CUDA(cudaMemcpyAsync(ws.d_points.p, pts, sizeof(float) * 3 * N, cudaMemcpyHostToDevice, stream));
+  HG_CUDA(cudaMemcpyAsync(ws.d_poses.p, flat.data(), sizeof(float) * flat.size(), cudaMemcpyHostToDevice, stream));
   const int64_t total = static_cast<int64_t>(S) * N;
   DiscretizeKernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
-      out->d_points.as<float>(), N, out->d_poses.as<float>(), S, resolution, 1.f / resolution, out->num_low_levels, -sp.wxy,
-      -sp.wz, out->d_cells.as<int>());
+      ws.d_points.as<float>(), N, ws.d_poses.as<float>(), S, resolution, 1.f / resolution, out->num_low_levels, -sp.wxy,
+      -sp.wz, ws.d_cells.as<int>());
   CountLaunch();
   HG_CUDA(cudaGetLastError());
   HG_CUDA(cudaStreamSynchronize(stream));  // 'flat' goes out of scope
   return HG_OK;
 }
 
-// Scores candidate records on the device; synchronous. 'kernel_ms' optional.
+// Scores candidates on the device; synchronous. Buffers live in the thread's workspace.
 struct Scorer {
   const hg_fcsm* m;
   const ScanSet* scans;
   cudaStream_t stream;
-  DeviceBuffer d_cand, d_sums;
-  size_t cap = 0;
-  PinnedBuffer h_cand, h_sums;
+  Workspace* ws;
   int64_t total_scored = 0;
   int launches = 0;
 
+  int ReduceExponent(int depth) const { return std::max(0, depth - m->options.full_resolution_depth + 1); }
+
   int Reserve(size_t n) {
-    int rc = h_cand.Reserve(n * sizeof(int4));
+    int rc = ws->h_cand.Reserve(n * sizeof(int4));
     if (rc != HG_OK) return rc;
-    rc = h_sums.Reserve(n * sizeof(int));
+    rc = ws->h_sums.Reserve(n * 8 * sizeof(int));
     if (rc != HG_OK) return rc;
-    if (n > cap) {
-      const size_t want = std::max<size_t>(n * 2, 4096);
-      rc = d_cand.Alloc(want * sizeof(int4));
-      if (rc != HG_OK) return rc;
-      rc = d_sums.Alloc(want * sizeof(int));
-      if (rc != HG_OK) return rc;
-      cap = want;
-    }
-    return HG_OK;
+    rc = ws->d_cand.Reserve(n * sizeof(int4));
+    if (rc != HG_OK) return rc;
+    return ws->d_sums.Reserve(n * 8 * sizeof(int));
   }
-  // Candidates must already be in h_cand (n records). Results land in h_sums.
+  int4* HostCandidates() const { return ws->h_cand.as<int4>(); }
+  const int* HostSums() const { return ws->h_sums.as<int>(); }
+
+  // Explicit candidates (already in HostCandidates(), n records) -> HostSums()[n].
   int Run(int depth, size_t n, float* kernel_ms) {
     if (n == 0) return HG_OK;
-    const int e = std::max(0, depth - m->options.full_resolution_depth + 1);
-    HG_CUDA(cudaMemcpyAsync(d_cand.p, h_cand.p, n * sizeof(int4), cudaMemcpyHostToDevice, stream));
+    HG_CUDA(cudaMemcpyAsync(ws->d_cand.p, ws->h_cand.p, n * sizeof(int4), cudaMemcpyHostToDevice, stream));
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (kernel_ms) {
       HG_CUDA(cudaEventCreate(&e0));
@@ -383,12 +552,12 @@ struct Scorer {
     }
     const int64_t threads = static_cast<int64_t>(n) * 32;
     ScoreKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
-        m->stack->levels[depth].table, scans->CellsOfDepth(depth), scans->N, e, d_cand.as<int4>(),
-        static_cast<int64_t>(n), d_sums.as<int>());
+        m->stack->levels[depth].table, scans->CellsOfDepth(depth), scans->N, ReduceExponent(depth),
+        ws->d_cand.as<int4>(), static_cast<int64_t>(n), ws->d_sums.as<int>());
     CountLaunch();
     HG_CUDA(cudaGetLastError());
     if (kernel_ms) HG_CUDA(cudaEventRecord(e1, stream));
-    HG_CUDA(cudaMemcpyAsync(h_sums.p, d_sums.p, n * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    HG_CUDA(cudaMemcpyAsync(ws->h_sums.p, ws->d_sums.p, n * sizeof(int), cudaMemcpyDeviceToHost, stream));
     HG_CUDA(cudaStreamSynchronize(stream));
     if (kernel_ms) {
       float ms = 0.f;
@@ -399,6 +568,81 @@ struct Scorer {
     }
     total_scored += static_cast<int64_t>(n);
     ++launches;
+    return HG_OK;
+  }
+
+  // Children of n parents (records in HostCandidates()) scored at 'child_depth':
+  // HostSums()[8 n], -1 where the child lies beyond the window.
+  int RunChildren(int child_depth, size_t n, int half, int wxy, int wz) {
+    if (n == 0) return HG_OK;
+    HG_CUDA(cudaMemcpyAsync(ws->d_cand.p, ws->h_cand.p, n * sizeof(int4), cudaMemcpyHostToDevice, stream));
+    const int64_t threads = static_cast<int64_t>(n) * 8 * 32;
+    ScoreChildrenKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
+        m->stack->levels[child_depth].table, scans->CellsOfDepth(child_depth), scans->N,
+        ReduceExponent(child_depth), ws->d_cand.as<int4>(), static_cast<int64_t>(n), half, wxy, wz,
+        ws->d_sums.as<int>());
+    CountLaunch();
+    HG_CUDA(cudaGetLastError());
+    HG_CUDA(cudaMemcpyAsync(ws->h_sums.p, ws->d_sums.p, n * 8 * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    HG_CUDA(cudaStreamSynchronize(stream));
+    ++launches;
+    return HG_OK;
+  }
+
+  // Scores the whole lowest-resolution lattice into ws->d_lattice (generation order).
+  int RunLattice(int depth, int nxy, int nz, int wxy, int wz, size_t n) {
+    if (n == 0) return HG_OK;
+    int rc = ws->d_lattice.Reserve(n * sizeof(int));
+    if (rc != HG_OK) return rc;
+    const int64_t threads = static_cast<int64_t>(n) * 32;
+    ScoreLatticeKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
+        m->stack->levels[depth].table, scans->CellsOfDepth(depth), scans->N, ReduceExponent(depth), nxy, nz, wxy,
+        wz, 1 << depth, static_cast<int64_t>(n), ws->d_lattice.as<int>());
+    CountLaunch();
+    HG_CUDA(cudaGetLastError());
+    total_scored += static_cast<int64_t>(n);
+    ++launches;
+    return HG_OK;
+  }
+  // All lattice sums to the host (strict order needs every one).
+  int DownloadLattice(size_t n, std::vector<int>* out) {
+    out->resize(n);
+    if (n == 0) return HG_OK;
+    HG_CUDA(cudaMemcpyAsync(out->data(), ws->d_lattice.p, n * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    HG_CUDA(cudaStreamSynchronize(stream));
+    return HG_OK;
+  }
+  // (generation index, sum) of the lattice candidates with sum >= threshold, in generation order.
+  int DownloadKept(size_t n, int threshold, std::vector<int2>* out) {
+    out->clear();
+    if (n == 0) return HG_OK;
+    const int chunks = static_cast<int>((n + kChunk - 1) / kChunk);
+    int rc = ws->d_chunks.Reserve((chunks + 1) * sizeof(int));
+    if (rc != HG_OK) return rc;
+    rc = ws->h_count.Reserve(sizeof(int));
+    if (rc != HG_OK) return rc;
+    CountKeptKernel<<<chunks, 256, 0, stream>>>(ws->d_lattice.as<int>(), static_cast<int64_t>(n), threshold,
+                                                ws->d_chunks.as<int>());
+    ScanChunksKernel<<<1, 1024, 0, stream>>>(ws->d_chunks.as<int>(), chunks);
+    CountLaunch(2);
+    HG_CUDA(cudaGetLastError());
+    HG_CUDA(cudaMemcpyAsync(ws->h_count.p, ws->d_chunks.as<int>() + chunks, sizeof(int), cudaMemcpyDeviceToHost,
+                            stream));
+    HG_CUDA(cudaStreamSynchronize(stream));
+    const int kept = *ws->h_count.as<int>();
+    if (kept == 0) return HG_OK;
+    rc = ws->d_kept.Reserve(static_cast<size_t>(kept) * sizeof(int2));
+    if (rc != HG_OK) return rc;
+    rc = ws->h_kept.Reserve(static_cast<size_t>(kept) * sizeof(int2));
+    if (rc != HG_OK) return rc;
+    WriteKeptKernel<<<chunks, 256, 0, stream>>>(ws->d_lattice.as<int>(), static_cast<int64_t>(n), threshold,
+                                                ws->d_chunks.as<int>(), ws->d_kept.as<int2>());
+    CountLaunch();
+    HG_CUDA(cudaGetLastError());
+    HG_CUDA(cudaMemcpyAsync(ws->h_kept.p, ws->d_kept.p, static_cast<size_t>(kept) * sizeof(int2),
+                            cudaMemcpyDeviceToHost, stream));
+    HG_CUDA(cudaStreamSynchronize(stream));
+    out->assign(ws->h_kept.as<int2>(), ws->h_kept.as<int2>() + kept);
     return HG_OK;
   }
 };
@@ -414,6 +658,8 @@ struct Node {
   int num_children;
 };
 
+constexpr int kChildrenPruned = -2;  // expanded; no child beat the bound, so none was materialised
+
 struct BestCandidate {
   int node = -1;
   float score = -std::numeric_limits<float>::infinity();
@@ -425,20 +671,65 @@ class BranchAndBoundSearch {
   BranchAndBoundSearch(const hg_fcsm* m, const SearchParameters& sp, const hg_node_data* data,
                        const ScanSet* scans, cudaStream_t stream)
       : m_(m), sp_(sp), data_(data), scans_(scans), stream_(stream) {
+    ws_ = &GetWorkspace(m->device);
     scorer_.m = m;
     scorer_.scans = scans;
     scorer_.stream = stream;
+    scorer_.ws = ws_;
   }
 
-  int Run(float min_score, BestCandidate* best_out) {
+  // strict = reproduce the reference's visiting order candidate by candidate.
+  // Otherwise the search runs on the reachable candidates only and returns the
+  // same candidate: the answer is the best valid leaf, ties going to the leaf
+  // the reference visits first; the only tie the fast order cannot settle by
+  // itself is one between top-level subtrees of equal score, which is detected
+  // afterwards (a probe of the winner's equal-score twins) and, if real,
+  // settled by rerunning in strict order.
+  int Run(float min_score, bool strict, BestCandidate* best_out) {
     const int max_depth = m_->options.branch_and_bound_depth - 1;
-    int rc = ScoreLowestResolution(max_depth);
+    strict_ = strict;
+    int rc = UploadLowResolutionCloud();
     if (rc != HG_OK) return rc;
-    rc = UploadLowResolutionCloud();
+    rc = ScoreLowestResolution(max_depth, min_score, strict, nullptr);
     if (rc != HG_OK) return rc;
     failed_ = HG_OK;
-    const BestCandidate best = Search(0, static_cast<int>(top_count_), max_depth, min_score);
+    BestCandidate best = Search(0, static_cast<int>(top_count_), max_depth, min_score);
     if (failed_ != HG_OK) return failed_;
+    if (!strict && best.node >= 0 && best.score > min_score) {
+      // Top-level ancestor of the winner and its equal-score twins.
+      const int ancestor = TopAncestor(best.node);
+      std::vector<int> twins;
+      for (size_t i = 0; i < top_count_; ++i)
+        if (static_cast<int>(i) != ancestor && nodes_[i].score == nodes_[ancestor].score) twins.push_back(top_index_[i]);
+      if (!twins.empty()) {
+        // Does a twin subtree hold a valid leaf with the winning score?
+        const Node winner = nodes_[best.node];
+        const float winner_low = best.low_resolution_score;
+        const float below = std::nextafter(best.score, -std::numeric_limits<float>::infinity());
+        strict_ = true;
+        wave_budget_ = 8;
+        rc = ScoreLowestResolution(max_depth, below, true, &twins);
+        if (rc != HG_OK) return rc;
+        const BestCandidate probe = Search(0, static_cast<int>(top_count_), max_depth, below);
+        if (failed_ != HG_OK) return failed_;
+        if (probe.node >= 0 && probe.score >= best.score) {
+          // A real tie across equal-score subtrees: only the strict order settles it.
+          if (TraceEnabled()) std::fprintf(stderr, "[hg trace] tie across twin subtrees: strict rerun\n");
+          wave_budget_ = 8;
+          rc = ScoreLowestResolution(max_depth, min_score, true, nullptr);
+          if (rc != HG_OK) return rc;
+          best = Search(0, static_cast<int>(top_count_), max_depth, min_score);
+          if (failed_ != HG_OK) return failed_;
+        } else {
+          // Keep the winner; re-home it in the (rebuilt) node table.
+          nodes_.clear();
+          nodes_.push_back(winner);
+          top_count_ = 0;
+          best.node = 0;
+          best.low_resolution_score = winner_low;
+        }
+      }
+    }
     *best_out = best;
     return HG_OK;
   }
@@ -458,52 +749,87 @@ class BranchAndBoundSearch {
 
  private:
   // GenerateLowestResolutionCandidates + ScoreCandidates(max_depth) (:328-398).
-  int ScoreLowestResolution(int max_depth) {
+  // strict: every candidate is kept and sorted exactly like the reference
+  // (std::sort over the generation order). Otherwise only candidates the
+  // reference's loop can reach (score > min_score, :437-440) are kept and sorted;
+  // their relative order can differ from the strict order only among equal scores.
+  int ScoreLowestResolution(int max_depth, float min_score, bool strict, const std::vector<int>* only) {
     PhaseTimer pt;
     const int step = 1 << max_depth;
-    std::vector<Node> generated;
-    for (int s = 0; s != scans_->S; ++s)
-      for (int z = -sp_.wz; z <= sp_.wz; z += step)
-        for (int y = -sp_.wxy; y <= sp_.wxy; y += step)
-          for (int x = -sp_.wxy; x <= sp_.wxy; x += step)
-            generated.push_back(Node{s, x, y, z, 0.f, std::numeric_limits<float>::quiet_NaN(), -1, 0});
-    const size_t n = generated.size();
-    int rc = scorer_.Reserve(n);
-    if (rc != HG_OK) return rc;
-    int4* hc = scorer_.h_cand.as<int4>();
-    for (size_t i = 0; i < n; ++i) hc[i] = make_int4(generated[i].scan, generated[i].ox, generated[i].oy, generated[i].oz);
-    const double t_gen = pt.Lap();
-    rc = scorer_.Run(max_depth, n, nullptr);
-    if (rc != HG_OK) return rc;
-    const double t_gpu = pt.Lap();
-    const int* sums = scorer_.h_sums.as<int>();
-    for (size_t i = 0; i < n; ++i) generated[i].score = ScoreFromSum(sums[i], scans_->N);
-    visited_ += static_cast<int64_t>(n);
-    // std::sort(..., std::greater<Candidate3D>()) over the generation order: the
-    // comparator only looks at the score, so sorting (score, index) keys with
-    // the same algorithm yields the reference's permutation, ties included.
+    const int nxy = (2 * sp_.wxy + step) / step, nz = (2 * sp_.wz + step) / step;
+    const int per_scan = nxy * nxy * nz;
+    const size_t n = static_cast<size_t>(scans_->S) * per_scan;
+    if (!lattice_scored_) {
+      int rc = scorer_.RunLattice(max_depth, nxy, nz, sp_.wxy, sp_.wz, n);
+      if (rc != HG_OK) return rc;
+      lattice_scored_ = true;
+      visited_ += static_cast<int64_t>(n);
+    }
+    // score(sum) is non-decreasing in sum: the smallest sum whose score beats min_score.
+    int64_t lo = 0, hi = static_cast<int64_t>(255) * scans_->N + 1;
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) / 2;
+      if (ScoreFromSum(static_cast<int>(mid), scans_->N) > min_score) hi = mid; else lo = mid + 1;
+    }
     struct Key {
       float score;
       uint32_t index;
     };
-    std::vector<Key> keys(n);
-    for (size_t i = 0; i < n; ++i) keys[i] = Key{generated[i].score, static_cast<uint32_t>(i)};
+    std::vector<Key> keys;
+    if (only != nullptr || strict) {
+      // Every sum is needed on the host.
+      if (h_lattice_sums_.size() != n) {
+        const int rc = scorer_.DownloadLattice(n, &h_lattice_sums_);
+        if (rc != HG_OK) return rc;
+      }
+      const int* sums = h_lattice_sums_.data();
+      if (only != nullptr) {
+        for (int i : *only) keys.push_back(Key{ScoreFromSum(sums[i], scans_->N), static_cast<uint32_t>(i)});
+      } else {
+        keys.reserve(n);
+        for (size_t i = 0; i < n; ++i) keys.push_back(Key{ScoreFromSum(sums[i], scans_->N), static_cast<uint32_t>(i)});
+      }
+    } else {
+      std::vector<int2> kept;
+      const int rc = scorer_.DownloadKept(n, static_cast<int>(lo), &kept);
+      if (rc != HG_OK) return rc;
+      keys.reserve(kept.size());
+      for (const int2& k : kept) keys.push_back(Key{ScoreFromSum(k.y, scans_->N), static_cast<uint32_t>(k.x)});
+    }
+    const double t_gpu = pt.Lap();
+    // std::sort(..., std::greater<Candidate3D>()) over the generation order: the
+    // comparator only looks at the score, so sorting (score, index) keys with
+    // the same algorithm yields the reference's permutation, ties included.
     std::sort(keys.begin(), keys.end(), [](const Key& a, const Key& b) { return a.score > b.score; });
-    nodes_.resize(n);
-    for (size_t i = 0; i < n; ++i) nodes_[i] = generated[keys[i].index];
-    top_count_ = n;
+    nodes_.clear();
+    nodes_.reserve(keys.size() * 2);
+    top_index_.clear();
+    for (const Key& k : keys) {
+      const int scan = static_cast<int>(k.index / per_scan);
+      int rem = static_cast<int>(k.index - static_cast<size_t>(scan) * per_scan);
+      const int iz = rem / (nxy * nxy);
+      rem -= iz * nxy * nxy;
+      const int iy = rem / nxy;
+      const int ix = rem - iy * nxy;
+      nodes_.push_back(Node{scan, -sp_.wxy + ix * step, -sp_.wxy + iy * step, -sp_.wz + iz * step, k.score,
+                            std::numeric_limits<float>::quiet_NaN(), -1, 0});
+      top_index_.push_back(static_cast<int>(k.index));
+    }
+    top_count_ = keys.size();
+    parent_of_.assign(nodes_.size(), -1);
+    leaves_pending_.clear();
     if (TraceEnabled())
-      std::fprintf(stderr, "[hg trace] lowest level: %zu candidates, generate %.1f ms, score(H2D+kernel+D2H) %.1f ms, sort %.1f ms\n",
-                   n, t_gen, t_gpu, pt.Lap());
+      std::fprintf(stderr, "[hg trace] lowest level: %zu candidates (%zu kept), score+select %.1f ms, sort+nodes %.1f ms\n",
+                   n, keys.size(), t_gpu, pt.Lap());
     return HG_OK;
   }
 
   int UploadLowResolutionCloud() {
     const int n = data_->num_low_resolution_points;
     if (n <= 0) return HG_OK;
-    int rc = d_low_points_.Alloc(sizeof(float) * 3 * n);
+    int rc = ws_->d_low_points.Reserve(sizeof(float) * 3 * n);
     if (rc != HG_OK) return rc;
-    HG_CUDA(cudaMemcpyAsync(d_low_points_.p, data_->low_resolution_point_cloud, sizeof(float) * 3 * n,
+    HG_CUDA(cudaMemcpyAsync(ws_->d_low_points.p, data_->low_resolution_point_cloud, sizeof(float) * 3 * n,
                             cudaMemcpyHostToDevice, stream_));
     return HG_OK;
   }
@@ -534,32 +860,16 @@ class BranchAndBoundSearch {
     best.score = min_score;
     for (int i = begin; i < begin + count; ++i) {
       if (nodes_[i].score <= min_score) break;
-      if (nodes_[i].first_child < 0) {
+      if (nodes_[i].first_child == -1) {
         failed_ = Speculate(begin, count, i, depth, min_score, best.score);
         if (failed_ != HG_OK) return unsuccessful;
       }
       visited_ += nodes_[i].num_children;
+      if (nodes_[i].first_child == kChildrenPruned) continue;  // every child <= a bound that best.score has reached
       const BestCandidate sub = Search(nodes_[i].first_child, nodes_[i].num_children, depth - 1, best.score);
       if (best.score < sub.score) best = sub;  // std::max(best, sub): the earlier one wins ties
     }
     return best;
-  }
-
-  // Children of a node in generation order (z outer, y, x inner; 'break' on the
-  // window edge, :441-461).
-  void AppendChildren(const Node& parent, int depth, std::vector<Node>* out) const {
-    const int half_width = 1 << (depth - 1);
-    for (int z : {0, half_width}) {
-      if (parent.oz + z > sp_.wz) break;
-      for (int y : {0, half_width}) {
-        if (parent.oy + y > sp_.wxy) break;
-        for (int x : {0, half_width}) {
-          if (parent.ox + x > sp_.wxy) break;
-          out->push_back(Node{parent.scan, parent.ox + x, parent.oy + y, parent.oz + z, 0.f,
-                              std::numeric_limits<float>::quiet_NaN(), -1, 0});
-        }
-      }
-    }
   }
 
   // Expands nodes_[trigger ..) of the sibling list [begin, begin+count) — every
@@ -573,49 +883,76 @@ class BranchAndBoundSearch {
     std::vector<int> wave;
     for (int i = trigger; i < begin + count; ++i) {
       if (nodes_[i].score <= list_min_score) break;
-      if (nodes_[i].first_child < 0) wave.push_back(i);
+      if (nodes_[i].first_child == -1) wave.push_back(i);
       if (static_cast<int64_t>(wave.size()) >= wave_budget_) break;
     }
     const int64_t budget = wave_budget_;
     wave_budget_ = std::min<int64_t>(wave_budget_ * 8, int64_t(1) << 17);
-    std::vector<Node> children;
-    std::vector<int> child_begin;
+    Node kids[8];
     for (int d = depth; d >= 1 && !wave.empty(); --d) {
-      children.clear();
-      child_begin.clear();
-      for (int p : wave) {
-        child_begin.push_back(static_cast<int>(children.size()));
-        AppendChildren(nodes_[p], d, &children);
+      const size_t np = wave.size();
+      int rc = scorer_.Reserve(np);
+      if (rc != HG_OK) return rc;
+      int4* hc = scorer_.HostCandidates();
+      for (size_t i = 0; i < np; ++i) {
+        const Node& p = nodes_[wave[i]];
+        hc[i] = make_int4(p.scan, p.ox, p.oy, p.oz);
       }
-      child_begin.push_back(static_cast<int>(children.size()));
-      const size_t n = children.size();
-      int rc = scorer_.Reserve(n);
+      const int half_width = 1 << (d - 1);
+      rc = scorer_.RunChildren(d - 1, np, half_width, sp_.wxy, sp_.wz);
       if (rc != HG_OK) return rc;
-      int4* hc = scorer_.h_cand.as<int4>();
-      for (size_t i = 0; i < n; ++i) hc[i] = make_int4(children[i].scan, children[i].ox, children[i].oy, children[i].oz);
-      rc = scorer_.Run(d - 1, n, nullptr);
-      if (rc != HG_OK) return rc;
-      const int* sums = scorer_.h_sums.as<int>();
-      for (size_t i = 0; i < n; ++i) children[i].score = ScoreFromSum(sums[i], scans_->N);
+      const int* sums = scorer_.HostSums();
+      // Smallest child sum that beats the bound (score is non-decreasing in the sum).
+      int64_t lo = 0, hi = static_cast<int64_t>(255) * scans_->N + 1;
+      while (lo < hi) {
+        const int64_t mid = (lo + hi) / 2;
+        if (ScoreFromSum(static_cast<int>(mid), scans_->N) > bound) hi = mid; else lo = mid + 1;
+      }
+      const int beats_bound = static_cast<int>(lo);
       std::vector<int> next;
-      for (size_t w = 0; w < wave.size(); ++w) {
-        Node* first = children.data() + child_begin[w];
-        const int nc = child_begin[w + 1] - child_begin[w];
-        // std::sort on <= 16 elements is an insertion sort in libstdc++: stable
-        // in generation order for equal scores.
+      for (size_t w = 0; w < np; ++w) {
+        const int* cs = sums + 8 * w;
+        int nc = 0, best_sum = -1;
+        for (int slot = 0; slot < 8; ++slot) {
+          if (cs[slot] < 0) continue;
+          ++nc;
+          best_sum = std::max(best_sum, cs[slot]);
+        }
+        scorer_.total_scored += nc;
+        Node& parent = nodes_[wave[w]];
+        if (!strict_ && best_sum < beats_bound) {
+          // The recursion into these children would stop at the first one
+          // (:437-440 / :414-419 with min_score = running best >= bound).
+          parent.first_child = kChildrenPruned;
+          parent.num_children = nc;
+          continue;
+        }
+        // Materialise in generation order (z outer, y, x inner), then the
+        // reference's sort: std::sort on <= 16 elements is an insertion sort in
+        // libstdc++, stable in generation order for equal scores.
+        int k = 0;
+        for (int slot = 0; slot < 8; ++slot) {
+          if (cs[slot] < 0) continue;
+          kids[k++] = Node{parent.scan, parent.ox + ((slot & 1) ? half_width : 0),
+                           parent.oy + ((slot & 2) ? half_width : 0), parent.oz + ((slot & 4) ? half_width : 0),
+                           ScoreFromSum(cs[slot], scans_->N), std::numeric_limits<float>::quiet_NaN(), -1, 0};
+        }
         for (int a = 1; a < nc; ++a) {
-          const Node v = first[a];
+          const Node v = kids[a];
           int b = a - 1;
-          while (b >= 0 && v.score > first[b].score) {
-            first[b + 1] = first[b];
+          while (b >= 0 && v.score > kids[b].score) {
+            kids[b + 1] = kids[b];
             --b;
           }
-          first[b + 1] = v;
+          kids[b + 1] = v;
         }
         const int at = static_cast<int>(nodes_.size());
-        nodes_.insert(nodes_.end(), first, first + nc);
-        nodes_[wave[w]].first_child = at;
-        nodes_[wave[w]].num_children = nc;
+        const int parent_index = wave[w];
+        nodes_.insert(nodes_.end(), kids, kids + nc);  // may reallocate: 'parent' is dead from here
+        parent_of_.resize(nodes_.size(), -1);
+        for (int c = 0; c < nc; ++c) parent_of_[at + c] = parent_index;
+        nodes_[parent_index].first_child = at;
+        nodes_[parent_index].num_children = nc;
         if (d - 1 >= 1) {
           for (int c = 0; c < nc; ++c) {
             if (nodes_[at + c].score <= bound) break;
@@ -663,35 +1000,37 @@ class BranchAndBoundSearch {
       for (int idx : leaves) nodes_[idx].low_resolution_score = -std::numeric_limits<float>::infinity();
       return HG_OK;
     }
-    int rc = h_poses_.Reserve(n * 7 * sizeof(float));
+    int rc = ws_->h_poses.Reserve(n * 7 * sizeof(float));
     if (rc != HG_OK) return rc;
-    rc = h_low_.Reserve(n * sizeof(float));
+    rc = ws_->h_low.Reserve(n * sizeof(float));
     if (rc != HG_OK) return rc;
-    if (n > low_cap_) {
-      low_cap_ = std::max<size_t>(2 * n, 1024);
-      rc = d_low_poses_.Alloc(low_cap_ * 7 * sizeof(float));
-      if (rc != HG_OK) return rc;
-      rc = d_low_scores_.Alloc(low_cap_ * sizeof(float));
-      if (rc != HG_OK) return rc;
-    }
-    float* hp = h_poses_.as<float>();
+    rc = ws_->d_low_poses.Reserve(n * 7 * sizeof(float));
+    if (rc != HG_OK) return rc;
+    rc = ws_->d_low_scores.Reserve(n * sizeof(float));
+    if (rc != HG_OK) return rc;
+    float* hp = ws_->h_poses.as<float>();
     for (size_t k = 0; k < n; ++k) {
       const Rigid r = PoseOf(nodes_[leaves[k]]);
       float* o = hp + 7 * k;
       o[0] = r.t.x; o[1] = r.t.y; o[2] = r.t.z; o[3] = r.q.w; o[4] = r.q.x; o[5] = r.q.y; o[6] = r.q.z;
     }
-    HG_CUDA(cudaMemcpyAsync(d_low_poses_.p, hp, n * 7 * sizeof(float), cudaMemcpyHostToDevice, stream_));
+    HG_CUDA(cudaMemcpyAsync(ws_->d_low_poses.p, hp, n * 7 * sizeof(float), cudaMemcpyHostToDevice, stream_));
     LowResolutionKernel<<<static_cast<unsigned>((n + 127) / 128), 128, 0, stream_>>>(
-        m_->low_grid->dev, d_low_points_.as<float>(), np, d_low_poses_.as<float>(), static_cast<int64_t>(n),
-        d_low_scores_.as<float>());
+        m_->low_grid->dev, ws_->d_low_points.as<float>(), np, ws_->d_low_poses.as<float>(), static_cast<int64_t>(n),
+        ws_->d_low_scores.as<float>());
     CountLaunch();
     ++low_launches_;
     HG_CUDA(cudaGetLastError());
-    HG_CUDA(cudaMemcpyAsync(h_low_.p, d_low_scores_.p, n * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+    HG_CUDA(cudaMemcpyAsync(ws_->h_low.p, ws_->d_low_scores.p, n * sizeof(float), cudaMemcpyDeviceToHost, stream_));
     HG_CUDA(cudaStreamSynchronize(stream_));
-    const float* hs = h_low_.as<float>();
+    const float* hs = ws_->h_low.as<float>();
     for (size_t k = 0; k < n; ++k) nodes_[leaves[k]].low_resolution_score = hs[k];
     return HG_OK;
+  }
+
+  int TopAncestor(int node) const {
+    while (node >= static_cast<int>(top_count_)) node = parent_of_[node];
+    return node;
   }
 
   const hg_fcsm* m_;
@@ -700,6 +1039,12 @@ class BranchAndBoundSearch {
   const ScanSet* scans_;
   cudaStream_t stream_;
   Scorer scorer_;
+  bool strict_ = false;
+  Workspace* ws_ = nullptr;
+  bool lattice_scored_ = false;
+  std::vector<int> h_lattice_sums_;  // lowest-resolution sums in generation order (strict / probe only)
+  std::vector<int> top_index_;       // generation index of nodes_[0 .. top_count_)
+  std::vector<int> parent_of_;
   std::vector<Node> nodes_;
   size_t top_count_ = 0;
   int64_t visited_ = 0;
@@ -707,9 +1052,6 @@ class BranchAndBoundSearch {
   int failed_ = HG_OK;
   int low_launches_ = 0;
   std::vector<int> leaves_pending_;
-  DeviceBuffer d_low_points_, d_low_poses_, d_low_scores_;
-  size_t low_cap_ = 0;
-  PinnedBuffer h_poses_, h_low_;
 };
 
 Rigid ToRigidF(const double* t, const double* q) {
@@ -739,7 +1081,7 @@ int MatchWithSearchParameters(const hg_fcsm* m, const SearchParameters& sp, cons
   result->num_discrete_scans = scans.S;
   BranchAndBoundSearch search(m, sp, data, &scans, stream);
   BestCandidate best;
-  rc = search.Run(min_score, &best);
+  rc = search.Run(min_score, m->options.strict_visit_order != 0, &best);
   if (rc != HG_OK) return rc;
   if (TraceEnabled())
     std::fprintf(stderr, "[hg trace] search: %d scans x %d pts, window %d/%d; discretise %.1f ms, branch-and-bound %.1f ms, scored %lld visited %lld launches %d\n",
@@ -914,13 +1256,14 @@ int hg_fcsm_score_candidates(const hg_fcsm* m, int wxy, int wz, double angular_s
   scorer.m = m;
   scorer.scans = &scans;
   scorer.stream = nullptr;
+  scorer.ws = &GetWorkspace(m->device);
   rc = scorer.Reserve(static_cast<size_t>(num_candidates));
   if (rc != HG_OK) return rc;
-  std::memcpy(scorer.h_cand.p, candidates, static_cast<size_t>(num_candidates) * sizeof(int4));
+  std::memcpy(scorer.HostCandidates(), candidates, static_cast<size_t>(num_candidates) * sizeof(int4));
   if (kernel_ms) *kernel_ms = 0.f;
   rc = scorer.Run(depth, static_cast<size_t>(num_candidates), kernel_ms);
   if (rc != HG_OK) return rc;
-  const int* hs = scorer.h_sums.as<int>();
+  const int* hs = scorer.HostSums();
   for (int64_t i = 0; i < num_candidates; ++i) {
     if (sums) sums[i] = hs[i];
     if (scores) scores[i] = ScoreFromSum(hs[i], scans.N);

@@ -209,6 +209,11 @@ typedef struct hg_fcsm_options {
   /* 1 = Eigen's SSE2 float summation orders (x86-64 reference build), 0 = Eigen's
    * generic scalar code. See DESIGN.md "float flavors". */
   int32_t float_flavor;
+  /* 0 (default): search only the candidates the reference's loop can reach and settle
+   * cross-subtree ties by a probe — same selected candidate, far less host work.
+   * 1: sort and visit every candidate exactly in the reference's order (the
+   * num_candidates_visited statistic then equals the reference's own count). */
+  int32_t strict_visit_order;
 } hg_fcsm_options;
 
 /* TrajectoryNode::Data fields the matcher reads (mapping/trajectory_node.h:45-62). */

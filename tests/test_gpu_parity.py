@@ -339,7 +339,7 @@ def node_inputs(world, n_high=600, n_low=150):
     return hi, lo, hist
 
 
-def world_matchers(oracle, hg, world, grid="tsdf", **opts):
+def world_matchers(oracle, hg, world, grid="tsdf", strict_visit_order=0, **opts):
     names = ("tsdf_hi", "tsdf_lo") if grid == "tsdf" else ("prob", "prob_lo")
     hi, lo, hist = node_inputs(world)
     o = dict(branch_and_bound_depth=6, full_resolution_depth=3, min_rotational_score=0.5,
@@ -350,7 +350,8 @@ def world_matchers(oracle, hg, world, grid="tsdf", **opts):
     truth_yaw = 2 * np.arctan2(world["truth"][6], world["truth"][3])
     submap_hist = oracle.rotate_histogram(hist, np.float32(truth_yaw))
     om = oracle.Fcsm(world["o_" + names[0]], world["o_" + names[1]], submap_hist, **o)
-    gm = hg.Fcsm(world["g_" + names[0]], world["g_" + names[1]], submap_hist, **o)
+    gm = hg.Fcsm(world["g_" + names[0]], world["g_" + names[1]], submap_hist,
+                 strict_visit_order=strict_visit_order, **o)
     return om, gm, hi, lo, hist
 
 
@@ -411,6 +412,7 @@ def assert_same_match(r0, r1):
 @pytest.mark.parametrize("grid", ["tsdf", "prob"])
 def test_match_selects_the_same_candidate(oracle, hg, world, grid):
     om, gm, hi, lo, hist = world_matchers(oracle, hg, world, grid)
+    _, gm_strict, _, _, _ = world_matchers(oracle, hg, world, grid, strict_visit_order=1)
     rng = np.random.RandomState(12)
     submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
     found = 0
@@ -419,9 +421,12 @@ def test_match_selects_the_same_candidate(oracle, hg, world, grid):
         for min_score in [0.2, 0.32]:
             r0 = om.match(node, submap, hi, lo, hist, min_score=min_score)
             r1 = gm.match(node, submap, hi, lo, hist, min_score=min_score)
+            r2 = gm_strict.match(node, submap, hi, lo, hist, min_score=min_score)
             assert_same_match(r0, r1)
-            assert r1["num_scored"] >= r1["num_visited"] > 0
-            assert r1["num_visited"] == r0["num_scored"]  # the replay consumed exactly the DFS's candidates
+            assert_same_match(r0, r2)
+            assert r2["num_scored"] >= r2["num_visited"] > 0
+            # strict order: the replay consumes exactly the candidates the reference's DFS scores
+            assert r2["num_visited"] == r0["num_scored"]
             found += int(r1["found"])
     assert found >= 3
     # a cloud that cannot pass the low-resolution gate gives a null result in both
