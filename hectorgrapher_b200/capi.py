@@ -46,7 +46,8 @@ class MatchResult(C.Structure):
                 ("pose_rotation", c_d * 4), ("rotational_score", c_f), ("low_resolution_score", c_f),
                 ("best_scan_index", C.c_int32), ("best_offset", C.c_int32 * 3),
                 ("num_discrete_scans", C.c_int32), ("num_candidates_scored", c_i64),
-                ("num_candidates_visited", c_i64), ("num_score_launches", C.c_int32)]
+                ("num_candidates_visited", c_i64), ("num_score_launches", C.c_int32),
+                ("num_lowest_resolution_candidates", c_i64), ("lowest_resolution_kernel_ms", c_f)]
 
 
 class ConstraintJob(C.Structure):
@@ -416,7 +417,9 @@ def _result_dict(r):
                 low_resolution_score=float(r.low_resolution_score), scan_index=float(r.best_scan_index),
                 ox=float(r.best_offset[0]), oy=float(r.best_offset[1]), oz=float(r.best_offset[2]),
                 num_scans=float(r.num_discrete_scans), num_scored=int(r.num_candidates_scored),
-                num_visited=int(r.num_candidates_visited), num_launches=int(r.num_score_launches))
+                num_visited=int(r.num_candidates_visited), num_launches=int(r.num_score_launches),
+                num_lattice=int(r.num_lowest_resolution_candidates),
+                lattice_kernel_ms=float(r.lowest_resolution_kernel_ms))
 
 
 class Fcsm:

@@ -525,6 +525,8 @@ struct Scorer {
   Workspace* ws;
   int64_t total_scored = 0;
   int launches = 0;
+  float lattice_ms = 0.f;
+  int64_t lattice_candidates = 0;
 
   int ReduceExponent(int depth) const { return std::max(0, depth - m->options.full_resolution_depth + 1); }
 
@@ -595,11 +597,21 @@ struct Scorer {
     int rc = ws->d_lattice.Reserve(n * sizeof(int));
     if (rc != HG_OK) return rc;
     const int64_t threads = static_cast<int64_t>(n) * 32;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    HG_CUDA(cudaEventCreate(&e0));
+    HG_CUDA(cudaEventCreate(&e1));
+    HG_CUDA(cudaEventRecord(e0, stream));
     ScoreLatticeKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
         m->stack->levels[depth].table, scans->CellsOfDepth(depth), scans->N, ReduceExponent(depth), nxy, nz, wxy,
         wz, 1 << depth, static_cast<int64_t>(n), ws->d_lattice.as<int>());
     CountLaunch();
     HG_CUDA(cudaGetLastError());
+    HG_CUDA(cudaEventRecord(e1, stream));
+    HG_CUDA(cudaEventSynchronize(e1));
+    HG_CUDA(cudaEventElapsedTime(&lattice_ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    lattice_candidates = static_cast<int64_t>(n);
     total_scored += static_cast<int64_t>(n);
     ++launches;
     return HG_OK;
@@ -738,6 +750,8 @@ class BranchAndBoundSearch {
   int64_t scored() const { return scorer_.total_scored; }
   int64_t visited() const { return visited_; }
   int launches() const { return scorer_.launches + low_launches_; }
+  float lattice_ms() const { return scorer_.lattice_ms; }
+  int64_t lattice_candidates() const { return scorer_.lattice_candidates; }
 
   // GetPoseFromCandidate (:400-406): Translation(resolution * offset) * scan pose.
   Rigid PoseOf(const Node& n) const {
@@ -899,8 +913,11 @@ class BranchAndBoundSearch {
         hc[i] = make_int4(p.scan, p.ox, p.oy, p.oz);
       }
       const int half_width = 1 << (d - 1);
+      PhaseTimer wt;
       rc = scorer_.RunChildren(d - 1, np, half_width, sp_.wxy, sp_.wz);
       if (rc != HG_OK) return rc;
+      wave_gpu_ms_ += wt.Lap();
+      wave_parents_ += static_cast<int64_t>(np);
       const int* sums = scorer_.HostSums();
       // Smallest child sum that beats the bound (score is non-decreasing in the sum).
       int64_t lo = 0, hi = static_cast<int64_t>(255) * scans_->N + 1;
@@ -946,6 +963,7 @@ class BranchAndBoundSearch {
           }
           kids[b + 1] = v;
         }
+        ++materialised_;
         const int at = static_cast<int>(nodes_.size());
         const int parent_index = wave[w];
         nodes_.insert(nodes_.end(), kids, kids + nc);  // may reallocate: 'parent' is dead from here
@@ -994,6 +1012,8 @@ class BranchAndBoundSearch {
   int LowResolutionFor(const std::vector<int>& leaves) {
     const size_t n = leaves.size();
     if (n == 0) return HG_OK;
+    PhaseTimer lt;
+    struct Acc { double* t; PhaseTimer* p; ~Acc() { *t += p->Lap(); } } acc{&low_ms_, &lt};
     const int np = data_->num_low_resolution_points;
     if (np <= 0) {
       // score / points->size() with an empty cloud is 0 / 0 in the reference.
@@ -1042,6 +1062,10 @@ class BranchAndBoundSearch {
   bool strict_ = false;
   Workspace* ws_ = nullptr;
   bool lattice_scored_ = false;
+ public:
+  double wave_gpu_ms_ = 0.0, low_ms_ = 0.0;
+  int64_t wave_parents_ = 0, materialised_ = 0;
+ private:
   std::vector<int> h_lattice_sums_;  // lowest-resolution sums in generation order (strict / probe only)
   std::vector<int> top_index_;       // generation index of nodes_[0 .. top_count_)
   std::vector<int> parent_of_;
@@ -1084,12 +1108,16 @@ int MatchWithSearchParameters(const hg_fcsm* m, const SearchParameters& sp, cons
   rc = search.Run(min_score, m->options.strict_visit_order != 0, &best);
   if (rc != HG_OK) return rc;
   if (TraceEnabled())
-    std::fprintf(stderr, "[hg trace] search: %d scans x %d pts, window %d/%d; discretise %.1f ms, branch-and-bound %.1f ms, scored %lld visited %lld launches %d\n",
-                 scans.S, scans.N, sp.wxy, sp.wz, t_scans, pt.Lap(), static_cast<long long>(search.scored()),
+    std::fprintf(stderr, "[hg trace] search: %d scans x %d pts, window %d/%d; discretise %.1f ms, branch-and-bound %.1f ms (waves on GPU %.1f ms, %lld parents, %lld materialised; leaf gate %.1f ms), scored %lld visited %lld launches %d\n",
+                 scans.S, scans.N, sp.wxy, sp.wz, t_scans, pt.Lap(), search.wave_gpu_ms_,
+                 static_cast<long long>(search.wave_parents_), static_cast<long long>(search.materialised_),
+                 search.low_ms_, static_cast<long long>(search.scored()),
                  static_cast<long long>(search.visited()), search.launches());
   result->num_candidates_scored = search.scored();
   result->num_candidates_visited = search.visited();
   result->num_score_launches = search.launches();
+  result->num_lowest_resolution_candidates = search.lattice_candidates();
+  result->lowest_resolution_kernel_ms = search.lattice_ms();
   if (best.node >= 0 && best.score > min_score) {
     const Node& n = search.node(best.node);
     const Rigid pose = search.PoseOf(n);

@@ -242,6 +242,8 @@ typedef struct hg_match_result {
   int64_t num_candidates_scored;     /* candidates the GPU scored (a superset of the DFS's) */
   int64_t num_candidates_visited;    /* candidates the reference's DFS order consumed */
   int32_t num_score_launches;
+  int64_t num_lowest_resolution_candidates; /* size of the lowest-resolution lattice (one launch) */
+  float lowest_resolution_kernel_ms;        /* its device time, CUDA events on the launching stream */
 } hg_match_result;
 
 /* FastCorrelativeScanMatcher3D(grid, low_resolution_grid, histogram, options)
