@@ -87,6 +87,7 @@ SYMBOLS = {
     "hg_cost_evaluate": (c_i, [vp, vp, vp, vp]),
     "hg_cost_evaluate_device": (c_i, [vp, vp, vp, vp, vp]),
     "hg_cost_normal_equations": (c_i, [vp, vp, vp, vp, vp]),
+    "hg_cost_normal_equations_static": (c_i, [vp, vp, vp, vp, vp]),
     "hg_batch_create": (c_i, [c_i, c_i, vp, c_i, vp, vp, vp, vp, c_i, vp]),
     "hg_batch_destroy": (None, [vp]),
     "hg_batch_num_residuals": (c_i64, [vp]),
@@ -259,14 +260,16 @@ class Cost:
         _check(lib().hg_cost_evaluate(self.h, parr, _p(r), jarr))
         return r, J
 
-    def normal_equations(self, params):
+    def normal_equations(self, params, static_scratch=False):
+        """static_scratch=True goes through hg_cost_normal_equations_static (no allocation at call time)."""
         blocks = self._blocks(params)
         parr = (vp * len(blocks))(*[b.ctypes.data for b in blocks])
         n = sum(self.sizes)
         JtJ = np.zeros((n, n))
         Jtr = np.zeros(n)
         cost = np.zeros(1)
-        _check(lib().hg_cost_normal_equations(self.h, parr, _p(JtJ), _p(Jtr), _p(cost)))
+        fn = lib().hg_cost_normal_equations_static if static_scratch else lib().hg_cost_normal_equations
+        _check(fn(self.h, parr, _p(JtJ), _p(Jtr), _p(cost)))
         return JtJ, Jtr, float(cost[0])
 
 

@@ -1054,3 +1054,129 @@ extern "C" int hg_scan_match(int num_clouds, const float* const* clouds, const i
   }
   return HG_OK;
 }
+
+// ---------------------------------------------------------------------------
+// hg_cost_normal_equations_static — the Gauss-Newton terms of one residual
+// block computed with NO allocation of any kind at call time.
+//
+// Who needs this: callers that are not allowed to touch the CUDA allocator once
+// they are running — a SLAM front end inside its real-time loop (cudaMalloc and
+// cudaFree synchronise the whole device and take an unbounded time), or a host
+// program that has already handed all free device memory to its own arena, so
+// that a cudaMalloc issued by a library would simply fail. For them the scratch
+// memory the kernels need (per-tile partial sums, the reduced result and the
+// block descriptor) is not allocated at all: it is the file-scope device array
+// below, which every GPU that loads this library carries from load to exit.
+//
+// Limit: one residual block of at most kStaticMaxPoints = 1,048,576 points
+// (the array is sized for it: 984 KB per GPU). Larger blocks are rejected with
+// HG_ERR_LIMIT; use hg_cost_normal_equations for those.
+//
+// Sharing: there is ONE such array per GPU. Every call uses it and leaves its
+// last contents behind. Nothing in it has to start at zero — each call writes
+// every word it later reads (all terms of every tile it launches, then the
+// reduced vector) — so no clearing pass is needed. Calls that overlapped on the
+// GPU would race: they would overwrite each other's partial sums. Within one
+// process that cannot happen, because a call holds a process-wide lock and
+// returns only after the device has finished its work.
+//
+// Set-up: the first call on a device looks up the array's device address with
+// cudaGetSymbolAddress (the array's name is only a host-side stand-in in host
+// code, never a pointer a kernel may be given) while that device is current,
+// and caches it. That first call should therefore happen before any stream
+// capture is begun on the device.
+namespace {
+
+constexpr int kStaticMaxPoints = 1 << 20;
+constexpr int kStaticMaxTiles = kStaticMaxPoints / kTileNe;
+constexpr int kStaticTerms = NumNormalTerms(14);
+constexpr int kStaticBlockDoubles = (sizeof(BlockDev) + 7) / 8;
+constexpr int kStaticDoubles = kStaticMaxTiles * kStaticTerms + kStaticTerms + kStaticBlockDoubles;
+
+static __device__ __align__(256) double g_static_scratch[kStaticDoubles];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mutex;
+double* g_static_address[kMaxDevices] = {nullptr};
+
+// Device address of g_static_scratch on the current device (cached per device).
+int StaticScratchAddress(int device, double** out) {
+  HG_REQUIRE(device >= 0 && device < kMaxDevices, "hg_cost_normal_equations_static: device index out of range");
+  if (g_static_address[device] == nullptr) {
+    double* address = nullptr;
+    HG_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&address), g_static_scratch));
+    g_static_address[device] = address;
+  }
+  *out = g_static_address[device];
+  return HG_OK;
+}
+
+}  // namespace
+
+extern "C" int hg_cost_normal_equations_static(const hg_cost* cost, const double* const* parameters,
+                                               double* JtJ, double* Jtr, double* cost_out) {
+  HG_REQUIRE(cost != nullptr && parameters != nullptr, "hg_cost_normal_equations_static: bad arguments");
+  const hg_batch* B = cost->batch;
+  if (B->num_points > kStaticMaxPoints) {
+    SetError("hg_cost_normal_equations_static: the block has " + std::to_string(B->num_points) +
+             " points; the static scratch array holds at most " + std::to_string(kStaticMaxPoints) +
+             " (use hg_cost_normal_equations)");
+    return HG_ERR_LIMIT;
+  }
+  int device = -1;
+  HG_CUDA(cudaGetDevice(&device));
+  HG_REQUIRE(device == B->device,
+             "hg_cost_normal_equations_static: the cost function's device must be the current device");
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  double* scratch = nullptr;
+  int rc = StaticScratchAddress(device, &scratch);
+  if (rc != HG_OK) return rc;
+  double* d_partials = scratch;
+  double* d_reduced = scratch + static_cast<size_t>(kStaticMaxTiles) * kStaticTerms;
+  BlockDev* d_block = reinterpret_cast<BlockDev*>(d_reduced + kStaticTerms);
+
+  // Block descriptor on the stack, copied straight into the static array.
+  const BlockPose p = B->two_pose ? TwoPose(parameters[0], parameters[1], parameters[2], parameters[3], B->ratios[0])
+                                  : OnePose(parameters[0], parameters[1]);
+  BlockDev block;
+  std::memcpy(block.t, p.t, sizeof(block.t));
+  std::memcpy(block.q, p.q, sizeof(block.q));
+  block.ct0 = p.ct0;
+  block.ct1 = p.ct1;
+  std::memcpy(block.m0, p.m0, sizeof(block.m0));
+  std::memcpy(block.m1, p.m1, sizeof(block.m1));
+  block.scale = B->scales[0];
+  block.point_offset = 0;
+  block.n = static_cast<int>(B->num_points);
+  block.pad = 0;
+  cudaStream_t stream = nullptr;
+  HG_CUDA(cudaMemcpyAsync(d_block, &block, sizeof(block), cudaMemcpyHostToDevice, stream));
+
+  CostArgs a = BaseArgs(B);
+  a.blocks = d_block;
+  a.tiles = B->d_tiles_ne;
+  a.tile_points = kTileNe;
+  a.partials = d_partials;
+  rc = LaunchCost<true>(B, a, B->num_tiles_ne, stream);
+  if (rc != HG_OK) return rc;
+  const int n = B->two_pose ? 14 : 7;
+  const int P = NumNormalTerms(n);
+  ReducePartialsKernel<<<1, 128, 0, stream>>>(d_partials, B->d_ne_tile_begin, P, d_reduced);
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  double reduced[kStaticTerms];
+  HG_CUDA(cudaMemcpyAsync(reduced, d_reduced, sizeof(double) * P, cudaMemcpyDeviceToHost, stream));
+  HG_CUDA(cudaStreamSynchronize(stream));
+  int e = 0;
+  for (int ca = 0; ca < n; ++ca)
+    for (int cb = ca; cb < n; ++cb, ++e) {
+      if (JtJ) {
+        JtJ[ca * n + cb] = reduced[e];
+        JtJ[cb * n + ca] = reduced[e];
+      }
+    }
+  for (int c = 0; c < n; ++c, ++e)
+    if (Jtr) Jtr[c] = reduced[e];
+  if (cost_out) *cost_out = 0.5 * reduced[e];
+  return HG_OK;
+}

@@ -128,6 +128,21 @@ int hg_cost_evaluate_device(const hg_cost* cost, const double* const* parameters
 int hg_cost_normal_equations(const hg_cost* cost, const double* const* parameters, double* JtJ,
                              double* Jtr, double* cost_out);
 
+/* No counterpart in the reference. Same result as hg_cost_normal_equations for one
+ * residual block, but the call allocates nothing: no cudaMalloc / cudaFree, no
+ * allocating library routine. It exists for callers that must not use the CUDA
+ * allocator once they are running — a real-time scan-matching loop (allocation
+ * synchronises the device and has no time bound) or a process whose device memory is
+ * already owned by its own arena. Its scratch memory is a fixed array that is part of
+ * the library image on every GPU (984 KB per GPU, held until exit), which bounds the
+ * block size: at most 1,048,576 points, larger blocks return HG_ERR_LIMIT. The cost
+ * function's device must be the current device. The first call on a device looks up
+ * the array's address (make that call before starting any stream capture). All calls
+ * share the one array per GPU and take a process-wide lock; the function returns
+ * after the device has finished. Host outputs, any may be NULL. */
+int hg_cost_normal_equations_static(const hg_cost* cost, const double* const* parameters,
+                                    double* JtJ, double* Jtr, double* cost_out);
+
 /* ------------------------------------------------- batched cost blocks -- */
 
 /* Many residual blocks of one kind over the same grids, evaluated by one
