@@ -245,9 +245,12 @@ def correlative_bench(hg, torch, w, rank, world, dist):
     rec = torch.tensor([dt, float(r["num_scored"]), float(r["found"]), float(r["score"]), float(r["scan_index"]),
                         r["ox"], r["oy"], r["oz"], float(r["num_scans"]), float(r["num_lattice"]),
                         float(r["lattice_kernel_ms"]), float(r["num_visited"])], dtype=torch.float64, device="cuda")
+    from hectorgrapher_b200 import dist as hgdist
+    # NCCL best-candidate reduce: one small record per rank, arg-max, ties to the lower scan index
+    best = hgdist.reduce_best_candidate((r["found"], r["score"], r["scan_index"], r["ox"], r["oy"], r["oz"]), dist)
     if dist is not None:
         allrec = [torch.zeros_like(rec) for _ in range(world)]
-        dist.all_gather(allrec, rec)  # NCCL: best-candidate reduce (tens of bytes per rank)
+        dist.all_gather(allrec, rec)  # timing / statistics only
         allrec = torch.stack(allrec).cpu().numpy()
     else:
         allrec = rec.cpu().numpy()[None]
@@ -255,12 +258,6 @@ def correlative_bench(hg, torch, w, rank, world, dist):
         return None
     tmax = float(allrec[:, 0].max())
     scored = float(allrec[:, 1].sum())
-    found = allrec[allrec[:, 2] > 0]
-    # arg-max over ranks; ties go to the lower scan index
-    best = None
-    if len(found):
-        order = np.lexsort((found[:, 4], -found[:, 3]))
-        best = found[order[0]]
     n_pts = len(high)
     peak, _ = measured_peak()
     cps = scored / tmax
@@ -274,8 +271,8 @@ def correlative_bench(hg, torch, w, rank, world, dist):
                     "N=%d pts, discrete scans sharded over %d rank(s); whole search incl. host replay" % (n_pts, world),
         "search_ms": 1e3 * tmax, "candidates_scored": scored, "candidates_visited_by_dfs": float(allrec[:, 11].sum()),
         "discrete_scans": float(allrec[:, 8].sum()),
-        "best": None if best is None else {"score": float(best[3]), "scan": int(best[4]),
-                                           "offset": [int(best[5]), int(best[6]), int(best[7])]},
+        "best": None if best is None else {"score": float(best[1]), "scan": int(best[2]),
+                                           "offset": [int(best[3]), int(best[4]), int(best[5])]},
         "lowest_resolution_kernel": {"candidates": lattice_n, "ms": lattice_ms, "candidates_per_s": lattice_cps},
         "roofline": {"bound": "hbm", "achieved": lattice_cps * (n_pts + 24) / world / 1e9, "peak": peak,
                      "unit": "GB/s", "frac": lattice_cps * (n_pts + 24) / world / 1e9 / peak, "traffic": None,

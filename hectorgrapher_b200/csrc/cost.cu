@@ -361,7 +361,7 @@ __device__ __forceinline__ ValueGrad Residual(const CostArgs& a, const double sc
 __host__ __device__ constexpr int NumNormalTerms(int n) { return n * (n + 1) / 2 + n + 1; }
 
 template <int LOOKUP, bool TWO_POSE, bool NORMAL_EQ>
-__global__ void __launch_bounds__(kThreads) CostKernel(const CostArgs a) {
+__global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const CostArgs a) {
   constexpr int NC = TWO_POSE ? 14 : 7;
   constexpr int ROW = NC + 1;  // row of [J | r] staged for the normal-equation reduction
   __shared__ BlockDev sb;
