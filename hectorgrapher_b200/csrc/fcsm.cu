@@ -154,6 +154,57 @@ __global__ void __launch_bounds__(256) ScoreLatticeKernel(const BrickTable level
   if (lane == 0) sums[warp] = sum;
 }
 
+// Same sums as ScoreLatticeKernel for a level that has a dense copy: one warp
+// scores KX x-adjacent lattice candidates at once, so that a point's cell is
+// loaded and range-checked in y and z once for KX gathers, and a gather is one
+// byte load without the brick-index indirection.
+template <int KX>
+__global__ void __launch_bounds__(256) ScoreLatticeDenseKernel(const DenseLevel level, const int* __restrict__ cells,
+                                                               const int N, const int reduction_exponent,
+                                                               const int nxy, const int nz, const int wxy,
+                                                               const int wz, const int step,
+                                                               const int64_t num_groups, int* __restrict__ sums) {
+  const int64_t warp = (blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= num_groups) return;
+  const int gx = (nxy + KX - 1) / KX;  // groups per lattice row
+  const int rows_per_scan = nxy * nz;
+  const int64_t row = warp / gx;  // (scan, iz, iy)
+  const int g = static_cast<int>(warp - row * gx);
+  const int scan = static_cast<int>(row / rows_per_scan);
+  const int rem = static_cast<int>(row - static_cast<int64_t>(scan) * rows_per_scan);
+  const int iz = rem / nxy, iy = rem - iz * nxy;
+  const int oy = ((-wxy + iy * step) >> reduction_exponent) - level.min[1];
+  const int oz = ((-wz + iz * step) >> reduction_exponent) - level.min[2];
+  int ox[KX];
+#pragma unroll
+  for (int k = 0; k < KX; ++k) ox[k] = ((-wxy + (g * KX + k) * step) >> reduction_exponent) - level.min[0];
+  const int* base = cells + static_cast<int64_t>(scan) * N * 3;
+  int sum[KX];
+#pragma unroll
+  for (int k = 0; k < KX; ++k) sum[k] = 0;
+  for (int i = lane; i < N; i += 32) {
+    const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1) + oy, z = __ldg(base + 3 * i + 2) + oz;
+    if (static_cast<unsigned>(y) < static_cast<unsigned>(level.dim[1]) &&
+        static_cast<unsigned>(z) < static_cast<unsigned>(level.dim[2])) {
+      const unsigned char* rowp = level.data + (static_cast<size_t>(z) * level.dim[1] + y) * level.dim[0];
+#pragma unroll
+      for (int k = 0; k < KX; ++k) {
+        const int xx = x + ox[k];
+        if (static_cast<unsigned>(xx) < static_cast<unsigned>(level.dim[0])) sum[k] += __ldg(rowp + xx);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < KX; ++k) {
+    int v = sum[k];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    const int ix = g * KX + k;
+    if (lane == 0 && ix < nxy) sums[row * nxy + ix] = v;
+  }
+}
+
 // Children of a wave of parents at 'depth' (the loop nest at :441-461): warp w
 // scores child slot w % 8 = (z, y, x) in {0, half}^3 of parent w / 8, so the
 // host uploads one record per parent and reads eight sums back. A child beyond
@@ -601,9 +652,18 @@ struct Scorer {
     HG_CUDA(cudaEventCreate(&e0));
     HG_CUDA(cudaEventCreate(&e1));
     HG_CUDA(cudaEventRecord(e0, stream));
-    ScoreLatticeKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
-        m->stack->levels[depth].table, scans->CellsOfDepth(depth), scans->N, ReduceExponent(depth), nxy, nz, wxy,
-        wz, 1 << depth, static_cast<int64_t>(n), ws->d_lattice.as<int>());
+    const hg_stack_level& L = m->stack->levels[depth];
+    if (L.dense.data != nullptr) {
+      constexpr int KX = 4;
+      const int64_t groups = static_cast<int64_t>(scans->S) * nz * nxy * ((nxy + KX - 1) / KX);
+      ScoreLatticeDenseKernel<KX><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>(
+          L.dense, scans->CellsOfDepth(depth), scans->N, ReduceExponent(depth), nxy, nz, wxy, wz, 1 << depth,
+          groups, ws->d_lattice.as<int>());
+    } else {
+      ScoreLatticeKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
+          L.table, scans->CellsOfDepth(depth), scans->N, ReduceExponent(depth), nxy, nz, wxy, wz, 1 << depth,
+          static_cast<int64_t>(n), ws->d_lattice.as<int>());
+    }
     CountLaunch();
     HG_CUDA(cudaGetLastError());
     HG_CUDA(cudaEventRecord(e1, stream));
@@ -700,13 +760,45 @@ class BranchAndBoundSearch {
   int Run(float min_score, bool strict, BestCandidate* best_out) {
     const int max_depth = m_->options.branch_and_bound_depth - 1;
     strict_ = strict;
+    global_bound_ = -std::numeric_limits<float>::infinity();
     int rc = UploadLowResolutionCloud();
     if (rc != HG_OK) return rc;
-    rc = ScoreLowestResolution(max_depth, min_score, strict, nullptr);
+    std::vector<Key> keys;
+    rc = CollectKeys(max_depth, min_score, strict, nullptr, &keys);
     if (rc != HG_OK) return rc;
+    constexpr size_t kDiveWidth = 4096;
+    float dive_bound = -std::numeric_limits<float>::infinity();
+    if (!strict && max_depth >= 1 && keys.size() > 2 * kDiveWidth) {
+      std::nth_element(keys.begin(), keys.begin() + kDiveWidth, keys.end(), [](const Key& a, const Key& b) {
+        return a.score > b.score || (a.score == b.score && a.index < b.index);
+      });
+      rc = GreedyDive(keys, kDiveWidth, max_depth, min_score, &dive_bound);
+      if (rc != HG_OK) return rc;
+      if (dive_bound > min_score) {
+        global_bound_ = dive_bound;
+        size_t kept = 0;
+        for (const Key& k : keys)
+          if (k.score >= dive_bound) keys[kept++] = k;
+        keys.resize(kept);
+      }
+    }
+    BuildTopLevel(&keys, strict);
     failed_ = HG_OK;
     BestCandidate best = Search(0, static_cast<int>(top_count_), max_depth, min_score);
     if (failed_ != HG_OK) return failed_;
+    if (!strict && global_bound_ > min_score && !(best.node >= 0 && best.score >= global_bound_)) {
+      // The dive's leaf was not reached again: a parent scored below its child
+      // somewhere (the pyramid is not a strict upper bound there). Redo without
+      // the global bound, which is correct by construction.
+      if (TraceEnabled()) std::fprintf(stderr, "[hg trace] global bound not confirmed: rerun without it\n");
+      global_bound_ = -std::numeric_limits<float>::infinity();
+      wave_budget_ = 8;
+      rc = CollectKeys(max_depth, min_score, false, nullptr, &keys);
+      if (rc != HG_OK) return rc;
+      BuildTopLevel(&keys, false);
+      best = Search(0, static_cast<int>(top_count_), max_depth, min_score);
+      if (failed_ != HG_OK) return failed_;
+    }
     if (!strict && best.node >= 0 && best.score > min_score) {
       // Top-level ancestor of the winner and its equal-score twins.
       const int ancestor = TopAncestor(best.node);
@@ -719,17 +811,20 @@ class BranchAndBoundSearch {
         const float winner_low = best.low_resolution_score;
         const float below = std::nextafter(best.score, -std::numeric_limits<float>::infinity());
         strict_ = true;
+        global_bound_ = -std::numeric_limits<float>::infinity();
         wave_budget_ = 8;
-        rc = ScoreLowestResolution(max_depth, below, true, &twins);
-        if (rc != HG_OK) return rc;
+        keys.clear();
+        for (int t : twins) keys.push_back(Key{nodes_[ancestor].score, static_cast<uint32_t>(t)});
+        BuildTopLevel(&keys, true);
         const BestCandidate probe = Search(0, static_cast<int>(top_count_), max_depth, below);
         if (failed_ != HG_OK) return failed_;
         if (probe.node >= 0 && probe.score >= best.score) {
           // A real tie across equal-score subtrees: only the strict order settles it.
           if (TraceEnabled()) std::fprintf(stderr, "[hg trace] tie across twin subtrees: strict rerun\n");
           wave_budget_ = 8;
-          rc = ScoreLowestResolution(max_depth, min_score, true, nullptr);
+          rc = CollectKeys(max_depth, min_score, true, nullptr, &keys);
           if (rc != HG_OK) return rc;
+          BuildTopLevel(&keys, true);
           best = Search(0, static_cast<int>(top_count_), max_depth, min_score);
           if (failed_ != HG_OK) return failed_;
         } else {
@@ -762,34 +857,32 @@ class BranchAndBoundSearch {
   }
 
  private:
-  // GenerateLowestResolutionCandidates + ScoreCandidates(max_depth) (:328-398).
-  // strict: every candidate is kept and sorted exactly like the reference
-  // (std::sort over the generation order). Otherwise only candidates the
-  // reference's loop can reach (score > min_score, :437-440) are kept and sorted;
-  // their relative order can differ from the strict order only among equal scores.
-  int ScoreLowestResolution(int max_depth, float min_score, bool strict, const std::vector<int>* only) {
+  struct Key {
+    float score;
+    uint32_t index;  // position in generation order
+  };
+
+  // GenerateLowestResolutionCandidates + ScoreCandidates(max_depth) (:328-398),
+  // without the sort: (score, generation index) of the lattice candidates in
+  // generation order. strict: all of them. Otherwise only those the reference's
+  // loop can reach (score > min_score, :437-440), compacted on the device.
+  // 'only' restricts the list to the given generation indices.
+  int CollectKeys(int max_depth, float min_score, bool strict, const std::vector<int>* only,
+                  std::vector<Key>* keys) {
     PhaseTimer pt;
     const int step = 1 << max_depth;
-    const int nxy = (2 * sp_.wxy + step) / step, nz = (2 * sp_.wz + step) / step;
-    const int per_scan = nxy * nxy * nz;
-    const size_t n = static_cast<size_t>(scans_->S) * per_scan;
+    nxy_ = (2 * sp_.wxy + step) / step;
+    nz_ = (2 * sp_.wz + step) / step;
+    per_scan_ = nxy_ * nxy_ * nz_;
+    step_ = step;
+    const size_t n = static_cast<size_t>(scans_->S) * per_scan_;
     if (!lattice_scored_) {
-      int rc = scorer_.RunLattice(max_depth, nxy, nz, sp_.wxy, sp_.wz, n);
+      int rc = scorer_.RunLattice(max_depth, nxy_, nz_, sp_.wxy, sp_.wz, n);
       if (rc != HG_OK) return rc;
       lattice_scored_ = true;
       visited_ += static_cast<int64_t>(n);
     }
-    // score(sum) is non-decreasing in sum: the smallest sum whose score beats min_score.
-    int64_t lo = 0, hi = static_cast<int64_t>(255) * scans_->N + 1;
-    while (lo < hi) {
-      const int64_t mid = (lo + hi) / 2;
-      if (ScoreFromSum(static_cast<int>(mid), scans_->N) > min_score) hi = mid; else lo = mid + 1;
-    }
-    struct Key {
-      float score;
-      uint32_t index;
-    };
-    std::vector<Key> keys;
+    keys->clear();
     if (only != nullptr || strict) {
       // Every sum is needed on the host.
       if (h_lattice_sums_.size() != n) {
@@ -798,43 +891,131 @@ class BranchAndBoundSearch {
       }
       const int* sums = h_lattice_sums_.data();
       if (only != nullptr) {
-        for (int i : *only) keys.push_back(Key{ScoreFromSum(sums[i], scans_->N), static_cast<uint32_t>(i)});
+        for (int i : *only) keys->push_back(Key{ScoreFromSum(sums[i], scans_->N), static_cast<uint32_t>(i)});
       } else {
-        keys.reserve(n);
-        for (size_t i = 0; i < n; ++i) keys.push_back(Key{ScoreFromSum(sums[i], scans_->N), static_cast<uint32_t>(i)});
+        keys->reserve(n);
+        for (size_t i = 0; i < n; ++i) keys->push_back(Key{ScoreFromSum(sums[i], scans_->N), static_cast<uint32_t>(i)});
       }
     } else {
       std::vector<int2> kept;
-      const int rc = scorer_.DownloadKept(n, static_cast<int>(lo), &kept);
+      const int rc = scorer_.DownloadKept(n, SmallestSumBeating(min_score), &kept);
       if (rc != HG_OK) return rc;
-      keys.reserve(kept.size());
-      for (const int2& k : kept) keys.push_back(Key{ScoreFromSum(k.y, scans_->N), static_cast<uint32_t>(k.x)});
+      keys->reserve(kept.size());
+      for (const int2& k : kept) keys->push_back(Key{ScoreFromSum(k.y, scans_->N), static_cast<uint32_t>(k.x)});
     }
-    const double t_gpu = pt.Lap();
-    // std::sort(..., std::greater<Candidate3D>()) over the generation order: the
-    // comparator only looks at the score, so sorting (score, index) keys with
-    // the same algorithm yields the reference's permutation, ties included.
-    std::sort(keys.begin(), keys.end(), [](const Key& a, const Key& b) { return a.score > b.score; });
+    if (TraceEnabled())
+      std::fprintf(stderr, "[hg trace] lowest level: %zu candidates (%zu kept), score+select %.1f ms\n", n,
+                   keys->size(), pt.Lap());
+    return HG_OK;
+  }
+
+  // score(sum) is non-decreasing in sum: the smallest sum whose score is > s.
+  int SmallestSumBeating(float s) const {
+    int64_t lo = 0, hi = static_cast<int64_t>(255) * scans_->N + 1;
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) / 2;
+      if (ScoreFromSum(static_cast<int>(mid), scans_->N) > s) hi = mid; else lo = mid + 1;
+    }
+    return static_cast<int>(lo);
+  }
+
+  Node NodeOfKey(const Key& k) const {
+    const int scan = static_cast<int>(k.index / per_scan_);
+    int rem = static_cast<int>(k.index - static_cast<size_t>(scan) * per_scan_);
+    const int iz = rem / (nxy_ * nxy_);
+    rem -= iz * nxy_ * nxy_;
+    const int iy = rem / nxy_;
+    const int ix = rem - iy * nxy_;
+    return Node{scan, -sp_.wxy + ix * step_, -sp_.wxy + iy * step_, -sp_.wz + iz * step_, k.score,
+                std::numeric_limits<float>::quiet_NaN(), -1, 0};
+  }
+
+  // Sorts the keys and makes them the top-level node list. strict: std::sort with
+  // std::greater<Candidate3D>'s comparison over the generation order — the
+  // comparator only looks at the score, so the same algorithm on (score, index)
+  // keys yields the reference's permutation, ties included. Otherwise a total
+  // order (score, then generation index).
+  void BuildTopLevel(std::vector<Key>* keys, bool strict) {
+    PhaseTimer pt;
+    if (strict) {
+      std::sort(keys->begin(), keys->end(), [](const Key& a, const Key& b) { return a.score > b.score; });
+    } else {
+      std::sort(keys->begin(), keys->end(), [](const Key& a, const Key& b) {
+        return a.score > b.score || (a.score == b.score && a.index < b.index);
+      });
+    }
     nodes_.clear();
-    nodes_.reserve(keys.size() * 2);
+    nodes_.reserve(keys->size() * 2);
     top_index_.clear();
-    for (const Key& k : keys) {
-      const int scan = static_cast<int>(k.index / per_scan);
-      int rem = static_cast<int>(k.index - static_cast<size_t>(scan) * per_scan);
-      const int iz = rem / (nxy * nxy);
-      rem -= iz * nxy * nxy;
-      const int iy = rem / nxy;
-      const int ix = rem - iy * nxy;
-      nodes_.push_back(Node{scan, -sp_.wxy + ix * step, -sp_.wxy + iy * step, -sp_.wz + iz * step, k.score,
-                            std::numeric_limits<float>::quiet_NaN(), -1, 0});
+    for (const Key& k : *keys) {
+      nodes_.push_back(NodeOfKey(k));
       top_index_.push_back(static_cast<int>(k.index));
     }
-    top_count_ = keys.size();
+    top_count_ = keys->size();
     parent_of_.assign(nodes_.size(), -1);
     leaves_pending_.clear();
+    if (TraceEnabled()) std::fprintf(stderr, "[hg trace] top level: %zu nodes, sort+build %.1f ms\n", top_count_, pt.Lap());
+  }
+
+  // A quick lower bound on the answer: the 'width' best lowest-resolution
+  // candidates are each followed greedily (best child per level, one launch per
+  // level for all of them) down to a leaf; the best such leaf that passes the
+  // low-resolution gate gives a score that the final answer cannot be below.
+  // Subtrees whose score is strictly below it can then be dropped without
+  // touching either the answer or its tie-breaking.
+  int GreedyDive(const std::vector<Key>& keys, size_t width, int max_depth, float min_score, float* bound) {
+    *bound = -std::numeric_limits<float>::infinity();
+    PhaseTimer pt;
+    std::vector<Node> cur;
+    cur.reserve(width);
+    for (size_t i = 0; i < width && i < keys.size(); ++i) cur.push_back(NodeOfKey(keys[i]));
+    for (int d = max_depth; d >= 1 && !cur.empty(); --d) {
+      const size_t np = cur.size();
+      int rc = scorer_.Reserve(np);
+      if (rc != HG_OK) return rc;
+      int4* hc = scorer_.HostCandidates();
+      for (size_t i = 0; i < np; ++i) hc[i] = make_int4(cur[i].scan, cur[i].ox, cur[i].oy, cur[i].oz);
+      const int half_width = 1 << (d - 1);
+      rc = scorer_.RunChildren(d - 1, np, half_width, sp_.wxy, sp_.wz);
+      if (rc != HG_OK) return rc;
+      const int* sums = scorer_.HostSums();
+      for (size_t i = 0; i < np; ++i) {
+        int best_slot = 0, best_sum = -1;
+        for (int slot = 0; slot < 8; ++slot) {
+          if (sums[8 * i + slot] < 0) continue;
+          ++scorer_.total_scored;
+          if (sums[8 * i + slot] > best_sum) {
+            best_sum = sums[8 * i + slot];
+            best_slot = slot;
+          }
+        }
+        Node& c = cur[i];
+        c.ox += (best_slot & 1) ? half_width : 0;
+        c.oy += (best_slot & 2) ? half_width : 0;
+        c.oz += (best_slot & 4) ? half_width : 0;
+        c.score = ScoreFromSum(std::max(best_sum, 0), scans_->N);
+      }
+    }
+    std::sort(cur.begin(), cur.end(), [](const Node& a, const Node& b) { return a.score > b.score; });
+    // Leaf gate in descending score, in batches, until one passes.
+    for (size_t at = 0; at < cur.size(); at += 256) {
+      const size_t end = std::min(cur.size(), at + 256);
+      if (cur[at].score <= min_score) break;
+      std::vector<Node> batch(cur.begin() + at, cur.begin() + end);
+      std::vector<float> low;
+      const int rc = LowResolutionScores(batch, &low);
+      if (rc != HG_OK) return rc;
+      for (size_t k = 0; k < batch.size(); ++k) {
+        if (batch[k].score <= min_score) break;
+        if (static_cast<double>(low[k]) >= m_->options.min_low_resolution_score) {
+          *bound = batch[k].score;
+          break;
+        }
+      }
+      if (*bound > -std::numeric_limits<float>::infinity()) break;
+    }
     if (TraceEnabled())
-      std::fprintf(stderr, "[hg trace] lowest level: %zu candidates (%zu kept), score+select %.1f ms, sort+nodes %.1f ms\n",
-                   n, keys.size(), t_gpu, pt.Lap());
+      std::fprintf(stderr, "[hg trace] greedy dive: %zu starts, bound %.6f, %.1f ms\n", cur.size(), *bound, pt.Lap());
     return HG_OK;
   }
 
@@ -873,9 +1054,15 @@ class BranchAndBoundSearch {
     BestCandidate best;
     best.score = min_score;
     for (int i = begin; i < begin + count; ++i) {
-      if (nodes_[i].score <= min_score) break;
+      // The reference compares against its min_score argument (:437-440); a
+      // candidate in (min_score, running best] still gets its children scored,
+      // but the recursion then stops at the first child and changes nothing.
+      // Outside strict order those candidates (and, the list being sorted, all
+      // that follow) are skipped.
+      if (nodes_[i].score <= (strict_ ? min_score : best.score)) break;
+      if (nodes_[i].score < global_bound_) break;  // cannot hold the answer or a tie with it
       if (nodes_[i].first_child == -1) {
-        failed_ = Speculate(begin, count, i, depth, min_score, best.score);
+        failed_ = Speculate(begin, count, i, depth, strict_ ? min_score : best.score, best.score);
         if (failed_ != HG_OK) return unsuccessful;
       }
       visited_ += nodes_[i].num_children;
@@ -896,7 +1083,7 @@ class BranchAndBoundSearch {
   int Speculate(int begin, int count, int trigger, int depth, float list_min_score, float bound) {
     std::vector<int> wave;
     for (int i = trigger; i < begin + count; ++i) {
-      if (nodes_[i].score <= list_min_score) break;
+      if (nodes_[i].score <= list_min_score || nodes_[i].score < global_bound_) break;
       if (nodes_[i].first_child == -1) wave.push_back(i);
       if (static_cast<int64_t>(wave.size()) >= wave_budget_) break;
     }
@@ -919,13 +1106,13 @@ class BranchAndBoundSearch {
       wave_gpu_ms_ += wt.Lap();
       wave_parents_ += static_cast<int64_t>(np);
       const int* sums = scorer_.HostSums();
-      // Smallest child sum that beats the bound (score is non-decreasing in the sum).
-      int64_t lo = 0, hi = static_cast<int64_t>(255) * scans_->N + 1;
-      while (lo < hi) {
-        const int64_t mid = (lo + hi) / 2;
-        if (ScoreFromSum(static_cast<int>(mid), scans_->N) > bound) hi = mid; else lo = mid + 1;
+      // Smallest child sum that beats the bound and is not below the global
+      // bound (score is non-decreasing in the sum).
+      int beats_bound = SmallestSumBeating(bound);
+      if (global_bound_ > -std::numeric_limits<float>::infinity()) {
+        const float just_below = std::nextafter(global_bound_, -std::numeric_limits<float>::infinity());
+        beats_bound = std::max(beats_bound, SmallestSumBeating(just_below));
       }
-      const int beats_bound = static_cast<int>(lo);
       std::vector<int> next;
       for (size_t w = 0; w < np; ++w) {
         const int* cs = sums + 8 * w;
@@ -973,7 +1160,7 @@ class BranchAndBoundSearch {
         nodes_[parent_index].num_children = nc;
         if (d - 1 >= 1) {
           for (int c = 0; c < nc; ++c) {
-            if (nodes_[at + c].score <= bound) break;
+            if (nodes_[at + c].score <= bound || nodes_[at + c].score < global_bound_) break;
             if (static_cast<int64_t>(next.size()) < budget) next.push_back(at + c);
           }
         } else {
@@ -1010,16 +1197,26 @@ class BranchAndBoundSearch {
   }
 
   int LowResolutionFor(const std::vector<int>& leaves) {
-    const size_t n = leaves.size();
+    if (leaves.empty()) return HG_OK;
+    std::vector<Node> list;
+    list.reserve(leaves.size());
+    for (int idx : leaves) list.push_back(nodes_[idx]);
+    std::vector<float> scores;
+    const int rc = LowResolutionScores(list, &scores);
+    if (rc != HG_OK) return rc;
+    for (size_t k = 0; k < leaves.size(); ++k) nodes_[leaves[k]].low_resolution_score = scores[k];
+    return HG_OK;
+  }
+
+  // CreateLowResolutionMatcher's closure for the candidate poses of 'list'.
+  int LowResolutionScores(const std::vector<Node>& list, std::vector<float>* out) {
+    const size_t n = list.size();
+    out->assign(n, -std::numeric_limits<float>::infinity());
     if (n == 0) return HG_OK;
     PhaseTimer lt;
     struct Acc { double* t; PhaseTimer* p; ~Acc() { *t += p->Lap(); } } acc{&low_ms_, &lt};
     const int np = data_->num_low_resolution_points;
-    if (np <= 0) {
-      // score / points->size() with an empty cloud is 0 / 0 in the reference.
-      for (int idx : leaves) nodes_[idx].low_resolution_score = -std::numeric_limits<float>::infinity();
-      return HG_OK;
-    }
+    if (np <= 0) return HG_OK;  // score / points->size() with an empty cloud is 0 / 0 in the reference: never passes
     int rc = ws_->h_poses.Reserve(n * 7 * sizeof(float));
     if (rc != HG_OK) return rc;
     rc = ws_->h_low.Reserve(n * sizeof(float));
@@ -1030,7 +1227,7 @@ class BranchAndBoundSearch {
     if (rc != HG_OK) return rc;
     float* hp = ws_->h_poses.as<float>();
     for (size_t k = 0; k < n; ++k) {
-      const Rigid r = PoseOf(nodes_[leaves[k]]);
+      const Rigid r = PoseOf(list[k]);
       float* o = hp + 7 * k;
       o[0] = r.t.x; o[1] = r.t.y; o[2] = r.t.z; o[3] = r.q.w; o[4] = r.q.x; o[5] = r.q.y; o[6] = r.q.z;
     }
@@ -1044,7 +1241,7 @@ class BranchAndBoundSearch {
     HG_CUDA(cudaMemcpyAsync(ws_->h_low.p, ws_->d_low_scores.p, n * sizeof(float), cudaMemcpyDeviceToHost, stream_));
     HG_CUDA(cudaStreamSynchronize(stream_));
     const float* hs = ws_->h_low.as<float>();
-    for (size_t k = 0; k < n; ++k) nodes_[leaves[k]].low_resolution_score = hs[k];
+    for (size_t k = 0; k < n; ++k) (*out)[k] = hs[k];
     return HG_OK;
   }
 
@@ -1062,6 +1259,8 @@ class BranchAndBoundSearch {
   bool strict_ = false;
   Workspace* ws_ = nullptr;
   bool lattice_scored_ = false;
+  float global_bound_ = -std::numeric_limits<float>::infinity();
+  int nxy_ = 0, nz_ = 0, per_scan_ = 0, step_ = 1;
  public:
   double wave_gpu_ms_ = 0.0, low_ms_ = 0.0;
   int64_t wave_parents_ = 0, materialised_ = 0;

@@ -104,8 +104,21 @@ struct hg_grid {
   std::vector<int32_t> brick_coords;
 };
 
+namespace hg {
+// Optional dense copy of a (small) precomputation level: a plain uint8 3-D array
+// over the bounding box of its bricks, x fastest. Coarse levels of the pyramid
+// are a few hundred KB; reading them densely saves the brick-index load.
+struct DenseLevel {
+  const unsigned char* data;  // nullptr = not available
+  int min[3];                 // cell coordinate of data[0]
+  int dim[3];                 // extent in cells
+};
+}  // namespace hg
+
 struct hg_stack_level {
   hg::BrickTable table;
+  hg::DenseLevel dense = {nullptr, {0, 0, 0}, {0, 0, 0}};
+  void* d_dense = nullptr;
   void* d_index = nullptr;
   void* d_bricks = nullptr;
   int64_t num_bricks = 0;

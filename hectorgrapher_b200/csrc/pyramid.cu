@@ -78,6 +78,19 @@ __global__ void __launch_bounds__(256) MaxPoolKernel(const BrickTable src, const
   }
 }
 
+// Expands the bricks of a level into its dense array (which starts zeroed).
+__global__ void __launch_bounds__(256) DensifyKernel(const unsigned char* __restrict__ bricks,
+                                                     const int32_t* __restrict__ brick_coords,
+                                                     const DenseLevel dense, unsigned char* __restrict__ out) {
+  const int b = blockIdx.x;
+  const int bx = brick_coords[3 * b], by = brick_coords[3 * b + 1], bz = brick_coords[3 * b + 2];
+  for (int v = threadIdx.x; v < 512; v += blockDim.x) {
+    const int x = (bx << 3) + (v & 7) - dense.min[0], y = (by << 3) + ((v >> 3) & 7) - dense.min[1],
+              z = (bz << 3) + (v >> 6) - dense.min[2];
+    out[(static_cast<size_t>(z) * dense.dim[1] + y) * dense.dim[0] + x] = bricks[static_cast<size_t>(b) * 512 + v];
+  }
+}
+
 __global__ void LookupU8Kernel(const BrickTable t, const int64_t n, const int32_t* __restrict__ xyz,
                                unsigned char* __restrict__ out) {
   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
@@ -205,6 +218,46 @@ int hg_stack_build(const hg_grid* grid, int branch_and_bound_depth, int full_res
       }
     }
   }
+  // Dense copies of the small levels (<= 32 MiB each).
+  for (int depth = 0; depth != branch_and_bound_depth; ++depth) {
+    hg_stack_level& L = s->levels[depth];
+    const std::vector<int32_t>& coords = s->brick_coords[depth];
+    if (L.num_bricks == 0) continue;
+    int lo[3], hi[3];
+    for (int64_t i = 0; i < L.num_bricks; ++i)
+      for (int k = 0; k < 3; ++k) {
+        const int c = coords[3 * i + k];
+        if (i == 0 || c < lo[k]) lo[k] = c;
+        if (i == 0 || c > hi[k]) hi[k] = c;
+      }
+    int64_t cells = 1;
+    for (int k = 0; k < 3; ++k) cells *= static_cast<int64_t>(hi[k] - lo[k] + 1) * 8;
+    if (cells > (int64_t(32) << 20)) continue;
+    int32_t* d_coords = nullptr;
+    if (cudaMalloc(&L.d_dense, static_cast<size_t>(cells)) != cudaSuccess ||
+        cudaMemset(L.d_dense, 0, static_cast<size_t>(cells)) != cudaSuccess ||
+        cudaMalloc(&d_coords, coords.size() * sizeof(int32_t)) != cudaSuccess ||
+        cudaMemcpy(d_coords, coords.data(), coords.size() * sizeof(int32_t), cudaMemcpyHostToDevice) != cudaSuccess) {
+      SetError("hg_stack_build: dense level allocation failed");
+      if (d_coords) cudaFree(d_coords);
+      return fail(HG_ERR_CUDA);
+    }
+    for (int k = 0; k < 3; ++k) {
+      L.dense.min[k] = lo[k] * 8;
+      L.dense.dim[k] = (hi[k] - lo[k] + 1) * 8;
+    }
+    DensifyKernel<<<static_cast<unsigned>(L.num_bricks), 256>>>(static_cast<const unsigned char*>(L.d_bricks),
+                                                               d_coords, L.dense,
+                                                               static_cast<unsigned char*>(L.d_dense));
+    CountLaunch();
+    const cudaError_t e = cudaDeviceSynchronize();
+    cudaFree(d_coords);
+    if (e != cudaSuccess) {
+      SetError(std::string("DensifyKernel: ") + cudaGetErrorString(e));
+      return fail(HG_ERR_CUDA);
+    }
+    L.dense.data = static_cast<const unsigned char*>(L.d_dense);
+  }
   if (cudaDeviceSynchronize() != cudaSuccess) {
     SetError("hg_stack_build: device error");
     return fail(HG_ERR_CUDA);
@@ -218,6 +271,7 @@ void hg_stack_destroy(hg_stack* stack) {
   for (hg_stack_level& L : stack->levels) {
     if (L.d_index) cudaFree(L.d_index);
     if (L.d_bricks) cudaFree(L.d_bricks);
+    if (L.d_dense) cudaFree(L.d_dense);
   }
   delete stack;
 }
