@@ -48,6 +48,15 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            return int(json.load(f)[kernel]["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def build_workload(seed=2, num_scans=NUM_SCANS, points_per_scan=POINTS_PER_SCAN):
     """C2 inputs: grids as voxel lists, 64 scans in their sensor frames, control poses, block table."""
     from hectorgrapher_b200 import synth
@@ -275,12 +284,60 @@ def correlative_bench(hg, torch, w, rank, world, dist):
                                            "offset": [int(best[3]), int(best[4]), int(best[5])]},
         "lowest_resolution_kernel": {"candidates": lattice_n, "ms": lattice_ms, "candidates_per_s": lattice_cps},
         "roofline": {"bound": "hbm", "achieved": lattice_cps * (n_pts + 24) / world / 1e9, "peak": peak,
-                     "unit": "GB/s", "frac": lattice_cps * (n_pts + 24) / world / 1e9 / peak, "traffic": None,
-                     "kernel": "ScoreLatticeKernel", "algorithmic_bytes_per_candidate": n_pts + 24,
+                     "unit": "GB/s", "frac": lattice_cps * (n_pts + 24) / world / 1e9 / peak,
+                     "traffic": measured_traffic("ScoreLatticeDenseKernel<4>") if world == 1 else None,
+                     "kernel": "ScoreLatticeDenseKernel<4>", "algorithmic_bytes_per_candidate": n_pts + 24,
                      "note": "per GPU; gathers are served by L1/L2 (the level-6 grid is a few hundred KB)"},
         "cpu_baseline": {"value": cpu_rate, "unit": "candidates/s", "cores": cpu_threads, "kind": "port",
                          "sample": cpu_desc},
     }
+
+
+def constraint_bench(hg, torch, w, rank, world, dist, pairs_per_rank=24):
+    """C5 sample: ConstraintBuilder3D::ComputeConstraint for (node, submap) pairs — local correlative
+    match + CeresScanMatcher3D refine — partitioned by job index over ranks."""
+    synth = w["synth"]
+    g_hi = hg.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT, *w["hi"])
+    g_lo = hg.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT, *w["lo"])
+    origin, yaw = w["map_poses"][3]
+    rng = np.random.RandomState(5)
+    cloud = synth.scan(origin, yaw, 64, 512, w["sph"], rng)
+    high = synth.voxel_downsample(cloud, 0.2, 2048, seed=6)
+    low = synth.voxel_downsample(cloud, 0.9, 256, seed=7)
+    hist = np.zeros(8, np.float32)
+    opts = dict(branch_and_bound_depth=7, full_resolution_depth=3, use_rotational_scan_matcher=False,
+                min_low_resolution_score=0.3, linear_xy_search_window=5.0, linear_z_search_window=1.0,
+                angular_search_window=float(np.deg2rad(15.0)))
+    m = hg.Fcsm(g_hi, g_lo, hist, **opts)
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    n_jobs = pairs_per_rank * world
+    jobs = []
+    for j in range(n_jobs):
+        node = np.concatenate([origin + np.array([rng.uniform(-2, 2), rng.uniform(-2, 2), rng.uniform(-0.4, 0.4)]),
+                               synth.quat_from_yaw(yaw + rng.uniform(-0.15, 0.15))])
+        jobs.append(dict(submap_index=0, full=False, node_pose=node, submap_pose=submap, high=high, low=low, hist=hist))
+    o = dict(min_score=0.55, global_localization_min_score=0.6, occupied_space_weights=(5.0, 30.0),
+             translation_weight=10.0, rotation_weight=1.0, max_num_iterations=10)
+    hg.constraints_run_batch([m], [g_hi], [g_lo], jobs[:2], o)  # warm-up
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    res = hg.constraints_run_batch([m], [g_hi], [g_lo], jobs, o, rank, world)
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    mine = [res[j] for j in range(rank, n_jobs, world)]
+    stats = torch.tensor([sum(r["found"] for r in mine), sum(r["num_scored"] for r in mine)], dtype=torch.float64,
+                         device="cuda")
+    if dist is not None:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+    if rank != 0:
+        return None
+    return {"workload": "C5 sample: %d (node, submap) pairs, local Match (5 m / 1 m / 15 deg, N=2048) + refine on "
+                        "{high, low} clouds; jobs partitioned by index over %d rank(s)" % (n_jobs, world),
+            "pairs_per_s": n_jobs / float(dt.item()), "ms_per_pair_per_gpu": 1e3 * float(dt.item()) / pairs_per_rank,
+            "constraints_found": int(stats[0].item()), "candidates_scored": float(stats[1].item())}
 
 
 def run_ours(args, rank, world, local_rank):
@@ -347,7 +404,6 @@ def run_ours(args, rank, world, local_rank):
     if dist is not None:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
     total_ms = float(total_ms.item())
-    clocks = sampler.stop() if sampler else None
 
     # sanity: finite outputs, non-trivial Jacobian
     chk = float(d_r.abs().sum().item())
@@ -376,6 +432,7 @@ def run_ours(args, rank, world, local_rank):
     if dist is not None:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_s = float(e2e_s.item())
+    clocks = sampler.stop() if sampler else None  # sampled across the device-timed and end-to-end loops
     assert abs(float(h_out[0].abs().sum()) - chk) <= 1e-9 * max(1.0, chk)
 
     # Gauss-Newton surface (no Jacobian materialised), for context
@@ -392,6 +449,12 @@ def run_ours(args, rank, world, local_rank):
     except Exception as ex:  # the headline must not be lost to the secondary metric
         log("[rank %d] correlative bench failed: %r" % (rank, ex))
         corr = {"error": repr(ex)}
+    cons = None
+    try:
+        cons = constraint_bench(hg, torch, w, rank, world, dist)
+    except Exception as ex:
+        log("[rank %d] constraint bench failed: %r" % (rank, ex))
+        cons = {"error": repr(ex)}
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -410,7 +473,10 @@ def run_ours(args, rank, world, local_rank):
                        "points_per_step_per_gpu": N, "multi_gpu": "replicas only (one window per GPU)",
                        "l2": "256 MiB flush write between timed steps; working set per step ~0.9 GB"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": measured_traffic("CostKernel<2,true,false>"),
+                         "traffic_note": "bytes per launch (ncu, profiles/r1_ncu_summary.md); algorithmic bytes per "
+                                         "launch = %d" % (ALG_BYTES_PER_POINT * N),
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_point": ALG_BYTES_PER_POINT, "kernel": "CostKernel<2,true,false>"},
             "cpu_baseline": {"value": cpu_rate, "unit": "points/s", "cores": cpu_threads, "kind": "port",
                              "sample": cpu_desc},
@@ -421,6 +487,7 @@ def run_ours(args, rank, world, local_rank):
             "normal_equations": {"ms_per_step": ne_ms, "points_per_s": N / (ne_ms * 1e-3),
                                  "note": "hg_batch_normal_equations: host poses in, 64 x (14x14 JtJ, Jtr, cost) out"},
             "correlative": corr,
+            "constraint_batch": cons,
         }
         print(json.dumps(line), flush=True)
     if dist is not None:

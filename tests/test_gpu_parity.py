@@ -518,3 +518,74 @@ def test_constraint_batch(oracle, hg, world):
         assert np.abs(res[j]["pose"][:3] - p0[:3]).max() < 1e-4
         if j % 2 == 0:
             assert np.abs(shard0[j]["pose"] - res[j]["pose"]).max() == 0
+
+
+# ------------------------------------------------------------ BASELINE.json configs --
+
+def test_config_c1_scan_to_submap(oracle, hg):
+    """C1: one scan of 32 x 640 = 20 480 points against a 5 cm TSDF (+ 0.45 m low-resolution grid):
+    one Evaluate and a full CeresScanMatcher3D::Match, GPU vs oracle."""
+    from hectorgrapher_b200 import synth
+    sph = synth.spheres()
+    poses = [synth.corkscrew_pose(k, 3) for k in range(3)]
+    hi = synth.build_tsdf(0.05, poses, 48, 512, sph)
+    lo = synth.build_tsdf(0.45, poses, 48, 512, sph)
+    o_hi, o_lo = oracle.Grid.tsdf(0.05, 2.5, 1000.0), oracle.Grid.tsdf(0.45, 2.5, 1000.0)
+    o_hi.set_raw(*hi)
+    o_lo.set_raw(*lo)
+    g_hi = hg.Grid.tsdf(0.05, 2.5, 1000.0, *hi, grid_size=o_hi.grid_size)
+    g_lo = hg.Grid.tsdf(0.45, 2.5, 1000.0, *lo, grid_size=o_lo.grid_size)
+    rng = np.random.RandomState(1)
+    origin, yaw = poses[1]
+    cloud = synth.scan(origin, yaw, 32, 640, sph, rng)
+    assert len(cloud) == 20480
+    truth = np.concatenate([origin, synth.quat_from_yaw(yaw)])
+    init = perturbed(truth, rng, 0.1, 0.05)
+    scale = 5.0 / np.sqrt(len(cloud))
+    r0, J0 = oracle.Cost("tsdf", scale, cloud, [o_hi]).evaluate(init)
+    r1, J1 = hg.Cost("tsdf", scale, cloud, [g_hi]).evaluate(init)
+    assert_close(r1, r0, "C1 residuals")
+    assert_close(J1[0], J0[0], "C1 translation jacobian")
+    assert_close(J1[1], J0[1], "C1 rotation jacobian")
+    low = synth.voxel_downsample(cloud, 0.5)
+    p0, s0, _ = oracle.scan_match([cloud, low], [o_hi, o_lo], [5.0, 30.0], 10.0, 1.0, init, max_num_iterations=12,
+                                  use_nonmonotonic_steps=False)
+    p1, s1 = hg.scan_match([cloud, low], [g_hi, g_lo], [5.0, 30.0], 10.0, 1.0, init, max_num_iterations=12,
+                           use_nonmonotonic_steps=False)
+    assert np.abs(p1[:3] - p0[:3]).max() < 1e-4
+    q0, q1 = p0[3:] / np.linalg.norm(p0[3:]), p1[3:] / np.linalg.norm(p1[3:])
+    assert 2 * np.arccos(min(1.0, abs(float(q0 @ q1)))) < 1e-4
+    assert s1[1] < s1[0]
+
+
+def test_config_c3_local_search(oracle, hg, world):
+    """C3: FastCorrelativeScanMatcher3D::Match with the reference's defaults (pose_graph.lua:40-49:
+    7-level pyramid, full_resolution_depth 3, windows 5 m / 1 m / 15 deg, min_rotational_score 0.77,
+    min_low_resolution_score 0.55), N = 2048 points. (The small test submap is observed sparsely, so
+    scores top out near 0.5; min_score is 0.25 here instead of pose_graph.lua's 0.55.)"""
+    synth = world["synth"]
+    rng = np.random.RandomState(3)
+    origin, yaw = world["poses"][1]
+    cloud = synth.scan(origin, yaw, 32, 512, world["sph"], rng)
+    hi = synth.voxel_downsample(cloud, 0.15, 2048, seed=3)
+    lo = synth.voxel_downsample(cloud, 0.9, 200, seed=4)
+    assert len(hi) == 2048
+    hist = synth.rotational_histogram(hi, 120)
+    submap_hist = oracle.rotate_histogram(hist, np.float32(yaw))
+    opts = dict(branch_and_bound_depth=7, full_resolution_depth=3, use_rotational_scan_matcher=True,
+                min_rotational_score=0.77, min_low_resolution_score=0.55, linear_xy_search_window=5.0,
+                linear_z_search_window=1.0, angular_search_window=float(np.deg2rad(15.0)))
+    om = oracle.Fcsm(world["o_tsdf_hi"], world["o_tsdf_lo"], submap_hist, **opts)
+    gm = hg.Fcsm(world["g_tsdf_hi"], world["g_tsdf_lo"], submap_hist, **opts)
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    hits = 0
+    for trial in range(2):
+        node = perturbed(world["truth"], rng, 0.0, 0.15)
+        node[:3] += np.array([rng.uniform(-2, 2), rng.uniform(-2, 2), rng.uniform(-0.5, 0.5)])
+        r0 = om.match(node, submap, hi, lo, hist, min_score=0.25)
+        r1 = gm.match(node, submap, hi, lo, hist, min_score=0.25)
+        assert_same_match(r0, r1)
+        hits += int(r1["found"])
+        if r1["found"]:
+            assert np.abs(np.array([r1["tx"], r1["ty"]]) - world["truth"][:2]).max() < 0.35
+    assert hits >= 1
