@@ -9,6 +9,9 @@
 // The thread-pool / task bookkeeping of the reference (:77-190, :297-337) is
 // control plane and stays with the caller; this entry point is the per-pair
 // compute, partitioned across GPUs by job index (one process per GPU).
+#include <chrono>
+#include <cstdlib>
+
 #include "hg_internal.cuh"
 
 extern "C" int hg_constraints_run_batch(const hg_fcsm* const* matchers, const hg_grid* const* grids,
@@ -29,6 +32,7 @@ extern "C" int hg_constraints_run_batch(const hg_fcsm* const* matchers, const hg
     out.pose[3] = 1.0;
     hg_match_result match;
     int rc;
+    const auto t0 = std::chrono::steady_clock::now();
     if (job.match_full_submap) {
       rc = hg_fcsm_match_full_submap(matchers[job.submap_index], job.global_node_pose + 3,
                                      job.global_submap_pose + 3, &job.data,
@@ -39,6 +43,7 @@ extern "C" int hg_constraints_run_batch(const hg_fcsm* const* matchers, const hg
     }
     if (rc != HG_OK) return rc;
     out.num_candidates_scored = match.num_candidates_scored;
+    const auto t1 = std::chrono::steady_clock::now();
     if (!match.found) continue;
     out.score = match.score;
     out.rotational_score = match.rotational_score;
@@ -56,6 +61,12 @@ extern "C" int hg_constraints_run_batch(const hg_fcsm* const* matchers, const hg
                        out.pose, nullptr);
     if (rc != HG_OK) return rc;
     out.found = 1;
+    if (std::getenv("HG_TRACE") != nullptr) {
+      const auto t2 = std::chrono::steady_clock::now();
+      std::fprintf(stderr, "[hg trace] constraint job %lld: match %.2f ms, refine %.2f ms\n", static_cast<long long>(j),
+                   std::chrono::duration<double, std::milli>(t1 - t0).count(),
+                   std::chrono::duration<double, std::milli>(t2 - t1).count());
+    }
   }
   return HG_OK;
 }

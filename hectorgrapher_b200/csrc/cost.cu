@@ -938,6 +938,7 @@ class LmCost {
  public:
   virtual ~LmCost() {}
   virtual bool Evaluate(double const* const* parameters, double* residuals, double** jacobians) const = 0;
+  virtual bool NormalEquations(double const* const*, double*, double*, double*) const { return false; }
   virtual int num_residuals() const = 0;
 };
 
@@ -947,6 +948,10 @@ class GpuScanCost : public LmCost {
   ~GpuScanCost() override { hg_cost_destroy(c_); }
   bool Evaluate(double const* const* p, double* r, double** J) const override {
     return hg_cost_evaluate(c_, p, r, J) == HG_OK;
+  }
+  // Fused J'J / J'r / cost on the device: the solver never needs the rows.
+  bool NormalEquations(double const* const* p, double* JtJ, double* Jtr, double* cost) const override {
+    return hg_cost_normal_equations(c_, p, JtJ, Jtr, cost) == HG_OK;
   }
   int num_residuals() const override { return hg_cost_num_residuals(c_); }
 

@@ -768,14 +768,18 @@ class BranchAndBoundSearch {
     if (rc != HG_OK) return rc;
     constexpr size_t kDiveWidth = 4096;
     float dive_bound = -std::numeric_limits<float>::infinity();
-    if (!strict && max_depth >= 1 && keys.size() > 2 * kDiveWidth) {
-      std::nth_element(keys.begin(), keys.begin() + kDiveWidth, keys.end(), [](const Key& a, const Key& b) {
-        return a.score > b.score || (a.score == b.score && a.index < b.index);
-      });
-      rc = GreedyDive(keys, kDiveWidth, max_depth, min_score, &dive_bound);
+    if (!strict && max_depth >= 1 && keys.size() >= 16) {
+      const size_t width = std::min(kDiveWidth, keys.size());
+      if (keys.size() > width) {
+        std::nth_element(keys.begin(), keys.begin() + width, keys.end(), [](const Key& a, const Key& b) {
+          return a.score > b.score || (a.score == b.score && a.index < b.index);
+        });
+      }
+      rc = GreedyDive(keys, width, max_depth, min_score, &dive_bound);
       if (rc != HG_OK) return rc;
       if (dive_bound > min_score) {
         global_bound_ = dive_bound;
+        wave_budget_ = 4096;  // the bound keeps the waves small: expand everything that survives it at once
         size_t kept = 0;
         for (const Key& k : keys)
           if (k.score >= dive_bound) keys[kept++] = k;

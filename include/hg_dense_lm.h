@@ -17,6 +17,9 @@
 // on success, radius /= 2^k on failure, and Ceres' default function /
 // gradient / parameter tolerances. The linear step solves the damped normal
 // equations by Cholesky instead of QR of the augmented Jacobian (same minimiser).
+// Only J'J, J'r and the cost are ever needed, so a cost function that can produce
+// those directly (member NormalEquations — the GPU blocks do, without
+// materialising their Jacobian) is asked for them instead of for rows.
 //
 // Templated on the cost-function type so that the same solver drives the GPU
 // cost functions of this library and (in tests) the CPU oracle's.
@@ -118,50 +121,36 @@ class DenseLmProblem {
   LmSummary Solve(const LmOptions& options) {
     LmSummary summary;
     Layout();
-    const int m = NumResiduals();
     const int n = num_local_;
-    std::vector<double> r(m), J(static_cast<size_t>(m) * n), r_new(m);
-    std::vector<double> g(n), scale(n), JtJ(static_cast<size_t>(n) * n), A(static_cast<size_t>(n) * n);
+    std::vector<double> H(static_cast<size_t>(n) * n), g(n), scale(n);
+    std::vector<double> Hs(static_cast<size_t>(n) * n), gs(n), A(static_cast<size_t>(n) * n);
     std::vector<double> delta(n), x_backup;
 
-    if (!EvaluateInternal(r.data(), J.data())) {
+    double cost = 0.0;
+    if (!EvaluateNormal(&cost, H.data(), g.data())) {
       summary.termination = 4;
       return summary;
     }
     ++summary.num_cost_evaluations;
     ++summary.num_jacobian_evaluations;
-    double cost = HalfSquaredNorm(r);
     summary.initial_cost = cost;
     summary.final_cost = cost;
 
-    // Jacobi scaling, computed once from the initial Jacobian (Ceres).
-    for (int j = 0; j < n; ++j) {
-      double s = 0.0;
-      for (int i = 0; i < m; ++i) s += J[static_cast<size_t>(i) * n + j] * J[static_cast<size_t>(i) * n + j];
-      scale[j] = 1.0 / (1.0 + std::sqrt(s));
-    }
-    auto build_normal = [&]() {
-      for (int i = 0; i < m; ++i)
-        for (int j = 0; j < n; ++j) J[static_cast<size_t>(i) * n + j] *= scale[j];
-      std::fill(JtJ.begin(), JtJ.end(), 0.0);
-      std::fill(g.begin(), g.end(), 0.0);
-      for (int i = 0; i < m; ++i) {
-        const double* row = &J[static_cast<size_t>(i) * n];
-        for (int a = 0; a < n; ++a) {
-          g[a] += row[a] * r[i];
-          for (int b = a; b < n; ++b) JtJ[static_cast<size_t>(a) * n + b] += row[a] * row[b];
-        }
+    // Jacobi scaling, computed once from the initial Jacobian's column norms (Ceres).
+    for (int j = 0; j < n; ++j) scale[j] = 1.0 / (1.0 + std::sqrt(std::max(0.0, H[static_cast<size_t>(j) * n + j])));
+    auto apply_scaling = [&]() {
+      for (int a = 0; a < n; ++a) {
+        gs[a] = g[a] * scale[a];
+        for (int b = 0; b < n; ++b) Hs[static_cast<size_t>(a) * n + b] = H[static_cast<size_t>(a) * n + b] * scale[a] * scale[b];
       }
-      for (int a = 0; a < n; ++a)
-        for (int b = 0; b < a; ++b) JtJ[static_cast<size_t>(a) * n + b] = JtJ[static_cast<size_t>(b) * n + a];
     };
-    build_normal();
-    auto max_abs_unscaled_gradient = [&]() {
+    apply_scaling();
+    auto max_abs_gradient = [&]() {
       double v = 0.0;
-      for (int a = 0; a < n; ++a) v = std::max(v, std::fabs(g[a] / scale[a]));
+      for (int a = 0; a < n; ++a) v = std::max(v, std::fabs(g[a]));
       return v;
     };
-    if (max_abs_unscaled_gradient() <= options.gradient_tolerance) {
+    if (max_abs_gradient() <= options.gradient_tolerance) {
       summary.termination = 2;
       return summary;
     }
@@ -179,22 +168,22 @@ class DenseLmProblem {
     for (int iter = 0; iter < options.max_num_iterations; ++iter) {
       ++summary.num_iterations;
       // Damped normal equations.
-      A = JtJ;
+      A = Hs;
       for (int a = 0; a < n; ++a) {
-        const double d = std::min(std::max(JtJ[static_cast<size_t>(a) * n + a], options.min_lm_diagonal),
+        const double d = std::min(std::max(Hs[static_cast<size_t>(a) * n + a], options.min_lm_diagonal),
                                   options.max_lm_diagonal);
         A[static_cast<size_t>(a) * n + a] += d / radius;
       }
-      bool step_ok = CholeskySolve(A, g, n, &delta);
+      bool step_ok = CholeskySolve(A, gs, n, &delta);
       double model_cost_change = 0.0;
       if (step_ok) {
         for (int a = 0; a < n; ++a) delta[a] = -delta[a];
-        // -(J d)'(r + J d / 2) = -(g'd + d'JtJ d / 2)
+        // -(J d)'(r + J d / 2) = -(g'd + d'J'J d / 2)
         double gd = 0.0, dJd = 0.0;
         for (int a = 0; a < n; ++a) {
-          gd += g[a] * delta[a];
+          gd += gs[a] * delta[a];
           double t = 0.0;
-          for (int b = 0; b < n; ++b) t += JtJ[static_cast<size_t>(a) * n + b] * delta[b];
+          for (int b = 0; b < n; ++b) t += Hs[static_cast<size_t>(a) * n + b] * delta[b];
           dJd += delta[a] * t;
         }
         model_cost_change = -(gd + 0.5 * dJd);
@@ -216,9 +205,10 @@ class DenseLmProblem {
       for (const Block& b : blocks_)
         for (int k = 0; k < b.size; ++k) x_norm2 += b.values[k] * b.values[k];
       ApplyDelta(delta, scale);
-      const bool eval_ok = EvaluateInternal(r_new.data(), nullptr);
+      double new_cost = 0.0;
+      const bool eval_ok = EvaluateCost(&new_cost);
       ++summary.num_cost_evaluations;
-      const double new_cost = eval_ok ? HalfSquaredNorm(r_new) : std::numeric_limits<double>::max();
+      if (!eval_ok) new_cost = std::numeric_limits<double>::max();
       double relative_decrease = (cost - new_cost) / model_cost_change;
       if (options.use_nonmonotonic_steps) {
         const double historical =
@@ -230,13 +220,12 @@ class DenseLmProblem {
         ++summary.num_successful_steps;
         const double cost_change = cost - new_cost;
         const double old_cost = cost;
-        cost = new_cost;
-        if (!EvaluateInternal(r.data(), J.data())) {
+        if (!EvaluateNormal(&cost, H.data(), g.data())) {
           summary.termination = 4;
           break;
         }
         ++summary.num_jacobian_evaluations;
-        build_normal();
+        apply_scaling();
         radius = radius / std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * relative_decrease - 1.0, 3));
         radius = std::min(options.max_trust_region_radius, radius);
         decrease_factor = 2.0;
@@ -263,7 +252,7 @@ class DenseLmProblem {
         } else {
           minimum_cost = cost;
         }
-        if (max_abs_unscaled_gradient() <= options.gradient_tolerance) {
+        if (max_abs_gradient() <= options.gradient_tolerance) {
           summary.termination = 2;
           break;
         }
@@ -392,6 +381,141 @@ class DenseLmProblem {
       P[2] = x[1];
       P[3] = x[0];
     }
+  }
+
+  // A cost function may offer its Gauss-Newton terms directly (ambient
+  // parameters, block order): bool NormalEquations(parameters, JtJ, Jtr, cost)
+  // returning false when it does not. Detected at compile time.
+  template <typename F>
+  static auto TryNormalEquations(const F* f, double const* const* p, double* JtJ, double* Jtr, double* c, int)
+      -> decltype(f->NormalEquations(p, JtJ, Jtr, c), bool()) {
+    return f->NormalEquations(p, JtJ, Jtr, c);
+  }
+  template <typename F>
+  static bool TryNormalEquations(const F*, double const* const*, double*, double*, double*, long) {
+    return false;
+  }
+
+  // cost = 1/2 |r|^2, H = J'J and g = J'r in the local (tangent) coordinates of
+  // the non-constant blocks (row-major n x n, n).
+  bool EvaluateNormal(double* cost, double* H, double* g) {
+    const int n = num_local_;
+    std::fill(H, H + static_cast<size_t>(n) * n, 0.0);
+    std::fill(g, g + n, 0.0);
+    *cost = 0.0;
+    std::vector<const double*> params;
+    std::vector<double> JtJ, Jtr, r;
+    std::vector<std::vector<double>> jac_store;
+    std::vector<double*> jac_ptrs;
+    for (const Residual& res : residuals_) {
+      const int nb = static_cast<int>(res.ids.size());
+      params.clear();
+      std::vector<int> off(nb + 1, 0);
+      for (int k = 0; k < nb; ++k) {
+        params.push_back(blocks_[res.ids[k]].values);
+        off[k + 1] = off[k] + blocks_[res.ids[k]].size;
+      }
+      const int na = off[nb];
+      JtJ.assign(static_cast<size_t>(na) * na, 0.0);
+      Jtr.assign(na, 0.0);
+      double c = 0.0;
+      if (!TryNormalEquations(res.f, params.data(), JtJ.data(), Jtr.data(), &c, 0)) {
+        const int nr = res.f->num_residuals();
+        r.assign(nr, 0.0);
+        jac_store.resize(nb);
+        jac_ptrs.resize(nb);
+        for (int k = 0; k < nb; ++k) {
+          jac_store[k].assign(static_cast<size_t>(nr) * blocks_[res.ids[k]].size, 0.0);
+          jac_ptrs[k] = blocks_[res.ids[k]].constant ? nullptr : jac_store[k].data();
+        }
+        if (!res.f->Evaluate(params.data(), r.data(), jac_ptrs.data())) return false;
+        for (int i = 0; i < nr; ++i) {
+          c += r[i] * r[i];
+          for (int ka = 0; ka < nb; ++ka) {
+            if (jac_ptrs[ka] == nullptr) continue;
+            const int sa = blocks_[res.ids[ka]].size;
+            const double* ra = jac_store[ka].data() + static_cast<size_t>(i) * sa;
+            for (int a = 0; a < sa; ++a) {
+              Jtr[off[ka] + a] += ra[a] * r[i];
+              for (int kb = ka; kb < nb; ++kb) {
+                if (jac_ptrs[kb] == nullptr) continue;
+                const int sb = blocks_[res.ids[kb]].size;
+                const double* rb = jac_store[kb].data() + static_cast<size_t>(i) * sb;
+                for (int b = 0; b < sb; ++b) JtJ[static_cast<size_t>(off[ka] + a) * na + off[kb] + b] += ra[a] * rb[b];
+              }
+            }
+          }
+        }
+        c *= 0.5;
+        for (int a = 0; a < na; ++a)
+          for (int b = 0; b < a; ++b) JtJ[static_cast<size_t>(a) * na + b] = JtJ[static_cast<size_t>(b) * na + a];
+      }
+      *cost += c;
+      // Project onto the tangent spaces: H += P_a' JtJ[a,b] P_b, g += P_a' Jtr[a].
+      for (int ka = 0; ka < nb; ++ka) {
+        const Block& A = blocks_[res.ids[ka]];
+        if (A.constant) continue;
+        double Pa[12];
+        LocalBasis(A, Pa);
+        for (int la = 0; la < A.local_size; ++la) {
+          double s = 0.0;
+          for (int a = 0; a < A.size; ++a) s += Pa[a * A.local_size + la] * Jtr[off[ka] + a];
+          g[A.local_offset + la] += s;
+        }
+        for (int kb = 0; kb < nb; ++kb) {
+          const Block& B = blocks_[res.ids[kb]];
+          if (B.constant) continue;
+          double Pb[12];
+          LocalBasis(B, Pb);
+          for (int la = 0; la < A.local_size; ++la)
+            for (int lb = 0; lb < B.local_size; ++lb) {
+              double s = 0.0;
+              for (int a = 0; a < A.size; ++a) {
+                double t = 0.0;
+                for (int b = 0; b < B.size; ++b) t += JtJ[static_cast<size_t>(off[ka] + a) * na + off[kb] + b] * Pb[b * B.local_size + lb];
+                s += Pa[a * A.local_size + la] * t;
+              }
+              H[static_cast<size_t>(A.local_offset + la) * n + B.local_offset + lb] += s;
+            }
+        }
+      }
+    }
+    return true;
+  }
+
+  // d(x (+) delta)/d delta at delta = 0, row-major size x local_size (identity for plain blocks).
+  static void LocalBasis(const Block& b, double* P) {
+    if (b.param == LocalParameterization::kIdentity) {
+      for (int a = 0; a < b.size; ++a)
+        for (int l = 0; l < b.size; ++l) P[a * b.size + l] = a == l ? 1.0 : 0.0;
+    } else {
+      PlusJacobian(b, P);
+    }
+  }
+
+  bool EvaluateCost(double* cost) {
+    *cost = 0.0;
+    std::vector<const double*> params;
+    std::vector<double> r, JtJ, Jtr;
+    for (const Residual& res : residuals_) {
+      params.clear();
+      int na = 0;
+      for (int id : res.ids) {
+        params.push_back(blocks_[id].values);
+        na += blocks_[id].size;
+      }
+      JtJ.assign(static_cast<size_t>(na) * na, 0.0);
+      Jtr.assign(na, 0.0);
+      double c = 0.0;
+      if (!TryNormalEquations(res.f, params.data(), JtJ.data(), Jtr.data(), &c, 0)) {
+        r.assign(res.f->num_residuals(), 0.0);
+        if (!res.f->Evaluate(params.data(), r.data(), nullptr)) return false;
+        for (double v : r) c += v * v;
+        c *= 0.5;
+      }
+      *cost += c;
+    }
+    return true;
   }
 
   bool EvaluateInternal(double* r, double* J) {
