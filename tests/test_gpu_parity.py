@@ -589,3 +589,107 @@ def test_config_c3_local_search(oracle, hg, world):
         if r1["found"]:
             assert np.abs(np.array([r1["tx"], r1["ty"]]) - world["truth"][:2]).max() < 0.35
     assert hits >= 1
+
+
+# ------------------------------------------------------------------ more edge cases --
+
+def test_three_level_pyramid_and_yaw_only(oracle, hg, world):
+    """Multi-resolution lookup over three TSDF levels (fall-through twice), and
+    CeresScanMatcher3D with only_optimize_yaw (YawOnlyQuaternionPlus)."""
+    synth = world["synth"]
+    mid = synth.build_tsdf(0.2, world["poses"], 32, 360, world["sph"])
+    o_mid = oracle.Grid.tsdf(0.2, 2.5, 1000.0)
+    o_mid.set_raw(*mid)
+    g_mid = hg.Grid.tsdf(0.2, 2.5, 1000.0, *mid, grid_size=o_mid.grid_size)
+    og = [world["o_tsdf_hi"], o_mid, world["o_tsdf_lo"]]
+    gg = [world["g_tsdf_hi"], g_mid, world["g_tsdf_lo"]]
+    rng = np.random.RandomState(2)
+    # shift the cloud so that many points leave the fine band and fall through to coarser levels
+    cloud = (world["cloud"] * np.float32(1.01) + np.float32(0.07)).astype(np.float32)
+    p = perturbed(world["truth"], rng)
+    r0, J0 = oracle.Cost("multires_tsdf", 0.03, cloud, og).evaluate(p)
+    r1, J1 = hg.Cost("multires_tsdf", 0.03, cloud, gg).evaluate(p)
+    assert_close(r1, r0, "3-level residuals")
+    assert_close(J1[0], J0[0])
+    assert_close(J1[1], J0[1])
+    # ascending-resolution check (interpolated_multi_resolution_tsdf.h:62-67)
+    with pytest.raises(hg.HgError):
+        hg.Cost("multires_tsdf", 0.03, cloud, [gg[1], gg[0]])
+    init = perturbed(world["truth"], rng, 0.05, 0.02)
+    p0, s0, _ = oracle.scan_match([world["cloud"]], [world["o_tsdf_hi"]], [5.0], 10.0, 1.0, init,
+                                  only_optimize_yaw=True, max_num_iterations=10, use_nonmonotonic_steps=False)
+    p1, s1 = hg.scan_match([world["cloud"]], [world["g_tsdf_hi"]], [5.0], 10.0, 1.0, init, only_optimize_yaw=True,
+                           max_num_iterations=10, use_nonmonotonic_steps=False)
+    assert np.abs(p1 - p0).max() < 1e-4
+
+
+def test_hash_indexed_grid_everywhere(oracle, hg, world):
+    """A grid whose bricks are so scattered that the dense brick index is replaced by the hash:
+    lookups, cost evaluation and the pyramid still agree with the oracle."""
+    xyz, tv, wv = world["tsdf_hi"]
+    far = np.array([[8000, 8000, 8000], [-8100, -8000, 7000]], np.int32)
+    xyz2 = np.concatenate([xyz, far])
+    tv2 = np.concatenate([tv, np.array([0x8000 | 20000, 0x8000 | 9000], np.uint16)])
+    wv2 = np.concatenate([wv, np.array([500, 700], np.uint16)])
+    og = oracle.Grid.tsdf(0.10, 2.5, 1000.0)
+    og.set_raw(xyz2, tv2, wv2)
+    gg = hg.Grid.tsdf(0.10, 2.5, 1000.0, xyz2, tv2, wv2)
+    assert gg.grid_size == og.grid_size == 16384
+    rng = np.random.RandomState(7)
+    q = np.concatenate([xyz2[rng.randint(0, len(xyz2), 5000)] + rng.randint(-2, 3, (5000, 3)), far + 1, far]).astype(np.int32)
+    for what in ["tsd", "weight"]:
+        assert (gg.lookup(what, q).view(np.uint32) == og.lookup(what, q).view(np.uint32)).all()
+    p = perturbed(world["truth"], rng)
+    r0, J0 = oracle.Cost("tsdf", 0.05, world["cloud"], [og]).evaluate(p)
+    r1, J1 = hg.Cost("tsdf", 0.05, world["cloud"], [gg]).evaluate(p)
+    assert_close(r1, r0)
+    assert_close(J1[1], J0[1])
+    os_, gs = oracle.Stack(og, 4, 2), hg.Stack(gg, 4, 2)
+    for d in range(4):
+        xo, vo = os_.export(d)
+        xo, vo = xo[vo != 0], vo[vo != 0]
+        xg, vg = gs.export(d)
+        a, b = np.lexsort(xo.T[::-1]), np.lexsort(xg.T[::-1])
+        assert len(xo) == len(xg) and (xo[a] == xg[b]).all() and (vo[a] == vg[b]).all()
+
+
+def test_gravity_alignment_and_scalar_float_flavor(oracle, hg, world):
+    """Non-identity gravity alignment feeds the rotational prefilter's initial yaw; float_flavor 0
+    (Eigen's scalar summation orders) is matched against the oracle in the same flavor."""
+    synth = world["synth"]
+    rng = np.random.RandomState(14)
+    node = perturbed(world["truth"], rng, 0.6, 0.05)
+    submap = np.array([0.2, 0.1, -0.1, *synth.small_rotation(rng, 0.1)])
+    gravity = synth.small_rotation(rng, 0.3)
+    for flavor in (1, 0):
+        oracle.lib().orc_set_float_flavor(flavor)
+        try:
+            om, gm, hi, lo, hist = world_matchers(oracle, hg, world, "tsdf", float_flavor=flavor)
+            p0, r0, c0 = om.discrete_scans(20, 6, 0.12, node, submap, hi, hist, gravity=gravity)
+            p1, r1, c1 = gm.discrete_scans(20, 6, 0.12, node, submap, hi, hist, gravity=gravity)
+            assert p0.shape == p1.shape and (p0.view(np.uint32) == p1.view(np.uint32)).all()
+            assert (r0.view(np.uint32) == r1.view(np.uint32)).all() and (c0 == c1).all()
+            a = om.match(node, submap, hi, lo, hist, gravity=gravity, min_score=0.2)
+            b = gm.match(node, submap, hi, lo, hist, gravity=gravity, min_score=0.2)
+            assert_same_match(a, b)
+        finally:
+            oracle.lib().orc_set_float_flavor(1)
+
+
+def test_far_and_degenerate_points(oracle, hg, world):
+    """Points far outside every grid, at the origin, and a scan of one point."""
+    rng = np.random.RandomState(3)
+    pts = np.concatenate([world["cloud"][:100], np.array([[0, 0, 0], [1e4, -1e4, 3e3], [500.5, 0.05, -0.05]], np.float32)])
+    p = perturbed(world["truth"], rng)
+    for kind, names in [("occupied", ["prob"]), ("multires_tsdf", ["tsdf_hi", "tsdf_lo"])]:
+        r0, J0 = oracle.Cost(kind, 0.1, pts, [world["o_" + n] for n in names]).evaluate(p)
+        r1, J1 = hg.Cost(kind, 0.1, pts, [world["g_" + n] for n in names]).evaluate(p)
+        assert_close(r1, r0, kind)
+        assert_close(J1[0], J0[0], kind)
+        assert_close(J1[1], J0[1], kind)
+    one = world["cloud"][5:6]
+    r0, J0 = oracle.Cost("interpolated_occupied", 1.0, one, [world["o_prob"]], 0.5).evaluate(np.concatenate([p, p]))
+    r1, J1 = hg.Cost("interpolated_occupied", 1.0, one, [world["g_prob"]], 0.5).evaluate(np.concatenate([p, p]))
+    assert_close(r1, r0)
+    for b in range(4):
+        assert_close(J1[b], J0[b])
