@@ -104,65 +104,28 @@ __device__ __forceinline__ double CellWidthReciprocal(const double seed, const d
 
 // Fetches the 2x2x2 stencil at (ix..ix+1, iy..iy+1, iz..iz+1) in the reference's
 // corner order 111,112,121,122,211,212,221,222 (first digit x, last digit z).
-// Branch-free for the dense brick index: the brick ids of the up to eight
-// bricks the stencil touches are loaded under predicates (a neighbour brick is
-// only needed when the stencil crosses the brick face on that axis, 1/8 of the
-// points per axis), then every corner selects its brick id and loads its voxel.
+// Submap bricks carry a one-voxel apron (hg_internal.cuh), so the whole stencil
+// lives in the brick of its lower corner: one index load, eight voxel loads at
+// fixed offsets, no branches on the brick faces.
 template <typename V>
 __device__ __forceinline__ void FetchStencil(const BrickTable& t, const int ix, const int iy,
                                              const int iz, V* v) {
-  const V zero = V();
-  if (t.hash_mask != 0) {  // sparse-extreme grids only (uniform branch)
+  const int id = BrickId(t, ix, iy, iz);
+  if (id < 0) {
+    const V zero = V();
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int x = ix + ((k >> 2) & 1), y = iy + ((k >> 1) & 1), z = iz + (k & 1);
-      const int id = BrickId(t, x, y, z);
-      v[k] = id < 0 ? zero : __ldg(static_cast<const V*>(t.bricks) + id * 512 + InBrick(x, y, z));
-    }
+    for (int k = 0; k < 8; ++k) v[k] = zero;
     return;
   }
-  const int bx = (ix >> 3) - t.bmin[0], by = (iy >> 3) - t.bmin[1], bz = (iz >> 3) - t.bmin[2];
-  const int lx = ix & 7, ly = iy & 7, lz = iz & 7;
-  const bool cx = lx == 7, cy = ly == 7, cz = lz == 7;
-  const bool vx0 = static_cast<unsigned>(bx) < static_cast<unsigned>(t.bdim[0]);
-  const bool vx1 = static_cast<unsigned>(bx + 1) < static_cast<unsigned>(t.bdim[0]);
-  const bool vy0 = static_cast<unsigned>(by) < static_cast<unsigned>(t.bdim[1]);
-  const bool vy1 = static_cast<unsigned>(by + 1) < static_cast<unsigned>(t.bdim[1]);
-  const bool vz0 = static_cast<unsigned>(bz) < static_cast<unsigned>(t.bdim[2]);
-  const bool vz1 = static_cast<unsigned>(bz + 1) < static_cast<unsigned>(t.bdim[2]);
-  const int sy = t.bdim[0], sz = t.bdim[0] * t.bdim[1];
-  const int32_t* p = t.index + (bz * sz + by * sy + bx);
-  // id[dz][dy][dx]
-  const int id000 = (vx0 && vy0 && vz0) ? __ldg(p) : -1;
-  const int id001 = (cx && vx1 && vy0 && vz0) ? __ldg(p + 1) : -1;
-  const int id010 = (cy && vx0 && vy1 && vz0) ? __ldg(p + sy) : -1;
-  const int id011 = (cx && cy && vx1 && vy1 && vz0) ? __ldg(p + sy + 1) : -1;
-  const int id100 = (cz && vx0 && vy0 && vz1) ? __ldg(p + sz) : -1;
-  const int id101 = (cz && cx && vx1 && vy0 && vz1) ? __ldg(p + sz + 1) : -1;
-  const int id110 = (cz && cy && vx0 && vy1 && vz1) ? __ldg(p + sz + sy) : -1;
-  const int id111 = (cz && cy && cx && vx1 && vy1 && vz1) ? __ldg(p + sz + sy + 1) : -1;
-  const int ox0 = lx, ox1 = (lx + 1) & 7;
-  const int oy0 = ly << 3, oy1 = ((ly + 1) & 7) << 3;
-  const int oz0 = lz << 6, oz1 = ((lz + 1) & 7) << 6;
-  const V* bricks = static_cast<const V*>(t.bricks);
-  // corner (kx, ky, kz) lives in brick (kx && cx, ky && cy, kz && cz)
-  const int i0 = id000;                                       // 111
-  const int i1 = cz ? id100 : id000;                          // 112
-  const int i2 = cy ? id010 : id000;                          // 121
-  const int i3 = cz ? (cy ? id110 : id100) : (cy ? id010 : id000);  // 122
-  const int i4 = cx ? id001 : id000;                          // 211
-  const int i5 = cz ? (cx ? id101 : id100) : (cx ? id001 : id000);  // 212
-  const int i6 = cy ? (cx ? id011 : id010) : (cx ? id001 : id000);  // 221
-  const int i7 = cz ? (cy ? (cx ? id111 : id110) : (cx ? id101 : id100))
-                    : (cy ? (cx ? id011 : id010) : (cx ? id001 : id000));  // 222
-  v[0] = i0 < 0 ? zero : __ldg(bricks + (i0 * 512 + (oz0 | oy0 | ox0)));
-  v[1] = i1 < 0 ? zero : __ldg(bricks + (i1 * 512 + (oz1 | oy0 | ox0)));
-  v[2] = i2 < 0 ? zero : __ldg(bricks + (i2 * 512 + (oz0 | oy1 | ox0)));
-  v[3] = i3 < 0 ? zero : __ldg(bricks + (i3 * 512 + (oz1 | oy1 | ox0)));
-  v[4] = i4 < 0 ? zero : __ldg(bricks + (i4 * 512 + (oz0 | oy0 | ox1)));
-  v[5] = i5 < 0 ? zero : __ldg(bricks + (i5 * 512 + (oz1 | oy0 | ox1)));
-  v[6] = i6 < 0 ? zero : __ldg(bricks + (i6 * 512 + (oz0 | oy1 | ox1)));
-  v[7] = i7 < 0 ? zero : __ldg(bricks + (i7 * 512 + (oz1 | oy1 | ox1)));
+  const V* base = static_cast<const V*>(t.bricks) + (id * kApronBrickVoxels + InApronBrick(ix, iy, iz));
+  v[0] = __ldg(base);
+  v[1] = __ldg(base + 81);
+  v[2] = __ldg(base + 9);
+  v[3] = __ldg(base + 90);
+  v[4] = __ldg(base + 1);
+  v[5] = __ldg(base + 82);
+  v[6] = __ldg(base + 10);
+  v[7] = __ldg(base + 91);
 }
 
 struct ValueGrad {
@@ -391,8 +354,8 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
     if (active) {
       const long long gi = sb.point_offset + i;
       const float* pp = a.points + gi * a.stride;
-      const double px = static_cast<double>(__ldg(pp)), py = static_cast<double>(__ldg(pp + 1)),
-                   pz = static_cast<double>(__ldg(pp + 2));
+      const double px = static_cast<double>(__ldcs(pp)), py = static_cast<double>(__ldcs(pp + 1)),
+                   pz = static_cast<double>(__ldcs(pp + 2));
       const double qw = sb.q[0], qx = sb.q[1], qy = sb.q[2], qz = sb.q[3];
       // uv = 2 (u x p); world = p + w uv + u x uv + t
       double uvx = qy * pz - qz * py, uvy = qz * px - qx * pz, uvz = qx * py - qy * px;
@@ -441,16 +404,18 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
       }
 
       if (!NORMAL_EQ) {
-        if (a.r) a.r[gi] = res;
+        // Outputs are written once and never re-read by the kernel: streaming
+        // stores keep them from evicting the voxel bricks out of L2.
+        if (a.r) __stcs(a.r + gi, res);
         if (a.jt0) {
           double* o = a.jt0 + gi * 3;
-          o[0] = J[0]; o[1] = J[1]; o[2] = J[2];
+          __stcs(o, J[0]); __stcs(o + 1, J[1]); __stcs(o + 2, J[2]);
         }
         if (a.jq0) {
           if (a.vec_store) {
             double2* o = reinterpret_cast<double2*>(a.jq0 + gi * 4);
-            o[0] = make_double2(J[3], J[4]);
-            o[1] = make_double2(J[5], J[6]);
+            __stcs(o, make_double2(J[3], J[4]));
+            __stcs(o + 1, make_double2(J[5], J[6]));
           } else {
             double* o = a.jq0 + gi * 4;
             o[0] = J[3]; o[1] = J[4]; o[2] = J[5]; o[3] = J[6];
@@ -459,13 +424,13 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
         if (TWO_POSE) {
           if (a.jt1) {
             double* o = a.jt1 + gi * 3;
-            o[0] = J[7]; o[1] = J[8]; o[2] = J[9];
+            __stcs(o, J[7]); __stcs(o + 1, J[8]); __stcs(o + 2, J[9]);
           }
           if (a.jq1) {
             if (a.vec_store) {
               double2* o = reinterpret_cast<double2*>(a.jq1 + gi * 4);
-              o[0] = make_double2(J[10], J[11]);
-              o[1] = make_double2(J[12], J[13]);
+              __stcs(o, make_double2(J[10], J[11]));
+              __stcs(o + 1, make_double2(J[12], J[13]));
             } else {
               double* o = a.jq1 + gi * 4;
               o[0] = J[10]; o[1] = J[11]; o[2] = J[12]; o[3] = J[13];

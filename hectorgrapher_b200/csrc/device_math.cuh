@@ -62,17 +62,22 @@ __device__ __forceinline__ int InBrick(const int x, const int y, const int z) {
   return ((z & 7) << 6) | ((y & 7) << 3) | (x & 7);
 }
 
+// Core position inside a 9x9x9 apron brick (submap grids).
+__device__ __forceinline__ int InApronBrick(const int x, const int y, const int z) {
+  return ((z & 7) * 9 + (y & 7)) * 9 + (x & 7);
+}
+
 __device__ __forceinline__ unsigned short LoadU16(const BrickTable& t, int x, int y, int z) {
   const int id = BrickId(t, x, y, z);
   if (id < 0) return 0;
-  return __ldg(static_cast<const unsigned short*>(t.bricks) + static_cast<size_t>(id) * 512 +
-               InBrick(x, y, z));
+  return __ldg(static_cast<const unsigned short*>(t.bricks) + static_cast<size_t>(id) * kApronBrickVoxels +
+               InApronBrick(x, y, z));
 }
 __device__ __forceinline__ ushort2 LoadTsdf(const BrickTable& t, int x, int y, int z) {
   const int id = BrickId(t, x, y, z);
   if (id < 0) return make_ushort2(0, 0);
-  return __ldg(static_cast<const ushort2*>(t.bricks) + static_cast<size_t>(id) * 512 +
-               InBrick(x, y, z));
+  return __ldg(static_cast<const ushort2*>(t.bricks) + static_cast<size_t>(id) * kApronBrickVoxels +
+               InApronBrick(x, y, z));
 }
 __device__ __forceinline__ unsigned char LoadU8(const BrickTable& t, int x, int y, int z) {
   const int id = BrickId(t, x, y, z);

@@ -19,7 +19,7 @@ std::atomic<uint64_t> g_kernel_launches{0};
 
 void SetError(const std::string& msg) { t_error = msg; }
 
-int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int voxel_bytes, BrickTable* table,
+int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int brick_bytes, BrickTable* table,
                      void** d_index, void** d_bricks) {
   const int64_t nb = static_cast<int64_t>(brick_coords.size() / 3);
   int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
@@ -55,7 +55,7 @@ int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int voxel_bytes, 
     HG_CUDA(cudaMalloc(d_index, entries.size() * sizeof(int32_t)));
     HG_CUDA(cudaMemcpy(*d_index, entries.data(), entries.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
     table->hash_mask = cap - 1;
-    const size_t hb = static_cast<size_t>(std::max<int64_t>(nb, 1)) * 512 * voxel_bytes;
+    const size_t hb = static_cast<size_t>(std::max<int64_t>(nb, 1)) * brick_bytes;
     HG_CUDA(cudaMalloc(d_bricks, hb));
     HG_CUDA(cudaMemset(*d_bricks, 0, hb));
     table->index = static_cast<const int32_t*>(*d_index);
@@ -71,9 +71,9 @@ int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int voxel_bytes, 
   }
   HG_CUDA(cudaMalloc(d_index, index.size() * sizeof(int32_t)));
   HG_CUDA(cudaMemcpy(*d_index, index.data(), index.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
-  const size_t brick_bytes = static_cast<size_t>(std::max<int64_t>(nb, 1)) * 512 * voxel_bytes;
-  HG_CUDA(cudaMalloc(d_bricks, brick_bytes));
-  HG_CUDA(cudaMemset(*d_bricks, 0, brick_bytes));
+  const size_t all_bytes = static_cast<size_t>(std::max<int64_t>(nb, 1)) * brick_bytes;
+  HG_CUDA(cudaMalloc(d_bricks, all_bytes));
+  HG_CUDA(cudaMemset(*d_bricks, 0, all_bytes));
   table->index = static_cast<const int32_t*>(*d_index);
   table->bricks = *d_bricks;
   return HG_OK;
@@ -113,9 +113,7 @@ int Flatten(int64_t n, const int32_t* xyz, MakeVoxel make, hg_grid* g) {
   std::unordered_map<BrickKey, int32_t, BrickKeyHash> ids;
   ids.reserve(static_cast<size_t>(n / 16 + 16));
   std::vector<int32_t>& coords = g->brick_coords;
-  std::vector<int32_t> brick_of(static_cast<size_t>(n));
-  for (int64_t i = 0; i < n; ++i) {
-    const BrickKey k{xyz[3 * i] >> 3, xyz[3 * i + 1] >> 3, xyz[3 * i + 2] >> 3};
+  auto brick_id = [&](const BrickKey& k) {
     auto it = ids.find(k);
     if (it == ids.end()) {
       const int32_t id = static_cast<int32_t>(coords.size() / 3);
@@ -124,21 +122,47 @@ int Flatten(int64_t n, const int32_t* xyz, MakeVoxel make, hg_grid* g) {
       coords.push_back(k.z);
       it = ids.emplace(k, id).first;
     }
-    brick_of[static_cast<size_t>(i)] = it->second;
+    return it->second;
+  };
+  // Pass 1: core bricks, in order of first appearance (these come first in the list).
+  std::vector<int32_t> brick_of(static_cast<size_t>(n));
+  for (int64_t i = 0; i < n; ++i) {
+    brick_of[static_cast<size_t>(i)] = brick_id(BrickKey{xyz[3 * i] >> 3, xyz[3 * i + 1] >> 3, xyz[3 * i + 2] >> 3});
+  }
+  const int64_t num_core = static_cast<int64_t>(coords.size() / 3);
+  // Pass 2: a voxel on a low face of its brick is also the apron of the brick(s) before it.
+  for (int64_t i = 0; i < n; ++i) {
+    const int x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+    if ((x & 7) && (y & 7) && (z & 7)) continue;
+    for (int dz = 0; dz <= ((z & 7) == 0 ? 1 : 0); ++dz)
+      for (int dy = 0; dy <= ((y & 7) == 0 ? 1 : 0); ++dy)
+        for (int dx = 0; dx <= ((x & 7) == 0 ? 1 : 0); ++dx)
+          if (dx | dy | dz) brick_id(BrickKey{(x >> 3) - dx, (y >> 3) - dy, (z >> 3) - dz});
   }
   const int64_t nb = static_cast<int64_t>(coords.size() / 3);
-  std::vector<Voxel> bricks(static_cast<size_t>(std::max<int64_t>(nb, 1)) * 512);
+  std::vector<Voxel> bricks(static_cast<size_t>(std::max<int64_t>(nb, 1)) * kApronBrickVoxels);
   std::memset(bricks.data(), 0, bricks.size() * sizeof(Voxel));
   for (int64_t i = 0; i < n; ++i) {
     const int x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
-    bricks[static_cast<size_t>(brick_of[static_cast<size_t>(i)]) * 512 +
-           (((z & 7) << 6) | ((y & 7) << 3) | (x & 7))] = make(i);
+    const Voxel v = make(i);
+    bricks[static_cast<size_t>(brick_of[static_cast<size_t>(i)]) * kApronBrickVoxels +
+           (((z & 7) * 9 + (y & 7)) * 9 + (x & 7))] = v;
+    if ((x & 7) && (y & 7) && (z & 7)) continue;
+    for (int dz = 0; dz <= ((z & 7) == 0 ? 1 : 0); ++dz)
+      for (int dy = 0; dy <= ((y & 7) == 0 ? 1 : 0); ++dy)
+        for (int dx = 0; dx <= ((x & 7) == 0 ? 1 : 0); ++dx) {
+          if (!(dx | dy | dz)) continue;
+          const int32_t id = ids.find(BrickKey{(x >> 3) - dx, (y >> 3) - dy, (z >> 3) - dz})->second;
+          const int lx = dx ? 8 : (x & 7), ly = dy ? 8 : (y & 7), lz = dz ? 8 : (z & 7);
+          bricks[static_cast<size_t>(id) * kApronBrickVoxels + ((lz * 9 + ly) * 9 + lx)] = v;
+        }
   }
-  const int rc = UploadBrickIndex(coords, sizeof(Voxel), &g->dev.table, &g->d_index, &g->d_bricks);
+  const int rc = UploadBrickIndex(coords, static_cast<int>(sizeof(Voxel)) * kApronBrickVoxels, &g->dev.table,
+                                  &g->d_index, &g->d_bricks);
   if (rc != HG_OK) return rc;
-  HG_CUDA(cudaMemcpy(g->d_bricks, bricks.data(), bricks.size() * sizeof(Voxel),
-                     cudaMemcpyHostToDevice));
-  g->num_bricks = nb;
+  HG_CUDA(cudaMemcpy(g->d_bricks, bricks.data(), bricks.size() * sizeof(Voxel), cudaMemcpyHostToDevice));
+  g->num_bricks = num_core;
+  g->num_all_bricks = nb;
   g->num_voxels = n;
   return HG_OK;
 }

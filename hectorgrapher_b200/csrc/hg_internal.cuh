@@ -41,9 +41,17 @@ inline void CountLaunch(uint64_t n = 1) { g_kernel_launches.fetch_add(n, std::me
 //   * 'index' is a dense int32 array over the bounding box of occupied 8x8x8
 //     bricks (brick coordinates = voxel index >> 3, arithmetic shift), holding
 //     the brick id or -1;
-//   * 'bricks' holds brick id * 512 voxels, z-major inside a brick exactly like
-//     the reference's FlatGrid (hybrid_grid_base.h:40-43): ((z*8)+y)*8+x.
-// Voxel type: uint16 (probability), ushort2 {tsd, weight} (TSDF), uint8 (precomputation).
+//   * 'bricks' holds the voxels, z-major inside a brick like the reference's
+//     FlatGrid (hybrid_grid_base.h:40-43). Precomputation levels (uint8) store
+//     the plain 8x8x8 = 512 voxels per brick: ((z*8)+y)*8+x.
+//     Submap grids (uint16 probability, ushort2 {tsd, weight} TSDF) store 9x9x9 =
+//     729 voxels per brick: the 8^3 core plus a one-voxel apron on the high side
+//     of each axis that repeats the neighbouring bricks' first planes, index
+//     ((z*9)+y)*9+x with x,y,z in [0,8]. A 2x2x2 interpolation stencil whose
+//     lower corner lies in a brick's core therefore never leaves that brick: one
+//     index load and eight voxel loads at fixed offsets. Bricks that hold only
+//     apron copies (no core voxel) are created where needed and listed after the
+//     core bricks.
 //   * when that bounding box would be too large (a few voxels at opposite
 //     corners of the +-8192 index range), 'index' is instead an open-addressing
 //     hash table of int4 {bx, by, bz, id} entries (id -1 = empty), selected by
@@ -66,6 +74,9 @@ __host__ __device__ inline unsigned BrickHash(int bx, int by, int bz) {
 // Value decoding constants: value -> float is v' = v & 0x7FFF; v' == 0 ? unknown
 // : v' * scale + offset with offset = lo - scale (value_conversion_tables.cc:29-51),
 // evaluated with separate round-to-nearest multiply and add.
+constexpr int kCoreBrickVoxels = 512;   // precomputation levels
+constexpr int kApronBrickVoxels = 729;  // submap grids
+
 struct ValueDecode {
   float scale;
   float offset;
@@ -93,7 +104,8 @@ struct hg_grid {
   hg::GridDev dev;
   int device = 0;
   int grid_size = 0;
-  int64_t num_bricks = 0;
+  int64_t num_bricks = 0;       // bricks with at least one core voxel (listed first)
+  int64_t num_all_bricks = 0;   // + apron-only bricks
   int64_t num_voxels = 0;
   float relative_truncation_distance = 0.f;
   float max_weight = 0.f;
@@ -136,6 +148,6 @@ struct hg_stack {
 namespace hg {
 // Builds a device brick table (index + zeroed bricks of 'voxel_bytes' each)
 // from a list of brick coordinates. Used by grid upload and the pyramid.
-int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int voxel_bytes, BrickTable* table,
+int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int brick_bytes, BrickTable* table,
                      void** d_index, void** d_bricks);
 }  // namespace hg

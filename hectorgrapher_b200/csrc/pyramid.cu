@@ -27,9 +27,12 @@ __global__ void __launch_bounds__(256) ConvertKernel(const GridDev g, const int6
                                                      unsigned char* __restrict__ out) {
   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= num_voxels) return;
+  // i-th core voxel (brick i / 512, z-major 8^3) inside the 9^3 apron brick.
+  const int v = static_cast<int>(i & 511);
+  const int64_t src = (i >> 9) * kApronBrickVoxels + (((v >> 6) * 9 + ((v >> 3) & 7)) * 9 + (v & 7));
   int cell_value = 0;
   if (g.kind == kGridProb) {
-    const unsigned short raw = static_cast<const unsigned short*>(g.table.bricks)[i];
+    const unsigned short raw = static_cast<const unsigned short*>(g.table.bricks)[src];
     if (raw != 0) {  // the reference iterates non-default voxels only
       // (ValueToProbability(v) - kMinProbability) * (255.f / (kMaxProbability - kMinProbability))
       const float kMin = 0.1f;
@@ -38,7 +41,7 @@ __global__ void __launch_bounds__(256) ConvertKernel(const GridDev g, const int6
       cell_value = RoundToIntF(__fmul_rn(__fsub_rn(p, kMin), __fdiv_rn(255.f, __fsub_rn(kMax, kMin))));
     }
   } else {
-    const ushort2 raw = static_cast<const ushort2*>(g.table.bricks)[i];
+    const ushort2 raw = static_cast<const ushort2*>(g.table.bricks)[src];
     if (raw.x != 0 || raw.y != 0) {
       const float tsd = Decode(g.a, raw.x);
       const float normalized = __fsub_rn(1.f, __fdiv_rn(fabsf(tsd), g.max_tsd));
@@ -170,8 +173,9 @@ int hg_stack_build(const hg_grid* grid, int branch_and_bound_depth, int full_res
   // Level 0: same brick set as the grid, uint8 voxels.
   {
     hg_stack_level& L = s->levels[0];
-    s->brick_coords[0] = grid->brick_coords;
-    rc = UploadBrickIndex(s->brick_coords[0], 1, &L.table, &L.d_index, &L.d_bricks);
+    // core bricks only: apron-only bricks hold no voxel of their own
+    s->brick_coords[0].assign(grid->brick_coords.begin(), grid->brick_coords.begin() + 3 * grid->num_bricks);
+    rc = UploadBrickIndex(s->brick_coords[0], kCoreBrickVoxels, &L.table, &L.d_index, &L.d_bricks);
     if (rc != HG_OK) return fail(rc);
     L.num_bricks = grid->num_bricks;
     const int64_t nv = grid->num_bricks * 512;
@@ -196,7 +200,7 @@ int hg_stack_build(const hg_grid* grid, int branch_and_bound_depth, int full_res
     hg_stack_level& L = s->levels[depth];
     const hg_stack_level& S = s->levels[depth - 1];
     s->brick_coords[depth] = TargetBricks(s->brick_coords[depth - 1], shift, half);
-    rc = UploadBrickIndex(s->brick_coords[depth], 1, &L.table, &L.d_index, &L.d_bricks);
+    rc = UploadBrickIndex(s->brick_coords[depth], kCoreBrickVoxels, &L.table, &L.d_index, &L.d_bricks);
     if (rc != HG_OK) return fail(rc);
     L.num_bricks = static_cast<int64_t>(s->brick_coords[depth].size() / 3);
     if (L.num_bricks > 0) {
@@ -223,7 +227,7 @@ int hg_stack_build(const hg_grid* grid, int branch_and_bound_depth, int full_res
     hg_stack_level& L = s->levels[depth];
     const std::vector<int32_t>& coords = s->brick_coords[depth];
     if (L.num_bricks == 0) continue;
-    int lo[3], hi[3];
+    int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
     for (int64_t i = 0; i < L.num_bricks; ++i)
       for (int k = 0; k < 3; ++k) {
         const int c = coords[3 * i + k];
