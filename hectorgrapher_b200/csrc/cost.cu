@@ -107,17 +107,17 @@ __device__ __forceinline__ double CellWidthReciprocal(const double seed, const d
 // Submap bricks carry a one-voxel apron (hg_internal.cuh), so the whole stencil
 // lives in the brick of its lower corner: one index load, eight voxel loads at
 // fixed offsets, no branches on the brick faces.
-template <typename V>
-__device__ __forceinline__ void FetchStencil(const BrickTable& t, const int ix, const int iy,
-                                             const int iz, V* v) {
-  const int id = BrickId(t, ix, iy, iz);
+// The voxels are the pre-decoded floats (GridDev::decoded); 'absent' is what a
+// voxel of a missing brick reads.
+__device__ __forceinline__ void FetchStencil(const GridDev& g, const int ix, const int iy, const int iz,
+                                             const float absent, float* v) {
+  const int id = BrickId(g.table, ix, iy, iz);
   if (id < 0) {
-    const V zero = V();
 #pragma unroll
-    for (int k = 0; k < 8; ++k) v[k] = zero;
+    for (int k = 0; k < 8; ++k) v[k] = absent;
     return;
   }
-  const V* base = static_cast<const V*>(t.bricks) + (id * kApronBrickVoxels + InApronBrick(ix, iy, iz));
+  const float* base = g.decoded + (id * kApronBrickVoxels + InApronBrick(ix, iy, iz));
   v[0] = __ldg(base);
   v[1] = __ldg(base + 81);
   v[2] = __ldg(base + 9);
@@ -140,11 +140,11 @@ __device__ __forceinline__ ValueGrad LookupOccupancy(const GridDev& g, const dou
   LowerVoxel(g, x, &x1, &x2, &ix);
   LowerVoxel(g, y, &y1, &y2, &iy);
   LowerVoxel(g, z, &z1, &z2, &iz);
-  unsigned short raw[8];
-  FetchStencil<unsigned short>(g.table, ix, iy, iz, raw);
+  float raw[8];
+  FetchStencil(g, ix, iy, iz, g.a.unknown, raw);
   double q[8];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) q[k] = static_cast<double>(Decode(g.a, raw[k]));
+  for (int k = 0; k < 8; ++k) q[k] = static_cast<double>(raw[k]);
   // Ceres' Jet / double is a multiplication by the reciprocal (jet.h), which is
   // what the reference's Jacobian-evaluating instantiation computes.
   const double sx = CellWidthReciprocal(g.inv_resolution_d, x2 - x1);
@@ -242,13 +242,13 @@ __device__ __forceinline__ bool LookupTsdfLevel(const GridDev& g, const double x
   LowerVoxel(g, x, &x1, &x2, &ix);
   LowerVoxel(g, y, &y1, &y2, &iy);
   LowerVoxel(g, z, &z1, &z2, &iz);
-  ushort2 raw[8];
-  FetchStencil<ushort2>(g.table, ix, iy, iz, raw);
+  float raw[8];
+  FetchStencil(g, ix, iy, iz, __int_as_float(0x7fc00000), raw);
   bool o[8];
   int observed = 0;
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    o[k] = (raw[k].y & 0x7FFFu) > 1u;
+    o[k] = raw[k] == raw[k];  // NaN marks an unobserved voxel
     observed += o[k] ? 1 : 0;
   }
   if (MULTI) {
@@ -260,7 +260,7 @@ __device__ __forceinline__ bool LookupTsdfLevel(const GridDev& g, const double x
   }
   double q[8];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) q[k] = static_cast<double>(Decode(g.a, raw[k].x));
+  for (int k = 0; k < 8; ++k) q[k] = static_cast<double>(raw[k]);
   const double sx = CellWidthReciprocal(g.inv_resolution_d, x2 - x1);
   const double sy = CellWidthReciprocal(g.inv_resolution_d, y2 - y1);
   const double sz = CellWidthReciprocal(g.inv_resolution_d, z2 - z1);

@@ -55,7 +55,7 @@ __device__ __forceinline__ int BrickId(const BrickTable& t, const int x, const i
       bz >= static_cast<unsigned>(t.bdim[2])) {
     return -1;
   }
-  return __ldg(t.index + (static_cast<size_t>(bz) * t.bdim[1] + by) * t.bdim[0] + bx);
+  return __ldg(t.index + ((static_cast<int>(bz) * t.bdim[1] + static_cast<int>(by)) * t.bdim[0] + static_cast<int>(bx)));
 }
 
 __device__ __forceinline__ int InBrick(const int x, const int y, const int z) {

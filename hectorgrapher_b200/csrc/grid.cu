@@ -177,6 +177,19 @@ ValueDecode MakeDecode(float unknown, float lo, float hi) {
   return d;
 }
 
+// Fills GridDev::decoded from the raw bricks (same float operations as Decode).
+__global__ void __launch_bounds__(256) DecodeBricksKernel(const GridDev g, const int64_t num_voxels,
+                                                          float* __restrict__ out) {
+  const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (i >= num_voxels) return;
+  if (g.kind == kGridProb) {
+    out[i] = Decode(g.a, static_cast<const unsigned short*>(g.table.bricks)[i]);
+  } else {
+    const ushort2 raw = static_cast<const ushort2*>(g.table.bricks)[i];
+    out[i] = (raw.y & 0x7FFFu) > 1u ? Decode(g.a, raw.x) : __int_as_float(0x7fc00000);
+  }
+}
+
 __global__ void LookupKernel(const GridDev g, const int what, const int64_t n,
                              const int32_t* __restrict__ xyz, float* __restrict__ out) {
   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
@@ -203,6 +216,18 @@ __global__ void CellIndexKernel(const float resolution, const float inv_resoluti
 }  // namespace hg
 
 using namespace hg;
+
+static int BuildDecodedBricks(hg_grid* g) {
+  const int64_t nv = std::max<int64_t>(g->num_all_bricks, 1) * kApronBrickVoxels;
+  HG_CUDA(cudaMalloc(&g->d_decoded, static_cast<size_t>(nv) * sizeof(float)));
+  g->dev.decoded = static_cast<const float*>(g->d_decoded);
+  DecodeBricksKernel<<<static_cast<unsigned>((nv + 255) / 256), 256>>>(g->dev, nv, static_cast<float*>(g->d_decoded));
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  HG_CUDA(cudaDeviceSynchronize());
+  return HG_OK;
+}
+
 
 extern "C" {
 
@@ -232,7 +257,8 @@ int hg_grid_upload_prob(float resolution, int grid_size, int64_t num_voxels, con
   g->dev.min_tsd = 0.f;
   g->dev.max_tsd = 0.f;
   g->grid_size = grid_size > 0 ? grid_size : DeriveGridSize(num_voxels, xyz);
-  const int rc = Flatten<uint16_t>(num_voxels, xyz, [values](int64_t i) { return values[i]; }, g);
+  int rc = Flatten<uint16_t>(num_voxels, xyz, [values](int64_t i) { return values[i]; }, g);
+  if (rc == HG_OK) rc = BuildDecodedBricks(g);
   if (rc != HG_OK) {
     hg_grid_destroy(g);
     return rc;
@@ -265,9 +291,10 @@ int hg_grid_upload_tsdf(float resolution, float relative_truncation_distance, fl
   g->dev.a = MakeDecode(min_tsd, min_tsd, max_tsd);
   g->dev.b = MakeDecode(0.f, 0.f, max_weight);
   g->grid_size = grid_size > 0 ? grid_size : DeriveGridSize(num_voxels, xyz);
-  const int rc = Flatten<ushort2>(
+  int rc = Flatten<ushort2>(
       num_voxels, xyz,
       [tsd_values, weight_values](int64_t i) { return make_ushort2(tsd_values[i], weight_values[i]); }, g);
+  if (rc == HG_OK) rc = BuildDecodedBricks(g);
   if (rc != HG_OK) {
     hg_grid_destroy(g);
     return rc;
@@ -280,6 +307,7 @@ void hg_grid_destroy(hg_grid* grid) {
   if (grid == nullptr) return;
   if (grid->d_index) cudaFree(grid->d_index);
   if (grid->d_bricks) cudaFree(grid->d_bricks);
+  if (grid->d_decoded) cudaFree(grid->d_decoded);
   delete grid;
 }
 

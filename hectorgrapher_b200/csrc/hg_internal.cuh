@@ -87,6 +87,11 @@ enum GridKind { kGridProb = 0, kGridTsdf = 1 };
 
 struct GridDev {
   BrickTable table;
+  // Same bricks (apron layout), pre-decoded for the cost kernels: one float per
+  // voxel. Probability grids: the decoded probability. TSDF grids: the decoded
+  // TSD of an observed voxel, NaN for an unobserved one (weight value 0 or 1) —
+  // the cost functors never read the TSD of an unobserved voxel.
+  const float* decoded;
   float resolution;
   float inv_resolution;     // fl(1 / resolution): fast path of the exact cell-index computation
   double inv_resolution_d;  // 1.0 / double(resolution): seed for the reciprocal of the cell width
@@ -111,6 +116,7 @@ struct hg_grid {
   float max_weight = 0.f;
   void* d_index = nullptr;
   void* d_bricks = nullptr;
+  void* d_decoded = nullptr;
   // Host copy of the brick coordinates (brick id -> brick coords), used to
   // derive the precomputation levels' brick sets.
   std::vector<int32_t> brick_coords;
