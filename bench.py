@@ -36,6 +36,15 @@ REL_TRUNC, MAX_WEIGHT = 2.5, 1000.0
 ALG_BYTES_PER_POINT = 164
 
 
+_JSON_OUT = None
+
+
+def emit(line):
+    out = _JSON_OUT if _JSON_OUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
@@ -187,7 +196,7 @@ def run_reference(args, rank, world):
                          "sample": "CPU restatement (oracle/) of the reference functor; " + desc},
         "e2e": {"value": value, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def correlative_inputs(w):
@@ -489,13 +498,19 @@ def run_ours(args, rank, world, local_rank):
             "correlative": corr,
             "constraint_batch": cons,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
 
 
 def main():
+    # Libraries (NCCL's version banner, for one) may print to stdout; the contract is ONE JSON line
+    # there. Route fd 1 to stderr for the whole run and keep the real stdout for that line.
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
