@@ -9,5 +9,5 @@ present, calls fail loudly.
 from . import capi  # noqa: F401
 from .capi import (  # noqa: F401
     Batch, Cost, Fcsm, Grid, HgError, Stack, build, constraints_run_batch, get_cell_index,
-    kernel_launch_count, lib, low_resolution_scores, scan_match, set_device,
+    adaptive_voxel_filter, kernel_launch_count, lib, low_resolution_scores, scan_match, set_device, voxel_filter,
 )

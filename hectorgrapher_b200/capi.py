@@ -110,6 +110,8 @@ SYMBOLS = {
     "hg_fcsm_score_candidates": (c_i, [vp, c_i, c_i, c_d, vp, vp, vp, c_i, c_i64, vp, vp, vp, vp]),
     "hg_low_resolution_scores": (c_i, [vp, vp, c_i, c_i64, vp, vp]),
     "hg_constraints_run_batch": (c_i, [vp, vp, vp, c_i, vp, c_i64, vp, c_i, c_i, vp]),
+    "hg_voxel_filter": (c_i, [c_f, vp, c_i, c_i64, vp, vp]),
+    "hg_adaptive_voxel_filter": (c_i, [c_f, c_i, c_f, vp, c_i, c_i64, vp, vp]),
 }
 
 
@@ -543,3 +545,21 @@ def constraints_run_batch(matchers, grids, low_grids, jobs, options, shard_index
                         num_scored=int(r.num_candidates_scored)))
     del keep
     return out
+
+
+def voxel_filter(size, pts, stride=3):
+    """Indices of the points sensor::VoxelFilter(size).Filter keeps."""
+    pts = _f32(pts).reshape(-1, stride)
+    kept = np.zeros(len(pts), np.int32)
+    n = c_i64(0)
+    _check(lib().hg_voxel_filter(size, _p(pts), stride, len(pts), C.byref(n), _p(kept)))
+    return kept[:n.value].copy()
+
+
+def adaptive_voxel_filter(max_length, min_num_points, max_range, pts, stride=3):
+    pts = _f32(pts).reshape(-1, stride)
+    kept = np.zeros(len(pts), np.int32)
+    n = c_i64(0)
+    _check(lib().hg_adaptive_voxel_filter(max_length, min_num_points, max_range, _p(pts), stride, len(pts),
+                                          C.byref(n), _p(kept)))
+    return kept[:n.value].copy()

@@ -220,6 +220,56 @@ struct InterpolatedMultiResolutionTSDFPerPointSpaceCostFunction3D {
   }
 };
 
+// sensor::VoxelFilter (sensor/internal/voxel_filter.h:30-60): Filter returns the first point of
+// every voxel, in input order. Works on any point type that starts with float xyz.
+class VoxelFilter {
+ public:
+  explicit VoxelFilter(float size) : size_(size) {}
+  // Indices of the kept points.
+  std::vector<int32_t> FilterIndices(const PointCloudView& cloud) const {
+    std::vector<int32_t> kept(static_cast<size_t>(cloud.size));
+    int64_t n = 0;
+    CheckOk(hg_voxel_filter(size_, cloud.data, cloud.stride, cloud.size, &n, kept.data()), "hg_voxel_filter");
+    kept.resize(static_cast<size_t>(n));
+    return kept;
+  }
+  // The filtered cloud itself (same stride as the input).
+  std::vector<float> Filter(const PointCloudView& cloud) const { return Gather(cloud, FilterIndices(cloud)); }
+  static std::vector<float> Gather(const PointCloudView& cloud, const std::vector<int32_t>& kept) {
+    std::vector<float> out;
+    out.reserve(kept.size() * cloud.stride);
+    for (const int32_t i : kept)
+      out.insert(out.end(), cloud.data + static_cast<size_t>(i) * cloud.stride,
+                 cloud.data + static_cast<size_t>(i + 1) * cloud.stride);
+    return out;
+  }
+
+ private:
+  float size_;
+};
+
+// sensor::AdaptiveVoxelFilter (sensor/internal/adaptive_voxel_filter.h:88-111);
+// options = proto::AdaptiveVoxelFilterOptions {max_length, min_num_points, max_range}.
+class AdaptiveVoxelFilter {
+ public:
+  AdaptiveVoxelFilter(float max_length, int min_num_points, float max_range)
+      : max_length_(max_length), min_num_points_(min_num_points), max_range_(max_range) {}
+  std::vector<float> Filter(const PointCloudView& cloud) const {
+    std::vector<int32_t> kept(static_cast<size_t>(cloud.size));
+    int64_t n = 0;
+    CheckOk(hg_adaptive_voxel_filter(max_length_, min_num_points_, max_range_, cloud.data, cloud.stride, cloud.size,
+                                     &n, kept.data()),
+            "hg_adaptive_voxel_filter");
+    kept.resize(static_cast<size_t>(n));
+    return VoxelFilter::Gather(cloud, kept);
+  }
+
+ private:
+  float max_length_;
+  int min_num_points_;
+  float max_range_;
+};
+
 // proto::CeresScanMatcherOptions3D (ceres_scan_matcher_3d.cc:40-62).
 struct CeresScanMatcherOptions3D {
   std::vector<double> occupied_space_weight;

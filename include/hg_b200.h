@@ -311,6 +311,22 @@ int hg_fcsm_score_candidates(const hg_fcsm* matcher, int linear_xy_window_size,
 int hg_low_resolution_scores(const hg_grid* low_resolution_grid, const float* points,
                              int num_points, int64_t num_poses, const float* poses, float* scores);
 
+/* -------------------------------------------------------- voxel filters -- */
+
+/* sensor::VoxelFilter(size).Filter (sensor/internal/voxel_filter.cc:25-73): the first
+ * point of every voxel of edge 'size', input order kept. Works for any point type whose
+ * first three floats are xyz (stride in floats). Host pointers; writes the indices of
+ * the kept points (capacity num_points) and their number. */
+int hg_voxel_filter(float size, const float* points, int stride_floats, int64_t num_points,
+                    int64_t* num_kept, int32_t* kept_indices);
+
+/* sensor::AdaptiveVoxelFilter(options).Filter (sensor/internal/adaptive_voxel_filter.h:34-111):
+ * drops points beyond max_range, then voxel-filters with the largest edge length <= max_length
+ * (halving, then bisection to within 10 %) that still leaves min_num_points points. */
+int hg_adaptive_voxel_filter(float max_length, int min_num_points, float max_range, const float* points,
+                             int stride_floats, int64_t num_points, int64_t* num_kept,
+                             int32_t* kept_indices);
+
 /* ------------------------------------------------- constraint batches -- */
 
 /* One (node, submap) pair of ConstraintBuilder3D::ComputeConstraint

@@ -14,6 +14,7 @@
 #include "fcsm.hpp"
 #include "grid.hpp"
 #include "interpolation.hpp"
+#include "voxel_filter.hpp"
 
 using namespace oracle;
 
@@ -521,6 +522,22 @@ double orc_fcsm_score_candidates(void* f, int wxy, int wz, double angular_window
     for (auto& t : pool) t.join();
   }
   return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+// ---- voxel filters (row N2) -----------------------------------------------------
+// Returns the number of kept points; writes their indices (input order) to 'kept' (capacity n).
+int orc_voxel_filter(float size, const float* pts, int stride, int n, int32_t* kept) {
+  std::vector<int> all(n);
+  for (int i = 0; i < n; ++i) all[i] = i;
+  const std::vector<int> r = VoxelFilterIndices(size, pts, stride, all);
+  for (size_t i = 0; i < r.size(); ++i) kept[i] = r[i];
+  return static_cast<int>(r.size());
+}
+int orc_adaptive_voxel_filter(float max_length, int min_num_points, float max_range, const float* pts,
+                              int stride, int n, int32_t* kept) {
+  const std::vector<int> r = AdaptiveVoxelFilterIndices(max_length, min_num_points, max_range, pts, stride, n);
+  for (size_t i = 0; i < r.size(); ++i) kept[i] = r[i];
+  return static_cast<int>(r.size());
 }
 
 float orc_low_resolution_score(void* low_grid, const float* pts, int n, const float* pose /* t3 q wxyz */) {

@@ -98,6 +98,8 @@ def lib():
         L.orc_low_resolution_score.restype = c_f
         L.orc_low_resolution_score.argtypes = [vp, vp, c_i, vp]
         L.orc_set_float_flavor.argtypes = [c_i]
+        L.orc_voxel_filter.argtypes = [c_f, vp, c_i, c_i, vp]
+        L.orc_adaptive_voxel_filter.argtypes = [c_f, c_i, c_f, vp, c_i, c_i, vp]
         _LIB = L
     return _LIB
 
@@ -419,3 +421,18 @@ class Fcsm:
 def low_resolution_score(low_grid, pts, pose7):
     pts, pose7 = _f32(pts).reshape(-1, 3), _f32(pose7)
     return lib().orc_low_resolution_score(low_grid.h, _p(pts), len(pts), _p(pose7))
+
+
+def voxel_filter(size, pts, stride=3):
+    """Indices of the points sensor::VoxelFilter(size).Filter keeps (first point per voxel, input order)."""
+    pts = _f32(pts).reshape(-1, stride)
+    kept = np.zeros(len(pts), np.int32)
+    n = lib().orc_voxel_filter(size, _p(pts), stride, len(pts), _p(kept))
+    return kept[:n].copy()
+
+
+def adaptive_voxel_filter(max_length, min_num_points, max_range, pts, stride=3):
+    pts = _f32(pts).reshape(-1, stride)
+    kept = np.zeros(len(pts), np.int32)
+    n = lib().orc_adaptive_voxel_filter(max_length, min_num_points, max_range, _p(pts), stride, len(pts), _p(kept))
+    return kept[:n].copy()

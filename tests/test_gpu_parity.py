@@ -693,3 +693,41 @@ def test_far_and_degenerate_points(oracle, hg, world):
     assert_close(r1, r0)
     for b in range(4):
         assert_close(J1[b], J0[b])
+
+
+# ------------------------------------------------------------------ voxel filters (N2) --
+
+def test_voxel_filter_bit_exact(oracle, hg, world):
+    """sensor::VoxelFilter on the device: exactly the points the CPU filter keeps, in input order."""
+    rng = np.random.RandomState(0)
+    clouds = [world["cloud"], rng.uniform(-30, 30, (50000, 3)).astype(np.float32),
+              np.array([[0, 0, 0], [0.1, -0.1, 0.1], [0.3, -0.1, 0], [0, 0, 0.1]], np.float32),          # voxel_filter_test.cc:30-37
+              np.array([[100000, 0, 0], [100000.001, -0.0001, 0.0001], [100000.003, -0.0001, 0], [-200000, 0, 0]],
+                       np.float32)]                                                                      # :39-46
+    for pts in clouds:
+        for size in [0.01, 0.05, 0.3, 1.7]:
+            a, b = hg.voxel_filter(size, pts), oracle.voxel_filter(size, pts)
+            assert a.tolist() == b.tolist(), (len(pts), size)
+    assert hg.voxel_filter(0.3, clouds[2]).tolist() == [0, 2]
+    assert hg.voxel_filter(0.01, clouds[3]).tolist() == [0, 3]
+    timed = np.array([[-100, 0.3, 0.4, float(i)] for i in range(100)], np.float32)                       # :48-55
+    assert hg.voxel_filter(0.3, timed, stride=4).tolist() == [0]
+    assert hg.voxel_filter(0.3, np.zeros((0, 3), np.float32)).tolist() == []
+    # half-cell boundaries: points exactly between two voxels round away from zero
+    k = rng.randint(-200, 200, (4000, 3))
+    halves = ((k + 0.5) * np.float32(0.25)).astype(np.float32)
+    assert hg.voxel_filter(0.25, halves).tolist() == oracle.voxel_filter(0.25, halves).tolist()
+
+
+def test_adaptive_voxel_filter_bit_exact(oracle, hg, world):
+    """sensor::AdaptiveVoxelFilter (max range, halving, bisection) — same kept indices as the CPU."""
+    rng = np.random.RandomState(1)
+    big = rng.uniform(-20, 20, (30000, 3)).astype(np.float32)
+    cases = [(world["cloud"], 2.0, 150, 50.0),      # trajectory_builder_3d.lua:23-27 high-resolution filter
+             (world["cloud"], 4.0, 200, 60.0),      # low-resolution filter
+             (big, 4.0, 200, 25.0), (big, 0.5, 150, 15.0), (big, 8.0, 25000, 100.0), (big[:100], 1.0, 500, 30.0),
+             (big, 0.05, 29000, 100.0)]             # cannot be met: gives up after the halving loop
+    for pts, max_length, min_points, max_range in cases:
+        a = hg.adaptive_voxel_filter(max_length, min_points, max_range, pts)
+        b = oracle.adaptive_voxel_filter(max_length, min_points, max_range, pts)
+        assert a.tolist() == b.tolist(), (len(pts), max_length, min_points, max_range, len(a), len(b))

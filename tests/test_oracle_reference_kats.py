@@ -304,3 +304,36 @@ def test_rotate_histogram(oracle):
     assert np.allclose(r, [0., 0., 1., 0.], atol=1e-5)
     r = oracle.rotate_histogram(h, np.float32(np.pi / 8))
     assert np.allclose(r, [0.5, 0.5, 0., 0.], atol=1e-5)
+
+
+def test_voxel_filter_first_point_in_each_voxel(oracle):
+    """cartographer/sensor/internal/voxel_filter_test.cc:30-37."""
+    pts = np.array([[0, 0, 0], [0.1, -0.1, 0.1], [0.3, -0.1, 0], [0, 0, 0.1]], np.float32)
+    assert oracle.voxel_filter(0.3, pts).tolist() == [0, 2]
+
+
+def test_voxel_filter_large_coordinates(oracle):
+    """voxel_filter_test.cc:39-46."""
+    pts = np.array([[100000, 0, 0], [100000.001, -0.0001, 0.0001], [100000.003, -0.0001, 0], [-200000, 0, 0]],
+                   np.float32)
+    assert oracle.voxel_filter(0.01, pts).tolist() == [0, 3]
+
+
+def test_voxel_filter_ignores_time(oracle):
+    """voxel_filter_test.cc:48-55 (TimedPointCloud: stride 4)."""
+    pts = np.array([[-100, 0.3, 0.4, float(i)] for i in range(100)], np.float32)
+    assert oracle.voxel_filter(0.3, pts, stride=4).tolist() == [0]
+
+
+def test_adaptive_voxel_filter_reaches_min_num_points(oracle):
+    """adaptive_voxel_filter.h:45-84: the result has at least min_num_points points whenever the
+    input has, is a subsequence of the input, and respects max_range."""
+    rng = np.random.RandomState(0)
+    pts = rng.uniform(-20, 20, (5000, 3)).astype(np.float32)
+    for max_length, min_points in [(4.0, 200), (0.5, 150), (8.0, 3000)]:
+        kept = oracle.adaptive_voxel_filter(max_length, min_points, 25.0, pts)
+        assert len(kept) >= min_points
+        assert (np.diff(kept) > 0).all()
+        assert (np.linalg.norm(pts[kept], axis=1) <= 25.0 + 1e-4).all()
+    few = oracle.adaptive_voxel_filter(1.0, 100, 25.0, pts[:50])
+    assert few.tolist() == [i for i in range(50) if np.linalg.norm(pts[i]) <= 25.0]
