@@ -27,6 +27,7 @@
 // otherwise. Outputs are written in Ceres' layout.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -341,7 +342,24 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
   __syncthreads();
 
   constexpr int P = NumNormalTerms(NC);
-  double acc = 0.0;  // NORMAL_EQ: this thread's term (threadIdx.x < P), accumulated over sub-tiles
+  // NORMAL_EQ: threads 0..127 and 128..255 each own one term (ne_term < P) over one
+  // half of the staged rows. Terms: upper-triangle pairs (ca <= cb), then J'r, then r'r.
+  double acc = 0.0;
+  const int ne_term = threadIdx.x & 127, ne_half = threadIdx.x >> 7;
+  int ne_ca = 0, ne_cb = 0;
+  if (NORMAL_EQ) {
+    int e = ne_term;
+    if (e < NC * (NC + 1) / 2) {
+      while (e >= NC - ne_ca) { e -= NC - ne_ca; ++ne_ca; }
+      ne_cb = ne_ca + e;
+    } else if (e < NC * (NC + 1) / 2 + NC) {
+      ne_ca = e - NC * (NC + 1) / 2;
+      ne_cb = NC;
+    } else {
+      ne_ca = NC;
+      ne_cb = NC;
+    }
+  }
 
   const int tile_end = min(sb.n, tile.start + a.tile_points);
   for (int base = tile.start; base < tile_end; base += kThreads) {
@@ -445,29 +463,31 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
       for (int c = 0; c < NC; ++c) my[c] = J[c];
       my[NC] = res;
       __syncthreads();
-      if (threadIdx.x < P) {
-        // Term e: upper-triangle pairs (ca <= cb) first, then J'r, then r'r.
-        int ca, cb;
-        int e = threadIdx.x;
-        if (e < NC * (NC + 1) / 2) {
-          ca = 0;
-          while (e >= NC - ca) { e -= NC - ca; ++ca; }
-          cb = ca + e;
-        } else if (e < NC * (NC + 1) / 2 + NC) {
-          ca = e - NC * (NC + 1) / 2;
-          cb = NC;
-        } else {
-          ca = NC;
-          cb = NC;
+      if (ne_term < P) {
+        // This thread's term over its half of the staged rows, four independent
+        // partial sums so that the FP64 adds do not form one long dependent chain.
+        const double* ra = rows + (ne_half * (kThreads / 2)) * ROW + ne_ca;
+        const double* rb = rows + (ne_half * (kThreads / 2)) * ROW + ne_cb;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll 4
+        for (int rr = 0; rr < kThreads / 2; rr += 4) {
+          s0 += ra[(rr + 0) * ROW] * rb[(rr + 0) * ROW];
+          s1 += ra[(rr + 1) * ROW] * rb[(rr + 1) * ROW];
+          s2 += ra[(rr + 2) * ROW] * rb[(rr + 2) * ROW];
+          s3 += ra[(rr + 3) * ROW] * rb[(rr + 3) * ROW];
         }
-        double s = 0.0;
-        for (int rr = 0; rr < kThreads; ++rr) s += rows[rr * ROW + ca] * rows[rr * ROW + cb];
-        acc += s;
+        acc += (s0 + s1) + (s2 + s3);
       }
       __syncthreads();
     }
   }
-  if (NORMAL_EQ && threadIdx.x < P) a.partials[static_cast<size_t>(blockIdx.x) * P + threadIdx.x] = acc;
+  if (NORMAL_EQ) {
+    // Combine the two halves (fixed order) and write this tile's partial vector.
+    if (ne_term < P && ne_half == 1) rows[ne_term] = acc;
+    __syncthreads();
+    if (ne_term < P && ne_half == 0) a.partials[static_cast<size_t>(blockIdx.x) * P + ne_term] = acc + rows[ne_term];
+  }
+
 }
 
 // Sums the tile partials of each residual block in tile order (deterministic).
@@ -505,6 +525,7 @@ struct hg_batch {
   // Tile tables for 256-point (output) and 1024-point (normal equations) tiles.
   TileDev* d_tiles_out = nullptr;
   int num_tiles_out = 0;
+  int tile_out = 256;
   TileDev* d_tiles_ne = nullptr;
   int num_tiles_ne = 0;
   int* d_ne_tile_begin = nullptr;  // num_blocks + 1
@@ -525,7 +546,7 @@ struct hg_cost {
 
 namespace {
 
-constexpr int kTileOut = 256;
+constexpr int kTileOut = 1024;
 constexpr int kTileNe = 1024;
 
 int LookupOfKind(int kind) {
@@ -683,7 +704,9 @@ int hg_batch_create(int kind, int num_blocks, const float* points, int stride_fl
   }
   std::vector<TileDev> tiles;
   std::vector<int> tile_begin;
-  BuildTiles(B->offsets, kTileOut, &tiles, nullptr);
+  B->tile_out = kTileOut;
+  if (const char* env = std::getenv("HG_TILE_OUT")) B->tile_out = std::max(256, (std::atoi(env) / 256) * 256);
+  BuildTiles(B->offsets, B->tile_out, &tiles, nullptr);
   B->num_tiles_out = static_cast<int>(tiles.size());
   HG_CUDA(cudaMalloc(&B->d_tiles_out, sizeof(TileDev) * std::max<size_t>(tiles.size(), 1)));
   if (!tiles.empty())
@@ -742,7 +765,7 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
   if (rc != HG_OK) return rc;
   CostArgs a = BaseArgs(B);
   a.tiles = B->d_tiles_out;
-  a.tile_points = kTileOut;
+  a.tile_points = B->tile_out;
   const int64_t N = B->num_points;
   if (!B->two_pose) {
     jt1 = nullptr;
