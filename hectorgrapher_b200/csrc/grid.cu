@@ -19,8 +19,8 @@ std::atomic<uint64_t> g_kernel_launches{0};
 
 void SetError(const std::string& msg) { t_error = msg; }
 
-int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int brick_bytes, BrickTable* table,
-                     void** d_index, void** d_bricks) {
+int BuildBrickIndexHost(const std::vector<int32_t>& brick_coords, BrickTable* table,
+                        std::vector<int32_t>* entries) {
   const int64_t nb = static_cast<int64_t>(brick_coords.size() / 3);
   int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
   for (int64_t i = 0; i < nb; ++i) {
@@ -42,35 +42,36 @@ int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int brick_bytes, 
   if (cells > (int64_t(1) << 26) || cells > 64 * nb + (int64_t(1) << 20)) {
     unsigned cap = 16;
     while (cap < 2 * static_cast<uint64_t>(nb) + 1) cap <<= 1;
-    std::vector<int32_t> entries(static_cast<size_t>(cap) * 4, -1);
+    entries->assign(static_cast<size_t>(cap) * 4, -1);
     for (int64_t i = 0; i < nb; ++i) {
       const int bx = brick_coords[3 * i], by = brick_coords[3 * i + 1], bz = brick_coords[3 * i + 2];
       unsigned h = BrickHash(bx, by, bz) & (cap - 1);
-      while (entries[4 * static_cast<size_t>(h) + 3] >= 0) h = (h + 1) & (cap - 1);
-      entries[4 * static_cast<size_t>(h)] = bx;
-      entries[4 * static_cast<size_t>(h) + 1] = by;
-      entries[4 * static_cast<size_t>(h) + 2] = bz;
-      entries[4 * static_cast<size_t>(h) + 3] = static_cast<int32_t>(i);
+      while ((*entries)[4 * static_cast<size_t>(h) + 3] >= 0) h = (h + 1) & (cap - 1);
+      (*entries)[4 * static_cast<size_t>(h)] = bx;
+      (*entries)[4 * static_cast<size_t>(h) + 1] = by;
+      (*entries)[4 * static_cast<size_t>(h) + 2] = bz;
+      (*entries)[4 * static_cast<size_t>(h) + 3] = static_cast<int32_t>(i);
     }
-    HG_CUDA(cudaMalloc(d_index, entries.size() * sizeof(int32_t)));
-    HG_CUDA(cudaMemcpy(*d_index, entries.data(), entries.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
     table->hash_mask = cap - 1;
-    const size_t hb = static_cast<size_t>(std::max<int64_t>(nb, 1)) * brick_bytes;
-    HG_CUDA(cudaMalloc(d_bricks, hb));
-    HG_CUDA(cudaMemset(*d_bricks, 0, hb));
-    table->index = static_cast<const int32_t*>(*d_index);
-    table->bricks = *d_bricks;
     return HG_OK;
   }
-  std::vector<int32_t> index(static_cast<size_t>(cells), -1);
+  entries->assign(static_cast<size_t>(cells), -1);
   for (int64_t i = 0; i < nb; ++i) {
     const int64_t bx = brick_coords[3 * i] - lo[0];
     const int64_t by = brick_coords[3 * i + 1] - lo[1];
     const int64_t bz = brick_coords[3 * i + 2] - lo[2];
-    index[(bz * table->bdim[1] + by) * table->bdim[0] + bx] = static_cast<int32_t>(i);
+    (*entries)[(bz * table->bdim[1] + by) * table->bdim[0] + bx] = static_cast<int32_t>(i);
   }
-  HG_CUDA(cudaMalloc(d_index, index.size() * sizeof(int32_t)));
-  HG_CUDA(cudaMemcpy(*d_index, index.data(), index.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  return HG_OK;
+}
+
+int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int brick_bytes, BrickTable* table,
+                     void** d_index, void** d_bricks) {
+  const int64_t nb = static_cast<int64_t>(brick_coords.size() / 3);
+  std::vector<int32_t> entries;
+  BuildBrickIndexHost(brick_coords, table, &entries);
+  HG_CUDA(cudaMalloc(d_index, entries.size() * sizeof(int32_t)));
+  HG_CUDA(cudaMemcpy(*d_index, entries.data(), entries.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
   const size_t all_bytes = static_cast<size_t>(std::max<int64_t>(nb, 1)) * brick_bytes;
   HG_CUDA(cudaMalloc(d_bricks, all_bytes));
   HG_CUDA(cudaMemset(*d_bricks, 0, all_bytes));
@@ -308,6 +309,7 @@ void hg_grid_destroy(hg_grid* grid) {
   if (grid->d_index) cudaFree(grid->d_index);
   if (grid->d_bricks) cudaFree(grid->d_bricks);
   if (grid->d_decoded) cudaFree(grid->d_decoded);
+  DestroyGridMutable(grid);
   delete grid;
 }
 

@@ -102,6 +102,8 @@ struct GridDev {
   int kind;
 };
 
+struct GridMutable;  // insert.cu: state of a grid that is written on the device
+
 }  // namespace hg
 
 // Host-side handle definitions (opaque in the public header).
@@ -120,9 +122,12 @@ struct hg_grid {
   // Host copy of the brick coordinates (brick id -> brick coords), used to
   // derive the precomputation levels' brick sets.
   std::vector<int32_t> brick_coords;
+  hg::GridMutable* mut = nullptr;  // created by the first device-side insertion
 };
 
 namespace hg {
+void DestroyGridMutable(hg_grid* grid);  // insert.cu
+
 // Optional dense copy of a (small) precomputation level: a plain uint8 3-D array
 // over the bounding box of its bricks, x fastest. Coarse levels of the pyramid
 // are a few hundred KB; reading them densely saves the brick-index load.
@@ -156,4 +161,8 @@ namespace hg {
 // from a list of brick coordinates. Used by grid upload and the pyramid.
 int UploadBrickIndex(const std::vector<int32_t>& brick_coords, int brick_bytes, BrickTable* table,
                      void** d_index, void** d_bricks);
+// Host half of UploadBrickIndex: fills table->{bmin, bdim, hash_mask} and the index
+// entries (dense int32 array, or int4 hash entries when hash_mask != 0).
+int BuildBrickIndexHost(const std::vector<int32_t>& brick_coords, BrickTable* table,
+                        std::vector<int32_t>* entries);
 }  // namespace hg

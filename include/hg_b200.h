@@ -80,6 +80,61 @@ int hg_grid_lookup(const hg_grid* grid, int what, int64_t n, const int32_t* xyz,
 /* HybridGridBase::GetCellIndex (hybrid_grid_base.h:428-433) on the device. */
 int hg_get_cell_index(float resolution, int64_t n, const float* points_xyz, int32_t* out_xyz);
 
+/* The grid's non-default voxels, i.e. what HybridGrid::ToProto / HybridGridTSDF::ToProto
+ * iterate (hybrid_grid.h:88-99, hybrid_grid_tsdf.h:119-134; order: brick by brick, z-major
+ * inside a brick — the reference's iterator order is a property of its tree and is not
+ * reproduced). values_b is the TSDF weight array (ignored for probability grids). Host
+ * pointers; *num_voxels receives the count and nothing is written when it exceeds
+ * max_voxels (call with max_voxels = 0 to size the arrays). */
+int hg_grid_export(const hg_grid* grid, int64_t max_voxels, int64_t* num_voxels, int32_t* xyz,
+                   uint16_t* values_a, uint16_t* values_b);
+
+/* ------------------------------------------ range-data insertion (N1) -- */
+
+/* proto::ProbabilityGridRangeDataInserterOptions3D
+ * (mapping/proto/3d/probability_grid_range_data_inserter_options_3d.proto). */
+typedef struct hg_occupancy_inserter_options {
+  double hit_probability;
+  double miss_probability;
+  int32_t num_free_space_voxels;
+  int32_t reserved;
+} hg_occupancy_inserter_options;
+
+/* OccupancyGridRangeDataInserter3D::Insert (mapping/3d/range_data_inserter_3d.cc:27-101)
+ * on a device-resident probability grid: every return's cell gets the hit odds, the last
+ * num_free_space_voxels cells of every ray the miss odds, each cell at most once per call
+ * with hits taking precedence (the update-marker rule of HybridGrid::ApplyLookupTable,
+ * hybrid_grid.h:119-130, including FinishUpdate). The grid grows as DynamicGrid does
+ * (hybrid_grid_base.h:385-403). 'returns' are host points, 'stride_floats' floats apart. */
+int hg_grid_insert_occupancy(hg_grid* grid, const hg_occupancy_inserter_options* options,
+                             const float origin[3], const float* returns, int stride_floats,
+                             int64_t num_returns);
+
+/* proto::TSDFRangeDataInserterOptions3D, the fields read by the branch without normal
+ * projection (mapping/proto/3d/tsdf_range_data_inserter_options_3d.proto). */
+typedef struct hg_tsdf_inserter_options {
+  double relative_truncation_distance;
+  double maximum_weight;
+  double weight_function_epsilon;
+  double weight_function_sigma;
+  double min_range;
+  double max_range;
+  double insertion_ratio;
+  int32_t num_free_space_voxels;
+  int32_t reserved;
+} hg_tsdf_inserter_options;
+
+/* TSDFRangeDataInserter3D::Insert with project_sdf_distance_to_scan_normal = false
+ * (mapping/3d/tsdf_range_data_inserter_3d.cc:700-722): insertion-ratio counter, NaN and
+ * range gates, then InsertHit's default ray cast (:294-343) and UpdateCell (:725-737) for
+ * every return. A cell's updates are applied in the reference's order (return by return,
+ * sample by sample), re-quantised to uint16 after each one like HybridGridTSDF::SetCell, so
+ * the stored voxels are the reference's bit for bit. num_updates (may be NULL) receives
+ * the number of (return, sample) cell updates applied. */
+int hg_grid_insert_tsdf(hg_grid* grid, const hg_tsdf_inserter_options* options,
+                        const float origin[3], const float* returns, int stride_floats,
+                        int64_t num_returns, int64_t* num_updates);
+
 /* ------------------------------------------------------- cost functions -- */
 
 /* The eight functors of mapping/internal/3d/scan_matching/, numbered in the

@@ -187,8 +187,9 @@ void orc_insert_occupancy(void* g, const float* origin, int n, const float* pts,
   inserter.Insert(Vector3f(origin[0], origin[1], origin[2]), ToCloud(pts, n, 3), h->prob.get());
 }
 void orc_insert_tsdf(void* g, const float* origin, int n, const float* pts,
-                     float relative_truncation_distance, float maximum_weight,
-                     int num_free_space_voxels, float epsilon, float sigma) {
+                     double relative_truncation_distance, double maximum_weight,
+                     int num_free_space_voxels, double epsilon, double sigma, double min_range,
+                     double max_range, double insertion_ratio) {
   auto* h = static_cast<GridHandle*>(g);
   TsdfInserterOptions o;
   o.relative_truncation_distance = relative_truncation_distance;
@@ -196,9 +197,10 @@ void orc_insert_tsdf(void* g, const float* origin, int n, const float* pts,
   o.num_free_space_voxels = num_free_space_voxels;
   o.weight_function_epsilon = epsilon;
   o.weight_function_sigma = sigma;
-  const Vector3f org(origin[0], origin[1], origin[2]);
-  for (int i = 0; i < n; ++i)
-    TsdfInsertHit(o, Vector3f(pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]), org, h->tsdf.get());
+  o.min_range = min_range;
+  o.max_range = max_range;
+  o.insertion_ratio = insertion_ratio;
+  TsdfInsert(o, Vector3f(origin[0], origin[1], origin[2]), ToCloud(pts, n, 3), h->tsdf.get());
 }
 
 // ---- interpolators (double path) -------------------------------------------

@@ -73,20 +73,27 @@ class OccupancyGridRangeDataInserter3D {
   const std::vector<uint16> miss_table_;
 };
 
+// proto::TSDFRangeDataInserterOptions3D: the numeric options are doubles in the proto
+// (mapping/proto/3d/tsdf_range_data_inserter_options_3d.proto) and are narrowed where the
+// reference narrows them.
 struct TsdfInserterOptions {
-  float relative_truncation_distance = 2.5f;
-  float maximum_weight = 1000.f;
+  double relative_truncation_distance = 2.5;
+  double maximum_weight = 1000.;
   int num_free_space_voxels = 0;
-  float weight_function_epsilon = 0.1f;
-  float weight_function_sigma = 4.f;
+  double weight_function_epsilon = 0.1;
+  double weight_function_sigma = 4.;
+  double min_range = 0.;
+  double max_range = 1e30;
+  double insertion_ratio = 1.;
 };
 
-// Default ray-cast branch of TSDFRangeDataInserter3D::InsertHit + UpdateCell.
+// Default ray-cast branch of TSDFRangeDataInserter3D::InsertHit (:294-343) + UpdateCell (:725-737).
 inline void TsdfInsertHit(const TsdfInserterOptions& options, const Vector3f& hit,
                           const Vector3f& origin, HybridGridTSDF* tsdf) {
   const Vector3f ray(hit.x - origin.x, hit.y - origin.y, hit.z - origin.z);
   const float range = std::sqrt(ray.x * ray.x + (ray.y * ray.y + ray.z * ray.z));
-  const float truncation_distance = options.relative_truncation_distance * tsdf->resolution();
+  const float truncation_distance =
+      static_cast<float>(options.relative_truncation_distance * tsdf->resolution());
   if (range < truncation_distance) return;
   const float truncation_ratio = truncation_distance / range;
   const bool update_free_space = options.num_free_space_voxels > 0;
@@ -101,6 +108,9 @@ inline void TsdfInsertHit(const TsdfInserterOptions& options, const Vector3f& hi
   const Array3i delta = end_cell - begin_cell;
   const int num_samples =
       std::max(std::abs(delta.x), std::max(std::abs(delta.y), std::abs(delta.z)));
+  const float epsilon = static_cast<float>(options.weight_function_epsilon);
+  const float sigma = static_cast<float>(options.weight_function_sigma);
+  const float maximum_weight = static_cast<float>(options.maximum_weight);
   for (int position = 0; position <= num_samples; ++position) {
     const Array3i cell(
         begin_cell.x + static_cast<int>(std::round(float(delta.x) * float(position) / float(num_samples))),
@@ -113,17 +123,40 @@ inline void TsdfInsertHit(const TsdfInserterOptions& options, const Vector3f& hi
     update_tsd = Clamp(update_tsd, -truncation_distance, truncation_distance);
     float update_weight = 1.0f;
     const float normalized = update_tsd / truncation_distance;
-    if (normalized < -options.weight_function_epsilon) {
-      update_weight = float(std::exp(-options.weight_function_sigma *
-                                     std::pow(-normalized - options.weight_function_epsilon, 2)));
+    if (normalized < -epsilon) {
+      // std::pow(float, int) and the product with the float sigma are evaluated in double.
+      update_weight = float(std::exp(-sigma * std::pow(-normalized - epsilon, 2)));
     }
     if (update_weight == 0.f) continue;
     const float old_weight = tsdf->GetWeight(cell);
     const float old_sdf = tsdf->GetTSD(cell);
     float updated_weight = old_weight + update_weight;
     const float updated_sdf = (old_sdf * old_weight + update_tsd * update_weight) / updated_weight;
-    updated_weight = std::min(updated_weight, options.maximum_weight);
+    updated_weight = std::min(updated_weight, maximum_weight);
     tsdf->SetCell(cell, updated_sdf, updated_weight);
+  }
+}
+
+// TSDFRangeDataInserter3D::Insert, the branch without normal projection (:700-722): the
+// insertion-ratio counter, NaN and range gates, then InsertHit per return.
+inline void TsdfInsert(const TsdfInserterOptions& options, const Vector3f& origin,
+                       const std::vector<Vector3f>& returns, HybridGridTSDF* tsdf) {
+  size_t num_inserted_points = 0;
+  size_t num_omitted_points = 0;
+  for (const Vector3f& hit : returns) {
+    if (double(num_inserted_points) <=
+        options.insertion_ratio * double(num_inserted_points + num_omitted_points)) {
+      num_inserted_points++;
+    } else {
+      num_omitted_points++;
+      continue;
+    }
+    if (std::isnan(hit.x) || std::isnan(hit.y) || std::isnan(hit.z)) continue;
+    const Vector3f r(hit.x - origin.x, hit.y - origin.y, hit.z - origin.z);
+    const float r0 = std::sqrt(r.x * r.x + (r.y * r.y + r.z * r.z));
+    if (r0 < options.min_range) continue;
+    if (r0 > options.max_range) continue;
+    TsdfInsertHit(options, hit, origin, tsdf);
   }
 }
 

@@ -62,7 +62,7 @@ def lib():
         L.orc_prob_grid_apply_odds.argtypes = [vp, vp, c_f]
         L.orc_prob_grid_finish_update.argtypes = [vp]
         L.orc_insert_occupancy.argtypes = [vp, vp, c_i, vp, c_f, c_f, c_i]
-        L.orc_insert_tsdf.argtypes = [vp, vp, c_i, vp, c_f, c_f, c_i, c_f, c_f]
+        L.orc_insert_tsdf.argtypes = [vp, vp, c_i, vp, c_d, c_d, c_i, c_d, c_d, c_d, c_d, c_d]
         L.orc_interpolate.argtypes = [vp, c_i, vp, vp]
         L.orc_cost_new.restype = vp
         L.orc_cost_new.argtypes = [c_i, c_d, vp, c_i, c_i, vp, c_i, c_d]
@@ -204,11 +204,13 @@ class Grid:
                                    num_free_space_voxels)
 
     def insert_tsdf(self, origin, pts, relative_truncation_distance=2.5, maximum_weight=1000.0,
-                    num_free_space_voxels=0, epsilon=0.1, sigma=4.0):
+                    num_free_space_voxels=0, epsilon=0.1, sigma=4.0, min_range=0.0, max_range=1e30,
+                    insertion_ratio=1.0):
         origin = _f32(origin)
         pts = _f32(pts).reshape(-1, 3)
         lib().orc_insert_tsdf(self.h, _p(origin), len(pts), _p(pts), relative_truncation_distance,
-                              maximum_weight, num_free_space_voxels, epsilon, sigma)
+                              maximum_weight, num_free_space_voxels, epsilon, sigma, min_range, max_range,
+                              insertion_ratio)
 
     def interpolate(self, xyz):
         xyz = _f64(xyz).reshape(-1, 3)

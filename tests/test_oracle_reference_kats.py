@@ -337,3 +337,83 @@ def test_adaptive_voxel_filter_reaches_min_num_points(oracle):
         assert (np.linalg.norm(pts[kept], axis=1) <= 25.0 + 1e-4).all()
     few = oracle.adaptive_voxel_filter(1.0, 100, 25.0, pts[:50])
     assert few.tolist() == [i for i in range(50) if np.linalg.norm(pts[i]) <= 25.0]
+
+
+def _insert_reference_point_cloud(g):
+    """range_data_inserter_3d_test.cc:43-51."""
+    g.insert_occupancy([0.0, 0.0, -4.0], [[-3, -1, 4], [-2, 0, 4], [-1, 1, 4], [0, 2, 4]], 0.7, 0.4, 1000)
+
+
+def test_range_data_inserter_insert_point_cloud(oracle):
+    """cartographer/mapping/3d/range_data_inserter_3d_test.cc:72-98 (resolution 1, hit 0.7, miss 0.4,
+    num_free_space_voxels 1000)."""
+    g = oracle.Grid.prob(1.0)
+    _insert_reference_point_cloud(g)
+
+    def p(x, y, z):
+        return g.lookup("probability", g.cell_index([[x, y, z]]))[0]
+
+    def known(x, y, z):
+        return g.lookup("raw_a", g.cell_index([[x, y, z]]))[0] != 0
+
+    for z in (-4.0, -3.0, -2.0):
+        assert abs(p(0.0, 0.0, z) - 0.4) < 1e-4
+    for x in range(-4, 5):
+        for y in range(-4, 5):
+            if x < -3 or x > 0 or y != x + 2:
+                assert not known(x, y, 4.0)
+            else:
+                assert abs(p(x, y, 4.0) - 0.7) < 1e-4
+
+
+def test_range_data_inserter_probability_progression(oracle):
+    """range_data_inserter_3d_test.cc:100-122."""
+    g = oracle.Grid.prob(1.0)
+    _insert_reference_point_cloud(g)
+
+    def p(x, y, z):
+        return g.lookup("probability", g.cell_index([[x, y, z]]))[0]
+
+    assert abs(p(-2, 0, 4) - 0.7) < 1e-4
+    assert abs(p(-2, 0, 3) - 0.4) < 1e-4
+    assert abs(p(0, 0, -3) - 0.4) < 1e-4
+    for _ in range(1000):
+        _insert_reference_point_cloud(g)
+    assert abs(p(-2, 0, 4) - 0.9) < 1e-3
+    assert abs(p(-2, 0, 3) - 0.1) < 1e-3
+    assert abs(p(0, 0, -3) - 0.1) < 1e-3
+
+
+def test_tsdf_insert_single_ray_properties(oracle):
+    """No reference test exists for TSDFRangeDataInserter3D; these are the properties its code
+    states (tsdf_range_data_inserter_3d.cc:294-343, 725-737): only cells within the truncation
+    distance of the hit along the ray are written, the TSD is range - |cell - origin| clamped,
+    the weight in front of the surface is 1 and repeated insertion keeps the TSD and adds weight."""
+    res, rtd = 0.1, 2.5
+    g = oracle.Grid.tsdf(res, rtd, 1000.0)
+    origin = np.array([0.0, 0.0, 0.0], np.float32)
+    hit = np.array([[2.0, 0.0, 0.0]], np.float32)
+    g.insert_tsdf(origin, hit, rtd, 1000.0, 0, 0.1, 4.0)
+    xyz, tsd_raw, w_raw = g.export()
+    assert len(xyz) >= 5 and (xyz[:, 1] == 0).all() and (xyz[:, 2] == 0).all()
+    centers = xyz[:, 0] * np.float32(res)
+    assert centers.min() >= 2.0 - rtd * res - res and centers.max() <= 2.0 + rtd * res + res
+    tsd = g.lookup("tsd", xyz)
+    w = g.lookup("weight", xyz)
+    want = np.clip(2.0 - centers, -rtd * res, rtd * res)
+    assert np.allclose(tsd, want, atol=2 * rtd * res / 32766 + 1e-6)
+    assert np.allclose(w[tsd > -0.1 * rtd * res], 1.0, atol=1e-1)
+    assert (w[tsd < -0.5 * rtd * res] < 0.9).all()
+    g.insert_tsdf(origin, hit, rtd, 1000.0, 0, 0.1, 4.0)
+    assert np.allclose(g.lookup("tsd", xyz), tsd, atol=1e-4)
+    assert np.allclose(g.lookup("weight", xyz), 2 * w, atol=1e-1)
+    # The gates of Insert (:700-722): range limits and the insertion ratio.
+    g2 = oracle.Grid.tsdf(res, rtd, 1000.0)
+    g2.insert_tsdf(origin, hit, rtd, 1000.0, 0, 0.1, 4.0, min_range=3.0)
+    assert len(g2.export()[0]) == 0
+    g2.insert_tsdf(origin, hit, rtd, 1000.0, 0, 0.1, 4.0, max_range=1.0)
+    assert len(g2.export()[0]) == 0
+    many = np.repeat(hit, 10, axis=0)
+    g2.insert_tsdf(origin, many, rtd, 1000.0, 0, 0.1, 4.0, insertion_ratio=0.3)
+    # the counter admits returns 0, 4, 7 (inserted <= 0.3 * seen)
+    assert abs(g2.lookup("weight", [[20, 0, 0]])[0] - 3.0) < 1e-1
