@@ -50,6 +50,18 @@ class MatchResult(C.Structure):
                 ("num_lowest_resolution_candidates", c_i64), ("lowest_resolution_kernel_ms", c_f)]
 
 
+class OccupancyInserterOptions(C.Structure):
+    _fields_ = [("hit_probability", c_d), ("miss_probability", c_d), ("num_free_space_voxels", C.c_int32),
+                ("reserved", C.c_int32)]
+
+
+class TsdfInserterOptions(C.Structure):
+    _fields_ = [("relative_truncation_distance", c_d), ("maximum_weight", c_d),
+                ("weight_function_epsilon", c_d), ("weight_function_sigma", c_d), ("min_range", c_d),
+                ("max_range", c_d), ("insertion_ratio", c_d), ("num_free_space_voxels", C.c_int32),
+                ("reserved", C.c_int32)]
+
+
 class ConstraintJob(C.Structure):
     _fields_ = [("submap_index", C.c_int32), ("match_full_submap", C.c_int32),
                 ("global_node_pose", c_d * 7), ("global_submap_pose", c_d * 7), ("data", NodeData)]
@@ -110,6 +122,9 @@ SYMBOLS = {
     "hg_fcsm_score_candidates": (c_i, [vp, c_i, c_i, c_d, vp, vp, vp, c_i, c_i64, vp, vp, vp, vp]),
     "hg_low_resolution_scores": (c_i, [vp, vp, c_i, c_i64, vp, vp]),
     "hg_constraints_run_batch": (c_i, [vp, vp, vp, c_i, vp, c_i64, vp, c_i, c_i, vp]),
+    "hg_grid_export": (c_i, [vp, c_i64, vp, vp, vp, vp]),
+    "hg_grid_insert_occupancy": (c_i, [vp, vp, vp, vp, c_i, c_i64]),
+    "hg_grid_insert_tsdf": (c_i, [vp, vp, vp, vp, c_i, c_i64, vp]),
     "hg_voxel_filter": (c_i, [c_f, vp, c_i, c_i64, vp, vp]),
     "hg_adaptive_voxel_filter": (c_i, [c_f, c_i, c_f, vp, c_i, c_i64, vp, vp]),
 }
@@ -209,6 +224,38 @@ class Grid:
         code = {"probability": 0, "tsd": 1, "weight": 2}[what]
         _check(lib().hg_grid_lookup(self.h, code, len(xyz), _p(xyz), _p(out)))
         return out
+
+    def export(self):
+        """(xyz [n,3] int32, values_a [n] uint16, values_b [n] uint16 or None): the non-default voxels."""
+        n = c_i64(0)
+        _check(lib().hg_grid_export(self.h, 0, C.byref(n), None, None, None))
+        xyz = np.zeros((n.value, 3), np.int32)
+        a = np.zeros(n.value, np.uint16)
+        b = np.zeros(n.value, np.uint16) if self.is_tsdf else None
+        if n.value:
+            _check(lib().hg_grid_export(self.h, n.value, C.byref(n), _p(xyz), _p(a),
+                                        _p(b) if b is not None else None))
+        return xyz, a, b
+
+    def insert_occupancy(self, origin, pts, hit_probability, miss_probability, num_free_space_voxels, stride=3):
+        """OccupancyGridRangeDataInserter3D::Insert on the device."""
+        origin = _f32(origin)
+        pts = _f32(pts).reshape(-1, stride)
+        o = OccupancyInserterOptions(hit_probability, miss_probability, num_free_space_voxels, 0)
+        _check(lib().hg_grid_insert_occupancy(self.h, C.byref(o), _p(origin), _p(pts), stride, len(pts)))
+
+    def insert_tsdf(self, origin, pts, relative_truncation_distance=2.5, maximum_weight=1000.0,
+                    num_free_space_voxels=0, epsilon=0.1, sigma=4.0, min_range=0.0, max_range=1e30,
+                    insertion_ratio=1.0, stride=3):
+        """TSDFRangeDataInserter3D::Insert (no normal projection) on the device; returns the number of
+        (return, sample) cell updates applied."""
+        origin = _f32(origin)
+        pts = _f32(pts).reshape(-1, stride)
+        o = TsdfInserterOptions(relative_truncation_distance, maximum_weight, epsilon, sigma, min_range,
+                                max_range, insertion_ratio, num_free_space_voxels, 0)
+        n = c_i64(0)
+        _check(lib().hg_grid_insert_tsdf(self.h, C.byref(o), _p(origin), _p(pts), stride, len(pts), C.byref(n)))
+        return n.value
 
 
 def get_cell_index(resolution, pts):
