@@ -349,6 +349,53 @@ def constraint_bench(hg, torch, w, rank, world, dist, pairs_per_rank=24):
             "constraints_found": int(stats[0].item()), "candidates_scored": float(stats[1].item())}
 
 
+def insertion_bench(hg, torch, w, scans=6):
+    """N1: TSDFRangeDataInserter3D::Insert of whole scans (100k returns each) into a device-resident
+    0.10 m TSDF submap, host points in, grid ready for matching out; CPU baseline = the oracle's
+    sequential inserter (the reference inserts on one thread). Rank 0 only: one submap does not shard."""
+    from oracle import pyoracle
+    synth = w["synth"]
+    clouds = []
+    for k in range(scans):
+        origin, yaw = w["map_poses"][k % len(w["map_poses"])]
+        rng = np.random.RandomState(100 + k)
+        c = synth.scan(origin, yaw, 64, 1600, w["sph"], rng)
+        q = synth.quat_from_yaw(yaw)
+        clouds.append((origin.astype(np.float32),
+                       (synth.quat_rotate(q, c.astype(np.float64)) + origin).astype(np.float32)))
+    opts = dict(relative_truncation_distance=2.5, maximum_weight=1000.0, num_free_space_voxels=0, epsilon=1.0,
+                sigma=4.0, min_range=0.4, max_range=60.0, insertion_ratio=1.0)
+    empty = np.zeros((0, 3), np.int32)
+    g = hg.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT, empty, [], [])
+    for origin, pts in clouds[:2]:  # warm-up: allocations, first bricks
+        g.insert_tsdf(origin, pts, **opts)
+    g = hg.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT, empty, [], [])
+    g.insert_tsdf(*clouds[0], **opts)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    updates = 0
+    returns = 0
+    for origin, pts in clouds[1:]:
+        updates += g.insert_tsdf(origin, pts, **opts)
+        returns += len(pts)
+    torch.cuda.synchronize()
+    gpu_s = time.perf_counter() - t0
+    o = pyoracle.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT)
+    o.insert_tsdf(*clouds[0], **opts)
+    t0 = time.perf_counter()
+    for origin, pts in clouds[1:3]:
+        o.insert_tsdf(origin, pts, **opts)
+    cpu_s = time.perf_counter() - t0
+    cpu_returns = sum(len(p) for _, p in clouds[1:3])
+    return {"workload": "N1: %d scans x ~%d returns inserted into a 0.10 m TSDF submap (default ray cast, "
+                        "truncation 2.5 voxels), host points in, apron + decoded copies regenerated after every "
+                        "scan" % (scans - 1, returns // max(1, scans - 1)),
+            "returns_per_s": returns / gpu_s, "cell_updates_per_s": updates / gpu_s,
+            "ms_per_scan": 1e3 * gpu_s / (scans - 1), "bricks": int(g.num_bricks),
+            "cpu_baseline": {"value": cpu_returns / cpu_s, "unit": "returns/s", "cores": 1, "kind": "port",
+                             "sample": "2 of the same scans, sequential oracle inserter"}}
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import hectorgrapher_b200 as hg
@@ -465,6 +512,14 @@ def run_ours(args, rank, world, local_rank):
         log("[rank %d] constraint bench failed: %r" % (rank, ex))
         cons = {"error": repr(ex)}
 
+    ins = None
+    if rank == 0:
+        try:
+            ins = insertion_bench(hg, torch, w)
+        except Exception as ex:
+            log("[rank 0] insertion bench failed: %r" % (ex,))
+            ins = {"error": repr(ex)}
+
     if rank == 0:
         peak, peak_src = measured_peak()
         ms_per_step = total_ms / args.steps
@@ -497,6 +552,7 @@ def run_ours(args, rank, world, local_rank):
                                  "note": "hg_batch_normal_equations: host poses in, 64 x (14x14 JtJ, Jtr, cost) out"},
             "correlative": corr,
             "constraint_batch": cons,
+            "insertion": ins,
         }
         emit(line)
     if dist is not None:

@@ -113,6 +113,7 @@ class DeviceGrid {
   }
   ~DeviceGrid() { hg_grid_destroy(grid_); }
   const hg_grid* get() const { return grid_; }
+  hg_grid* mutable_get() { return grid_; }  // for the range-data inserters
 
  private:
   explicit DeviceGrid(hg_grid* g) : grid_(g) {}
@@ -268,6 +269,44 @@ class AdaptiveVoxelFilter {
   float max_length_;
   int min_num_points_;
   float max_range_;
+};
+
+// sensor::RangeData (sensor/range_data.h:45-57) as a view: origin + returns ('misses' are not
+// read by the 3D inserters).
+struct RangeDataView {
+  std::array<float, 3> origin{{0.f, 0.f, 0.f}};
+  PointCloudView returns;
+};
+
+// mapping::OccupancyGridRangeDataInserter3D (mapping/3d/range_data_inserter_3d.h:33-52); options =
+// proto::ProbabilityGridRangeDataInserterOptions3D. Insert writes the device-resident grid in place.
+class OccupancyGridRangeDataInserter3D {
+ public:
+  explicit OccupancyGridRangeDataInserter3D(const hg_occupancy_inserter_options& options) : options_(options) {}
+  void Insert(const RangeDataView& range_data, DeviceGrid* grid) const {
+    CheckOk(hg_grid_insert_occupancy(grid->mutable_get(), &options_, range_data.origin.data(),
+                                     range_data.returns.data, range_data.returns.stride, range_data.returns.size),
+            "hg_grid_insert_occupancy");
+  }
+
+ private:
+  hg_occupancy_inserter_options options_;
+};
+
+// mapping::TSDFRangeDataInserter3D (mapping/3d/tsdf_range_data_inserter_3d.h:32-46) for
+// project_sdf_distance_to_scan_normal = false; options = the fields of
+// proto::TSDFRangeDataInserterOptions3D that branch reads.
+class TSDFRangeDataInserter3D {
+ public:
+  explicit TSDFRangeDataInserter3D(const hg_tsdf_inserter_options& options) : options_(options) {}
+  void Insert(const RangeDataView& range_data, DeviceGrid* grid) const {
+    CheckOk(hg_grid_insert_tsdf(grid->mutable_get(), &options_, range_data.origin.data(), range_data.returns.data,
+                                range_data.returns.stride, range_data.returns.size, nullptr),
+            "hg_grid_insert_tsdf");
+  }
+
+ private:
+  hg_tsdf_inserter_options options_;
 };
 
 // proto::CeresScanMatcherOptions3D (ceres_scan_matcher_3d.cc:40-62).

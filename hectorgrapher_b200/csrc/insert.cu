@@ -18,8 +18,8 @@
 //      (return, sample) pair its sequence number — the reference's visiting order;
 //   2. one thread per (return, sample) computes the cell and the update (tsd, weight)
 //      with the reference's float operations and emits a 42-bit cell key;
-//   3. a stable radix sort by key groups the updates of a cell and keeps them in
-//      sequence order inside the group;
+//   3. a stable radix sort by key (the update pair rides along as the value) groups the
+//      updates of a cell and keeps them in sequence order inside the group;
 //   4. new bricks are created (host bookkeeping over the few thousand touched bricks);
 //   5. one thread per touched cell replays that cell's updates in order on the stored
 //      uint16 pair — bit-identical to the sequential loop, no atomics on voxel data;
@@ -31,7 +31,9 @@
 #include <thrust/iterator/counting_iterator.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <unordered_map>
 
@@ -67,6 +69,26 @@ inline void CoordsOfBrickKey(const uint64_t k, int* bx, int* by, int* bz) {
   *by = static_cast<int>((k >> 11) & 2047u) - 1024;
   *bz = static_cast<int>((k >> 22) & 2047u) - 1024;
 }
+
+// HG_TRACE=1 prints phase timings of every insertion to stderr (synchronises at phase ends).
+struct PhaseTrace {
+  bool on;
+  std::chrono::steady_clock::time_point t;
+  std::string text;
+  PhaseTrace() : on(std::getenv("HG_TRACE") != nullptr), t(std::chrono::steady_clock::now()) {}
+  void Mark(const char* what) {
+    if (!on) return;
+    cudaDeviceSynchronize();
+    const auto now = std::chrono::steady_clock::now();
+    char buf[96];
+    std::snprintf(buf, sizeof(buf), " %s %.3f", what, std::chrono::duration<double, std::milli>(now - t).count());
+    text += buf;
+    t = now;
+  }
+  ~PhaseTrace() {
+    if (on) std::fprintf(stderr, "[hg insert]%s ms\n", text.c_str());
+  }
+};
 
 struct DevBuf {
   void* p = nullptr;
@@ -113,8 +135,8 @@ struct GridMutable {
   std::vector<uint64_t> apron_keys;
   int64_t cap_all = 0;       // bricks that fit d_bricks / d_decoded
   size_t cap_index = 0;      // bytes of d_index
-  DevBuf coords, points, mask, counts, offsets, keys[2], vals[2], ut, uw, flags, starts, brick_heads,
-      brick_keys, temp, state, num;
+  DevBuf coords, points, mask, counts, offsets, keys[2], vals[2], flags, starts, brick_heads, brick_keys, temp,
+      state, num;
   uint16_t* d_tables = nullptr;  // hit table, miss table (32768 entries each)
   float table_hit = -1.f, table_miss = -1.f;
   void* h_pinned = nullptr;  // small pinned staging area
@@ -125,7 +147,7 @@ void DestroyGridMutable(hg_grid* grid) {
   if (m == nullptr) return;
   if (m->d_core) cudaFree(m->d_core);
   for (DevBuf* b : {&m->coords, &m->points, &m->mask, &m->counts, &m->offsets, &m->keys[0], &m->keys[1],
-                    &m->vals[0], &m->vals[1], &m->ut, &m->uw, &m->flags, &m->starts, &m->brick_heads,
+                    &m->vals[0], &m->vals[1], &m->flags, &m->starts, &m->brick_heads,
                     &m->brick_keys, &m->temp, &m->state, &m->num}) {
     b->Free();
   }
@@ -180,6 +202,7 @@ __global__ void __launch_bounds__(256) BuildApronKernel(const GridDev g, const i
 }
 
 struct RayParams {
+  int stride;  // floats between consecutive returns
   float ox, oy, oz;
   float resolution, inv_resolution;
   // TSDF
@@ -244,7 +267,7 @@ __global__ void __launch_bounds__(256) TsdfCountKernel(const RayParams p, const 
   int c = 0;
   if (mask == nullptr || mask[i]) {
     Ray r;
-    if (SetupTsdfRay(p, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], &r)) c = r.num_samples + 1;
+    if (SetupTsdfRay(p, pts[static_cast<size_t>(p.stride) * i], pts[static_cast<size_t>(p.stride) * i + 1], pts[static_cast<size_t>(p.stride) * i + 2], &r)) c = r.num_samples + 1;
   }
   counts[i] = c;
 }
@@ -268,24 +291,22 @@ __device__ __forceinline__ bool CellInRange(const int x, const int y, const int 
 __global__ void __launch_bounds__(256) TsdfEmitKernel(const RayParams p, const float* __restrict__ pts,
                                                       const int* __restrict__ offsets, const int n,
                                                       const int total, uint64_t* __restrict__ keys,
-                                                      unsigned* __restrict__ vals, float* __restrict__ ut,
-                                                      float* __restrict__ uw, InsertState* __restrict__ state) {
+                                                      float2* __restrict__ updates,
+                                                      InsertState* __restrict__ state) {
   const int u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= total) return;
   const int i = OwnerOf(offsets, n, u);
   const int position = u - offsets[i];
   Ray r;
-  SetupTsdfRay(p, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], &r);
+  SetupTsdfRay(p, pts[static_cast<size_t>(p.stride) * i], pts[static_cast<size_t>(p.stride) * i + 1], pts[static_cast<size_t>(p.stride) * i + 2], &r);
   const float fp = static_cast<float>(position), fn = static_cast<float>(r.num_samples);
   const int cx = r.bx + RoundToIntF(__fdiv_rn(__fmul_rn(static_cast<float>(r.dx), fp), fn));
   const int cy = r.by + RoundToIntF(__fdiv_rn(__fmul_rn(static_cast<float>(r.dy), fp), fn));
   const int cz = r.bz + RoundToIntF(__fdiv_rn(__fmul_rn(static_cast<float>(r.dz), fp), fn));
-  vals[u] = static_cast<unsigned>(u);
   if (!CellInRange(cx, cy, cz)) {
     atomicOr(&state->error, 1);
     keys[u] = 0;
-    ut[u] = 0.f;
-    uw[u] = 0.f;
+    updates[u] = make_float2(0.f, 0.f);
     return;
   }
   keys[u] = CellKey(cx, cy, cz);
@@ -303,8 +324,7 @@ __global__ void __launch_bounds__(256) TsdfEmitKernel(const RayParams p, const f
     const double t = static_cast<double>(__fsub_rn(-normalized, p.epsilon));
     weight = static_cast<float>(exp(__dmul_rn(static_cast<double>(-p.sigma), __dmul_rn(t, t))));
   }
-  ut[u] = tsd;
-  uw[u] = weight;
+  updates[u] = make_float2(tsd, weight);
 }
 
 template <int SHIFT>
@@ -353,10 +373,9 @@ struct TsdfApplyParams {
 // that cell's updates in sequence order.
 __global__ void __launch_bounds__(128) TsdfApplyKernel(const BrickTable table, const TsdfApplyParams p,
                                                        const uint64_t* __restrict__ keys,
-                                                       const unsigned* __restrict__ vals,
+                                                       const float2* __restrict__ updates,
                                                        const int* __restrict__ starts, const int num_cells,
-                                                       const int total, const float* __restrict__ ut,
-                                                       const float* __restrict__ uw, ushort2* __restrict__ core,
+                                                       const int total, ushort2* __restrict__ core,
                                                        InsertState* __restrict__ state) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= num_cells) return;
@@ -373,27 +392,43 @@ __global__ void __launch_bounds__(128) TsdfApplyKernel(const BrickTable table, c
   ushort2 v = *voxel;
   const bool was_default = v.x == 0 && v.y == 0;
   bool wrote = false;
-  for (int k = s; k < e; ++k) {
-    const unsigned u = vals[k];
-    const float update_weight = uw[u];
-    if (update_weight == 0.f) continue;
-    const float update_sdf = ut[u];
-    const float old_weight = Decode(p.weight, v.y);
-    const float old_sdf = Decode(p.tsd, v.x);
-    float updated_weight = __fadd_rn(old_weight, update_weight);
-    const float updated_sdf = __fdiv_rn(
-        __fadd_rn(__fmul_rn(old_sdf, old_weight), __fmul_rn(update_sdf, update_weight)), updated_weight);
-    updated_weight = updated_weight < p.maximum_weight ? updated_weight : p.maximum_weight;  // std::min
-    float c = updated_sdf;
-    if (c > p.max_tsd) c = p.max_tsd;
-    if (c < p.min_tsd) c = p.min_tsd;
-    float w = updated_weight;
-    if (w > p.max_weight) w = p.max_weight;
-    if (w < 0.f) w = 0.f;
-    v.x = static_cast<unsigned short>(
-        (RoundToIntF(__fmul_rn(__fsub_rn(c, p.min_tsd), p.tsd_resolution)) + 1 + 0x8000) & 0xFFFF);
-    v.y = static_cast<unsigned short>(RoundToIntF(__fmul_rn(__fsub_rn(w, 0.f), p.weight_resolution)) + 1);
-    wrote = true;
+  // The chain is sequential by definition; its updates are fetched a chunk ahead so that only
+  // the arithmetic is on the critical path. Padding entries have weight 0 and are skipped like
+  // the reference skips zero-weight updates.
+  constexpr int kChunk = 8;
+  float2 ahead[kChunk];
+#pragma unroll
+  for (int i = 0; i < kChunk; ++i) ahead[i] = s + i < e ? __ldg(updates + s + i) : make_float2(0.f, 0.f);
+  for (int k = s; k < e; k += kChunk) {
+    float2 current[kChunk];
+#pragma unroll
+    for (int i = 0; i < kChunk; ++i) current[i] = ahead[i];
+#pragma unroll
+    for (int i = 0; i < kChunk; ++i) {
+      ahead[i] = k + kChunk + i < e ? __ldg(updates + k + kChunk + i) : make_float2(0.f, 0.f);
+    }
+#pragma unroll
+    for (int i = 0; i < kChunk; ++i) {
+      const float update_weight = current[i].y;
+      if (update_weight == 0.f) continue;
+      const float update_sdf = current[i].x;
+      const float old_weight = Decode(p.weight, v.y);
+      const float old_sdf = Decode(p.tsd, v.x);
+      float updated_weight = __fadd_rn(old_weight, update_weight);
+      const float updated_sdf = __fdiv_rn(
+          __fadd_rn(__fmul_rn(old_sdf, old_weight), __fmul_rn(update_sdf, update_weight)), updated_weight);
+      updated_weight = updated_weight < p.maximum_weight ? updated_weight : p.maximum_weight;  // std::min
+      float c = updated_sdf;
+      if (c > p.max_tsd) c = p.max_tsd;
+      if (c < p.min_tsd) c = p.min_tsd;
+      float w = updated_weight;
+      if (w > p.max_weight) w = p.max_weight;
+      if (w < 0.f) w = 0.f;
+      v.x = static_cast<unsigned short>(
+          (RoundToIntF(__fmul_rn(__fsub_rn(c, p.min_tsd), p.tsd_resolution)) + 1 + 0x8000) & 0xFFFF);
+      v.y = static_cast<unsigned short>(RoundToIntF(__fmul_rn(__fsub_rn(w, 0.f), p.weight_resolution)) + 1);
+      wrote = true;
+    }
   }
   if (wrote) {
     *voxel = v;
@@ -423,7 +458,7 @@ __global__ void __launch_bounds__(256) OccupancyCountKernel(const RayParams p, c
   if (i >= n) return;
   Ray r;
   int hx, hy, hz;
-  SetupOccupancyRay(p, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], &r, &hx, &hy, &hz);
+  SetupOccupancyRay(p, pts[static_cast<size_t>(p.stride) * i], pts[static_cast<size_t>(p.stride) * i + 1], pts[static_cast<size_t>(p.stride) * i + 2], &r, &hx, &hy, &hz);
   counts[i] = 1 + min(r.num_samples, max(p.num_free_space_voxels, 0));
 }
 
@@ -440,7 +475,7 @@ __global__ void __launch_bounds__(256) OccupancyEmitKernel(const RayParams p, co
   const int k = u - offsets[i];
   Ray r;
   int cx, cy, cz;
-  SetupOccupancyRay(p, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], &r, &cx, &cy, &cz);
+  SetupOccupancyRay(p, pts[static_cast<size_t>(p.stride) * i], pts[static_cast<size_t>(p.stride) * i + 1], pts[static_cast<size_t>(p.stride) * i + 2], &r, &cx, &cy, &cz);
   unsigned miss = 0;
   if (k > 0) {
     const int position = max(0, r.num_samples - p.num_free_space_voxels) + (k - 1);
@@ -643,11 +678,11 @@ int RebuildReadCopies(hg_grid* g) {
   return HG_OK;
 }
 
-// Uploads the returns as packed xyz.
+// Uploads the returns as they are (one contiguous copy); the kernels read them with the stride.
 int UploadReturns(GridMutable* m, const float* returns, const int stride, const int64_t n) {
-  if (m->points.Ensure(static_cast<size_t>(n) * 3 * sizeof(float)) != HG_OK) return HG_ERR_CUDA;
-  HG_CUDA(cudaMemcpy2D(m->points.p, 3 * sizeof(float), returns, static_cast<size_t>(stride) * sizeof(float),
-                       3 * sizeof(float), static_cast<size_t>(n), cudaMemcpyHostToDevice));
+  const size_t bytes = (static_cast<size_t>(n - 1) * stride + 3) * sizeof(float);
+  if (m->points.Ensure(bytes) != HG_OK) return HG_ERR_CUDA;
+  HG_CUDA(cudaMemcpy(m->points.p, returns, bytes, cudaMemcpyHostToDevice));
   return HG_OK;
 }
 
@@ -743,6 +778,7 @@ int hg_grid_insert_tsdf(hg_grid* grid, const hg_tsdf_inserter_options* options, 
 
   RayParams p;
   memset(&p, 0, sizeof(p));
+  p.stride = stride_floats;
   p.ox = origin[0];
   p.oy = origin[1];
   p.oz = origin[2];
@@ -757,8 +793,10 @@ int hg_grid_insert_tsdf(hg_grid* grid, const hg_tsdf_inserter_options* options, 
   p.min_range = options->min_range;
   p.max_range = options->max_range;
 
+  PhaseTrace trace;
   rc = UploadReturns(m, returns, stride_floats, n);
   if (rc != HG_OK) return rc;
+  trace.Mark("upload");
   // The insertion-ratio counter (:701-708) depends only on the position in the cloud.
   const unsigned char* d_mask = nullptr;
   if (options->insertion_ratio < 1.0) {
@@ -787,34 +825,38 @@ int hg_grid_insert_tsdf(hg_grid* grid, const hg_tsdf_inserter_options* options, 
   if (rc != HG_OK) return rc;
   if (total == 0) return HG_OK;
   HG_REQUIRE(total > 0, "hg_grid_insert_tsdf: more than 2^31 cell updates in one call");
+  trace.Mark("count+scan");
 
   for (int k = 0; k < 2; ++k) {
     if (m->keys[k].Ensure(static_cast<size_t>(total) * sizeof(uint64_t)) != HG_OK) return HG_ERR_CUDA;
-    if (m->vals[k].Ensure(static_cast<size_t>(total) * sizeof(unsigned)) != HG_OK) return HG_ERR_CUDA;
+    if (m->vals[k].Ensure(static_cast<size_t>(total) * sizeof(uint64_t)) != HG_OK) return HG_ERR_CUDA;
   }
-  if (m->ut.Ensure(static_cast<size_t>(total) * sizeof(float)) != HG_OK) return HG_ERR_CUDA;
-  if (m->uw.Ensure(static_cast<size_t>(total) * sizeof(float)) != HG_OK) return HG_ERR_CUDA;
   TsdfEmitKernel<<<Blocks(total, 256), 256>>>(p, m->points.as<float>(), m->offsets.as<int>(), n, total,
-                                               m->keys[0].as<uint64_t>(), m->vals[0].as<unsigned>(),
-                                               m->ut.as<float>(), m->uw.as<float>(), m->state.as<InsertState>());
+                                               m->keys[0].as<uint64_t>(), m->vals[0].as<float2>(),
+                                               m->state.as<InsertState>());
   CountLaunch();
   HG_CUDA(cudaGetLastError());
   int err = 0;
   HG_CUDA(cudaMemcpy(&err, m->state.p, sizeof(int), cudaMemcpyDeviceToHost));
   HG_REQUIRE(err == 0, "hg_grid_insert_tsdf: a ray leaves the largest grid (cells beyond +-8192); the reference "
                        "CHECK-fails in DynamicGrid::Grow");
+  trace.Mark("emit");
 
   cub::DoubleBuffer<uint64_t> keys(m->keys[0].as<uint64_t>(), m->keys[1].as<uint64_t>());
-  cub::DoubleBuffer<unsigned> vals(m->vals[0].as<unsigned>(), m->vals[1].as<unsigned>());
+  // The (tsd, weight) pair travels through the sort as one 64-bit value; the sort is stable, so
+  // the updates of a cell stay in sequence order.
+  cub::DoubleBuffer<uint64_t> vals(m->vals[0].as<uint64_t>(), m->vals[1].as<uint64_t>());
   size_t bytes = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, bytes, keys, vals, total, 0, kCellKeyBits);
   if (m->temp.Ensure(bytes) != HG_OK) return HG_ERR_CUDA;
   HG_CUDA(cub::DeviceRadixSort::SortPairs(m->temp.p, bytes, keys, vals, total, 0, kCellKeyBits));
   CountLaunch(4);
+  trace.Mark("sort");
 
   int num_cells = 0;
   rc = GroupAndCreateBricks<0>(grid, keys.Current(), total, &num_cells);
   if (rc != HG_OK) return rc;
+  trace.Mark("group+bricks");
 
   TsdfApplyParams ap;
   ap.tsd = grid->dev.a;
@@ -825,15 +867,17 @@ int hg_grid_insert_tsdf(hg_grid* grid, const hg_tsdf_inserter_options* options, 
   ap.max_weight = grid->max_weight;
   ap.weight_resolution = 32766.f / (grid->max_weight - 0.f);              // :28
   ap.maximum_weight = static_cast<float>(options->maximum_weight);
-  TsdfApplyKernel<<<Blocks(num_cells, 128), 128>>>(grid->dev.table, ap, keys.Current(), vals.Current(),
-                                                    m->starts.as<int>(), num_cells, total, m->ut.as<float>(),
-                                                    m->uw.as<float>(), static_cast<ushort2*>(m->d_core),
-                                                    m->state.as<InsertState>());
+  TsdfApplyKernel<<<Blocks(num_cells, 128), 128>>>(grid->dev.table, ap, keys.Current(),
+                                                    reinterpret_cast<const float2*>(vals.Current()),
+                                                    m->starts.as<int>(), num_cells, total,
+                                                    static_cast<ushort2*>(m->d_core), m->state.as<InsertState>());
   CountLaunch();
   HG_CUDA(cudaGetLastError());
+  trace.Mark("apply");
   rc = FinishInsertion(grid, "hg_grid_insert_tsdf");
   if (rc != HG_OK) return rc;
   HG_CUDA(cudaDeviceSynchronize());
+  trace.Mark("rebuild");
   if (num_updates) *num_updates = total;
   return HG_OK;
 }
@@ -888,6 +932,7 @@ int hg_grid_insert_occupancy(hg_grid* grid, const hg_occupancy_inserter_options*
 
   RayParams p;
   memset(&p, 0, sizeof(p));
+  p.stride = stride_floats;
   p.ox = origin[0];
   p.oy = origin[1];
   p.oz = origin[2];

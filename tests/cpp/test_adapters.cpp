@@ -3,6 +3,7 @@
 //   ceres_scan_matcher_3d_test.cc:36-117      (7-point cloud, occupancy grid, pose recovered)
 //   fast_correlative_scan_matcher_3d_test.cc  (Match returns a result / a null result)
 //   constraint_builder_3d_test.cc:62-72       (CallsBack)
+//   range_data_inserter_3d_test.cc:43-98      (hit / miss probabilities after one insertion)
 // Prints "ADAPTERS OK" and exits 0 on success. With argument "compile-only" it exits before
 // touching the GPU (used by the CPU-side test to check that the header compiles and links).
 #include <cmath>
@@ -140,6 +141,39 @@ int main(int argc, char** argv) {
     std::promise<size_t> again;
     builder.WhenDone([&again](const hg::ConstraintBuilder3D::Result& r) { again.set_value(r.size()); });
     if (again.get_future().get() != 0) return Fail("empty WhenDone");
+  }
+  // --- range-data inserters (range_data_inserter_3d_test.cc:43-98) ---------------------------
+  {
+    auto occupancy = hg::DeviceGrid::FromHybridGrid(1.f, 0, 0, nullptr, nullptr);
+    hg_occupancy_inserter_options oo = {0.7, 0.4, 1000, 0};
+    hg::OccupancyGridRangeDataInserter3D inserter(oo);
+    const float returns[4][3] = {{-3.f, -1.f, 4.f}, {-2.f, 0.f, 4.f}, {-1.f, 1.f, 4.f}, {0.f, 2.f, 4.f}};
+    hg::RangeDataView range_data;
+    range_data.origin = {{0.f, 0.f, -4.f}};
+    range_data.returns.data = &returns[0][0];
+    range_data.returns.size = 4;
+    inserter.Insert(range_data, occupancy.get());
+    const int32_t cells[3][3] = {{0, 0, -4}, {-2, 0, 4}, {-2, 0, 3}};
+    float probability[3];
+    if (hg_grid_lookup(occupancy->get(), 0, 3, &cells[0][0], probability) != HG_OK) return Fail("lookup");
+    if (std::fabs(probability[0] - 0.4f) > 1e-4f || std::fabs(probability[1] - 0.7f) > 1e-4f ||
+        std::fabs(probability[2] - 0.4f) > 1e-4f)
+      return Fail("OccupancyGridRangeDataInserter3D probabilities");
+
+    auto tsdf = hg::DeviceGrid::FromHybridGridTSDF(0.1f, 2.5f, 1000.f, 0, 0, nullptr, nullptr, nullptr);
+    hg_tsdf_inserter_options to = {2.5, 1000., 1.0, 4., 0.4, 15.0, 1.0, 0, 0};
+    hg::TSDFRangeDataInserter3D tsdf_inserter(to);
+    const float hit[1][3] = {{2.f, 0.f, 0.f}};
+    range_data.origin = {{0.f, 0.f, 0.f}};
+    range_data.returns.data = &hit[0][0];
+    range_data.returns.size = 1;
+    tsdf_inserter.Insert(range_data, tsdf.get());
+    const int32_t surface[2][3] = {{20, 0, 0}, {19, 0, 0}};
+    float tsd[2], weight[2];
+    if (hg_grid_lookup(tsdf->get(), 1, 2, &surface[0][0], tsd) != HG_OK) return Fail("tsd lookup");
+    if (hg_grid_lookup(tsdf->get(), 2, 2, &surface[0][0], weight) != HG_OK) return Fail("weight lookup");
+    if (std::fabs(tsd[0]) > 1e-3f || std::fabs(tsd[1] - 0.1f) > 1e-3f || std::fabs(weight[0] - 1.f) > 0.05f)
+      return Fail("TSDFRangeDataInserter3D voxels");
   }
   std::printf("ADAPTERS OK (%llu kernel launches)\n", static_cast<unsigned long long>(hg_kernel_launch_count()));
   return 0;
