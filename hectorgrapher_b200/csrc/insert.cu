@@ -5,7 +5,7 @@
 //   mapping/3d/hybrid_grid.h:76-82, 119-130            FinishUpdate / ApplyLookupTable (update marker)
 //   mapping/probability_values.cc:76-87                ComputeLookupTableToApplyOdds
 //   mapping/3d/tsdf_range_data_inserter_3d.cc:294-343  InsertHit, default ray cast
-//   mapping/3d/tsdf_range_data_inserter_3d.cc:700-737  Insert (no normal projection), UpdateCell
+//   mapping/3d/tsdf_range_data_inserter_3d.cc:395-401, 700-737  Insert (no normal projection), UpdateCell
 //   mapping/3d/hybrid_grid_tsdf.h:87-93                SetCell (TSD value carries bit 15)
 //   mapping/2d/tsd_value_converter.h:39-55             TSDToValue / WeightToValue
 //   mapping/3d/hybrid_grid_base.h:385-403              DynamicGrid::Grow
