@@ -531,6 +531,9 @@ struct hg_batch {
   int* d_ne_tile_begin = nullptr;  // num_blocks + 1
   // Per-call scratch, guarded by 'mu' (calls on one handle serialise on it).
   mutable std::mutex mu;
+  // Stream of the host-pointer entry points when the caller passes none: the legacy default
+  // stream, or the owning host thread's stream for the cost functions of hg_scan_match.
+  cudaStream_t stream = nullptr;
   mutable BlockDev* d_blocks = nullptr;
   mutable BlockDev* h_blocks = nullptr;  // pinned
   mutable double* d_partials = nullptr;
@@ -697,7 +700,7 @@ int hg_batch_create(int kind, int num_blocks, const float* points, int stride_fl
   B->num_grids = num_grids;
 
   const size_t point_bytes = static_cast<size_t>(std::max<int64_t>(B->num_points, 1)) * stride_floats * sizeof(float);
-  HG_CUDA(cudaMalloc(&B->d_points, point_bytes));
+  HG_ALLOC(B->d_points, CachedDeviceAlloc(point_bytes));
   if (B->num_points > 0) {
     HG_CUDA(cudaMemcpy(B->d_points, points, static_cast<size_t>(B->num_points) * stride_floats * sizeof(float),
                        cudaMemcpyHostToDevice));
@@ -708,39 +711,39 @@ int hg_batch_create(int kind, int num_blocks, const float* points, int stride_fl
   if (const char* env = std::getenv("HG_TILE_OUT")) B->tile_out = std::max(256, (std::atoi(env) / 256) * 256);
   BuildTiles(B->offsets, B->tile_out, &tiles, nullptr);
   B->num_tiles_out = static_cast<int>(tiles.size());
-  HG_CUDA(cudaMalloc(&B->d_tiles_out, sizeof(TileDev) * std::max<size_t>(tiles.size(), 1)));
+  HG_ALLOC(B->d_tiles_out, CachedDeviceAlloc(sizeof(TileDev) * std::max<size_t>(tiles.size(), 1)));
   if (!tiles.empty())
     HG_CUDA(cudaMemcpy(B->d_tiles_out, tiles.data(), sizeof(TileDev) * tiles.size(), cudaMemcpyHostToDevice));
   BuildTiles(B->offsets, kTileNe, &tiles, &tile_begin);
   B->num_tiles_ne = static_cast<int>(tiles.size());
-  HG_CUDA(cudaMalloc(&B->d_tiles_ne, sizeof(TileDev) * std::max<size_t>(tiles.size(), 1)));
+  HG_ALLOC(B->d_tiles_ne, CachedDeviceAlloc(sizeof(TileDev) * std::max<size_t>(tiles.size(), 1)));
   if (!tiles.empty())
     HG_CUDA(cudaMemcpy(B->d_tiles_ne, tiles.data(), sizeof(TileDev) * tiles.size(), cudaMemcpyHostToDevice));
-  HG_CUDA(cudaMalloc(&B->d_ne_tile_begin, sizeof(int) * tile_begin.size()));
+  HG_ALLOC(B->d_ne_tile_begin, CachedDeviceAlloc(sizeof(int) * tile_begin.size()));
   HG_CUDA(cudaMemcpy(B->d_ne_tile_begin, tile_begin.data(), sizeof(int) * tile_begin.size(), cudaMemcpyHostToDevice));
 
-  HG_CUDA(cudaMalloc(&B->d_blocks, sizeof(BlockDev) * num_blocks));
-  HG_CUDA(cudaMallocHost(&B->h_blocks, sizeof(BlockDev) * num_blocks));
+  HG_ALLOC(B->d_blocks, CachedDeviceAlloc(sizeof(BlockDev) * num_blocks));
+  HG_ALLOC(B->h_blocks, CachedPinnedAlloc(sizeof(BlockDev) * num_blocks));
   const int P = NumNormalTerms(two ? 14 : 7);
-  HG_CUDA(cudaMalloc(&B->d_partials, sizeof(double) * P * std::max(B->num_tiles_ne, 1)));
-  HG_CUDA(cudaMalloc(&B->d_ne_out, sizeof(double) * P * num_blocks));
-  HG_CUDA(cudaMallocHost(&B->h_ne_out, sizeof(double) * P * num_blocks));
+  HG_ALLOC(B->d_partials, CachedDeviceAlloc(sizeof(double) * P * std::max(B->num_tiles_ne, 1)));
+  HG_ALLOC(B->d_ne_out, CachedDeviceAlloc(sizeof(double) * P * num_blocks));
+  HG_ALLOC(B->h_ne_out, CachedPinnedAlloc(sizeof(double) * P * num_blocks));
   *out = B.release();
   return HG_OK;
 }
 
 void hg_batch_destroy(hg_batch* B) {
   if (B == nullptr) return;
-  cudaFree(B->d_points);
-  cudaFree(B->d_tiles_out);
-  cudaFree(B->d_tiles_ne);
-  cudaFree(B->d_ne_tile_begin);
-  cudaFree(B->d_blocks);
-  if (B->h_blocks) cudaFreeHost(B->h_blocks);
-  cudaFree(B->d_partials);
-  cudaFree(B->d_ne_out);
-  if (B->h_ne_out) cudaFreeHost(B->h_ne_out);
-  cudaFree(B->d_out);
+  CachedFree(B->d_points);
+  CachedFree(B->d_tiles_out);
+  CachedFree(B->d_tiles_ne);
+  CachedFree(B->d_ne_tile_begin);
+  CachedFree(B->d_blocks);
+  CachedFree(B->h_blocks);
+  CachedFree(B->d_partials);
+  CachedFree(B->d_ne_out);
+  CachedFree(B->h_ne_out);
+  CachedFree(B->d_out);
   delete B;
 }
 
@@ -759,7 +762,7 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
                       const int32_t* pose_index1, int device_outputs, double* residuals, double* jt0,
                       double* jq0, double* jt1, double* jq1, void* cuda_stream) {
   HG_REQUIRE(B != nullptr && poses != nullptr && num_poses >= 1, "hg_batch_evaluate: bad arguments");
-  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  cudaStream_t stream = cuda_stream != nullptr ? static_cast<cudaStream_t>(cuda_stream) : B->stream;
   std::lock_guard<std::mutex> lock(B->mu);
   int rc = PrepareBlocks(B, poses, num_poses, pose_index0, pose_index1, stream);
   if (rc != HG_OK) return rc;
@@ -779,10 +782,10 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
   // Host outputs: stage in device memory, then one copy per requested array.
   const size_t need = static_cast<size_t>(N) * 15;
   if (B->d_out_doubles < need) {
-    if (B->d_out) cudaFree(B->d_out);
+    CachedFree(B->d_out);
     B->d_out = nullptr;
     B->d_out_doubles = 0;
-    HG_CUDA(cudaMalloc(&B->d_out, std::max<size_t>(need, 1) * sizeof(double)));
+    HG_ALLOC(B->d_out, CachedDeviceAlloc(std::max<size_t>(need, 1) * sizeof(double)));
     B->d_out_doubles = need;
   }
   // 4-wide arrays first so that they stay 32-byte aligned for any N.
@@ -809,7 +812,7 @@ int hg_batch_normal_equations(const hg_batch* B, const double* poses, int num_po
                               double* Jtr, double* cost_out) {
   HG_REQUIRE(B != nullptr && poses != nullptr && num_poses >= 1, "hg_batch_normal_equations: bad arguments");
   std::lock_guard<std::mutex> lock(B->mu);
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = B->stream;
   int rc = PrepareBlocks(B, poses, num_poses, pose_index0, pose_index1, stream);
   if (rc != HG_OK) return rc;
   CostArgs a = BaseArgs(B);
@@ -1019,6 +1022,7 @@ extern "C" int hg_scan_match(int num_clouds, const float* const* clouds, const i
     hg_cost* c = nullptr;
     const int kind = grids[i]->dev.kind == kGridProb ? HG_COST_OCCUPIED_SPACE : HG_COST_TSDF_SPACE;
     const int rc = hg_cost_create(kind, scaling, clouds[i], 3, cloud_sizes[i], &grids[i], 1, 0.0, &c);
+    if (rc == HG_OK) c->batch->stream = ThreadStream();  // concurrent matches do not share the legacy stream
     if (rc != HG_OK) return rc;
     owned.emplace_back(new GpuScanCost(c));
     problem.AddResidualBlock(owned.back().get(), {tb, qb});

@@ -1294,12 +1294,10 @@ int MatchWithSearchParameters(const hg_fcsm* m, const SearchParameters& sp, cons
   std::memset(result, 0, sizeof(*result));
   result->pose_rotation[0] = 1.0;
   HG_CUDA(cudaSetDevice(m->device));
-  cudaStream_t stream = nullptr;
-  HG_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-  struct StreamGuard {
-    cudaStream_t s;
-    ~StreamGuard() { cudaStreamDestroy(s); }
-  } guard{stream};
+  // The calling host thread's own non-blocking stream: searches driven by different host
+  // threads overlap on the device.
+  cudaStream_t stream = ThreadStream();
+  HG_REQUIRE(stream != nullptr, "hg_fcsm: cannot create a stream");
   ScanSet scans;
   PhaseTimer pt;
   int rc = GenerateDiscreteScans(m, sp, data, node_pose, submap_pose, shard_index, num_shards, stream, &scans);

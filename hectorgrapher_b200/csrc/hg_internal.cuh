@@ -36,6 +36,23 @@ inline void CountLaunch(uint64_t n = 1) { g_kernel_launches.fetch_add(n, std::me
     }                                  \
   } while (0)
 
+// ------------------------------------------------------------ allocation --
+// alloc.cu: blocks released by a host thread are cached by that thread and reused (no
+// cudaFree on the per-pair path); a block may be released by another thread than the
+// one that allocated it. ThreadStream() is a non-blocking stream owned by the calling
+// host thread (one per device), created on first use.
+void* CachedDeviceAlloc(size_t bytes);  // nullptr + SetError on failure
+void* CachedPinnedAlloc(size_t bytes);
+void CachedFree(void* p);
+cudaStream_t ThreadStream();
+
+#define HG_ALLOC(var, expr)                          \
+  do {                                               \
+    void* _p = (expr);                               \
+    if (_p == nullptr) return HG_ERR_CUDA;           \
+    (var) = static_cast<decltype(var)>(_p);          \
+  } while (0)
+
 // ----------------------------------------------------------- brick table --
 // A sparse voxel grid flattened for the device:
 //   * 'index' is a dense int32 array over the bounding box of occupied 8x8x8
