@@ -302,51 +302,130 @@ def correlative_bench(hg, torch, w, rank, world, dist):
     }
 
 
-def constraint_bench(hg, torch, w, rank, world, dist, pairs_per_rank=24):
-    """C5 sample: ConstraintBuilder3D::ComputeConstraint for (node, submap) pairs — local correlative
-    match + CeresScanMatcher3D refine — partitioned by job index over ranks."""
-    synth = w["synth"]
-    g_hi = hg.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT, *w["hi"])
-    g_lo = hg.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT, *w["lo"])
-    origin, yaw = w["map_poses"][3]
-    rng = np.random.RandomState(5)
-    cloud = synth.scan(origin, yaw, 64, 512, w["sph"], rng)
+C5_FCSM_OPTIONS = dict(branch_and_bound_depth=7, full_resolution_depth=3, use_rotational_scan_matcher=False,
+                       min_low_resolution_score=0.3, linear_xy_search_window=5.0, linear_z_search_window=1.0,
+                       angular_search_window=float(np.deg2rad(15.0)))
+C5_OPTIONS = dict(min_score=0.55, global_localization_min_score=0.6, occupied_space_weights=(5.0, 30.0),
+                  translation_weight=10.0, rotation_weight=1.0, max_num_iterations=10)
+C5_INSERTER = dict(relative_truncation_distance=REL_TRUNC, maximum_weight=MAX_WEIGHT, num_free_space_voxels=0,
+                   epsilon=1.0, sigma=4.0, min_range=0.4, max_range=60.0, insertion_ratio=1.0)
+
+
+def c5_submap_inputs(synth, sph, s, num_submaps):
+    """Submap s of C5: three scans around a pose of the corkscrew (inserted into 0.10 m / 0.45 m TSDF
+    grids) and one node scan taken at the pose itself, down-sampled like the adaptive voxel filter does."""
+    origin, yaw = synth.corkscrew_pose(s, max(num_submaps, 2))
+    scans = []
+    for k, d in enumerate(([0.0, 0.0, 0.0], [0.6, -0.4, 0.1], [-0.5, 0.5, -0.1])):
+        o = origin + np.array(d)
+        c = synth.scan(o, yaw + 0.2 * k, 64, 1024, sph, np.random.RandomState(1000 * s + k))
+        q = synth.quat_from_yaw(yaw + 0.2 * k)
+        scans.append((o.astype(np.float32), (synth.quat_rotate(q, c.astype(np.float64)) + o).astype(np.float32)))
+    cloud = synth.scan(origin, yaw, 64, 512, sph, np.random.RandomState(1000 * s + 7))
     high = synth.voxel_downsample(cloud, 0.2, 2048, seed=6)
     low = synth.voxel_downsample(cloud, 0.9, 256, seed=7)
-    hist = np.zeros(8, np.float32)
-    opts = dict(branch_and_bound_depth=7, full_resolution_depth=3, use_rotational_scan_matcher=False,
-                min_low_resolution_score=0.3, linear_xy_search_window=5.0, linear_z_search_window=1.0,
-                angular_search_window=float(np.deg2rad(15.0)))
-    m = hg.Fcsm(g_hi, g_lo, hist, **opts)
+    return origin, yaw, scans, high, low
+
+
+def c5_jobs(synth, s, local_index, origin, yaw, high, low, hist, nodes, seed=5):
+    rng = np.random.RandomState(seed + 31 * s)
     submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
-    n_jobs = pairs_per_rank * world
     jobs = []
-    for j in range(n_jobs):
+    for _ in range(nodes):
         node = np.concatenate([origin + np.array([rng.uniform(-2, 2), rng.uniform(-2, 2), rng.uniform(-0.4, 0.4)]),
                                synth.quat_from_yaw(yaw + rng.uniform(-0.15, 0.15))])
-        jobs.append(dict(submap_index=0, full=False, node_pose=node, submap_pose=submap, high=high, low=low, hist=hist))
-    o = dict(min_score=0.55, global_localization_min_score=0.6, occupied_space_weights=(5.0, 30.0),
-             translation_weight=10.0, rotation_weight=1.0, max_num_iterations=10)
-    hg.constraints_run_batch([m], [g_hi], [g_lo], jobs[:2], o)  # warm-up
+        jobs.append(dict(submap_index=local_index, full=False, node_pose=node, submap_pose=submap, high=high,
+                         low=low, hist=hist))
+    return jobs
+
+
+def cpu_baseline_pairs(synth, sph, num_submaps, pairs=16, threads=None):
+    """The oracle's FastCorrelativeScanMatcher3D::Match + CeresScanMatcher3D-style refine for 'pairs' jobs of
+    submap 0, one pair per host thread (how ConstraintBuilder3D's pool runs them)."""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import pyoracle
+    threads = threads or os.cpu_count() or 1
+    origin, yaw, scans, high, low = c5_submap_inputs(synth, sph, 0, num_submaps)
+    g_hi = pyoracle.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT)
+    g_lo = pyoracle.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT)
+    for o, pts in scans:
+        g_hi.insert_tsdf(o, pts, **C5_INSERTER)
+        g_lo.insert_tsdf(o, pts, **C5_INSERTER)
+    hist = np.zeros(8, np.float32)
+    m = pyoracle.Fcsm(g_hi, g_lo, hist, **C5_FCSM_OPTIONS)
+    jobs = c5_jobs(synth, 0, 0, origin, yaw, high, low, hist, pairs)
+
+    def one(j):
+        r = m.match(j["node_pose"], j["submap_pose"], high, low, hist, min_score=C5_OPTIONS["min_score"])
+        if r["found"]:
+            pose = np.array([r["tx"], r["ty"], r["tz"], r["qw"], r["qx"], r["qy"], r["qz"]])
+            pyoracle.scan_match([high, low], [g_hi, g_lo], C5_OPTIONS["occupied_space_weights"],
+                                C5_OPTIONS["translation_weight"], C5_OPTIONS["rotation_weight"], pose,
+                                max_num_iterations=C5_OPTIONS["max_num_iterations"], use_nonmonotonic_steps=False)
+        return r["found"], r["num_scored"]
+
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        out = list(ex.map(one, jobs))
+    dt = time.perf_counter() - t0
+    return pairs / dt, threads, "%d pairs of submap 0 (match + refine), %d host threads, %d found" % (
+        pairs, threads, sum(int(f) for f, _ in out))
+
+
+def constraint_bench(hg, torch, w, rank, world, dist, num_submaps=8, nodes_per_submap=24, cpu=True):
+    """C5: ConstraintBuilder3D::ComputeConstraint for (node, submap) pairs — local correlative match +
+    CeresScanMatcher3D refine. Submaps are partitioned over ranks (the owner holds that submap's grids and
+    pyramid); each submap is built on its owner by device-side TSDF insertion."""
+    synth, sph = w["synth"], w["sph"]
+    hist = np.zeros(8, np.float32)
+    empty = np.zeros((0, 3), np.int32)
+    mine = [s for s in range(num_submaps) if s % world == rank]
+    matchers, g_his, g_los, jobs = [], [], [], []
+    for local, s in enumerate(mine):
+        origin, yaw, scans, high, low = c5_submap_inputs(synth, sph, s, num_submaps)
+        g_hi = hg.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT, empty, [], [])
+        g_lo = hg.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT, empty, [], [])
+        for o, pts in scans:
+            g_hi.insert_tsdf(o, pts, **C5_INSERTER)
+            g_lo.insert_tsdf(o, pts, **C5_INSERTER)
+        g_his.append(g_hi)
+        g_los.append(g_lo)
+        matchers.append(hg.Fcsm(g_hi, g_lo, hist, **C5_FCSM_OPTIONS))
+        jobs += c5_jobs(synth, s, local, origin, yaw, high, low, hist, nodes_per_submap)
+    if mine:
+        hg.ConstraintBatch(matchers[:1], g_his[:1], g_los[:1], jobs[:16], C5_OPTIONS).run()  # warm-up
+    batch = hg.ConstraintBatch(matchers, g_his, g_los, jobs, C5_OPTIONS) if mine else None
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
     t0 = time.perf_counter()
-    res = hg.constraints_run_batch([m], [g_hi], [g_lo], jobs, o, rank, world)
+    if batch is not None:
+        batch.run()
     torch.cuda.synchronize()
     dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-    mine = [res[j] for j in range(rank, n_jobs, world)]
-    stats = torch.tensor([sum(r["found"] for r in mine), sum(r["num_scored"] for r in mine)], dtype=torch.float64,
-                         device="cuda")
+    found, scored = batch.totals() if batch is not None else (0, 0)
+    stats = torch.tensor([found, scored, len(jobs)], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         dist.all_reduce(stats, op=dist.ReduceOp.SUM)
     if rank != 0:
         return None
-    return {"workload": "C5 sample: %d (node, submap) pairs, local Match (5 m / 1 m / 15 deg, N=2048) + refine on "
-                        "{high, low} clouds; jobs partitioned by index over %d rank(s)" % (n_jobs, world),
-            "pairs_per_s": n_jobs / float(dt.item()), "ms_per_pair_per_gpu": 1e3 * float(dt.item()) / pairs_per_rank,
-            "constraints_found": int(stats[0].item()), "candidates_scored": float(stats[1].item())}
+    n_jobs = int(stats[2].item())
+    out = {"workload": "C5: %d submaps x %d nodes = %d (node, submap) pairs, local Match (5 m / 1 m / 15 deg, "
+                       "N=2048) + refine on {high, low} clouds; submaps partitioned over %d rank(s), built by "
+                       "device-side TSDF insertion" % (num_submaps, nodes_per_submap, n_jobs, world),
+           "pairs_per_s": n_jobs / float(dt.item()), "seconds": float(dt.item()),
+           "ms_per_pair_per_gpu": 1e3 * float(dt.item()) * world / max(n_jobs, 1),
+           "constraints_found": int(stats[0].item()), "candidates_scored": float(stats[1].item()),
+           "candidates_per_s": float(stats[1].item()) / float(dt.item()),
+           "pairs_in_flight_per_gpu": int(os.environ.get("HG_CONSTRAINT_THREADS", "8"))}
+    if cpu:
+        try:
+            rate, threads, desc = cpu_baseline_pairs(synth, sph, num_submaps)
+            out["cpu_baseline"] = {"value": rate, "unit": "pairs/s", "cores": threads, "kind": "port", "sample": desc}
+        except Exception as ex:
+            out["cpu_baseline"] = {"error": repr(ex)}
+    return out
 
 
 def insertion_bench(hg, torch, w, scans=6):
@@ -507,7 +586,10 @@ def run_ours(args, rank, world, local_rank):
         corr = {"error": repr(ex)}
     cons = None
     try:
-        cons = constraint_bench(hg, torch, w, rank, world, dist)
+        if args.c5_full:
+            cons = constraint_bench(hg, torch, w, rank, world, dist, num_submaps=100, nodes_per_submap=100)
+        else:
+            cons = constraint_bench(hg, torch, w, rank, world, dist)
     except Exception as ex:
         log("[rank %d] constraint bench failed: %r" % (rank, ex))
         cons = {"error": repr(ex)}
@@ -572,6 +654,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--c5-full", action="store_true",
+                    help="run the constraint batch at BASELINE.json's full C5 size (100 submaps x 100 nodes)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -555,43 +555,70 @@ def low_resolution_scores(low_grid, pts, poses7):
     return out
 
 
+class ConstraintBatch:
+    """Marshals a list of jobs once (dicts: submap_index, full, node_pose, submap_pose, high, low, hist,
+    gravity) so that run() is just the hg_constraints_run_batch call."""
+
+    def __init__(self, matchers, grids, low_grids, jobs, options):
+        n = len(jobs)
+        self.n = n
+        self.arr = (ConstraintJob * n)()
+        self.keep = [matchers, grids, low_grids]
+        cache = {}
+        for i, j in enumerate(jobs):
+            self.arr[i].submap_index = j["submap_index"]
+            self.arr[i].match_full_submap = int(j.get("full", False))
+            for k in range(7):
+                self.arr[i].global_node_pose[k] = float(j["node_pose"][k])
+                self.arr[i].global_submap_pose[k] = float(j["submap_pose"][k])
+            key = (id(j["high"]), id(j["low"]), id(j["hist"]), tuple(j.get("gravity", (1, 0, 0, 0))))
+            if key not in cache:  # jobs that share their clouds share one marshalled copy
+                cache[key] = make_node_data(j["high"], j["low"], j["hist"], j.get("gravity", (1, 0, 0, 0)))
+                self.keep.append((j["high"], j["low"], j["hist"]))
+            d, ka = cache[key]
+            self.arr[i].data = d
+            self.keep.append(ka)
+        opt = ConstraintOptions()
+        opt.min_score = options.get("min_score", 0.55)
+        opt.global_localization_min_score = options.get("global_localization_min_score", 0.6)
+        w = options.get("occupied_space_weights", (5.0, 30.0))
+        opt.occupied_space_weights[0], opt.occupied_space_weights[1] = w
+        opt.translation_weight = options.get("translation_weight", 10.0)
+        opt.rotation_weight = options.get("rotation_weight", 1.0)
+        opt.only_optimize_yaw = int(options.get("only_optimize_yaw", False))
+        opt.max_num_iterations = options.get("max_num_iterations", 10)
+        opt.use_nonmonotonic_steps = int(options.get("use_nonmonotonic_steps", False))
+        self.opt = opt
+        self.res = (ConstraintResult * n)()
+        self.marr = (vp * len(matchers))(*[m.h for m in matchers])
+        self.garr = _grid_array(grids)
+        self.larr = _grid_array(low_grids)
+        self.num_submaps = len(matchers)
+
+    def run(self, shard_index=0, num_shards=1):
+        _check(lib().hg_constraints_run_batch(self.marr, self.garr, self.larr, self.num_submaps, self.arr, self.n,
+                                              C.byref(self.opt), shard_index, num_shards, self.res))
+        return self
+
+    def results(self):
+        out = []
+        for i in range(self.n):
+            r = self.res[i]
+            out.append(dict(found=int(r.found), score=float(r.score), pose=np.array(list(r.pose)),
+                            rotational_score=float(r.rotational_score),
+                            low_resolution_score=float(r.low_resolution_score),
+                            num_scored=int(r.num_candidates_scored)))
+        return out
+
+    def totals(self):
+        """(constraints found, candidates scored) over all jobs."""
+        return (sum(int(self.res[i].found) for i in range(self.n)),
+                sum(int(self.res[i].num_candidates_scored) for i in range(self.n)))
+
+
 def constraints_run_batch(matchers, grids, low_grids, jobs, options, shard_index=0, num_shards=1):
     """jobs: list of dicts(submap_index, full, node_pose, submap_pose, high, low, hist, gravity)."""
-    n = len(jobs)
-    arr = (ConstraintJob * n)()
-    keep = []
-    for i, j in enumerate(jobs):
-        arr[i].submap_index = j["submap_index"]
-        arr[i].match_full_submap = int(j.get("full", False))
-        for k in range(7):
-            arr[i].global_node_pose[k] = float(j["node_pose"][k])
-            arr[i].global_submap_pose[k] = float(j["submap_pose"][k])
-        d, ka = make_node_data(j["high"], j["low"], j["hist"], j.get("gravity", (1, 0, 0, 0)))
-        arr[i].data = d
-        keep.append(ka)
-    opt = ConstraintOptions()
-    opt.min_score = options.get("min_score", 0.55)
-    opt.global_localization_min_score = options.get("global_localization_min_score", 0.6)
-    w = options.get("occupied_space_weights", (5.0, 30.0))
-    opt.occupied_space_weights[0], opt.occupied_space_weights[1] = w
-    opt.translation_weight = options.get("translation_weight", 10.0)
-    opt.rotation_weight = options.get("rotation_weight", 1.0)
-    opt.only_optimize_yaw = int(options.get("only_optimize_yaw", False))
-    opt.max_num_iterations = options.get("max_num_iterations", 10)
-    opt.use_nonmonotonic_steps = int(options.get("use_nonmonotonic_steps", False))
-    res = (ConstraintResult * n)()
-    marr = (vp * len(matchers))(*[m.h for m in matchers])
-    _check(lib().hg_constraints_run_batch(marr, _grid_array(grids), _grid_array(low_grids), len(matchers), arr,
-                                          n, C.byref(opt), shard_index, num_shards, res))
-    out = []
-    for i in range(n):
-        r = res[i]
-        out.append(dict(found=int(r.found), score=float(r.score), pose=np.array(list(r.pose)),
-                        rotational_score=float(r.rotational_score),
-                        low_resolution_score=float(r.low_resolution_score),
-                        num_scored=int(r.num_candidates_scored)))
-    del keep
-    return out
+    return ConstraintBatch(matchers, grids, low_grids, jobs, options).run(shard_index, num_shards).results()
 
 
 def voxel_filter(size, pts, stride=3):
