@@ -731,3 +731,61 @@ def test_adaptive_voxel_filter_bit_exact(oracle, hg, world):
         a = hg.adaptive_voxel_filter(max_length, min_points, max_range, pts)
         b = oracle.adaptive_voxel_filter(max_length, min_points, max_range, pts)
         assert a.tolist() == b.tolist(), (len(pts), max_length, min_points, max_range, len(a), len(b))
+
+
+# ------------------------------------------------ BASELINE.json configs[1] at full size --
+
+def test_config_c2_full_size(oracle, hg):
+    """C2 exactly as bench.py times it: 64 two-pose multi-resolution TSDF blocks x 100 000 points in one
+    batched Evaluate. At this size the oracle takes minutes, so the check is (a) the oracle on a random
+    sample of points of several blocks — rows are per-point, so a sub-cloud with the block's scaling factor
+    must give the same rows —, (b) properties that do not depend on the size: the fused normal equations
+    equal J'J / J'r of the materialised rows, and reversing the points of the batch reverses the rows
+    bit for bit."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    w = bench.build_workload()
+    N = len(w["points"])
+    assert N == 64 * 100000
+    g_hi = hg.Grid.tsdf(bench.HI_RES, bench.REL_TRUNC, bench.MAX_WEIGHT, *w["hi"])
+    g_lo = hg.Grid.tsdf(bench.LO_RES, bench.REL_TRUNC, bench.MAX_WEIGHT, *w["lo"])
+    batch = hg.Batch("interpolated_multires_tsdf", w["points"], w["offsets"], w["scales"], [g_hi, g_lo], w["ratios"])
+    r, J = batch.evaluate(w["poses"], w["i0"], w["i1"])
+    assert np.isfinite(r).all() and all(np.isfinite(j).all() for j in J)
+    assert np.abs(J[1]).max() > 1e-4 and np.abs(J[3]).max() > 1e-4
+
+    # (a) oracle on a sample
+    o_hi = oracle.Grid.tsdf(bench.HI_RES, bench.REL_TRUNC, bench.MAX_WEIGHT)
+    o_hi.set_raw(*w["hi"])
+    o_lo = oracle.Grid.tsdf(bench.LO_RES, bench.REL_TRUNC, bench.MAX_WEIGHT)
+    o_lo.set_raw(*w["lo"])
+    rng = np.random.RandomState(21)
+    for b in (0, 17, 40, 63):
+        pick = np.sort(rng.choice(100000, 600, replace=False)) + b * 100000
+        oc = oracle.Cost("interpolated_multires_tsdf", w["scales"][b], w["points"][pick], [o_hi, o_lo], w["ratios"][b])
+        r0, J0 = oc.evaluate(np.concatenate([w["poses"][w["i0"][b]], w["poses"][w["i1"][b]]]))
+        assert_close(r[pick], r0, "C2 block %d residuals" % b)
+        for k in range(4):
+            assert_close(J[k][pick], J0[k], "C2 block %d jacobian %d" % (b, k))
+
+    # (b1) fused normal equations == J'J, J'r, 0.5 r'r of the rows, per block
+    JtJ, Jtr, cost = batch.normal_equations(w["poses"], w["i0"], w["i1"])
+    for b in (0, 31, 63):
+        s = slice(b * 100000, (b + 1) * 100000)
+        rows = np.hstack([J[0][s], J[1][s], J[2][s], J[3][s]])
+        want = rows.T @ rows
+        scale = np.abs(want).max()
+        assert np.abs(JtJ[b] - want).max() <= 1e-9 * scale
+        assert np.abs(Jtr[b] - rows.T @ r[s]).max() <= 1e-9 * max(1.0, np.abs(Jtr[b]).max())
+        assert abs(cost[b] - 0.5 * float(r[s] @ r[s])) <= 1e-9 * max(1.0, cost[b])
+
+    # (b2) reversing the points inside every block reverses the rows, bit for bit
+    rev = np.ascontiguousarray(w["points"].reshape(64, 100000, 3)[:, ::-1, :].reshape(-1, 3))
+    batch_rev = hg.Batch("interpolated_multires_tsdf", rev, w["offsets"], w["scales"], [g_hi, g_lo], w["ratios"])
+    r2, J2 = batch_rev.evaluate(w["poses"], w["i0"], w["i1"])
+    assert (r2.reshape(64, 100000)[:, ::-1] == r.reshape(64, 100000)).all()
+    for k in range(4):
+        width = J[k].shape[1]
+        assert (J2[k].reshape(64, 100000, width)[:, ::-1] == J[k].reshape(64, 100000, width)).all()
