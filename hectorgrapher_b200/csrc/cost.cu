@@ -323,13 +323,14 @@ __device__ __forceinline__ ValueGrad Residual(const CostArgs& a, const double sc
 // Number of Gauss-Newton outputs for n ambient parameters: upper triangle of
 // J'J, J'r, and sum r^2.
 __host__ __device__ constexpr int NumNormalTerms(int n) { return n * (n + 1) / 2 + n + 1; }
+// Terms the kernel accumulates per tile: those of the 7-vector u (see CostKernel).
+constexpr int kNormalTermsU = NumNormalTerms(7);
 
 template <int LOOKUP, bool TWO_POSE, bool NORMAL_EQ>
 __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const CostArgs a) {
   constexpr int NC = TWO_POSE ? 14 : 7;
-  constexpr int ROW = NC + 1;  // row of [J | r] staged for the normal-equation reduction
   __shared__ BlockDev sb;
-  extern __shared__ double rows[];  // NORMAL_EQ only: kThreads x ROW
+  extern __shared__ double red[];  // NORMAL_EQ only: kNormalTermsU x kThreads
 
   const TileDev tile = a.tiles[blockIdx.x];
   {
@@ -341,24 +342,15 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
   }
   __syncthreads();
 
-  constexpr int P = NumNormalTerms(NC);
-  // NORMAL_EQ: threads 0..127 and 128..255 each own one term (ne_term < P) over one
-  // half of the staged rows. Terms: upper-triangle pairs (ca <= cb), then J'r, then r'r.
-  double acc = 0.0;
-  const int ne_term = threadIdx.x & 127, ne_half = threadIdx.x >> 7;
-  int ne_ca = 0, ne_cb = 0;
+  // NORMAL_EQ: every row of [J | r] is u M with u = (grad value, grad . d world / d q) — 7 numbers
+  // per point — and a block-constant 7 x NC matrix M (identity for one pose; the interpolation
+  // weights and d q / d q0, d q / d q1 for two). So J'J = M' (sum u u') M: the kernel only sums
+  // the 36 terms of u and r (upper triangle of u u', u r, r r) per thread in registers, and
+  // ReducePartialsKernel applies M once per block.
+  double S[kNormalTermsU];
   if (NORMAL_EQ) {
-    int e = ne_term;
-    if (e < NC * (NC + 1) / 2) {
-      while (e >= NC - ne_ca) { e -= NC - ne_ca; ++ne_ca; }
-      ne_cb = ne_ca + e;
-    } else if (e < NC * (NC + 1) / 2 + NC) {
-      ne_ca = e - NC * (NC + 1) / 2;
-      ne_cb = NC;
-    } else {
-      ne_ca = NC;
-      ne_cb = NC;
-    }
+#pragma unroll
+    for (int e = 0; e < kNormalTermsU; ++e) S[e] = 0.0;
   }
 
   const int tile_end = min(sb.n, tile.start + a.tile_points);
@@ -408,7 +400,17 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
       const double dzz_ = qw * ez2 + 0.0 + (qx * ez1 - qy * ez0);
       const double az = v.gx * dzx_ + v.gy * dzy_ + v.gz * dzz_;
 
-      if (!TWO_POSE) {
+      if (NORMAL_EQ) {
+        const double u[7] = {v.gx, v.gy, v.gz, aw, ax, ay, az};
+        int e = 0;
+#pragma unroll
+        for (int ca = 0; ca < 7; ++ca)
+#pragma unroll
+          for (int cb = ca; cb < 7; ++cb) S[e++] += u[ca] * u[cb];
+#pragma unroll
+        for (int ca = 0; ca < 7; ++ca) S[28 + ca] += u[ca] * res;
+        S[35] += res * res;
+      } else if (!TWO_POSE) {
         J[0] = v.gx; J[1] = v.gy; J[2] = v.gz;
         J[3] = aw; J[4] = ax; J[5] = ay; J[6] = az;
       } else {
@@ -457,48 +459,91 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
         }
       }
     }
-    if (NORMAL_EQ) {
-      double* my = rows + threadIdx.x * ROW;
-#pragma unroll
-      for (int c = 0; c < NC; ++c) my[c] = J[c];
-      my[NC] = res;
-      __syncthreads();
-      if (ne_term < P) {
-        // This thread's term over its half of the staged rows, four independent
-        // partial sums so that the FP64 adds do not form one long dependent chain.
-        const double* ra = rows + (ne_half * (kThreads / 2)) * ROW + ne_ca;
-        const double* rb = rows + (ne_half * (kThreads / 2)) * ROW + ne_cb;
-        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-#pragma unroll 4
-        for (int rr = 0; rr < kThreads / 2; rr += 4) {
-          s0 += ra[(rr + 0) * ROW] * rb[(rr + 0) * ROW];
-          s1 += ra[(rr + 1) * ROW] * rb[(rr + 1) * ROW];
-          s2 += ra[(rr + 2) * ROW] * rb[(rr + 2) * ROW];
-          s3 += ra[(rr + 3) * ROW] * rb[(rr + 3) * ROW];
-        }
-        acc += (s0 + s1) + (s2 + s3);
-      }
-      __syncthreads();
-    }
   }
   if (NORMAL_EQ) {
-    // Combine the two halves (fixed order) and write this tile's partial vector.
-    if (ne_term < P && ne_half == 1) rows[ne_term] = acc;
+    // Tile total of every term in a fixed order: thread-private sums -> shared memory
+    // [term][thread] (conflict-free both ways) -> one warp per term: 8 values per lane, then
+    // a shuffle tree.
+#pragma unroll
+    for (int e = 0; e < kNormalTermsU; ++e) red[e * kThreads + threadIdx.x] = S[e];
     __syncthreads();
-    if (ne_term < P && ne_half == 0) a.partials[static_cast<size_t>(blockIdx.x) * P + ne_term] = acc + rows[ne_term];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int e = warp; e < kNormalTermsU; e += kThreads / 32) {
+      double s = 0.0;
+#pragma unroll
+      for (int k = 0; k < kThreads / 32; ++k) s += red[e * kThreads + k * 32 + lane];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+      if (lane == 0) a.partials[static_cast<size_t>(blockIdx.x) * kNormalTermsU + e] = s;
+    }
   }
-
 }
 
-// Sums the tile partials of each residual block in tile order (deterministic).
-__global__ void ReducePartialsKernel(const double* __restrict__ partials, const int* __restrict__ tile_begin,
-                                     const int P, double* __restrict__ out) {
+// Sums the tile partials of each residual block in tile order (deterministic), then maps the
+// 36 terms of u to the block's parameters: one pose — u is the Jacobian row, the terms are the
+// output; two poses — row = u M with M = [ct0 I3, 0 | 0, m0 | ct1 I3, 0 | 0, m1] (7 x 14), so
+// J'J = M' S M, J'r = M' (sum u r). Output per block: upper triangle of J'J, J'r, r'r.
+__global__ void __launch_bounds__(128) ReducePartialsKernel(const double* __restrict__ partials,
+                                                            const int* __restrict__ tile_begin,
+                                                            const BlockDev* __restrict__ blocks,
+                                                            const int two_pose, double* __restrict__ out) {
+  __shared__ double S[kNormalTermsU];
   const int b = blockIdx.x;
   const int e = threadIdx.x;
+  if (e < kNormalTermsU) {
+    double s = 0.0;
+    for (int t = tile_begin[b]; t < tile_begin[b + 1]; ++t) s += partials[static_cast<size_t>(t) * kNormalTermsU + e];
+    S[e] = s;
+  }
+  __syncthreads();
+  if (!two_pose) {
+    if (e < kNormalTermsU) out[static_cast<size_t>(b) * kNormalTermsU + e] = S[e];
+    return;
+  }
+  constexpr int NC = 14, P = NumNormalTerms(NC);
   if (e >= P) return;
-  double s = 0.0;
-  for (int t = tile_begin[b]; t < tile_begin[b + 1]; ++t) s += partials[static_cast<size_t>(t) * P + e];
-  out[static_cast<size_t>(b) * P + e] = s;
+  const BlockDev& blk = blocks[b];
+  // Column c of M as a 7-vector.
+  const auto column = [&blk](const int c, double* m) {
+#pragma unroll
+    for (int i = 0; i < 7; ++i) m[i] = 0.0;
+    if (c < 3) {
+      m[c] = blk.ct0;
+    } else if (c < 7) {
+      for (int k = 0; k < 4; ++k) m[3 + k] = blk.m0[4 * k + (c - 3)];
+    } else if (c < 10) {
+      m[c - 7] = blk.ct1;
+    } else {
+      for (int k = 0; k < 4; ++k) m[3 + k] = blk.m1[4 * k + (c - 10)];
+    }
+  };
+  const auto sym = [](const int i, const int j) {  // index of (i, j) in the upper triangle of the 7 x 7 sums
+    const int lo = i < j ? i : j, hi = i < j ? j : i;
+    return lo * 7 - lo * (lo - 1) / 2 + (hi - lo);
+  };
+  double value;
+  if (e < NC * (NC + 1) / 2) {
+    int ca = 0, r = e;
+    while (r >= NC - ca) { r -= NC - ca; ++ca; }
+    const int cb = ca + r;
+    double ma[7], mb[7];
+    column(ca, ma);
+    column(cb, mb);
+    value = 0.0;
+    for (int i = 0; i < 7; ++i) {
+      double row = 0.0;
+      for (int j = 0; j < 7; ++j) row += S[sym(i, j)] * mb[j];
+      value += ma[i] * row;
+    }
+  } else if (e < NC * (NC + 1) / 2 + NC) {
+    double m[7];
+    column(e - NC * (NC + 1) / 2, m);
+    value = 0.0;
+    for (int i = 0; i < 7; ++i) value += m[i] * S[28 + i];
+  } else {
+    value = S[35];
+  }
+  out[static_cast<size_t>(b) * P + e] = value;
 }
 
 }  // namespace hg
@@ -581,8 +626,7 @@ void BuildTiles(const std::vector<int64_t>& offsets, int tile_points, std::vecto
 template <bool NE>
 int LaunchCost(const hg_batch* B, const CostArgs& args, int num_tiles, cudaStream_t stream) {
   if (num_tiles == 0) return HG_OK;
-  const int NC = B->two_pose ? 14 : 7;
-  const size_t smem = NE ? static_cast<size_t>(kThreads) * (NC + 1) * sizeof(double) : 0;
+  const size_t smem = NE ? static_cast<size_t>(kThreads) * kNormalTermsU * sizeof(double) : 0;
 #define HG_LAUNCH(L, T)                                                                         \
   do {                                                                                          \
     if (NE && smem > 48 * 1024) {                                                               \
@@ -725,7 +769,7 @@ int hg_batch_create(int kind, int num_blocks, const float* points, int stride_fl
   HG_ALLOC(B->d_blocks, CachedDeviceAlloc(sizeof(BlockDev) * num_blocks));
   HG_ALLOC(B->h_blocks, CachedPinnedAlloc(sizeof(BlockDev) * num_blocks));
   const int P = NumNormalTerms(two ? 14 : 7);
-  HG_ALLOC(B->d_partials, CachedDeviceAlloc(sizeof(double) * P * std::max(B->num_tiles_ne, 1)));
+  HG_ALLOC(B->d_partials, CachedDeviceAlloc(sizeof(double) * kNormalTermsU * std::max(B->num_tiles_ne, 1)));
   HG_ALLOC(B->d_ne_out, CachedDeviceAlloc(sizeof(double) * P * num_blocks));
   HG_ALLOC(B->h_ne_out, CachedPinnedAlloc(sizeof(double) * P * num_blocks));
   *out = B.release();
@@ -823,7 +867,8 @@ int hg_batch_normal_equations(const hg_batch* B, const double* poses, int num_po
   if (rc != HG_OK) return rc;
   const int n = B->two_pose ? 14 : 7;
   const int P = NumNormalTerms(n);
-  ReducePartialsKernel<<<B->num_blocks, 128, 0, stream>>>(B->d_partials, B->d_ne_tile_begin, P, B->d_ne_out);
+  ReducePartialsKernel<<<B->num_blocks, 128, 0, stream>>>(B->d_partials, B->d_ne_tile_begin, B->d_blocks,
+                                                          B->two_pose ? 1 : 0, B->d_ne_out);
   CountLaunch();
   HG_CUDA(cudaGetLastError());
   HG_CUDA(cudaMemcpyAsync(B->h_ne_out, B->d_ne_out, sizeof(double) * P * B->num_blocks,
@@ -1158,7 +1203,8 @@ extern "C" int hg_cost_normal_equations_static(const hg_cost* cost, const double
   if (rc != HG_OK) return rc;
   const int n = B->two_pose ? 14 : 7;
   const int P = NumNormalTerms(n);
-  ReducePartialsKernel<<<1, 128, 0, stream>>>(d_partials, B->d_ne_tile_begin, P, d_reduced);
+  ReducePartialsKernel<<<1, 128, 0, stream>>>(d_partials, B->d_ne_tile_begin, d_block, B->two_pose ? 1 : 0,
+                                              d_reduced);
   CountLaunch();
   HG_CUDA(cudaGetLastError());
   double reduced[kStaticTerms];
