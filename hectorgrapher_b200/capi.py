@@ -62,6 +62,17 @@ class TsdfInserterOptions(C.Structure):
                 ("reserved", C.c_int32)]
 
 
+class GridProtoInfo(C.Structure):
+    _fields_ = [("resolution", c_f), ("relative_truncation_distance", c_f), ("max_weight", c_f),
+                ("is_tsdf", C.c_int32), ("num_voxels", c_i64)]
+
+
+class SubmapInfo(C.Structure):
+    _fields_ = [("trajectory_id", C.c_int32), ("submap_index", C.c_int32), ("local_pose", c_d * 7),
+                ("num_range_data", C.c_int32), ("finished", C.c_int32), ("high_is_tsdf", C.c_int32),
+                ("low_is_tsdf", C.c_int32), ("histogram_size", C.c_int32), ("reserved", C.c_int32)]
+
+
 class ConstraintJob(C.Structure):
     _fields_ = [("submap_index", C.c_int32), ("match_full_submap", C.c_int32),
                 ("global_node_pose", c_d * 7), ("global_submap_pose", c_d * 7), ("data", NodeData)]
@@ -123,6 +134,14 @@ SYMBOLS = {
     "hg_low_resolution_scores": (c_i, [vp, vp, c_i, c_i64, vp, vp]),
     "hg_constraints_run_batch": (c_i, [vp, vp, vp, c_i, vp, c_i64, vp, c_i, c_i, vp]),
     "hg_grid_export": (c_i, [vp, c_i64, vp, vp, vp, vp]),
+    "hg_grid_proto_decode": (c_i, [vp, c_i64, c_i, vp, c_i64, vp, vp, vp]),
+    "hg_grid_from_proto": (c_i, [vp, c_i64, c_i, vp]),
+    "hg_grid_to_proto": (c_i, [vp, vp, c_i64, vp]),
+    "hg_pbstream_open": (c_i, [C.c_char_p, vp]),
+    "hg_pbstream_next_submap": (c_i, [vp, vp, vp]),
+    "hg_pbstream_submap_grid": (c_i, [vp, c_i, vp]),
+    "hg_pbstream_submap_histogram": (c_i, [vp, c_i, vp]),
+    "hg_pbstream_close": (None, [vp]),
     "hg_grid_insert_occupancy": (c_i, [vp, vp, vp, vp, c_i, c_i64]),
     "hg_grid_insert_tsdf": (c_i, [vp, vp, vp, vp, c_i, c_i64, vp]),
     "hg_voxel_filter": (c_i, [c_f, vp, c_i, c_i64, vp, vp]),
@@ -225,6 +244,22 @@ class Grid:
         _check(lib().hg_grid_lookup(self.h, code, len(xyz), _p(xyz), _p(out)))
         return out
 
+    @staticmethod
+    def from_proto(data, tsdf):
+        """HybridGrid(proto) / HybridGridTSDF(proto) from a serialized message (bytes)."""
+        buf = (C.c_char * len(data)).from_buffer_copy(data)
+        out = vp()
+        _check(lib().hg_grid_from_proto(buf, len(data), int(tsdf), C.byref(out)))
+        return Grid(out, bool(tsdf))
+
+    def to_proto(self):
+        """Serialized proto::HybridGrid / proto::HybridGridTSDF (bytes)."""
+        n = c_i64(0)
+        _check(lib().hg_grid_to_proto(self.h, None, 0, C.byref(n)))
+        buf = (C.c_char * max(n.value, 1))()
+        _check(lib().hg_grid_to_proto(self.h, buf, n.value, C.byref(n)))
+        return bytes(buf[:n.value])
+
     def export(self):
         """(xyz [n,3] int32, values_a [n] uint16, values_b [n] uint16 or None): the non-default voxels."""
         n = c_i64(0)
@@ -256,6 +291,59 @@ class Grid:
         n = c_i64(0)
         _check(lib().hg_grid_insert_tsdf(self.h, C.byref(o), _p(origin), _p(pts), stride, len(pts), C.byref(n)))
         return n.value
+
+
+def grid_proto_decode(data, tsdf):
+    """Host-only decode of a serialized grid message: (info dict, xyz, values_a, values_b or None)."""
+    buf = (C.c_char * max(len(data), 1)).from_buffer_copy(data if data else b"\0")
+    info = GridProtoInfo()
+    _check(lib().hg_grid_proto_decode(buf, len(data), int(tsdf), C.byref(info), 0, None, None, None))
+    n = info.num_voxels
+    xyz = np.zeros((n, 3), np.int32)
+    a = np.zeros(n, np.uint16)
+    b = np.zeros(n, np.uint16) if tsdf else None
+    if n:
+        _check(lib().hg_grid_proto_decode(buf, len(data), int(tsdf), C.byref(info), n, _p(xyz), _p(a),
+                                          _p(b) if tsdf else None))
+    d = dict(resolution=info.resolution, relative_truncation_distance=info.relative_truncation_distance,
+             max_weight=info.max_weight, num_voxels=n)
+    return d, xyz, a, b
+
+
+class PbStream:
+    """Iterates the 3D submaps of a .pbstream file: yields (info dict, high Grid or None, low Grid or
+    None, histogram)."""
+
+    def __init__(self, path, upload=True):
+        self.h = vp()
+        self.upload = upload
+        _check(lib().hg_pbstream_open(str(path).encode(), C.byref(self.h)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().hg_pbstream_close(self.h)
+            self.h = None
+
+    def __iter__(self):
+        while True:
+            has = C.c_int(0)
+            info = SubmapInfo()
+            _check(lib().hg_pbstream_next_submap(self.h, C.byref(has), C.byref(info)))
+            if not has.value:
+                return
+            d = dict(trajectory_id=info.trajectory_id, submap_index=info.submap_index,
+                     local_pose=np.array(list(info.local_pose)), num_range_data=info.num_range_data,
+                     finished=bool(info.finished), high_is_tsdf=info.high_is_tsdf, low_is_tsdf=info.low_is_tsdf)
+            hist = np.zeros(info.histogram_size, np.float32)
+            _check(lib().hg_pbstream_submap_histogram(self.h, info.histogram_size, _p(hist) if len(hist) else None))
+            grids = [None, None]
+            if self.upload:
+                for which, flag in enumerate((info.high_is_tsdf, info.low_is_tsdf)):
+                    if flag >= 0:
+                        out = vp()
+                        _check(lib().hg_pbstream_submap_grid(self.h, which, C.byref(out)))
+                        grids[which] = Grid(out, bool(flag))
+            yield d, grids[0], grids[1], hist
 
 
 def get_cell_index(resolution, pts):

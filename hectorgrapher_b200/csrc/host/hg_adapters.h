@@ -27,6 +27,7 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <string>
 #include <thread>
 #include <utility>
 #include <vector>
@@ -110,6 +111,22 @@ class DeviceGrid {
                                 weight, &g),
             "hg_grid_upload_tsdf");
     return std::shared_ptr<DeviceGrid>(new DeviceGrid(g));
+  }
+  // HybridGrid(const proto::HybridGrid&) / HybridGridTSDF(const proto::HybridGridTSDF&) from the
+  // serialized message (proto.SerializeAsString()); hybrid_grid.h:61-73, hybrid_grid_tsdf.h:69-83.
+  static std::shared_ptr<DeviceGrid> FromProto(const std::string& serialized, bool tsdf) {
+    hg_grid* g = nullptr;
+    CheckOk(hg_grid_from_proto(serialized.data(), static_cast<int64_t>(serialized.size()), tsdf ? 1 : 0, &g),
+            "hg_grid_from_proto");
+    return std::shared_ptr<DeviceGrid>(new DeviceGrid(g));
+  }
+  // ToProto().SerializeAsString() (hybrid_grid.h:88-99, hybrid_grid_tsdf.h:119-134).
+  std::string ToProto() const {
+    int64_t size = 0;
+    CheckOk(hg_grid_to_proto(grid_, nullptr, 0, &size), "hg_grid_to_proto");
+    std::string out(static_cast<size_t>(size), '\0');
+    if (size > 0) CheckOk(hg_grid_to_proto(grid_, &out[0], size, &size), "hg_grid_to_proto");
+    return out;
   }
   ~DeviceGrid() { hg_grid_destroy(grid_); }
   const hg_grid* get() const { return grid_; }

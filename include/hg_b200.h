@@ -89,6 +89,70 @@ int hg_get_cell_index(float resolution, int64_t n, const float* points_xyz, int3
 int hg_grid_export(const hg_grid* grid, int64_t max_voxels, int64_t* num_voxels, int32_t* xyz,
                    uint16_t* values_a, uint16_t* values_b);
 
+/* ------------------------------------------- grid wire format (N3) -- */
+
+/* Scalar fields of proto::HybridGrid / proto::HybridGridTSDF
+ * (mapping/proto/3d/hybrid_grid.proto:19-29, hybrid_grid_tsdf.proto:19-32). */
+typedef struct hg_grid_proto_info {
+  float resolution;
+  float relative_truncation_distance; /* TSDF only (field 8, as stored — see hg_grid_to_proto) */
+  float max_weight;                   /* TSDF only (field 9) */
+  int32_t is_tsdf;
+  int64_t num_voxels;
+} hg_grid_proto_info;
+
+/* Decodes a serialized proto::HybridGrid (is_tsdf = 0) or proto::HybridGridTSDF (is_tsdf = 1)
+ * message on the host: packed or unpacked repeated fields, zig-zag indices, unknown fields
+ * skipped; the index and value arrays must have equal lengths like the CHECKs of the
+ * constructors (hybrid_grid.h:63-66, hybrid_grid_tsdf.h:73-77). Fills *info; writes the
+ * voxels only if capacity >= info->num_voxels (arrays may be NULL when capacity is 0).
+ * values_b receives the weights of a TSDF grid. No device work. */
+int hg_grid_proto_decode(const void* bytes, int64_t size, int is_tsdf, hg_grid_proto_info* info,
+                         int64_t capacity, int32_t* xyz, uint16_t* values_a, uint16_t* values_b);
+
+/* HybridGrid(const proto::HybridGrid&) / HybridGridTSDF(const proto::HybridGridTSDF&)
+ * (hybrid_grid.h:61-73, hybrid_grid_tsdf.h:69-83): decode + upload. Values go through the
+ * constructors' SetProbability(ValueToProbability(v)) / SetCell(ValueToTSD(t), ValueToWeight(w))
+ * round trip, i.e. the update marker of a stored TSD value is dropped and re-added and value
+ * 0 becomes 1. */
+int hg_grid_from_proto(const void* bytes, int64_t size, int is_tsdf, hg_grid** out);
+
+/* HybridGrid::ToProto / HybridGridTSDF::ToProto (hybrid_grid.h:88-99, hybrid_grid_tsdf.h:119-134)
+ * serialized to wire format (packed repeated fields, the encoding protobuf emits for proto3).
+ * Like the reference, the TSDF message's relative_truncation_distance field receives
+ * ValueConverter().getMaxTSD() — the truncation distance in metres, not the relative one
+ * (hybrid_grid_tsdf.h:131) — so a grid that is written and read back truncates at
+ * max_tsd * resolution. *size receives the message size; nothing is written if it exceeds
+ * capacity. Voxel order: see hg_grid_export. */
+int hg_grid_to_proto(const hg_grid* grid, void* buffer, int64_t capacity, int64_t* size);
+
+/* A .pbstream file (io/proto_stream.cc:27-106: magic, then size-prefixed gzip chunks holding
+ * a SerializationHeader and SerializedData messages, mapping/proto/serialization.proto:72-88),
+ * read for its 3D submaps. */
+typedef struct hg_pbstream hg_pbstream;
+
+typedef struct hg_submap_info {
+  int32_t trajectory_id;   /* SubmapId (pose_graph.proto:22-25) */
+  int32_t submap_index;
+  double local_pose[7];    /* Submap3D.local_pose, t3 q4 (w, x, y, z) */
+  int32_t num_range_data;
+  int32_t finished;
+  int32_t high_is_tsdf;    /* which member of the oneofs is set; -1 = none */
+  int32_t low_is_tsdf;
+  int32_t histogram_size;  /* rotational_scan_matcher_histogram */
+  int32_t reserved;
+} hg_submap_info;
+
+int hg_pbstream_open(const char* path, hg_pbstream** out);
+/* Advances to the next SerializedData that holds a Submap3D (everything else is skipped).
+ * *has_submap = 0 at the end of the stream. */
+int hg_pbstream_next_submap(hg_pbstream* stream, int* has_submap, hg_submap_info* info);
+/* Uploads the current submap's high- (which = 0) or low-resolution (which = 1) grid. */
+int hg_pbstream_submap_grid(hg_pbstream* stream, int which, hg_grid** out);
+/* Copies the current submap's rotational scan matcher histogram (capacity in floats). */
+int hg_pbstream_submap_histogram(hg_pbstream* stream, int capacity, float* histogram);
+void hg_pbstream_close(hg_pbstream* stream);
+
 /* ------------------------------------------ range-data insertion (N1) -- */
 
 /* proto::ProbabilityGridRangeDataInserterOptions3D
