@@ -145,6 +145,14 @@ struct hg_grid {
 namespace hg {
 void DestroyGridMutable(hg_grid* grid);  // insert.cu
 
+// scan_match.cu: CeresScanMatcher3D::Match solved entirely on the device (arguments of
+// hg_scan_match). HG_ERR_LIMIT when the problem does not fit the kernel.
+int ScanMatchOnDevice(int num_clouds, const float* const* clouds, const int32_t* cloud_sizes,
+                      const hg_grid* const* grids, const double* occupied_space_weights,
+                      double translation_weight, double rotation_weight, int only_optimize_yaw,
+                      int max_num_iterations, int use_nonmonotonic_steps, const double* target_translation,
+                      const double* initial_pose, double* pose_out, double* summary_out);
+
 // Optional dense copy of a (small) precomputation level: a plain uint8 3-D array
 // over the bounding box of its bricks, x fastest. Coarse levels of the pyramid
 // are a few hundred KB; reading them densely saves the brick-index load.

@@ -1,0 +1,280 @@
+// Interpolated lookups of the submap grids with analytic gradients — the device form of
+// InterpolatedGrid::GetProbability, InterpolatedTSDF::GetTSD and one level of
+// InterpolatedMultiResolutionTSDF (paths under
+// /root/reference/cartographer/mapping/internal/3d/scan_matching):
+//   interpolated_grid.h:50-102            tricubic-Hermite occupancy lookup
+//   interpolated_tsdf.h:29-46, 71-116     weight-aware trilinear TSDF lookup
+//   interpolated_multi_resolution_tsdf.h:82-137  one level of the fine-to-coarse fall-through
+//   interpolated_tsdf.h:159-192           lower-voxel selection (float/double mix)
+// plus the pose chain rule shared by the cost kernels (cost.cu) and the on-device scan
+// matcher (scan_match.cu).
+#pragma once
+
+#include "device_math.cuh"
+
+namespace hg {
+
+// Lower-voxel selection for one axis (interpolated_tsdf.h:159-192): narrow to
+// float, containing cell, its float centre, one float step down if the centre
+// lies above the double coordinate; x2 is the float sum centre + resolution.
+// The reference re-derives the cell index of the lower centre with a second
+// GetCellIndex; that is i or i - 1 exactly (|fl(i*res)/res - i| << 0.5 for the
+// +-8192 index range), so no second division is needed.
+__device__ __forceinline__ void LowerVoxel(const GridDev& g, const double x, double* x1, double* x2,
+                                           int* index) {
+  const float xf = __double2float_rn(x);
+  int i = CellIndexFast(xf, g.resolution, g.inv_resolution);
+  float c = __fmul_rn(__int2float_rn(i), g.resolution);
+  if (static_cast<double>(c) > x) {
+    c = __fsub_rn(c, g.resolution);
+    --i;
+  }
+  *x1 = static_cast<double>(c);
+  *x2 = static_cast<double>(__fadd_rn(c, g.resolution));
+  *index = i;
+}
+
+// 1 / d for d = x2 - x1, which equals the resolution up to float rounding of the
+// cell centres: two Newton steps from 1 / double(resolution) converge to full
+// double precision (the seed is already within ~1e-7 relative).
+__device__ __forceinline__ double CellWidthReciprocal(const double seed, const double d) {
+  double r = seed * (2.0 - d * seed);
+  r = r * (2.0 - d * r);
+  return r;
+}
+
+// Fetches the 2x2x2 stencil at (ix..ix+1, iy..iy+1, iz..iz+1) in the reference's
+// corner order 111,112,121,122,211,212,221,222 (first digit x, last digit z).
+// Submap bricks carry a one-voxel apron (hg_internal.cuh), so the whole stencil
+// lives in the brick of its lower corner: one index load, eight voxel loads at
+// fixed offsets, no branches on the brick faces.
+// The voxels are the pre-decoded floats (GridDev::decoded); 'absent' is what a
+// voxel of a missing brick reads.
+__device__ __forceinline__ void FetchStencil(const GridDev& g, const int ix, const int iy, const int iz,
+                                             const float absent, float* v) {
+  const int id = BrickId(g.table, ix, iy, iz);
+  if (id < 0) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = absent;
+    return;
+  }
+  const float* base = g.decoded + (id * kApronBrickVoxels + InApronBrick(ix, iy, iz));
+  v[0] = __ldg(base);
+  v[1] = __ldg(base + 81);
+  v[2] = __ldg(base + 9);
+  v[3] = __ldg(base + 90);
+  v[4] = __ldg(base + 1);
+  v[5] = __ldg(base + 82);
+  v[6] = __ldg(base + 10);
+  v[7] = __ldg(base + 91);
+}
+
+struct ValueGrad {
+  double v, gx, gy, gz;  // value and gradient w.r.t. the world point
+};
+
+// interpolated_grid.h:50-102
+__device__ __forceinline__ ValueGrad LookupOccupancy(const GridDev& g, const double x, const double y,
+                                                     const double z) {
+  double x1, y1, z1, x2, y2, z2;
+  int ix, iy, iz;
+  LowerVoxel(g, x, &x1, &x2, &ix);
+  LowerVoxel(g, y, &y1, &y2, &iy);
+  LowerVoxel(g, z, &z1, &z2, &iz);
+  float raw[8];
+  FetchStencil(g, ix, iy, iz, g.a.unknown, raw);
+  double q[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) q[k] = static_cast<double>(raw[k]);
+  // Ceres' Jet / double is a multiplication by the reciprocal (jet.h), which is
+  // what the reference's Jacobian-evaluating instantiation computes.
+  const double sx = CellWidthReciprocal(g.inv_resolution_d, x2 - x1);
+  const double sy = CellWidthReciprocal(g.inv_resolution_d, y2 - y1);
+  const double sz = CellWidthReciprocal(g.inv_resolution_d, z2 - z1);
+  const double nx = (x - x1) * sx, ny = (y - y1) * sy, nz = (z - z1) * sz;
+  const double nxx = nx * nx, nxxx = nx * nxx, nyy = ny * ny, nyyy = ny * nyy, nzz = nz * nz,
+               nzzz = nz * nzz;
+  // Derivatives of n^2, n^3 with respect to n.
+  const double dzz = 2.0 * nz, dzzz = 3.0 * nzz, dyy = 2.0 * ny, dyyy = 3.0 * nyy, dxx = 2.0 * nx,
+               dxxx = 3.0 * nxx;
+  // z stage: value and d/dnz.
+  double a[4], az[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const double qa = q[2 * k], qb = q[2 * k + 1];
+    a[k] = (qa - qb) * nzzz * 2. + (qb - qa) * nzz * 3. + qa;
+    az[k] = (qa - qb) * dzzz * 2. + (qb - qa) * dzz * 3.;
+  }
+  // y stage: pairs (a0, a1) -> x = 1 side, (a2, a3) -> x = 2 side.
+  double b[2], by[2], bz[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const double qa = a[2 * k], qb = a[2 * k + 1];
+    b[k] = (qa - qb) * nyyy * 2. + (qb - qa) * nyy * 3. + qa;
+    by[k] = (qa - qb) * dyyy * 2. + (qb - qa) * dyy * 3.;
+    const double za = az[2 * k], zb = az[2 * k + 1];
+    bz[k] = (za - zb) * nyyy * 2. + (zb - za) * nyy * 3. + za;
+  }
+  ValueGrad r;
+  r.v = (b[0] - b[1]) * nxxx * 2. + (b[1] - b[0]) * nxx * 3. + b[0];
+  r.gx = ((b[0] - b[1]) * dxxx * 2. + (b[1] - b[0]) * dxx * 3.) * sx;
+  r.gy = ((by[0] - by[1]) * nxxx * 2. + (by[1] - by[0]) * nxx * 3. + by[0]) * sy;
+  r.gz = ((bz[0] - bz[1]) * nxxx * 2. + (bz[1] - bz[0]) * nxx * 3. + bz[0]) * sz;
+  return r;
+}
+
+// interpolated_tsdf.h:29-46 on (value, partials) tuples, branch-free. The
+// reference's weights only ever decide "observed or not" (w == 0.0 tests; sums
+// of non-negative weights are zero iff both are), so a flag per voxel carries
+// them exactly: a stored weight value of 0 or 1 decodes to 0.0f, anything larger
+// to a positive weight (value_conversion_tables.cc:29-51 with lower bound 0).
+// Copy branches pass the upstream partials through; both-unobserved is a constant.
+struct Q1 { double v, dz; bool o; };
+struct Q2 { double v, dy, dz; bool o; };
+
+__device__ __forceinline__ Q1 BlendZ(const double unknown, const double q1, const double q2,
+                                     const bool o1, const bool o2, const double n) {
+  Q1 r;
+  const double d = q2 - q1;
+  const bool both = o1 && o2;
+  r.v = both ? d * n + q1 : (o1 ? q1 : (o2 ? q2 : unknown));
+  r.dz = both ? d : 0.0;
+  r.o = o1 || o2;
+  return r;
+}
+__device__ __forceinline__ Q2 BlendY(const double unknown, const Q1& a, const Q1& b, const double n) {
+  Q2 r;
+  const bool both = a.o && b.o;
+  const double d = b.v - a.v;
+  r.v = both ? d * n + a.v : (a.o ? a.v : (b.o ? b.v : unknown));
+  r.dy = both ? d : 0.0;
+  r.dz = both ? (b.dz - a.dz) * n + a.dz : (a.o ? a.dz : (b.o ? b.dz : 0.0));
+  r.o = a.o || b.o;
+  return r;
+}
+
+// Shared tail of the TSDF lookups: 7 weight-aware blends, z then y then x.
+__device__ __forceinline__ ValueGrad BlendTsdf(const double unknown, const bool* o, const double* q,
+                                               const double nx, const double ny, const double nz,
+                                               const double sx, const double sy, const double sz) {
+  const Q1 q11 = BlendZ(unknown, q[0], q[1], o[0], o[1], nz);
+  const Q1 q12 = BlendZ(unknown, q[2], q[3], o[2], o[3], nz);
+  const Q1 q21 = BlendZ(unknown, q[4], q[5], o[4], o[5], nz);
+  const Q1 q22 = BlendZ(unknown, q[6], q[7], o[6], o[7], nz);
+  const Q2 q1 = BlendY(unknown, q11, q12, ny);
+  const Q2 q2 = BlendY(unknown, q21, q22, ny);
+  ValueGrad r;
+  const bool both = q1.o && q2.o;
+  const double d = q2.v - q1.v;
+  r.v = both ? d * nx + q1.v : (q1.o ? q1.v : (q2.o ? q2.v : unknown));
+  r.gx = both ? d * sx : 0.0;
+  r.gy = (both ? (q2.dy - q1.dy) * nx + q1.dy : (q1.o ? q1.dy : (q2.o ? q2.dy : 0.0))) * sy;
+  r.gz = (both ? (q2.dz - q1.dz) * nx + q1.dz : (q1.o ? q1.dz : (q2.o ? q2.dz : 0.0))) * sz;
+  return r;
+}
+
+// One pyramid level. Returns false when the level must be skipped
+// (multi-resolution rule: any unobserved corner), true otherwise.
+template <bool MULTI>
+__device__ __forceinline__ bool LookupTsdfLevel(const GridDev& g, const double x, const double y,
+                                                const double z, ValueGrad* out) {
+  double x1, y1, z1, x2, y2, z2;
+  int ix, iy, iz;
+  LowerVoxel(g, x, &x1, &x2, &ix);
+  LowerVoxel(g, y, &y1, &y2, &iy);
+  LowerVoxel(g, z, &z1, &z2, &iz);
+  float raw[8];
+  FetchStencil(g, ix, iy, iz, __int_as_float(0x7fc00000), raw);
+  bool o[8];
+  int observed = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    o[k] = raw[k] == raw[k];  // NaN marks an unobserved voxel
+    observed += o[k] ? 1 : 0;
+  }
+  if (MULTI) {
+    if (observed < 8) return false;  // interpolated_multi_resolution_tsdf.h:99-106
+  } else if (observed == 0) {        // interpolated_tsdf.h:87-90
+    out->v = static_cast<double>(g.min_tsd);
+    out->gx = out->gy = out->gz = 0.0;
+    return true;
+  }
+  double q[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) q[k] = static_cast<double>(raw[k]);
+  const double sx = CellWidthReciprocal(g.inv_resolution_d, x2 - x1);
+  const double sy = CellWidthReciprocal(g.inv_resolution_d, y2 - y1);
+  const double sz = CellWidthReciprocal(g.inv_resolution_d, z2 - z1);
+  const double nx = (x - x1) * sx, ny = (y - y1) * sy, nz = (z - z1) * sz;
+  if (MULTI) {
+    // every corner observed: plain trilinear blend (all seven blends take the lerp branch)
+    const double a0 = (q[1] - q[0]) * nz + q[0], d0 = q[1] - q[0];
+    const double a1 = (q[3] - q[2]) * nz + q[2], d1 = q[3] - q[2];
+    const double a2 = (q[5] - q[4]) * nz + q[4], d2 = q[5] - q[4];
+    const double a3 = (q[7] - q[6]) * nz + q[6], d3 = q[7] - q[6];
+    const double b0 = (a1 - a0) * ny + a0, b0y = a1 - a0, b0z = (d1 - d0) * ny + d0;
+    const double b1 = (a3 - a2) * ny + a2, b1y = a3 - a2, b1z = (d3 - d2) * ny + d2;
+    out->v = (b1 - b0) * nx + b0;
+    out->gx = (b1 - b0) * sx;
+    out->gy = ((b1y - b0y) * nx + b0y) * sy;
+    out->gz = ((b1z - b0z) * nx + b0z) * sz;
+    return true;
+  }
+  // interpolated_tsdf.h:34 hard-codes -0.3 for a pair of unobserved voxels.
+  *out = BlendTsdf(-0.3, o, q, nx, ny, nz, sx, sy, sz);
+  return true;
+}
+
+// LOOKUP: 0 occupancy, 1 TSDF, 2 multi-resolution TSDF. Returns the residual
+// and its gradient w.r.t. the world point, both already scaled.
+
+// world = R(q) p + t with Eigen's _transformVector formula on the raw (not normalised)
+// quaternion (transform/rigid_transform.h:191-196): uv = 2 (u x p); world = p + w uv + u x uv + t.
+struct WorldPoint {
+  double x, y, z;
+  double uvx, uvy, uvz;
+};
+__device__ __forceinline__ WorldPoint TransformPoint(const double qw, const double qx, const double qy,
+                                                     const double qz, const double tx, const double ty,
+                                                     const double tz, const double px, const double py,
+                                                     const double pz) {
+  WorldPoint w;
+  double uvx = qy * pz - qz * py, uvy = qz * px - qx * pz, uvz = qx * py - qy * px;
+  uvx += uvx; uvy += uvy; uvz += uvz;
+  w.uvx = uvx; w.uvy = uvy; w.uvz = uvz;
+  w.x = px + qw * uvx + (qy * uvz - qz * uvy) + tx;
+  w.y = py + qw * uvy + (qz * uvx - qx * uvz) + ty;
+  w.z = pz + qw * uvz + (qx * uvy - qy * uvx) + tz;
+  return w;
+}
+
+// a_k = grad . d world / d q_k for k = w, x, y, z (closed form of the formula above).
+__device__ __forceinline__ void RotationTerms(const double qw, const double qx, const double qy, const double qz,
+                                              const double px, const double py, const double pz,
+                                              const WorldPoint& w, const ValueGrad& v, double* aw, double* ax,
+                                              double* ay, double* az) {
+  const double uvx = w.uvx, uvy = w.uvy, uvz = w.uvz;
+  // d/dw = uv
+  *aw = v.gx * uvx + v.gy * uvy + v.gz * uvz;
+  // d/du_k = w (2 e_k x p) + e_k x uv + u x (2 e_k x p)
+  // k = x: 2 e_x x p = (0, -2pz, 2py)
+  const double ex0 = 0.0, ex1 = -2.0 * pz, ex2 = 2.0 * py;
+  const double dxx_ = qw * ex0 + 0.0 + (qy * ex2 - qz * ex1);
+  const double dxy_ = qw * ex1 - uvz + (qz * ex0 - qx * ex2);
+  const double dxz_ = qw * ex2 + uvy + (qx * ex1 - qy * ex0);
+  *ax = v.gx * dxx_ + v.gy * dxy_ + v.gz * dxz_;
+  // k = y: 2 e_y x p = (2pz, 0, -2px);  e_y x uv = (uvz, 0, -uvx)
+  const double ey0 = 2.0 * pz, ey1 = 0.0, ey2 = -2.0 * px;
+  const double dyx_ = qw * ey0 + uvz + (qy * ey2 - qz * ey1);
+  const double dyy_ = qw * ey1 + 0.0 + (qz * ey0 - qx * ey2);
+  const double dyz_ = qw * ey2 - uvx + (qx * ey1 - qy * ey0);
+  *ay = v.gx * dyx_ + v.gy * dyy_ + v.gz * dyz_;
+  // k = z: 2 e_z x p = (-2py, 2px, 0);  e_z x uv = (-uvy, uvx, 0)
+  const double ez0 = -2.0 * py, ez1 = 2.0 * px, ez2 = 0.0;
+  const double dzx_ = qw * ez0 - uvy + (qy * ez2 - qz * ez1);
+  const double dzy_ = qw * ez1 + uvx + (qz * ez0 - qx * ez2);
+  const double dzz_ = qw * ez2 + 0.0 + (qx * ez1 - qy * ez0);
+  *az = v.gx * dzx_ + v.gy * dzy_ + v.gz * dzz_;
+}
+
+}  // namespace hg

@@ -1,0 +1,529 @@
+// CeresScanMatcher3D::Match as ONE kernel launch: the whole
+// Levenberg-Marquardt solve of the 7-DoF refine runs on the device, no host round trip per
+// iteration.
+//
+// Reference behaviour reproduced (paths under /root/reference/cartographer):
+//   mapping/internal/3d/scan_matching/ceres_scan_matcher_3d.cc:72-95, 120-172   problem set-up
+//   .../occupied_space_cost_function_3d.h, tsdf_space_cost_function_3d.h         scan blocks
+//   .../translation_delta_cost_functor_3d.h:31-45, rotation_delta_cost_functor_3d.h:35-54
+//   mapping/internal/3d/rotation_parameterization.h:27-39                        yaw-only plus
+// The solver is the trust-region loop of include/hg_dense_lm.h (Ceres' LM strategy) restated
+// for a fixed 6- or 4-dimensional tangent space; hg_scan_match keeps the host loop for
+// HG_SCAN_MATCH_HOST=1 and the tests compare the two.
+//
+// One CTA of 512 threads per problem: every evaluation strides the points of all clouds over
+// the threads (the Jacobian row of a one-pose block is the 7-vector u of cost.cu, so a thread
+// adds 36 products per point into registers), warps reduce by shuffles, 36 threads add the
+// per-warp sums in warp order, and thread 0 runs the LM bookkeeping and the 6x6 Cholesky.
+// A clouds-worth of points (a few thousand) is a few microseconds per evaluation; the host
+// loop it replaces paid two launches, two synchronisations and two PCIe round trips per
+// evaluation.
+#include <cstdlib>
+#include <cstring>
+
+#include "interpolation.cuh"
+
+namespace hg {
+namespace {
+
+constexpr int kLmThreads = 512;
+constexpr int kLmWarps = kLmThreads / 32;
+constexpr int kMaxClouds = 4;
+constexpr int kTerms = 36;  // upper triangle of u u' (28), u r (7), r r (1)
+
+struct ScanMatchArgs {
+  GridDev grids[kMaxClouds];
+  const float* points[kMaxClouds];
+  int n[kMaxClouds];
+  double scale[kMaxClouds];
+  int num_clouds;
+  int only_optimize_yaw;
+  int max_num_iterations;
+  int use_nonmonotonic_steps;
+  double translation_weight, rotation_weight;
+  double target_t[3];
+  double target_q[4];
+  double pose[7];
+  double* out;  // pose[7], summary[6], termination
+};
+
+// LmOptions defaults of include/hg_dense_lm.h (Ceres' defaults).
+constexpr double kInitialRadius = 1e4, kMaxRadius = 1e16, kMinRadius = 1e-32;
+constexpr double kMinRelativeDecrease = 1e-3, kMinLmDiagonal = 1e-6, kMaxLmDiagonal = 1e32;
+constexpr double kFunctionTolerance = 1e-6, kGradientTolerance = 1e-10, kParameterTolerance = 1e-8;
+constexpr int kMaxConsecutiveNonmonotonicSteps = 5;
+
+__device__ void QuatProduct(const double* z, const double* w, double* zw) {
+  zw[0] = z[0] * w[0] - z[1] * w[1] - z[2] * w[2] - z[3] * w[3];
+  zw[1] = z[0] * w[1] + z[1] * w[0] + z[2] * w[3] - z[3] * w[2];
+  zw[2] = z[0] * w[2] - z[1] * w[3] + z[2] * w[0] + z[3] * w[1];
+  zw[3] = z[0] * w[3] + z[1] * w[2] - z[2] * w[1] + z[3] * w[0];
+}
+
+// Lower Cholesky of the n x n matrix A (row-major, n <= 6), then A x = b.
+__device__ bool CholeskySolve(double* A, const double* b, const int n, double* x) {
+  for (int j = 0; j < n; ++j) {
+    double d = A[j * n + j];
+    for (int k = 0; k < j; ++k) d -= A[j * n + k] * A[j * n + k];
+    if (!(d > 0.0) || !isfinite(d)) return false;
+    const double l = sqrt(d);
+    A[j * n + j] = l;
+    for (int i = j + 1; i < n; ++i) {
+      double s = A[i * n + j];
+      for (int k = 0; k < j; ++k) s -= A[i * n + k] * A[j * n + k];
+      A[i * n + j] = s / l;
+    }
+  }
+  double y[6];
+  for (int i = 0; i < n; ++i) {
+    double s = b[i];
+    for (int k = 0; k < i; ++k) s -= A[i * n + k] * y[k];
+    y[i] = s / A[i * n + i];
+  }
+  for (int i = n - 1; i >= 0; --i) {
+    double s = y[i];
+    for (int k = i + 1; k < n; ++k) s -= A[k * n + i] * x[k];
+    x[i] = s / A[i * n + i];
+  }
+  return true;
+}
+
+// State of the solve; lives in shared memory, touched by thread 0 only.
+struct LmState {
+  double x[7], x_backup[7], x_min[7];
+  double H[36], g[6], Hs[36], gs[6], scale[6], delta[6];
+  double cost, radius, decrease_factor;
+  double reference_cost, candidate_cost, minimum_cost;
+  double accumulated_reference_model_cost_change, accumulated_candidate_model_cost_change;
+  double model_cost_change, step_norm2, x_norm2;
+  double initial_cost;
+  int num_consecutive_nonmonotonic_steps;
+  int iterations, successful_steps, cost_evaluations, jacobian_evaluations, termination;
+  int n;
+  int phase;  // 0 = first evaluation pending, 1 = candidate evaluation pending
+  int done;
+};
+
+// From the summed terms at pose x: cost, H = J'J and g = J'r in tangent coordinates.
+__device__ void AssembleNormal(const ScanMatchArgs& a, const double* S, const double* x, const int n,
+                               double* cost, double* H, double* g) {
+  double JtJ[49], Jtr[7];
+  int e = 0;
+  for (int i = 0; i < 7; ++i)
+    for (int j = i; j < 7; ++j, ++e) JtJ[i * 7 + j] = JtJ[j * 7 + i] = S[e];
+  for (int i = 0; i < 7; ++i) Jtr[i] = S[28 + i];
+  double c = 0.5 * S[35];
+  // translation_delta_cost_functor_3d.h:31-45: r = s (t - target), J = s I.
+  {
+    const double s = a.translation_weight;
+    double rr = 0.0;
+    for (int k = 0; k < 3; ++k) {
+      const double r = s * (x[k] - a.target_t[k]);
+      JtJ[k * 7 + k] += s * s;
+      Jtr[k] += s * r;
+      rr += r * r;
+    }
+    c += 0.5 * rr;
+  }
+  // rotation_delta_cost_functor_3d.h:35-54: r = s imag(target^-1 q), linear in q.
+  {
+    const double s = a.rotation_weight;
+    const double z[4] = {a.target_q[0], -a.target_q[1], -a.target_q[2], -a.target_q[3]};
+    const double* w = x + 3;
+    const double M[12] = {z[1], z[0], -z[3], z[2], z[2], z[3], z[0], -z[1], z[3], -z[2], z[1], z[0]};
+    double r[3];
+    r[0] = s * (z[0] * w[1] + z[1] * w[0] + z[2] * w[3] - z[3] * w[2]);
+    r[1] = s * (z[0] * w[2] - z[1] * w[3] + z[2] * w[0] + z[3] * w[1]);
+    r[2] = s * (z[0] * w[3] + z[1] * w[2] - z[2] * w[1] + z[3] * w[0]);
+    for (int p = 0; p < 4; ++p) {
+      double jr = 0.0;
+      for (int k = 0; k < 3; ++k) jr += (s * M[k * 4 + p]) * r[k];
+      Jtr[3 + p] += jr;
+      for (int q = 0; q < 4; ++q) {
+        double t = 0.0;
+        for (int k = 0; k < 3; ++k) t += (s * M[k * 4 + p]) * (s * M[k * 4 + q]);
+        JtJ[(3 + p) * 7 + 3 + q] += t;
+      }
+    }
+    c += 0.5 * (r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
+  }
+  *cost = c;
+  // Tangent basis P (7 x n): identity for t; ceres::QuaternionParameterization::ComputeJacobian
+  // or the yaw-only plus (rotation_parameterization.h:27-39) for q.
+  double P[42];
+  for (int i = 0; i < 7 * n; ++i) P[i] = 0.0;
+  for (int k = 0; k < 3; ++k) P[k * n + k] = 1.0;
+  const double* q = x + 3;
+  if (n == 6) {
+    const double Pq[12] = {-q[1], -q[2], -q[3], q[0], q[3], -q[2], -q[3], q[0], q[1], q[2], -q[1], q[0]};
+    for (int r = 0; r < 4; ++r)
+      for (int l = 0; l < 3; ++l) P[(3 + r) * n + 3 + l] = Pq[r * 3 + l];
+  } else {
+    const double Pq[4] = {-q[3], -q[2], q[1], q[0]};
+    for (int r = 0; r < 4; ++r) P[(3 + r) * n + 3] = Pq[r];
+  }
+  for (int la = 0; la < n; ++la) {
+    double s = 0.0;
+    for (int i = 0; i < 7; ++i) s += P[i * n + la] * Jtr[i];
+    g[la] = s;
+    for (int lb = 0; lb < n; ++lb) {
+      double h = 0.0;
+      for (int i = 0; i < 7; ++i) {
+        double t = 0.0;
+        for (int j = 0; j < 7; ++j) t += JtJ[i * 7 + j] * P[j * n + lb];
+        h += P[i * n + la] * t;
+      }
+      H[la * n + lb] = h;
+    }
+  }
+}
+
+__device__ void ApplyScaling(LmState* s) {
+  const int n = s->n;
+  for (int a = 0; a < n; ++a) {
+    s->gs[a] = s->g[a] * s->scale[a];
+    for (int b = 0; b < n; ++b) s->Hs[a * n + b] = s->H[a * n + b] * s->scale[a] * s->scale[b];
+  }
+}
+
+__device__ double MaxAbsGradient(const LmState* s) {
+  double v = 0.0;
+  for (int a = 0; a < s->n; ++a) v = fmax(v, fabs(s->g[a]));
+  return v;
+}
+
+// x (+) delta: identity for t; exp(delta) * q or the yaw-only plus for q.
+__device__ void ApplyDelta(LmState* s, const int yaw_only) {
+  for (int k = 0; k < 3; ++k) s->x[k] += s->delta[k] * s->scale[k];
+  double* q = s->x + 3;
+  double out[4];
+  if (!yaw_only) {
+    const double dx = s->delta[3] * s->scale[3], dy = s->delta[4] * s->scale[4], dz = s->delta[5] * s->scale[5];
+    const double norm = sqrt(dx * dx + dy * dy + dz * dz);
+    if (norm > 0.0) {
+      const double sin_by_norm = sin(norm) / norm;
+      const double q_delta[4] = {cos(norm), sin_by_norm * dx, sin_by_norm * dy, sin_by_norm * dz};
+      QuatProduct(q_delta, q, out);
+      for (int k = 0; k < 4; ++k) q[k] = out[k];
+    }
+  } else {
+    double c = s->delta[3] * s->scale[3];
+    c = c > 0.5 ? 0.5 : (c < -0.5 ? -0.5 : c);
+    const double q_delta[4] = {sqrt(1. - c * c), 0., 0., c};
+    QuatProduct(q_delta, q, out);
+    for (int k = 0; k < 4; ++k) q[k] = out[k];
+  }
+}
+
+// Computes steps until one needs an evaluation (returns with the candidate in s->x) or the
+// solve ends (s->done). DenseLmProblem::Solve, the part of the loop before the evaluation.
+__device__ void NextCandidate(LmState* s, const ScanMatchArgs& a) {
+  const int n = s->n;
+  while (s->iterations < a.max_num_iterations) {
+    ++s->iterations;
+    double A[36];
+    for (int i = 0; i < n * n; ++i) A[i] = s->Hs[i];
+    for (int i = 0; i < n; ++i) {
+      const double d = fmin(fmax(s->Hs[i * n + i], kMinLmDiagonal), kMaxLmDiagonal);
+      A[i * n + i] += d / s->radius;
+    }
+    bool step_ok = CholeskySolve(A, s->gs, n, s->delta);
+    if (step_ok) {
+      for (int i = 0; i < n; ++i) s->delta[i] = -s->delta[i];
+      double gd = 0.0, dJd = 0.0;
+      for (int i = 0; i < n; ++i) {
+        gd += s->gs[i] * s->delta[i];
+        double t = 0.0;
+        for (int j = 0; j < n; ++j) t += s->Hs[i * n + j] * s->delta[j];
+        dJd += s->delta[i] * t;
+      }
+      s->model_cost_change = -(gd + 0.5 * dJd);
+      if (!(s->model_cost_change > 0.0)) step_ok = false;
+    }
+    if (!step_ok) {
+      s->radius /= s->decrease_factor;
+      s->decrease_factor *= 2.0;
+      if (s->radius < kMinRadius) {
+        s->termination = 4;
+        s->done = 1;
+        return;
+      }
+      continue;
+    }
+    for (int k = 0; k < 7; ++k) s->x_backup[k] = s->x[k];
+    s->step_norm2 = 0.0;
+    s->x_norm2 = 0.0;
+    for (int i = 0; i < n; ++i) s->step_norm2 += (s->delta[i] * s->scale[i]) * (s->delta[i] * s->scale[i]);
+    for (int k = 0; k < 7; ++k) s->x_norm2 += s->x[k] * s->x[k];
+    ApplyDelta(s, a.only_optimize_yaw);
+    s->phase = 1;
+    return;
+  }
+  s->done = 1;  // iteration limit
+}
+
+// The evaluation at s->x has been summed into S. DenseLmProblem::Solve, the part after it.
+__device__ void Advance(LmState* s, const ScanMatchArgs& a, const double* S) {
+  const int n = s->n;
+  if (s->phase == 0) {
+    AssembleNormal(a, S, s->x, n, &s->cost, s->H, s->g);
+    ++s->cost_evaluations;
+    ++s->jacobian_evaluations;
+    s->initial_cost = s->cost;
+    s->minimum_cost = s->cost;
+    for (int j = 0; j < n; ++j) s->scale[j] = 1.0 / (1.0 + sqrt(fmax(0.0, s->H[j * n + j])));
+    ApplyScaling(s);
+    if (MaxAbsGradient(s) <= kGradientTolerance) {
+      s->termination = 2;
+      s->done = 1;
+      return;
+    }
+    s->radius = kInitialRadius;
+    s->decrease_factor = 2.0;
+    s->reference_cost = s->candidate_cost = s->minimum_cost = s->cost;
+    s->accumulated_reference_model_cost_change = 0.0;
+    s->accumulated_candidate_model_cost_change = 0.0;
+    s->num_consecutive_nonmonotonic_steps = 0;
+    for (int k = 0; k < 7; ++k) s->x_min[k] = s->x[k];
+    NextCandidate(s, a);
+    return;
+  }
+  // Candidate evaluated: its normal equations are only used if the step is accepted (the
+  // host loop re-evaluates at the accepted point, which gives these same numbers).
+  double new_cost, Hn[36], gn[6];
+  AssembleNormal(a, S, s->x, n, &new_cost, Hn, gn);
+  ++s->cost_evaluations;
+  const bool eval_ok = isfinite(new_cost);
+  if (!eval_ok) new_cost = 1.7976931348623157e308;
+  double relative_decrease = (s->cost - new_cost) / s->model_cost_change;
+  if (a.use_nonmonotonic_steps) {
+    const double historical = (s->reference_cost - new_cost) /
+                              (s->accumulated_reference_model_cost_change + s->model_cost_change);
+    relative_decrease = fmax(relative_decrease, historical);
+  }
+  if (eval_ok && relative_decrease > kMinRelativeDecrease) {
+    ++s->successful_steps;
+    const double cost_change = s->cost - new_cost;
+    const double old_cost = s->cost;
+    s->cost = new_cost;
+    for (int i = 0; i < n * n; ++i) s->H[i] = Hn[i];
+    for (int i = 0; i < n; ++i) s->g[i] = gn[i];
+    ++s->jacobian_evaluations;
+    ApplyScaling(s);
+    const double t = 2.0 * relative_decrease - 1.0;
+    s->radius = s->radius / fmax(1.0 / 3.0, 1.0 - t * t * t);
+    s->radius = fmin(kMaxRadius, s->radius);
+    s->decrease_factor = 2.0;
+    if (a.use_nonmonotonic_steps) {
+      s->accumulated_candidate_model_cost_change += s->model_cost_change;
+      s->accumulated_reference_model_cost_change += s->model_cost_change;
+      if (s->cost < s->minimum_cost) {
+        s->minimum_cost = s->cost;
+        for (int k = 0; k < 7; ++k) s->x_min[k] = s->x[k];
+        s->num_consecutive_nonmonotonic_steps = 0;
+        s->candidate_cost = s->cost;
+        s->accumulated_candidate_model_cost_change = 0.0;
+      } else {
+        ++s->num_consecutive_nonmonotonic_steps;
+        if (s->cost > s->candidate_cost) {
+          s->candidate_cost = s->cost;
+          s->accumulated_candidate_model_cost_change = 0.0;
+        }
+      }
+      if (s->num_consecutive_nonmonotonic_steps == kMaxConsecutiveNonmonotonicSteps) {
+        s->reference_cost = s->candidate_cost;
+        s->accumulated_reference_model_cost_change = s->accumulated_candidate_model_cost_change;
+      }
+    } else {
+      s->minimum_cost = s->cost;
+    }
+    if (MaxAbsGradient(s) <= kGradientTolerance) {
+      s->termination = 2;
+      s->done = 1;
+      return;
+    }
+    if (fabs(cost_change) <= kFunctionTolerance * old_cost) {
+      s->termination = 1;
+      s->done = 1;
+      return;
+    }
+    if (sqrt(s->step_norm2) <= kParameterTolerance * (sqrt(s->x_norm2) + kParameterTolerance)) {
+      s->termination = 3;
+      s->done = 1;
+      return;
+    }
+  } else {
+    for (int k = 0; k < 7; ++k) s->x[k] = s->x_backup[k];
+    s->radius /= s->decrease_factor;
+    s->decrease_factor *= 2.0;
+    if (s->radius < kMinRadius) {
+      s->termination = 4;
+      s->done = 1;
+      return;
+    }
+    if (sqrt(s->step_norm2) <= kParameterTolerance * (sqrt(s->x_norm2) + kParameterTolerance)) {
+      s->termination = 3;
+      s->done = 1;
+      return;
+    }
+  }
+  NextCandidate(s, a);
+}
+
+__global__ void __launch_bounds__(kLmThreads, 1) ScanMatchKernel(const ScanMatchArgs a) {
+  __shared__ LmState st;
+  __shared__ double warp_sums[kLmWarps][kTerms];
+  __shared__ double totals[kTerms];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int k = 0; k < 7; ++k) st.x[k] = a.pose[k];
+    st.n = a.only_optimize_yaw ? 4 : 6;
+    st.phase = 0;
+    st.done = 0;
+    st.termination = 0;
+    st.iterations = st.successful_steps = st.cost_evaluations = st.jacobian_evaluations = 0;
+  }
+  __syncthreads();
+  for (;;) {
+    // ---- evaluate all scan blocks at st.x ------------------------------------------------
+    const double tx = st.x[0], ty = st.x[1], tz = st.x[2];
+    const double qw = st.x[3], qx = st.x[4], qy = st.x[5], qz = st.x[6];
+    double S[kTerms];
+#pragma unroll
+    for (int e = 0; e < kTerms; ++e) S[e] = 0.0;
+    for (int c = 0; c < a.num_clouds; ++c) {
+      const GridDev& grid = a.grids[c];
+      const float* pts = a.points[c];
+      const double scale = a.scale[c];
+      for (int i = tid; i < a.n[c]; i += kLmThreads) {
+        const double px = static_cast<double>(pts[3 * i]), py = static_cast<double>(pts[3 * i + 1]),
+                     pz = static_cast<double>(pts[3 * i + 2]);
+        const WorldPoint wp = TransformPoint(qw, qx, qy, qz, tx, ty, tz, px, py, pz);
+        ValueGrad v;
+        if (grid.kind == kGridProb) {
+          const ValueGrad p = LookupOccupancy(grid, wp.x, wp.y, wp.z);
+          v.v = scale * (1. - p.v);  // occupied_space_cost_function_3d.h:77
+          v.gx = -scale * p.gx;
+          v.gy = -scale * p.gy;
+          v.gz = -scale * p.gz;
+        } else {
+          ValueGrad t;
+          LookupTsdfLevel<false>(grid, wp.x, wp.y, wp.z, &t);
+          v.v = scale * t.v;  // tsdf_space_cost_function_3d.h:76
+          v.gx = scale * t.gx;
+          v.gy = scale * t.gy;
+          v.gz = scale * t.gz;
+        }
+        double u[7];
+        u[0] = v.gx; u[1] = v.gy; u[2] = v.gz;
+        RotationTerms(qw, qx, qy, qz, px, py, pz, wp, v, &u[3], &u[4], &u[5], &u[6]);
+        int e = 0;
+#pragma unroll
+        for (int ca = 0; ca < 7; ++ca)
+#pragma unroll
+          for (int cb = ca; cb < 7; ++cb) S[e++] += u[ca] * u[cb];
+#pragma unroll
+        for (int ca = 0; ca < 7; ++ca) S[28 + ca] += u[ca] * v.v;
+        S[35] += v.v * v.v;
+      }
+    }
+    // ---- fixed-order reduction: lanes (shuffle tree), then warps in order -------------------
+#pragma unroll
+    for (int e = 0; e < kTerms; ++e) {
+      double s = S[e];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+      if (lane == 0) warp_sums[warp][e] = s;
+    }
+    __syncthreads();
+    if (tid < kTerms) {
+      double s = 0.0;
+      for (int w = 0; w < kLmWarps; ++w) s += warp_sums[w][tid];
+      totals[tid] = s;
+    }
+    __syncthreads();
+    if (tid == 0) Advance(&st, a, totals);
+    __syncthreads();
+    if (st.done) break;
+  }
+  if (tid == 0) {
+    double cost = st.cost;
+    if (a.use_nonmonotonic_steps && st.minimum_cost < cost) {  // Ceres reports the best point seen
+      for (int k = 0; k < 7; ++k) st.x[k] = st.x_min[k];
+      cost = st.minimum_cost;
+    }
+    for (int k = 0; k < 7; ++k) a.out[k] = st.x[k];
+    a.out[7] = st.initial_cost;
+    a.out[8] = cost;
+    a.out[9] = st.iterations;
+    a.out[10] = st.successful_steps;
+    a.out[11] = st.cost_evaluations;
+    a.out[12] = st.jacobian_evaluations;
+    a.out[13] = st.termination;
+  }
+}
+
+}  // namespace
+
+// Device-side CeresScanMatcher3D::Match. Returns HG_ERR_LIMIT when the problem does not fit the
+// kernel (more than kMaxClouds clouds); the caller then uses the host loop.
+int ScanMatchOnDevice(int num_clouds, const float* const* clouds, const int32_t* cloud_sizes,
+                      const hg_grid* const* grids, const double* occupied_space_weights,
+                      double translation_weight, double rotation_weight, int only_optimize_yaw,
+                      int max_num_iterations, int use_nonmonotonic_steps, const double* target_translation,
+                      const double* initial_pose, double* pose_out, double* summary_out) {
+  if (num_clouds > kMaxClouds) return HG_ERR_LIMIT;
+  ScanMatchArgs a;
+  std::memset(&a, 0, sizeof(a));
+  cudaStream_t stream = ThreadStream();
+  HG_REQUIRE(stream != nullptr, "hg_scan_match: cannot create a stream");
+  size_t total_floats = 0;
+  for (int i = 0; i < num_clouds; ++i) total_floats += static_cast<size_t>(cloud_sizes[i]) * 3;
+  float* d_points = static_cast<float*>(CachedDeviceAlloc(total_floats * sizeof(float)));
+  double* d_out = static_cast<double*>(CachedDeviceAlloc(14 * sizeof(double)));
+  double* h_out = static_cast<double*>(CachedPinnedAlloc(14 * sizeof(double)));
+  struct Release {
+    void* p[3];
+    ~Release() {
+      for (void* q : p) CachedFree(q);
+    }
+  } release{{d_points, d_out, h_out}};
+  if (d_points == nullptr || d_out == nullptr || h_out == nullptr) return HG_ERR_CUDA;
+  size_t offset = 0;
+  for (int i = 0; i < num_clouds; ++i) {
+    a.grids[i] = grids[i]->dev;
+    a.points[i] = d_points + offset;
+    a.n[i] = cloud_sizes[i];
+    // ceres_scan_matcher_3d.cc:138-139 / :149-150
+    a.scale[i] = occupied_space_weights[i] / std::sqrt(static_cast<double>(cloud_sizes[i]));
+    HG_CUDA(cudaMemcpyAsync(d_points + offset, clouds[i], static_cast<size_t>(cloud_sizes[i]) * 3 * sizeof(float),
+                            cudaMemcpyHostToDevice, stream));
+    offset += static_cast<size_t>(cloud_sizes[i]) * 3;
+  }
+  a.num_clouds = num_clouds;
+  a.only_optimize_yaw = only_optimize_yaw;
+  a.max_num_iterations = max_num_iterations;
+  a.use_nonmonotonic_steps = use_nonmonotonic_steps;
+  a.translation_weight = translation_weight;
+  a.rotation_weight = rotation_weight;
+  for (int k = 0; k < 3; ++k) a.target_t[k] = target_translation[k];
+  for (int k = 0; k < 4; ++k) a.target_q[k] = initial_pose[3 + k];
+  for (int k = 0; k < 7; ++k) a.pose[k] = initial_pose[k];
+  a.out = d_out;
+  ScanMatchKernel<<<1, kLmThreads, 0, stream>>>(a);
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  HG_CUDA(cudaMemcpyAsync(h_out, d_out, 14 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  HG_CUDA(cudaStreamSynchronize(stream));
+  if (static_cast<int>(h_out[13]) == 4) {
+    SetError("hg_scan_match: the trust region collapsed (no descent step could be computed)");
+    return HG_ERR_CUDA;
+  }
+  for (int k = 0; k < 7; ++k) pose_out[k] = h_out[k];
+  if (summary_out) {
+    for (int k = 0; k < 6; ++k) summary_out[k] = h_out[7 + k];
+  }
+  return HG_OK;
+}
+
+}  // namespace hg

@@ -789,3 +789,46 @@ def test_config_c2_full_size(oracle, hg):
     for k in range(4):
         width = J[k].shape[1]
         assert (J2[k].reshape(64, 100000, width)[:, ::-1] == J[k].reshape(64, 100000, width)).all()
+
+
+def test_device_scan_match_equals_host_loop(oracle, hg, world):
+    """hg_scan_match solves on the device in one launch (scan_match.cu); HG_SCAN_MATCH_HOST=1 selects
+    the host loop of include/hg_dense_lm.h over the fused normal equations. Same solver, same
+    problem: the poses agree to rounding, the iteration counts exactly; both agree with the oracle
+    (Jet cost functions under the same host solver) to the 1e-4 bar."""
+    import os
+    rng = np.random.RandomState(33)
+    cloud = world["cloud"]
+    low = cloud[::7]
+    cases = [
+        (["g_tsdf_hi", "g_tsdf_lo"], ["o_tsdf_hi", "o_tsdf_lo"], dict()),
+        (["g_prob", "g_prob_lo"], ["o_prob", "o_prob_lo"], dict()),
+        (["g_tsdf_hi"], ["o_tsdf_hi"], dict(only_optimize_yaw=True)),
+        (["g_tsdf_hi", "g_tsdf_lo"], ["o_tsdf_hi", "o_tsdf_lo"], dict(use_nonmonotonic_steps=True,
+                                                                         max_num_iterations=25)),
+    ]
+    for gnames, onames, extra in cases:
+        clouds = [cloud, low][:len(gnames)]
+        weights = [5.0, 30.0][:len(gnames)]
+        kw = dict(max_num_iterations=12, use_nonmonotonic_steps=False)
+        kw.update(extra)
+        for trial in range(3):
+            start = perturbed(world["truth"], rng, 0.08, 0.03)
+            os.environ.pop("HG_SCAN_MATCH_HOST", None)
+            pose_d, sum_d = hg.scan_match(clouds, [world[n] for n in gnames], weights, 10.0, 1.0, start, **kw)
+            os.environ["HG_SCAN_MATCH_HOST"] = "1"
+            try:
+                pose_h, sum_h = hg.scan_match(clouds, [world[n] for n in gnames], weights, 10.0, 1.0, start, **kw)
+            finally:
+                os.environ.pop("HG_SCAN_MATCH_HOST", None)
+            assert np.abs(pose_d - pose_h).max() < 1e-9, (gnames, extra, pose_d, pose_h)
+            assert (sum_d[2:] == sum_h[2:]).all(), (sum_d, sum_h)   # iterations, steps, evaluations
+            assert abs(sum_d[1] - sum_h[1]) <= 1e-9 * max(1.0, sum_h[1])
+            assert sum_d[1] < sum_d[0]
+            pose_o = oracle.scan_match(clouds, [world[n] for n in onames], weights, 10.0, 1.0, start, **kw)[0]
+            assert np.abs(pose_d[:3] - pose_o[:3]).max() < 1e-4
+            assert min(np.abs(pose_d[3:] - pose_o[3:]).max(), np.abs(pose_d[3:] + pose_o[3:]).max()) < 1e-4
+    # more clouds than the kernel takes: the host loop answers
+    many = [cloud[k::9] for k in range(5)]
+    pose, _ = hg.scan_match(many, [world["g_tsdf_hi"]] * 5, [1.0] * 5, 10.0, 1.0, world["truth"])
+    assert np.isfinite(pose).all()
