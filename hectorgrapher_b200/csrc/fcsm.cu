@@ -205,6 +205,115 @@ __global__ void __launch_bounds__(256) ScoreLatticeDenseKernel(const DenseLevel 
   }
 }
 
+// Lowest-resolution level re-laid out for the lattice: lattice candidates that are adjacent in
+// x are 'cs' = step >> reduction_exponent level cells apart, so the voxels one scan point reads
+// for a whole lattice row are every cs-th cell of one x-row of the level. Each x-row is
+// therefore stored as cs residue rows (cells x with x mod cs = r, in order of x / cs): the
+// voxels of consecutive x-candidates become CONSECUTIVE BYTES, four per 32-bit load. Rows
+// carry kLatticePadLeft zero bytes before and kLatticePadRight after their payload, so that any
+// window of up to 32 candidates that touches the payload can be read without bounds checks.
+struct LatticeRows {
+  const unsigned* data = nullptr;  // [(z * dim1 + y) * cs + r][row_words]
+  int min[3] = {0, 0, 0};
+  int dim[3] = {0, 0, 0};
+  int cs_log2 = 0;
+  int row_words = 0;
+  int payload = 0;  // bytes of payload per residue row: ceil(dim0 / cs)
+};
+constexpr int kLatticePadLeft = 32, kLatticePadRight = 40;
+
+__global__ void __launch_bounds__(256) BuildLatticeRowsKernel(const DenseLevel dense, const LatticeRows rows,
+                                                              const int64_t total_bytes,
+                                                              unsigned char* __restrict__ out) {
+  const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (i >= total_bytes) return;
+  const int row_bytes = rows.row_words * 4;
+  const int64_t row = i / row_bytes;
+  const int j = static_cast<int>(i - row * row_bytes);
+  const int r = static_cast<int>(row & ((1 << rows.cs_log2) - 1));
+  const int64_t zy = row >> rows.cs_log2;
+  const int q = j - kLatticePadLeft;
+  const int x = (q << rows.cs_log2) + r;
+  unsigned char v = 0;
+  if (q >= 0 && x < dense.dim[0]) v = dense.data[zy * dense.dim[0] + x];
+  out[i] = v;
+}
+
+// Same sums as ScoreLatticeKernel, from the residue rows: one warp scores KX = 4 * KXW
+// x-adjacent lattice candidates; a lane reads, per scan point, KXW + 1 aligned words that hold
+// the KX voxels, realigns them with funnel shifts and adds them four at a time as two packed
+// pairs of 16-bit sums (flushed to 32-bit accumulators before they can overflow).
+template <int KXW>
+__global__ void __launch_bounds__(256) ScoreLatticePackedKernel(const LatticeRows rows, const int* __restrict__ cells,
+                                                                const int N, const int reduction_exponent,
+                                                                const int nxy, const int nz, const int wxy,
+                                                                const int wz, const int step,
+                                                                const int64_t num_groups, int* __restrict__ sums) {
+  constexpr int KX = 4 * KXW;
+  const int64_t warp = (blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= num_groups) return;
+  const int gx = (nxy + KX - 1) / KX;  // groups per lattice row
+  const int rows_per_scan = nxy * nz;
+  const int64_t row = warp / gx;  // (scan, iz, iy)
+  const int g = static_cast<int>(warp - row * gx);
+  const int scan = static_cast<int>(row / rows_per_scan);
+  const int rem = static_cast<int>(row - static_cast<int64_t>(scan) * rows_per_scan);
+  const int iz = rem / nxy, iy = rem - iz * nxy;
+  const int oy = ((-wxy + iy * step) >> reduction_exponent) - rows.min[1];
+  const int oz = ((-wz + iz * step) >> reduction_exponent) - rows.min[2];
+  const int ox0 = ((-wxy + (g * KX) * step) >> reduction_exponent) - rows.min[0];
+  const int cs_mask = (1 << rows.cs_log2) - 1;
+  const int* base = cells + static_cast<int64_t>(scan) * N * 3;
+  int sum[KX];
+#pragma unroll
+  for (int k = 0; k < KX; ++k) sum[k] = 0;
+  for (int chunk = lane; chunk < N; chunk += 32 * 256) {
+    unsigned even[KXW], odd[KXW];
+#pragma unroll
+    for (int j = 0; j < KXW; ++j) even[j] = odd[j] = 0u;
+    const int chunk_end = min(N, chunk + 32 * 256);  // at most 256 points per lane: 256 * 255 < 65536
+    for (int i = chunk; i < chunk_end; i += 32) {
+      const int x = __ldg(base + 3 * i) + ox0, y = __ldg(base + 3 * i + 1) + oy, z = __ldg(base + 3 * i + 2) + oz;
+      const int q0 = x >> rows.cs_log2;
+      if (static_cast<unsigned>(y) >= static_cast<unsigned>(rows.dim[1]) ||
+          static_cast<unsigned>(z) >= static_cast<unsigned>(rows.dim[2]) || q0 < -kLatticePadLeft ||
+          q0 >= rows.payload) {
+        continue;
+      }
+      const int b = kLatticePadLeft + q0;
+      const unsigned* rowp = rows.data +
+                             ((static_cast<size_t>(z) * rows.dim[1] + y) * (cs_mask + 1) + (x & cs_mask)) * rows.row_words +
+                             (b >> 2);
+      const unsigned shift = (b & 3) * 8;
+      unsigned w[KXW + 1];
+#pragma unroll
+      for (int j = 0; j <= KXW; ++j) w[j] = __ldg(rowp + j);
+#pragma unroll
+      for (int j = 0; j < KXW; ++j) {
+        const unsigned v = __funnelshift_r(w[j], w[j + 1], shift);
+        even[j] += v & 0x00FF00FFu;
+        odd[j] += (v >> 8) & 0x00FF00FFu;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < KXW; ++j) {
+      sum[4 * j] += even[j] & 0xFFFFu;
+      sum[4 * j + 1] += odd[j] & 0xFFFFu;
+      sum[4 * j + 2] += even[j] >> 16;
+      sum[4 * j + 3] += odd[j] >> 16;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < KX; ++k) {
+    int v = sum[k];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    const int ix = g * KX + k;
+    if (lane == 0 && ix < nxy) sums[row * nxy + ix] = v;
+  }
+}
+
 // Children of a wave of parents at 'depth' (the loop nest at :441-461): warp w
 // scores child slot w % 8 = (z, y, x) in {0, half}^3 of parent w / 8, so the
 // host uploads one record per parent and reads eight sums back. A child beyond
@@ -456,6 +565,9 @@ struct hg_fcsm {
   std::vector<float> histogram;
   float resolution = 0.f;
   int width_in_voxels = 0;
+  // Residue-row copy of the lowest-resolution level for the lattice kernel (see LatticeRows).
+  LatticeRows lattice_rows;
+  void* d_lattice_rows = nullptr;
 };
 
 namespace {
@@ -653,7 +765,21 @@ struct Scorer {
     HG_CUDA(cudaEventCreate(&e1));
     HG_CUDA(cudaEventRecord(e0, stream));
     const hg_stack_level& L = m->stack->levels[depth];
-    if (L.dense.data != nullptr) {
+    const LatticeRows& R = m->lattice_rows;
+    const bool packed = R.data != nullptr && depth == static_cast<int>(m->stack->levels.size()) - 1 && nxy >= 5 &&
+                        ((1 << depth) >> ReduceExponent(depth)) == (1 << R.cs_log2);
+    if (packed) {
+      const int* cells = scans->CellsOfDepth(depth);
+      const int e = ReduceExponent(depth);
+#define HG_PACKED(KXW)                                                                                    \
+  do {                                                                                                    \
+    const int64_t groups = static_cast<int64_t>(scans->S) * nz * nxy * ((nxy + 4 * KXW - 1) / (4 * KXW)); \
+    ScoreLatticePackedKernel<KXW><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>(  \
+        R, cells, scans->N, e, nxy, nz, wxy, wz, 1 << depth, groups, ws->d_lattice.as<int>());            \
+  } while (0)
+      if (nxy <= 8) HG_PACKED(2); else if (nxy <= 20) HG_PACKED(5); else HG_PACKED(8);
+#undef HG_PACKED
+    } else if (L.dense.data != nullptr) {
       constexpr int KX = 4;
       const int64_t groups = static_cast<int64_t>(scans->S) * nz * nxy * ((nxy + KX - 1) / KX);
       ScoreLatticeDenseKernel<KX><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>(
@@ -674,6 +800,26 @@ struct Scorer {
     lattice_candidates = static_cast<int64_t>(n);
     total_scored += static_cast<int64_t>(n);
     ++launches;
+    if (packed && std::getenv("HG_LATTICE_CHECK") != nullptr) {
+      // Development / test aid: the packed kernel against the brick-table kernel, every sum.
+      std::vector<int> got(n), want(n);
+      HG_CUDA(cudaMemcpyAsync(got.data(), ws->d_lattice.p, n * sizeof(int), cudaMemcpyDeviceToHost, stream));
+      DeviceBuffer check;
+      rc = check.Reserve(n * sizeof(int));
+      if (rc != HG_OK) return rc;
+      ScoreLatticeKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
+          L.table, scans->CellsOfDepth(depth), scans->N, ReduceExponent(depth), nxy, nz, wxy, wz, 1 << depth,
+          static_cast<int64_t>(n), check.as<int>());
+      HG_CUDA(cudaMemcpyAsync(want.data(), check.p, n * sizeof(int), cudaMemcpyDeviceToHost, stream));
+      HG_CUDA(cudaStreamSynchronize(stream));
+      for (size_t i = 0; i < n; ++i) {
+        if (got[i] != want[i]) {
+          SetError("HG_LATTICE_CHECK: packed lattice sum " + std::to_string(i) + " is " + std::to_string(got[i]) +
+                   ", the brick-table kernel gives " + std::to_string(want[i]));
+          return HG_ERR_CUDA;
+        }
+      }
+    }
     return HG_OK;
   }
   // All lattice sums to the host (strict order needs every one).
@@ -1380,12 +1526,41 @@ int hg_fcsm_create(const hg_grid* grid, const hg_grid* low_resolution_grid,
     m->histogram.assign(rotational_scan_matcher_histogram, rotational_scan_matcher_histogram + histogram_size);
   const int rc = hg_stack_build(grid, options->branch_and_bound_depth, options->full_resolution_depth, &m->stack);
   if (rc != HG_OK) return rc;
+  // Residue rows of the lowest-resolution level for the lattice kernel.
+  const int depth = static_cast<int>(m->stack->levels.size()) - 1;
+  const hg_stack_level& L = m->stack->levels[depth];
+  if (depth >= 1 && L.dense.data != nullptr) {
+    const int e = std::max(0, depth - options->full_resolution_depth + 1);
+    LatticeRows& R = m->lattice_rows;
+    R.cs_log2 = depth - e;
+    for (int k = 0; k < 3; ++k) {
+      R.min[k] = L.dense.min[k];
+      R.dim[k] = L.dense.dim[k];
+    }
+    R.payload = (R.dim[0] + (1 << R.cs_log2) - 1) >> R.cs_log2;
+    R.row_words = (kLatticePadLeft + R.payload + kLatticePadRight + 3) / 4;
+    const int64_t total = static_cast<int64_t>(R.dim[2]) * R.dim[1] * (int64_t(1) << R.cs_log2) * R.row_words * 4;
+    if (total <= (int64_t(256) << 20)) {
+      if (cudaMalloc(&m->d_lattice_rows, static_cast<size_t>(total)) != cudaSuccess) {
+        cudaGetLastError();  // optional copy: the brick / dense kernels still work
+        m->d_lattice_rows = nullptr;
+      } else {
+        BuildLatticeRowsKernel<<<static_cast<unsigned>((total + 255) / 256), 256>>>(
+            L.dense, R, total, static_cast<unsigned char*>(m->d_lattice_rows));
+        CountLaunch();
+        HG_CUDA(cudaGetLastError());
+        HG_CUDA(cudaDeviceSynchronize());
+        R.data = static_cast<const unsigned*>(m->d_lattice_rows);
+      }
+    }
+  }
   *out = m.release();
   return HG_OK;
 }
 
 void hg_fcsm_destroy(hg_fcsm* m) {
   if (m == nullptr) return;
+  if (m->d_lattice_rows) cudaFree(m->d_lattice_rows);
   hg_stack_destroy(m->stack);
   delete m;
 }

@@ -832,3 +832,35 @@ def test_device_scan_match_equals_host_loop(oracle, hg, world):
     many = [cloud[k::9] for k in range(5)]
     pose, _ = hg.scan_match(many, [world["g_tsdf_hi"]] * 5, [1.0] * 5, 10.0, 1.0, world["truth"])
     assert np.isfinite(pose).all()
+
+
+@pytest.mark.parametrize("depth,frd,window", [(7, 3, 5.0), (6, 3, 3.0), (5, 5, 2.0), (8, 2, 7.0), (4, 1, 1.5)])
+def test_packed_lattice_kernel_equals_brick_kernel(oracle, hg, world, depth, frd, window):
+    """The lowest-resolution lattice is scored from a residue-row copy of the level with packed 16-bit
+    sums (ScoreLatticePackedKernel). HG_LATTICE_CHECK=1 makes every search recompute the lattice with
+    the plain brick-table kernel and compare all sums; the searches must also return the oracle's
+    candidate. Shapes: half-resolution levels (cell stride 2^(frd-1)), full-resolution only (stride
+    2^(depth-1)), lattice rows of 5 ... 33+ candidates."""
+    import os
+    hi, lo, hist = node_inputs(world)
+    hi = hi[:300]
+    opts = dict(branch_and_bound_depth=depth, full_resolution_depth=frd, use_rotational_scan_matcher=False,
+                min_low_resolution_score=0.3, linear_xy_search_window=window, linear_z_search_window=0.6,
+                angular_search_window=0.06)
+    om = oracle.Fcsm(world["o_tsdf_hi"], world["o_tsdf_lo"], hist, **opts)
+    gm = hg.Fcsm(world["g_tsdf_hi"], world["g_tsdf_lo"], hist, **opts)
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    rng = np.random.RandomState(depth * 10 + frd)
+    os.environ["HG_LATTICE_CHECK"] = "1"
+    try:
+        for trial in range(2):
+            node = perturbed(world["truth"], rng, 0.8, 0.04)
+            r1 = gm.match(node, submap, hi, lo, hist, min_score=0.25)
+            r0 = om.match(node, submap, hi, lo, hist, min_score=0.25)
+            assert_same_match(r0, r1)
+        if depth == 7:
+            r1 = gm.match(world["truth"], submap, hi[:150], lo, hist, min_score=0.4, full=True)
+            r0 = om.match(world["truth"], submap, hi[:150], lo, hist, min_score=0.4, full=True)
+            assert_same_match(r0, r1)
+    finally:
+        os.environ.pop("HG_LATTICE_CHECK", None)
