@@ -294,9 +294,11 @@ def correlative_bench(hg, torch, w, rank, world, dist):
         "lowest_resolution_kernel": {"candidates": lattice_n, "ms": lattice_ms, "candidates_per_s": lattice_cps},
         "roofline": {"bound": "hbm", "achieved": lattice_cps * (n_pts + 24) / world / 1e9, "peak": peak,
                      "unit": "GB/s", "frac": lattice_cps * (n_pts + 24) / world / 1e9 / peak,
-                     "traffic": measured_traffic("ScoreLatticeDenseKernel<4>") if world == 1 else None,
-                     "kernel": "ScoreLatticeDenseKernel<4>", "algorithmic_bytes_per_candidate": n_pts + 24,
-                     "note": "per GPU; gathers are served by L1/L2 (the level-6 grid is a few hundred KB)"},
+                     "traffic": measured_traffic("ScoreLatticePackedKernel<5>") if world == 1 else None,
+                     "kernel": "ScoreLatticePackedKernel<5>", "algorithmic_bytes_per_candidate": n_pts + 24,
+                     "note": "per GPU. SURVEY 8(d) counts one byte per (candidate, point) gather against the HBM "
+                             "peak; the level-6 grid is a few hundred KB and is served by L1, so the fraction "
+                             "can exceed 1 - DRAM traffic per launch is in 'traffic'"},
         "cpu_baseline": {"value": cpu_rate, "unit": "candidates/s", "cores": cpu_threads, "kind": "port",
                          "sample": cpu_desc},
     }
@@ -418,7 +420,8 @@ def constraint_bench(hg, torch, w, rank, world, dist, num_submaps=8, nodes_per_s
            "ms_per_pair_per_gpu": 1e3 * float(dt.item()) * world / max(n_jobs, 1),
            "constraints_found": int(stats[0].item()), "candidates_scored": float(stats[1].item()),
            "candidates_per_s": float(stats[1].item()) / float(dt.item()),
-           "pairs_in_flight_per_gpu": int(os.environ.get("HG_CONSTRAINT_THREADS", "8"))}
+           "pairs_in_flight_per_gpu": int(os.environ.get(
+               "HG_CONSTRAINT_THREADS", max(4, min(16, (os.cpu_count() or 8) // max(1, world)))))}
     if cpu:
         try:
             rate, threads, desc = cpu_baseline_pairs(synth, sph, num_submaps)

@@ -9,6 +9,7 @@
 // The thread-pool / task bookkeeping of the reference (:77-190, :297-337) is
 // control plane and stays with the caller; this entry point is the per-pair
 // compute, partitioned across GPUs by job index (one process per GPU).
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -27,7 +28,8 @@ namespace {
 // flight (each search on its own non-blocking stream with its own thread-local scratch,
 // see fcsm.cu) fill it. The workers live as long as the process so that their scratch
 // (pinned buffers in particular) is allocated once. HG_CONSTRAINT_THREADS sets the number
-// of pairs in flight (default 8, 1 = compute on the calling thread).
+// of pairs in flight (default: host cores per rank, clamped to 4..16; 1 = compute on the
+// calling thread).
 class WorkerPool {
  public:
   static WorkerPool& Get() {
@@ -63,7 +65,13 @@ class WorkerPool {
 
  private:
   WorkerPool() {
-    int n = 8;
+    // Default: the host cores this process can count on (one process per GPU: the cores are
+    // shared by LOCAL_WORLD_SIZE ranks), between 4 and 16 — the workers mostly wait on their
+    // streams, and 16 in flight is where a B200 stops gaining on the C5 workload.
+    int ranks = 1;
+    if (const char* env = std::getenv("LOCAL_WORLD_SIZE")) ranks = std::max(1, std::atoi(env));
+    int n = static_cast<int>(std::thread::hardware_concurrency()) / ranks;
+    n = n < 4 ? 4 : (n > 16 ? 16 : n);
     if (const char* env = std::getenv("HG_CONSTRAINT_THREADS")) n = std::atoi(env);
     n = n < 1 ? 1 : (n > 64 ? 64 : n);
     for (int i = 0; i < n; ++i) {

@@ -61,7 +61,7 @@ __device__ void QuatProduct(const double* z, const double* w, double* zw) {
 }
 
 // Lower Cholesky of the n x n matrix A (row-major, n <= 6), then A x = b.
-__device__ bool CholeskySolve(double* A, const double* b, const int n, double* x) {
+__device__ bool CholeskySolve(double* A, const double* b, const int n, double* y, double* x) {
   for (int j = 0; j < n; ++j) {
     double d = A[j * n + j];
     for (int k = 0; k < j; ++k) d -= A[j * n + k] * A[j * n + k];
@@ -74,7 +74,6 @@ __device__ bool CholeskySolve(double* A, const double* b, const int n, double* x
       A[i * n + j] = s / l;
     }
   }
-  double y[6];
   for (int i = 0; i < n; ++i) {
     double s = b[i];
     for (int k = 0; k < i; ++k) s -= A[i * n + k] * y[k];
@@ -104,78 +103,102 @@ struct LmState {
   int done;
 };
 
-// From the summed terms at pose x: cost, H = J'J and g = J'r in tangent coordinates.
+// Shared scratch of one evaluation: ambient normal equations, tangent basis, projected system.
+struct EvalShared {
+  double JtJ[49], Jtr[7], P[42], H[36], g[6], A[36], y[6];
+  double M[12];  // rotation-delta Jacobian / s (constant over the solve)
+  double cost;
+};
+
+// ceres::QuaternionParameterization::ComputeJacobian as (sign, component of q) per entry.
+__constant__ signed char kPlusSign[12] = {-1, -1, -1, 1, 1, -1, -1, 1, 1, 1, -1, 1};
+__constant__ signed char kPlusIndex[12] = {1, 2, 3, 0, 3, 2, 3, 0, 1, 2, 1, 0};
+// Yaw-only plus (rotation_parameterization.h:27-39): d/dc of (sqrt(1 - c^2), 0, 0, c) * q at 0.
+__constant__ signed char kYawSign[4] = {-1, -1, 1, 1};
+__constant__ signed char kYawIndex[4] = {3, 2, 1, 0};
+
+// From the summed terms S at pose x: cost, H = J'J and g = J'r in tangent coordinates, computed
+// by the first ~110 threads of the CTA (one matrix entry each) instead of one thread's loops.
+// Contains two __syncthreads(): every thread of the CTA must call it.
 __device__ void AssembleNormal(const ScanMatchArgs& a, const double* S, const double* x, const int n,
-                               double* cost, double* H, double* g) {
-  double JtJ[49], Jtr[7];
-  int e = 0;
-  for (int i = 0; i < 7; ++i)
-    for (int j = i; j < 7; ++j, ++e) JtJ[i * 7 + j] = JtJ[j * 7 + i] = S[e];
-  for (int i = 0; i < 7; ++i) Jtr[i] = S[28 + i];
-  double c = 0.5 * S[35];
-  // translation_delta_cost_functor_3d.h:31-45: r = s (t - target), J = s I.
-  {
-    const double s = a.translation_weight;
+                               const int tid, EvalShared* ev) {
+  // rotation_delta_cost_functor_3d.h:35-54: r = s imag(target^-1 q) = s M q, J = s M (3 x 4).
+  const double* M = ev->M;
+  const double st = a.translation_weight, sr = a.rotation_weight;
+  if (tid < 49) {
+    const int i = tid / 7, j = tid - 7 * i;
+    const int lo = i < j ? i : j, hi = i < j ? j : i;
+    double v = S[lo * 7 - lo * (lo - 1) / 2 + (hi - lo)];
+    if (i < 3 && i == j) v += st * st;  // translation_delta_cost_functor_3d.h:31-45: J = s I
+    if (i >= 3 && j >= 3) {
+      double t = 0.0;
+      for (int k = 0; k < 3; ++k) t += (sr * M[k * 4 + i - 3]) * (sr * M[k * 4 + j - 3]);
+      v += t;
+    }
+    ev->JtJ[tid] = v;
+  } else if (tid < 56) {
+    const int i = tid - 49;
+    double v = S[28 + i];
+    if (i < 3) {
+      v += st * (st * (x[i] - a.target_t[i]));
+    } else {
+      double jr = 0.0;
+      for (int k = 0; k < 3; ++k) {
+        const double r = sr * (M[k * 4] * x[3] + M[k * 4 + 1] * x[4] + M[k * 4 + 2] * x[5] + M[k * 4 + 3] * x[6]);
+        jr += (sr * M[k * 4 + i - 3]) * r;
+      }
+      v += jr;
+    }
+    ev->Jtr[i] = v;
+  } else if (tid == 56) {
+    double c = 0.5 * S[35];
     double rr = 0.0;
     for (int k = 0; k < 3; ++k) {
-      const double r = s * (x[k] - a.target_t[k]);
-      JtJ[k * 7 + k] += s * s;
-      Jtr[k] += s * r;
+      const double r = st * (x[k] - a.target_t[k]);
       rr += r * r;
     }
     c += 0.5 * rr;
-  }
-  // rotation_delta_cost_functor_3d.h:35-54: r = s imag(target^-1 q), linear in q.
-  {
-    const double s = a.rotation_weight;
-    const double z[4] = {a.target_q[0], -a.target_q[1], -a.target_q[2], -a.target_q[3]};
-    const double* w = x + 3;
-    const double M[12] = {z[1], z[0], -z[3], z[2], z[2], z[3], z[0], -z[1], z[3], -z[2], z[1], z[0]};
-    double r[3];
-    r[0] = s * (z[0] * w[1] + z[1] * w[0] + z[2] * w[3] - z[3] * w[2]);
-    r[1] = s * (z[0] * w[2] - z[1] * w[3] + z[2] * w[0] + z[3] * w[1]);
-    r[2] = s * (z[0] * w[3] + z[1] * w[2] - z[2] * w[1] + z[3] * w[0]);
-    for (int p = 0; p < 4; ++p) {
-      double jr = 0.0;
-      for (int k = 0; k < 3; ++k) jr += (s * M[k * 4 + p]) * r[k];
-      Jtr[3 + p] += jr;
-      for (int q = 0; q < 4; ++q) {
-        double t = 0.0;
-        for (int k = 0; k < 3; ++k) t += (s * M[k * 4 + p]) * (s * M[k * 4 + q]);
-        JtJ[(3 + p) * 7 + 3 + q] += t;
+    rr = 0.0;
+    for (int k = 0; k < 3; ++k) {
+      const double r = sr * (M[k * 4] * x[3] + M[k * 4 + 1] * x[4] + M[k * 4 + 2] * x[5] + M[k * 4 + 3] * x[6]);
+      rr += r * r;
+    }
+    ev->cost = c + 0.5 * rr;
+  } else if (tid >= 64 && tid < 64 + 7 * n) {
+    // Tangent basis P (7 x n): identity for t; ceres::QuaternionParameterization::ComputeJacobian
+    // or the yaw-only plus (rotation_parameterization.h:27-39) for q.
+    const int e = tid - 64, i = e / n, l = e - i * n;
+    const double* q = x + 3;
+    double v = 0.0;
+    if (i < 3) {
+      v = (l == i) ? 1.0 : 0.0;
+    } else if (l >= 3) {
+      if (n == 6) {
+        const int k = (i - 3) * 3 + (l - 3);
+        v = kPlusSign[k] * q[kPlusIndex[k]];
+      } else {
+        v = kYawSign[i - 3] * q[kYawIndex[i - 3]];
       }
     }
-    c += 0.5 * (r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
+    ev->P[e] = v;
   }
-  *cost = c;
-  // Tangent basis P (7 x n): identity for t; ceres::QuaternionParameterization::ComputeJacobian
-  // or the yaw-only plus (rotation_parameterization.h:27-39) for q.
-  double P[42];
-  for (int i = 0; i < 7 * n; ++i) P[i] = 0.0;
-  for (int k = 0; k < 3; ++k) P[k * n + k] = 1.0;
-  const double* q = x + 3;
-  if (n == 6) {
-    const double Pq[12] = {-q[1], -q[2], -q[3], q[0], q[3], -q[2], -q[3], q[0], q[1], q[2], -q[1], q[0]};
-    for (int r = 0; r < 4; ++r)
-      for (int l = 0; l < 3; ++l) P[(3 + r) * n + 3 + l] = Pq[r * 3 + l];
-  } else {
-    const double Pq[4] = {-q[3], -q[2], q[1], q[0]};
-    for (int r = 0; r < 4; ++r) P[(3 + r) * n + 3] = Pq[r];
-  }
-  for (int la = 0; la < n; ++la) {
-    double s = 0.0;
-    for (int i = 0; i < 7; ++i) s += P[i * n + la] * Jtr[i];
-    g[la] = s;
-    for (int lb = 0; lb < n; ++lb) {
-      double h = 0.0;
-      for (int i = 0; i < 7; ++i) {
-        double t = 0.0;
-        for (int j = 0; j < 7; ++j) t += JtJ[i * 7 + j] * P[j * n + lb];
-        h += P[i * n + la] * t;
-      }
-      H[la * n + lb] = h;
+  __syncthreads();
+  if (tid < n * n) {
+    const int la = tid / n, lb = tid - la * n;
+    double h = 0.0;
+    for (int i = 0; i < 7; ++i) {
+      double t = 0.0;
+      for (int j = 0; j < 7; ++j) t += ev->JtJ[i * 7 + j] * ev->P[j * n + lb];
+      h += ev->P[i * n + la] * t;
     }
+    ev->H[tid] = h;
+  } else if (tid >= 64 && tid < 64 + n) {
+    const int la = tid - 64;
+    double g = 0.0;
+    for (int i = 0; i < 7; ++i) g += ev->P[i * n + la] * ev->Jtr[i];
+    ev->g[la] = g;
   }
+  __syncthreads();
 }
 
 __device__ void ApplyScaling(LmState* s) {
@@ -217,17 +240,17 @@ __device__ void ApplyDelta(LmState* s, const int yaw_only) {
 
 // Computes steps until one needs an evaluation (returns with the candidate in s->x) or the
 // solve ends (s->done). DenseLmProblem::Solve, the part of the loop before the evaluation.
-__device__ void NextCandidate(LmState* s, const ScanMatchArgs& a) {
+__device__ void NextCandidate(LmState* s, const ScanMatchArgs& a, EvalShared* ev) {
   const int n = s->n;
+  double* A = ev->A;
   while (s->iterations < a.max_num_iterations) {
     ++s->iterations;
-    double A[36];
     for (int i = 0; i < n * n; ++i) A[i] = s->Hs[i];
     for (int i = 0; i < n; ++i) {
       const double d = fmin(fmax(s->Hs[i * n + i], kMinLmDiagonal), kMaxLmDiagonal);
       A[i * n + i] += d / s->radius;
     }
-    bool step_ok = CholeskySolve(A, s->gs, n, s->delta);
+    bool step_ok = CholeskySolve(A, s->gs, n, ev->y, s->delta);
     if (step_ok) {
       for (int i = 0; i < n; ++i) s->delta[i] = -s->delta[i];
       double gd = 0.0, dJd = 0.0;
@@ -263,10 +286,12 @@ __device__ void NextCandidate(LmState* s, const ScanMatchArgs& a) {
 }
 
 // The evaluation at s->x has been summed into S. DenseLmProblem::Solve, the part after it.
-__device__ void Advance(LmState* s, const ScanMatchArgs& a, const double* S) {
+__device__ void Advance(LmState* s, const ScanMatchArgs& a, EvalShared* ev) {
   const int n = s->n;
   if (s->phase == 0) {
-    AssembleNormal(a, S, s->x, n, &s->cost, s->H, s->g);
+    s->cost = ev->cost;
+    for (int i = 0; i < n * n; ++i) s->H[i] = ev->H[i];
+    for (int i = 0; i < n; ++i) s->g[i] = ev->g[i];
     ++s->cost_evaluations;
     ++s->jacobian_evaluations;
     s->initial_cost = s->cost;
@@ -285,13 +310,14 @@ __device__ void Advance(LmState* s, const ScanMatchArgs& a, const double* S) {
     s->accumulated_candidate_model_cost_change = 0.0;
     s->num_consecutive_nonmonotonic_steps = 0;
     for (int k = 0; k < 7; ++k) s->x_min[k] = s->x[k];
-    NextCandidate(s, a);
+    NextCandidate(s, a, ev);
     return;
   }
   // Candidate evaluated: its normal equations are only used if the step is accepted (the
   // host loop re-evaluates at the accepted point, which gives these same numbers).
-  double new_cost, Hn[36], gn[6];
-  AssembleNormal(a, S, s->x, n, &new_cost, Hn, gn);
+  double new_cost = ev->cost;
+  const double* Hn = ev->H;
+  const double* gn = ev->g;
   ++s->cost_evaluations;
   const bool eval_ok = isfinite(new_cost);
   if (!eval_ok) new_cost = 1.7976931348623157e308;
@@ -367,13 +393,14 @@ __device__ void Advance(LmState* s, const ScanMatchArgs& a, const double* S) {
       return;
     }
   }
-  NextCandidate(s, a);
+  NextCandidate(s, a, ev);
 }
 
 __global__ void __launch_bounds__(kLmThreads, 1) ScanMatchKernel(const ScanMatchArgs a) {
   __shared__ LmState st;
   __shared__ double warp_sums[kLmWarps][kTerms];
   __shared__ double totals[kTerms];
+  __shared__ EvalShared ev;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
     for (int k = 0; k < 7; ++k) st.x[k] = a.pose[k];
@@ -382,6 +409,10 @@ __global__ void __launch_bounds__(kLmThreads, 1) ScanMatchKernel(const ScanMatch
     st.done = 0;
     st.termination = 0;
     st.iterations = st.successful_steps = st.cost_evaluations = st.jacobian_evaluations = 0;
+    const double z0 = a.target_q[0], z1 = -a.target_q[1], z2 = -a.target_q[2], z3 = -a.target_q[3];
+    ev.M[0] = z1; ev.M[1] = z0; ev.M[2] = -z3; ev.M[3] = z2;
+    ev.M[4] = z2; ev.M[5] = z3; ev.M[6] = z0; ev.M[7] = -z1;
+    ev.M[8] = z3; ev.M[9] = -z2; ev.M[10] = z1; ev.M[11] = z0;
   }
   __syncthreads();
   for (;;) {
@@ -442,7 +473,8 @@ __global__ void __launch_bounds__(kLmThreads, 1) ScanMatchKernel(const ScanMatch
       totals[tid] = s;
     }
     __syncthreads();
-    if (tid == 0) Advance(&st, a, totals);
+    AssembleNormal(a, totals, st.x, st.n, tid, &ev);
+    if (tid == 0) Advance(&st, a, &ev);
     __syncthreads();
     if (st.done) break;
   }
