@@ -864,3 +864,29 @@ def test_packed_lattice_kernel_equals_brick_kernel(oracle, hg, world, depth, frd
             assert_same_match(r0, r1)
     finally:
         os.environ.pop("HG_LATTICE_CHECK", None)
+
+
+def test_packed_lattice_kernel_many_points(oracle, hg, world):
+    """More than 8192 points per scan: a lane of the packed lattice kernel adds more than 256 voxels
+    per candidate, so its 16-bit partial sums are flushed to 32 bits between chunks."""
+    import os
+    hi, lo, hist = node_inputs(world)
+    rng = np.random.RandomState(4)
+    big = np.concatenate([hi + rng.normal(0, 0.01, hi.shape).astype(np.float32) for _ in range(16)])[:9500]
+    assert len(big) > 8192 + 1000
+    # depth 5: lattice step 16 cells, 7 candidates per lattice row
+    opts = dict(branch_and_bound_depth=5, full_resolution_depth=3, use_rotational_scan_matcher=False,
+                min_low_resolution_score=0.3, linear_xy_search_window=5.0, linear_z_search_window=0.6,
+                angular_search_window=0.02)
+    om = oracle.Fcsm(world["o_tsdf_hi"], world["o_tsdf_lo"], hist, **opts)
+    gm = hg.Fcsm(world["g_tsdf_hi"], world["g_tsdf_lo"], hist, **opts)
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    node = world["truth"] + np.array([0.3, -0.2, 0.05, 0, 0, 0, 0])
+    os.environ["HG_LATTICE_CHECK"] = "1"
+    try:
+        r1 = gm.match(node, submap, big, lo, hist, min_score=0.1)
+    finally:
+        os.environ.pop("HG_LATTICE_CHECK", None)
+    r0 = om.match(node, submap, big, lo, hist, min_score=0.1)
+    assert_same_match(r0, r1)
+    assert r1["found"] == 1.0 and r1["num_scored"] > 49
