@@ -890,3 +890,34 @@ def test_packed_lattice_kernel_many_points(oracle, hg, world):
     r0 = om.match(node, submap, big, lo, hist, min_score=0.1)
     assert_same_match(r0, r1)
     assert r1["found"] == 1.0 and r1["num_scored"] > 49
+
+
+def test_handles_are_usable_from_several_host_threads(oracle, hg, world):
+    """include/hg_b200.h: handles may be used from several host threads for evaluate / match calls
+    (the reference's matcher is const-callable from pool threads, fast_correlative_scan_matcher_3d.h:75-100).
+    Eight threads share one matcher, one cost function and one grid; every result equals the serial one."""
+    from concurrent.futures import ThreadPoolExecutor
+    om, gm, hi, lo, hist = world_matchers(oracle, hg, world, "tsdf")
+    rng = np.random.RandomState(77)
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    nodes = [perturbed(world["truth"], rng, 1.0, 0.06) for _ in range(16)]
+    cost = hg.Cost("tsdf", 0.05, world["cloud"], [world["g_tsdf_hi"]])
+    poses = [perturbed(world["truth"], rng) for _ in range(16)]
+    serial_match = [gm.match(n, submap, hi, lo, hist, min_score=0.2) for n in nodes]
+    serial_eval = [cost.evaluate(p) for p in poses]
+    serial_refine = [hg.scan_match([world["cloud"]], [world["g_tsdf_hi"]], [5.0], 10.0, 1.0, p)[0] for p in poses]
+
+    def work(i):
+        m = gm.match(nodes[i], submap, hi, lo, hist, min_score=0.2)
+        r, J = cost.evaluate(poses[i])
+        pose = hg.scan_match([world["cloud"]], [world["g_tsdf_hi"]], [5.0], 10.0, 1.0, poses[i])[0]
+        return m, r, J, pose
+
+    with ThreadPoolExecutor(8) as ex:
+        for rounds in range(3):
+            out = list(ex.map(work, range(16)))
+            for i, (m, r, J, pose) in enumerate(out):
+                assert_same_match(serial_match[i], m)
+                assert (r == serial_eval[i][0]).all()
+                assert all((a == b).all() for a, b in zip(J, serial_eval[i][1]))
+                assert (pose == serial_refine[i]).all()
