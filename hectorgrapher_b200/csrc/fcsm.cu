@@ -760,10 +760,15 @@ struct Scorer {
     int rc = ws->d_lattice.Reserve(n * sizeof(int));
     if (rc != HG_OK) return rc;
     const int64_t threads = static_cast<int64_t>(n) * 32;
+    // The kernel time is reported for full-submap searches (bench.py's roofline); a local search
+    // is a few microseconds of kernel and skips the event calls.
+    const bool timed = n >= (size_t(1) << 20);
     cudaEvent_t e0 = nullptr, e1 = nullptr;
-    HG_CUDA(cudaEventCreate(&e0));
-    HG_CUDA(cudaEventCreate(&e1));
-    HG_CUDA(cudaEventRecord(e0, stream));
+    if (timed) {
+      HG_CUDA(cudaEventCreate(&e0));
+      HG_CUDA(cudaEventCreate(&e1));
+      HG_CUDA(cudaEventRecord(e0, stream));
+    }
     const hg_stack_level& L = m->stack->levels[depth];
     const LatticeRows& R = m->lattice_rows;
     const bool packed = R.data != nullptr && depth == static_cast<int>(m->stack->levels.size()) - 1 && nxy >= 5 &&
@@ -792,11 +797,13 @@ struct Scorer {
     }
     CountLaunch();
     HG_CUDA(cudaGetLastError());
-    HG_CUDA(cudaEventRecord(e1, stream));
-    HG_CUDA(cudaEventSynchronize(e1));
-    HG_CUDA(cudaEventElapsedTime(&lattice_ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
+    if (timed) {
+      HG_CUDA(cudaEventRecord(e1, stream));
+      HG_CUDA(cudaEventSynchronize(e1));
+      HG_CUDA(cudaEventElapsedTime(&lattice_ms, e0, e1));
+      cudaEventDestroy(e0);
+      cudaEventDestroy(e1);
+    }
     lattice_candidates = static_cast<int64_t>(n);
     total_scored += static_cast<int64_t>(n);
     ++launches;
@@ -1017,6 +1024,7 @@ class BranchAndBoundSearch {
   // generation order. strict: all of them. Otherwise only those the reference's
   // loop can reach (score > min_score, :437-440), compacted on the device.
   // 'only' restricts the list to the given generation indices.
+  static constexpr size_t kSmallLattice = 1 << 16;
   int CollectKeys(int max_depth, float min_score, bool strict, const std::vector<int>* only,
                   std::vector<Key>* keys) {
     PhaseTimer pt;
@@ -1045,6 +1053,18 @@ class BranchAndBoundSearch {
       } else {
         keys->reserve(n);
         for (size_t i = 0; i < n; ++i) keys->push_back(Key{ScoreFromSum(sums[i], scans_->N), static_cast<uint32_t>(i)});
+      }
+    } else if (n <= kSmallLattice) {
+      // A local search: a few thousand sums. One copy and a host filter cost less than the three
+      // compaction kernels and their two synchronisations.
+      if (h_lattice_sums_.size() != n) {
+        const int rc = scorer_.DownloadLattice(n, &h_lattice_sums_);
+        if (rc != HG_OK) return rc;
+      }
+      const int threshold = SmallestSumBeating(min_score);
+      for (size_t i = 0; i < n; ++i) {
+        if (h_lattice_sums_[i] >= threshold)
+          keys->push_back(Key{ScoreFromSum(h_lattice_sums_[i], scans_->N), static_cast<uint32_t>(i)});
       }
     } else {
       std::vector<int2> kept;
