@@ -215,3 +215,35 @@ def test_occupancy_insertion_matches_oracle(oracle, hg, free):
     # bad options are rejected like CreateProbabilityGridRangeDataInserterOptions3D's CHECKs
     with pytest.raises(hg.HgError):
         g.insert_occupancy(origin, pts, 0.45, 0.49, free)
+
+
+def test_insertion_with_hash_indexed_bricks(oracle, hg):
+    """Returns 700 m apart: the brick bounding box is far too large for a dense index, so the grid
+    switches to the open-addressing brick hash (hg_internal.cuh) while it is being written."""
+    res = 0.10
+    g = hg.Grid.tsdf(res, 2.5, 1000.0, np.zeros((0, 3), np.int32), [], [])
+    o = oracle.Grid.tsdf(res, 2.5, 1000.0)
+    origin = np.array([0.0, 0.0, 0.0], np.float32)
+    rng = np.random.RandomState(8)
+    near = rng.uniform(-3, 3, (200, 3)).astype(np.float32)
+    for pts in (near, np.array([[700.0, 10.0, -3.0], [-690.0, -700.0, 5.0]], np.float32), near + np.float32(0.05)):
+        g.insert_tsdf(origin, pts)
+        o.insert_tsdf(origin, pts)
+        assert_same_grid(g, o)
+    assert g.grid_size == 16384
+    xyz = g.export()[0]
+    assert (g.lookup("tsd", xyz) == o.lookup("tsd", xyz)).all()
+    # the cost function reads the same grid through the hash
+    cloud = near[:64]
+    pose = np.array([0.01, -0.02, 0.005, 1, 0, 0, 0], float)
+    gr, gJ = hg.Cost("tsdf", 0.1, cloud, [g]).evaluate(pose)
+    orr, oJ = oracle.Cost("tsdf", 0.1, cloud, [o]).evaluate(pose)
+    assert np.allclose(gr, orr, rtol=1e-5, atol=1e-9)
+    assert all(np.allclose(a, b, rtol=1e-5, atol=1e-9) for a, b in zip(gJ, oJ))
+    # occupancy grid likewise
+    gp = hg.Grid.prob(res, np.zeros((0, 3), np.int32), [])
+    op = oracle.Grid.prob(res)
+    for pts in (near, np.array([[700.0, 10.0, -3.0], [-690.0, -700.0, 5.0]], np.float32)):
+        gp.insert_occupancy(origin, pts, 0.55, 0.49, 2)
+        op.insert_occupancy(origin, pts, 0.55, 0.49, 2)
+        assert_same_grid(gp, op)
