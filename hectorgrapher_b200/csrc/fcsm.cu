@@ -426,6 +426,23 @@ __global__ void __launch_bounds__(256) WriteKeptKernel(const int* __restrict__ s
   }
 }
 
+// Histogram of the lattice sums >= tmin in kHistogramBins bins of width 1 << shift.
+constexpr int kHistogramBins = 2048;
+__global__ void __launch_bounds__(256) HistogramKernel(const int* __restrict__ sums, const int64_t n, const int tmin,
+                                                       const int shift, int* __restrict__ bins) {
+  __shared__ int local[kHistogramBins];
+  for (int k = threadIdx.x; k < kHistogramBins; k += 256) local[k] = 0;
+  __syncthreads();
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int v = sums[i];
+    if (v >= tmin) atomicAdd(&local[min(kHistogramBins - 1, (v - tmin) >> shift)], 1);
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < kHistogramBins; k += 256)
+    if (local[k] != 0) atomicAdd(&bins[k], local[k]);
+}
+
 // LowResolutionMatcher closure: one thread per pose; the float accumulation is
 // sequential over the points in cloud order, exactly like the reference loop.
 __global__ void __launch_bounds__(128) LowResolutionKernel(const GridDev g, const float* __restrict__ points,
@@ -837,6 +854,56 @@ struct Scorer {
     HG_CUDA(cudaStreamSynchronize(stream));
     return HG_OK;
   }
+  // Number of lattice candidates with sum >= threshold.
+  int CountKept(size_t n, int threshold, int* count) {
+    *count = 0;
+    if (n == 0) return HG_OK;
+    const int chunks = static_cast<int>((n + kChunk - 1) / kChunk);
+    int rc = ws->d_chunks.Reserve((chunks + 1) * sizeof(int));
+    if (rc != HG_OK) return rc;
+    rc = ws->h_count.Reserve(sizeof(int));
+    if (rc != HG_OK) return rc;
+    CountKeptKernel<<<chunks, 256, 0, stream>>>(ws->d_lattice.as<int>(), static_cast<int64_t>(n), threshold,
+                                                ws->d_chunks.as<int>());
+    ScanChunksKernel<<<1, 1024, 0, stream>>>(ws->d_chunks.as<int>(), chunks);
+    CountLaunch(2);
+    HG_CUDA(cudaGetLastError());
+    HG_CUDA(cudaMemcpyAsync(ws->h_count.p, ws->d_chunks.as<int>() + chunks, sizeof(int), cudaMemcpyDeviceToHost,
+                            stream));
+    HG_CUDA(cudaStreamSynchronize(stream));
+    *count = *ws->h_count.as<int>();
+    return HG_OK;
+  }
+  // A threshold T >= tmin such that at least 'want' lattice candidates have sum >= T (as large as
+  // a 2048-bin histogram of the sums can tell), or tmin if fewer than 'want' reach tmin.
+  int TopThreshold(size_t n, int tmin, int want, int* threshold) {
+    *threshold = tmin;
+    const int64_t range = static_cast<int64_t>(255) * scans->N - tmin + 1;
+    if (range <= 0 || n == 0) return HG_OK;
+    int shift = 0;
+    while ((range >> shift) > kHistogramBins) ++shift;
+    int rc = ws->d_sums.Reserve(kHistogramBins * sizeof(int));
+    if (rc != HG_OK) return rc;
+    rc = ws->h_sums.Reserve(kHistogramBins * sizeof(int));
+    if (rc != HG_OK) return rc;
+    HG_CUDA(cudaMemsetAsync(ws->d_sums.p, 0, kHistogramBins * sizeof(int), stream));
+    HistogramKernel<<<592, 256, 0, stream>>>(ws->d_lattice.as<int>(), static_cast<int64_t>(n), tmin, shift,
+                                             ws->d_sums.as<int>());
+    CountLaunch();
+    HG_CUDA(cudaGetLastError());
+    HG_CUDA(cudaMemcpyAsync(ws->h_sums.p, ws->d_sums.p, kHistogramBins * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    HG_CUDA(cudaStreamSynchronize(stream));
+    const int* bins = ws->h_sums.as<int>();
+    int64_t above = 0;
+    for (int b = kHistogramBins - 1; b >= 0; --b) {
+      above += bins[b];
+      if (above >= want) {
+        *threshold = tmin + (b << shift);
+        return HG_OK;
+      }
+    }
+    return HG_OK;
+  }
   // (generation index, sum) of the lattice candidates with sum >= threshold, in generation order.
   int DownloadKept(size_t n, int threshold, std::vector<int2>* out) {
     out->clear();
@@ -917,9 +984,10 @@ class BranchAndBoundSearch {
     int rc = UploadLowResolutionCloud();
     if (rc != HG_OK) return rc;
     std::vector<Key> keys;
+    allow_partial_keys_ = !strict && max_depth >= 1;
     rc = CollectKeys(max_depth, min_score, strict, nullptr, &keys);
+    allow_partial_keys_ = false;
     if (rc != HG_OK) return rc;
-    constexpr size_t kDiveWidth = 4096;
     float dive_bound = -std::numeric_limits<float>::infinity();
     if (!strict && max_depth >= 1 && keys.size() >= 16) {
       const size_t width = std::min(kDiveWidth, keys.size());
@@ -933,10 +1001,18 @@ class BranchAndBoundSearch {
       if (dive_bound > min_score) {
         global_bound_ = dive_bound;
         wave_budget_ = 4096;  // the bound keeps the waves small: expand everything that survives it at once
-        size_t kept = 0;
-        for (const Key& k : keys)
-          if (k.score >= dive_bound) keys[kept++] = k;
-        keys.resize(kept);
+        if (partial_keys_) {
+          rc = CollectKeysReaching(dive_bound, &keys);  // only the top candidates are here so far
+          if (rc != HG_OK) return rc;
+        } else {
+          size_t kept = 0;
+          for (const Key& k : keys)
+            if (k.score >= dive_bound) keys[kept++] = k;
+          keys.resize(kept);
+        }
+      } else if (partial_keys_) {
+        rc = CollectKeys(max_depth, min_score, false, nullptr, &keys);  // no bound: every candidate > min_score
+        if (rc != HG_OK) return rc;
       }
     }
     BuildTopLevel(&keys, strict);
@@ -1025,6 +1101,9 @@ class BranchAndBoundSearch {
   // loop can reach (score > min_score, :437-440), compacted on the device.
   // 'only' restricts the list to the given generation indices.
   static constexpr size_t kSmallLattice = 1 << 16;
+  static constexpr size_t kDiveWidth = 4096;
+  bool allow_partial_keys_ = false;  // CollectKeys may return only the best candidates ...
+  bool partial_keys_ = false;        // ... and did
   int CollectKeys(int max_depth, float min_score, bool strict, const std::vector<int>* only,
                   std::vector<Key>* keys) {
     PhaseTimer pt;
@@ -1067,8 +1146,24 @@ class BranchAndBoundSearch {
           keys->push_back(Key{ScoreFromSum(h_lattice_sums_[i], scans_->N), static_cast<uint32_t>(i)});
       }
     } else {
+      // A full-submap search keeps hundreds of thousands of candidates above min_score, of which the
+      // greedy dive needs the best few thousand and the search afterwards only those that reach
+      // the dive's bound. When allowed (first call of Run), fetch only the top ones now; Run
+      // fetches the rest by threshold once the bound is known.
+      int threshold = SmallestSumBeating(min_score);
+      partial_keys_ = false;
+      if (allow_partial_keys_) {
+        int total = 0;
+        int rc = scorer_.CountKept(n, threshold, &total);
+        if (rc != HG_OK) return rc;
+        if (static_cast<size_t>(total) > 8 * kDiveWidth) {
+          rc = scorer_.TopThreshold(n, threshold, static_cast<int>(kDiveWidth), &threshold);
+          if (rc != HG_OK) return rc;
+          partial_keys_ = true;
+        }
+      }
       std::vector<int2> kept;
-      const int rc = scorer_.DownloadKept(n, SmallestSumBeating(min_score), &kept);
+      const int rc = scorer_.DownloadKept(n, threshold, &kept);
       if (rc != HG_OK) return rc;
       keys->reserve(kept.size());
       for (const int2& k : kept) keys->push_back(Key{ScoreFromSum(k.y, scans_->N), static_cast<uint32_t>(k.x)});
@@ -1076,6 +1171,23 @@ class BranchAndBoundSearch {
     if (TraceEnabled())
       std::fprintf(stderr, "[hg trace] lowest level: %zu candidates (%zu kept), score+select %.1f ms\n", n,
                    keys->size(), pt.Lap());
+    return HG_OK;
+  }
+
+  // All lattice candidates with score >= bound (sum >= the smallest sum that reaches it).
+  int CollectKeysReaching(float bound, std::vector<Key>* keys) {
+    const size_t n = static_cast<size_t>(scans_->S) * per_scan_;
+    int64_t lo = 0, hi = static_cast<int64_t>(255) * scans_->N + 1;
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) / 2;
+      if (ScoreFromSum(static_cast<int>(mid), scans_->N) >= bound) hi = mid; else lo = mid + 1;
+    }
+    std::vector<int2> kept;
+    const int rc = scorer_.DownloadKept(n, static_cast<int>(lo), &kept);
+    if (rc != HG_OK) return rc;
+    keys->clear();
+    keys->reserve(kept.size());
+    for (const int2& k : kept) keys->push_back(Key{ScoreFromSum(k.y, scans_->N), static_cast<uint32_t>(k.x)});
     return HG_OK;
   }
 
