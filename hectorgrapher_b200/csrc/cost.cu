@@ -141,6 +141,13 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
   }
 
   const int tile_end = min(sb.n, tile.start + a.tile_points);
+  // The point of the NEXT round is loaded while this round's stencil gathers are in flight.
+  // (Not in the normal-equation variant, which has no registers to spare.)
+  float nx = 0.f, ny = 0.f, nz = 0.f;
+  if (!NORMAL_EQ && tile.start + static_cast<int>(threadIdx.x) < tile_end) {
+    const float* pp = a.points + (sb.point_offset + tile.start + threadIdx.x) * a.stride;
+    nx = __ldcs(pp); ny = __ldcs(pp + 1); nz = __ldcs(pp + 2);
+  }
   for (int base = tile.start; base < tile_end; base += kThreads) {
     const int i = base + threadIdx.x;
     const bool active = i < tile_end;
@@ -148,11 +155,17 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
     double J[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) J[c] = 0.0;
+    if (NORMAL_EQ && active) {
+      const float* pp = a.points + (sb.point_offset + i) * a.stride;
+      nx = __ldcs(pp); ny = __ldcs(pp + 1); nz = __ldcs(pp + 2);
+    }
+    const double px = static_cast<double>(nx), py = static_cast<double>(ny), pz = static_cast<double>(nz);
+    if (!NORMAL_EQ && i + kThreads < tile_end) {
+      const float* pp = a.points + (sb.point_offset + i + kThreads) * a.stride;
+      nx = __ldcs(pp); ny = __ldcs(pp + 1); nz = __ldcs(pp + 2);
+    }
     if (active) {
       const long long gi = sb.point_offset + i;
-      const float* pp = a.points + gi * a.stride;
-      const double px = static_cast<double>(__ldcs(pp)), py = static_cast<double>(__ldcs(pp + 1)),
-                   pz = static_cast<double>(__ldcs(pp + 2));
       const double qw = sb.q[0], qx = sb.q[1], qy = sb.q[2], qz = sb.q[3];
       const WorldPoint wp = TransformPoint(qw, qx, qy, qz, sb.t[0], sb.t[1], sb.t[2], px, py, pz);
       const ValueGrad v = Residual<LOOKUP>(a, sb.scale, wp.x, wp.y, wp.z);
