@@ -203,6 +203,32 @@ void orc_insert_tsdf(void* g, const float* origin, int n, const float* pts,
   TsdfInsert(o, Vector3f(origin[0], origin[1], origin[2]), ToCloud(pts, n, 3), h->tsdf.get());
 }
 
+// ---- pose helpers pinned by the reference's own tests -----------------------
+// transform/timestamped_transform.h:39-48; poses are t3 q4 (w, x, y, z).
+void orc_interpolate_transform(const double* start, const double* end, double factor, double* out) {
+  const Rigid3<double> a(Vec3<double>(start[0], start[1], start[2]), Quat<double>(start[3], start[4], start[5], start[6]));
+  const Rigid3<double> b(Vec3<double>(end[0], end[1], end[2]), Quat<double>(end[3], end[4], end[5], end[6]));
+  const Rigid3<double> r = InterpolateTransform(a, b, factor);
+  out[0] = r.translation.x; out[1] = r.translation.y; out[2] = r.translation.z;
+  out[3] = r.rotation.w; out[4] = r.rotation.x; out[5] = r.rotation.y; out[6] = r.rotation.z;
+}
+// rotation_delta_cost_functor_3d.h:35-54: residuals[3] (and the 3 x 4 Jacobian if asked).
+void orc_rotation_delta(double scaling_factor, const double* target_wxyz, const double* rotation_wxyz,
+                        double* residuals, double* jacobian) {
+  RotationDeltaCostFunction f(scaling_factor, target_wxyz);
+  const double* params[1] = {rotation_wxyz};
+  double* jac[1] = {jacobian};
+  f.Evaluate(params, residuals, jacobian ? jac : nullptr);
+}
+// translation_delta_cost_functor_3d.h:31-45
+void orc_translation_delta(double scaling_factor, const double* target, const double* translation,
+                           double* residuals, double* jacobian) {
+  TranslationDeltaCostFunction f(scaling_factor, target);
+  const double* params[1] = {translation};
+  double* jac[1] = {jacobian};
+  f.Evaluate(params, residuals, jacobian ? jac : nullptr);
+}
+
 // ---- interpolators (double path) -------------------------------------------
 void orc_interpolate(void* g, int n, const double* xyz, double* out) {
   auto* h = static_cast<GridHandle*>(g);

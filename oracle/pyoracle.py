@@ -288,6 +288,36 @@ class Cost:
         return lib().orc_cost_time(self.h, parr, repeats, threads)
 
 
+def interpolate_transform(start, end, factor):
+    """transform::InterpolateTransform on (t3, q4 = w, x, y, z) poses."""
+    out = np.zeros(7)
+    f = lib().orc_interpolate_transform
+    f.argtypes = [vp, vp, c_d, vp]
+    f.restype = None
+    f(_p(_f64(start)), _p(_f64(end)), float(factor), _p(out))
+    return out
+
+
+def rotation_delta(scaling_factor, target_wxyz, rotation_wxyz, jacobian=False):
+    r = np.zeros(3)
+    J = np.zeros((3, 4)) if jacobian else None
+    f = lib().orc_rotation_delta
+    f.argtypes = [c_d, vp, vp, vp, vp]
+    f.restype = None
+    f(float(scaling_factor), _p(_f64(target_wxyz)), _p(_f64(rotation_wxyz)), _p(r), _p(J))
+    return (r, J) if jacobian else r
+
+
+def translation_delta(scaling_factor, target, translation, jacobian=False):
+    r = np.zeros(3)
+    J = np.zeros((3, 3)) if jacobian else None
+    f = lib().orc_translation_delta
+    f.argtypes = [c_d, vp, vp, vp, vp]
+    f.restype = None
+    f(float(scaling_factor), _p(_f64(target)), _p(_f64(translation)), _p(r), _p(J))
+    return (r, J) if jacobian else r
+
+
 def scan_match(clouds, grids, weights, translation_weight, rotation_weight, initial_pose,
                target_translation=None, only_optimize_yaw=False, max_num_iterations=10,
                use_nonmonotonic_steps=True):

@@ -30,3 +30,14 @@ def test_adapters_on_gpu():
     out = subprocess.run([BIN], text=True, capture_output=True)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "ADAPTERS OK" in out.stdout
+
+
+def test_host_pose_preparation():
+    """tests/cpp/test_pose_prep.cpp: the product's host-side InterpolateTransform + slerp Jacobians
+    against transform/timestamped_transform_test.cc and central differences (CPU only)."""
+    exe = os.path.join(ROOT, "tests", "cpp", "test_pose_prep.bin")
+    subprocess.check_call(["g++", "-std=c++11", "-O2", "-ffp-contract=off", "-o", exe,
+                           os.path.join(ROOT, "tests", "cpp", "test_pose_prep.cpp")])
+    out = subprocess.run([exe], text=True, capture_output=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "POSE PREP OK" in out.stdout

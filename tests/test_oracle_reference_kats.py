@@ -417,3 +417,62 @@ def test_tsdf_insert_single_ray_properties(oracle):
     g2.insert_tsdf(origin, many, rtd, 1000.0, 0, 0.1, 4.0, insertion_ratio=0.3)
     # the counter admits returns 0, 4, 7 (inserted <= 0.3 * seen)
     assert abs(g2.lookup("weight", [[20, 0, 0]])[0] - 3.0) < 1e-1
+
+
+def _quat_axis_angle(angle, axis):
+    axis = np.asarray(axis, float)
+    axis = axis / np.linalg.norm(axis)
+    return np.concatenate([[np.cos(angle / 2)], np.sin(angle / 2) * axis])
+
+
+def _quat_mul(a, b):
+    w1, x1, y1, z1 = a
+    w2, x2, y2, z2 = b
+    return np.array([w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2, w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2,
+                     w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2, w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2])
+
+
+def test_interpolate_transform(oracle):
+    """cartographer/transform/timestamped_transform_test.cc:37-80: identity -> (10,10,10) with a 2 rad
+    rotation about z; the interpolant at 'factor' is Translation(factor t) * Rotation(factor 2 about z)."""
+    t0 = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    t1 = np.concatenate([[10., 10., 10.], _quat_axis_angle(2.0, [0, 0, 1])])
+    assert np.abs(oracle.interpolate_transform(t0, t1, 0.0) - t0).max() < 1e-6
+    assert np.abs(oracle.interpolate_transform(t0, t1, 1.0) - t1).max() < 1e-6
+    for k in range(21):
+        f = k / 20.0
+        want = np.concatenate([f * t1[:3], _quat_axis_angle(2.0 * f, [0, 0, 1])])
+        assert np.abs(oracle.interpolate_transform(t0, t1, f) - want).max() < 1e-6
+
+
+def test_rotation_delta_cost_functor(oracle):
+    """mapping/internal/3d/scan_matching/rotation_delta_cost_functor_3d_test.cc:50-86 (precision 1e-8)."""
+    def cost(rotation, scale, target):
+        r = oracle.rotation_delta(scale, target, rotation)
+        return float(r @ r)
+
+    identity = np.array([1.0, 0, 0, 0])
+    assert abs(cost(identity, 1.0, identity)) < 1e-8
+    rot = _quat_axis_angle(0.9, [0.2, 0.1, 0.3])
+    assert abs(cost(rot, 1.0, rot)) < 1e-8
+    s, angle = 1.2, 0.8
+    rotation = _quat_axis_angle(angle, [0.2, 0.1, 0.8])
+    target = _quat_axis_angle(0.2, [-0.5, 0.3, 0.4])
+    expected = (s * np.sin(angle / 2.0)) ** 2
+    assert abs(cost(rotation, s, identity) - expected) < 1e-8
+    assert abs(cost(_quat_mul(target, rotation), s, target) - expected) < 1e-8
+    assert abs(cost(_quat_mul(rotation, target), s, target) - expected) < 1e-8
+    # the Jacobian is the constant matrix the GPU matcher and the host solver use
+    r, J = oracle.rotation_delta(s, target, rotation, jacobian=True)
+    eps = 1e-6
+    for c in range(4):
+        d = np.zeros(4)
+        d[c] = eps
+        num = (oracle.rotation_delta(s, target, rotation + d) - oracle.rotation_delta(s, target, rotation - d)) / (2 * eps)
+        assert np.abs(J[:, c] - num).max() < 1e-8
+
+
+def test_translation_delta_cost_functor(oracle):
+    """translation_delta_cost_functor_3d.h:31-45: s (t - target), Jacobian s I."""
+    r, J = oracle.translation_delta(2.5, [1.0, -2.0, 0.5], [1.5, -2.0, 0.0], jacobian=True)
+    assert np.allclose(r, [1.25, 0.0, -1.25]) and np.allclose(J, 2.5 * np.eye(3))

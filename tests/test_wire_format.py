@@ -163,3 +163,36 @@ def test_pbstream_submaps_feed_the_matcher(oracle, hg, expected):
     stack = hg.Stack(hi1, 4, 3)
     assert len(stack.export(0)[0]) > 0
     hg.Fcsm(hi1, lo1, np.zeros(8, np.float32), branch_and_bound_depth=4, full_resolution_depth=3)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_decode_random_messages_against_protobuf(hg, seed):
+    """Random grids (the whole +-8192 index range, value 0 and marker-carrying values, empty grids,
+    packed and unpacked encodings, an unknown field in front) encoded by the protobuf runtime and
+    decoded by the library; CPU only."""
+    import sys
+    sys.path.insert(0, G)
+    import make_wire_golden as mw
+    M = mw.build_messages()
+    rng = np.random.RandomState(100 + seed)
+    n = [0, 1, 7, 300, 2000, 5000][seed]
+    xyz = rng.randint(-8192, 8192, (n, 3)).astype(np.int32)
+    a = rng.randint(0, 65536, n).astype(np.uint16)
+    b = rng.randint(0, 65536, n).astype(np.uint16)
+    res = float(np.float32(rng.uniform(0.01, 2.0)))
+    for name in ("HybridGrid", "HybridGridUnpacked"):
+        data = mw.fill_grid(M[name](), xyz, a, resolution=res).SerializeToString()
+        data = b"\x92\x03\x03abc" + data  # field 50, length-delimited: skipped
+        info, gx, ga, gb = hg.grid_proto_decode(data, tsdf=False)
+        assert info["num_voxels"] == n and info["resolution"] == np.float32(res)
+        assert (gx == xyz).all() and (ga == a).all()
+    data = mw.fill_grid(M["HybridGridTSDF"](), xyz, a, b, res, 0.25, 123.5).SerializeToString()
+    info, gx, ga, gb = hg.grid_proto_decode(data, tsdf=True)
+    assert info["relative_truncation_distance"] == 0.25 and info["max_weight"] == 123.5
+    assert (gx == xyz).all() and (ga == a).all() and (gb == b).all()
+    # negative int32 values are 10-byte varints on the wire; the decoder narrows them like protobuf does
+    msg = M["HybridGrid"]()
+    msg.resolution = 0.5
+    msg.x_indices.append(1), msg.y_indices.append(-2), msg.z_indices.append(3), msg.values.append(-1)
+    info, gx, ga, _ = hg.grid_proto_decode(msg.SerializeToString(), tsdf=False)
+    assert (gx == [[1, -2, 3]]).all() and ga[0] == 0xFFFF
