@@ -243,12 +243,11 @@ __global__ void __launch_bounds__(256) BuildLatticeRowsKernel(const DenseLevel d
 // x-adjacent lattice candidates; a lane reads, per scan point, KXW + 1 aligned words that hold
 // the KX voxels, realigns them with funnel shifts and adds them four at a time as two packed
 // pairs of 16-bit sums (flushed to 32-bit accumulators before they can overflow).
-template <int KXW>
-__global__ void __launch_bounds__(256) ScoreLatticePackedKernel(const LatticeRows rows, const int* __restrict__ cells,
-                                                                const int N, const int reduction_exponent,
-                                                                const int nxy, const int nz, const int wxy,
-                                                                const int wz, const int step,
-                                                                const int64_t num_groups, int* __restrict__ sums) {
+template <int KXW, bool ONE_CHUNK>
+__global__ void __launch_bounds__(256, ONE_CHUNK ? 6 : 4)
+    ScoreLatticePackedKernel(const LatticeRows rows, const int* __restrict__ cells, const int N,
+                             const int reduction_exponent, const int nxy, const int nz, const int wxy, const int wz,
+                             const int step, const int64_t num_groups, int* __restrict__ sums) {
   constexpr int KX = 4 * KXW;
   const int64_t warp = (blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -265,14 +264,19 @@ __global__ void __launch_bounds__(256) ScoreLatticePackedKernel(const LatticeRow
   const int ox0 = ((-wxy + (g * KX) * step) >> reduction_exponent) - rows.min[0];
   const int cs_mask = (1 << rows.cs_log2) - 1;
   const int* base = cells + static_cast<int64_t>(scan) * N * 3;
-  int sum[KX];
+  // ONE_CHUNK (N <= 8192): a lane adds at most 256 voxels per candidate, 256 * 255 < 65536, so the
+  // packed 16-bit sums never overflow and no 32-bit accumulators are live in the loop (fewer
+  // registers, 6 CTAs/SM). Otherwise the packed sums are flushed every 256 points per lane.
+  int sum[ONE_CHUNK ? 1 : KX];
+  if (!ONE_CHUNK) {
 #pragma unroll
-  for (int k = 0; k < KX; ++k) sum[k] = 0;
+    for (int k = 0; k < KX; ++k) sum[k] = 0;
+  }
+  unsigned even[KXW], odd[KXW];
   for (int chunk = lane; chunk < N; chunk += 32 * 256) {
-    unsigned even[KXW], odd[KXW];
 #pragma unroll
     for (int j = 0; j < KXW; ++j) even[j] = odd[j] = 0u;
-    const int chunk_end = min(N, chunk + 32 * 256);  // at most 256 points per lane: 256 * 255 < 65536
+    const int chunk_end = min(N, chunk + 32 * 256);
     for (int i = chunk; i < chunk_end; i += 32) {
       const int x = __ldg(base + 3 * i) + ox0, y = __ldg(base + 3 * i + 1) + oy, z = __ldg(base + 3 * i + 2) + oz;
       const int q0 = x >> rows.cs_log2;
@@ -296,17 +300,25 @@ __global__ void __launch_bounds__(256) ScoreLatticePackedKernel(const LatticeRow
         odd[j] += (v >> 8) & 0x00FF00FFu;
       }
     }
+    if (!ONE_CHUNK) {
 #pragma unroll
-    for (int j = 0; j < KXW; ++j) {
-      sum[4 * j] += even[j] & 0xFFFFu;
-      sum[4 * j + 1] += odd[j] & 0xFFFFu;
-      sum[4 * j + 2] += even[j] >> 16;
-      sum[4 * j + 3] += odd[j] >> 16;
+      for (int j = 0; j < KXW; ++j) {
+        sum[4 * j] += even[j] & 0xFFFFu;
+        sum[4 * j + 1] += odd[j] & 0xFFFFu;
+        sum[4 * j + 2] += even[j] >> 16;
+        sum[4 * j + 3] += odd[j] >> 16;
+      }
     }
   }
 #pragma unroll
   for (int k = 0; k < KX; ++k) {
-    int v = sum[k];
+    int v;
+    if (ONE_CHUNK) {
+      const unsigned packed = (k & 1) ? odd[k >> 2] : even[k >> 2];
+      v = static_cast<int>((k & 2) ? (packed >> 16) : (packed & 0xFFFFu));
+    } else {
+      v = sum[k];
+    }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
     const int ix = g * KX + k;
@@ -796,8 +808,13 @@ struct Scorer {
 #define HG_PACKED(KXW)                                                                                    \
   do {                                                                                                    \
     const int64_t groups = static_cast<int64_t>(scans->S) * nz * nxy * ((nxy + 4 * KXW - 1) / (4 * KXW)); \
-    ScoreLatticePackedKernel<KXW><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>(  \
-        R, cells, scans->N, e, nxy, nz, wxy, wz, 1 << depth, groups, ws->d_lattice.as<int>());            \
+    if (scans->N <= 8192) {                                                                               \
+      ScoreLatticePackedKernel<KXW, true><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>( \
+          R, cells, scans->N, e, nxy, nz, wxy, wz, 1 << depth, groups, ws->d_lattice.as<int>());          \
+    } else {                                                                                              \
+      ScoreLatticePackedKernel<KXW, false><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>( \
+          R, cells, scans->N, e, nxy, nz, wxy, wz, 1 << depth, groups, ws->d_lattice.as<int>());          \
+    }                                                                                                     \
   } while (0)
       if (nxy <= 8) HG_PACKED(2); else if (nxy <= 20) HG_PACKED(5); else HG_PACKED(8);
 #undef HG_PACKED
