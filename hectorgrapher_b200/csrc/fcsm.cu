@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(256) BuildLatticeRowsKernel(const DenseLevel d
 // the KX voxels, realigns them with funnel shifts and adds them four at a time as two packed
 // pairs of 16-bit sums (flushed to 32-bit accumulators before they can overflow).
 template <int KXW, bool ONE_CHUNK>
-__global__ void __launch_bounds__(256, ONE_CHUNK ? 6 : 4)
+__global__ void __launch_bounds__(256, ONE_CHUNK ? 8 : 4)
     ScoreLatticePackedKernel(const LatticeRows rows, const int* __restrict__ cells, const int N,
                              const int reduction_exponent, const int nxy, const int nz, const int wxy, const int wz,
                              const int step, const int64_t num_groups, int* __restrict__ sums) {
