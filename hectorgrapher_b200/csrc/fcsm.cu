@@ -330,7 +330,18 @@ __global__ void __launch_bounds__(256, ONE_CHUNK ? 8 : 4)
 // scores child slot w % 8 = (z, y, x) in {0, half}^3 of parent w / 8, so the
 // host uploads one record per parent and reads eight sums back. A child beyond
 // the search window (the reference's 'break') gets -1.
-__global__ void __launch_bounds__(256) ScoreChildrenKernel(const BrickTable level, const int* __restrict__ cells,
+__device__ __forceinline__ int LoadDenseU8(const DenseLevel& d, const int x, const int y, const int z) {
+  const unsigned ux = static_cast<unsigned>(x - d.min[0]), uy = static_cast<unsigned>(y - d.min[1]),
+                 uz = static_cast<unsigned>(z - d.min[2]);
+  if (ux >= static_cast<unsigned>(d.dim[0]) || uy >= static_cast<unsigned>(d.dim[1]) ||
+      uz >= static_cast<unsigned>(d.dim[2])) {
+    return 0;
+  }
+  return __ldg(d.data + (static_cast<size_t>(uz) * d.dim[1] + uy) * d.dim[0] + ux);
+}
+
+__global__ void __launch_bounds__(256) ScoreChildrenKernel(const BrickTable level, const DenseLevel dense,
+                                                           const int* __restrict__ cells,
                                                            const int N, const int reduction_exponent,
                                                            const int4* __restrict__ parents,
                                                            const int64_t num_parents, const int half,
@@ -348,9 +359,16 @@ __global__ void __launch_bounds__(256) ScoreChildrenKernel(const BrickTable leve
   const int ox = cx >> reduction_exponent, oy = cy >> reduction_exponent, oz = cz >> reduction_exponent;
   const int* base = cells + static_cast<int64_t>(p.x) * N * 3;
   int sum = 0;
-  for (int i = lane; i < N; i += 32) {
-    const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
-    sum += LoadU8(level, x + ox, y + oy, z + oz);
+  if (dense.data != nullptr) {  // one byte load per gather instead of brick index + voxel
+    for (int i = lane; i < N; i += 32) {
+      const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
+      sum += LoadDenseU8(dense, x + ox, y + oy, z + oz);
+    }
+  } else {
+    for (int i = lane; i < N; i += 32) {
+      const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
+      sum += LoadU8(level, x + ox, y + oy, z + oz);
+    }
   }
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
@@ -772,8 +790,8 @@ struct Scorer {
     HG_CUDA(cudaMemcpyAsync(ws->d_cand.p, ws->h_cand.p, n * sizeof(int4), cudaMemcpyHostToDevice, stream));
     const int64_t threads = static_cast<int64_t>(n) * 8 * 32;
     ScoreChildrenKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
-        m->stack->levels[child_depth].table, scans->CellsOfDepth(child_depth), scans->N,
-        ReduceExponent(child_depth), ws->d_cand.as<int4>(), static_cast<int64_t>(n), half, wxy, wz,
+        m->stack->levels[child_depth].table, m->stack->levels[child_depth].dense, scans->CellsOfDepth(child_depth),
+        scans->N, ReduceExponent(child_depth), ws->d_cand.as<int4>(), static_cast<int64_t>(n), half, wxy, wz,
         ws->d_sums.as<int>());
     CountLaunch();
     HG_CUDA(cudaGetLastError());
