@@ -473,32 +473,50 @@ __global__ void __launch_bounds__(256) HistogramKernel(const int* __restrict__ s
     if (local[k] != 0) atomicAdd(&bins[k], local[k]);
 }
 
-// LowResolutionMatcher closure: one thread per pose; the float accumulation is
-// sequential over the points in cloud order, exactly like the reference loop.
+// LowResolutionMatcher closure; the float accumulation is sequential over the points in cloud
+// order, exactly like the reference loop.
+// One warp per pose: the lanes evaluate the points' values in parallel (the lookups are the
+// latency), then lane 0 adds them in cloud order with the same float additions as the loop.
+constexpr int kLowChunk = 1024;  // values staged per warp and round
 __global__ void __launch_bounds__(128) LowResolutionKernel(const GridDev g, const float* __restrict__ points,
                                                            const int N, const float* __restrict__ poses,
                                                            const int64_t num_poses, float* __restrict__ scores) {
-  const int64_t p = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  __shared__ float staged[4][kLowChunk];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t p = blockIdx.x * static_cast<int64_t>(4) + warp;
   if (p >= num_poses) return;
   const float* P = poses + 7 * p;
   const float tx = P[0], ty = P[1], tz = P[2], qw = P[3], qx = P[4], qy = P[5], qz = P[6];
+  float* mine = staged[warp];
   float score = 0.f;
-  for (int i = 0; i < N; ++i) {
-    float wx, wy, wz;
-    RotateF(qw, qx, qy, qz, points[3 * i], points[3 * i + 1], points[3 * i + 2], &wx, &wy, &wz);
-    wx = __fadd_rn(wx, tx);
-    wy = __fadd_rn(wy, ty);
-    wz = __fadd_rn(wz, tz);
-    const int cx = CellIndexFast(wx, g.resolution, g.inv_resolution), cy = CellIndexFast(wy, g.resolution, g.inv_resolution),
-              cz = CellIndexFast(wz, g.resolution, g.inv_resolution);
-    if (g.kind == kGridProb) {
-      score = __fadd_rn(score, Decode(g.a, LoadU16(g.table, cx, cy, cz)));
-    } else {
-      const float tsd = Decode(g.a, LoadTsdf(g.table, cx, cy, cz).x);
-      score = __fadd_rn(score, __fsub_rn(1.f, fabsf(__fdiv_rn(tsd, g.max_tsd))));
+  for (int base = 0; base < N; base += kLowChunk) {
+    const int count = min(kLowChunk, N - base);
+    for (int k = lane; k < count; k += 32) {
+      const int i = base + k;
+      float wx, wy, wz;
+      RotateF(qw, qx, qy, qz, points[3 * i], points[3 * i + 1], points[3 * i + 2], &wx, &wy, &wz);
+      wx = __fadd_rn(wx, tx);
+      wy = __fadd_rn(wy, ty);
+      wz = __fadd_rn(wz, tz);
+      const int cx = CellIndexFast(wx, g.resolution, g.inv_resolution),
+                cy = CellIndexFast(wy, g.resolution, g.inv_resolution),
+                cz = CellIndexFast(wz, g.resolution, g.inv_resolution);
+      float v;
+      if (g.kind == kGridProb) {
+        v = Decode(g.a, LoadU16(g.table, cx, cy, cz));
+      } else {
+        const float tsd = Decode(g.a, LoadTsdf(g.table, cx, cy, cz).x);
+        v = __fsub_rn(1.f, fabsf(__fdiv_rn(tsd, g.max_tsd)));
+      }
+      mine[k] = v;
     }
+    __syncwarp();
+    if (lane == 0) {
+      for (int k = 0; k < count; ++k) score = __fadd_rn(score, mine[k]);
+    }
+    __syncwarp();
   }
-  scores[p] = __fdiv_rn(score, static_cast<float>(N));
+  if (lane == 0) scores[p] = __fdiv_rn(score, static_cast<float>(N));
 }
 
 // ------------------------------------------------------------- host parts --
@@ -1553,7 +1571,7 @@ class BranchAndBoundSearch {
       o[0] = r.t.x; o[1] = r.t.y; o[2] = r.t.z; o[3] = r.q.w; o[4] = r.q.x; o[5] = r.q.y; o[6] = r.q.z;
     }
     HG_CUDA(cudaMemcpyAsync(ws_->d_low_poses.p, hp, n * 7 * sizeof(float), cudaMemcpyHostToDevice, stream_));
-    LowResolutionKernel<<<static_cast<unsigned>((n + 127) / 128), 128, 0, stream_>>>(
+    LowResolutionKernel<<<static_cast<unsigned>((n + 3) / 4), 128, 0, stream_>>>(
         m_->low_grid->dev, ws_->d_low_points.as<float>(), np, ws_->d_low_poses.as<float>(), static_cast<int64_t>(n),
         ws_->d_low_scores.as<float>());
     CountLaunch();
@@ -1860,7 +1878,7 @@ int hg_low_resolution_scores(const hg_grid* low_resolution_grid, const float* po
   if (rc != HG_OK) return rc;
   HG_CUDA(cudaMemcpy(d_points.p, points, sizeof(float) * 3 * num_points, cudaMemcpyHostToDevice));
   HG_CUDA(cudaMemcpy(d_poses.p, poses, sizeof(float) * 7 * num_poses, cudaMemcpyHostToDevice));
-  LowResolutionKernel<<<static_cast<unsigned>((num_poses + 127) / 128), 128>>>(
+  LowResolutionKernel<<<static_cast<unsigned>((num_poses + 3) / 4), 128>>>(
       low_resolution_grid->dev, d_points.as<float>(), num_points, d_poses.as<float>(), num_poses,
       d_scores.as<float>());
   CountLaunch();
