@@ -20,11 +20,11 @@
 // operation by operation (no FMA contraction) so that the same 2x2x2 stencil is
 // chosen.
 //
-// Layout: one thread per point, 256-thread CTAs, one CTA per tile of points of
-// one residual block. Voxels come from the brick table (hg_internal.cuh): one
-// 4-byte index load + up to eight voxel loads per pyramid level when the
-// stencil stays inside one 8^3 brick (67 % of points), eight index loads
-// otherwise. Outputs are written in Ceres' layout.
+// Layout: one thread per point, 256-thread CTAs, one CTA per tile of 1024 points of
+// one residual block. Voxels come from the pre-decoded apron bricks (hg_internal.cuh,
+// interpolation.cuh): one 4-byte brick-index load + eight float loads at fixed offsets
+// per pyramid level. Outputs are written in Ceres' layout with streaming stores; the
+// normal-equation variant sums the 36 terms of the per-point 7-vector in registers.
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>

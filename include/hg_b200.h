@@ -169,7 +169,11 @@ typedef struct hg_occupancy_inserter_options {
  * num_free_space_voxels cells of every ray the miss odds, each cell at most once per call
  * with hits taking precedence (the update-marker rule of HybridGrid::ApplyLookupTable,
  * hybrid_grid.h:119-130, including FinishUpdate). The grid grows as DynamicGrid does
- * (hybrid_grid_base.h:385-403). 'returns' are host points, 'stride_floats' floats apart. */
+ * (hybrid_grid_base.h:385-403). 'returns' are host points, 'stride_floats' floats apart.
+ * Like the reference's Insert on a submap's grid, an insertion must not run concurrently
+ * with any other use of the same grid (cost functions and matchers created BEFORE an
+ * insertion keep reading the grid's previous device buffers only until the call returns;
+ * re-create them afterwards, as the reference re-creates its scan matchers per submap). */
 int hg_grid_insert_occupancy(hg_grid* grid, const hg_occupancy_inserter_options* options,
                              const float origin[3], const float* returns, int stride_floats,
                              int64_t num_returns);
