@@ -337,7 +337,9 @@ struct hg_batch {
   std::vector<int64_t> offsets;  // num_blocks + 1
   std::vector<double> scales;
   std::vector<double> ratios;
-  GridDev grids[HG_MAX_PYRAMID_LEVELS];
+  // The grids are read through their handles at every call, so that a cost function created
+  // before a device-side insertion (insert.cu) sees the grid's current buffers afterwards.
+  const hg_grid* grids[HG_MAX_PYRAMID_LEVELS];
   int num_grids = 0;
   float* d_points = nullptr;
   // Tile tables for 256-point (output) and 1024-point (normal equations) tiles.
@@ -456,7 +458,7 @@ int PrepareBlocks(const hg_batch* B, const double* poses, int num_poses, const i
 CostArgs BaseArgs(const hg_batch* B) {
   CostArgs a;
   std::memset(&a, 0, sizeof(a));
-  for (int i = 0; i < B->num_grids; ++i) a.grids[i] = B->grids[i];
+  for (int i = 0; i < B->num_grids; ++i) a.grids[i] = B->grids[i]->dev;
   a.num_grids = B->num_grids;
   a.points = B->d_points;
   a.stride = B->stride;
@@ -513,7 +515,7 @@ int hg_batch_create(int kind, int num_blocks, const float* points, int stride_fl
   } else {
     B->ratios.assign(num_blocks, 0.0);
   }
-  for (int i = 0; i < num_grids; ++i) B->grids[i] = grids[i]->dev;
+  for (int i = 0; i < num_grids; ++i) B->grids[i] = grids[i];
   B->num_grids = num_grids;
 
   const size_t point_bytes = static_cast<size_t>(std::max<int64_t>(B->num_points, 1)) * stride_floats * sizeof(float);

@@ -171,9 +171,9 @@ typedef struct hg_occupancy_inserter_options {
  * hybrid_grid.h:119-130, including FinishUpdate). The grid grows as DynamicGrid does
  * (hybrid_grid_base.h:385-403). 'returns' are host points, 'stride_floats' floats apart.
  * Like the reference's Insert on a submap's grid, an insertion must not run concurrently
- * with any other use of the same grid (cost functions and matchers created BEFORE an
- * insertion keep reading the grid's previous device buffers only until the call returns;
- * re-create them afterwards, as the reference re-creates its scan matchers per submap). */
+ * with any other use of the same grid. Cost functions created before an insertion read the
+ * grid's new content afterwards; a precomputation stack / matcher is a snapshot of the grid
+ * at hg_stack_build / hg_fcsm_create time, as in the reference (built per finished submap). */
 int hg_grid_insert_occupancy(hg_grid* grid, const hg_occupancy_inserter_options* options,
                              const float origin[3], const float* returns, int stride_floats,
                              int64_t num_returns);

@@ -247,3 +247,28 @@ def test_insertion_with_hash_indexed_bricks(oracle, hg):
         gp.insert_occupancy(origin, pts, 0.55, 0.49, 2)
         op.insert_occupancy(origin, pts, 0.55, 0.49, 2)
         assert_same_grid(gp, op)
+
+
+def test_cost_function_created_before_an_insertion_sees_the_new_grid(oracle, hg):
+    """The active submap is matched against and written to alternately
+    (optimizing_local_trajectory_builder.cc); a cost function that outlives an insertion reads the
+    grid's current device buffers, also after they were reallocated for new bricks."""
+    from hectorgrapher_b200 import synth
+    g = hg.Grid.tsdf(0.10, 2.5, 1000.0, np.zeros((0, 3), np.int32), [], [])
+    o = oracle.Grid.tsdf(0.10, 2.5, 1000.0)
+    origin, pts = world_scan(0, 3, rings=8, azimuths=90)
+    g.insert_tsdf(origin, pts, epsilon=1.0)
+    o.insert_tsdf(origin, pts, epsilon=1.0)
+    sensor, yaw = synth.corkscrew_pose(1, 3)
+    cloud = synth.scan(sensor, yaw, 8, 64, synth.spheres(), np.random.RandomState(2))
+    pose = np.concatenate([sensor, synth.quat_from_yaw(yaw)])
+    cost = hg.Cost("tsdf", 0.1, cloud, [g])
+    before = cost.evaluate(pose)[0]
+    for k in (1, 2):  # many new bricks: index, brick and decoded buffers are reallocated
+        origin, pts = world_scan(k, 3)
+        g.insert_tsdf(origin, pts, epsilon=1.0)
+        o.insert_tsdf(origin, pts, epsilon=1.0)
+    r, J = cost.evaluate(pose)
+    r0, J0 = oracle.Cost("tsdf", 0.1, cloud, [o]).evaluate(pose)
+    assert np.allclose(r, r0, rtol=1e-5, atol=1e-9) and not np.allclose(r, before)
+    assert all(np.allclose(a, b, rtol=1e-5, atol=1e-9) for a, b in zip(J, J0))
