@@ -431,6 +431,67 @@ def constraint_bench(hg, torch, w, rank, world, dist, num_submaps=8, nodes_per_s
     return out
 
 
+def c1_bench(hg, torch, w):
+    """C1 (BASELINE.json configs[0], the reference's own CPU-runnable case): one 32 x 640 scan against a
+    5 cm TSDF submap (+ 0.45 m low-resolution grid for the two-cloud Match). Evaluate through the
+    ceres::CostFunction surface with host pointers, and a full CeresScanMatcher3D::Match; the oracle
+    on one thread beside it (the reference runs each scan matcher with num_threads = 1)."""
+    from oracle import pyoracle
+    synth, sph = w["synth"], w["sph"]
+    empty = np.zeros((0, 3), np.int32)
+    g_hi = hg.Grid.tsdf(0.05, REL_TRUNC, MAX_WEIGHT, empty, [], [])
+    g_lo = hg.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT, empty, [], [])
+    o_hi = pyoracle.Grid.tsdf(0.05, REL_TRUNC, MAX_WEIGHT)
+    o_lo = pyoracle.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT)
+    origin, yaw = w["map_poses"][2]
+    for k, d in enumerate(([0.0, 0.0, 0.0], [0.4, -0.3, 0.1], [-0.3, 0.4, -0.1])):
+        o = origin + np.array(d)
+        c = synth.scan(o, yaw + 0.1 * k, 32, 640, sph, np.random.RandomState(300 + k))
+        pts = (synth.quat_rotate(synth.quat_from_yaw(yaw + 0.1 * k), c.astype(np.float64)) + o).astype(np.float32)
+        for g in (g_hi, g_lo, o_hi, o_lo):
+            g.insert_tsdf(o.astype(np.float32), pts, **C5_INSERTER)
+    rng = np.random.RandomState(1)
+    cloud = synth.scan(origin, yaw, 32, 640, sph, rng)
+    low = synth.voxel_downsample(cloud, 0.9, 1024, seed=3)
+    start = np.concatenate([origin + rng.uniform(-0.1, 0.1, 3), synth.quat_from_yaw(yaw + rng.uniform(-0.05, 0.05))])
+    scale = 1.0 / np.sqrt(len(cloud))
+    cost = hg.Cost("tsdf", scale, cloud, [g_hi])
+    for _ in range(5):
+        cost.evaluate(start)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    reps = 100
+    for _ in range(reps):
+        cost.evaluate(start)
+    eval_ms = 1e3 * (time.perf_counter() - t0) / reps
+    for _ in range(3):
+        hg.scan_match([cloud, low], [g_hi, g_lo], [5.0, 30.0], 10.0, 1.0, start, max_num_iterations=12,
+                      use_nonmonotonic_steps=False)
+    t0 = time.perf_counter()
+    for _ in range(20):
+        pose, summary = hg.scan_match([cloud, low], [g_hi, g_lo], [5.0, 30.0], 10.0, 1.0, start,
+                                      max_num_iterations=12, use_nonmonotonic_steps=False)
+    match_ms = 1e3 * (time.perf_counter() - t0) / 20
+    ocost = pyoracle.Cost("tsdf", scale, cloud, [o_hi])
+    ocost.evaluate(start)
+    t0 = time.perf_counter()
+    for _ in range(3):
+        ocost.evaluate(start)
+    cpu_eval_ms = 1e3 * (time.perf_counter() - t0) / 3
+    t0 = time.perf_counter()
+    opose = pyoracle.scan_match([cloud, low], [o_hi, o_lo], [5.0, 30.0], 10.0, 1.0, start, max_num_iterations=12,
+                                use_nonmonotonic_steps=False)[0]
+    cpu_match_ms = 1e3 * (time.perf_counter() - t0)
+    return {"workload": "C1: one 32 x 640 scan (%d points) against a 5 cm TSDF submap; Evaluate = "
+                        "ceres::CostFunction::Evaluate with host pointers (residuals + 2 Jacobian blocks back over "
+                        "PCIe), Match = CeresScanMatcher3D::Match on {scan, 1024-point low-resolution cloud}" % len(cloud),
+            "evaluate_ms": eval_ms, "evaluate_points_per_s": len(cloud) / (eval_ms * 1e-3),
+            "match_ms": match_ms, "match_iterations": int(summary[2]),
+            "pose_difference_to_cpu": float(np.abs(pose[:3] - opose[:3]).max()),
+            "cpu_baseline": {"evaluate_ms": cpu_eval_ms, "match_ms": cpu_match_ms, "cores": 1, "kind": "port",
+                             "sample": "oracle Jet functor / oracle cost functions under the same LM, 1 thread"}}
+
+
 def insertion_bench(hg, torch, w, scans=6):
     """N1: TSDFRangeDataInserter3D::Insert of whole scans (100k returns each) into a device-resident
     0.10 m TSDF submap, host points in, grid ready for matching out; CPU baseline = the oracle's
@@ -598,12 +659,18 @@ def run_ours(args, rank, world, local_rank):
         cons = {"error": repr(ex)}
 
     ins = None
+    c1 = None
     if rank == 0:
         try:
             ins = insertion_bench(hg, torch, w)
         except Exception as ex:
             log("[rank 0] insertion bench failed: %r" % (ex,))
             ins = {"error": repr(ex)}
+        try:
+            c1 = c1_bench(hg, torch, w)
+        except Exception as ex:
+            log("[rank 0] C1 bench failed: %r" % (ex,))
+            c1 = {"error": repr(ex)}
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -638,6 +705,7 @@ def run_ours(args, rank, world, local_rank):
             "correlative": corr,
             "constraint_batch": cons,
             "insertion": ins,
+            "c1_scan_to_submap": c1,
         }
         emit(line)
     if dist is not None:

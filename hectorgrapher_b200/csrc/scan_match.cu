@@ -11,17 +11,22 @@
 // for a fixed 6- or 4-dimensional tangent space; hg_scan_match keeps the host loop for
 // HG_SCAN_MATCH_HOST=1 and the tests compare the two.
 //
-// One CTA of 512 threads per problem: every evaluation strides the points of all clouds over
-// the threads (the Jacobian row of a one-pose block is the 7-vector u of cost.cu, so a thread
+// One CTA of 512 threads per problem (a thread-block cluster of eight for clouds above 4096
+// points, reduced through distributed shared memory): every evaluation strides the points of all
+// clouds over the threads (the Jacobian row of a one-pose block is the 7-vector u of cost.cu, so a thread
 // adds 36 products per point into registers), warps reduce by shuffles, 36 threads add the
 // per-warp sums in warp order, and thread 0 runs the LM bookkeeping and the 6x6 Cholesky.
 // A clouds-worth of points (a few thousand) is a few microseconds per evaluation; the host
 // loop it replaces paid two launches, two synchronisations and two PCIe round trips per
 // evaluation.
+#include <cooperative_groups.h>
+
 #include <cstdlib>
 #include <cstring>
 
 #include "interpolation.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace hg {
 namespace {
@@ -396,13 +401,23 @@ __device__ void Advance(LmState* s, const ScanMatchArgs& a, EvalShared* ev) {
   NextCandidate(s, a, ev);
 }
 
-__global__ void __launch_bounds__(kLmThreads, 1) ScanMatchKernel(const ScanMatchArgs a) {
+// CLUSTER = 1: one CTA. CLUSTER = 8: a thread-block cluster; every CTA evaluates its share of the
+// points and reduces it to 36 totals in its own shared memory, CTA 0 adds the eight vectors in rank
+// order through distributed shared memory and runs the solver, the others read the next pose (and
+// the stop flag) from CTA 0's shared memory. Two cluster barriers per evaluation.
+template <int CLUSTER>
+__global__ void __cluster_dims__(CLUSTER, 1, 1) __launch_bounds__(kLmThreads, 1)
+    ScanMatchKernel(const ScanMatchArgs a) {
   __shared__ LmState st;
   __shared__ double warp_sums[kLmWarps][kTerms];
   __shared__ double totals[kTerms];
+  __shared__ double grand[kTerms];
   __shared__ EvalShared ev;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = CLUSTER == 1 ? 0 : static_cast<int>(cluster.block_rank());
+  const LmState* st0 = CLUSTER == 1 ? &st : cluster.map_shared_rank(&st, 0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  if (tid == 0) {
+  if (rank == 0 && tid == 0) {
     for (int k = 0; k < 7; ++k) st.x[k] = a.pose[k];
     st.n = a.only_optimize_yaw ? 4 : 6;
     st.phase = 0;
@@ -414,11 +429,11 @@ __global__ void __launch_bounds__(kLmThreads, 1) ScanMatchKernel(const ScanMatch
     ev.M[4] = z2; ev.M[5] = z3; ev.M[6] = z0; ev.M[7] = -z1;
     ev.M[8] = z3; ev.M[9] = -z2; ev.M[10] = z1; ev.M[11] = z0;
   }
-  __syncthreads();
+  if (CLUSTER == 1) __syncthreads(); else cluster.sync();
   for (;;) {
-    // ---- evaluate all scan blocks at st.x ------------------------------------------------
-    const double tx = st.x[0], ty = st.x[1], tz = st.x[2];
-    const double qw = st.x[3], qx = st.x[4], qy = st.x[5], qz = st.x[6];
+    // ---- evaluate this CTA's share of all scan blocks at the current pose -----------------
+    const double tx = st0->x[0], ty = st0->x[1], tz = st0->x[2];
+    const double qw = st0->x[3], qx = st0->x[4], qy = st0->x[5], qz = st0->x[6];
     double S[kTerms];
 #pragma unroll
     for (int e = 0; e < kTerms; ++e) S[e] = 0.0;
@@ -426,7 +441,7 @@ __global__ void __launch_bounds__(kLmThreads, 1) ScanMatchKernel(const ScanMatch
       const GridDev& grid = a.grids[c];
       const float* pts = a.points[c];
       const double scale = a.scale[c];
-      for (int i = tid; i < a.n[c]; i += kLmThreads) {
+      for (int i = rank * kLmThreads + tid; i < a.n[c]; i += kLmThreads * CLUSTER) {
         const double px = static_cast<double>(pts[3 * i]), py = static_cast<double>(pts[3 * i + 1]),
                      pz = static_cast<double>(pts[3 * i + 2]);
         const WorldPoint wp = TransformPoint(qw, qx, qy, qz, tx, ty, tz, px, py, pz);
@@ -473,12 +488,24 @@ __global__ void __launch_bounds__(kLmThreads, 1) ScanMatchKernel(const ScanMatch
       totals[tid] = s;
     }
     __syncthreads();
-    AssembleNormal(a, totals, st.x, st.n, tid, &ev);
-    if (tid == 0) Advance(&st, a, &ev);
-    __syncthreads();
-    if (st.done) break;
+    if (CLUSTER > 1) cluster.sync();  // every CTA's totals are in place
+    if (rank == 0) {
+      if (CLUSTER > 1) {
+        if (tid < kTerms) {
+          double s = 0.0;
+          for (int r = 0; r < CLUSTER; ++r) s += cluster.map_shared_rank(totals, r)[tid];
+          grand[tid] = s;
+        }
+        __syncthreads();
+      }
+      AssembleNormal(a, CLUSTER > 1 ? grand : totals, st.x, st.n, tid, &ev);
+      if (tid == 0) Advance(&st, a, &ev);
+    }
+    if (CLUSTER == 1) __syncthreads(); else cluster.sync();  // the next pose / the stop flag is published
+    if (st0->done) break;
   }
-  if (tid == 0) {
+  if (CLUSTER > 1) cluster.sync();  // nobody leaves while CTA 0's shared memory may still be read
+  if (rank == 0 && tid == 0) {
     double cost = st.cost;
     if (a.use_nonmonotonic_steps && st.minimum_cost < cost) {  // Ceres reports the best point seen
       for (int k = 0; k < 7; ++k) st.x[k] = st.x_min[k];
@@ -542,7 +569,12 @@ int ScanMatchOnDevice(int num_clouds, const float* const* clouds, const int32_t*
   for (int k = 0; k < 4; ++k) a.target_q[k] = initial_pose[3 + k];
   for (int k = 0; k < 7; ++k) a.pose[k] = initial_pose[k];
   a.out = d_out;
-  ScanMatchKernel<<<1, kLmThreads, 0, stream>>>(a);
+  // A few thousand points are one CTA's worth; a full-resolution scan gets a cluster of eight.
+  if (total_floats / 3 > 4096) {
+    ScanMatchKernel<8><<<8, kLmThreads, 0, stream>>>(a);
+  } else {
+    ScanMatchKernel<1><<<1, kLmThreads, 0, stream>>>(a);
+  }
   CountLaunch();
   HG_CUDA(cudaGetLastError());
   HG_CUDA(cudaMemcpyAsync(h_out, d_out, 14 * sizeof(double), cudaMemcpyDeviceToHost, stream));

@@ -807,8 +807,13 @@ def test_device_scan_match_equals_host_loop(oracle, hg, world):
         (["g_tsdf_hi", "g_tsdf_lo"], ["o_tsdf_hi", "o_tsdf_lo"], dict(use_nonmonotonic_steps=True,
                                                                          max_num_iterations=25)),
     ]
+    # more than 4096 points: the solve runs on a cluster of eight CTAs (distributed shared memory)
+    big = np.concatenate([cloud + rng.normal(0, 0.004, cloud.shape).astype(np.float32) for _ in range(4)])
+    assert len(big) > 3 * 4096
+    cases.append((["g_tsdf_hi", "g_tsdf_lo"], ["o_tsdf_hi", "o_tsdf_lo"], dict(big=True)))
     for gnames, onames, extra in cases:
-        clouds = [cloud, low][:len(gnames)]
+        extra = dict(extra)
+        clouds = [big if extra.pop("big", False) else cloud, low][:len(gnames)]
         weights = [5.0, 30.0][:len(gnames)]
         kw = dict(max_num_iterations=12, use_nonmonotonic_steps=False)
         kw.update(extra)
