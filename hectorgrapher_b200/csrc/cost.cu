@@ -361,6 +361,8 @@ struct hg_batch {
   mutable double* h_ne_out = nullptr;  // pinned
   mutable double* d_out = nullptr;     // staging for host-pointer evaluate
   mutable size_t d_out_doubles = 0;
+  mutable double* h_out = nullptr;     // pinned staging for small host-pointer evaluates
+  mutable size_t h_out_doubles = 0;
 };
 
 struct hg_cost {
@@ -563,6 +565,7 @@ void hg_batch_destroy(hg_batch* B) {
   CachedFree(B->d_ne_out);
   CachedFree(B->h_ne_out);
   CachedFree(B->d_out);
+  CachedFree(B->h_out);
   delete B;
 }
 
@@ -617,6 +620,28 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
   a.vec_store = 1;
   rc = LaunchCost<false>(B, a, B->num_tiles_out, stream);
   if (rc != HG_OK) return rc;
+  // Small blocks (a scan matcher's Evaluate: ~1 MB into Ceres' pageable arrays): one DMA of the
+  // whole staging area into pinned memory and host copies from there cost less than up to five
+  // separate pageable device-to-host copies.
+  constexpr size_t kPinnedStageDoubles = size_t(1) << 20;  // 8 MB
+  if (need <= kPinnedStageDoubles) {
+    if (B->h_out_doubles < need) {
+      CachedFree(B->h_out);
+      B->h_out = nullptr;
+      B->h_out_doubles = 0;
+      HG_ALLOC(B->h_out, CachedPinnedAlloc(std::max<size_t>(need, 1) * sizeof(double)));
+      B->h_out_doubles = need;
+    }
+    HG_CUDA(cudaMemcpyAsync(B->h_out, d, need * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    HG_CUDA(cudaStreamSynchronize(stream));
+    const double* h = B->h_out;
+    if (jq0) std::memcpy(jq0, h, sizeof(double) * N * 4);
+    if (jq1) std::memcpy(jq1, h + 4 * N, sizeof(double) * N * 4);
+    if (jt0) std::memcpy(jt0, h + 8 * N, sizeof(double) * N * 3);
+    if (jt1) std::memcpy(jt1, h + 11 * N, sizeof(double) * N * 3);
+    if (residuals) std::memcpy(residuals, h + 14 * N, sizeof(double) * N);
+    return HG_OK;
+  }
   if (residuals) HG_CUDA(cudaMemcpyAsync(residuals, a.r, sizeof(double) * N, cudaMemcpyDeviceToHost, stream));
   if (jt0) HG_CUDA(cudaMemcpyAsync(jt0, a.jt0, sizeof(double) * N * 3, cudaMemcpyDeviceToHost, stream));
   if (jq0) HG_CUDA(cudaMemcpyAsync(jq0, a.jq0, sizeof(double) * N * 4, cudaMemcpyDeviceToHost, stream));
