@@ -757,6 +757,7 @@ struct Scorer {
   int64_t lattice_candidates = 0;
 
   int ReduceExponent(int depth) const { return std::max(0, depth - m->options.full_resolution_depth + 1); }
+  static constexpr size_t kZeroCopyParents = 512;
 
   int Reserve(size_t n) {
     int rc = ws->h_cand.Reserve(n * sizeof(int4));
@@ -805,8 +806,23 @@ struct Scorer {
   // HostSums()[8 n], -1 where the child lies beyond the window.
   int RunChildren(int child_depth, size_t n, int half, int wxy, int wz) {
     if (n == 0) return HG_OK;
-    HG_CUDA(cudaMemcpyAsync(ws->d_cand.p, ws->h_cand.p, n * sizeof(int4), cudaMemcpyHostToDevice, stream));
     const int64_t threads = static_cast<int64_t>(n) * 8 * 32;
+    if (n <= kZeroCopyParents) {
+      // A small wave (a local search has dozens of them): the kernel reads the parent records
+      // from, and writes the sums to, the pinned host buffers directly (they are mapped into the
+      // device's address space), so the wave is one launch and one synchronisation instead of
+      // copy + launch + copy + synchronisation.
+      ScoreChildrenKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
+          m->stack->levels[child_depth].table, m->stack->levels[child_depth].dense,
+          scans->CellsOfDepth(child_depth), scans->N, ReduceExponent(child_depth), ws->h_cand.as<int4>(),
+          static_cast<int64_t>(n), half, wxy, wz, ws->h_sums.as<int>());
+      CountLaunch();
+      HG_CUDA(cudaGetLastError());
+      HG_CUDA(cudaStreamSynchronize(stream));
+      ++launches;
+      return HG_OK;
+    }
+    HG_CUDA(cudaMemcpyAsync(ws->d_cand.p, ws->h_cand.p, n * sizeof(int4), cudaMemcpyHostToDevice, stream));
     ScoreChildrenKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
         m->stack->levels[child_depth].table, m->stack->levels[child_depth].dense, scans->CellsOfDepth(child_depth),
         scans->N, ReduceExponent(child_depth), ws->d_cand.as<int4>(), static_cast<int64_t>(n), half, wxy, wz,
@@ -1570,15 +1586,24 @@ class BranchAndBoundSearch {
       float* o = hp + 7 * k;
       o[0] = r.t.x; o[1] = r.t.y; o[2] = r.t.z; o[3] = r.q.w; o[4] = r.q.x; o[5] = r.q.y; o[6] = r.q.z;
     }
-    HG_CUDA(cudaMemcpyAsync(ws_->d_low_poses.p, hp, n * 7 * sizeof(float), cudaMemcpyHostToDevice, stream_));
-    LowResolutionKernel<<<static_cast<unsigned>((n + 3) / 4), 128, 0, stream_>>>(
-        m_->low_grid->dev, ws_->d_low_points.as<float>(), np, ws_->d_low_poses.as<float>(), static_cast<int64_t>(n),
-        ws_->d_low_scores.as<float>());
-    CountLaunch();
-    ++low_launches_;
-    HG_CUDA(cudaGetLastError());
-    HG_CUDA(cudaMemcpyAsync(ws_->h_low.p, ws_->d_low_scores.p, n * sizeof(float), cudaMemcpyDeviceToHost, stream_));
-    HG_CUDA(cudaStreamSynchronize(stream_));
+    if (n <= 256) {  // poses and scores through the mapped pinned buffers: one launch, one synchronisation
+      LowResolutionKernel<<<static_cast<unsigned>((n + 3) / 4), 128, 0, stream_>>>(
+          m_->low_grid->dev, ws_->d_low_points.as<float>(), np, hp, static_cast<int64_t>(n), ws_->h_low.as<float>());
+      CountLaunch();
+      ++low_launches_;
+      HG_CUDA(cudaGetLastError());
+      HG_CUDA(cudaStreamSynchronize(stream_));
+    } else {
+      HG_CUDA(cudaMemcpyAsync(ws_->d_low_poses.p, hp, n * 7 * sizeof(float), cudaMemcpyHostToDevice, stream_));
+      LowResolutionKernel<<<static_cast<unsigned>((n + 3) / 4), 128, 0, stream_>>>(
+          m_->low_grid->dev, ws_->d_low_points.as<float>(), np, ws_->d_low_poses.as<float>(),
+          static_cast<int64_t>(n), ws_->d_low_scores.as<float>());
+      CountLaunch();
+      ++low_launches_;
+      HG_CUDA(cudaGetLastError());
+      HG_CUDA(cudaMemcpyAsync(ws_->h_low.p, ws_->d_low_scores.p, n * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+      HG_CUDA(cudaStreamSynchronize(stream_));
+    }
     const float* hs = ws_->h_low.as<float>();
     for (size_t k = 0; k < n; ++k) (*out)[k] = hs[k];
     return HG_OK;
