@@ -225,9 +225,12 @@ class Grid:
         return Grid(out, True)
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().hg_grid_destroy(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().hg_grid_destroy(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown: module globals may already be gone
+            pass
 
     @property
     def grid_size(self):
@@ -320,9 +323,12 @@ class PbStream:
         _check(lib().hg_pbstream_open(str(path).encode(), C.byref(self.h)))
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().hg_pbstream_close(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().hg_pbstream_close(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown: module globals may already be gone
+            pass
 
     def __iter__(self):
         while True:
@@ -373,9 +379,12 @@ class Cost:
         self.sizes = [3, 4] * (self.nblocks // 2)
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().hg_cost_destroy(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().hg_cost_destroy(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown: module globals may already be gone
+            pass
 
     def _blocks(self, params):
         params = _f64(params).reshape(-1)
@@ -430,9 +439,12 @@ class Batch:
         self.h = out
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().hg_batch_destroy(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().hg_batch_destroy(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown: module globals may already be gone
+            pass
 
     def update_points(self, pts):
         """pts: host array (pinned torch tensors are passed via .numpy())."""
@@ -505,9 +517,12 @@ class Stack:
         self.depth = lib().hg_stack_depth(self.h)
 
     def __del__(self):
-        if getattr(self, "h", None) and self.owned:
-            lib().hg_stack_destroy(self.h)
-        self.h = None
+        try:
+            if getattr(self, "h", None) and self.owned:
+                lib().hg_stack_destroy(self.h)
+            self.h = None
+        except Exception:  # interpreter shutdown: module globals may already be gone
+            pass
 
     def lookup(self, d, xyz):
         xyz = _i32(xyz).reshape(-1, 3)
@@ -581,9 +596,12 @@ class Fcsm:
         self.h = out
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().hg_fcsm_destroy(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().hg_fcsm_destroy(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown: module globals may already be gone
+            pass
 
     def stack(self):
         return Stack(self.grid, 0, 0, handle=lib().hg_fcsm_stack(self.h), owner=self)

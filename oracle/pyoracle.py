@@ -136,9 +136,12 @@ class Grid:
         return Grid(lib().orc_tsdf_grid_new(resolution, relative_truncation_distance, max_weight), True)
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().orc_grid_free(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().orc_grid_free(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown: module globals may already be gone
+            pass
 
     @property
     def grid_size(self):
@@ -258,9 +261,12 @@ class Cost:
         self.sizes = [3, 4] * (self.nblocks // 2)
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().orc_cost_free(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().orc_cost_free(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown: module globals may already be gone
+            pass
 
     def _params(self, params):
         params = _f64(params).reshape(-1)
@@ -344,9 +350,12 @@ class Stack:
         self.h = lib().orc_stack_new(grid.h, depth, full_resolution_depth)
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().orc_stack_free(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().orc_stack_free(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown: module globals may already be gone
+            pass
 
     def export(self, d):
         n = lib().orc_stack_num_voxels(self.h, d)
@@ -406,9 +415,12 @@ class Fcsm:
                                     o["linear_z_search_window"], o["angular_search_window"])
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().orc_fcsm_free(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().orc_fcsm_free(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown: module globals may already be gone
+            pass
 
     def match(self, node_pose, submap_pose, high, low, hist, gravity=(1, 0, 0, 0), min_score=0.55,
               full=False):
