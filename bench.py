@@ -539,6 +539,31 @@ def insertion_bench(hg, torch, w, scans=6):
                              "sample": "2 of the same scans, sequential oracle inserter"}}
 
 
+def bind_to_gpu_numa_node(torch, local_rank):
+    """One process per GPU: run on (and allocate pinned host memory from) the NUMA node the GPU hangs off,
+    so that the end-to-end copies of several ranks do not all cross the socket interconnect. Best effort:
+    a box without NUMA information (or a single node) is left alone. Returns a description for the log."""
+    try:
+        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id
+        dom = torch.cuda.get_device_properties(local_rank).pci_domain_id
+        dev = torch.cuda.get_device_properties(local_rank).pci_device_id
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bus, dev)
+        node = int(open(path).read().strip())
+        if node < 0:
+            return "no NUMA node reported for the GPU"
+        cpus = []
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus += list(range(int(lo), int(hi or lo) + 1))
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return "NUMA node %d has no CPU this process may use" % node
+        os.sched_setaffinity(0, allowed)
+        return "bound to NUMA node %d (%d CPUs)" % (node, len(allowed))
+    except Exception as ex:  # no sysfs, old torch, containers without the files ...
+        return "not bound (%s)" % type(ex).__name__
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import hectorgrapher_b200 as hg
@@ -548,6 +573,8 @@ def run_ours(args, rank, world, local_rank):
     hg.lib()
     torch.cuda.set_device(local_rank)
     hg.set_device(local_rank)
+    if world > 1:
+        log("[rank %d] %s" % (rank, bind_to_gpu_numa_node(torch, local_rank)))
     dist = None
     if world > 1:
         import torch.distributed as dist_mod
