@@ -143,3 +143,63 @@ def test_residual_definitions(oracle):
     prob.set_probability([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1], [1, 1, 0], [1, 0, 1], [0, 1, 1], [1, 1, 1]], 0.8)
     pr = oracle.Cost("occupied", s, np.array([[0.05, 0.05, 0.05]], np.float32), [prob]).evaluate(ident, jacobians=False)[0]
     assert abs(pr[0] - s * (1.0 - prob.interpolate([[0.05, 0.05, 0.05]])[0])) < 1e-12
+
+
+def test_branch_and_bound_returns_the_best_leaf_of_an_exhaustive_search(oracle):
+    """fast_correlative_scan_matcher_3d.cc:408-471 claims the branch-and-bound returns the best-scoring
+    leaf (full-resolution candidate) above min_score that passes the low-resolution gate. Checked by brute
+    force: every (scan, x, y, z) leaf of a small window is scored, gated and the maximum compared."""
+    from hectorgrapher_b200 import synth
+    sph = synth.spheres()
+    hi = oracle.Grid.tsdf(0.10, 2.5, 1000.0)
+    lo = oracle.Grid.tsdf(0.45, 2.5, 1000.0)
+    for k in range(2):
+        origin, yaw = synth.corkscrew_pose(k, 2)
+        cloud = synth.scan(origin, yaw, 24, 300, sph, np.random.RandomState(50 + k))
+        world = (synth.quat_rotate(synth.quat_from_yaw(yaw), cloud.astype(np.float64)) + origin).astype(np.float32)
+        hi.insert_tsdf(origin.astype(np.float32), world, epsilon=1.0)
+        lo.insert_tsdf(origin.astype(np.float32), world, epsilon=1.0)
+    origin, yaw = synth.corkscrew_pose(1, 2)
+    cloud = synth.scan(origin, yaw, 12, 40, sph, np.random.RandomState(77))[:400]
+    high = synth.voxel_downsample(cloud, 0.2, 200, seed=6)
+    low = synth.voxel_downsample(cloud, 0.9, 50, seed=7)
+    hist = np.zeros(8, np.float32)
+    opts = dict(branch_and_bound_depth=4, full_resolution_depth=2, use_rotational_scan_matcher=False,
+                min_low_resolution_score=0.3, linear_xy_search_window=0.6, linear_z_search_window=0.3,
+                angular_search_window=0.04)
+    m = oracle.Fcsm(hi, lo, hist, **opts)
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    rng = np.random.RandomState(3)
+    found = 0
+    for trial in range(3):
+        node = np.concatenate([origin + rng.uniform(-0.3, 0.3, 3) * [1, 1, 0.3], synth.quat_from_yaw(yaw + rng.uniform(-0.02, 0.02))])
+        min_score = 0.2
+        res = m.match(node, submap, high, low, hist, min_score=min_score)
+        wxy, wz = 6, 3
+        poses, rot, cells = m.discrete_scans(wxy, wz, 0.04, node, submap, high, hist)
+        S = len(poses)
+        assert S == int(res["num_scans"]) and S >= 3
+        cand = np.array([(s, x, y, z) for s in range(S) for z in range(-wz, wz + 1) for y in range(-wxy, wxy + 1)
+                         for x in range(-wxy, wxy + 1)], np.int32)
+        sums, scores, _ = m.score_candidates(wxy, wz, 0.04, node, submap, high, hist, 0, cand)
+        order = np.argsort(-scores, kind="stable")
+        best = None
+        for i in order:
+            if not scores[i] > min_score:
+                break
+            s, x, y, z = cand[i]
+            pose = poses[s].copy()
+            pose[:3] = np.float32(0.1) * cand[i][1:].astype(np.float32) + pose[:3]
+            if oracle.low_resolution_score(lo, low, pose) >= 0.3:
+                best = i
+                break
+        if best is None:
+            assert res["found"] == 0.0
+            continue
+        assert res["found"] == 1.0
+        assert np.float32(res["score"]) == scores[best]
+        if (scores == scores[best]).sum() == 1:  # a unique maximum identifies the candidate
+            assert (int(res["scan_index"]), int(res["ox"]), int(res["oy"]), int(res["oz"])) == tuple(cand[best])
+        assert res["num_scored"] < len(cand)  # the search prunes
+        found += 1
+    assert found >= 2  # the comparison is not vacuous
