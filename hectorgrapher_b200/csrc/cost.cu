@@ -783,16 +783,22 @@ class GpuScanCost : public LmCost {
   explicit GpuScanCost(hg_cost* c) : c_(c) {}
   ~GpuScanCost() override { hg_cost_destroy(c_); }
   bool Evaluate(double const* const* p, double* r, double** J) const override {
-    return hg_cost_evaluate(c_, p, r, J) == HG_OK;
+    const bool ok = hg_cost_evaluate(c_, p, r, J) == HG_OK;
+    if (!ok) failed_ = true;
+    return ok;
   }
   // Fused J'J / J'r / cost on the device: the solver never needs the rows.
   bool NormalEquations(double const* const* p, double* JtJ, double* Jtr, double* cost) const override {
-    return hg_cost_normal_equations(c_, p, JtJ, Jtr, cost) == HG_OK;
+    const bool ok = hg_cost_normal_equations(c_, p, JtJ, Jtr, cost) == HG_OK;
+    if (!ok) failed_ = true;
+    return ok;
   }
+  bool failed() const { return failed_; }
   int num_residuals() const override { return hg_cost_num_residuals(c_); }
 
  private:
   hg_cost* c_;
+  mutable bool failed_ = false;  // a device evaluation returned an error
 };
 
 // translation_delta_cost_functor_3d.h:31-45
@@ -873,9 +879,8 @@ extern "C" int hg_scan_match(int num_clouds, const float* const* clouds, const i
   const int qb = problem.AddParameterBlock(q, 4, only_optimize_yaw ? hg::LocalParameterization::kYawOnlyQuaternion
                                                                    : hg::LocalParameterization::kQuaternion);
   std::vector<std::unique_ptr<LmCost>> owned;
+  std::vector<const GpuScanCost*> scan_costs;
   for (int i = 0; i < num_clouds; ++i) {
-    HG_REQUIRE(occupied_space_weights[i] > 0., "hg_scan_match: occupied_space_weight must be > 0");
-    HG_REQUIRE(cloud_sizes[i] > 0, "hg_scan_match: empty point cloud");
     // ceres_scan_matcher_3d.cc:138-139 / :149-150
     const double scaling = occupied_space_weights[i] / std::sqrt(static_cast<double>(cloud_sizes[i]));
     hg_cost* c = nullptr;
@@ -883,7 +888,8 @@ extern "C" int hg_scan_match(int num_clouds, const float* const* clouds, const i
     const int rc = hg_cost_create(kind, scaling, clouds[i], 3, cloud_sizes[i], &grids[i], 1, 0.0, &c);
     if (rc == HG_OK) c->batch->stream = ThreadStream();  // concurrent matches do not share the legacy stream
     if (rc != HG_OK) return rc;
-    owned.emplace_back(new GpuScanCost(c));
+    scan_costs.push_back(new GpuScanCost(c));
+    owned.emplace_back(const_cast<GpuScanCost*>(scan_costs.back()));
     problem.AddResidualBlock(owned.back().get(), {tb, qb});
   }
   owned.emplace_back(new TranslationDelta(translation_weight, target_translation));
@@ -894,9 +900,13 @@ extern "C" int hg_scan_match(int num_clouds, const float* const* clouds, const i
   options.max_num_iterations = max_num_iterations;
   options.use_nonmonotonic_steps = use_nonmonotonic_steps != 0;
   const hg::LmSummary s = problem.Solve(options);
-  if (s.termination == 4) {
-    SetError(std::string("hg_scan_match: evaluation failed: ") + hg_last_error());
-    return HG_ERR_CUDA;
+  // Ceres' own FAILURE (five invalid steps in a row) still yields the best pose seen, and the
+  // reference does not look at the termination type; only a failed device call is an error here.
+  for (const GpuScanCost* c : scan_costs) {
+    if (c->failed()) {
+      SetError(std::string("hg_scan_match: evaluation failed: ") + hg_last_error());
+      return HG_ERR_CUDA;
+    }
   }
   for (int k = 0; k < 3; ++k) pose_out[k] = t[k];
   for (int k = 0; k < 4; ++k) pose_out[3 + k] = q[k];

@@ -7,9 +7,9 @@
 //   .../occupied_space_cost_function_3d.h, tsdf_space_cost_function_3d.h         scan blocks
 //   .../translation_delta_cost_functor_3d.h:31-45, rotation_delta_cost_functor_3d.h:35-54
 //   mapping/internal/3d/rotation_parameterization.h:27-39                        yaw-only plus
-// The solver is the trust-region loop of include/hg_dense_lm.h (Ceres' LM strategy) restated
-// for a fixed 6- or 4-dimensional tangent space; hg_scan_match keeps the host loop for
-// HG_SCAN_MATCH_HOST=1 and the tests compare the two.
+// The solver is the state machine of include/hg_trust_region.h (Ceres 1.13's trust-region loop,
+// restated) — the same code the host loop of include/hg_dense_lm.h drives; hg_scan_match keeps
+// that host loop for HG_SCAN_MATCH_HOST=1 and the tests compare the two.
 //
 // One CTA of 512 threads per problem (a thread-block cluster of eight for clouds above 4096
 // points, reduced through distributed shared memory): every evaluation strides the points of all
@@ -24,6 +24,7 @@
 #include <cstdlib>
 #include <cstring>
 
+#include "../../include/hg_trust_region.h"
 #include "interpolation.cuh"
 
 namespace cg = cooperative_groups;
@@ -52,12 +53,6 @@ struct ScanMatchArgs {
   double* out;  // pose[7], summary[6], termination
 };
 
-// LmOptions defaults of include/hg_dense_lm.h (Ceres' defaults).
-constexpr double kInitialRadius = 1e4, kMaxRadius = 1e16, kMinRadius = 1e-32;
-constexpr double kMinRelativeDecrease = 1e-3, kMinLmDiagonal = 1e-6, kMaxLmDiagonal = 1e32;
-constexpr double kFunctionTolerance = 1e-6, kGradientTolerance = 1e-10, kParameterTolerance = 1e-8;
-constexpr int kMaxConsecutiveNonmonotonicSteps = 5;
-
 __device__ void QuatProduct(const double* z, const double* w, double* zw) {
   zw[0] = z[0] * w[0] - z[1] * w[1] - z[2] * w[2] - z[3] * w[3];
   zw[1] = z[0] * w[1] + z[1] * w[0] + z[2] * w[3] - z[3] * w[2];
@@ -65,44 +60,11 @@ __device__ void QuatProduct(const double* z, const double* w, double* zw) {
   zw[3] = z[0] * w[3] + z[1] * w[2] - z[2] * w[1] + z[3] * w[0];
 }
 
-// Lower Cholesky of the n x n matrix A (row-major, n <= 6), then A x = b.
-__device__ bool CholeskySolve(double* A, const double* b, const int n, double* y, double* x) {
-  for (int j = 0; j < n; ++j) {
-    double d = A[j * n + j];
-    for (int k = 0; k < j; ++k) d -= A[j * n + k] * A[j * n + k];
-    if (!(d > 0.0) || !isfinite(d)) return false;
-    const double l = sqrt(d);
-    A[j * n + j] = l;
-    for (int i = j + 1; i < n; ++i) {
-      double s = A[i * n + j];
-      for (int k = 0; k < j; ++k) s -= A[i * n + k] * A[j * n + k];
-      A[i * n + j] = s / l;
-    }
-  }
-  for (int i = 0; i < n; ++i) {
-    double s = b[i];
-    for (int k = 0; k < i; ++k) s -= A[i * n + k] * y[k];
-    y[i] = s / A[i * n + i];
-  }
-  for (int i = n - 1; i >= 0; --i) {
-    double s = y[i];
-    for (int k = i + 1; k < n; ++k) s -= A[k * n + i] * x[k];
-    x[i] = s / A[i * n + i];
-  }
-  return true;
-}
-
-// State of the solve; lives in shared memory, touched by thread 0 only.
+// State of the solve; lives in shared memory, written by thread 0 only. 'eval_x' is the pose
+// every thread evaluates next.
 struct LmState {
-  double x[7], x_backup[7], x_min[7];
-  double H[36], g[6], Hs[36], gs[6], scale[6], delta[6];
-  double cost, radius, decrease_factor;
-  double reference_cost, candidate_cost, minimum_cost;
-  double accumulated_reference_model_cost_change, accumulated_candidate_model_cost_change;
-  double model_cost_change, step_norm2, x_norm2;
-  double initial_cost;
-  int num_consecutive_nonmonotonic_steps;
-  int iterations, successful_steps, cost_evaluations, jacobian_evaluations, termination;
+  TrustRegionCore<6> core;
+  double x[7], candidate_x[7], best[7], eval_x[7];
   int n;
   int phase;  // 0 = first evaluation pending, 1 = candidate evaluation pending
   int done;
@@ -206,199 +168,82 @@ __device__ void AssembleNormal(const ScanMatchArgs& a, const double* S, const do
   __syncthreads();
 }
 
-__device__ void ApplyScaling(LmState* s) {
-  const int n = s->n;
-  for (int a = 0; a < n; ++a) {
-    s->gs[a] = s->g[a] * s->scale[a];
-    for (int b = 0; b < n; ++b) s->Hs[a * n + b] = s->H[a * n + b] * s->scale[a] * s->scale[b];
-  }
-}
-
-__device__ double MaxAbsGradient(const LmState* s) {
-  double v = 0.0;
-  for (int a = 0; a < s->n; ++a) v = fmax(v, fabs(s->g[a]));
-  return v;
-}
-
-// x (+) delta: identity for t; exp(delta) * q or the yaw-only plus for q.
-__device__ void ApplyDelta(LmState* s, const int yaw_only) {
-  for (int k = 0; k < 3; ++k) s->x[k] += s->delta[k] * s->scale[k];
-  double* q = s->x + 3;
-  double out[4];
+// Evaluator::Plus for the pose (t, q): identity for t; ceres::QuaternionParameterization::Plus
+// (exp(delta) * q) or the yaw-only plus (rotation_parameterization.h:27-39) for q.
+__device__ void Plus(const double* x, const double* delta, const int yaw_only, double* out) {
+  for (int k = 0; k < 3; ++k) out[k] = x[k] + delta[k];
+  for (int k = 3; k < 7; ++k) out[k] = x[k];
   if (!yaw_only) {
-    const double dx = s->delta[3] * s->scale[3], dy = s->delta[4] * s->scale[4], dz = s->delta[5] * s->scale[5];
+    const double dx = delta[3], dy = delta[4], dz = delta[5];
     const double norm = sqrt(dx * dx + dy * dy + dz * dz);
     if (norm > 0.0) {
       const double sin_by_norm = sin(norm) / norm;
       const double q_delta[4] = {cos(norm), sin_by_norm * dx, sin_by_norm * dy, sin_by_norm * dz};
-      QuatProduct(q_delta, q, out);
-      for (int k = 0; k < 4; ++k) q[k] = out[k];
+      QuatProduct(q_delta, x + 3, out + 3);
     }
   } else {
-    double c = s->delta[3] * s->scale[3];
+    double c = delta[3];
     c = c > 0.5 ? 0.5 : (c < -0.5 ? -0.5 : c);
     const double q_delta[4] = {sqrt(1. - c * c), 0., 0., c};
-    QuatProduct(q_delta, q, out);
-    for (int k = 0; k < 4; ++k) q[k] = out[k];
+    QuatProduct(q_delta, x + 3, out + 3);
   }
 }
 
-// Computes steps until one needs an evaluation (returns with the candidate in s->x) or the
-// solve ends (s->done). DenseLmProblem::Solve, the part of the loop before the evaluation.
-__device__ void NextCandidate(LmState* s, const ScanMatchArgs& a, EvalShared* ev) {
-  const int n = s->n;
-  double* A = ev->A;
-  while (s->iterations < a.max_num_iterations) {
-    ++s->iterations;
-    for (int i = 0; i < n * n; ++i) A[i] = s->Hs[i];
-    for (int i = 0; i < n; ++i) {
-      const double d = fmin(fmax(s->Hs[i * n + i], kMinLmDiagonal), kMaxLmDiagonal);
-      A[i * n + i] += d / s->radius;
-    }
-    bool step_ok = CholeskySolve(A, s->gs, n, ev->y, s->delta);
-    if (step_ok) {
-      for (int i = 0; i < n; ++i) s->delta[i] = -s->delta[i];
-      double gd = 0.0, dJd = 0.0;
-      for (int i = 0; i < n; ++i) {
-        gd += s->gs[i] * s->delta[i];
-        double t = 0.0;
-        for (int j = 0; j < n; ++j) t += s->Hs[i * n + j] * s->delta[j];
-        dJd += s->delta[i] * t;
-      }
-      s->model_cost_change = -(gd + 0.5 * dJd);
-      if (!(s->model_cost_change > 0.0)) step_ok = false;
-    }
-    if (!step_ok) {
-      s->radius /= s->decrease_factor;
-      s->decrease_factor *= 2.0;
-      if (s->radius < kMinRadius) {
-        s->termination = 4;
-        s->done = 1;
-        return;
-      }
-      continue;
-    }
-    for (int k = 0; k < 7; ++k) s->x_backup[k] = s->x[k];
-    s->step_norm2 = 0.0;
-    s->x_norm2 = 0.0;
-    for (int i = 0; i < n; ++i) s->step_norm2 += (s->delta[i] * s->scale[i]) * (s->delta[i] * s->scale[i]);
-    for (int k = 0; k < 7; ++k) s->x_norm2 += s->x[k] * s->x[k];
-    ApplyDelta(s, a.only_optimize_yaw);
-    s->phase = 1;
+// |Plus(x, -g) - x|_inf (TrustRegionMinimizer::EvaluateGradientAndJacobian).
+__device__ double GradientMaxNorm(const double* x, const double* g, const int n, const int yaw_only) {
+  double neg[6], moved[7];
+  for (int i = 0; i < n; ++i) neg[i] = -g[i];
+  Plus(x, neg, yaw_only, moved);
+  double v = 0.0;
+  for (int k = 0; k < 7; ++k) v = fmax(v, fabs(x[k] - moved[k]));
+  return v;
+}
+
+// Asks the core for the next step; publishes the candidate pose or ends the solve.
+__device__ void NextCandidate(LmState* s, const ScanMatchArgs& a) {
+  double delta[6];
+  if (s->core.NextStep(delta) != kEvaluate) {
+    s->done = 1;
     return;
   }
-  s->done = 1;  // iteration limit
+  Plus(s->x, delta, a.only_optimize_yaw, s->candidate_x);
+  for (int k = 0; k < 7; ++k) s->eval_x[k] = s->candidate_x[k];
+  s->phase = 1;
 }
 
-// The evaluation at s->x has been summed into S. DenseLmProblem::Solve, the part after it.
-__device__ void Advance(LmState* s, const ScanMatchArgs& a, EvalShared* ev) {
+// The evaluation at s->eval_x is in ev (cost, H, g). DenseLmProblem::Solve of
+// include/hg_dense_lm.h, the part between two evaluations. The candidate's normal equations are
+// only used if the step is accepted (the host loop re-evaluates at the accepted point, which
+// gives these same numbers).
+__device__ void Advance(LmState* s, const ScanMatchArgs& a, const EvalShared* ev) {
   const int n = s->n;
   if (s->phase == 0) {
-    s->cost = ev->cost;
-    for (int i = 0; i < n * n; ++i) s->H[i] = ev->H[i];
-    for (int i = 0; i < n; ++i) s->g[i] = ev->g[i];
-    ++s->cost_evaluations;
-    ++s->jacobian_evaluations;
-    s->initial_cost = s->cost;
-    s->minimum_cost = s->cost;
-    for (int j = 0; j < n; ++j) s->scale[j] = 1.0 / (1.0 + sqrt(fmax(0.0, s->H[j * n + j])));
-    ApplyScaling(s);
-    if (MaxAbsGradient(s) <= kGradientTolerance) {
-      s->termination = 2;
-      s->done = 1;
-      return;
-    }
-    s->radius = kInitialRadius;
-    s->decrease_factor = 2.0;
-    s->reference_cost = s->candidate_cost = s->minimum_cost = s->cost;
-    s->accumulated_reference_model_cost_change = 0.0;
-    s->accumulated_candidate_model_cost_change = 0.0;
-    s->num_consecutive_nonmonotonic_steps = 0;
-    for (int k = 0; k < 7; ++k) s->x_min[k] = s->x[k];
-    NextCandidate(s, a, ev);
+    TrustRegionOptions options;
+    options.max_num_iterations = a.max_num_iterations;
+    options.use_nonmonotonic_steps = a.use_nonmonotonic_steps != 0;
+    s->core.Start(n, options, ev->cost, ev->H, ev->g, GradientMaxNorm(s->x, ev->g, n, a.only_optimize_yaw));
+    NextCandidate(s, a);
     return;
   }
-  // Candidate evaluated: its normal equations are only used if the step is accepted (the
-  // host loop re-evaluates at the accepted point, which gives these same numbers).
-  double new_cost = ev->cost;
-  const double* Hn = ev->H;
-  const double* gn = ev->g;
-  ++s->cost_evaluations;
-  const bool eval_ok = isfinite(new_cost);
-  if (!eval_ok) new_cost = 1.7976931348623157e308;
-  double relative_decrease = (s->cost - new_cost) / s->model_cost_change;
-  if (a.use_nonmonotonic_steps) {
-    const double historical = (s->reference_cost - new_cost) /
-                              (s->accumulated_reference_model_cost_change + s->model_cost_change);
-    relative_decrease = fmax(relative_decrease, historical);
+  const double cost = isfinite(ev->cost) ? ev->cost : 1.7976931348623157e308;
+  double step_norm2 = 0.0, x_norm2 = 0.0;
+  for (int k = 0; k < 7; ++k) {
+    const double d = s->x[k] - s->candidate_x[k];
+    step_norm2 += d * d;
+    x_norm2 += s->x[k] * s->x[k];
   }
-  if (eval_ok && relative_decrease > kMinRelativeDecrease) {
-    ++s->successful_steps;
-    const double cost_change = s->cost - new_cost;
-    const double old_cost = s->cost;
-    s->cost = new_cost;
-    for (int i = 0; i < n * n; ++i) s->H[i] = Hn[i];
-    for (int i = 0; i < n; ++i) s->g[i] = gn[i];
-    ++s->jacobian_evaluations;
-    ApplyScaling(s);
-    const double t = 2.0 * relative_decrease - 1.0;
-    s->radius = s->radius / fmax(1.0 / 3.0, 1.0 - t * t * t);
-    s->radius = fmin(kMaxRadius, s->radius);
-    s->decrease_factor = 2.0;
-    if (a.use_nonmonotonic_steps) {
-      s->accumulated_candidate_model_cost_change += s->model_cost_change;
-      s->accumulated_reference_model_cost_change += s->model_cost_change;
-      if (s->cost < s->minimum_cost) {
-        s->minimum_cost = s->cost;
-        for (int k = 0; k < 7; ++k) s->x_min[k] = s->x[k];
-        s->num_consecutive_nonmonotonic_steps = 0;
-        s->candidate_cost = s->cost;
-        s->accumulated_candidate_model_cost_change = 0.0;
-      } else {
-        ++s->num_consecutive_nonmonotonic_steps;
-        if (s->cost > s->candidate_cost) {
-          s->candidate_cost = s->cost;
-          s->accumulated_candidate_model_cost_change = 0.0;
-        }
-      }
-      if (s->num_consecutive_nonmonotonic_steps == kMaxConsecutiveNonmonotonicSteps) {
-        s->reference_cost = s->candidate_cost;
-        s->accumulated_reference_model_cost_change = s->accumulated_candidate_model_cost_change;
-      }
-    } else {
-      s->minimum_cost = s->cost;
-    }
-    if (MaxAbsGradient(s) <= kGradientTolerance) {
-      s->termination = 2;
-      s->done = 1;
-      return;
-    }
-    if (fabs(cost_change) <= kFunctionTolerance * old_cost) {
-      s->termination = 1;
-      s->done = 1;
-      return;
-    }
-    if (sqrt(s->step_norm2) <= kParameterTolerance * (sqrt(s->x_norm2) + kParameterTolerance)) {
-      s->termination = 3;
-      s->done = 1;
-      return;
-    }
-  } else {
-    for (int k = 0; k < 7; ++k) s->x[k] = s->x_backup[k];
-    s->radius /= s->decrease_factor;
-    s->decrease_factor *= 2.0;
-    if (s->radius < kMinRadius) {
-      s->termination = 4;
-      s->done = 1;
-      return;
-    }
-    if (sqrt(s->step_norm2) <= kParameterTolerance * (sqrt(s->x_norm2) + kParameterTolerance)) {
-      s->termination = 3;
-      s->done = 1;
-      return;
+  const int action = s->core.CandidateEvaluated(cost, sqrt(step_norm2), sqrt(x_norm2));
+  if (action == kDone) {
+    s->done = 1;
+    return;
+  }
+  if (action == kAccepted) {
+    for (int k = 0; k < 7; ++k) s->x[k] = s->candidate_x[k];
+    if (s->core.Accepted(cost, ev->H, ev->g, GradientMaxNorm(s->x, ev->g, n, a.only_optimize_yaw))) {
+      for (int k = 0; k < 7; ++k) s->best[k] = s->x[k];
     }
   }
-  NextCandidate(s, a, ev);
+  NextCandidate(s, a);
 }
 
 // CLUSTER = 1: one CTA. CLUSTER = 8: a thread-block cluster; every CTA evaluates its share of the
@@ -418,12 +263,10 @@ __global__ void __cluster_dims__(CLUSTER, 1, 1) __launch_bounds__(kLmThreads, 1)
   const LmState* st0 = CLUSTER == 1 ? &st : cluster.map_shared_rank(&st, 0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (rank == 0 && tid == 0) {
-    for (int k = 0; k < 7; ++k) st.x[k] = a.pose[k];
+    for (int k = 0; k < 7; ++k) st.x[k] = st.best[k] = st.eval_x[k] = a.pose[k];
     st.n = a.only_optimize_yaw ? 4 : 6;
     st.phase = 0;
     st.done = 0;
-    st.termination = 0;
-    st.iterations = st.successful_steps = st.cost_evaluations = st.jacobian_evaluations = 0;
     const double z0 = a.target_q[0], z1 = -a.target_q[1], z2 = -a.target_q[2], z3 = -a.target_q[3];
     ev.M[0] = z1; ev.M[1] = z0; ev.M[2] = -z3; ev.M[3] = z2;
     ev.M[4] = z2; ev.M[5] = z3; ev.M[6] = z0; ev.M[7] = -z1;
@@ -432,8 +275,8 @@ __global__ void __cluster_dims__(CLUSTER, 1, 1) __launch_bounds__(kLmThreads, 1)
   if (CLUSTER == 1) __syncthreads(); else cluster.sync();
   for (;;) {
     // ---- evaluate this CTA's share of all scan blocks at the current pose -----------------
-    const double tx = st0->x[0], ty = st0->x[1], tz = st0->x[2];
-    const double qw = st0->x[3], qx = st0->x[4], qy = st0->x[5], qz = st0->x[6];
+    const double tx = st0->eval_x[0], ty = st0->eval_x[1], tz = st0->eval_x[2];
+    const double qw = st0->eval_x[3], qx = st0->eval_x[4], qy = st0->eval_x[5], qz = st0->eval_x[6];
     double S[kTerms];
 #pragma unroll
     for (int e = 0; e < kTerms; ++e) S[e] = 0.0;
@@ -498,7 +341,7 @@ __global__ void __cluster_dims__(CLUSTER, 1, 1) __launch_bounds__(kLmThreads, 1)
         }
         __syncthreads();
       }
-      AssembleNormal(a, CLUSTER > 1 ? grand : totals, st.x, st.n, tid, &ev);
+      AssembleNormal(a, CLUSTER > 1 ? grand : totals, st.eval_x, st.n, tid, &ev);
       if (tid == 0) Advance(&st, a, &ev);
     }
     if (CLUSTER == 1) __syncthreads(); else cluster.sync();  // the next pose / the stop flag is published
@@ -506,19 +349,15 @@ __global__ void __cluster_dims__(CLUSTER, 1, 1) __launch_bounds__(kLmThreads, 1)
   }
   if (CLUSTER > 1) cluster.sync();  // nobody leaves while CTA 0's shared memory may still be read
   if (rank == 0 && tid == 0) {
-    double cost = st.cost;
-    if (a.use_nonmonotonic_steps && st.minimum_cost < cost) {  // Ceres reports the best point seen
-      for (int k = 0; k < 7; ++k) st.x[k] = st.x_min[k];
-      cost = st.minimum_cost;
-    }
-    for (int k = 0; k < 7; ++k) a.out[k] = st.x[k];
-    a.out[7] = st.initial_cost;
-    a.out[8] = cost;
-    a.out[9] = st.iterations;
-    a.out[10] = st.successful_steps;
-    a.out[11] = st.cost_evaluations;
-    a.out[12] = st.jacobian_evaluations;
-    a.out[13] = st.termination;
+    // Ceres hands back the lowest-cost accepted iterate.
+    for (int k = 0; k < 7; ++k) a.out[k] = st.best[k];
+    a.out[7] = st.core.initial_cost;
+    a.out[8] = st.core.minimum_cost;
+    a.out[9] = st.core.iteration;
+    a.out[10] = st.core.num_successful_steps;
+    a.out[11] = st.core.num_cost_evaluations;
+    a.out[12] = st.core.num_jacobian_evaluations;
+    a.out[13] = st.core.termination;
   }
 }
 
@@ -579,10 +418,8 @@ int ScanMatchOnDevice(int num_clouds, const float* const* clouds, const int32_t*
   HG_CUDA(cudaGetLastError());
   HG_CUDA(cudaMemcpyAsync(h_out, d_out, 14 * sizeof(double), cudaMemcpyDeviceToHost, stream));
   HG_CUDA(cudaStreamSynchronize(stream));
-  if (static_cast<int>(h_out[13]) == 4) {
-    SetError("hg_scan_match: the trust region collapsed (no descent step could be computed)");
-    return HG_ERR_CUDA;
-  }
+  // A solve that Ceres would end as FAILURE (five invalid steps in a row) still returns the best
+  // pose seen: the reference does not look at the summary's termination type.
   for (int k = 0; k < 7; ++k) pose_out[k] = h_out[k];
   if (summary_out) {
     for (int k = 0; k < 6; ++k) summary_out[k] = h_out[7 + k];

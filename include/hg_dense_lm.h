@@ -10,16 +10,16 @@
 // Ceres is linked, the cost functions of this library plug into it directly
 // (they implement ceres::CostFunction::Evaluate) and this header is unused.
 //
-// The loop follows Ceres' published TrustRegionMinimizer + LevenbergMarquardt
-// strategy: Jacobi column scaling 1/(1+||J_j||), damping diag(J'J)/radius
-// clamped to [1e-6, 1e32], step quality rho = cost change / model cost change
-// (optionally the non-monotonic variant), radius /= max(1/3, 1-(2 rho-1)^3)
-// on success, radius /= 2^k on failure, and Ceres' default function /
-// gradient / parameter tolerances. The linear step solves the damped normal
-// equations by Cholesky instead of QR of the augmented Jacobian (same minimiser).
-// Only J'J, J'r and the cost are ever needed, so a cost function that can produce
-// those directly (member NormalEquations — the GPU blocks do, without
-// materialising their Jacobian) is asked for them instead of for rows.
+// The solve is the trust-region loop of include/hg_trust_region.h — Ceres 1.13's
+// TrustRegionMinimizer / LevenbergMarquardtStrategy / TrustRegionStepEvaluator restated
+// function by function — driven here with host-side evaluations; the device-side
+// solve of csrc/scan_match.cu drives the same state machine. This class adds what
+// Ceres' Problem / Evaluator do around it: parameter blocks with local
+// parameterizations (Plus and its Jacobian), the projection of every residual
+// block's Jacobian onto the tangent spaces, and the projected gradient norm
+// |Plus(x, -g) - x|. Only J'J, J'r and the cost are ever needed, so a cost function
+// that can produce those directly (member NormalEquations — the GPU blocks do,
+// without materialising their Jacobian) is asked for them instead of for rows.
 //
 // Templated on the cost-function type so that the same solver drives the GPU
 // cost functions of this library and (in tests) the CPU oracle's.
@@ -31,6 +31,8 @@
 #include <limits>
 #include <vector>
 
+#include "hg_trust_region.h"
+
 namespace hg {
 
 enum class LocalParameterization {
@@ -41,19 +43,22 @@ enum class LocalParameterization {
   kYawOnlyQuaternion = 2,
 };
 
-struct LmOptions {
-  int max_num_iterations = 10;
-  bool use_nonmonotonic_steps = false;
-  int max_consecutive_nonmonotonic_steps = 5;
-  double initial_trust_region_radius = 1e4;
-  double max_trust_region_radius = 1e16;
-  double min_trust_region_radius = 1e-32;
-  double min_relative_decrease = 1e-3;
-  double min_lm_diagonal = 1e-6;
-  double max_lm_diagonal = 1e32;
-  double function_tolerance = 1e-6;
-  double gradient_tolerance = 1e-10;
-  double parameter_tolerance = 1e-8;
+// One entry of ceres::Solver::Summary::iterations (the fields the tests look at).
+struct LmIteration {
+  int iteration = 0;
+  double cost = 0.0;               // cost at the current iterate x
+  double candidate_cost = 0.0;     // cost at the candidate of this iteration
+  double model_cost_change = 0.0;
+  double relative_decrease = 0.0;  // step quality
+  double radius = 0.0;             // after this iteration's update
+  double gradient_max_norm = 0.0;
+  bool successful = false;
+};
+
+struct LmOptions : TrustRegionOptions {
+  LmOptions() { max_num_iterations = 10; }
+  // Optional per-iteration log (Ceres' Solver::Summary::iterations), for tests.
+  std::vector<LmIteration>* trace = nullptr;
 };
 
 struct LmSummary {
@@ -63,12 +68,17 @@ struct LmSummary {
   int num_successful_steps = 0;
   int num_cost_evaluations = 0;  // residual-only + residual+Jacobian
   int num_jacobian_evaluations = 0;
-  int termination = 0;  // 0 max iterations, 1 function tol, 2 gradient tol, 3 parameter tol, 4 failure
+  // 0 max iterations, 1 function tolerance, 2 gradient tolerance, 3 parameter tolerance,
+  // 4 failure (evaluation failed, or 5 invalid steps in a row), 5 minimum trust-region radius
+  int termination = 0;
 };
 
 template <typename CostFunctionT>
 class DenseLmProblem {
  public:
+  // Tangent-space size limit of Solve (the fixed-size arrays of TrustRegionCore).
+  static constexpr int kMaxLocalParameters = 24;
+
   // Returns the block id. 'values' stays owned by the caller and is updated in place.
   int AddParameterBlock(double* values, int size, LocalParameterization p) {
     Block b;
@@ -118,174 +128,76 @@ class DenseLmProblem {
     return num_local_;
   }
 
+  // ceres::Solve for this problem: the trust-region loop of include/hg_trust_region.h (Ceres
+  // 1.13's TrustRegionMinimizer, restated) driven with host-side evaluations.
   LmSummary Solve(const LmOptions& options) {
     LmSummary summary;
     Layout();
     const int n = num_local_;
-    std::vector<double> H(static_cast<size_t>(n) * n), g(n), scale(n);
-    std::vector<double> Hs(static_cast<size_t>(n) * n), gs(n), A(static_cast<size_t>(n) * n);
-    std::vector<double> delta(n), x_backup;
-
-    double cost = 0.0;
-    if (!EvaluateNormal(&cost, H.data(), g.data())) {
-      summary.termination = 4;
+    if (n > kMaxLocalParameters) {
+      summary.termination = kTerminationFailure;
       return summary;
     }
-    ++summary.num_cost_evaluations;
-    ++summary.num_jacobian_evaluations;
-    summary.initial_cost = cost;
-    summary.final_cost = cost;
-
-    // Jacobi scaling, computed once from the initial Jacobian's column norms (Ceres).
-    for (int j = 0; j < n; ++j) scale[j] = 1.0 / (1.0 + std::sqrt(std::max(0.0, H[static_cast<size_t>(j) * n + j])));
-    auto apply_scaling = [&]() {
-      for (int a = 0; a < n; ++a) {
-        gs[a] = g[a] * scale[a];
-        for (int b = 0; b < n; ++b) Hs[static_cast<size_t>(a) * n + b] = H[static_cast<size_t>(a) * n + b] * scale[a] * scale[b];
-      }
-    };
-    apply_scaling();
-    auto max_abs_gradient = [&]() {
+    std::vector<double> H(static_cast<size_t>(n) * n), g(n), delta(n), x, candidate_x, best, tmp;
+    SaveState(&x);
+    best = x;
+    double cost = 0.0;
+    // |Plus(x, -g) - x|_inf: the gradient norm Ceres tests (EvaluateGradientAndJacobian).
+    auto gradient_max_norm = [&]() {
+      for (int a = 0; a < n; ++a) delta[a] = -g[a];
+      Plus(x, delta, &tmp);
       double v = 0.0;
-      for (int a = 0; a < n; ++a) v = std::max(v, std::fabs(g[a]));
+      for (size_t k = 0; k < x.size(); ++k) v = std::max(v, std::fabs(x[k] - tmp[k]));
       return v;
     };
-    if (max_abs_gradient() <= options.gradient_tolerance) {
-      summary.termination = 2;
+    auto log_iteration = [&](const TrustRegionCore<kMaxLocalParameters>& core) {
+      if (options.trace == nullptr) return;
+      LmIteration it;
+      it.iteration = core.iteration;
+      it.cost = core.x_cost;
+      it.candidate_cost = core.candidate_cost;
+      it.model_cost_change = core.model_cost_change;
+      it.relative_decrease = core.step_quality;
+      it.radius = core.radius;
+      it.gradient_max_norm = core.gradient_max_norm;
+      it.successful = core.step_is_successful;
+      options.trace->push_back(it);
+    };
+    TrustRegionCore<kMaxLocalParameters> core;
+    if (!EvaluateNormal(&cost, H.data(), g.data())) {
+      summary.termination = kTerminationFailure;
       return summary;
     }
-
-    double radius = options.initial_trust_region_radius;
-    double decrease_factor = 2.0;
-    // Non-monotonic bookkeeping (Ceres trust_region_minimizer).
-    double reference_cost = cost, candidate_cost = cost, minimum_cost = cost;
-    double accumulated_reference_model_cost_change = 0.0;
-    double accumulated_candidate_model_cost_change = 0.0;
-    int num_consecutive_nonmonotonic_steps = 0;
-    std::vector<double> x_min;
-    SaveState(&x_min);
-
-    for (int iter = 0; iter < options.max_num_iterations; ++iter) {
-      ++summary.num_iterations;
-      // Damped normal equations.
-      A = Hs;
-      for (int a = 0; a < n; ++a) {
-        const double d = std::min(std::max(Hs[static_cast<size_t>(a) * n + a], options.min_lm_diagonal),
-                                  options.max_lm_diagonal);
-        A[static_cast<size_t>(a) * n + a] += d / radius;
-      }
-      bool step_ok = CholeskySolve(A, gs, n, &delta);
-      double model_cost_change = 0.0;
-      if (step_ok) {
-        for (int a = 0; a < n; ++a) delta[a] = -delta[a];
-        // -(J d)'(r + J d / 2) = -(g'd + d'J'J d / 2)
-        double gd = 0.0, dJd = 0.0;
-        for (int a = 0; a < n; ++a) {
-          gd += gs[a] * delta[a];
-          double t = 0.0;
-          for (int b = 0; b < n; ++b) t += Hs[static_cast<size_t>(a) * n + b] * delta[b];
-          dJd += delta[a] * t;
-        }
-        model_cost_change = -(gd + 0.5 * dJd);
-        if (!(model_cost_change > 0.0)) step_ok = false;
-      }
-      if (!step_ok) {
-        radius /= decrease_factor;
-        decrease_factor *= 2.0;
-        if (radius < options.min_trust_region_radius) {
-          summary.termination = 4;
-          break;
-        }
-        continue;
-      }
-      // Candidate.
-      SaveState(&x_backup);
-      double step_norm2 = 0.0, x_norm2 = 0.0;
-      for (int a = 0; a < n; ++a) step_norm2 += (delta[a] * scale[a]) * (delta[a] * scale[a]);
-      for (const Block& b : blocks_)
-        for (int k = 0; k < b.size; ++k) x_norm2 += b.values[k] * b.values[k];
-      ApplyDelta(delta, scale);
-      double new_cost = 0.0;
-      const bool eval_ok = EvaluateCost(&new_cost);
-      ++summary.num_cost_evaluations;
-      if (!eval_ok) new_cost = std::numeric_limits<double>::max();
-      double relative_decrease = (cost - new_cost) / model_cost_change;
-      if (options.use_nonmonotonic_steps) {
-        const double historical =
-            (reference_cost - new_cost) / (accumulated_reference_model_cost_change + model_cost_change);
-        relative_decrease = std::max(relative_decrease, historical);
-      }
-      if (eval_ok && relative_decrease > options.min_relative_decrease) {
-        // Accept.
-        ++summary.num_successful_steps;
-        const double cost_change = cost - new_cost;
-        const double old_cost = cost;
+    core.Start(n, options, cost, H.data(), g.data(), gradient_max_norm());
+    log_iteration(core);
+    while (core.NextStep(delta.data()) == kEvaluate) {
+      Plus(x, delta, &candidate_x);
+      RestoreState(candidate_x);
+      double candidate_cost = 0.0;
+      if (!EvaluateCost(&candidate_cost)) candidate_cost = std::numeric_limits<double>::max();
+      double step_norm2 = 0.0;
+      for (size_t k = 0; k < x.size(); ++k) step_norm2 += (x[k] - candidate_x[k]) * (x[k] - candidate_x[k]);
+      const int action = core.CandidateEvaluated(candidate_cost, std::sqrt(step_norm2), Norm(x));
+      if (action == kAccepted) {
+        x = candidate_x;
         if (!EvaluateNormal(&cost, H.data(), g.data())) {
-          summary.termination = 4;
+          core.Fail();
           break;
         }
-        ++summary.num_jacobian_evaluations;
-        apply_scaling();
-        radius = radius / std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * relative_decrease - 1.0, 3));
-        radius = std::min(options.max_trust_region_radius, radius);
-        decrease_factor = 2.0;
-        if (options.use_nonmonotonic_steps) {
-          accumulated_candidate_model_cost_change += model_cost_change;
-          accumulated_reference_model_cost_change += model_cost_change;
-          if (cost < minimum_cost) {
-            minimum_cost = cost;
-            SaveState(&x_min);
-            num_consecutive_nonmonotonic_steps = 0;
-            candidate_cost = cost;
-            accumulated_candidate_model_cost_change = 0.0;
-          } else {
-            ++num_consecutive_nonmonotonic_steps;
-            if (cost > candidate_cost) {
-              candidate_cost = cost;
-              accumulated_candidate_model_cost_change = 0.0;
-            }
-          }
-          if (num_consecutive_nonmonotonic_steps == options.max_consecutive_nonmonotonic_steps) {
-            reference_cost = candidate_cost;
-            accumulated_reference_model_cost_change = accumulated_candidate_model_cost_change;
-          }
-        } else {
-          minimum_cost = cost;
-        }
-        if (max_abs_gradient() <= options.gradient_tolerance) {
-          summary.termination = 2;
-          break;
-        }
-        if (std::fabs(cost_change) <= options.function_tolerance * old_cost) {
-          summary.termination = 1;
-          break;
-        }
-        if (std::sqrt(step_norm2) <=
-            options.parameter_tolerance * (std::sqrt(x_norm2) + options.parameter_tolerance)) {
-          summary.termination = 3;
-          break;
-        }
-      } else {
-        RestoreState(x_backup);
-        radius /= decrease_factor;
-        decrease_factor *= 2.0;
-        if (radius < options.min_trust_region_radius) {
-          summary.termination = 4;
-          break;
-        }
-        if (std::sqrt(step_norm2) <=
-            options.parameter_tolerance * (std::sqrt(x_norm2) + options.parameter_tolerance)) {
-          summary.termination = 3;
-          break;
-        }
+        if (core.Accepted(cost, H.data(), g.data(), gradient_max_norm())) best = x;
       }
+      log_iteration(core);
+      if (action == kDone) break;
     }
-    if (options.use_nonmonotonic_steps && minimum_cost < cost) {
-      // Ceres reports the best point seen.
-      RestoreState(x_min);
-      cost = minimum_cost;
-    }
-    summary.final_cost = cost;
+    // Ceres hands back the lowest-cost iterate that was accepted.
+    RestoreState(best);
+    summary.initial_cost = core.initial_cost;
+    summary.final_cost = core.minimum_cost;
+    summary.num_iterations = core.iteration;
+    summary.num_successful_steps = core.num_successful_steps;
+    summary.num_cost_evaluations = core.num_cost_evaluations;
+    summary.num_jacobian_evaluations = core.num_jacobian_evaluations;
+    summary.termination = core.termination;
     return summary;
   }
 
@@ -337,32 +249,46 @@ class DenseLmProblem {
     zw[3] = z[0] * w[3] + z[1] * w[2] - z[2] * w[1] + z[3] * w[0];
   }
 
-  void ApplyDelta(const std::vector<double>& delta, const std::vector<double>& scale) {
-    for (Block& b : blocks_) {
+  // Evaluator::Plus: ambient x (all blocks, SaveState order) moved by the tangent-space delta
+  // of the non-constant blocks. ceres::QuaternionParameterization::Plus /
+  // YawOnlyQuaternionPlus (rotation_parameterization.h:27-39).
+  void Plus(const std::vector<double>& x, const std::vector<double>& delta, std::vector<double>* out) const {
+    *out = x;
+    size_t at = 0;
+    for (const Block& b : blocks_) {
+      const double* xb = &x[at];
+      double* ob = &(*out)[at];
+      at += b.size;
       if (b.constant) continue;
       const double* d = &delta[b.local_offset];
-      const double* s = &scale[b.local_offset];
       if (b.param == LocalParameterization::kIdentity) {
-        for (int k = 0; k < b.size; ++k) b.values[k] += d[k] * s[k];
+        for (int k = 0; k < b.size; ++k) ob[k] = xb[k] + d[k];
       } else if (b.param == LocalParameterization::kQuaternion) {
-        const double dx = d[0] * s[0], dy = d[1] * s[1], dz = d[2] * s[2];
-        const double norm = std::sqrt(dx * dx + dy * dy + dz * dz);
+        const double norm = std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
         if (norm > 0.0) {
           const double sin_by_norm = std::sin(norm) / norm;
-          const double q_delta[4] = {std::cos(norm), sin_by_norm * dx, sin_by_norm * dy, sin_by_norm * dz};
-          double out[4];
-          QuatProduct(q_delta, b.values, out);
-          for (int k = 0; k < 4; ++k) b.values[k] = out[k];
+          const double q_delta[4] = {std::cos(norm), sin_by_norm * d[0], sin_by_norm * d[1], sin_by_norm * d[2]};
+          QuatProduct(q_delta, xb, ob);
         }
       } else {
-        double c = d[0] * s[0];
+        double c = d[0];
         c = c > 0.5 ? 0.5 : (c < -0.5 ? -0.5 : c);
         const double q_delta[4] = {std::sqrt(1. - c * c), 0., 0., c};
-        double out[4];
-        QuatProduct(q_delta, b.values, out);
-        for (int k = 0; k < 4; ++k) b.values[k] = out[k];
+        QuatProduct(q_delta, xb, ob);
       }
     }
+  }
+
+  // 2-norm over the non-constant blocks (Ceres' reduced program holds only those).
+  double Norm(const std::vector<double>& x) const {
+    double s = 0.0;
+    size_t at = 0;
+    for (const Block& b : blocks_) {
+      if (!b.constant)
+        for (int k = 0; k < b.size; ++k) s += x[at + k] * x[at + k];
+      at += b.size;
+    }
+    return std::sqrt(s);
   }
 
   // d(x (+) delta)/d delta at delta = 0, row-major size x local_size.
@@ -565,36 +491,6 @@ class DenseLmProblem {
         }
       }
       row0 += nr;
-    }
-    return true;
-  }
-
-  static bool CholeskySolve(std::vector<double> A, const std::vector<double>& b, int n,
-                            std::vector<double>* x) {
-    // In-place lower Cholesky.
-    for (int j = 0; j < n; ++j) {
-      double d = A[static_cast<size_t>(j) * n + j];
-      for (int k = 0; k < j; ++k) d -= A[static_cast<size_t>(j) * n + k] * A[static_cast<size_t>(j) * n + k];
-      if (!(d > 0.0) || !std::isfinite(d)) return false;
-      const double l = std::sqrt(d);
-      A[static_cast<size_t>(j) * n + j] = l;
-      for (int i = j + 1; i < n; ++i) {
-        double s = A[static_cast<size_t>(i) * n + j];
-        for (int k = 0; k < j; ++k) s -= A[static_cast<size_t>(i) * n + k] * A[static_cast<size_t>(j) * n + k];
-        A[static_cast<size_t>(i) * n + j] = s / l;
-      }
-    }
-    std::vector<double> y(n);
-    for (int i = 0; i < n; ++i) {
-      double s = b[i];
-      for (int k = 0; k < i; ++k) s -= A[static_cast<size_t>(i) * n + k] * y[k];
-      y[i] = s / A[static_cast<size_t>(i) * n + i];
-    }
-    x->assign(n, 0.0);
-    for (int i = n - 1; i >= 0; --i) {
-      double s = y[i];
-      for (int k = i + 1; k < n; ++k) s -= A[static_cast<size_t>(k) * n + i] * (*x)[k];
-      (*x)[i] = s / A[static_cast<size_t>(i) * n + i];
     }
     return true;
   }

@@ -296,6 +296,9 @@ double orc_cost_time(void* c, const double* const* params, int repeats, int thre
   return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
+int orc_scan_match_trace(int, const float* const*, const int*, void* const*, const double*, double, double, int, int,
+                         int, const double*, const double*, double*, double*, double*, int);
+
 // ---- CeresScanMatcher3D::Match restated on the dense LM of include/hg_dense_lm.h
 // (ceres_scan_matcher_3d.cc:72-95, :120-172). clouds[i]/grids[i] pairs.
 int orc_scan_match(int num_clouds, const float* const* clouds, const int* cloud_sizes,
@@ -304,6 +307,19 @@ int orc_scan_match(int num_clouds, const float* const* clouds, const int* cloud_
                    int max_num_iterations, int use_nonmonotonic_steps,
                    const double* target_translation, const double* initial_pose /* t3 q4 */,
                    double* pose_out /* t3 q4 */, double* summary_out /* initial, final, iters */) {
+  return orc_scan_match_trace(num_clouds, clouds, cloud_sizes, grids, occupied_space_weights, translation_weight,
+                              rotation_weight, only_optimize_yaw, max_num_iterations, use_nonmonotonic_steps,
+                              target_translation, initial_pose, pose_out, summary_out, nullptr, 0);
+}
+
+// Same, and the per-iteration log (Solver::Summary::iterations): 7 doubles per entry —
+// iteration, cost, candidate cost, model cost change, step quality, radius, successful.
+int orc_scan_match_trace(int num_clouds, const float* const* clouds, const int* cloud_sizes,
+                         void* const* grids, const double* occupied_space_weights,
+                         double translation_weight, double rotation_weight, int only_optimize_yaw,
+                         int max_num_iterations, int use_nonmonotonic_steps,
+                         const double* target_translation, const double* initial_pose,
+                         double* pose_out, double* summary_out, double* trace_out, int trace_capacity) {
   double t[3] = {initial_pose[0], initial_pose[1], initial_pose[2]};
   double q[4] = {initial_pose[3], initial_pose[4], initial_pose[5], initial_pose[6]};
   hg::DenseLmProblem<CostFunction> problem;
@@ -333,7 +349,15 @@ int orc_scan_match(int num_clouds, const float* const* clouds, const int* cloud_
   hg::LmOptions options;
   options.max_num_iterations = max_num_iterations;
   options.use_nonmonotonic_steps = use_nonmonotonic_steps != 0;
+  std::vector<hg::LmIteration> trace;
+  if (trace_out != nullptr) options.trace = &trace;
   const hg::LmSummary s = problem.Solve(options);
+  for (size_t i = 0; i < trace.size() && static_cast<int>(i) < trace_capacity; ++i) {
+    double* o = trace_out + 7 * i;
+    o[0] = trace[i].iteration; o[1] = trace[i].cost; o[2] = trace[i].candidate_cost;
+    o[3] = trace[i].model_cost_change; o[4] = trace[i].relative_decrease; o[5] = trace[i].radius;
+    o[6] = trace[i].successful ? 1.0 : 0.0;
+  }
   for (int k = 0; k < 3; ++k) pose_out[k] = t[k];
   for (int k = 0; k < 4; ++k) pose_out[3 + k] = q[k];
   if (summary_out != nullptr) {

@@ -73,6 +73,7 @@ def lib():
         L.orc_cost_time.restype = c_d
         L.orc_cost_time.argtypes = [vp, vp, c_i, c_i]
         L.orc_scan_match.argtypes = [c_i, vp, vp, vp, vp, c_d, c_d, c_i, c_i, c_i, vp, vp, vp, vp]
+        L.orc_scan_match_trace.argtypes = [c_i, vp, vp, vp, vp, c_d, c_d, c_i, c_i, c_i, vp, vp, vp, vp, vp, c_i]
         L.orc_stack_new.restype = vp
         L.orc_stack_new.argtypes = [vp, c_i, c_i]
         L.orc_stack_free.argtypes = [vp]
@@ -326,7 +327,9 @@ def translation_delta(scaling_factor, target, translation, jacobian=False):
 
 def scan_match(clouds, grids, weights, translation_weight, rotation_weight, initial_pose,
                target_translation=None, only_optimize_yaw=False, max_num_iterations=10,
-               use_nonmonotonic_steps=True):
+               use_nonmonotonic_steps=True, trace=None):
+    """trace: a list that receives one row per solver iteration (iteration, cost, candidate cost,
+    model cost change, step quality, radius, successful)."""
     clouds = [_f32(c).reshape(-1, 3) for c in clouds]
     carr = (vp * len(clouds))(*[c.ctypes.data for c in clouds])
     sizes = _i32([len(c) for c in clouds])
@@ -336,10 +339,13 @@ def scan_match(clouds, grids, weights, translation_weight, rotation_weight, init
     target = _f64(initial_pose[:3] if target_translation is None else target_translation)
     pose = np.zeros(7)
     summary = np.zeros(6)
-    term = lib().orc_scan_match(len(clouds), carr, _p(sizes), garr, _p(weights), translation_weight,
-                                rotation_weight, int(only_optimize_yaw), max_num_iterations,
-                                int(use_nonmonotonic_steps), _p(target), _p(initial_pose), _p(pose),
-                                _p(summary))
+    rows = np.zeros((max_num_iterations + 2, 7))
+    term = lib().orc_scan_match_trace(len(clouds), carr, _p(sizes), garr, _p(weights), translation_weight,
+                                      rotation_weight, int(only_optimize_yaw), max_num_iterations,
+                                      int(use_nonmonotonic_steps), _p(target), _p(initial_pose), _p(pose),
+                                      _p(summary), _p(rows), len(rows))
+    if trace is not None:
+        trace.extend(rows[:int(summary[2]) + 1].tolist())
     return pose, summary, term
 
 

@@ -791,6 +791,34 @@ def test_config_c2_full_size(oracle, hg):
         assert (J2[k].reshape(64, 100000, width)[:, ::-1] == J[k].reshape(64, 100000, width)).all()
 
 
+@pytest.mark.parametrize("initial", [0, 1, 2, 3, 4])
+def test_reference_ceres_fixture_on_gpu(oracle, hg, initial):
+    """ceres_scan_matcher_3d_test.cc:36-117 through hg_scan_match at the reference's settings
+    (use_nonmonotonic_steps, max_num_iterations = 10; final cost < 1e-2, IsNearly 3e-2): the
+    one-launch device solve and the host loop over GPU costs, each against the same solver over
+    the oracle's Jet costs."""
+    import os
+    from test_oracle_reference_kats import CERES_FIXTURE_STARTS, ceres_fixture, is_nearly
+    cloud, grid_points, start, expected_t, expected_q = ceres_fixture(None, CERES_FIXTURE_STARTS[initial])
+    og = oracle.Grid.prob(1.0)
+    og.set_probability(og.cell_index(grid_points), 1.0)
+    ex, ev = og.export()
+    gg = hg.Grid.prob(1.0, ex, ev, grid_size=og.grid_size)
+    kw = dict(max_num_iterations=10, use_nonmonotonic_steps=True)
+    pose_o, sum_o, _ = oracle.scan_match([cloud], [og], [1.0], 0.01, 0.1, start, **kw)
+    for host in (False, True):
+        if host:
+            os.environ["HG_SCAN_MATCH_HOST"] = "1"
+        try:
+            pose, summary = hg.scan_match([cloud], [gg], [1.0], 0.01, 0.1, start, **kw)
+        finally:
+            os.environ.pop("HG_SCAN_MATCH_HOST", None)
+        assert abs(summary[1]) < 1e-2
+        assert is_nearly(pose, expected_t, expected_q, 3e-2)
+        assert (summary[2:] == sum_o[2:]).all(), (summary, sum_o)  # same accept / reject sequence
+        assert np.abs(pose - pose_o).max() < 1e-4
+
+
 def test_device_scan_match_equals_host_loop(oracle, hg, world):
     """hg_scan_match solves on the device in one launch (scan_match.cu); HG_SCAN_MATCH_HOST=1 selects
     the host loop of include/hg_dense_lm.h over the fused normal equations. Same solver, same
