@@ -117,6 +117,7 @@ SYMBOLS = {
     "hg_batch_update_points": (c_i, [vp, vp, c_i]),
     "hg_batch_evaluate": (c_i, [vp, vp, c_i, vp, vp, c_i, vp, vp, vp, vp, vp, vp]),
     "hg_batch_normal_equations": (c_i, [vp, vp, c_i, vp, vp, vp, vp, vp]),
+    "hg_batch_level_usage": (c_i, [vp, vp, c_i, vp, vp, vp]),
     "hg_scan_match": (c_i, [c_i, vp, vp, vp, vp, c_d, c_d, c_i, c_i, c_i, vp, vp, vp, vp]),
     "hg_stack_build": (c_i, [vp, c_i, c_i, vp]),
     "hg_stack_destroy": (None, [vp]),
@@ -482,6 +483,16 @@ class Batch:
         _check(lib().hg_batch_normal_equations(self.h, _p(poses), len(poses), _p(i0), _p(i1), _p(JtJ), _p(Jtr),
                                                _p(cost)))
         return JtJ, Jtr, cost
+
+
+    def level_usage(self, poses, i0, i1=None):
+        """Points answered by each pyramid level, last entry = by none (multi-resolution kinds)."""
+        poses = _f64(poses).reshape(-1, 7)
+        i0 = _i32(i0)
+        i1 = None if i1 is None else _i32(i1)
+        counts = np.zeros(len(self.grids) + 1, np.int64)
+        _check(lib().hg_batch_level_usage(self.h, _p(poses), len(poses), _p(i0), _p(i1), _p(counts)))
+        return counts
 
 
 def scan_match(clouds, grids, weights, translation_weight, rotation_weight, initial_pose,

@@ -300,6 +300,14 @@ int hg_batch_normal_equations(const hg_batch* batch, const double* poses, int nu
                               const int32_t* pose_index0, const int32_t* pose_index1, double* JtJ,
                               double* Jtr, double* cost_out);
 
+/* Diagnostic for multi-resolution TSDF batches: how many points each pyramid level answers
+ * (InterpolatedMultiResolutionTSDF::GetTSD takes the first level whose eight corners are all
+ * observed, interpolated_multi_resolution_tsdf.h:99-106). counts[l] for level l of the batch's
+ * grid list, counts[num_grids] for points no level answers (they read the finest level's
+ * minimum TSD, :136). counts has num_grids + 1 entries. */
+int hg_batch_level_usage(const hg_batch* batch, const double* poses, int num_poses,
+                         const int32_t* pose_index0, const int32_t* pose_index1, int64_t* counts);
+
 /* CeresScanMatcher3D::Match (ceres_scan_matcher_3d.cc:72-95, problem set-up
  * :120-172) for num_clouds (cloud, grid) pairs: occupied-space / TSDF blocks
  * scaled by occupied_space_weights[i] / sqrt(N_i), plus the translation and
