@@ -347,128 +347,6 @@ __global__ void __launch_bounds__(kThreads) LevelUsageKernel(const CostArgs a, u
   }
 }
 
-// EXPERIMENT (HG_COST_PIPE=<CTAs per SM>): multi-resolution TSDF residual + Jacobian with the finest
-// level's stencil loads of the NEXT point issued before the current point's blend, chain rule and
-// stores, so two points' gathers are in flight per thread. Same arithmetic as
-// CostKernel<2, TWO_POSE, false>.
-template <bool TWO_POSE, int MINB>
-__global__ void __launch_bounds__(kThreads, MINB) CostKernelPipelined(const CostArgs a) {
-  constexpr int NC = TWO_POSE ? 14 : 7;
-  __shared__ BlockDev sb;
-  const TileDev tile = a.tiles[blockIdx.x];
-  {
-    const int words = sizeof(BlockDev) / 8;
-    const double* src = reinterpret_cast<const double*>(a.blocks + tile.block);
-    double* dst = reinterpret_cast<double*>(&sb);
-    if (threadIdx.x < words) dst[threadIdx.x] = src[threadIdx.x];
-  }
-  __syncthreads();
-  const int tile_end = min(sb.n, tile.start + a.tile_points);
-  const int first = tile.start + threadIdx.x;
-  // p2: point two rounds ahead (loading); (p1, w1, raw1): next round's point, world point, stencil.
-  float p2x = 0.f, p2y = 0.f, p2z = 0.f, p1x = 0.f, p1y = 0.f, p1z = 0.f;
-  double w1x = 0.0, w1y = 0.0, w1z = 0.0;
-  float raw1[8];
-#pragma unroll
-  for (int k = 0; k < 8; ++k) raw1[k] = 0.f;
-  if (first < tile_end) {
-    const float* pp = a.points + (sb.point_offset + first) * a.stride;
-    p1x = __ldcs(pp); p1y = __ldcs(pp + 1); p1z = __ldcs(pp + 2);
-    const WorldPoint w = TransformPoint(sb.q[0], sb.q[1], sb.q[2], sb.q[3], sb.t[0], sb.t[1], sb.t[2],
-                                        static_cast<double>(p1x), static_cast<double>(p1y), static_cast<double>(p1z));
-    w1x = w.x; w1y = w.y; w1z = w.z;
-    FetchLevelStencil(a.grids[0], w1x, w1y, w1z, raw1);
-  }
-  if (first + kThreads < tile_end) {
-    const float* pp = a.points + (sb.point_offset + first + kThreads) * a.stride;
-    p2x = __ldcs(pp); p2y = __ldcs(pp + 1); p2z = __ldcs(pp + 2);
-  }
-  for (int base = tile.start; base < tile_end; base += kThreads) {
-    const int i = base + threadIdx.x;
-    if (i >= tile_end) break;
-    const double px = static_cast<double>(p1x), py = static_cast<double>(p1y), pz = static_cast<double>(p1z);
-    const double wx = w1x, wy = w1y, wz = w1z;
-    float raw[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) raw[k] = raw1[k];
-    if (i + kThreads < tile_end) {
-      p1x = p2x; p1y = p2y; p1z = p2z;
-      const WorldPoint w = TransformPoint(sb.q[0], sb.q[1], sb.q[2], sb.q[3], sb.t[0], sb.t[1], sb.t[2],
-                                          static_cast<double>(p1x), static_cast<double>(p1y), static_cast<double>(p1z));
-      w1x = w.x; w1y = w.y; w1z = w.z;
-      FetchLevelStencil(a.grids[0], w1x, w1y, w1z, raw1);
-    }
-    if (i + 2 * kThreads < tile_end) {
-      const float* pp = a.points + (sb.point_offset + i + 2 * kThreads) * a.stride;
-      p2x = __ldcs(pp); p2y = __ldcs(pp + 1); p2z = __ldcs(pp + 2);
-    }
-    ValueGrad t;
-    bool found = FinishMultiLevel(a.grids[0], wx, wy, wz, raw, &t);
-#pragma unroll
-    for (int l = 1; l < HG_MAX_PYRAMID_LEVELS; ++l) {
-      if (l < a.num_grids && !found) found = LookupTsdfLevel<true>(a.grids[l], wx, wy, wz, &t);
-    }
-    if (!found) {
-      t.v = static_cast<double>(a.grids[0].min_tsd);
-      t.gx = t.gy = t.gz = 0.0;
-    }
-    ValueGrad v;
-    v.v = sb.scale * t.v; v.gx = sb.scale * t.gx; v.gy = sb.scale * t.gy; v.gz = sb.scale * t.gz;
-    const double qw = sb.q[0], qx = sb.q[1], qy = sb.q[2], qz = sb.q[3];
-    WorldPoint wp;
-    wp.x = wx; wp.y = wy; wp.z = wz;
-    wp.uvx = qy * pz - qz * py; wp.uvy = qz * px - qx * pz; wp.uvz = qx * py - qy * px;
-    wp.uvx += wp.uvx; wp.uvy += wp.uvy; wp.uvz += wp.uvz;
-    double aw, ax, ay, az;
-    RotationTerms(qw, qx, qy, qz, px, py, pz, wp, v, &aw, &ax, &ay, &az);
-    double J[NC];
-    if (!TWO_POSE) {
-      J[0] = v.gx; J[1] = v.gy; J[2] = v.gz;
-      J[3] = aw; J[4] = ax; J[5] = ay; J[6] = az;
-    } else {
-      J[0] = v.gx * sb.ct0; J[1] = v.gy * sb.ct0; J[2] = v.gz * sb.ct0;
-      J[7] = v.gx * sb.ct1; J[8] = v.gy * sb.ct1; J[9] = v.gz * sb.ct1;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        J[3 + j] = aw * sb.m0[j] + ax * sb.m0[4 + j] + ay * sb.m0[8 + j] + az * sb.m0[12 + j];
-        J[10 + j] = aw * sb.m1[j] + ax * sb.m1[4 + j] + ay * sb.m1[8 + j] + az * sb.m1[12 + j];
-      }
-    }
-    const long long gi = sb.point_offset + i;
-    if (a.r) __stcs(a.r + gi, v.v);
-    if (a.jt0) {
-      double* o = a.jt0 + gi * 3;
-      __stcs(o, J[0]); __stcs(o + 1, J[1]); __stcs(o + 2, J[2]);
-    }
-    if (a.jq0) {
-      if (a.vec_store) {
-        double2* o = reinterpret_cast<double2*>(a.jq0 + gi * 4);
-        __stcs(o, make_double2(J[3], J[4]));
-        __stcs(o + 1, make_double2(J[5], J[6]));
-      } else {
-        double* o = a.jq0 + gi * 4;
-        o[0] = J[3]; o[1] = J[4]; o[2] = J[5]; o[3] = J[6];
-      }
-    }
-    if (TWO_POSE) {
-      if (a.jt1) {
-        double* o = a.jt1 + gi * 3;
-        __stcs(o, J[7]); __stcs(o + 1, J[8]); __stcs(o + 2, J[9]);
-      }
-      if (a.jq1) {
-        if (a.vec_store) {
-          double2* o = reinterpret_cast<double2*>(a.jq1 + gi * 4);
-          __stcs(o, make_double2(J[10], J[11]));
-          __stcs(o + 1, make_double2(J[12], J[13]));
-        } else {
-          double* o = a.jq1 + gi * 4;
-          o[0] = J[10]; o[1] = J[11]; o[2] = J[12]; o[3] = J[13];
-        }
-      }
-    }
-  }
-}
-
 }  // namespace hg
 
 using namespace hg;
@@ -562,25 +440,6 @@ int LaunchCost(const hg_batch* B, const CostArgs& args, int num_tiles, cudaStrea
     }                                                                                           \
     CostKernel<L, T, NE><<<num_tiles, kThreads, smem, stream>>>(args);                          \
   } while (0)
-  if (!NE && B->lookup == 2) {
-    if (const char* env = std::getenv("HG_COST_PIPE")) {  // experiment: software-pipelined stencil gather
-      const int minb = std::atoi(env);
-      if (minb >= 2 && minb <= 4) {
-        if (B->two_pose) {
-          if (minb == 4) CostKernelPipelined<true, 4><<<num_tiles, kThreads, 0, stream>>>(args);
-          else if (minb == 3) CostKernelPipelined<true, 3><<<num_tiles, kThreads, 0, stream>>>(args);
-          else CostKernelPipelined<true, 2><<<num_tiles, kThreads, 0, stream>>>(args);
-        } else {
-          if (minb == 4) CostKernelPipelined<false, 4><<<num_tiles, kThreads, 0, stream>>>(args);
-          else if (minb == 3) CostKernelPipelined<false, 3><<<num_tiles, kThreads, 0, stream>>>(args);
-          else CostKernelPipelined<false, 2><<<num_tiles, kThreads, 0, stream>>>(args);
-        }
-        CountLaunch();
-        HG_CUDA(cudaGetLastError());
-        return HG_OK;
-      }
-    }
-  }
   if (B->lookup == 0) {
     if (B->two_pose) HG_LAUNCH(0, true); else HG_LAUNCH(0, false);
   } else if (B->lookup == 1) {

@@ -225,48 +225,6 @@ __device__ __forceinline__ bool LookupTsdfLevel(const GridDev& g, const double x
   return true;
 }
 
-// The two halves of LookupTsdfLevel<true> for kernels that issue the stencil loads of one point
-// ahead of using them: FetchLevelStencil starts the nine loads, FinishMultiLevel consumes them.
-__device__ __forceinline__ void FetchLevelStencil(const GridDev& g, const double x, const double y, const double z,
-                                                  float* raw) {
-  double x1, x2;
-  int ix, iy, iz;
-  LowerVoxel(g, x, &x1, &x2, &ix);
-  LowerVoxel(g, y, &x1, &x2, &iy);
-  LowerVoxel(g, z, &x1, &x2, &iz);
-  FetchStencil(g, ix, iy, iz, __int_as_float(0x7fc00000), raw);
-}
-__device__ __forceinline__ bool FinishMultiLevel(const GridDev& g, const double x, const double y, const double z,
-                                                 const float* raw, ValueGrad* out) {
-  bool all = true;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) all = all && (raw[k] == raw[k]);
-  if (!all) return false;  // interpolated_multi_resolution_tsdf.h:99-106
-  double x1, y1, z1, x2, y2, z2;
-  int i;
-  LowerVoxel(g, x, &x1, &x2, &i);
-  LowerVoxel(g, y, &y1, &y2, &i);
-  LowerVoxel(g, z, &z1, &z2, &i);
-  double q[8];
-#pragma unroll
-  for (int k = 0; k < 8; ++k) q[k] = static_cast<double>(raw[k]);
-  const double sx = CellWidthReciprocal(g.inv_resolution_d, x2 - x1);
-  const double sy = CellWidthReciprocal(g.inv_resolution_d, y2 - y1);
-  const double sz = CellWidthReciprocal(g.inv_resolution_d, z2 - z1);
-  const double nx = (x - x1) * sx, ny = (y - y1) * sy, nz = (z - z1) * sz;
-  const double a0 = (q[1] - q[0]) * nz + q[0], d0 = q[1] - q[0];
-  const double a1 = (q[3] - q[2]) * nz + q[2], d1 = q[3] - q[2];
-  const double a2 = (q[5] - q[4]) * nz + q[4], d2 = q[5] - q[4];
-  const double a3 = (q[7] - q[6]) * nz + q[6], d3 = q[7] - q[6];
-  const double b0 = (a1 - a0) * ny + a0, b0y = a1 - a0, b0z = (d1 - d0) * ny + d0;
-  const double b1 = (a3 - a2) * ny + a2, b1y = a3 - a2, b1z = (d3 - d2) * ny + d2;
-  out->v = (b1 - b0) * nx + b0;
-  out->gx = (b1 - b0) * sx;
-  out->gy = ((b1y - b0y) * nx + b0y) * sy;
-  out->gz = ((b1z - b0z) * nx + b0z) * sz;
-  return true;
-}
-
 // LOOKUP: 0 occupancy, 1 TSDF, 2 multi-resolution TSDF. Returns the residual
 // and its gradient w.r.t. the world point, both already scaled.
 

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """A/B timing of the C2 cost kernel under environment switches (development aid).
 
-  python tools/ab_cost.py [--once] "HG_COST_PIPE=0" "HG_COST_PIPE=3" ...
+  python tools/ab_cost.py [--once] "HG_TILE_OUT=1024" "HG_TILE_OUT=512" ...
 
 Each argument is a space-separated list of VAR=VALUE settings applied before the timed calls
 (the library reads them per call). Same protocol as bench.py's M1: device-resident outputs, CUDA
@@ -42,12 +42,12 @@ def main():
           (usage / usage.sum()).round(4).tolist(), flush=True)
     reference = None
     once = "--once" in sys.argv
-    configs = [a for a in sys.argv[1:] if a != "--once"] or ["HG_COST_PIPE=0", "HG_COST_PIPE=3"]
+    configs = [a for a in sys.argv[1:] if a != "--once"] or [""]
     for rnd in range(1 if once else 2):
         for cfg in configs:
             for kv in cfg.split():
                 k, v = kv.split("=")
-                os.environ[k] = v
+                os.environ[k] = v  # note: HG_TILE_OUT is read when the batch is created, not per call
             for o in outs:
                 o.zero_()
             for _ in range(1 if once else 3):
