@@ -382,8 +382,26 @@ struct hg_batch {
   // Stream of the host-pointer entry points when the caller passes none: the legacy default
   // stream, or the owning host thread's stream for the cost functions of hg_scan_match.
   cudaStream_t stream = nullptr;
-  mutable BlockDev* d_blocks = nullptr;
-  mutable BlockDev* h_blocks = nullptr;  // pinned
+  // Block descriptors travel through a ring of (pinned, device) slots: an evaluation with device
+  // outputs returns while its descriptor copy and its kernel are still queued, so the next call
+  // must not write the same staging memory. A slot is reused only after the event recorded behind
+  // the work that reads it has completed.
+  static constexpr int kBlockSlots = 4;
+  mutable BlockDev* d_blocks[kBlockSlots] = {nullptr, nullptr, nullptr, nullptr};
+  mutable BlockDev* h_blocks[kBlockSlots] = {nullptr, nullptr, nullptr, nullptr};  // pinned
+  mutable cudaEvent_t slot_done[kBlockSlots] = {nullptr, nullptr, nullptr, nullptr};
+  mutable int next_slot = 0;
+  // End-to-end pipeline of the host-pointer surface (large batches): the batch is cut into chunks
+  // of whole blocks; hg_batch_update_points queues the chunks' points on 'copy_in', evaluate runs a
+  // chunk's tiles as soon as its points are there and hands its outputs to 'copy_out', so that
+  // host-to-device copies, kernels and device-to-host copies of different chunks overlap.
+  static constexpr int kMaxChunks = 8;
+  std::vector<int> chunk_block_begin;  // num_chunks + 1
+  std::vector<int> out_tile_begin;     // num_blocks + 1: first output tile of every block
+  mutable cudaStream_t copy_in = nullptr, copy_out = nullptr;
+  mutable cudaEvent_t chunk_in[kMaxChunks] = {nullptr};
+  mutable cudaEvent_t chunk_done[kMaxChunks] = {nullptr};
+  mutable bool points_pending = false;  // chunk_in events guard d_points
   mutable double* d_partials = nullptr;
   mutable double* d_ne_out = nullptr;
   mutable double* h_ne_out = nullptr;  // pinned
@@ -453,9 +471,38 @@ int LaunchCost(const hg_batch* B, const CostArgs& args, int num_tiles, cudaStrea
   return HG_OK;
 }
 
-// Fills the pinned block descriptors from host poses and copies them to the device.
+int LazyEvent(cudaEvent_t* e) {
+  if (*e == nullptr) HG_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  return HG_OK;
+}
+
+// Waits until nothing queued by earlier calls still reads the batch's device buffers.
+int WaitForSlots(const hg_batch* B) {
+  for (int k = 0; k < hg_batch::kBlockSlots; ++k)
+    if (B->slot_done[k] != nullptr) HG_CUDA(cudaEventSynchronize(B->slot_done[k]));
+  return HG_OK;
+}
+
+// Fills a free slot's pinned block descriptors from host poses and queues their copy to the
+// device on 'stream'. The caller records B->slot_done[*slot] behind the last launch that reads them.
 int PrepareBlocks(const hg_batch* B, const double* poses, int num_poses, const int32_t* i0,
-                  const int32_t* i1, cudaStream_t stream) {
+                  const int32_t* i1, cudaStream_t stream, int* slot_out) {
+  const int slot = B->next_slot;
+  B->next_slot = (slot + 1) % hg_batch::kBlockSlots;
+  *slot_out = slot;
+  if (B->d_blocks[slot] == nullptr) {
+    BlockDev* dev = nullptr;
+    HG_ALLOC(dev, CachedDeviceAlloc(sizeof(BlockDev) * B->num_blocks));
+    B->d_blocks[slot] = dev;
+  }
+  if (B->h_blocks[slot] == nullptr) {
+    BlockDev* pinned = nullptr;
+    HG_ALLOC(pinned, CachedPinnedAlloc(sizeof(BlockDev) * B->num_blocks));
+    B->h_blocks[slot] = pinned;
+  }
+  int rc = LazyEvent(&B->slot_done[slot]);
+  if (rc != HG_OK) return rc;
+  HG_CUDA(cudaEventSynchronize(B->slot_done[slot]));  // never recorded = complete
   for (int b = 0; b < B->num_blocks; ++b) {
     const int a0 = i0 ? i0[b] : 0;
     HG_REQUIRE(a0 >= 0 && a0 < num_poses, "pose_index0 out of range");
@@ -468,7 +515,7 @@ int PrepareBlocks(const hg_batch* B, const double* poses, int num_poses, const i
     } else {
       p = OnePose(poses + 7 * a0, poses + 7 * a0 + 3);
     }
-    BlockDev& d = B->h_blocks[b];
+    BlockDev& d = B->h_blocks[slot][b];
     std::memcpy(d.t, p.t, sizeof(d.t));
     std::memcpy(d.q, p.q, sizeof(d.q));
     d.ct0 = p.ct0;
@@ -480,8 +527,18 @@ int PrepareBlocks(const hg_batch* B, const double* poses, int num_poses, const i
     d.n = static_cast<int>(B->offsets[b + 1] - B->offsets[b]);
     d.pad = 0;
   }
-  HG_CUDA(cudaMemcpyAsync(B->d_blocks, B->h_blocks, sizeof(BlockDev) * B->num_blocks,
+  HG_CUDA(cudaMemcpyAsync(B->d_blocks[slot], B->h_blocks[slot], sizeof(BlockDev) * B->num_blocks,
                           cudaMemcpyHostToDevice, stream));
+  return HG_OK;
+}
+
+// Points queued by hg_batch_update_points: work on 'stream' that reads all of them waits for the
+// last chunk (the chunks arrive in order on one stream).
+int WaitForAllPoints(const hg_batch* B, cudaStream_t stream) {
+  if (B->points_pending) {
+    const int last = static_cast<int>(B->chunk_block_begin.size()) - 2;
+    HG_CUDA(cudaStreamWaitEvent(stream, B->chunk_in[last], 0));
+  }
   return HG_OK;
 }
 
@@ -492,8 +549,8 @@ CostArgs BaseArgs(const hg_batch* B) {
   a.num_grids = B->num_grids;
   a.points = B->d_points;
   a.stride = B->stride;
-  a.blocks = B->d_blocks;
-  return a;
+  return a;  // a.blocks: the slot PrepareBlocks filled
+
 }
 
 }  // namespace
@@ -558,8 +615,25 @@ int hg_batch_create(int kind, int num_blocks, const float* points, int stride_fl
   std::vector<int> tile_begin;
   B->tile_out = kTileOut;
   if (const char* env = std::getenv("HG_TILE_OUT")) B->tile_out = std::max(256, (std::atoi(env) / 256) * 256);
-  BuildTiles(B->offsets, B->tile_out, &tiles, nullptr);
+  BuildTiles(B->offsets, B->tile_out, &tiles, &B->out_tile_begin);
   B->num_tiles_out = static_cast<int>(tiles.size());
+  {
+    // Chunks of whole blocks for the end-to-end pipeline: at most kMaxChunks, each of at least
+    // ~256k points.
+    int max_chunks = hg_batch::kMaxChunks;
+    if (const char* env = std::getenv("HG_E2E_CHUNKS")) max_chunks = std::min(max_chunks, std::max(1, std::atoi(env)));
+    const int64_t target = std::max<int64_t>(int64_t(1) << 18, (B->num_points + max_chunks - 1) / max_chunks);
+    B->chunk_block_begin.assign(1, 0);
+    int64_t in_chunk = 0;
+    for (int b = 0; b < num_blocks; ++b) {
+      in_chunk += B->offsets[b + 1] - B->offsets[b];
+      const int chunks_so_far = static_cast<int>(B->chunk_block_begin.size());
+      if (b + 1 == num_blocks || (in_chunk >= target && chunks_so_far < max_chunks)) {
+        B->chunk_block_begin.push_back(b + 1);
+        in_chunk = 0;
+      }
+    }
+  }
   HG_ALLOC(B->d_tiles_out, CachedDeviceAlloc(sizeof(TileDev) * std::max<size_t>(tiles.size(), 1)));
   if (!tiles.empty())
     HG_CUDA(cudaMemcpy(B->d_tiles_out, tiles.data(), sizeof(TileDev) * tiles.size(), cudaMemcpyHostToDevice));
@@ -571,8 +645,6 @@ int hg_batch_create(int kind, int num_blocks, const float* points, int stride_fl
   HG_ALLOC(B->d_ne_tile_begin, CachedDeviceAlloc(sizeof(int) * tile_begin.size()));
   HG_CUDA(cudaMemcpy(B->d_ne_tile_begin, tile_begin.data(), sizeof(int) * tile_begin.size(), cudaMemcpyHostToDevice));
 
-  HG_ALLOC(B->d_blocks, CachedDeviceAlloc(sizeof(BlockDev) * num_blocks));
-  HG_ALLOC(B->h_blocks, CachedPinnedAlloc(sizeof(BlockDev) * num_blocks));
   const int P = NumNormalTerms(two ? 14 : 7);
   HG_ALLOC(B->d_partials, CachedDeviceAlloc(sizeof(double) * kNormalTermsU * std::max(B->num_tiles_ne, 1)));
   HG_ALLOC(B->d_ne_out, CachedDeviceAlloc(sizeof(double) * P * num_blocks));
@@ -587,8 +659,21 @@ void hg_batch_destroy(hg_batch* B) {
   CachedFree(B->d_tiles_out);
   CachedFree(B->d_tiles_ne);
   CachedFree(B->d_ne_tile_begin);
-  CachedFree(B->d_blocks);
-  CachedFree(B->h_blocks);
+  // Work queued by evaluations that returned early may still read these buffers.
+  WaitForSlots(B);
+  if (B->copy_in) cudaStreamSynchronize(B->copy_in);
+  if (B->copy_out) cudaStreamSynchronize(B->copy_out);
+  for (int k = 0; k < hg_batch::kBlockSlots; ++k) {
+    CachedFree(B->d_blocks[k]);
+    CachedFree(B->h_blocks[k]);
+    if (B->slot_done[k]) cudaEventDestroy(B->slot_done[k]);
+  }
+  for (int k = 0; k < hg_batch::kMaxChunks; ++k) {
+    if (B->chunk_in[k]) cudaEventDestroy(B->chunk_in[k]);
+    if (B->chunk_done[k]) cudaEventDestroy(B->chunk_done[k]);
+  }
+  if (B->copy_in) cudaStreamDestroy(B->copy_in);
+  if (B->copy_out) cudaStreamDestroy(B->copy_out);
   CachedFree(B->d_partials);
   CachedFree(B->d_ne_out);
   CachedFree(B->h_ne_out);
@@ -603,8 +688,26 @@ int hg_batch_update_points(hg_batch* B, const float* points, int stride_floats) 
   HG_REQUIRE(B != nullptr && points != nullptr && stride_floats == B->stride,
              "hg_batch_update_points: bad arguments");
   std::lock_guard<std::mutex> lock(B->mu);
-  HG_CUDA(cudaMemcpy(B->d_points, points, static_cast<size_t>(B->num_points) * B->stride * sizeof(float),
-                     cudaMemcpyHostToDevice));
+  // Evaluations that returned early (device outputs) may still be reading the old points.
+  int rc = WaitForSlots(B);
+  if (rc != HG_OK) return rc;
+  if (B->copy_in == nullptr) HG_CUDA(cudaStreamCreateWithFlags(&B->copy_in, cudaStreamNonBlocking));
+  // One copy per chunk of blocks, each followed by an event: the next evaluation starts on a chunk
+  // as soon as its points have arrived. The call returns when the copies are queued (pageable
+  // memory: when the runtime has staged them).
+  const int num_chunks = static_cast<int>(B->chunk_block_begin.size()) - 1;
+  for (int c = 0; c < num_chunks; ++c) {
+    const int64_t p0 = B->offsets[B->chunk_block_begin[c]], p1 = B->offsets[B->chunk_block_begin[c + 1]];
+    rc = LazyEvent(&B->chunk_in[c]);
+    if (rc != HG_OK) return rc;
+    if (p1 > p0) {
+      HG_CUDA(cudaMemcpyAsync(B->d_points + p0 * B->stride, points + p0 * B->stride,
+                              static_cast<size_t>(p1 - p0) * B->stride * sizeof(float), cudaMemcpyHostToDevice,
+                              B->copy_in));
+    }
+    HG_CUDA(cudaEventRecord(B->chunk_in[c], B->copy_in));
+  }
+  B->points_pending = true;
   return HG_OK;
 }
 
@@ -614,9 +717,11 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
   HG_REQUIRE(B != nullptr && poses != nullptr && num_poses >= 1, "hg_batch_evaluate: bad arguments");
   cudaStream_t stream = cuda_stream != nullptr ? static_cast<cudaStream_t>(cuda_stream) : B->stream;
   std::lock_guard<std::mutex> lock(B->mu);
-  int rc = PrepareBlocks(B, poses, num_poses, pose_index0, pose_index1, stream);
+  int slot = 0;
+  int rc = PrepareBlocks(B, poses, num_poses, pose_index0, pose_index1, stream, &slot);
   if (rc != HG_OK) return rc;
   CostArgs a = BaseArgs(B);
+  a.blocks = B->d_blocks[slot];
   a.tiles = B->d_tiles_out;
   a.tile_points = B->tile_out;
   const int64_t N = B->num_points;
@@ -625,13 +730,21 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
     jq1 = nullptr;
   }
   if (device_outputs) {
+    rc = WaitForAllPoints(B, stream);
+    if (rc != HG_OK) return rc;
     a.r = residuals; a.jt0 = jt0; a.jq0 = jq0; a.jt1 = jt1; a.jq1 = jq1;
     a.vec_store = ((reinterpret_cast<uintptr_t>(jq0) | reinterpret_cast<uintptr_t>(jq1)) % 16 == 0) ? 1 : 0;
-    return LaunchCost<false>(B, a, B->num_tiles_out, stream);
+    rc = LaunchCost<false>(B, a, B->num_tiles_out, stream);
+    if (rc != HG_OK) return rc;
+    HG_CUDA(cudaEventRecord(B->slot_done[slot], stream));  // returns without waiting: see the slot ring
+    return HG_OK;
   }
   // Host outputs: stage in device memory, then one copy per requested array.
   const size_t need = static_cast<size_t>(N) * 15;
   if (B->d_out_doubles < need) {
+    rc = WaitForSlots(B);  // nothing queued may still write the old staging area
+    if (rc != HG_OK) return rc;
+    if (B->copy_out) HG_CUDA(cudaStreamSynchronize(B->copy_out));
     CachedFree(B->d_out);
     B->d_out = nullptr;
     B->d_out_doubles = 0;
@@ -646,13 +759,15 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
   a.jt1 = jt1 ? d + 11 * N : nullptr;
   a.r = residuals ? d + 14 * N : nullptr;
   a.vec_store = 1;
-  rc = LaunchCost<false>(B, a, B->num_tiles_out, stream);
-  if (rc != HG_OK) return rc;
   // Small blocks (a scan matcher's Evaluate: ~1 MB into Ceres' pageable arrays): one DMA of the
   // whole staging area into pinned memory and host copies from there cost less than up to five
   // separate pageable device-to-host copies.
   constexpr size_t kPinnedStageDoubles = size_t(1) << 20;  // 8 MB
   if (need <= kPinnedStageDoubles) {
+    rc = WaitForAllPoints(B, stream);
+    if (rc != HG_OK) return rc;
+    rc = LaunchCost<false>(B, a, B->num_tiles_out, stream);
+    if (rc != HG_OK) return rc;
     if (B->h_out_doubles < need) {
       CachedFree(B->h_out);
       B->h_out = nullptr;
@@ -661,7 +776,9 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
       B->h_out_doubles = need;
     }
     HG_CUDA(cudaMemcpyAsync(B->h_out, d, need * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    HG_CUDA(cudaEventRecord(B->slot_done[slot], stream));
     HG_CUDA(cudaStreamSynchronize(stream));
+    B->points_pending = false;
     const double* h = B->h_out;
     if (jq0) std::memcpy(jq0, h, sizeof(double) * N * 4);
     if (jq1) std::memcpy(jq1, h + 4 * N, sizeof(double) * N * 4);
@@ -670,12 +787,41 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
     if (residuals) std::memcpy(residuals, h + 14 * N, sizeof(double) * N);
     return HG_OK;
   }
-  if (residuals) HG_CUDA(cudaMemcpyAsync(residuals, a.r, sizeof(double) * N, cudaMemcpyDeviceToHost, stream));
-  if (jt0) HG_CUDA(cudaMemcpyAsync(jt0, a.jt0, sizeof(double) * N * 3, cudaMemcpyDeviceToHost, stream));
-  if (jq0) HG_CUDA(cudaMemcpyAsync(jq0, a.jq0, sizeof(double) * N * 4, cudaMemcpyDeviceToHost, stream));
-  if (jt1) HG_CUDA(cudaMemcpyAsync(jt1, a.jt1, sizeof(double) * N * 3, cudaMemcpyDeviceToHost, stream));
-  if (jq1) HG_CUDA(cudaMemcpyAsync(jq1, a.jq1, sizeof(double) * N * 4, cudaMemcpyDeviceToHost, stream));
+  // Large batches: chunk by chunk. A chunk's kernel waits only for that chunk's points (when
+  // hg_batch_update_points queued them), and its outputs start their way to the host while the
+  // next chunk computes and later chunks' points are still arriving: PCIe carries both directions
+  // at once, so the step costs about what the device-to-host copies alone cost.
+  if (B->copy_out == nullptr) HG_CUDA(cudaStreamCreateWithFlags(&B->copy_out, cudaStreamNonBlocking));
+  const int num_chunks = static_cast<int>(B->chunk_block_begin.size()) - 1;
+  for (int c = 0; c < num_chunks; ++c) {
+    const int b0 = B->chunk_block_begin[c], b1 = B->chunk_block_begin[c + 1];
+    const int t0 = B->out_tile_begin[b0], t1 = B->out_tile_begin[b1];
+    const int64_t p0 = B->offsets[b0], n = B->offsets[b1] - p0;
+    if (B->points_pending) HG_CUDA(cudaStreamWaitEvent(stream, B->chunk_in[c], 0));
+    CostArgs ac = a;
+    ac.tiles = B->d_tiles_out + t0;
+    rc = LaunchCost<false>(B, ac, t1 - t0, stream);
+    if (rc != HG_OK) return rc;
+    rc = LazyEvent(&B->chunk_done[c]);
+    if (rc != HG_OK) return rc;
+    HG_CUDA(cudaEventRecord(B->chunk_done[c], stream));
+    HG_CUDA(cudaStreamWaitEvent(B->copy_out, B->chunk_done[c], 0));
+    if (n == 0) continue;
+    if (residuals)
+      HG_CUDA(cudaMemcpyAsync(residuals + p0, a.r + p0, sizeof(double) * n, cudaMemcpyDeviceToHost, B->copy_out));
+    if (jt0)
+      HG_CUDA(cudaMemcpyAsync(jt0 + 3 * p0, a.jt0 + 3 * p0, sizeof(double) * n * 3, cudaMemcpyDeviceToHost, B->copy_out));
+    if (jq0)
+      HG_CUDA(cudaMemcpyAsync(jq0 + 4 * p0, a.jq0 + 4 * p0, sizeof(double) * n * 4, cudaMemcpyDeviceToHost, B->copy_out));
+    if (jt1)
+      HG_CUDA(cudaMemcpyAsync(jt1 + 3 * p0, a.jt1 + 3 * p0, sizeof(double) * n * 3, cudaMemcpyDeviceToHost, B->copy_out));
+    if (jq1)
+      HG_CUDA(cudaMemcpyAsync(jq1 + 4 * p0, a.jq1 + 4 * p0, sizeof(double) * n * 4, cudaMemcpyDeviceToHost, B->copy_out));
+  }
+  HG_CUDA(cudaEventRecord(B->slot_done[slot], stream));
+  HG_CUDA(cudaStreamSynchronize(B->copy_out));
   HG_CUDA(cudaStreamSynchronize(stream));
+  B->points_pending = false;
   return HG_OK;
 }
 
@@ -685,23 +831,29 @@ int hg_batch_normal_equations(const hg_batch* B, const double* poses, int num_po
   HG_REQUIRE(B != nullptr && poses != nullptr && num_poses >= 1, "hg_batch_normal_equations: bad arguments");
   std::lock_guard<std::mutex> lock(B->mu);
   cudaStream_t stream = B->stream;
-  int rc = PrepareBlocks(B, poses, num_poses, pose_index0, pose_index1, stream);
+  int slot = 0;
+  int rc = PrepareBlocks(B, poses, num_poses, pose_index0, pose_index1, stream, &slot);
   if (rc != HG_OK) return rc;
   CostArgs a = BaseArgs(B);
+  a.blocks = B->d_blocks[slot];
   a.tiles = B->d_tiles_ne;
   a.tile_points = kTileNe;
   a.partials = B->d_partials;
+  rc = WaitForAllPoints(B, stream);
+  if (rc != HG_OK) return rc;
   rc = LaunchCost<true>(B, a, B->num_tiles_ne, stream);
   if (rc != HG_OK) return rc;
   const int n = B->two_pose ? 14 : 7;
   const int P = NumNormalTerms(n);
-  ReducePartialsKernel<<<B->num_blocks, 128, 0, stream>>>(B->d_partials, B->d_ne_tile_begin, B->d_blocks,
+  ReducePartialsKernel<<<B->num_blocks, 128, 0, stream>>>(B->d_partials, B->d_ne_tile_begin, B->d_blocks[slot],
                                                           B->two_pose ? 1 : 0, B->d_ne_out);
   CountLaunch();
   HG_CUDA(cudaGetLastError());
   HG_CUDA(cudaMemcpyAsync(B->h_ne_out, B->d_ne_out, sizeof(double) * P * B->num_blocks,
                           cudaMemcpyDeviceToHost, stream));
+  HG_CUDA(cudaEventRecord(B->slot_done[slot], stream));
   HG_CUDA(cudaStreamSynchronize(stream));
+  B->points_pending = false;
   for (int b = 0; b < B->num_blocks; ++b) {
     const double* s = B->h_ne_out + static_cast<size_t>(b) * P;
     int e = 0;
@@ -726,11 +878,15 @@ int hg_batch_level_usage(const hg_batch* B, const double* poses, int num_poses, 
   HG_REQUIRE(B->lookup == 2, "hg_batch_level_usage: only multi-resolution TSDF cost functions have levels");
   std::lock_guard<std::mutex> lock(B->mu);
   cudaStream_t stream = B->stream;
-  int rc = PrepareBlocks(B, poses, num_poses, pose_index0, pose_index1, stream);
+  int slot = 0;
+  int rc = PrepareBlocks(B, poses, num_poses, pose_index0, pose_index1, stream, &slot);
   if (rc != HG_OK) return rc;
   CostArgs a = BaseArgs(B);
+  a.blocks = B->d_blocks[slot];
   a.tiles = B->d_tiles_out;
   a.tile_points = B->tile_out;
+  rc = WaitForAllPoints(B, stream);
+  if (rc != HG_OK) return rc;
   unsigned long long* d_counts = static_cast<unsigned long long*>(
       CachedDeviceAlloc(sizeof(unsigned long long) * (HG_MAX_PYRAMID_LEVELS + 1)));
   HG_REQUIRE(d_counts != nullptr, "hg_batch_level_usage: out of device memory");
@@ -1083,6 +1239,8 @@ extern "C" int hg_cost_normal_equations_static(const hg_cost* cost, const double
   a.tiles = B->d_tiles_ne;
   a.tile_points = kTileNe;
   a.partials = d_partials;
+  rc = WaitForAllPoints(B, stream);  // points queued by hg_batch_update_points (an event wait: no allocation)
+  if (rc != HG_OK) return rc;
   rc = LaunchCost<true>(B, a, B->num_tiles_ne, stream);
   if (rc != HG_OK) return rc;
   const int n = B->two_pose ? 14 : 7;

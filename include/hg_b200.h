@@ -280,7 +280,14 @@ int hg_batch_create(int kind, int num_blocks, const float* points, int stride_fl
                     const hg_grid* const* grids, int num_grids, hg_batch** out);
 void hg_batch_destroy(hg_batch* batch);
 int64_t hg_batch_num_residuals(const hg_batch* batch);
-/* Replaces the point clouds (same offsets) from HOST memory: the next window of scans. */
+/* Replaces the point clouds (same offsets) from HOST memory: the next window of scans.
+ * The copy is queued chunk by chunk on a stream of the batch and the call returns; the next
+ * evaluation of the batch starts on a chunk of blocks as soon as that chunk's points have
+ * arrived (with host outputs it also sends each chunk's results back while later chunks are
+ * still being copied in and computed). Pinned 'points' must therefore stay unchanged until the
+ * next evaluation with host outputs (or hg_batch_normal_equations) has returned, or the device
+ * has been synchronised; pageable memory is staged by the CUDA runtime before the call returns.
+ * Waits for evaluations with device outputs that are still queued on the old points. */
 int hg_batch_update_points(hg_batch* batch, const float* points, int stride_floats);
 
 /* Evaluates every block. 'poses' = num_poses x 7 doubles (t3, q4) on the host;
@@ -288,7 +295,10 @@ int hg_batch_update_points(hg_batch* batch, const float* points, int stride_floa
  * Outputs are HOST pointers when device_outputs == 0, DEVICE pointers otherwise;
  * any may be NULL. Layout: residuals[N]; jt0[N x 3], jq0[N x 4], jt1[N x 3],
  * jq1[N x 4] row-major, so the slice of block b is exactly the jacobians[k]
- * array Ceres would pass for it. */
+ * array Ceres would pass for it. With host outputs the call returns when the outputs
+ * are in place. With device outputs it returns once the work is queued on 'cuda_stream'
+ * (the batch's own stream when NULL): several such calls may be in flight, each with its
+ * own poses — the block descriptors go through a ring of staging slots. */
 int hg_batch_evaluate(const hg_batch* batch, const double* poses, int num_poses,
                       const int32_t* pose_index0, const int32_t* pose_index1, int device_outputs,
                       double* residuals, double* jt0, double* jq0, double* jt1, double* jq1,

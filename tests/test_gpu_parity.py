@@ -954,3 +954,82 @@ def test_handles_are_usable_from_several_host_threads(oracle, hg, world):
                 assert (r == serial_eval[i][0]).all()
                 assert all((a == b).all() for a, b in zip(J, serial_eval[i][1]))
                 assert (pose == serial_refine[i]).all()
+
+
+def test_queued_device_evaluations_keep_their_own_poses(oracle, hg, world):
+    """hg_batch_evaluate with device outputs returns while its block-descriptor copy and kernel are
+    still queued. Two such calls with different poses behind a busy stream must each use their own
+    poses (the descriptors go through a ring of staging slots), and more calls than the ring has
+    slots must still be correct."""
+    import torch
+    rng = np.random.RandomState(91)
+    cloud = world["cloud"]
+    clouds = [cloud, cloud[::2], cloud[1::2]]
+    pts = np.concatenate(clouds)
+    offsets = np.cumsum([0] + [len(c) for c in clouds]).astype(np.int64)
+    scales = np.array([0.1, 0.2, 0.3])
+    ratios = np.array([0.3, 0.6, 0.9])
+    batch = hg.Batch("interpolated_multires_tsdf", pts, offsets, scales, [world["g_tsdf_hi"], world["g_tsdf_lo"]], ratios)
+    i0 = np.array([0, 0, 1], np.int32)
+    i1 = np.array([1, 2, 2], np.int32)
+    N = len(pts)
+    dev = torch.device("cuda", 0)
+    stream = torch.cuda.Stream()
+    pose_sets = [np.ascontiguousarray([perturbed(world["truth"], rng, 0.2, 0.08) for _ in range(3)]) for _ in range(7)]
+    expected = [batch.evaluate(p, i0, i1) for p in pose_sets]
+    outs = [[torch.zeros(N * k, dtype=torch.float64, device=dev) for k in (1, 3, 4, 3, 4)] for _ in pose_sets]
+    with torch.cuda.stream(stream):
+        torch.cuda._sleep(400_000_000)  # ~0.2 s of busy stream: everything below queues up behind it
+        for p, o in zip(pose_sets, outs):
+            batch.evaluate_raw(p.ctypes.data, len(p), i0.ctypes.data, i1.ctypes.data, True,
+                               *[t.data_ptr() for t in o], stream.cuda_stream)
+    stream.synchronize()
+    for (r, J), o in zip(expected, outs):
+        assert (o[0].cpu().numpy() == r).all()
+        for a, b in zip(J, o[1:]):
+            assert (b.cpu().numpy().reshape(a.shape) == a).all()
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+def test_chunked_host_evaluate_after_update_points(oracle, hg, world, pinned):
+    """Large batches with host outputs run chunk by chunk (points in, kernel, results out overlap);
+    hg_batch_update_points only queues its copies. Results must equal a batch created on the new
+    points, for pinned and pageable host memory, repeatedly."""
+    import torch
+    rng = np.random.RandomState(92)
+    cloud = world["cloud"]
+    blocks = max(96, 600000 // len(cloud) + 1)
+    sizes = [len(cloud) - (b % 5) for b in range(blocks)]  # ragged, odd sizes
+    offsets = np.cumsum([0] + sizes).astype(np.int64)
+    N = int(offsets[-1])
+    assert N * 15 > (1 << 20) and N > 2 * (1 << 18)  # the chunked path, several chunks
+    scales = rng.uniform(0.05, 0.2, blocks)
+    ratios = rng.uniform(0, 1, blocks)
+    i0 = rng.randint(0, 4, blocks).astype(np.int32)
+    i1 = rng.randint(0, 4, blocks).astype(np.int32)
+    poses = np.ascontiguousarray([perturbed(world["truth"], rng, 0.2, 0.08) for _ in range(4)])
+    grids = [world["g_tsdf_hi"], world["g_tsdf_lo"]]
+
+    def points(seed):
+        r = np.random.RandomState(seed)
+        return np.concatenate([cloud[:n] + r.normal(0, 0.01, (n, 3)).astype(np.float32) for n in sizes])
+
+    batch = hg.Batch("interpolated_multires_tsdf", points(0), offsets, scales, grids, ratios)
+    for seed in (1, 2):
+        new = points(seed)
+        host = torch.from_numpy(new.copy())
+        if pinned:
+            host = host.pin_memory()
+        batch.update_points(host.numpy())
+        r, J = batch.evaluate(poses, i0, i1)
+        fresh = hg.Batch("interpolated_multires_tsdf", new, offsets, scales, grids, ratios)
+        r2, J2 = fresh.evaluate(poses, i0, i1)
+        assert (r == r2).all()
+        for a, b in zip(J, J2):
+            assert (a == b).all()
+        # and against the oracle on one block
+        b = 7
+        oc = oracle.Cost("interpolated_multires_tsdf", scales[b], new[offsets[b]:offsets[b + 1]],
+                         [world["o_tsdf_hi"], world["o_tsdf_lo"]], ratios[b])
+        ro, Jo = oc.evaluate(np.concatenate([poses[i0[b]], poses[i1[b]]]))
+        assert_close(r[offsets[b]:offsets[b + 1]], ro, "residuals of block 7")
