@@ -47,7 +47,8 @@ class MatchResult(C.Structure):
                 ("best_scan_index", C.c_int32), ("best_offset", C.c_int32 * 3),
                 ("num_discrete_scans", C.c_int32), ("num_candidates_scored", c_i64),
                 ("num_candidates_visited", c_i64), ("num_score_launches", C.c_int32),
-                ("num_lowest_resolution_candidates", c_i64), ("lowest_resolution_kernel_ms", c_f)]
+                ("num_lowest_resolution_candidates", c_i64), ("lowest_resolution_kernel_ms", c_f),
+                ("best_ancestor_score", c_f), ("best_ancestor_index", c_i64), ("dive_bound", c_f)]
 
 
 class OccupancyInserterOptions(C.Structure):
@@ -130,6 +131,10 @@ SYMBOLS = {
     "hg_fcsm_stack": (vp, [vp]),
     "hg_fcsm_match": (c_i, [vp, vp, vp, vp, c_f, vp]),
     "hg_fcsm_match_full_submap": (c_i, [vp, vp, vp, vp, c_f, c_i, c_i, vp]),
+    "hg_fcsm_match_batch": (c_i, [vp, c_i, vp, vp, vp, c_f, vp]),
+    "hg_fcsm_full_submap_begin": (c_i, [vp, vp, vp, vp, c_f, c_i, c_i, vp, vp]),
+    "hg_fcsm_full_submap_finish": (c_i, [vp, c_f, vp]),
+    "hg_fcsm_search_abandon": (None, [vp]),
     "hg_fcsm_discrete_scans": (c_i, [vp, c_i, c_i, c_d, vp, vp, vp, c_i, vp, vp, vp, vp]),
     "hg_fcsm_score_candidates": (c_i, [vp, c_i, c_i, c_d, vp, vp, vp, c_i, c_i64, vp, vp, vp, vp]),
     "hg_low_resolution_scores": (c_i, [vp, vp, c_i, c_i64, vp, vp]),
@@ -585,7 +590,9 @@ def _result_dict(r):
                 num_scans=float(r.num_discrete_scans), num_scored=int(r.num_candidates_scored),
                 num_visited=int(r.num_candidates_visited), num_launches=int(r.num_score_launches),
                 num_lattice=int(r.num_lowest_resolution_candidates),
-                lattice_kernel_ms=float(r.lowest_resolution_kernel_ms))
+                lattice_kernel_ms=float(r.lowest_resolution_kernel_ms),
+                ancestor_score=float(r.best_ancestor_score), ancestor_index=int(r.best_ancestor_index),
+                dive_bound=float(r.dive_bound))
 
 
 class Fcsm:
@@ -631,6 +638,39 @@ class Fcsm:
             _check(lib().hg_fcsm_match(self.h, _p(node_pose), _p(submap_pose), C.byref(data), min_score,
                                        C.byref(res)))
         del keep
+        return _result_dict(res)
+
+    def match_batch(self, node_poses, submap_poses, nodes, min_score=0.55):
+        """nodes: list of (high, low, hist[, gravity]) tuples; one device-resident search for all."""
+        n = len(nodes)
+        node_poses = _f64(node_poses).reshape(n, 7)
+        submap_poses = _f64(submap_poses).reshape(n, 7)
+        datas = (NodeData * n)()
+        keep = []
+        for k, node in enumerate(nodes):
+            d, ka = make_node_data(*node)
+            datas[k] = d
+            keep.append(ka)
+        res = (MatchResult * n)()
+        _check(lib().hg_fcsm_match_batch(self.h, n, _p(node_poses), _p(submap_poses), datas, min_score, res))
+        del keep
+        return [_result_dict(r) for r in res]
+
+    def full_submap_begin(self, node_rotation, submap_rotation, high, low, hist, gravity=(1, 0, 0, 0),
+                          min_score=0.55, shard_index=0, num_shards=1):
+        """First half of a sharded MatchFullSubmap; returns (handle, dive bound). The handle keeps the
+        node data alive; pass it to full_submap_finish on the same thread."""
+        nq, sq = _f64(node_rotation), _f64(submap_rotation)
+        data, keep = make_node_data(high, low, hist, gravity)
+        out = vp()
+        bound = C.c_float(0)
+        _check(lib().hg_fcsm_full_submap_begin(self.h, _p(nq), _p(sq), C.byref(data), min_score, shard_index,
+                                               num_shards, C.byref(out), C.byref(bound)))
+        return (out, data, keep), float(bound.value)
+
+    def full_submap_finish(self, handle, bound):
+        res = MatchResult()
+        _check(lib().hg_fcsm_full_submap_finish(handle[0], float(bound), C.byref(res)))
         return _result_dict(res)
 
     def discrete_scans(self, wxy, wz, angular_window, node_pose, submap_pose, high, hist, gravity=(1, 0, 0, 0)):

@@ -608,6 +608,9 @@ struct Workspace {
   DeviceBuffer d_lattice, d_chunks, d_kept;                    // lowest-resolution lattice
   DeviceBuffer d_low_points, d_low_poses, d_low_scores;        // leaf gate
   PinnedBuffer h_cand, h_sums, h_kept, h_poses, h_low, h_count;
+  // device-resident search (DeviceSearch)
+  DeviceBuffer d_upload, d_starts, d_lists, d_ctrl;
+  PinnedBuffer h_upload, h_ctrl;
 };
 Workspace& GetWorkspace(int device) {
   thread_local std::map<int, std::unique_ptr<Workspace>> spaces;
@@ -654,9 +657,12 @@ struct ScanSet {
   }
 };
 
-int GenerateDiscreteScans(const hg_fcsm* m, const SearchParameters& sp, const hg_node_data* data,
-                          const Rigid& node_pose, const Rigid& submap_pose, int shard_index, int num_shards,
-                          cudaStream_t stream, ScanSet* out) {
+// Host half of GenerateDiscreteScans (:276-326): yaw list, rotational prefilter, per-yaw poses of
+// the scans this shard keeps. Fills out->{poses, rotational_scores, global_scan_index, S, N, frd,
+// num_low_levels}; no device work.
+int ComputeScanPoses(const hg_fcsm* m, const SearchParameters& sp, const hg_node_data* data,
+                     const Rigid& node_pose, const Rigid& submap_pose, int shard_index, int num_shards,
+                     ScanSet* out) {
   const int flavor = m->options.float_flavor;
   const int N = data->num_high_resolution_points;
   HG_REQUIRE(N > 0 && data->high_resolution_point_cloud != nullptr, "empty high resolution point cloud");
@@ -710,17 +716,27 @@ int GenerateDiscreteScans(const hg_fcsm* m, const SearchParameters& sp, const hg
     out->rotational_scores.push_back(m->options.use_rotational_scan_matcher ? scores[i] : 1.0f);
     out->global_scan_index.push_back(global_index);
   }
-  const int S = static_cast<int>(out->poses.size());
-  out->S = S;
+  out->S = static_cast<int>(out->poses.size());
   out->N = N;
   const int D = m->options.branch_and_bound_depth;
   out->frd = std::min(m->options.full_resolution_depth, D);
   out->num_low_levels = D - out->frd;
+  return HG_OK;
+}
+
+int GenerateDiscreteScans(const hg_fcsm* m, const SearchParameters& sp, const hg_node_data* data,
+                          const Rigid& node_pose, const Rigid& submap_pose, int shard_index, int num_shards,
+                          cudaStream_t stream, ScanSet* out) {
+  int rc = ComputeScanPoses(m, sp, data, node_pose, submap_pose, shard_index, num_shards, out);
+  if (rc != HG_OK) return rc;
+  const int S = out->S, N = out->N;
+  const float* pts = data->high_resolution_point_cloud;
+  const float resolution = m->resolution;
   if (S == 0) return HG_OK;
 
   Workspace& ws = GetWorkspace(m->device);
   out->ws = &ws;
-  int rc = ws.d_points.Reserve(sizeof(float) * 3 * N);
+  rc = ws.d_points.Reserve(sizeof(float) * 3 * N);
   if (rc != HG_OK) return rc;
   rc = ws.d_poses.Reserve(sizeof(float) * 7 * S);
   if (rc != HG_OK) return rc;
@@ -742,6 +758,52 @@ int GenerateDiscreteScans(const hg_fcsm* m, const SearchParameters& sp, const hg
   CountLaunch();
   HG_CUDA(cudaGetLastError());
   HG_CUDA(cudaStreamSynchronize(stream));  // 'flat' goes out of scope
+  return HG_OK;
+}
+
+inline int ReduceExponentOf(const hg_fcsm* m, int depth) {
+  return std::max(0, depth - m->options.full_resolution_depth + 1);
+}
+
+// Launches the scoring of one search's whole lowest-resolution lattice (S scans x nz x nxy x nxy
+// candidates in generation order) into 'out'. Picks the residue-row kernel, the dense-level
+// kernel or the brick-table kernel, whichever the level offers. *packed_out tells which.
+int LaunchLattice(const hg_fcsm* m, const int* cells, int S, int N, int depth, int nxy, int nz, int wxy, int wz,
+                  int* out, cudaStream_t stream, bool* packed_out) {
+  const size_t n = static_cast<size_t>(S) * nxy * nxy * nz;
+  if (n == 0) return HG_OK;
+  const int64_t threads = static_cast<int64_t>(n) * 32;
+  const hg_stack_level& L = m->stack->levels[depth];
+  const LatticeRows& R = m->lattice_rows;
+  const int e = ReduceExponentOf(m, depth);
+  const bool packed = R.data != nullptr && depth == static_cast<int>(m->stack->levels.size()) - 1 && nxy >= 5 &&
+                      ((1 << depth) >> e) == (1 << R.cs_log2);
+  if (packed_out) *packed_out = packed;
+  if (packed) {
+#define HG_PACKED(KXW)                                                                                    \
+  do {                                                                                                    \
+    const int64_t groups = static_cast<int64_t>(S) * nz * nxy * ((nxy + 4 * KXW - 1) / (4 * KXW));        \
+    if (N <= 8192) {                                                                                      \
+      ScoreLatticePackedKernel<KXW, true><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>( \
+          R, cells, N, e, nxy, nz, wxy, wz, 1 << depth, groups, out);                                     \
+    } else {                                                                                              \
+      ScoreLatticePackedKernel<KXW, false><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>( \
+          R, cells, N, e, nxy, nz, wxy, wz, 1 << depth, groups, out);                                     \
+    }                                                                                                     \
+  } while (0)
+    if (nxy <= 8) HG_PACKED(2); else if (nxy <= 20) HG_PACKED(5); else HG_PACKED(8);
+#undef HG_PACKED
+  } else if (L.dense.data != nullptr) {
+    constexpr int KX = 4;
+    const int64_t groups = static_cast<int64_t>(S) * nz * nxy * ((nxy + KX - 1) / KX);
+    ScoreLatticeDenseKernel<KX><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>(
+        L.dense, cells, N, e, nxy, nz, wxy, wz, 1 << depth, groups, out);
+  } else {
+    ScoreLatticeKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
+        L.table, cells, N, e, nxy, nz, wxy, wz, 1 << depth, static_cast<int64_t>(n), out);
+  }
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
   return HG_OK;
 }
 
@@ -851,38 +913,10 @@ struct Scorer {
       HG_CUDA(cudaEventRecord(e0, stream));
     }
     const hg_stack_level& L = m->stack->levels[depth];
-    const LatticeRows& R = m->lattice_rows;
-    const bool packed = R.data != nullptr && depth == static_cast<int>(m->stack->levels.size()) - 1 && nxy >= 5 &&
-                        ((1 << depth) >> ReduceExponent(depth)) == (1 << R.cs_log2);
-    if (packed) {
-      const int* cells = scans->CellsOfDepth(depth);
-      const int e = ReduceExponent(depth);
-#define HG_PACKED(KXW)                                                                                    \
-  do {                                                                                                    \
-    const int64_t groups = static_cast<int64_t>(scans->S) * nz * nxy * ((nxy + 4 * KXW - 1) / (4 * KXW)); \
-    if (scans->N <= 8192) {                                                                               \
-      ScoreLatticePackedKernel<KXW, true><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>( \
-          R, cells, scans->N, e, nxy, nz, wxy, wz, 1 << depth, groups, ws->d_lattice.as<int>());          \
-    } else {                                                                                              \
-      ScoreLatticePackedKernel<KXW, false><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>( \
-          R, cells, scans->N, e, nxy, nz, wxy, wz, 1 << depth, groups, ws->d_lattice.as<int>());          \
-    }                                                                                                     \
-  } while (0)
-      if (nxy <= 8) HG_PACKED(2); else if (nxy <= 20) HG_PACKED(5); else HG_PACKED(8);
-#undef HG_PACKED
-    } else if (L.dense.data != nullptr) {
-      constexpr int KX = 4;
-      const int64_t groups = static_cast<int64_t>(scans->S) * nz * nxy * ((nxy + KX - 1) / KX);
-      ScoreLatticeDenseKernel<KX><<<static_cast<unsigned>((groups * 32 + 255) / 256), 256, 0, stream>>>(
-          L.dense, scans->CellsOfDepth(depth), scans->N, ReduceExponent(depth), nxy, nz, wxy, wz, 1 << depth,
-          groups, ws->d_lattice.as<int>());
-    } else {
-      ScoreLatticeKernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
-          L.table, scans->CellsOfDepth(depth), scans->N, ReduceExponent(depth), nxy, nz, wxy, wz, 1 << depth,
-          static_cast<int64_t>(n), ws->d_lattice.as<int>());
-    }
-    CountLaunch();
-    HG_CUDA(cudaGetLastError());
+    bool packed = false;
+    rc = LaunchLattice(m, scans->CellsOfDepth(depth), scans->S, scans->N, depth, nxy, nz, wxy, wz,
+                       ws->d_lattice.as<int>(), stream, &packed);
+    if (rc != HG_OK) return rc;
     if (timed) {
       HG_CUDA(cudaEventRecord(e1, stream));
       HG_CUDA(cudaEventSynchronize(e1));
@@ -1647,8 +1681,8 @@ Rigid ToRigidF(const double* t, const double* q) {
                   static_cast<float>(q[3])}};
 }
 
-// MatchWithSearchParameters (:202-228).
-int MatchWithSearchParameters(const hg_fcsm* m, const SearchParameters& sp, const Rigid& node_pose,
+// MatchWithSearchParameters (:202-228) with the branch-and-bound replayed on the host.
+int HostReplayMatch(const hg_fcsm* m, const SearchParameters& sp, const Rigid& node_pose,
                               const Rigid& submap_pose, const hg_node_data* data, float min_score,
                               int shard_index, int num_shards, hg_match_result* result) {
   std::memset(result, 0, sizeof(*result));
@@ -1701,6 +1735,793 @@ int MatchWithSearchParameters(const hg_fcsm* m, const SearchParameters& sp, cons
   return HG_OK;
 }
 
+}  // namespace
+
+namespace hg {
+namespace {
+
+// ------------------------------------------------ device-resident search --
+//
+// The same search without a host decision per level, for one problem or a batch of problems that
+// share a matcher (all the (node, submap) pairs of one submap). Order-independent form of the
+// reference's depth-first search: the answer is the best-scoring leaf with
+// score > min_score that passes the low-resolution gate, and — every level of the pyramid being a
+// maximum over the finer one — a subtree whose root scores below a known valid leaf cannot hold it.
+//   phase A  lattice (one launch per problem), then a GREEDY DIVE from the best lattice candidate
+//            of every discrete scan: best child per level, one launch per level for all starts of
+//            all problems; the low-resolution gate on the dive's leaves gives every problem a
+//            bound B = score of its best valid dive leaf;
+//   phase B  every lattice candidate with score >= B seeds a frontier that is expanded level by
+//            level on the device (children with score >= B are appended to the next level's list
+//            with an atomic counter; the launches are persistent grids that read the counts from
+//            device memory), the gate runs on all surviving leaves, and the leaves that reach the
+//            best valid score are returned.
+// One synchronisation at the end (two when the caller exchanges the bound between the phases, as
+// the sharded full-submap search does). Without a bound (no dive leaf passed the gate) B is
+// "score > min_score". Exactly one winner is the answer, ties included in the sense that equal
+// scores were all kept; several winners (an exact tie), a bound that phase B cannot reach again
+// (a parent scored below its child: the pyramid is designed, not proven, to be an upper bound)
+// or a full list send that problem through the host replay above, which settles them in the
+// reference's visiting order.
+
+constexpr float kScoreMin = 0.1f;
+constexpr float kScoreMax = 1.f - kScoreMin;
+constexpr float kScoreScale = (kScoreMax - kScoreMin) / 255.f;
+
+// ScoreFromSum on the device: the same three float operations, unfused.
+__device__ __forceinline__ float DeviceScore(const int sum, const int num_points) {
+  const float value = __fdiv_rn(static_cast<float>(sum), static_cast<float>(num_points));
+  return __fadd_rn(kScoreMin, __fmul_rn(value, kScoreScale));
+}
+
+struct ProblemDev {
+  int scan_begin, S;       // this problem's discrete scans in the batch-wide scan list
+  int N, NL;               // high- and low-resolution points
+  long long cells_offset;  // ints into the batch's cell array: [level][scan][point][3]
+  long long level_stride;  // ints per level = S * N * 3
+  int low_offset;          // points into the batch's low-resolution cloud array
+  int wxy, wz;
+  float min_score;
+};
+
+// One discrete scan: owning problem and the pieces of GetPoseFromCandidate (:400-406) that do not
+// depend on the offset — translation of the scan pose and the renormalised rotation.
+struct ScanDev {
+  int problem;
+  float tx, ty, tz;
+  float qw, qx, qy, qz;
+};
+
+struct WinnerRec {
+  int scan, ox, oy, oz;  // scan = index in the batch-wide scan list
+  int sum;
+  float low;
+  int ancestor_sum;  // lattice sum of the leaf's lowest-resolution ancestor
+  int problem;
+};
+
+struct SearchDev {
+  const ProblemDev* problems;
+  const ScanDev* scans;
+  const int* cells;
+  const float* low_points;
+  const int* lattice;  // [total_scans * per_scan]
+  int4* starts;        // [total_scans] dive state
+  int* start_sums;     // -1 = the scan's best lattice candidate does not beat min_score
+  int* bound_bits;     // [P] score bits of the best valid dive leaf, 0 = none
+  int* thresh_bits;    // [P] phase B keeps score bits >= this
+  int* best_bits;      // [P] best valid leaf of phase B
+  int* win_count;      // [P]
+  int4* list[2];       // frontier of depth d in list[d & 1]
+  int* list_sum[2];
+  float* leaf_low;
+  int* counts;         // [depth] entries of the depth's list (may exceed list_cap: overflow)
+  int list_cap;
+  WinnerRec* winners;
+  int* winners_total;
+  int winners_cap;
+  unsigned long long* scored;  // [P] candidates scored below the lattice
+  int total_scans, per_scan, nxy, nz, step, max_depth, frd;
+  double min_low_resolution_score;
+};
+
+__device__ __forceinline__ const int* CellsOf(const SearchDev& s, const ProblemDev& P, const int local_scan,
+                                              const int depth) {
+  const int level = max(0, depth - s.frd + 1);
+  return s.cells + P.cells_offset + level * P.level_stride + static_cast<long long>(local_scan) * P.N * 3;
+}
+
+// Sum of one candidate at one depth, computed by a whole warp (every lane returns the total).
+__device__ __forceinline__ int WarpCandidateSum(const BrickTable& level, const DenseLevel& dense, const int* base,
+                                                const int N, const int ox, const int oy, const int oz,
+                                                const int lane) {
+  int sum = 0;
+  if (dense.data != nullptr) {
+    for (int i = lane; i < N; i += 32) {
+      const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
+      sum += LoadDenseU8(dense, x + ox, y + oy, z + oz);
+    }
+  } else {
+    for (int i = lane; i < N; i += 32) {
+      const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
+      sum += LoadU8(level, x + ox, y + oy, z + oz);
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+  return sum;
+}
+
+// Dive start of every discrete scan: its best lattice candidate (first one on equal sums).
+__global__ void __launch_bounds__(256) ArgmaxPerScanKernel(const SearchDev s) {
+  const int sg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (sg >= s.total_scans) return;
+  const int* sums = s.lattice + static_cast<long long>(sg) * s.per_scan;
+  int best = -1, at = 0x7fffffff;
+  for (int i = lane; i < s.per_scan; i += 32) {
+    const int v = sums[i];
+    if (v > best) {
+      best = v;
+      at = i;
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    const int ob = __shfl_xor_sync(0xffffffffu, best, d), oa = __shfl_xor_sync(0xffffffffu, at, d);
+    if (ob > best || (ob == best && oa < at)) {
+      best = ob;
+      at = oa;
+    }
+  }
+  if (lane != 0) return;
+  const ProblemDev& P = s.problems[s.scans[sg].problem];
+  const int iz = at / (s.nxy * s.nxy), rem = at - iz * s.nxy * s.nxy, iy = rem / s.nxy, ix = rem - iy * s.nxy;
+  s.starts[sg] = make_int4(sg, -P.wxy + ix * s.step, -P.wxy + iy * s.step, -P.wz + iz * s.step);
+  s.start_sums[sg] = DeviceScore(best, P.N) > P.min_score ? best : -1;
+}
+
+// One level of the dive: a CTA per start, a warp per child slot (z, y, x in {0, half}^3, the loop
+// nest at :441-461), the best child replaces the start.
+__global__ void __launch_bounds__(256) DiveLevelKernel(const SearchDev s, const BrickTable level,
+                                                       const DenseLevel dense, const int child_depth) {
+  __shared__ int slot_sum[8];
+  const int sg = blockIdx.x;
+  if (s.start_sums[sg] < 0) return;  // CTA-uniform
+  const int slot = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int4 p = s.starts[sg];
+  const ProblemDev& P = s.problems[s.scans[sg].problem];
+  const int half = 1 << child_depth;
+  const int cx = p.y + ((slot & 1) ? half : 0), cy = p.z + ((slot & 2) ? half : 0), cz = p.w + ((slot & 4) ? half : 0);
+  int sum = -1;
+  if (cx <= P.wxy && cy <= P.wxy && cz <= P.wz) {
+    const int e = max(0, child_depth - s.frd + 1);
+    sum = WarpCandidateSum(level, dense, CellsOf(s, P, sg - P.scan_begin, child_depth), P.N, cx >> e, cy >> e,
+                           cz >> e, lane);
+  }
+  if (lane == 0) slot_sum[slot] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int best = 0, valid = 0;
+    for (int k = 0; k < 8; ++k) {
+      valid += slot_sum[k] >= 0 ? 1 : 0;
+      if (slot_sum[k] > slot_sum[best]) best = k;
+    }
+    s.starts[sg] = make_int4(sg, p.y + ((best & 1) ? half : 0), p.z + ((best & 2) ? half : 0),
+                             p.w + ((best & 4) ? half : 0));
+    s.start_sums[sg] = slot_sum[best];
+    atomicAdd(&s.scored[s.scans[sg].problem], static_cast<unsigned long long>(valid));
+  }
+}
+
+// LowResolutionMatcher closure (low_resolution_matcher.cc:24-69) for candidates: a warp per
+// candidate evaluates the points' values in parallel and lane 0 adds them in cloud order — the
+// reference's float sum, bit for bit (see LowResolutionKernel). DIVE: the candidates are the dive
+// leaves and a valid one raises its problem's bound; otherwise they are phase B's leaves, the
+// score is kept and a valid one raises its problem's best.
+struct GateArgs {
+  GridDev grid;                // the low-resolution grid
+  float candidate_resolution;  // resolution the candidate offsets count in (the matcher's grid)
+};
+template <bool DIVE>
+__global__ void __launch_bounds__(128) GateKernel(const SearchDev s, const GateArgs g) {
+  __shared__ float staged[4][kLowChunk];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int count = DIVE ? s.total_scans : min(s.counts[0], s.list_cap);
+  float* mine = staged[warp];
+  for (int item = blockIdx.x * 4 + warp; item < count; item += gridDim.x * 4) {
+    const int4 c = DIVE ? s.starts[item] : s.list[0][item];
+    const int sum = DIVE ? s.start_sums[item] : s.list_sum[0][item];
+    if (sum < 0) continue;  // warp-uniform
+    const ScanDev sc = s.scans[c.x];
+    const ProblemDev& P = s.problems[sc.problem];
+    const float score_value = DeviceScore(sum, P.N);
+    // GetPoseFromCandidate (:400-406): Translation(resolution * offset) * scan pose, in float.
+    const float tx = __fadd_rn(sc.tx, __fmul_rn(g.candidate_resolution, static_cast<float>(c.y)));
+    const float ty = __fadd_rn(sc.ty, __fmul_rn(g.candidate_resolution, static_cast<float>(c.z)));
+    const float tz = __fadd_rn(sc.tz, __fmul_rn(g.candidate_resolution, static_cast<float>(c.w)));
+    float low = -__int_as_float(0x7f800000);  // an empty cloud is 0 / 0 in the reference: never passes
+    if (P.NL > 0) {
+      const float* points = s.low_points + 3 * static_cast<long long>(P.low_offset);
+      float acc = 0.f;
+      for (int base = 0; base < P.NL; base += kLowChunk) {
+        const int n = min(kLowChunk, P.NL - base);
+        for (int k = lane; k < n; k += 32) {
+          const int i = base + k;
+          float wx, wy, wz;
+          RotateF(sc.qw, sc.qx, sc.qy, sc.qz, points[3 * i], points[3 * i + 1], points[3 * i + 2], &wx, &wy, &wz);
+          wx = __fadd_rn(wx, tx);
+          wy = __fadd_rn(wy, ty);
+          wz = __fadd_rn(wz, tz);
+          const int cx = CellIndexFast(wx, g.grid.resolution, g.grid.inv_resolution),
+                    cy = CellIndexFast(wy, g.grid.resolution, g.grid.inv_resolution),
+                    cz = CellIndexFast(wz, g.grid.resolution, g.grid.inv_resolution);
+          float v;
+          if (g.grid.kind == kGridProb) {
+            v = Decode(g.grid.a, LoadU16(g.grid.table, cx, cy, cz));
+          } else {
+            const float tsd = Decode(g.grid.a, LoadTsdf(g.grid.table, cx, cy, cz).x);
+            v = __fsub_rn(1.f, fabsf(__fdiv_rn(tsd, g.grid.max_tsd)));
+          }
+          mine[k] = v;
+        }
+        __syncwarp();
+        if (lane == 0) {
+          for (int k = 0; k < n; ++k) acc = __fadd_rn(acc, mine[k]);
+        }
+        __syncwarp();
+      }
+      low = __fdiv_rn(acc, static_cast<float>(P.NL));
+    }
+    if (lane == 0) {
+      const bool valid = score_value > P.min_score && static_cast<double>(low) >= s.min_low_resolution_score;
+      if (DIVE) {
+        if (valid) atomicMax(&s.bound_bits[sc.problem], __float_as_int(score_value));
+      } else {
+        s.leaf_low[item] = low;
+        if (valid) atomicMax(&s.best_bits[sc.problem], __float_as_int(score_value));
+      }
+    }
+  }
+}
+
+// Phase B keeps candidates whose score bits are >= thresh_bits: the problem's bound (the larger of
+// its own dive's and, for a sharded search, the one the other shards found), or the smallest
+// score above min_score when there is none. Scores are >= 0.1, so their bit patterns order like
+// the floats.
+__global__ void ThresholdKernel(const SearchDev s, const int num_problems, const float external_bound) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= num_problems) return;
+  float t = nextafterf(s.problems[p].min_score, __int_as_float(0x7f800000));
+  if (!(t > 0.f)) t = 0.f;
+  int bits = __float_as_int(t);
+  bits = max(bits, s.bound_bits[p]);
+  if (external_bound > 0.f) bits = max(bits, __float_as_int(external_bound));
+  s.thresh_bits[p] = bits;
+}
+
+// Warp-aggregated append of the lanes with 'keep' set; returns each lane's position (or -1).
+__device__ __forceinline__ int WarpAppend(int* counter, const bool keep) {
+  const unsigned mask = __ballot_sync(0xffffffffu, keep);
+  if (mask == 0) return -1;
+  const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+  int base = 0;
+  if (lane == leader) base = atomicAdd(counter, __popc(mask));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  return keep ? base + __popc(mask & ((1u << lane) - 1u)) : -1;
+}
+
+// Lattice candidates that reach their problem's threshold -> the frontier of the lowest
+// resolution.
+__global__ void __launch_bounds__(256) SeedKernel(const SearchDev s) {
+  const long long n = static_cast<long long>(s.total_scans) * s.per_scan;
+  const int d = s.max_depth;
+  for (long long base = static_cast<long long>(blockIdx.x) * blockDim.x; base < n;
+       base += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long i = base + threadIdx.x;
+    bool keep = false;
+    int sg = 0, at = 0, sum = 0;
+    if (i < n) {
+      sg = static_cast<int>(i / s.per_scan);
+      at = static_cast<int>(i - static_cast<long long>(sg) * s.per_scan);
+      sum = s.lattice[i];
+      const int p = s.scans[sg].problem;
+      keep = __float_as_int(DeviceScore(sum, s.problems[p].N)) >= s.thresh_bits[p];
+    }
+    const int pos = WarpAppend(&s.counts[d], keep);
+    if (keep) {
+      if (pos < s.list_cap) {
+        const ProblemDev& P = s.problems[s.scans[sg].problem];
+        const int iz = at / (s.nxy * s.nxy), rem = at - iz * s.nxy * s.nxy, iy = rem / s.nxy, ix = rem - iy * s.nxy;
+        s.list[d & 1][pos] = make_int4(sg, -P.wxy + ix * s.step, -P.wxy + iy * s.step, -P.wz + iz * s.step);
+        s.list_sum[d & 1][pos] = sum;
+      }
+    }
+  }
+}
+
+// Children of the frontier of 'child_depth + 1' that reach the threshold -> frontier of
+// child_depth. A warp per (parent, slot); persistent grid, the parent count is read from the device.
+__global__ void __launch_bounds__(256) ExpandKernel(const SearchDev s, const BrickTable level, const DenseLevel dense,
+                                                    const int child_depth) {
+  const int d = child_depth + 1;
+  const int parents = min(s.counts[d], s.list_cap);
+  const int lane = threadIdx.x & 31;
+  const long long warps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  const int half = 1 << child_depth;
+  const int e = max(0, child_depth - s.frd + 1);
+  for (long long w = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+       w < static_cast<long long>(parents) * 8; w += warps) {
+    const int4 p = s.list[d & 1][w >> 3];
+    const int slot = static_cast<int>(w & 7);
+    const int problem = s.scans[p.x].problem;
+    const ProblemDev& P = s.problems[problem];
+    const int cx = p.y + ((slot & 1) ? half : 0), cy = p.z + ((slot & 2) ? half : 0), cz = p.w + ((slot & 4) ? half : 0);
+    if (cx > P.wxy || cy > P.wxy || cz > P.wz) continue;  // the reference's 'break'
+    const int sum = WarpCandidateSum(level, dense, CellsOf(s, P, p.x - P.scan_begin, child_depth), P.N, cx >> e,
+                                     cy >> e, cz >> e, lane);
+    if (lane == 0) atomicAdd(&s.scored[problem], 1ull);
+    if (lane == 0 && __float_as_int(DeviceScore(sum, P.N)) >= s.thresh_bits[problem]) {
+      const int pos = atomicAdd(&s.counts[child_depth], 1);
+      if (pos < s.list_cap) {
+        s.list[child_depth & 1][pos] = make_int4(p.x, cx, cy, cz);
+        s.list_sum[child_depth & 1][pos] = sum;
+      }
+    }
+  }
+}
+
+// The valid leaves that reach their problem's best valid score.
+__global__ void __launch_bounds__(256) WinnersKernel(const SearchDev s) {
+  const int count = min(s.counts[0], s.list_cap);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+    const int4 c = s.list[0][i];
+    const int sum = s.list_sum[0][i];
+    const int problem = s.scans[c.x].problem;
+    const ProblemDev& P = s.problems[problem];
+    const float score_value = DeviceScore(sum, P.N);
+    const float low = s.leaf_low[i];
+    if (!(score_value > P.min_score) || !(static_cast<double>(low) >= s.min_low_resolution_score)) continue;
+    if (__float_as_int(score_value) != s.best_bits[problem]) continue;
+    atomicAdd(&s.win_count[problem], 1);
+    const int at = atomicAdd(s.winners_total, 1);
+    if (at >= s.winners_cap) continue;
+    const int ix = (c.y + P.wxy) >> s.max_depth, iy = (c.z + P.wxy) >> s.max_depth, iz = (c.w + P.wz) >> s.max_depth;
+    WinnerRec r;
+    r.scan = c.x; r.ox = c.y; r.oy = c.z; r.oz = c.w;
+    r.sum = sum;
+    r.low = low;
+    r.ancestor_sum = s.lattice[static_cast<long long>(c.x) * s.per_scan + (iz * s.nxy + iy) * s.nxy + ix];
+    r.problem = problem;
+    s.winners[at] = r;
+  }
+}
+
+}  // namespace
+}  // namespace hg
+
+namespace {
+
+struct CtrlDev {
+  int counts[32];
+  int winners_total;
+  int pad;
+};
+
+// Host driver of the device-resident search: problems are added (host half of
+// GenerateDiscreteScans), then phase A and phase B are queued on the calling thread's stream.
+class DeviceSearch {
+ public:
+  struct Outcome {
+    bool found = false;
+    bool needs_host_replay = false;  // exact tie, unconfirmed bound or a full list
+    int scan = 0, ox = 0, oy = 0, oz = 0;  // scan = local index in the problem's scan list
+    float score = 0.f, low = 0.f;
+    float ancestor_score = 0.f;
+    int64_t ancestor_index = 0;  // generation index of the lowest-resolution ancestor, unsharded scan numbering
+    int64_t scored = 0;
+    float local_bound = 0.f;  // this problem's own dive bound (0 = none)
+  };
+
+  DeviceSearch(const hg_fcsm* m, cudaStream_t stream) : m_(m), stream_(stream), ws_(&GetWorkspace(m->device)) {}
+  ~DeviceSearch() {
+    if (e0_) cudaEventDestroy(e0_);
+    if (e1_) cudaEventDestroy(e1_);
+  }
+
+  int AddProblem(const SearchParameters& sp, const Rigid& node_pose, const Rigid& submap_pose,
+                 const hg_node_data* data, float min_score, int shard_index, int num_shards) {
+    if (!problems_.empty()) {
+      HG_REQUIRE(sp.wxy == problems_[0].sp.wxy && sp.wz == problems_[0].sp.wz,
+                 "device search: the problems of one batch must share their search window");
+    }
+    problems_.emplace_back();
+    Problem& p = problems_.back();
+    p.sp = sp;
+    p.data = data;
+    p.min_score = min_score;
+    return ComputeScanPoses(m_, sp, data, node_pose, submap_pose, shard_index, num_shards, &p.scans);
+  }
+  int num_problems() const { return static_cast<int>(problems_.size()); }
+  const ScanSet& scans(int p) const { return problems_[p].scans; }
+  float lattice_ms() const { return lattice_ms_; }
+  int64_t lattice_candidates(int p) const { return static_cast<int64_t>(problems_[p].scans.S) * per_scan_; }
+  int launches() const { return launches_; }
+
+  // Uploads, discretises, scores the lattices, dives and gates the dive's leaves.
+  int RunPhaseA(bool time_lattice) {
+    const int P = num_problems();
+    const int D = m_->options.branch_and_bound_depth;
+    max_depth_ = D - 1;
+    HG_REQUIRE(D >= 1 && D <= 32, "device search: bad branch_and_bound_depth");
+    const SearchParameters& sp = problems_[0].sp;
+    step_ = 1 << max_depth_;
+    nxy_ = (2 * sp.wxy + step_) / step_;
+    nz_ = (2 * sp.wz + step_) / step_;
+    per_scan_ = nxy_ * nxy_ * nz_;
+    // ---- layout of the upload arena: points | low points | scan poses (7 floats) | ScanDev | ProblemDev
+    size_t n_points = 0, n_low = 0, n_scans = 0, cell_ints = 0;
+    std::vector<ProblemDev> pd(P);
+    for (int p = 0; p < P; ++p) {
+      const ScanSet& sc = problems_[p].scans;
+      ProblemDev& d = pd[p];
+      d.scan_begin = static_cast<int>(n_scans);
+      d.S = sc.S;
+      d.N = sc.N;
+      d.NL = std::max(0, problems_[p].data->num_low_resolution_points);
+      d.cells_offset = static_cast<long long>(cell_ints);
+      d.level_stride = static_cast<long long>(sc.S) * sc.N * 3;
+      d.low_offset = static_cast<int>(n_low);
+      d.wxy = sp.wxy;
+      d.wz = sp.wz;
+      d.min_score = problems_[p].min_score;
+      problems_[p].point_offset = n_points;
+      n_points += static_cast<size_t>(sc.N);
+      n_low += static_cast<size_t>(d.NL);
+      n_scans += static_cast<size_t>(sc.S);
+      cell_ints += static_cast<size_t>(1 + sc.num_low_levels) * sc.S * sc.N * 3;
+    }
+    total_scans_ = static_cast<int>(n_scans);
+    HG_REQUIRE(n_scans * static_cast<size_t>(per_scan_) < (size_t(1) << 31), "device search: lattice too large");
+    if (total_scans_ == 0) return HG_OK;
+    const size_t off_low = n_points * 3 * sizeof(float);
+    const size_t off_poses = off_low + n_low * 3 * sizeof(float);
+    const size_t off_scans = (off_poses + n_scans * 7 * sizeof(float) + 15) & ~size_t(15);
+    const size_t off_problems = (off_scans + n_scans * sizeof(ScanDev) + 15) & ~size_t(15);
+    const size_t upload_bytes = off_problems + P * sizeof(ProblemDev);
+    int rc = ws_->h_upload.Reserve(upload_bytes);
+    if (rc != HG_OK) return rc;
+    rc = ws_->d_upload.Reserve(upload_bytes);
+    if (rc != HG_OK) return rc;
+    char* h = ws_->h_upload.as<char>();
+    const int flavor = m_->options.float_flavor;
+    for (int p = 0; p < P; ++p) {
+      const Problem& pr = problems_[p];
+      std::memcpy(h + pr.point_offset * 3 * sizeof(float), pr.data->high_resolution_point_cloud,
+                  static_cast<size_t>(pr.scans.N) * 3 * sizeof(float));
+      if (pd[p].NL > 0) {
+        std::memcpy(h + off_low + static_cast<size_t>(pd[p].low_offset) * 3 * sizeof(float),
+                    pr.data->low_resolution_point_cloud, static_cast<size_t>(pd[p].NL) * 3 * sizeof(float));
+      }
+      float* poses = reinterpret_cast<float*>(h + off_poses) + 7 * static_cast<size_t>(pd[p].scan_begin);
+      ScanDev* sd = reinterpret_cast<ScanDev*>(h + off_scans) + pd[p].scan_begin;
+      for (int s = 0; s < pr.scans.S; ++s) {
+        const Rigid& r = pr.scans.poses[s];
+        float* o = poses + 7 * s;
+        o[0] = r.t.x; o[1] = r.t.y; o[2] = r.t.z; o[3] = r.q.w; o[4] = r.q.x; o[5] = r.q.y; o[6] = r.q.z;
+        // GetPoseFromCandidate with a zero offset: what every candidate of this scan shares.
+        const Rigid leaf = fgeom::RigidProduct(Rigid{V3{0.f, 0.f, 0.f}, Q4{1.f, 0.f, 0.f, 0.f}}, r, flavor);
+        sd[s] = ScanDev{p, leaf.t.x, leaf.t.y, leaf.t.z, leaf.q.w, leaf.q.x, leaf.q.y, leaf.q.z};
+      }
+    }
+    std::memcpy(h + off_problems, pd.data(), P * sizeof(ProblemDev));
+    HG_CUDA(cudaMemcpyAsync(ws_->d_upload.p, h, upload_bytes, cudaMemcpyHostToDevice, stream_));
+    char* d = ws_->d_upload.as<char>();
+    // ---- device state
+    const size_t lattice_n = n_scans * per_scan_;
+    list_cap_ = kListCapacity;
+    winners_cap_ = std::max(256, 4 * P);
+    if ((rc = ws_->d_cells.Reserve(cell_ints * sizeof(int))) != HG_OK) return rc;
+    if ((rc = ws_->d_lattice.Reserve(lattice_n * sizeof(int))) != HG_OK) return rc;
+    if ((rc = ws_->d_starts.Reserve(n_scans * (sizeof(int4) + sizeof(int)))) != HG_OK) return rc;
+    if ((rc = ws_->d_lists.Reserve(static_cast<size_t>(list_cap_) * (2 * sizeof(int4) + 2 * sizeof(int) + sizeof(float)))) != HG_OK)
+      return rc;
+    // control block: CtrlDev | per problem: bound, thresh, best, win_count (ints) | scored (u64) | winners
+    const size_t off_pp = sizeof(CtrlDev);
+    const size_t off_scored = (off_pp + 4 * P * sizeof(int) + 7) & ~size_t(7);
+    const size_t off_win = (off_scored + P * sizeof(unsigned long long) + 15) & ~size_t(15);
+    ctrl_bytes_ = off_win + winners_cap_ * sizeof(WinnerRec);
+    off_pp_ = off_pp;
+    off_scored_ = off_scored;
+    off_win_ = off_win;
+    if ((rc = ws_->d_ctrl.Reserve(ctrl_bytes_)) != HG_OK) return rc;
+    if ((rc = ws_->h_ctrl.Reserve(ctrl_bytes_)) != HG_OK) return rc;
+    HG_CUDA(cudaMemsetAsync(ws_->d_ctrl.p, 0, off_win, stream_));
+    char* c = ws_->d_ctrl.as<char>();
+    SearchDev& s = dev_;
+    s.problems = reinterpret_cast<const ProblemDev*>(d + off_problems);
+    s.scans = reinterpret_cast<const ScanDev*>(d + off_scans);
+    s.cells = ws_->d_cells.as<int>();
+    s.low_points = reinterpret_cast<const float*>(d + off_low);
+    s.lattice = ws_->d_lattice.as<int>();
+    s.starts = ws_->d_starts.as<int4>();
+    s.start_sums = reinterpret_cast<int*>(ws_->d_starts.as<int4>() + n_scans);
+    int* pp = reinterpret_cast<int*>(c + off_pp);
+    s.bound_bits = pp;
+    s.thresh_bits = pp + P;
+    s.best_bits = pp + 2 * P;
+    s.win_count = pp + 3 * P;
+    char* l = ws_->d_lists.as<char>();
+    s.list[0] = reinterpret_cast<int4*>(l);
+    s.list[1] = s.list[0] + list_cap_;
+    s.list_sum[0] = reinterpret_cast<int*>(s.list[1] + list_cap_);
+    s.list_sum[1] = s.list_sum[0] + list_cap_;
+    s.leaf_low = reinterpret_cast<float*>(s.list_sum[1] + list_cap_);
+    CtrlDev* ctrl = reinterpret_cast<CtrlDev*>(c);
+    s.counts = ctrl->counts;
+    s.list_cap = list_cap_;
+    s.winners = reinterpret_cast<WinnerRec*>(c + off_win);
+    s.winners_total = &ctrl->winners_total;
+    s.winners_cap = winners_cap_;
+    s.scored = reinterpret_cast<unsigned long long*>(c + off_scored);
+    s.total_scans = total_scans_;
+    s.per_scan = per_scan_;
+    s.nxy = nxy_;
+    s.nz = nz_;
+    s.step = step_;
+    s.max_depth = max_depth_;
+    s.frd = problems_[0].scans.frd;
+    s.min_low_resolution_score = m_->options.min_low_resolution_score;
+    // ---- discretise and score the lattice, problem by problem
+    const float* d_points = reinterpret_cast<const float*>(d);
+    const float* d_poses = reinterpret_cast<const float*>(d + off_poses);
+    const float resolution = m_->resolution;
+    for (int p = 0; p < P; ++p) {
+      const ScanSet& sc = problems_[p].scans;
+      if (sc.S == 0) continue;
+      const int64_t total = static_cast<int64_t>(sc.S) * sc.N;
+      DiscretizeKernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream_>>>(
+          d_points + 3 * problems_[p].point_offset, sc.N, d_poses + 7 * static_cast<size_t>(pd[p].scan_begin), sc.S,
+          resolution, 1.f / resolution, sc.num_low_levels, -sp.wxy, -sp.wz, ws_->d_cells.as<int>() + pd[p].cells_offset);
+      CountLaunch();
+      ++launches_;
+    }
+    HG_CUDA(cudaGetLastError());
+    if (time_lattice) {
+      HG_CUDA(cudaEventCreate(&e0_));
+      HG_CUDA(cudaEventCreate(&e1_));
+      HG_CUDA(cudaEventRecord(e0_, stream_));
+    }
+    const int lattice_level = std::max(0, max_depth_ - s.frd + 1);
+    for (int p = 0; p < P; ++p) {
+      const ScanSet& sc = problems_[p].scans;
+      if (sc.S == 0) continue;
+      const int* cells = ws_->d_cells.as<int>() + pd[p].cells_offset + lattice_level * pd[p].level_stride;
+      rc = LaunchLattice(m_, cells, sc.S, sc.N, max_depth_, nxy_, nz_, sp.wxy, sp.wz,
+                         ws_->d_lattice.as<int>() + static_cast<size_t>(pd[p].scan_begin) * per_scan_, stream_, nullptr);
+      if (rc != HG_OK) return rc;
+      ++launches_;
+    }
+    if (time_lattice) HG_CUDA(cudaEventRecord(e1_, stream_));
+    // ---- dive
+    ArgmaxPerScanKernel<<<(total_scans_ * 32 + 255) / 256, 256, 0, stream_>>>(s);
+    CountLaunch();
+    ++launches_;
+    for (int depth = max_depth_; depth >= 1; --depth) {
+      const hg_stack_level& L = m_->stack->levels[depth - 1];
+      DiveLevelKernel<<<total_scans_, 256, 0, stream_>>>(s, L.table, L.dense, depth - 1);
+      CountLaunch();
+      ++launches_;
+    }
+    GateKernel<true><<<std::min(PersistentBlocks(16), (total_scans_ + 3) / 4), 128, 0, stream_>>>(s, GateGrid());
+    CountLaunch();
+    ++launches_;
+    HG_CUDA(cudaGetLastError());
+    phase_a_done_ = true;
+    return HG_OK;
+  }
+
+  // Synchronises and returns every problem's own dive bound (0 = none).
+  int ReadBounds(std::vector<float>* bounds) {
+    const int P = num_problems();
+    bounds->assign(P, 0.f);
+    if (total_scans_ == 0) return HG_OK;
+    HG_CUDA(cudaMemcpyAsync(ws_->h_ctrl.as<char>() + off_pp_, ws_->d_ctrl.as<char>() + off_pp_, P * sizeof(int),
+                            cudaMemcpyDeviceToHost, stream_));
+    HG_CUDA(cudaStreamSynchronize(stream_));
+    const int* bits = reinterpret_cast<const int*>(ws_->h_ctrl.as<char>() + off_pp_);
+    for (int p = 0; p < P; ++p) std::memcpy(&(*bounds)[p], &bits[p], sizeof(float));
+    return HG_OK;
+  }
+
+  // Frontier expansion under the bound, leaf gate, winners; one synchronisation at the end.
+  // external_bound > 0: a bound found elsewhere (other shards of the same search).
+  int RunPhaseB(float external_bound, std::vector<Outcome>* outcomes) {
+    const int P = num_problems();
+    outcomes->assign(P, Outcome());
+    if (total_scans_ == 0) return HG_OK;
+    const SearchDev& s = dev_;
+    ThresholdKernel<<<(P + 127) / 128, 128, 0, stream_>>>(s, P, external_bound);
+    SeedKernel<<<PersistentBlocks(8), 256, 0, stream_>>>(s);
+    CountLaunch(2);
+    launches_ += 2;
+    for (int depth = max_depth_; depth >= 1; --depth) {
+      const hg_stack_level& L = m_->stack->levels[depth - 1];
+      ExpandKernel<<<PersistentBlocks(8), 256, 0, stream_>>>(s, L.table, L.dense, depth - 1);
+      CountLaunch();
+      ++launches_;
+    }
+    GateKernel<false><<<PersistentBlocks(16), 128, 0, stream_>>>(s, GateGrid());
+    WinnersKernel<<<PersistentBlocks(4), 256, 0, stream_>>>(s);
+    CountLaunch(2);
+    launches_ += 2;
+    HG_CUDA(cudaGetLastError());
+    HG_CUDA(cudaMemcpyAsync(ws_->h_ctrl.p, ws_->d_ctrl.p, ctrl_bytes_, cudaMemcpyDeviceToHost, stream_));
+    HG_CUDA(cudaStreamSynchronize(stream_));
+    if (e0_ != nullptr) HG_CUDA(cudaEventElapsedTime(&lattice_ms_, e0_, e1_));
+    const char* h = ws_->h_ctrl.as<char>();
+    const CtrlDev* ctrl = reinterpret_cast<const CtrlDev*>(h);
+    const int* pp = reinterpret_cast<const int*>(h + off_pp_);
+    const unsigned long long* scored = reinterpret_cast<const unsigned long long*>(h + off_scored_);
+    const WinnerRec* winners = reinterpret_cast<const WinnerRec*>(h + off_win_);
+    bool overflow = false;
+    for (int dd = 0; dd <= max_depth_; ++dd) overflow = overflow || ctrl->counts[dd] > list_cap_;
+    if (TraceEnabled()) {
+      std::fprintf(stderr, "[hg trace] device search: %d problems, %d scans, frontier sizes", P, total_scans_);
+      for (int dd = max_depth_; dd >= 0; --dd) std::fprintf(stderr, " %d", ctrl->counts[dd]);
+      std::fprintf(stderr, ", winners %d\n", ctrl->winners_total);
+    }
+    const int recorded = std::min(ctrl->winners_total, winners_cap_);
+    for (int p = 0; p < P; ++p) {
+      Outcome& o = (*outcomes)[p];
+      const ScanSet& sc = problems_[p].scans;
+      o.scored = static_cast<int64_t>(scored[p]) + static_cast<int64_t>(sc.S) * per_scan_;
+      std::memcpy(&o.local_bound, &pp[p], sizeof(float));
+      const int thresh_bits = pp[P + p], wins = pp[3 * P + p];
+      if (overflow || ctrl->winners_total > winners_cap_) {
+        o.needs_host_replay = sc.S > 0;
+        continue;
+      }
+      if (wins == 0) {
+        // The problem's own bound is a leaf phase B must meet again; if it did not, a parent
+        // scored below its child somewhere.
+        o.needs_host_replay = pp[p] != 0 && thresh_bits == pp[p];
+        continue;
+      }
+      if (wins > 1) {
+        o.needs_host_replay = true;  // exact tie: the reference's visiting order decides
+        continue;
+      }
+      for (int k = 0; k < recorded; ++k) {
+        const WinnerRec& w = winners[k];
+        if (w.problem != p) continue;
+        o.found = true;
+        o.scan = w.scan - scan_begin(p);
+        o.ox = w.ox; o.oy = w.oy; o.oz = w.oz;
+        o.score = ScoreFromSum(w.sum, sc.N);
+        o.low = w.low;
+        o.ancestor_score = ScoreFromSum(w.ancestor_sum, sc.N);
+        const int ix = (w.ox + problems_[p].sp.wxy) >> max_depth_, iy = (w.oy + problems_[p].sp.wxy) >> max_depth_,
+                  iz = (w.oz + problems_[p].sp.wz) >> max_depth_;
+        o.ancestor_index = static_cast<int64_t>(sc.global_scan_index[o.scan]) * per_scan_ + (iz * nxy_ + iy) * nxy_ + ix;
+        break;
+      }
+    }
+    return HG_OK;
+  }
+
+  // GetPoseFromCandidate (:400-406).
+  Rigid PoseOf(int p, const Outcome& o) const {
+    const Rigid translation{V3{m_->resolution * static_cast<float>(o.ox), m_->resolution * static_cast<float>(o.oy),
+                               m_->resolution * static_cast<float>(o.oz)},
+                            Q4{1.f, 0.f, 0.f, 0.f}};
+    return fgeom::RigidProduct(translation, problems_[p].scans.poses[o.scan], m_->options.float_flavor);
+  }
+
+ private:
+  static constexpr int kListCapacity = 1 << 20;
+  struct Problem {
+    SearchParameters sp;
+    const hg_node_data* data = nullptr;
+    float min_score = 0.f;
+    ScanSet scans;
+    size_t point_offset = 0;
+  };
+  int scan_begin(int p) const {
+    int b = 0;
+    for (int k = 0; k < p; ++k) b += problems_[k].scans.S;
+    return b;
+  }
+  GateArgs GateGrid() const { return GateArgs{m_->low_grid->dev, m_->resolution}; }
+  static int PersistentBlocks(int per_sm) {
+    static const int sms = [] {
+      int dev = 0, n = 148;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+      return n;
+    }();
+    return sms * per_sm;
+  }
+
+  const hg_fcsm* m_;
+  cudaStream_t stream_;
+  Workspace* ws_;
+  std::vector<Problem> problems_;
+  SearchDev dev_;
+  int max_depth_ = 0, step_ = 1, nxy_ = 0, nz_ = 0, per_scan_ = 0, total_scans_ = 0;
+  int list_cap_ = 0, winners_cap_ = 0;
+  size_t ctrl_bytes_ = 0, off_pp_ = 0, off_scored_ = 0, off_win_ = 0;
+  cudaEvent_t e0_ = nullptr, e1_ = nullptr;
+  float lattice_ms_ = 0.f;
+  int launches_ = 0;
+  bool phase_a_done_ = false;
+};
+
+void FillResult(const DeviceSearch& search, int p, const DeviceSearch::Outcome& o, hg_match_result* result) {
+  const ScanSet& scans = search.scans(p);
+  std::memset(result, 0, sizeof(*result));
+  result->pose_rotation[0] = 1.0;
+  result->num_discrete_scans = scans.S;
+  result->num_candidates_scored = o.scored;
+  result->num_candidates_visited = o.scored;
+  result->num_score_launches = search.launches();
+  result->num_lowest_resolution_candidates = search.lattice_candidates(p);
+  result->lowest_resolution_kernel_ms = search.lattice_ms();
+  result->dive_bound = o.local_bound;
+  if (!o.found) return;
+  const Rigid pose = search.PoseOf(p, o);
+  result->found = 1;
+  result->score = o.score;
+  result->pose_translation[0] = pose.t.x;
+  result->pose_translation[1] = pose.t.y;
+  result->pose_translation[2] = pose.t.z;
+  result->pose_rotation[0] = pose.q.w;
+  result->pose_rotation[1] = pose.q.x;
+  result->pose_rotation[2] = pose.q.y;
+  result->pose_rotation[3] = pose.q.z;
+  result->rotational_score = scans.rotational_scores[o.scan];
+  result->low_resolution_score = o.low;
+  result->best_scan_index = scans.global_scan_index[o.scan];
+  result->best_offset[0] = o.ox;
+  result->best_offset[1] = o.oy;
+  result->best_offset[2] = o.oz;
+  result->best_ancestor_score = o.ancestor_score;
+  result->best_ancestor_index = o.ancestor_index;
+}
+
+// HG_SEARCH_HOST_REPLAY=1 sends every search through the host replay (tests compare the two).
+bool ForceHostReplay() { return std::getenv("HG_SEARCH_HOST_REPLAY") != nullptr; }
+
+// MatchWithSearchParameters (:202-228): device-resident search; strict visiting order, exact ties
+// and the other cases DeviceSearch hands back go through the host replay.
+int MatchWithSearchParameters(const hg_fcsm* m, const SearchParameters& sp, const Rigid& node_pose,
+                              const Rigid& submap_pose, const hg_node_data* data, float min_score,
+                              int shard_index, int num_shards, hg_match_result* result) {
+  if (m->options.strict_visit_order != 0 || ForceHostReplay()) {
+    return HostReplayMatch(m, sp, node_pose, submap_pose, data, min_score, shard_index, num_shards, result);
+  }
+  HG_CUDA(cudaSetDevice(m->device));
+  cudaStream_t stream = ThreadStream();
+  HG_REQUIRE(stream != nullptr, "hg_fcsm: cannot create a stream");
+  PhaseTimer pt;
+  DeviceSearch search(m, stream);
+  int rc = search.AddProblem(sp, node_pose, submap_pose, data, min_score, shard_index, num_shards);
+  if (rc != HG_OK) return rc;
+  const bool time_lattice = static_cast<int64_t>(search.scans(0).S) * search.scans(0).N >= (int64_t(1) << 20);
+  rc = search.RunPhaseA(time_lattice);
+  if (rc != HG_OK) return rc;
+  std::vector<DeviceSearch::Outcome> outcomes;
+  rc = search.RunPhaseB(0.f, &outcomes);
+  if (rc != HG_OK) return rc;
+  if (TraceEnabled()) std::fprintf(stderr, "[hg trace] device search: %.2f ms\n", pt.Lap());
+  if (outcomes[0].needs_host_replay) {
+    if (TraceEnabled()) std::fprintf(stderr, "[hg trace] device search handed the problem to the host replay\n");
+    return HostReplayMatch(m, sp, node_pose, submap_pose, data, min_score, shard_index, num_shards, result);
+  }
+  FillResult(search, 0, outcomes[0], result);
+  return HG_OK;
+}
+
 int CheckNodeData(const hg_node_data* d) {
   HG_REQUIRE(d != nullptr, "null node data");
   HG_REQUIRE(d->num_high_resolution_points > 0 && d->high_resolution_point_cloud != nullptr,
@@ -1709,6 +2530,18 @@ int CheckNodeData(const hg_node_data* d) {
   HG_REQUIRE(d->num_low_resolution_points == 0 || d->low_resolution_point_cloud != nullptr,
              "node data: null low resolution point cloud");
   return HG_OK;
+}
+
+// MatchFullSubmap's window (:181-192).
+SearchParameters FullSubmapWindow(const hg_fcsm* m, const hg_node_data* data) {
+  float max_point_distance = 0.f;
+  const float* pts = data->high_resolution_point_cloud;
+  for (int i = 0; i < data->num_high_resolution_points; ++i) {
+    max_point_distance = std::max(max_point_distance, fgeom::Norm3(V3{pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]}));
+  }
+  const int linear_window_size =
+      (m->width_in_voxels + 1) / 2 + static_cast<int>(std::lround(max_point_distance / m->resolution + 0.5f));
+  return SearchParameters{linear_window_size, linear_window_size, M_PI};
 }
 
 SearchParameters LocalWindow(const hg_fcsm* m) {
@@ -1800,20 +2633,141 @@ int hg_fcsm_match_full_submap(const hg_fcsm* m, const double* global_node_rotati
              "hg_fcsm_match_full_submap: bad shard");
   const int rc = CheckNodeData(data);
   if (rc != HG_OK) return rc;
-  // :181-192
-  float max_point_distance = 0.f;
-  const float* pts = data->high_resolution_point_cloud;
-  for (int i = 0; i < data->num_high_resolution_points; ++i) {
-    max_point_distance = std::max(max_point_distance, fgeom::Norm3(V3{pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]}));
-  }
-  const int linear_window_size =
-      (m->width_in_voxels + 1) / 2 + static_cast<int>(std::lround(max_point_distance / m->resolution + 0.5f));
-  const SearchParameters sp{linear_window_size, linear_window_size, M_PI};
+  const SearchParameters sp = FullSubmapWindow(m, data);
   const double zero[3] = {0., 0., 0.};
   return MatchWithSearchParameters(m, sp, ToRigidF(zero, global_node_rotation),
                                    ToRigidF(zero, global_submap_rotation), data, min_score, shard_index,
                                    num_shards, result);
 }
+
+int hg_fcsm_match_batch(const hg_fcsm* m, int num_problems, const double* global_node_poses,
+                        const double* global_submap_poses, const hg_node_data* data, float min_score,
+                        hg_match_result* results) {
+  HG_REQUIRE(m && num_problems >= 0 && (num_problems == 0 || (global_node_poses && global_submap_poses && data && results)),
+             "hg_fcsm_match_batch: bad arguments");
+  for (int p = 0; p < num_problems; ++p) {
+    const int rc = CheckNodeData(&data[p]);
+    if (rc != HG_OK) return rc;
+  }
+  const SearchParameters sp = LocalWindow(m);
+  if (m->options.strict_visit_order != 0 || ForceHostReplay()) {
+    for (int p = 0; p < num_problems; ++p) {
+      const int rc = HostReplayMatch(m, sp, ToRigidF(global_node_poses + 7 * p, global_node_poses + 7 * p + 3),
+                                     ToRigidF(global_submap_poses + 7 * p, global_submap_poses + 7 * p + 3), &data[p],
+                                     min_score, 0, 1, &results[p]);
+      if (rc != HG_OK) return rc;
+    }
+    return HG_OK;
+  }
+  HG_CUDA(cudaSetDevice(m->device));
+  cudaStream_t stream = ThreadStream();
+  HG_REQUIRE(stream != nullptr, "hg_fcsm: cannot create a stream");
+  // Sub-batches bounded by the memory of the discretised scans (12 bytes per scan point and level).
+  constexpr int64_t kMaxCellInts = int64_t(1) << 28;  // 1 GiB
+  int begin = 0;
+  while (begin < num_problems) {
+    DeviceSearch search(m, stream);
+    int64_t cell_ints = 0;
+    int end = begin;
+    while (end < num_problems && end - begin < 1024) {
+      int rc = search.AddProblem(sp, ToRigidF(global_node_poses + 7 * end, global_node_poses + 7 * end + 3),
+                                 ToRigidF(global_submap_poses + 7 * end, global_submap_poses + 7 * end + 3), &data[end],
+                                 min_score, 0, 1);
+      if (rc != HG_OK) return rc;
+      const ScanSet& sc = search.scans(end - begin);
+      cell_ints += static_cast<int64_t>(1 + sc.num_low_levels) * sc.S * sc.N * 3;
+      ++end;
+      if (cell_ints >= kMaxCellInts) break;
+    }
+    int rc = search.RunPhaseA(false);
+    if (rc != HG_OK) return rc;
+    std::vector<DeviceSearch::Outcome> outcomes;
+    rc = search.RunPhaseB(0.f, &outcomes);
+    if (rc != HG_OK) return rc;
+    for (int p = begin; p < end; ++p) {
+      if (outcomes[p - begin].needs_host_replay) {
+        rc = HostReplayMatch(m, sp, ToRigidF(global_node_poses + 7 * p, global_node_poses + 7 * p + 3),
+                             ToRigidF(global_submap_poses + 7 * p, global_submap_poses + 7 * p + 3), &data[p], min_score,
+                             0, 1, &results[p]);
+        if (rc != HG_OK) return rc;
+      } else {
+        FillResult(search, p - begin, outcomes[p - begin], &results[p]);
+      }
+    }
+    begin = end;
+  }
+  return HG_OK;
+}
+
+}  // extern "C"
+
+// A sharded MatchFullSubmap between its two phases.
+struct hg_fcsm_search {
+  const hg_fcsm* m = nullptr;
+  SearchParameters sp{0, 0, 0.};
+  Rigid node_pose, submap_pose;
+  const hg_node_data* data = nullptr;
+  float min_score = 0.f;
+  int shard_index = 0, num_shards = 1;
+  std::unique_ptr<DeviceSearch> search;  // null: the host replay does everything in 'finish'
+};
+
+extern "C" {
+
+int hg_fcsm_full_submap_begin(const hg_fcsm* m, const double* global_node_rotation,
+                              const double* global_submap_rotation, const hg_node_data* data, float min_score,
+                              int shard_index, int num_shards, hg_fcsm_search** search_out, float* dive_bound) {
+  HG_REQUIRE(m && global_node_rotation && global_submap_rotation && search_out && dive_bound,
+             "hg_fcsm_full_submap_begin: bad arguments");
+  HG_REQUIRE(num_shards >= 1 && shard_index >= 0 && shard_index < num_shards, "hg_fcsm_full_submap_begin: bad shard");
+  int rc = CheckNodeData(data);
+  if (rc != HG_OK) return rc;
+  *dive_bound = 0.f;
+  std::unique_ptr<hg_fcsm_search> h(new hg_fcsm_search);
+  h->m = m;
+  h->sp = FullSubmapWindow(m, data);
+  const double zero[3] = {0., 0., 0.};
+  h->node_pose = ToRigidF(zero, global_node_rotation);
+  h->submap_pose = ToRigidF(zero, global_submap_rotation);
+  h->data = data;
+  h->min_score = min_score;
+  h->shard_index = shard_index;
+  h->num_shards = num_shards;
+  if (m->options.strict_visit_order == 0 && !ForceHostReplay()) {
+    HG_CUDA(cudaSetDevice(m->device));
+    cudaStream_t stream = ThreadStream();
+    HG_REQUIRE(stream != nullptr, "hg_fcsm: cannot create a stream");
+    h->search.reset(new DeviceSearch(m, stream));
+    rc = h->search->AddProblem(h->sp, h->node_pose, h->submap_pose, data, min_score, shard_index, num_shards);
+    if (rc != HG_OK) return rc;
+    rc = h->search->RunPhaseA(true);
+    if (rc != HG_OK) return rc;
+    std::vector<float> bounds;
+    rc = h->search->ReadBounds(&bounds);
+    if (rc != HG_OK) return rc;
+    *dive_bound = bounds[0];
+  }
+  *search_out = h.release();
+  return HG_OK;
+}
+
+int hg_fcsm_full_submap_finish(hg_fcsm_search* search, float bound, hg_match_result* result) {
+  HG_REQUIRE(search != nullptr && result != nullptr, "hg_fcsm_full_submap_finish: bad arguments");
+  std::unique_ptr<hg_fcsm_search> h(search);
+  if (h->search) {
+    std::vector<DeviceSearch::Outcome> outcomes;
+    const int rc = h->search->RunPhaseB(bound, &outcomes);
+    if (rc != HG_OK) return rc;
+    if (!outcomes[0].needs_host_replay) {
+      FillResult(*h->search, 0, outcomes[0], result);
+      return HG_OK;
+    }
+  }
+  return HostReplayMatch(h->m, h->sp, h->node_pose, h->submap_pose, h->data, h->min_score, h->shard_index,
+                         h->num_shards, result);
+}
+
+void hg_fcsm_search_abandon(hg_fcsm_search* search) { delete search; }
 
 int hg_fcsm_discrete_scans(const hg_fcsm* m, int wxy, int wz, double angular_search_window,
                            const double* global_node_pose, const double* global_submap_pose,

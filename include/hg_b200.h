@@ -400,6 +400,15 @@ typedef struct hg_match_result {
   int32_t num_score_launches;
   int64_t num_lowest_resolution_candidates; /* size of the lowest-resolution lattice (one launch) */
   float lowest_resolution_kernel_ms;        /* its device time, CUDA events on the launching stream */
+  /* What a reduce over shards needs to order equal leaf scores the way the reference's search
+   * visits them (fast_correlative_scan_matcher_3d.cc:384, 437-468: subtrees in descending order of
+   * their lowest-resolution score): score of the winner's lowest-resolution ancestor and that
+   * ancestor's position in the unsharded generation order (:328-361). */
+  float best_ancestor_score;
+  int64_t best_ancestor_index;
+  /* Score of the best valid leaf the greedy dive found (0 = none): a lower bound on the answer
+   * that shards may exchange before the frontier expansion. */
+  float dive_bound;
 } hg_match_result;
 
 /* FastCorrelativeScanMatcher3D(grid, low_resolution_grid, histogram, options)
@@ -424,6 +433,32 @@ int hg_fcsm_match_full_submap(const hg_fcsm* matcher, const double* global_node_
                               const double* global_submap_rotation, const hg_node_data* data,
                               float min_score, int shard_index, int num_shards,
                               hg_match_result* result);
+
+/* FastCorrelativeScanMatcher3D::Match for many nodes against this matcher's submap in one
+ * device-resident search — what ConstraintBuilder3D's thread pool does one task at a time for the
+ * pairs of a submap (constraint_builder_3d.cc:97-106, 213-246). Poses are num_problems x 7
+ * doubles (t3 q4); results[p] is what hg_fcsm_match returns for problem p. */
+int hg_fcsm_match_batch(const hg_fcsm* matcher, int num_problems, const double* global_node_poses,
+                        const double* global_submap_poses, const hg_node_data* data, float min_score,
+                        hg_match_result* results);
+
+/* MatchFullSubmap (:176-200) of one shard in two steps, so that the shards of a multi-GPU search
+ * can exchange one number in between: 'begin' scores the shard's lowest-resolution candidates and
+ * follows the best one of every discrete scan greedily down to a leaf; *dive_bound receives the
+ * score of the best such leaf that passes the low-resolution gate (0 = none) — a lower bound on
+ * the answer of the WHOLE search. 'finish' takes the largest bound any shard found (or 0) and
+ * searches this shard under it; it consumes the handle. Same answer as
+ * hg_fcsm_match_full_submap on every shard; a shard whose scans hold nothing that reaches the
+ * bound reports found == 0. Both calls must come from the same host thread, with no other search
+ * of that thread in between; 'data' must stay valid until 'finish' returns. */
+typedef struct hg_fcsm_search hg_fcsm_search;
+int hg_fcsm_full_submap_begin(const hg_fcsm* matcher, const double* global_node_rotation,
+                              const double* global_submap_rotation, const hg_node_data* data,
+                              float min_score, int shard_index, int num_shards,
+                              hg_fcsm_search** search, float* dive_bound);
+int hg_fcsm_full_submap_finish(hg_fcsm_search* search, float bound, hg_match_result* result);
+/* Drops a search that will not be finished. */
+void hg_fcsm_search_abandon(hg_fcsm_search* search);
 
 /* Stage-level entry points (parity tests and the candidates/s benchmark). */
 

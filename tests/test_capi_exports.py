@@ -61,4 +61,4 @@ def test_no_cpu_fallback(hg):
 def test_structs_match_header_layout(hg):
     assert C.sizeof(hg.capi.FcsmOptions) == 64
     assert C.sizeof(hg.capi.NodeData) == 80
-    assert C.sizeof(hg.capi.MatchResult) == 136
+    assert C.sizeof(hg.capi.MatchResult) == 152
