@@ -167,6 +167,88 @@ int ComputeConstraint(const hg_fcsm* const* matchers, const hg_grid* const* grid
   return HG_OK;
 }
 
+// All the local-window pairs of one submap (a slice of them): ONE device-resident search for the
+// whole group (hg_fcsm_match_batch), then ONE launch that refines every match found
+// (ScanMatchBatchOnDevice, a CTA per pair) — constraint_builder_3d.cc:210-272 for each pair, without
+// a host thread per pair driving its own chain of small launches.
+int ComputeConstraintGroup(const hg_fcsm* const* matchers, const hg_grid* const* grids,
+                           const hg_grid* const* low_resolution_grids, const hg_constraint_job* jobs,
+                           const hg_constraint_options* options, const std::vector<int64_t>& group,
+                           hg_constraint_result* results) {
+  const int n = static_cast<int>(group.size());
+  if (n == 0) return HG_OK;
+  const int submap = jobs[group[0]].submap_index;
+  std::vector<double> node_poses(7 * static_cast<size_t>(n)), submap_poses(7 * static_cast<size_t>(n));
+  std::vector<hg_node_data> data(n);
+  std::vector<hg_match_result> matches(n);
+  for (int k = 0; k < n; ++k) {
+    const hg_constraint_job& job = jobs[group[k]];
+    std::copy(job.global_node_pose, job.global_node_pose + 7, &node_poses[7 * k]);
+    std::copy(job.global_submap_pose, job.global_submap_pose + 7, &submap_poses[7 * k]);
+    data[k] = job.data;
+  }
+  const auto t0 = std::chrono::steady_clock::now();
+  int rc = hg_fcsm_match_batch(matchers[submap], n, node_poses.data(), submap_poses.data(), data.data(),
+                               options->min_score, matches.data());
+  if (rc != HG_OK) return rc;
+  const auto t1 = std::chrono::steady_clock::now();
+  std::vector<hg::ScanMatchBatchItem> items;
+  std::vector<int> item_of;
+  for (int k = 0; k < n; ++k) {
+    hg_constraint_result& out = results[group[k]];
+    out = hg_constraint_result{};
+    out.pose[3] = 1.0;
+    out.num_candidates_scored = matches[k].num_candidates_scored;
+    if (!matches[k].found) continue;
+    out.score = matches[k].score;
+    out.rotational_score = matches[k].rotational_score;
+    out.low_resolution_score = matches[k].low_resolution_score;
+    const hg_constraint_job& job = jobs[group[k]];
+    hg::ScanMatchBatchItem it{};
+    it.num_clouds = job.data.num_low_resolution_points > 0 ? 2 : 1;
+    it.clouds[0] = job.data.high_resolution_point_cloud;
+    it.clouds[1] = job.data.low_resolution_point_cloud;
+    it.sizes[0] = job.data.num_high_resolution_points;
+    it.sizes[1] = job.data.num_low_resolution_points;
+    it.grids[0] = grids[submap];
+    it.grids[1] = low_resolution_grids[submap];
+    for (int c = 0; c < 3; ++c) it.target_translation[c] = it.initial_pose[c] = matches[k].pose_translation[c];
+    for (int c = 0; c < 4; ++c) it.initial_pose[3 + c] = matches[k].pose_rotation[c];
+    items.push_back(it);
+    item_of.push_back(k);
+  }
+  if (items.empty()) return HG_OK;
+  std::vector<double> poses(7 * items.size());
+  rc = hg::ScanMatchBatchOnDevice(static_cast<int>(items.size()), items.data(), options->occupied_space_weights,
+                                  options->translation_weight, options->rotation_weight, options->only_optimize_yaw,
+                                  options->max_num_iterations, options->use_nonmonotonic_steps, poses.data(), nullptr);
+  if (rc == HG_ERR_LIMIT) {  // a cloud too large for the one-CTA solve: pair by pair
+    for (size_t i = 0; i < items.size(); ++i) {
+      const hg::ScanMatchBatchItem& it = items[i];
+      rc = hg_scan_match(it.num_clouds, it.clouds, it.sizes, it.grids, options->occupied_space_weights,
+                         options->translation_weight, options->rotation_weight, options->only_optimize_yaw,
+                         options->max_num_iterations, options->use_nonmonotonic_steps, it.target_translation,
+                         it.initial_pose, &poses[7 * i], nullptr);
+      if (rc != HG_OK) return rc;
+    }
+  } else if (rc != HG_OK) {
+    return rc;
+  }
+  for (size_t i = 0; i < items.size(); ++i) {
+    hg_constraint_result& out = results[group[item_of[i]]];
+    std::copy(&poses[7 * i], &poses[7 * i] + 7, out.pose);
+    out.found = 1;
+  }
+  static const bool trace = std::getenv("HG_TRACE") != nullptr;
+  if (trace) {
+    const auto t2 = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[hg trace] constraint group of %d pairs (submap %d): match %.2f ms, refine of %zu %.2f ms\n", n,
+                 submap, std::chrono::duration<double, std::milli>(t1 - t0).count(), items.size(),
+                 std::chrono::duration<double, std::milli>(t2 - t1).count());
+  }
+  return HG_OK;
+}
+
 }  // namespace
 
 extern "C" int hg_constraints_run_batch(const hg_fcsm* const* matchers, const hg_grid* const* grids,
@@ -182,17 +264,46 @@ extern "C" int hg_constraints_run_batch(const hg_fcsm* const* matchers, const hg
     HG_REQUIRE(jobs[j].submap_index >= 0 && jobs[j].submap_index < num_submaps,
                "hg_constraints_run_batch: submap index out of range");
   }
-  const auto one = [&](const int64_t j) {
-    return ComputeConstraint(matchers, grids, low_resolution_grids, jobs[j], options, j, &results[j]);
+  // Local-window pairs are grouped by submap and searched / refined a group at a time; a
+  // full-submap pair is a search of its own. HG_CONSTRAINT_GROUP bounds the group size (1 = the
+  // pair-at-a-time path of round 1).
+  static const int group_limit = [] {
+    const char* env = std::getenv("HG_CONSTRAINT_GROUP");
+    return env != nullptr ? std::max(1, std::atoi(env)) : 128;
+  }();
+  std::vector<std::vector<int64_t>> units;
+  {
+    std::vector<std::vector<int64_t>> open(num_submaps);
+    for (int64_t j = shard_index; j < num_jobs; j += num_shards) {
+      if (jobs[j].match_full_submap || group_limit == 1) {
+        units.push_back({j});
+        continue;
+      }
+      std::vector<int64_t>& g = open[jobs[j].submap_index];
+      g.push_back(j);
+      if (static_cast<int>(g.size()) >= group_limit) {
+        units.push_back(std::move(g));
+        g.clear();
+      }
+    }
+    for (std::vector<int64_t>& g : open)
+      if (!g.empty()) units.push_back(std::move(g));
+  }
+  const auto one = [&](const int64_t u) {
+    const std::vector<int64_t>& unit = units[u];
+    if (unit.size() == 1 && (jobs[unit[0]].match_full_submap || group_limit == 1)) {
+      return ComputeConstraint(matchers, grids, low_resolution_grids, jobs[unit[0]], options, unit[0], &results[unit[0]]);
+    }
+    return ComputeConstraintGroup(matchers, grids, low_resolution_grids, jobs, options, unit, results);
   };
-  const int64_t mine = (num_jobs - shard_index + num_shards - 1) / num_shards;
+  const int64_t num_units = static_cast<int64_t>(units.size());
   static const bool serial = [] {
     const char* env = std::getenv("HG_CONSTRAINT_THREADS");
     return env != nullptr && std::atoi(env) <= 1;
   }();
-  if (serial || mine <= 1) {
-    for (int64_t j = shard_index; j < num_jobs; j += num_shards) {
-      const int rc = one(j);
+  if (serial || num_units <= 1) {
+    for (int64_t u = 0; u < num_units; ++u) {
+      const int rc = one(u);
       if (rc != HG_OK) return rc;
     }
     return HG_OK;
@@ -201,5 +312,5 @@ extern "C" int hg_constraints_run_batch(const hg_fcsm* const* matchers, const hg
   HG_CUDA(cudaGetDevice(&device));
   // Everything the calling thread has queued (grid uploads, pyramids) must be visible to the workers.
   HG_CUDA(cudaDeviceSynchronize());
-  return WorkerPool::Get().Run(shard_index, num_jobs, num_shards, device, one);
+  return WorkerPool::Get().Run(0, num_units, 1, device, one);
 }

@@ -1782,6 +1782,7 @@ struct ProblemDev {
   int low_offset;          // points into the batch's low-resolution cloud array
   int wxy, wz;
   float min_score;
+  long long point_offset;  // points into the batch's high-resolution cloud array
 };
 
 // One discrete scan: owning problem and the pieces of GetPoseFromCandidate (:400-406) that do not
@@ -1831,25 +1832,108 @@ __device__ __forceinline__ const int* CellsOf(const SearchDev& s, const ProblemD
   return s.cells + P.cells_offset + level * P.level_stride + static_cast<long long>(local_scan) * P.N * 3;
 }
 
-// Sum of one candidate at one depth, computed by a whole warp (every lane returns the total).
-__device__ __forceinline__ int WarpCandidateSum(const BrickTable& level, const DenseLevel& dense, const int* base,
-                                                const int N, const int ox, const int oy, const int oz,
-                                                const int lane) {
-  int sum = 0;
-  if (dense.data != nullptr) {
-    for (int i = lane; i < N; i += 32) {
-      const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
-      sum += LoadDenseU8(dense, x + ox, y + oy, z + oz);
-    }
-  } else {
-    for (int i = lane; i < N; i += 32) {
-      const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
-      sum += LoadU8(level, x + ox, y + oy, z + oz);
+// DiscretizeKernel for every (scan, point) of a batch in one launch: blockIdx.y = scan of the
+// batch-wide list, blockIdx.x = chunk of 256 points.
+__global__ void __launch_bounds__(256) DiscretizeBatchKernel(const ProblemDev* __restrict__ problems,
+                                                             const ScanDev* __restrict__ scans,
+                                                             const float* __restrict__ points,
+                                                             const float* __restrict__ poses, const float resolution,
+                                                             const float inv_resolution, const int num_low_levels,
+                                                             int* __restrict__ cells) {
+  const int sg = blockIdx.y;
+  const ProblemDev& P = problems[scans[sg].problem];
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= P.N) return;
+  const float* pt = points + 3 * (P.point_offset + i);
+  const float* Q = poses + 7 * static_cast<long long>(sg);
+  float wx, wy, wz;
+  RotateF(Q[3], Q[4], Q[5], Q[6], pt[0], pt[1], pt[2], &wx, &wy, &wz);
+  wx = __fadd_rn(wx, Q[0]);
+  wy = __fadd_rn(wy, Q[1]);
+  wz = __fadd_rn(wz, Q[2]);
+  const int cx = CellIndexFast(wx, resolution, inv_resolution), cy = CellIndexFast(wy, resolution, inv_resolution),
+            cz = CellIndexFast(wz, resolution, inv_resolution);
+  int* o = cells + P.cells_offset + (static_cast<long long>(sg - P.scan_begin) * P.N + i) * 3;
+  o[0] = cx; o[1] = cy; o[2] = cz;
+  const int start_xy = -P.wxy, start_z = -P.wz;
+  for (int l = 1; l <= num_low_levels; ++l) {
+    o += P.level_stride;
+    o[0] = ((cx + start_xy) >> l) - (start_xy >> l);
+    o[1] = ((cy + start_xy) >> l) - (start_xy >> l);
+    o[2] = ((cz + start_z) >> l) - (start_z >> l);
+  }
+}
+
+// Lowest-resolution lattice of a batch of small searches (a local window has a handful of
+// lattice candidates per scan): a CTA per (scan, eight candidates) loads every point's cell once
+// for the eight gathers. Same sums as ScoreLatticeKernel, generation order.
+__global__ void __launch_bounds__(256) LatticeBatchKernel(const SearchDev s, const BrickTable level,
+                                                          const DenseLevel dense, int* __restrict__ lattice) {
+  __shared__ int warp_sums[8][8];
+  const int sg = blockIdx.y;
+  const int first = blockIdx.x * 8;
+  const ProblemDev& P = s.problems[s.scans[sg].problem];
+  const int e = max(0, s.max_depth - s.frd + 1);
+  const int* base = CellsOf(s, P, sg - P.scan_begin, s.max_depth);
+  int ox[8], oy[8], oz[8];
+  unsigned valid = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int at = first + k;
+    ox[k] = oy[k] = oz[k] = 0;
+    if (at < s.per_scan) {
+      const int iz = at / (s.nxy * s.nxy), rem = at - iz * s.nxy * s.nxy, iy = rem / s.nxy, ix = rem - iy * s.nxy;
+      ox[k] = (-P.wxy + ix * s.step) >> e;
+      oy[k] = (-P.wxy + iy * s.step) >> e;
+      oz[k] = (-P.wz + iz * s.step) >> e;
+      valid |= 1u << k;
     }
   }
+  int sums[8];
 #pragma unroll
-  for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
-  return sum;
+  for (int k = 0; k < 8; ++k) sums[k] = 0;
+#pragma unroll 2
+  for (int i = threadIdx.x; i < P.N; i += 256) {
+    const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if ((valid >> k) & 1u) {
+        sums[k] += dense.data != nullptr ? LoadDenseU8(dense, x + ox[k], y + oy[k], z + oz[k])
+                                         : LoadU8(level, x + ox[k], y + oy[k], z + oz[k]);
+      }
+    }
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) sums[k] += __shfl_xor_sync(0xffffffffu, sums[k], d);
+    if (lane == 0) warp_sums[warp][k] = sums[k];
+  }
+  __syncthreads();
+  if (threadIdx.x < 8 && first + threadIdx.x < s.per_scan) {
+    int t = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += warp_sums[w][threadIdx.x];
+    lattice[static_cast<long long>(sg) * s.per_scan + first + threadIdx.x] = t;
+  }
+}
+
+// Keeps the dive starts of the 'keep' best-scoring scans of every problem (a CTA per problem,
+// rank by counting); the others are marked dead. The dive only has to produce a good bound.
+__global__ void __launch_bounds__(256) SelectStartsKernel(const SearchDev s, const int keep) {
+  const ProblemDev& P = s.problems[blockIdx.x];
+  if (P.S <= keep || P.S > 2048) return;
+  int* sums = s.start_sums + P.scan_begin;
+  __shared__ int snapshot[2048];
+  for (int t = threadIdx.x; t < P.S; t += 256) snapshot[t] = sums[t];
+  __syncthreads();
+  for (int t = threadIdx.x; t < P.S; t += 256) {
+    const int mine = snapshot[t];
+    int rank = 0;
+    for (int j = 0; j < P.S; ++j) rank += (snapshot[j] > mine || (snapshot[j] == mine && j < t)) ? 1 : 0;
+    if (rank >= keep) sums[t] = -1;
+  }
 }
 
 // Dive start of every discrete scan: its best lattice candidate (first one on equal sums).
@@ -1881,37 +1965,114 @@ __global__ void __launch_bounds__(256) ArgmaxPerScanKernel(const SearchDev s) {
   s.start_sums[sg] = DeviceScore(best, P.N) > P.min_score ? best : -1;
 }
 
-// One level of the dive: a CTA per start, a warp per child slot (z, y, x in {0, half}^3, the loop
-// nest at :441-461), the best child replaces the start.
+// Sums of the eight children of one parent (slot = 4 z + 2 y + x, offsets {0, half}^3, the loop
+// nest at :441-461), computed by a whole CTA of 256 threads: every point's cell is loaded once and
+// feeds eight independent gathers. 'valid' masks the children beyond the search window (the
+// reference's 'break'); their sums stay 0. The totals land in totals[0..7] (shared memory); the
+// function ends with a __syncthreads().
+__device__ __forceinline__ void BlockChildrenSums(const BrickTable& level, const DenseLevel& dense, const int* base,
+                                                  const int N, const int px, const int py, const int pz,
+                                                  const int half, const int e, const unsigned valid,
+                                                  int (*warp_sums)[8], int* totals) {
+  int sums[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int ox[2] = {px >> e, (px + half) >> e}, oy[2] = {py >> e, (py + half) >> e},
+            oz[2] = {pz >> e, (pz + half) >> e};
+#pragma unroll
+  for (int k = 0; k < 8; ++k) sums[k] = 0;
+  if (dense.data != nullptr) {
+    const int dx = dense.dim[0], dy = dense.dim[1], dz = dense.dim[2];
+#pragma unroll 2
+    for (int i = threadIdx.x; i < N; i += 256) {
+      const int x = __ldg(base + 3 * i) - dense.min[0], y = __ldg(base + 3 * i + 1) - dense.min[1],
+                z = __ldg(base + 3 * i + 2) - dense.min[2];
+      int xs[2], rows[4];
+      bool xin[2], rin[4];
+#pragma unroll
+      for (int a = 0; a < 2; ++a) {
+        xs[a] = x + ox[a];
+        xin[a] = static_cast<unsigned>(xs[a]) < static_cast<unsigned>(dx);
+      }
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          const int yy = y + oy[b], zz = z + oz[c];
+          rin[2 * c + b] = static_cast<unsigned>(yy) < static_cast<unsigned>(dy) &&
+                           static_cast<unsigned>(zz) < static_cast<unsigned>(dz);
+          rows[2 * c + b] = (zz * dy + yy) * dx;
+        }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (((valid >> k) & 1u) && rin[k >> 1] && xin[k & 1]) sums[k] += __ldg(dense.data + rows[k >> 1] + xs[k & 1]);
+      }
+    }
+  } else {
+#pragma unroll 2
+    for (int i = threadIdx.x; i < N; i += 256) {
+      const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if ((valid >> k) & 1u) sums[k] += LoadU8(level, x + ox[k & 1], y + oy[(k >> 1) & 1], z + oz[k >> 2]);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) sums[k] += __shfl_xor_sync(0xffffffffu, sums[k], d);
+    if (lane == 0) warp_sums[warp][k] = sums[k];
+  }
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    int t = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += warp_sums[w][threadIdx.x];
+    totals[threadIdx.x] = t;
+  }
+  __syncthreads();
+}
+
+// Children of (px, py, pz) that lie inside the window, as a bit mask over the slots.
+__device__ __forceinline__ unsigned ValidChildren(const int px, const int py, const int pz, const int half,
+                                                  const int wxy, const int wz) {
+  unsigned valid = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int cx = px + ((k & 1) ? half : 0), cy = py + ((k & 2) ? half : 0), cz = pz + ((k & 4) ? half : 0);
+    if (cx <= wxy && cy <= wxy && cz <= wz) valid |= 1u << k;
+  }
+  return valid;
+}
+
+// One level of the dive: a CTA per start scores its eight children and the best one (the first
+// on equal sums) replaces the start.
 __global__ void __launch_bounds__(256) DiveLevelKernel(const SearchDev s, const BrickTable level,
                                                        const DenseLevel dense, const int child_depth) {
-  __shared__ int slot_sum[8];
+  __shared__ int warp_sums[8][8];
+  __shared__ int totals[8];
   const int sg = blockIdx.x;
   if (s.start_sums[sg] < 0) return;  // CTA-uniform
-  const int slot = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int4 p = s.starts[sg];
   const ProblemDev& P = s.problems[s.scans[sg].problem];
   const int half = 1 << child_depth;
-  const int cx = p.y + ((slot & 1) ? half : 0), cy = p.z + ((slot & 2) ? half : 0), cz = p.w + ((slot & 4) ? half : 0);
-  int sum = -1;
-  if (cx <= P.wxy && cy <= P.wxy && cz <= P.wz) {
-    const int e = max(0, child_depth - s.frd + 1);
-    sum = WarpCandidateSum(level, dense, CellsOf(s, P, sg - P.scan_begin, child_depth), P.N, cx >> e, cy >> e,
-                           cz >> e, lane);
-  }
-  if (lane == 0) slot_sum[slot] = sum;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int best = 0, valid = 0;
-    for (int k = 0; k < 8; ++k) {
-      valid += slot_sum[k] >= 0 ? 1 : 0;
-      if (slot_sum[k] > slot_sum[best]) best = k;
+  const int e = max(0, child_depth - s.frd + 1);
+  const unsigned valid = ValidChildren(p.y, p.z, p.w, half, P.wxy, P.wz);
+  BlockChildrenSums(level, dense, CellsOf(s, P, sg - P.scan_begin, child_depth), P.N, p.y, p.z, p.w, half, e, valid,
+                    warp_sums, totals);
+  if (threadIdx.x != 0) return;
+  int best = 0, best_sum = -1;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    if (((valid >> k) & 1u) && totals[k] > best_sum) {
+      best_sum = totals[k];
+      best = k;
     }
-    s.starts[sg] = make_int4(sg, p.y + ((best & 1) ? half : 0), p.z + ((best & 2) ? half : 0),
-                             p.w + ((best & 4) ? half : 0));
-    s.start_sums[sg] = slot_sum[best];
-    atomicAdd(&s.scored[s.scans[sg].problem], static_cast<unsigned long long>(valid));
   }
+  s.starts[sg] = make_int4(sg, p.y + ((best & 1) ? half : 0), p.z + ((best & 2) ? half : 0),
+                           p.w + ((best & 4) ? half : 0));
+  s.start_sums[sg] = best_sum;
+  atomicAdd(&s.scored[s.scans[sg].problem], static_cast<unsigned long long>(__popc(valid)));
 }
 
 // LowResolutionMatcher closure (low_resolution_matcher.cc:24-69) for candidates: a warp per
@@ -2041,33 +2202,36 @@ __global__ void __launch_bounds__(256) SeedKernel(const SearchDev s) {
 }
 
 // Children of the frontier of 'child_depth + 1' that reach the threshold -> frontier of
-// child_depth. A warp per (parent, slot); persistent grid, the parent count is read from the device.
+// child_depth. A CTA per parent; persistent grid, the parent count is read from the device.
 __global__ void __launch_bounds__(256) ExpandKernel(const SearchDev s, const BrickTable level, const DenseLevel dense,
                                                     const int child_depth) {
+  __shared__ int warp_sums[8][8];
+  __shared__ int totals[8];
   const int d = child_depth + 1;
   const int parents = min(s.counts[d], s.list_cap);
-  const int lane = threadIdx.x & 31;
-  const long long warps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
   const int half = 1 << child_depth;
   const int e = max(0, child_depth - s.frd + 1);
-  for (long long w = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
-       w < static_cast<long long>(parents) * 8; w += warps) {
-    const int4 p = s.list[d & 1][w >> 3];
-    const int slot = static_cast<int>(w & 7);
+  for (int w = blockIdx.x; w < parents; w += gridDim.x) {
+    const int4 p = s.list[d & 1][w];
     const int problem = s.scans[p.x].problem;
     const ProblemDev& P = s.problems[problem];
-    const int cx = p.y + ((slot & 1) ? half : 0), cy = p.z + ((slot & 2) ? half : 0), cz = p.w + ((slot & 4) ? half : 0);
-    if (cx > P.wxy || cy > P.wxy || cz > P.wz) continue;  // the reference's 'break'
-    const int sum = WarpCandidateSum(level, dense, CellsOf(s, P, p.x - P.scan_begin, child_depth), P.N, cx >> e,
-                                     cy >> e, cz >> e, lane);
-    if (lane == 0) atomicAdd(&s.scored[problem], 1ull);
-    if (lane == 0 && __float_as_int(DeviceScore(sum, P.N)) >= s.thresh_bits[problem]) {
-      const int pos = atomicAdd(&s.counts[child_depth], 1);
-      if (pos < s.list_cap) {
-        s.list[child_depth & 1][pos] = make_int4(p.x, cx, cy, cz);
-        s.list_sum[child_depth & 1][pos] = sum;
+    const unsigned valid = ValidChildren(p.y, p.z, p.w, half, P.wxy, P.wz);
+    BlockChildrenSums(level, dense, CellsOf(s, P, p.x - P.scan_begin, child_depth), P.N, p.y, p.z, p.w, half, e, valid,
+                      warp_sums, totals);
+    if (threadIdx.x < 32) {  // lanes 0..7 of the first warp each decide one child
+      const int lane = threadIdx.x;
+      const int mine = lane < 8 ? totals[lane] : 0;
+      const bool keep = lane < 8 && ((valid >> lane) & 1u) &&
+                        __float_as_int(DeviceScore(mine, P.N)) >= s.thresh_bits[problem];
+      const int pos = WarpAppend(&s.counts[child_depth], keep);
+      if (keep && pos < s.list_cap) {
+        s.list[child_depth & 1][pos] = make_int4(p.x, p.y + ((lane & 1) ? half : 0), p.z + ((lane & 2) ? half : 0),
+                                                 p.w + ((lane & 4) ? half : 0));
+        s.list_sum[child_depth & 1][pos] = mine;
       }
+      if (lane == 0) atomicAdd(&s.scored[problem], static_cast<unsigned long long>(__popc(valid)));
     }
+    __syncthreads();  // 'totals' is rewritten by the next parent
   }
 }
 
@@ -2175,6 +2339,7 @@ class DeviceSearch {
       d.wxy = sp.wxy;
       d.wz = sp.wz;
       d.min_score = problems_[p].min_score;
+      d.point_offset = static_cast<long long>(n_points);
       problems_[p].point_offset = n_points;
       n_points += static_cast<size_t>(sc.N);
       n_low += static_cast<size_t>(d.NL);
@@ -2272,19 +2437,29 @@ class DeviceSearch {
     s.max_depth = max_depth_;
     s.frd = problems_[0].scans.frd;
     s.min_low_resolution_score = m_->options.min_low_resolution_score;
-    // ---- discretise and score the lattice, problem by problem
+    // ---- discretise: one launch for the batch (per problem when the grid would not fit)
     const float* d_points = reinterpret_cast<const float*>(d);
     const float* d_poses = reinterpret_cast<const float*>(d + off_poses);
     const float resolution = m_->resolution;
-    for (int p = 0; p < P; ++p) {
-      const ScanSet& sc = problems_[p].scans;
-      if (sc.S == 0) continue;
-      const int64_t total = static_cast<int64_t>(sc.S) * sc.N;
-      DiscretizeKernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream_>>>(
-          d_points + 3 * problems_[p].point_offset, sc.N, d_poses + 7 * static_cast<size_t>(pd[p].scan_begin), sc.S,
-          resolution, 1.f / resolution, sc.num_low_levels, -sp.wxy, -sp.wz, ws_->d_cells.as<int>() + pd[p].cells_offset);
+    int max_n = 0;
+    for (int p = 0; p < P; ++p) max_n = std::max(max_n, problems_[p].scans.N);
+    if (total_scans_ <= 65535) {
+      DiscretizeBatchKernel<<<dim3((max_n + 255) / 256, total_scans_), 256, 0, stream_>>>(
+          s.problems, s.scans, d_points, d_poses, resolution, 1.f / resolution, problems_[0].scans.num_low_levels,
+          ws_->d_cells.as<int>());
       CountLaunch();
       ++launches_;
+    } else {
+      for (int p = 0; p < P; ++p) {
+        const ScanSet& sc = problems_[p].scans;
+        if (sc.S == 0) continue;
+        const int64_t total = static_cast<int64_t>(sc.S) * sc.N;
+        DiscretizeKernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream_>>>(
+            d_points + 3 * problems_[p].point_offset, sc.N, d_poses + 7 * static_cast<size_t>(pd[p].scan_begin), sc.S,
+            resolution, 1.f / resolution, sc.num_low_levels, -sp.wxy, -sp.wz, ws_->d_cells.as<int>() + pd[p].cells_offset);
+        CountLaunch();
+        ++launches_;
+      }
     }
     HG_CUDA(cudaGetLastError());
     if (time_lattice) {
@@ -2292,21 +2467,36 @@ class DeviceSearch {
       HG_CUDA(cudaEventCreate(&e1_));
       HG_CUDA(cudaEventRecord(e0_, stream_));
     }
+    // ---- lattice: small lattices (local windows) in one launch for the batch; a large one
+    // (full submap) per problem through the residue-row kernel
     const int lattice_level = std::max(0, max_depth_ - s.frd + 1);
-    for (int p = 0; p < P; ++p) {
-      const ScanSet& sc = problems_[p].scans;
-      if (sc.S == 0) continue;
-      const int* cells = ws_->d_cells.as<int>() + pd[p].cells_offset + lattice_level * pd[p].level_stride;
-      rc = LaunchLattice(m_, cells, sc.S, sc.N, max_depth_, nxy_, nz_, sp.wxy, sp.wz,
-                         ws_->d_lattice.as<int>() + static_cast<size_t>(pd[p].scan_begin) * per_scan_, stream_, nullptr);
-      if (rc != HG_OK) return rc;
+    if (nxy_ < 5 && total_scans_ <= 65535) {
+      const hg_stack_level& L = m_->stack->levels[max_depth_];
+      LatticeBatchKernel<<<dim3((per_scan_ + 7) / 8, total_scans_), 256, 0, stream_>>>(s, L.table, L.dense,
+                                                                                      ws_->d_lattice.as<int>());
+      CountLaunch();
       ++launches_;
+    } else {
+      for (int p = 0; p < P; ++p) {
+        const ScanSet& sc = problems_[p].scans;
+        if (sc.S == 0) continue;
+        const int* cells = ws_->d_cells.as<int>() + pd[p].cells_offset + lattice_level * pd[p].level_stride;
+        rc = LaunchLattice(m_, cells, sc.S, sc.N, max_depth_, nxy_, nz_, sp.wxy, sp.wz,
+                           ws_->d_lattice.as<int>() + static_cast<size_t>(pd[p].scan_begin) * per_scan_, stream_, nullptr);
+        if (rc != HG_OK) return rc;
+        ++launches_;
+      }
     }
     if (time_lattice) HG_CUDA(cudaEventRecord(e1_, stream_));
     // ---- dive
     ArgmaxPerScanKernel<<<(total_scans_ * 32 + 255) / 256, 256, 0, stream_>>>(s);
     CountLaunch();
     ++launches_;
+    if (P > 1) {  // a batch of local searches: a few dozen starts per problem give the bound
+      SelectStartsKernel<<<P, 256, 0, stream_>>>(s, kDiveStartsPerProblem);
+      CountLaunch();
+      ++launches_;
+    }
     for (int depth = max_depth_; depth >= 1; --depth) {
       const hg_stack_level& L = m_->stack->levels[depth - 1];
       DiveLevelKernel<<<total_scans_, 256, 0, stream_>>>(s, L.table, L.dense, depth - 1);
@@ -2420,6 +2610,7 @@ class DeviceSearch {
 
  private:
   static constexpr int kListCapacity = 1 << 20;
+  static constexpr int kDiveStartsPerProblem = 32;
   struct Problem {
     SearchParameters sp;
     const hg_node_data* data = nullptr;
@@ -2666,6 +2857,7 @@ int hg_fcsm_match_batch(const hg_fcsm* m, int num_problems, const double* global
   constexpr int64_t kMaxCellInts = int64_t(1) << 28;  // 1 GiB
   int begin = 0;
   while (begin < num_problems) {
+    PhaseTimer pt;
     DeviceSearch search(m, stream);
     int64_t cell_ints = 0;
     int end = begin;
@@ -2679,11 +2871,16 @@ int hg_fcsm_match_batch(const hg_fcsm* m, int num_problems, const double* global
       ++end;
       if (cell_ints >= kMaxCellInts) break;
     }
+    const double t_add = pt.Lap();
     int rc = search.RunPhaseA(false);
     if (rc != HG_OK) return rc;
+    const double t_a = pt.Lap();
     std::vector<DeviceSearch::Outcome> outcomes;
     rc = search.RunPhaseB(0.f, &outcomes);
     if (rc != HG_OK) return rc;
+    if (TraceEnabled())
+      std::fprintf(stderr, "[hg trace] batch of %d: scan poses %.2f ms, phase A queued in %.2f ms, phase B + wait %.2f ms\n",
+                   end - begin, t_add, t_a, pt.Lap());
     for (int p = begin; p < end; ++p) {
       if (outcomes[p - begin].needs_host_replay) {
         rc = HostReplayMatch(m, sp, ToRigidF(global_node_poses + 7 * p, global_node_poses + 7 * p + 3),

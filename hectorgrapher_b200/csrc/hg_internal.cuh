@@ -153,6 +153,21 @@ int ScanMatchOnDevice(int num_clouds, const float* const* clouds, const int32_t*
                       int max_num_iterations, int use_nonmonotonic_steps, const double* target_translation,
                       const double* initial_pose, double* pose_out, double* summary_out);
 
+// scan_match.cu: the same for a batch of problems in one launch (one CTA each; every problem at most
+// 4 clouds and 4096 points in total, HG_ERR_LIMIT otherwise). poses_out: n x 7, summaries_out: n x 6 or null.
+struct ScanMatchBatchItem {
+  int num_clouds;
+  const float* clouds[4];
+  int32_t sizes[4];
+  const hg_grid* grids[4];
+  double target_translation[3];
+  double initial_pose[7];
+};
+int ScanMatchBatchOnDevice(int num_problems, const ScanMatchBatchItem* items, const double* occupied_space_weights,
+                           double translation_weight, double rotation_weight, int only_optimize_yaw,
+                           int max_num_iterations, int use_nonmonotonic_steps, double* poses_out,
+                           double* summaries_out);
+
 // Optional dense copy of a (small) precomputation level: a plain uint8 3-D array
 // over the bounding box of its bricks, x fastest. Coarse levels of the pyramid
 // are a few hundred KB; reading them densely saves the brick-index load.

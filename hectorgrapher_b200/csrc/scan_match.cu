@@ -251,8 +251,7 @@ __device__ void Advance(LmState* s, const ScanMatchArgs& a, const EvalShared* ev
 // order through distributed shared memory and runs the solver, the others read the next pose (and
 // the stop flag) from CTA 0's shared memory. Two cluster barriers per evaluation.
 template <int CLUSTER>
-__global__ void __cluster_dims__(CLUSTER, 1, 1) __launch_bounds__(kLmThreads, 1)
-    ScanMatchKernel(const ScanMatchArgs a) {
+__device__ __forceinline__ void ScanMatchBody(const ScanMatchArgs& a) {
   __shared__ LmState st;
   __shared__ double warp_sums[kLmWarps][kTerms];
   __shared__ double totals[kTerms];
@@ -361,6 +360,26 @@ __global__ void __cluster_dims__(CLUSTER, 1, 1) __launch_bounds__(kLmThreads, 1)
   }
 }
 
+template <int CLUSTER>
+__global__ void __cluster_dims__(CLUSTER, 1, 1) __launch_bounds__(kLmThreads, 1)
+    ScanMatchKernel(const ScanMatchArgs a) {
+  ScanMatchBody<CLUSTER>(a);
+}
+
+// One CTA per problem of a batch (the refines of all the constraints found for a submap): the
+// arguments come from device memory.
+__global__ void __launch_bounds__(kLmThreads, 1) ScanMatchBatchKernel(const ScanMatchArgs* __restrict__ args) {
+  __shared__ ScanMatchArgs a;
+  {
+    const int words = sizeof(ScanMatchArgs) / 4;
+    const int* src = reinterpret_cast<const int*>(args + blockIdx.x);
+    int* dst = reinterpret_cast<int*>(&a);
+    for (int k = threadIdx.x; k < words; k += kLmThreads) dst[k] = src[k];
+  }
+  __syncthreads();
+  ScanMatchBody<1>(a);
+}
+
 }  // namespace
 
 // Device-side CeresScanMatcher3D::Match. Returns HG_ERR_LIMIT when the problem does not fit the
@@ -423,6 +442,78 @@ int ScanMatchOnDevice(int num_clouds, const float* const* clouds, const int32_t*
   for (int k = 0; k < 7; ++k) pose_out[k] = h_out[k];
   if (summary_out) {
     for (int k = 0; k < 6; ++k) summary_out[k] = h_out[7 + k];
+  }
+  return HG_OK;
+}
+
+// CeresScanMatcher3D::Match for a batch of problems in ONE launch (a CTA each). Every problem has
+// at most kMaxClouds clouds and at most 4096 points in total; HG_ERR_LIMIT otherwise (the caller
+// then solves that batch problem by problem).
+int ScanMatchBatchOnDevice(int num_problems, const ScanMatchBatchItem* items, const double* occupied_space_weights,
+                           double translation_weight, double rotation_weight, int only_optimize_yaw,
+                           int max_num_iterations, int use_nonmonotonic_steps, double* poses_out,
+                           double* summaries_out) {
+  if (num_problems == 0) return HG_OK;
+  static_assert(sizeof(ScanMatchArgs) % 4 == 0, "ScanMatchArgs is copied word by word");
+  size_t total_floats = 0;
+  for (int p = 0; p < num_problems; ++p) {
+    if (items[p].num_clouds > kMaxClouds || items[p].num_clouds < 1) return HG_ERR_LIMIT;
+    size_t floats = 0;
+    for (int i = 0; i < items[p].num_clouds; ++i) floats += static_cast<size_t>(items[p].sizes[i]) * 3;
+    if (floats / 3 > 4096) return HG_ERR_LIMIT;
+    total_floats += floats;
+  }
+  cudaStream_t stream = ThreadStream();
+  HG_REQUIRE(stream != nullptr, "hg_scan_match: cannot create a stream");
+  const size_t off_args = (total_floats * sizeof(float) + 15) & ~size_t(15);
+  const size_t upload_bytes = off_args + num_problems * sizeof(ScanMatchArgs);
+  char* h_up = static_cast<char*>(CachedPinnedAlloc(upload_bytes));
+  char* d_up = static_cast<char*>(CachedDeviceAlloc(upload_bytes));
+  double* d_out = static_cast<double*>(CachedDeviceAlloc(num_problems * 14 * sizeof(double)));
+  double* h_out = static_cast<double*>(CachedPinnedAlloc(num_problems * 14 * sizeof(double)));
+  struct Release {
+    void* p[4];
+    ~Release() {
+      for (void* q : p) CachedFree(q);
+    }
+  } release{{h_up, d_up, d_out, h_out}};
+  if (h_up == nullptr || d_up == nullptr || d_out == nullptr || h_out == nullptr) return HG_ERR_CUDA;
+  ScanMatchArgs* h_args = reinterpret_cast<ScanMatchArgs*>(h_up + off_args);
+  size_t offset = 0;
+  for (int p = 0; p < num_problems; ++p) {
+    const ScanMatchBatchItem& it = items[p];
+    ScanMatchArgs& a = h_args[p];
+    std::memset(&a, 0, sizeof(a));
+    for (int i = 0; i < it.num_clouds; ++i) {
+      a.grids[i] = it.grids[i]->dev;
+      a.points[i] = reinterpret_cast<const float*>(d_up) + offset;
+      a.n[i] = it.sizes[i];
+      a.scale[i] = occupied_space_weights[i] / std::sqrt(static_cast<double>(it.sizes[i]));  // :138-139 / :149-150
+      std::memcpy(reinterpret_cast<float*>(h_up) + offset, it.clouds[i], static_cast<size_t>(it.sizes[i]) * 3 * sizeof(float));
+      offset += static_cast<size_t>(it.sizes[i]) * 3;
+    }
+    a.num_clouds = it.num_clouds;
+    a.only_optimize_yaw = only_optimize_yaw;
+    a.max_num_iterations = max_num_iterations;
+    a.use_nonmonotonic_steps = use_nonmonotonic_steps;
+    a.translation_weight = translation_weight;
+    a.rotation_weight = rotation_weight;
+    for (int k = 0; k < 3; ++k) a.target_t[k] = it.target_translation[k];
+    for (int k = 0; k < 4; ++k) a.target_q[k] = it.initial_pose[3 + k];
+    for (int k = 0; k < 7; ++k) a.pose[k] = it.initial_pose[k];
+    a.out = d_out + 14 * static_cast<size_t>(p);
+  }
+  HG_CUDA(cudaMemcpyAsync(d_up, h_up, upload_bytes, cudaMemcpyHostToDevice, stream));
+  ScanMatchBatchKernel<<<num_problems, kLmThreads, 0, stream>>>(reinterpret_cast<const ScanMatchArgs*>(d_up + off_args));
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  HG_CUDA(cudaMemcpyAsync(h_out, d_out, num_problems * 14 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  HG_CUDA(cudaStreamSynchronize(stream));
+  for (int p = 0; p < num_problems; ++p) {
+    for (int k = 0; k < 7; ++k) poses_out[7 * p + k] = h_out[14 * p + k];
+    if (summaries_out) {
+      for (int k = 0; k < 6; ++k) summaries_out[6 * p + k] = h_out[14 * p + 7 + k];
+    }
   }
   return HG_OK;
 }
