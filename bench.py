@@ -199,35 +199,73 @@ def run_reference(args, rank, world):
     emit(line)
 
 
-def correlative_inputs(w):
+# pose_graph.lua:20, 44-45 (constraint_builder min_score, fast_correlative_scan_matcher_3d thresholds)
+POSE_GRAPH_MIN_SCORE = 0.55
+POSE_GRAPH_MIN_ROTATIONAL_SCORE = 0.77
+POSE_GRAPH_MIN_LOW_RESOLUTION_SCORE = 0.55
+HISTOGRAM_SIZE = 120  # pose_graph.lua: rotational_histogram_size
+
+
+def submap_histogram(w):
+    """The submap's rotational histogram the way the reference accumulates it (mapping/3d/submap_3d.cc:
+    every inserted scan's histogram rotated into the submap frame and added): one coarse scan per map pose."""
+    synth = w["synth"]
+    total = np.zeros(HISTOGRAM_SIZE, np.float32)
+    for k, (origin, yaw) in enumerate(w["map_poses"]):
+        cloud = synth.scan(origin, yaw, 32, 256, w["sph"], np.random.RandomState(700 + k))
+        pts = synth.voxel_downsample(cloud, 0.2, 2048, seed=8)
+        total += synth.rotate_histogram(synth.rotational_histogram(pts, HISTOGRAM_SIZE), np.float32(yaw))
+    return total
+
+
+def correlative_inputs(w, rotational=True, num_points=2048):
+    """C3 / C4 inputs at the reference's configured thresholds (pose_graph.lua:20, 40-49). rotational=False
+    switches the rotational prefilter off, so that every discrete scan of the sweep is searched (the
+    stress variant: ~8 M lowest-resolution candidates for MatchFullSubmap)."""
     synth = w["synth"]
     origin, yaw = w["map_poses"][3]
     rng = np.random.RandomState(4)
     cloud = synth.scan(origin, yaw, 64, 512, w["sph"], rng)
-    high = synth.voxel_downsample(cloud, 0.2, 2048, seed=4)
+    if num_points > 2048:
+        cloud = synth.scan(origin, yaw, 128, 1024, w["sph"], np.random.RandomState(4))
+    high = synth.voxel_downsample(cloud, 0.2 if num_points <= 2048 else 0.05, num_points, seed=4)
     low = synth.voxel_downsample(cloud, 0.9, 256, seed=5)
-    hist = synth.rotational_histogram(high, 120)
-    opts = dict(branch_and_bound_depth=7, full_resolution_depth=3, use_rotational_scan_matcher=False,
-                min_low_resolution_score=0.3, linear_xy_search_window=5.0, linear_z_search_window=1.0,
-                angular_search_window=float(np.deg2rad(15.0)))
+    hist = synth.rotational_histogram(synth.voxel_downsample(cloud, 0.2, 2048, seed=4), HISTOGRAM_SIZE)
+    opts = dict(branch_and_bound_depth=7, full_resolution_depth=3, use_rotational_scan_matcher=rotational,
+                min_rotational_score=POSE_GRAPH_MIN_ROTATIONAL_SCORE,
+                min_low_resolution_score=POSE_GRAPH_MIN_LOW_RESOLUTION_SCORE, linear_xy_search_window=5.0,
+                linear_z_search_window=1.0, angular_search_window=float(np.deg2rad(15.0)))
     node = np.concatenate([[0, 0, 0], synth.quat_from_yaw(yaw + 0.4)])
     submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
-    return high, low, hist, opts, node, submap
+    return dict(high=high, low=low, hist=hist, submap_hist=submap_histogram(w), opts=opts, node=node,
+                submap=submap, origin=origin, yaw=yaw, min_score=POSE_GRAPH_MIN_SCORE)
+
+
+def local_search_offsets(ci, count, seed=3):
+    """C3: node poses inside the local window around the truth (seeded)."""
+    from hectorgrapher_b200 import synth
+    rng = np.random.RandomState(seed)
+    out = []
+    for _ in range(count):
+        t = ci["origin"] + np.array([rng.uniform(-3, 3), rng.uniform(-3, 3), rng.uniform(-0.6, 0.6)])
+        out.append(np.concatenate([t, synth.quat_from_yaw(ci["yaw"] + rng.uniform(-0.2, 0.2))]))
+    return out
 
 
 def cpu_baseline_candidates(w, seconds=8.0, threads=None):
     """CPU restatement of ScoreCandidates on a bounded sample of C4's lowest-resolution lattice."""
     from oracle import pyoracle as o
     threads = threads or os.cpu_count() or 1
-    high, low, hist, opts, node, submap = correlative_inputs(w)
+    ci = correlative_inputs(w, rotational=False)
+    high, hist, node, submap = ci["high"], ci["hist"], ci["node"], ci["submap"]
     hi = o.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT)
     hi.set_raw(*w["hi"])
     lo = o.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT)
     lo.set_raw(*w["lo"])
-    m = o.Fcsm(hi, lo, hist, **opts)
+    m = o.Fcsm(hi, lo, ci["submap_hist"], **ci["opts"])
     wxy = wz = (hi.grid_size + 1) // 2 + int(np.floor(np.linalg.norm(high, axis=1).max() / HI_RES + 0.5 + 0.5))
     rng = np.random.RandomState(0)
-    depth = opts["branch_and_bound_depth"] - 1
+    depth = ci["opts"]["branch_and_bound_depth"] - 1
     def sample(n):
         # lattice positions over the first 8 discrete scans of a narrow yaw window
         return np.stack([rng.randint(0, 8, n), rng.randint(-wxy, wxy + 1, n) // 64 * 64,
@@ -240,68 +278,196 @@ def cpu_baseline_candidates(w, seconds=8.0, threads=None):
     return n / t, "%d lowest-resolution candidates x %d pts, %d threads" % (n, len(high), threads), threads
 
 
-def correlative_bench(hg, torch, w, rank, world, dist):
-    """C4: MatchFullSubmap on the 0.10 m TSDF submap; discrete scans sharded round-robin over ranks,
-    best candidate gathered over NCCL. Returns a dict for the `correlative` key (rank 0) or None."""
-    g_hi = hg.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT, *w["hi"])
-    g_lo = hg.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT, *w["lo"])
-    high, low, hist, opts, node, submap = correlative_inputs(w)
-    m = hg.Fcsm(g_hi, g_lo, hist, **opts)
-    # warm-up (also sizes the per-thread workspace), then timed searches on this rank's shard
-    m.match(node, submap, high, low, hist, min_score=0.3, full=True, shard_index=rank, num_shards=world)
+def golden():
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "c4_golden.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
+# ncu (profiles/r2_ncu_summary.md): global-load sectors of ScoreLatticePackedKernel<5,1> per (candidate, point)
+# gather; the level it reads is L1-resident, so the kernel is bound by the L1 data path, not by HBM.
+LATTICE_L1_SECTORS_PER_GATHER = 0.1224
+L1_BYTES_PER_CLK_PER_SM = 128
+NUM_SMS = 148
+
+
+def sharded_full_submap(m, ci, rank, world, dist):
+    """One MatchFullSubmap over all ranks: phase A on this rank's discrete scans, one all-reduce-max of the
+    dive bound, phase B under the common bound, all-gather of the best records and selection — all of it
+    inside the caller's timed region. Returns (winner dict or None, order_unresolved, this rank's result)."""
+    from hectorgrapher_b200 import dist as hgdist
+    handle, bound = m.full_submap_begin(ci["node"][3:], ci["submap"][3:], ci["high"], ci["low"], ci["hist"],
+                                        min_score=ci["min_score"], shard_index=rank, num_shards=world)
+    bound = hgdist.all_reduce_max_bound(bound, dist)
+    mine = m.full_submap_finish(handle, bound)
+    best, unresolved = hgdist.reduce_best_candidate(mine, dist)
+    return best, unresolved, mine
+
+
+def correlative_variant(hg, torch, w, rank, world, dist, g_hi, g_lo, rotational, reps=5):
+    ci = correlative_inputs(w, rotational=rotational)
+    m = hg.Fcsm(g_hi, g_lo, ci["submap_hist"], **ci["opts"])
+    for _ in range(2):  # warm-up: sizes the per-thread workspace, first NCCL calls
+        sharded_full_submap(m, ci, rank, world, dist)
     torch.cuda.synchronize()
-    reps = 3
-    dts, r = [], None
+    dts = []
+    best = mine = None
     for _ in range(reps):
         if dist is not None:
             dist.barrier()
+        torch.cuda.synchronize()
         t0 = time.perf_counter()
-        r = m.match(node, submap, high, low, hist, min_score=0.3, full=True, shard_index=rank, num_shards=world)
+        best, unresolved, mine = sharded_full_submap(m, ci, rank, world, dist)
         torch.cuda.synchronize()
         dts.append(time.perf_counter() - t0)
     dt = float(np.median(dts))
-    rec = torch.tensor([dt, float(r["num_scored"]), float(r["found"]), float(r["score"]), float(r["scan_index"]),
-                        r["ox"], r["oy"], r["oz"], float(r["num_scans"]), float(r["num_lattice"]),
-                        float(r["lattice_kernel_ms"]), float(r["num_visited"])], dtype=torch.float64, device="cuda")
-    from hectorgrapher_b200 import dist as hgdist
-    # NCCL best-candidate reduce: one small record per rank, arg-max, ties to the lower scan index
-    best = hgdist.reduce_best_candidate((r["found"], r["score"], r["scan_index"], r["ox"], r["oy"], r["oz"]), dist)
+    rec = torch.tensor([dt, float(mine["num_scored"]), float(mine["num_scans"]), float(mine["num_lattice"]),
+                        float(mine["lattice_kernel_ms"]), float(mine["dive_bound"])], dtype=torch.float64, device="cuda")
     if dist is not None:
         allrec = [torch.zeros_like(rec) for _ in range(world)]
-        dist.all_gather(allrec, rec)  # timing / statistics only
+        dist.all_gather(allrec, rec)  # statistics only, after the timed region
         allrec = torch.stack(allrec).cpu().numpy()
     else:
         allrec = rec.cpu().numpy()[None]
     if rank != 0:
         return None
+    name = "configured" if rotational else "full_sweep"
+    want = golden().get(name)
+    checked = None
+    if want is not None:
+        got = (best["found"], best["score"], best["scan_index"], best["ox"], best["oy"], best["oz"]) if best else (0.0,) * 6
+        exp = (want["found"], want["score"], want["scan_index"], want["ox"], want["oy"], want["oz"])
+        assert tuple(float(np.float32(v)) for v in got) == tuple(float(np.float32(v)) for v in exp), (
+            "C4 %s: selected candidate %r differs from the oracle's %r (tests/golden/c4_golden.json)" % (name, got, exp))
+        checked = "equals the CPU oracle's MatchFullSubmap (tests/golden/c4_golden.json)"
     tmax = float(allrec[:, 0].max())
     scored = float(allrec[:, 1].sum())
-    n_pts = len(high)
-    peak, _ = measured_peak()
-    cps = scored / tmax
-    lattice_n = float(allrec[:, 9].sum())
-    lattice_ms = float(allrec[:, 10].max())
-    lattice_cps = lattice_n / (lattice_ms * 1e-3) if lattice_ms > 0 else 0.0
+    lattice_n = float(allrec[:, 3].sum())
+    lattice_ms = float(allrec[:, 4].max())
+    return {"search_ms": 1e3 * tmax, "candidates_scored": scored, "candidates_per_s": scored / tmax,
+            "discrete_scans": float(allrec[:, 2].sum()),
+            "best": None if best is None else {"score": float(best["score"]), "scan": int(best["scan_index"]),
+                                               "offset": [int(best["ox"]), int(best["oy"]), int(best["oz"])],
+                                               "check": checked, "order_unresolved": bool(unresolved)},
+            "dive_bound": float(allrec[:, 5].max()),
+            "lowest_resolution_kernel": {"candidates": lattice_n, "ms_max_over_ranks": lattice_ms,
+                                         "candidates_per_s_per_gpu": (lattice_n / world) / (lattice_ms * 1e-3)
+                                         if lattice_ms > 0 else 0.0},
+            "num_points": len(ci["high"])}
+
+
+def correlative_bench(hg, torch, w, rank, world, dist, clocks_mhz=None):
+    """M2 on C4: MatchFullSubmap on the 0.10 m TSDF submap at pose_graph.lua's thresholds, discrete scans
+    dealt round-robin over the ranks. The timed region is the whole search as a multi-GPU caller runs it:
+    per-rank phase A, NCCL all-reduce-max of the dive bound, phase B, NCCL all-gather of the best records and
+    the selection. Two variants: 'configured' (rotational prefilter on, as the reference runs) and
+    'full_sweep' (prefilter off: every yaw of the sweep is searched, ~8 M lowest-resolution candidates)."""
+    g_hi = hg.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT, *w["hi"])
+    g_lo = hg.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT, *w["lo"])
+    configured = correlative_variant(hg, torch, w, rank, world, dist, g_hi, g_lo, True)
+    sweep = correlative_variant(hg, torch, w, rank, world, dist, g_hi, g_lo, False)
+    if rank != 0:
+        return None
+    n_pts = sweep["num_points"]
+    lat = sweep["lowest_resolution_kernel"]
+    sm_mhz = clocks_mhz or 1965.0
+    l1_peak = NUM_SMS * L1_BYTES_PER_CLK_PER_SM * sm_mhz * 1e6 / 1e9  # GB/s
+    l1_achieved = lat["candidates_per_s_per_gpu"] * n_pts * LATTICE_L1_SECTORS_PER_GATHER * 32 / 1e9
     cpu_rate, cpu_desc, cpu_threads = cpu_baseline_candidates(w)
     return {
-        "metric": "correlative candidates scored/s", "value": cps, "unit": "candidates/s",
-        "workload": "C4 MatchFullSubmap, 0.10 m TSDF submap, 7-level pyramid (full_resolution_depth 3), "
-                    "N=%d pts, discrete scans sharded over %d rank(s); whole search incl. host replay" % (n_pts, world),
-        "search_ms": 1e3 * tmax, "candidates_scored": scored, "candidates_visited_by_dfs": float(allrec[:, 11].sum()),
-        "discrete_scans": float(allrec[:, 8].sum()),
-        "best": None if best is None else {"score": float(best[1]), "scan": int(best[2]),
-                                           "offset": [int(best[3]), int(best[4]), int(best[5])]},
-        "lowest_resolution_kernel": {"candidates": lattice_n, "ms": lattice_ms, "candidates_per_s": lattice_cps},
-        "roofline": {"bound": "hbm", "achieved": lattice_cps * (n_pts + 24) / world / 1e9, "peak": peak,
-                     "unit": "GB/s", "frac": lattice_cps * (n_pts + 24) / world / 1e9 / peak,
-                     "traffic": measured_traffic("ScoreLatticePackedKernel<5>") if world == 1 else None,
-                     "kernel": "ScoreLatticePackedKernel<5>", "algorithmic_bytes_per_candidate": n_pts + 24,
-                     "note": "per GPU. SURVEY 8(d) counts one byte per (candidate, point) gather against the HBM "
-                             "peak; the level-6 grid is a few hundred KB and is served by L1, so the fraction "
-                             "can exceed 1 - DRAM traffic per launch is in 'traffic'"},
+        "metric": "correlative candidates scored/s", "value": sweep["candidates_per_s"], "unit": "candidates/s",
+        "workload": "C4 MatchFullSubmap, 0.10 m TSDF submap, 7-level pyramid (full_resolution_depth 3), N=%d pts, "
+                    "min_score %.2f / min_low_resolution_score %.2f (pose_graph.lua:20, 45), discrete scans dealt "
+                    "over %d rank(s); timed: phase A + NCCL all-reduce-max of the dive bound + phase B + NCCL "
+                    "all-gather of the best records + selection. 'value' is the full sweep (rotational prefilter "
+                    "off); 'configured' has it on at min_rotational_score %.2f" % (
+                        n_pts, POSE_GRAPH_MIN_SCORE, POSE_GRAPH_MIN_LOW_RESOLUTION_SCORE, world,
+                        POSE_GRAPH_MIN_ROTATIONAL_SCORE),
+        "search_ms": sweep["search_ms"], "candidates_scored": sweep["candidates_scored"],
+        "full_sweep": sweep, "configured": configured,
+        "roofline": {"bound": "l1", "kernel": "ScoreLatticePackedKernel<5,true>", "unit": "GB/s",
+                     "achieved": l1_achieved, "peak": l1_peak, "frac": l1_achieved / l1_peak,
+                     "traffic": measured_traffic("ScoreLatticePackedKernel<5>"),
+                     "note": "per GPU, lowest-resolution lattice kernel of the full sweep. The level it gathers "
+                             "from is a few hundred KB and L1-resident (ncu: 47 MB of DRAM traffic per 8 M-candidate "
+                             "launch), so HBM is not the bound; the bound is the L1 data path: achieved = global-load "
+                             "sectors (ncu: %.4f per gather, four voxels per 32-bit load) x 32 B x gathers/s; peak = "
+                             "%d SMs x %d B/clk x %.0f MHz. SURVEY 8(d)'s byte model (N + 24 B per candidate against "
+                             "HBM) would read %.2f of the HBM peak." % (
+                                 LATTICE_L1_SECTORS_PER_GATHER, NUM_SMS, L1_BYTES_PER_CLK_PER_SM, sm_mhz,
+                                 lat["candidates_per_s_per_gpu"] * (n_pts + 24) / 1e9 / measured_peak()[0])},
         "cpu_baseline": {"value": cpu_rate, "unit": "candidates/s", "cores": cpu_threads, "kind": "port",
                          "sample": cpu_desc},
     }
+
+
+def cpu_baseline_local_search(w, ci, offsets, threads=None):
+    """The oracle's FastCorrelativeScanMatcher3D::Match on a few of the same offsets, one search per thread."""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import pyoracle as o
+    threads = threads or os.cpu_count() or 1
+    hi = o.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT)
+    hi.set_raw(*w["hi"])
+    lo = o.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT)
+    lo.set_raw(*w["lo"])
+    m = o.Fcsm(hi, lo, ci["submap_hist"], **ci["opts"])
+    offsets = offsets[:max(threads, 4)]
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        rs = list(ex.map(lambda nd: m.match(nd, ci["submap"], ci["high"], ci["low"], ci["hist"],
+                                            min_score=ci["min_score"]), offsets))
+    dt = time.perf_counter() - t0
+    scored = sum(int(r["num_scored"]) for r in rs)
+    return {"searches_per_s": len(offsets) / dt, "value": scored / dt, "unit": "candidates/s", "cores": threads,
+            "kind": "port", "sample": "%d of the same searches, one per host thread" % len(offsets)}
+
+
+def local_search_bench(hg, torch, w, rank, world, dist):
+    """C3: FastCorrelativeScanMatcher3D::Match (pose_graph.lua:40-49: 7-level pyramid, full_resolution_depth 3,
+    5 m / 1 m / 15 deg windows, thresholds 0.55 / 0.77 / 0.55) for 100 seeded node poses inside the window, N = 2048
+    points, and 10 at N = 20480; one batched device-resident search per cloud size. Rank 0 only (replicas)."""
+    if rank != 0:
+        return None
+    g_hi = hg.Grid.tsdf(HI_RES, REL_TRUNC, MAX_WEIGHT, *w["hi"])
+    g_lo = hg.Grid.tsdf(LO_RES, REL_TRUNC, MAX_WEIGHT, *w["lo"])
+    out = {"workload": "C3: local Match, 0.10 m TSDF submap, 7-level pyramid (full_resolution_depth 3), windows 5 m / "
+                       "1 m / 15 deg, min_score 0.55, min_rotational_score 0.77, min_low_resolution_score 0.55; seeded "
+                       "node poses inside the window, one hg_fcsm_match_batch per cloud size"}
+    want = golden().get("c3")
+    for n_points, count in ((2048, 100), (20480, 10)):
+        ci = correlative_inputs(w, rotational=True, num_points=n_points)
+        m = hg.Fcsm(g_hi, g_lo, ci["submap_hist"], **ci["opts"])
+        offsets = local_search_offsets(ci, count)
+        submaps = [ci["submap"]] * count
+        nodes = [(ci["high"], ci["low"], ci["hist"])] * count
+        m.match_batch(offsets, submaps, nodes, min_score=ci["min_score"])  # warm-up
+        torch.cuda.synchronize()
+        dts = []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            rs = m.match_batch(offsets, submaps, nodes, min_score=ci["min_score"])
+            dts.append(time.perf_counter() - t0)
+        dt = float(np.median(dts))
+        scored = sum(r["num_scored"] for r in rs)
+        entry = {"points": len(ci["high"]), "searches": count, "found": int(sum(r["found"] for r in rs)),
+                 "ms_per_search": 1e3 * dt / count, "searches_per_s": count / dt, "candidates_scored": scored,
+                 "candidates_per_s": scored / dt, "discrete_scans_per_search": float(np.mean([r["num_scans"] for r in rs]))}
+        if n_points == 2048 and want is not None:
+            keys = want["keys"]
+            for r, row in zip(rs, want["rows"]):
+                got = [float(r[k]) for k in keys]
+                assert got[0] == row[0] and (got[0] == 0 or got[:8] == row[:8]), (
+                    "C3: search result %r differs from the oracle's %r" % (got, row))
+            entry["check"] = "all %d results equal the CPU oracle's (tests/golden/c4_golden.json)" % count
+        if n_points == 2048:
+            try:
+                entry["cpu_baseline"] = cpu_baseline_local_search(w, ci, offsets)
+            except Exception as ex:
+                entry["cpu_baseline"] = {"error": repr(ex)}
+        out["n%d" % n_points] = entry
+    return out
 
 
 C5_FCSM_OPTIONS = dict(branch_and_bound_depth=7, full_resolution_depth=3, use_rotational_scan_matcher=False,
@@ -374,7 +540,7 @@ def cpu_baseline_pairs(synth, sph, num_submaps, pairs=16, threads=None):
         pairs, threads, sum(int(f) for f, _ in out))
 
 
-def constraint_bench(hg, torch, w, rank, world, dist, num_submaps=8, nodes_per_submap=24, cpu=True):
+def constraint_bench(hg, torch, w, rank, world, dist, num_submaps=100, nodes_per_submap=100, cpu=True):
     """C5: ConstraintBuilder3D::ComputeConstraint for (node, submap) pairs — local correlative match +
     CeresScanMatcher3D refine. Submaps are partitioned over ranks (the owner holds that submap's grids and
     pyramid); each submap is built on its owner by device-side TSDF insertion."""
@@ -394,9 +560,9 @@ def constraint_bench(hg, torch, w, rank, world, dist, num_submaps=8, nodes_per_s
         g_los.append(g_lo)
         matchers.append(hg.Fcsm(g_hi, g_lo, hist, **C5_FCSM_OPTIONS))
         jobs += c5_jobs(synth, s, local, origin, yaw, high, low, hist, nodes_per_submap)
-    if mine:
-        hg.ConstraintBatch(matchers[:1], g_his[:1], g_los[:1], jobs[:16], C5_OPTIONS).run()  # warm-up
     batch = hg.ConstraintBatch(matchers, g_his, g_los, jobs, C5_OPTIONS) if mine else None
+    if batch is not None:
+        batch.run()  # warm-up at full size: every worker thread's scratch memory reaches its steady-state size
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
@@ -415,7 +581,9 @@ def constraint_bench(hg, torch, w, rank, world, dist, num_submaps=8, nodes_per_s
     n_jobs = int(stats[2].item())
     out = {"workload": "C5: %d submaps x %d nodes = %d (node, submap) pairs, local Match (5 m / 1 m / 15 deg, "
                        "N=2048) + refine on {high, low} clouds; submaps partitioned over %d rank(s), built by "
-                       "device-side TSDF insertion" % (num_submaps, nodes_per_submap, n_jobs, world),
+                       "device-side TSDF insertion; pairs of a submap searched and refined in groups (one device-resident "
+                       "search + one refine launch per group); timed after one untimed pass of the same batch" % (
+                           num_submaps, nodes_per_submap, n_jobs, world),
            "pairs_per_s": n_jobs / float(dt.item()), "seconds": float(dt.item()),
            "ms_per_pair_per_gpu": 1e3 * float(dt.item()) * world / max(n_jobs, 1),
            "constraints_found": int(stats[0].item()), "candidates_scored": float(stats[1].item()),
@@ -671,14 +839,24 @@ def run_ours(args, rank, world, local_rank):
 
     corr = None
     try:
-        corr = correlative_bench(hg, torch, w, rank, world, dist)
+        corr = correlative_bench(hg, torch, w, rank, world, dist,
+                                 clocks_mhz=(clocks or {}).get("sm_mhz") if clocks else None)
     except Exception as ex:  # the headline must not be lost to the secondary metric
         log("[rank %d] correlative bench failed: %r" % (rank, ex))
         corr = {"error": repr(ex)}
+    if dist is not None:
+        # every rank must leave the correlative section together, whatever happened in it
+        dist.barrier()
+    local = None
+    try:
+        local = local_search_bench(hg, torch, w, rank, world, dist)
+    except Exception as ex:
+        log("[rank %d] local search bench failed: %r" % (rank, ex))
+        local = {"error": repr(ex)}
     cons = None
     try:
-        if args.c5_full:
-            cons = constraint_bench(hg, torch, w, rank, world, dist, num_submaps=100, nodes_per_submap=100)
+        if args.c5_small:
+            cons = constraint_bench(hg, torch, w, rank, world, dist, num_submaps=8, nodes_per_submap=24)
         else:
             cons = constraint_bench(hg, torch, w, rank, world, dist)
     except Exception as ex:
@@ -730,6 +908,7 @@ def run_ours(args, rank, world, local_rank):
             "normal_equations": {"ms_per_step": ne_ms, "points_per_s": N / (ne_ms * 1e-3),
                                  "note": "hg_batch_normal_equations: host poses in, 64 x (14x14 JtJ, Jtr, cost) out"},
             "correlative": corr,
+            "local_search": local,
             "constraint_batch": cons,
             "insertion": ins,
             "c1_scan_to_submap": c1,
@@ -752,6 +931,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--c5-small", action="store_true", help="C5 on 8 x 24 pairs instead of 100 x 100 (quick runs)")
     ap.add_argument("--c5-full", action="store_true",
                     help="run the constraint batch at BASELINE.json's full C5 size (100 submaps x 100 nodes)")
     args = ap.parse_args()

@@ -135,6 +135,9 @@ SYMBOLS = {
     "hg_fcsm_full_submap_begin": (c_i, [vp, vp, vp, vp, c_f, c_i, c_i, vp, vp]),
     "hg_fcsm_full_submap_finish": (c_i, [vp, c_f, vp]),
     "hg_fcsm_search_abandon": (None, [vp]),
+    "hg_pack_best_record": (c_i, [vp, vp]),
+    "hg_unpack_best_record": (c_i, [vp, vp]),
+    "hg_select_best_record": (c_i, [vp, c_i, vp, vp]),
     "hg_fcsm_discrete_scans": (c_i, [vp, c_i, c_i, c_d, vp, vp, vp, c_i, vp, vp, vp, vp]),
     "hg_fcsm_score_candidates": (c_i, [vp, c_i, c_i, c_d, vp, vp, vp, c_i, c_i64, vp, vp, vp, vp]),
     "hg_low_resolution_scores": (c_i, [vp, vp, c_i, c_i64, vp, vp]),
@@ -593,6 +596,49 @@ def _result_dict(r):
                 lattice_kernel_ms=float(r.lowest_resolution_kernel_ms),
                 ancestor_score=float(r.best_ancestor_score), ancestor_index=int(r.best_ancestor_index),
                 dive_bound=float(r.dive_bound))
+
+
+BEST_RECORD_DOUBLES = 20
+
+
+def _result_struct(d):
+    """MatchResult from a result dict (the fields the best-record exchange carries)."""
+    r = MatchResult()
+    r.found = int(d["found"])
+    r.score = d["score"]
+    for k, n in enumerate(("tx", "ty", "tz")):
+        r.pose_translation[k] = d[n]
+    for k, n in enumerate(("qw", "qx", "qy", "qz")):
+        r.pose_rotation[k] = d[n]
+    r.rotational_score = d["rotational_score"]
+    r.low_resolution_score = d["low_resolution_score"]
+    r.best_scan_index = int(d["scan_index"])
+    for k, n in enumerate(("ox", "oy", "oz")):
+        r.best_offset[k] = int(d[n])
+    r.num_candidates_scored = int(d.get("num_scored", 0))
+    r.best_ancestor_score = d.get("ancestor_score", 0.0)
+    r.best_ancestor_index = int(d.get("ancestor_index", 0))
+    return r
+
+
+def pack_best_record(result):
+    """hg_pack_best_record of a result dict -> numpy array of BEST_RECORD_DOUBLES doubles."""
+    rec = np.zeros(BEST_RECORD_DOUBLES)
+    r = _result_struct(result)
+    _check(lib().hg_pack_best_record(C.byref(r), _p(rec)))
+    return rec
+
+
+def select_best_record(records):
+    """hg_select_best_record over [n, BEST_RECORD_DOUBLES] records -> (result dict or None, order_unresolved)."""
+    records = _f64(records).reshape(-1, BEST_RECORD_DOUBLES)
+    winner, unresolved = C.c_int(-1), C.c_int(0)
+    _check(lib().hg_select_best_record(_p(records), len(records), C.byref(winner), C.byref(unresolved)))
+    if winner.value < 0:
+        return None, False
+    r = MatchResult()
+    _check(lib().hg_unpack_best_record(_p(np.ascontiguousarray(records[winner.value])), C.byref(r)))
+    return _result_dict(r), bool(unresolved.value)
 
 
 class Fcsm:

@@ -2966,6 +2966,82 @@ int hg_fcsm_full_submap_finish(hg_fcsm_search* search, float bound, hg_match_res
 
 void hg_fcsm_search_abandon(hg_fcsm_search* search) { delete search; }
 
+// ---- best-record exchange between the shards of one search --------------------------------
+// Layout of a record (HG_BEST_RECORD_DOUBLES doubles): 0 found, 1 score, 2 ancestor score,
+// 3 ancestor generation index, 4 scan index, 5..7 offset, 8..14 pose (t3 q4), 15 rotational score,
+// 16 low-resolution score, 17 candidates scored, 18..19 reserved.
+int hg_pack_best_record(const hg_match_result* r, double* record) {
+  HG_REQUIRE(r != nullptr && record != nullptr, "hg_pack_best_record: bad arguments");
+  for (int k = 0; k < HG_BEST_RECORD_DOUBLES; ++k) record[k] = 0.0;
+  record[0] = r->found ? 1.0 : 0.0;
+  record[1] = r->score;
+  record[2] = r->best_ancestor_score;
+  record[3] = static_cast<double>(r->best_ancestor_index);
+  record[4] = r->best_scan_index;
+  for (int k = 0; k < 3; ++k) record[5 + k] = r->best_offset[k];
+  for (int k = 0; k < 3; ++k) record[8 + k] = r->pose_translation[k];
+  for (int k = 0; k < 4; ++k) record[11 + k] = r->pose_rotation[k];
+  record[15] = r->rotational_score;
+  record[16] = r->low_resolution_score;
+  record[17] = static_cast<double>(r->num_candidates_scored);
+  return HG_OK;
+}
+
+int hg_unpack_best_record(const double* record, hg_match_result* r) {
+  HG_REQUIRE(r != nullptr && record != nullptr, "hg_unpack_best_record: bad arguments");
+  std::memset(r, 0, sizeof(*r));
+  r->found = record[0] > 0.0 ? 1 : 0;
+  r->score = static_cast<float>(record[1]);
+  r->best_ancestor_score = static_cast<float>(record[2]);
+  r->best_ancestor_index = static_cast<int64_t>(record[3]);
+  r->best_scan_index = static_cast<int32_t>(record[4]);
+  for (int k = 0; k < 3; ++k) r->best_offset[k] = static_cast<int32_t>(record[5 + k]);
+  for (int k = 0; k < 3; ++k) r->pose_translation[k] = record[8 + k];
+  for (int k = 0; k < 4; ++k) r->pose_rotation[k] = record[11 + k];
+  r->rotational_score = static_cast<float>(record[15]);
+  r->low_resolution_score = static_cast<float>(record[16]);
+  r->num_candidates_scored = static_cast<int64_t>(record[17]);
+  return HG_OK;
+}
+
+// The reference's search keeps the first best leaf it visits (std::max keeps the earlier of equal
+// scores, :465-466) and visits the lowest-resolution candidates in descending order of their
+// score (:384, :437). Across shards that is: the higher leaf score; on equal leaf scores the leaf
+// whose lowest-resolution ancestor scores higher; ancestors of equal score are ordered by the
+// reference's std::sort, which no shard can reproduce alone — the earlier generation index is
+// taken and *order_unresolved is set so that the caller can rerun unsharded in strict order.
+int hg_select_best_record(const double* records, int num_records, int* winner, int* order_unresolved) {
+  HG_REQUIRE(records != nullptr && num_records >= 0 && winner != nullptr, "hg_select_best_record: bad arguments");
+  *winner = -1;
+  if (order_unresolved) *order_unresolved = 0;
+  for (int k = 0; k < num_records; ++k) {
+    const double* r = records + static_cast<size_t>(k) * HG_BEST_RECORD_DOUBLES;
+    if (!(r[0] > 0.0)) continue;
+    if (*winner < 0) {
+      *winner = k;
+      continue;
+    }
+    const double* b = records + static_cast<size_t>(*winner) * HG_BEST_RECORD_DOUBLES;
+    if (r[1] != b[1]) {
+      if (r[1] > b[1]) {
+        *winner = k;
+        if (order_unresolved) *order_unresolved = 0;
+      }
+      continue;
+    }
+    if (r[2] != b[2]) {
+      if (r[2] > b[2]) {
+        *winner = k;
+        if (order_unresolved) *order_unresolved = 0;
+      }
+      continue;
+    }
+    if (order_unresolved) *order_unresolved = 1;
+    if (r[3] < b[3]) *winner = k;
+  }
+  return HG_OK;
+}
+
 int hg_fcsm_discrete_scans(const hg_fcsm* m, int wxy, int wz, double angular_search_window,
                            const double* global_node_pose, const double* global_submap_pose,
                            const hg_node_data* data, int max_scans, int32_t* num_scans, float* poses,

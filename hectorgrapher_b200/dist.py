@@ -12,22 +12,32 @@ def shard_indices(n, rank, world):
     return np.arange(rank, n, world, dtype=np.int64)
 
 
-def reduce_best_candidate(record, dist, device="cuda"):
-    """record = (found, score, global_scan_index, ox, oy, oz) of this rank's search. All-gathers one
-    small record per rank and returns the winning record as a tuple of floats (None if no rank found a
-    match): highest score; equal scores go to the lower global scan index, then the lower rank."""
-    mine = torch.tensor([float(v) for v in record], dtype=torch.float64, device=device)
+def all_reduce_max_bound(bound, dist, device="cuda"):
+    """The optional mid-search exchange of a sharded MatchFullSubmap: the largest dive bound
+    any shard found (hg_fcsm_full_submap_begin), one 4-byte all-reduce-max."""
     if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
-        allrec = mine.cpu().numpy()[None]
+        return float(bound)
+    t = torch.tensor([float(bound)], dtype=torch.float32, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def reduce_best_candidate(result, dist, device="cuda"):
+    """result: this rank's match result (dict of hectorgrapher_b200.capi, or None). All-gathers one
+    fixed-size record per rank (hg_pack_best_record) and selects the winner with the library's rule
+    (hg_select_best_record: leaf score, then the score of the leaf's lowest-resolution ancestor, then its
+    generation index — the order in which the reference's search would have met the leaves). Returns
+    (winning result dict or None, order_unresolved)."""
+    from . import capi
+    mine = capi.pack_best_record(result) if result is not None else np.zeros(capi.BEST_RECORD_DOUBLES)
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        allrec = mine[None]
     else:
-        bufs = [torch.zeros_like(mine) for _ in range(dist.get_world_size())]
-        dist.all_gather(bufs, mine)
+        t = torch.as_tensor(mine, dtype=torch.float64, device=device)
+        bufs = [torch.zeros_like(t) for _ in range(dist.get_world_size())]
+        dist.all_gather(bufs, t)
         allrec = torch.stack(bufs).cpu().numpy()
-    found = allrec[allrec[:, 0] > 0]
-    if len(found) == 0:
-        return None
-    order = np.lexsort((found[:, 2], -found[:, 1]))
-    return tuple(float(v) for v in found[order[0]])
+    return capi.select_best_record(allrec)
 
 
 def gather_job_results(local, owned, dist, device="cuda"):

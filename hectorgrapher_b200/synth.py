@@ -235,6 +235,19 @@ def rotational_histogram(points, size=120):
     return hist
 
 
+def rotate_histogram(histogram, angle):
+    """RotationalScanMatcher::RotateHistogram (rotational_scan_matcher.cc:121-143) in float32: how a
+    submap's histogram is made from a node's (inputs for the benchmarks and tests only)."""
+    h = np.asarray(histogram, np.float32)
+    size = len(h)
+    rotate_by = np.float32((-np.float32(angle) * size) / np.pi)
+    full = int(round_half_away(np.float64(rotate_by - np.float32(0.5))))
+    frac = np.float32(rotate_by - np.float32(full))
+    full %= size
+    idx = np.arange(size)
+    return (frac * h[(idx + 1 + full) % size] + (np.float32(1) - frac) * h[(idx + full) % size]).astype(np.float32)
+
+
 def voxel_downsample(points, size, max_points=None, seed=0):
     """One point per voxel of edge 'size' (the role of sensor::VoxelFilter before the matcher)."""
     c = cell_index(points, size)

@@ -460,6 +460,21 @@ int hg_fcsm_full_submap_finish(hg_fcsm_search* search, float bound, hg_match_res
 /* Drops a search that will not be finished. */
 void hg_fcsm_search_abandon(hg_fcsm_search* search);
 
+/* The one exchange of a sharded search: every shard packs its result into a
+ * fixed-size record of HG_BEST_RECORD_DOUBLES doubles, the caller all-gathers the records (for
+ * instance ncclAllGather with ncclDouble, or torch.distributed), and every rank selects the same
+ * winner. Order: the reference's search keeps the FIRST best leaf it visits and visits the
+ * lowest-resolution candidates in descending order of their score
+ * (fast_correlative_scan_matcher_3d.cc:384, 437-440, 465-466): higher leaf score first; equal
+ * leaf scores go to the leaf whose lowest-resolution ancestor scores higher. Ancestors of equal
+ * score are ordered by the reference's std::sort of the whole lowest-resolution list, which only
+ * an unsharded search in strict order reproduces: the earlier generation index wins here and
+ * *order_unresolved (may be NULL) is set. *winner = index of the winning record, -1 if none. */
+#define HG_BEST_RECORD_DOUBLES 20
+int hg_pack_best_record(const hg_match_result* result, double* record);
+int hg_unpack_best_record(const double* record, hg_match_result* result);
+int hg_select_best_record(const double* records, int num_records, int* winner, int* order_unresolved);
+
 /* Stage-level entry points (parity tests and the candidates/s benchmark). */
 
 /* GenerateDiscreteScans (:276-326) for an explicit window. Host outputs, any
