@@ -48,7 +48,8 @@ class MatchResult(C.Structure):
                 ("num_discrete_scans", C.c_int32), ("num_candidates_scored", c_i64),
                 ("num_candidates_visited", c_i64), ("num_score_launches", C.c_int32),
                 ("num_lowest_resolution_candidates", c_i64), ("lowest_resolution_kernel_ms", c_f),
-                ("best_ancestor_score", c_f), ("best_ancestor_index", c_i64), ("dive_bound", c_f)]
+                ("best_ancestor_score", c_f), ("best_ancestor_index", c_i64), ("dive_bound", c_f),
+                ("order_unresolved", C.c_int32)]
 
 
 class OccupancyInserterOptions(C.Structure):
@@ -595,7 +596,7 @@ def _result_dict(r):
                 num_lattice=int(r.num_lowest_resolution_candidates),
                 lattice_kernel_ms=float(r.lowest_resolution_kernel_ms),
                 ancestor_score=float(r.best_ancestor_score), ancestor_index=int(r.best_ancestor_index),
-                dive_bound=float(r.dive_bound))
+                dive_bound=float(r.dive_bound), order_unresolved=int(r.order_unresolved))
 
 
 BEST_RECORD_DOUBLES = 20
@@ -618,6 +619,7 @@ def _result_struct(d):
     r.num_candidates_scored = int(d.get("num_scored", 0))
     r.best_ancestor_score = d.get("ancestor_score", 0.0)
     r.best_ancestor_index = int(d.get("ancestor_index", 0))
+    r.order_unresolved = int(d.get("order_unresolved", 0))
     return r
 
 

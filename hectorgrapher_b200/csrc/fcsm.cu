@@ -273,6 +273,8 @@ __global__ void __launch_bounds__(256, ONE_CHUNK ? 8 : 4)
     for (int k = 0; k < KX; ++k) sum[k] = 0;
   }
   unsigned even[KXW], odd[KXW];
+#pragma unroll
+  for (int j = 0; j < KXW; ++j) even[j] = odd[j] = 0u;  // lanes beyond a cloud of fewer than 32 points add nothing
   for (int chunk = lane; chunk < N; chunk += 32 * 256) {
 #pragma unroll
     for (int j = 0; j < KXW; ++j) even[j] = odd[j] = 0u;
@@ -521,33 +523,65 @@ __global__ void __launch_bounds__(128) LowResolutionKernel(const GridDev g, cons
 
 // ------------------------------------------------------------- host parts --
 
-// rotational_scan_matcher.cc:121-143
-std::vector<float> RotateHistogram(const std::vector<float>& histogram, const float angle) {
+// rotational_scan_matcher.cc:134-155, written into 'out' (size of the histogram). The indices
+// (i + full_buckets) % size are stepped instead of divided; the float operations are the
+// reference's: fraction * h1 + (1 - fraction) * h0, unfused (-ffp-contract=off).
+void RotateHistogram(const std::vector<float>& histogram, const float angle, float* out) {
   const long size = static_cast<long>(histogram.size());
+  if (size == 0) return;
   const float rotate_by_buckets = static_cast<float>((-angle * size) / M_PI);
   int full_buckets = static_cast<int>(std::lround(rotate_by_buckets - 0.5f));
   const float fraction = rotate_by_buckets - full_buckets;
   while (full_buckets < 0) full_buckets += static_cast<int>(size);
-  std::vector<float> out(histogram.size());
+  long i0 = full_buckets % size, i1 = (full_buckets + 1) % size;
+  const float one_minus = 1.f - fraction;
   for (long i = 0; i != size; ++i) {
-    const float h0 = histogram[(i + full_buckets) % size];
-    const float h1 = histogram[(i + 1 + full_buckets) % size];
-    out[i] = fraction * h1 + (1.f - fraction) * h0;
+    out[i] = fraction * histogram[i1] + one_minus * histogram[i0];
+    if (++i0 == size) i0 = 0;
+    if (++i1 == size) i1 = 0;
   }
-  return out;
 }
 
-// rotational_scan_matcher.cc:106-117 (plain left-to-right float sums).
-float MatchHistograms(const std::vector<float>& submap, const std::vector<float>& scan) {
-  float scan_sq = 0.f, submap_sq = 0.f, dot = 0.f;
-  for (size_t i = 0; i < scan.size(); ++i) {
-    scan_sq += scan[i] * scan[i];
-    submap_sq += submap[i] * submap[i];
-    dot += submap[i] * scan[i];
+// Eigen's sum of n floats over a VectorXf expression (Eigen 3.3 Core/Redux.h; Eigen is not
+// vendored in the reference, restated from memory): flavor 1 = the SSE2 build of an x86-64
+// reference — packets of 4 from the aligned start, two packet accumulators taking alternate
+// packets, their sum, one more packet when their number is odd, predux (a0 + a2) + (a1 + a3),
+// scalar tail; flavor 0 = the generic scalar code, left to right.
+template <typename Term>
+float EigenSum(const long n, const int flavor, const Term& term) {
+  if (flavor != 1 || n < 4) {
+    float res = term(0);
+    for (long i = 1; i < n; ++i) res = res + term(i);
+    return res;
   }
-  const float normalization = std::sqrt(scan_sq) * std::sqrt(submap_sq);
+  const long aligned_end2 = (n / 8) * 8, aligned_end = (n / 4) * 4;
+  float p0[4], p1[4];
+  for (int k = 0; k < 4; ++k) p0[k] = term(k);
+  if (aligned_end > 4) {
+    for (int k = 0; k < 4; ++k) p1[k] = term(4 + k);
+    for (long index = 8; index < aligned_end2; index += 8) {
+      for (int k = 0; k < 4; ++k) p0[k] = p0[k] + term(index + k);
+      for (int k = 0; k < 4; ++k) p1[k] = p1[k] + term(index + 4 + k);
+    }
+    for (int k = 0; k < 4; ++k) p0[k] = p0[k] + p1[k];
+    if (aligned_end > aligned_end2) {
+      for (int k = 0; k < 4; ++k) p0[k] = p0[k] + term(aligned_end2 + k);
+    }
+  }
+  float res = (p0[0] + p0[2]) + (p0[1] + p0[3]);
+  for (long i = aligned_end; i < n; ++i) res = res + term(i);
+  return res;
+}
+
+// rotational_scan_matcher.cc:121-132 (VectorXf::norm and ::dot). 'submap_norm' is the submap
+// histogram's norm, which does not depend on the yaw.
+float MatchHistograms(const std::vector<float>& submap, const float submap_norm, const float* scan, const int flavor) {
+  const long n = static_cast<long>(submap.size());
+  if (n == 0) return 1.f;
+  const float scan_norm = std::sqrt(EigenSum(n, flavor, [&](long i) { return scan[i] * scan[i]; }));
+  const float normalization = scan_norm * submap_norm;
   if (normalization < 1e-3f) return 1.f;
-  return dot / normalization;
+  return EigenSum(n, flavor, [&](long i) { return submap[i] * scan[i]; }) / normalization;
 }
 
 struct SearchParameters {
@@ -693,8 +727,14 @@ int ComputeScanPoses(const hg_fcsm* m, const SearchParameters& sp, const hg_node
     const std::vector<float> scan_hist(data->rotational_scan_matcher_histogram,
                                        data->rotational_scan_matcher_histogram + data->histogram_size);
     scores.reserve(angles.size());
-    for (const float angle : angles)
-      scores.push_back(MatchHistograms(m->histogram, RotateHistogram(scan_hist, initial_angle + angle)));
+    const long hn = static_cast<long>(m->histogram.size());
+    const float submap_norm =
+        hn == 0 ? 0.f : std::sqrt(EigenSum(hn, flavor, [&](long i) { return m->histogram[i] * m->histogram[i]; }));
+    std::vector<float> rotated(scan_hist.size());
+    for (const float angle : angles) {
+      RotateHistogram(scan_hist, initial_angle + angle, rotated.data());
+      scores.push_back(MatchHistograms(m->histogram, submap_norm, rotated.data(), flavor));
+    }
   }
   out->poses.clear();
   out->rotational_scores.clear();
@@ -2261,6 +2301,29 @@ __global__ void __launch_bounds__(256) WinnersKernel(const SearchDev s) {
   }
 }
 
+// Sums of explicit candidates (scan of the batch-wide list, offset) at one depth: a warp each. Used
+// to order exactly tied winners (the scores of their ancestors decide).
+__global__ void __launch_bounds__(256) ScoreListKernel(const SearchDev s, const BrickTable level, const DenseLevel dense,
+                                                       const int depth, const int4* __restrict__ candidates,
+                                                       const int n, int* __restrict__ sums) {
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= n) return;
+  const int4 c = candidates[w];
+  const ProblemDev& P = s.problems[s.scans[c.x].problem];
+  const int e = max(0, depth - s.frd + 1);
+  const int ox = c.y >> e, oy = c.z >> e, oz = c.w >> e;
+  const int* base = CellsOf(s, P, c.x - P.scan_begin, depth);
+  int sum = 0;
+  for (int i = lane; i < P.N; i += 32) {
+    const int x = __ldg(base + 3 * i), y = __ldg(base + 3 * i + 1), z = __ldg(base + 3 * i + 2);
+    sum += dense.data != nullptr ? LoadDenseU8(dense, x + ox, y + oy, z + oz) : LoadU8(level, x + ox, y + oy, z + oz);
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+  if (lane == 0) sums[w] = sum;
+}
+
 }  // namespace
 }  // namespace hg
 
@@ -2285,6 +2348,7 @@ class DeviceSearch {
     int64_t ancestor_index = 0;  // generation index of the lowest-resolution ancestor, unsharded scan numbering
     int64_t scored = 0;
     float local_bound = 0.f;  // this problem's own dive bound (0 = none)
+    bool order_unresolved = false;  // tied winners below equal-scoring ancestors inside one shard of a sweep
   };
 
   DeviceSearch(const hg_fcsm* m, cudaStream_t stream) : m_(m), stream_(stream), ws_(&GetWorkspace(m->device)) {}
@@ -2578,13 +2642,30 @@ class DeviceSearch {
         o.needs_host_replay = pp[p] != 0 && thresh_bits == pp[p];
         continue;
       }
+      int chosen = -1;
       if (wins > 1) {
-        o.needs_host_replay = true;  // exact tie: the reference's visiting order decides
-        continue;
+        // exact tie: the leaf the reference's search meets first wins
+        std::vector<WinnerRec> tied;
+        for (int k = 0; k < recorded; ++k)
+          if (winners[k].problem == p) tied.push_back(winners[k]);
+        int first = -1;
+        const int rc = FirstVisited(p, tied, &first, &o.order_unresolved);
+        if (rc != HG_OK) return rc;
+        if (first < 0) {
+          o.needs_host_replay = true;
+          continue;
+        }
+        for (int k = 0; k < recorded; ++k) {
+          const WinnerRec& w = winners[k];
+          if (w.problem == p && w.scan == tied[first].scan && w.ox == tied[first].ox && w.oy == tied[first].oy &&
+              w.oz == tied[first].oz) {
+            chosen = k;
+          }
+        }
       }
       for (int k = 0; k < recorded; ++k) {
         const WinnerRec& w = winners[k];
-        if (w.problem != p) continue;
+        if (w.problem != p || (chosen >= 0 && k != chosen)) continue;
         o.found = true;
         o.scan = w.scan - scan_begin(p);
         o.ox = w.ox; o.oy = w.oy; o.oz = w.oz;
@@ -2598,6 +2679,148 @@ class DeviceSearch {
       }
     }
     return HG_OK;
+  }
+
+  // Among exactly tied winners of problem p, the one the reference's depth-first search meets first
+  // (:408-471): subtrees are visited in the order of the sorted candidate lists — the lowest-resolution
+  // list by std::sort on the score (:384), every list of children by score with equal scores in
+  // generation order (std::sort on <= 16 elements is an insertion sort in libstdc++: stable) — and
+  // std::max keeps the earlier of equal leaves. So the winners are compared by the scores of their
+  // ancestors, level by level from the top. *first = -1 when this cannot be settled here.
+  int FirstVisited(int p, const std::vector<WinnerRec>& tied, int* first, bool* order_unresolved) {
+    *first = -1;
+    *order_unresolved = false;
+    const int n = static_cast<int>(tied.size());
+    if (n < 2 || n > 4096) return HG_OK;
+    const SearchParameters& sp = problems_[p].sp;
+    const ScanSet& sc = problems_[p].scans;
+    // ancestors at depth d = 1 .. max_depth - 1 (the leaf's sum and the top ancestor's are known)
+    const auto ancestor = [&](const WinnerRec& w, int d, int* o) {
+      o[0] = -sp.wxy + (((w.ox + sp.wxy) >> d) << d);
+      o[1] = -sp.wxy + (((w.oy + sp.wxy) >> d) << d);
+      o[2] = -sp.wz + (((w.oz + sp.wz) >> d) << d);
+    };
+    // scores[d][k]: score of winner k's ancestor at depth d (the reference compares float scores)
+    std::vector<std::vector<float>> scores(max_depth_ + 1, std::vector<float>(n, 0.f));
+    for (int k = 0; k < n; ++k) {
+      scores[0][k] = ScoreFromSum(tied[k].sum, sc.N);
+      scores[max_depth_][k] = ScoreFromSum(tied[k].ancestor_sum, sc.N);
+    }
+    if (max_depth_ >= 2) {
+      const size_t bytes = static_cast<size_t>(n) * (sizeof(int4) + sizeof(int));
+      int rc = ws_->h_cand.Reserve(bytes);
+      if (rc != HG_OK) return rc;
+      if ((rc = ws_->d_cand.Reserve(bytes)) != HG_OK) return rc;
+      int4* hc = ws_->h_cand.as<int4>();
+      int* hs = reinterpret_cast<int*>(hc + n);
+      int4* dc = ws_->d_cand.as<int4>();
+      int* ds = reinterpret_cast<int*>(dc + n);
+      for (int d = 1; d < max_depth_; ++d) {
+        for (int k = 0; k < n; ++k) {
+          int o[3];
+          ancestor(tied[k], d, o);
+          hc[k] = make_int4(tied[k].scan, o[0], o[1], o[2]);
+        }
+        const hg_stack_level& L = m_->stack->levels[d];
+        HG_CUDA(cudaMemcpyAsync(dc, hc, n * sizeof(int4), cudaMemcpyHostToDevice, stream_));
+        ScoreListKernel<<<(n * 32 + 255) / 256, 256, 0, stream_>>>(dev_, L.table, L.dense, d, dc, n, ds);
+        CountLaunch();
+        ++launches_;
+        HG_CUDA(cudaGetLastError());
+        HG_CUDA(cudaMemcpyAsync(hs, ds, n * sizeof(int), cudaMemcpyDeviceToHost, stream_));
+        HG_CUDA(cudaStreamSynchronize(stream_));
+        for (int k = 0; k < n; ++k) scores[d][k] = ScoreFromSum(hs[k], sc.N);
+      }
+    }
+    // generation index of the top ancestor in this problem's lattice (local scans)
+    const auto top_index = [&](const WinnerRec& w) {
+      const int ix = (w.ox + sp.wxy) >> max_depth_, iy = (w.oy + sp.wxy) >> max_depth_, iz = (w.oz + sp.wz) >> max_depth_;
+      return static_cast<int64_t>(w.scan - scan_begin(p)) * per_scan_ + (iz * nxy_ + iy) * nxy_ + ix;
+    };
+    // Position of the distinct top ancestors in the sorted lowest-resolution list. Different scores:
+    // descending. Equal scores: the permutation std::sort gives the whole list (introsort is not stable, but
+    // it is a function of the comparison results alone), reproduced by sorting (score, index) keys of the
+    // whole lattice in generation order with the same comparison.
+    std::vector<int64_t> tops(n);
+    for (int k = 0; k < n; ++k) tops[k] = top_index(tied[k]);
+    bool equal_tops_differ = false;
+    for (int a = 0; a < n && !equal_tops_differ; ++a)
+      for (int b = a + 1; b < n; ++b)
+        if (tops[a] != tops[b] && scores[max_depth_][a] == scores[max_depth_][b]) {
+          equal_tops_differ = true;
+          break;
+        }
+    std::vector<int64_t> position(n, 0);
+    const bool whole_sweep = UnshardedScans(sc);
+    if (equal_tops_differ && whole_sweep) {
+      const size_t ln = static_cast<size_t>(sc.S) * per_scan_;
+      std::vector<int> lattice(ln);
+      HG_CUDA(cudaMemcpyAsync(lattice.data(), dev_.lattice + static_cast<size_t>(scan_begin(p)) * per_scan_,
+                              ln * sizeof(int), cudaMemcpyDeviceToHost, stream_));
+      HG_CUDA(cudaStreamSynchronize(stream_));
+      struct Key {
+        float score;
+        uint32_t index;
+      };
+      std::vector<Key> keys(ln);
+      for (size_t i = 0; i < ln; ++i) keys[i] = Key{ScoreFromSum(lattice[i], sc.N), static_cast<uint32_t>(i)};
+      std::sort(keys.begin(), keys.end(), [](const Key& a, const Key& b) { return a.score > b.score; });
+      std::vector<uint32_t> where(ln);
+      for (size_t i = 0; i < ln; ++i) where[keys[i].index] = static_cast<uint32_t>(i);
+      for (int k = 0; k < n; ++k) position[k] = where[tops[k]];
+    } else {
+      // Distinct scores order the tops. Equal scores of different tops inside ONE SHARD of a sweep: the
+      // permutation of the whole list is not known here; the earlier generation index stands in, as in
+      // hg_select_best_record.
+      *order_unresolved = equal_tops_differ;
+      std::vector<int> order(n);
+      for (int k = 0; k < n; ++k) order[k] = k;
+      std::sort(order.begin(), order.end(), [&](int a, int b) {
+        if (scores[max_depth_][a] != scores[max_depth_][b]) return scores[max_depth_][a] > scores[max_depth_][b];
+        return tops[a] < tops[b];
+      });
+      for (int r = 0; r < n; ++r) position[order[r]] = r;
+      for (int r = 1; r < n; ++r)  // the same node gets the same position
+        if (tops[order[r]] == tops[order[r - 1]]) position[order[r]] = position[order[r - 1]];
+    }
+    const auto slot_at = [&](const WinnerRec& w, int d) {  // generation slot of the depth-d ancestor among its siblings
+      int o[3], q[3];
+      ancestor(w, d, o);
+      ancestor(w, d + 1, q);
+      return ((o[2] != q[2]) ? 4 : 0) | ((o[1] != q[1]) ? 2 : 0) | ((o[0] != q[0]) ? 1 : 0);
+    };
+    const auto before = [&](int a, int b) {  // is winner a met before winner b?
+      if (tops[a] != tops[b]) return position[a] < position[b];
+      for (int d = max_depth_ - 1; d >= 0; --d) {
+        int oa[3], ob[3];
+        ancestor(tied[a], d, oa);
+        ancestor(tied[b], d, ob);
+        if (oa[0] == ob[0] && oa[1] == ob[1] && oa[2] == ob[2]) continue;
+        if (scores[d][a] != scores[d][b]) return scores[d][a] > scores[d][b];
+        return slot_at(tied[a], d) < slot_at(tied[b], d);
+      }
+      return false;
+    };
+    int best = 0;
+    for (int k = 1; k < n; ++k)
+      if (before(k, best)) best = k;
+    if (TraceEnabled()) {
+      for (int k = 0; k < n; ++k) {
+        std::fprintf(stderr, "[hg trace] tied winner %d: scan %d offset (%d, %d, %d) top %lld position %lld scores", k,
+                     tied[k].scan - scan_begin(p), tied[k].ox, tied[k].oy, tied[k].oz, static_cast<long long>(tops[k]),
+                     static_cast<long long>(position[k]));
+        for (int d = max_depth_; d >= 0; --d) std::fprintf(stderr, " %.6f", scores[d][k]);
+        std::fprintf(stderr, "%s\n", k == best ? "  <- first" : "");
+      }
+    }
+    *first = best;
+    return HG_OK;
+  }
+  // The whole yaw sweep is in this problem (not a shard of it): the global scan numbering is 0 .. S-1.
+  static bool UnshardedScans(const ScanSet& sc) {
+    for (int k = 0; k < sc.S; ++k)
+      if (sc.global_scan_index[k] != k) return false;
+    return true;
   }
 
   // GetPoseFromCandidate (:400-406).
@@ -2678,6 +2901,7 @@ void FillResult(const DeviceSearch& search, int p, const DeviceSearch::Outcome& 
   result->best_offset[2] = o.oz;
   result->best_ancestor_score = o.ancestor_score;
   result->best_ancestor_index = o.ancestor_index;
+  result->order_unresolved = o.order_unresolved ? 1 : 0;
 }
 
 // HG_SEARCH_HOST_REPLAY=1 sends every search through the host replay (tests compare the two).
@@ -2969,7 +3193,7 @@ void hg_fcsm_search_abandon(hg_fcsm_search* search) { delete search; }
 // ---- best-record exchange between the shards of one search --------------------------------
 // Layout of a record (HG_BEST_RECORD_DOUBLES doubles): 0 found, 1 score, 2 ancestor score,
 // 3 ancestor generation index, 4 scan index, 5..7 offset, 8..14 pose (t3 q4), 15 rotational score,
-// 16 low-resolution score, 17 candidates scored, 18..19 reserved.
+// 16 low-resolution score, 17 candidates scored, 18 order unresolved inside the shard, 19 reserved.
 int hg_pack_best_record(const hg_match_result* r, double* record) {
   HG_REQUIRE(r != nullptr && record != nullptr, "hg_pack_best_record: bad arguments");
   for (int k = 0; k < HG_BEST_RECORD_DOUBLES; ++k) record[k] = 0.0;
@@ -2984,6 +3208,7 @@ int hg_pack_best_record(const hg_match_result* r, double* record) {
   record[15] = r->rotational_score;
   record[16] = r->low_resolution_score;
   record[17] = static_cast<double>(r->num_candidates_scored);
+  record[18] = r->order_unresolved;
   return HG_OK;
 }
 
@@ -3001,6 +3226,7 @@ int hg_unpack_best_record(const double* record, hg_match_result* r) {
   r->rotational_score = static_cast<float>(record[15]);
   r->low_resolution_score = static_cast<float>(record[16]);
   r->num_candidates_scored = static_cast<int64_t>(record[17]);
+  r->order_unresolved = static_cast<int32_t>(record[18]);
   return HG_OK;
 }
 
@@ -3039,6 +3265,9 @@ int hg_select_best_record(const double* records, int num_records, int* winner, i
     if (order_unresolved) *order_unresolved = 1;
     if (r[3] < b[3]) *winner = k;
   }
+  // a shard that could not order its own tied leaves passes that on
+  if (*winner >= 0 && order_unresolved && records[static_cast<size_t>(*winner) * HG_BEST_RECORD_DOUBLES + 18] > 0.0)
+    *order_unresolved = 1;
   return HG_OK;
 }
 

@@ -409,6 +409,10 @@ typedef struct hg_match_result {
   /* Score of the best valid leaf the greedy dive found (0 = none): a lower bound on the answer
    * that shards may exchange before the frontier expansion. */
   float dive_bound;
+  /* 1 when the search was one shard of a sweep and several of its leaves tied for the best score
+   * below DIFFERENT lowest-resolution candidates of EQUAL score: their order in the reference is
+   * that of std::sort over the whole (unsharded) list; the earlier generation index was taken. */
+  int32_t order_unresolved;
 } hg_match_result;
 
 /* FastCorrelativeScanMatcher3D(grid, low_resolution_grid, histogram, options)

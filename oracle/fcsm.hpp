@@ -263,18 +263,49 @@ inline std::vector<float> RotateHistogram(const std::vector<float>& histogram, c
   return out;
 }
 
-// Eigen's vectorised float reductions (norm/dot over VectorXf) sum in packet
-// order; restated here as a plain left-to-right sum — see DESIGN.md "unpinned".
-inline float MatchHistograms(const std::vector<float>& submap, const std::vector<float>& scan) {
-  float scan_sq = 0.f, submap_sq = 0.f, dot = 0.f;
-  for (size_t i = 0; i < scan.size(); ++i) {
-    scan_sq += scan[i] * scan[i];
-    submap_sq += submap[i] * submap[i];
-    dot += submap[i] * scan[i];
+// Eigen's sum of n floats term(0) .. term(n-1) over a VectorXf expression
+// (Eigen 3.3 Core/Redux.h, restated from memory — Eigen is not vendored in the reference):
+//   flavor 1, the SSE2 build an x86-64 reference runs: redux_impl<LinearVectorizedTraversal,
+//     NoUnrolling> — packets of 4 floats from the (16-byte aligned) start, two packet accumulators
+//     taking alternate packets, accumulator 0 + accumulator 1, one more packet if an odd number of
+//     packets, then predux (a0 + a2) + (a1 + a3) (arch/SSE/PacketMath.h, SSE2 version), then the
+//     scalar tail;
+//   flavor 0, the generic scalar code: left to right.
+template <typename Term>
+inline float EigenSum(const long n, const Term& term) {
+  if (FloatFlavor::Get() != 1 || n < 4) {
+    float res = term(0);
+    for (long i = 1; i < n; ++i) res = res + term(i);
+    return res;
   }
-  const float normalization = std::sqrt(scan_sq) * std::sqrt(submap_sq);
+  const long aligned_end2 = (n / 8) * 8, aligned_end = (n / 4) * 4;
+  float p0[4], p1[4];
+  for (int k = 0; k < 4; ++k) p0[k] = term(k);
+  if (aligned_end > 4) {
+    for (int k = 0; k < 4; ++k) p1[k] = term(4 + k);
+    for (long index = 8; index < aligned_end2; index += 8) {
+      for (int k = 0; k < 4; ++k) p0[k] = p0[k] + term(index + k);
+      for (int k = 0; k < 4; ++k) p1[k] = p1[k] + term(index + 4 + k);
+    }
+    for (int k = 0; k < 4; ++k) p0[k] = p0[k] + p1[k];
+    if (aligned_end > aligned_end2) {
+      for (int k = 0; k < 4; ++k) p0[k] = p0[k] + term(aligned_end2 + k);
+    }
+  }
+  float res = (p0[0] + p0[2]) + (p0[1] + p0[3]);
+  for (long i = aligned_end; i < n; ++i) res = res + term(i);
+  return res;
+}
+
+// rotational_scan_matcher.cc:121-132: VectorXf::norm() = sqrt(sum of squares), VectorXf::dot().
+inline float MatchHistograms(const std::vector<float>& submap, const std::vector<float>& scan) {
+  const long n = static_cast<long>(scan.size());
+  if (n == 0) return 1.f;
+  const float scan_norm = std::sqrt(EigenSum(n, [&](long i) { return scan[i] * scan[i]; }));
+  const float submap_norm = std::sqrt(EigenSum(n, [&](long i) { return submap[i] * submap[i]; }));
+  const float normalization = scan_norm * submap_norm;
   if (normalization < 1e-3f) return 1.f;
-  return dot / normalization;
+  return EigenSum(n, [&](long i) { return submap[i] * scan[i]; }) / normalization;
 }
 
 inline std::vector<float> RotationalMatch(const std::vector<float>& submap_histogram,

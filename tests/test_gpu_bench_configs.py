@@ -1,0 +1,285 @@
+"""GPU parity on the configurations bench.py times (C3, C4, C5), against the CPU oracle run
+on the box's host cores and against the oracle's frozen answers under tests/golden/c4_golden.json
+(tests/golden/make_c4_golden.py). Bars: integer candidate sums and the selected candidate bit-exact,
+solved pose within 1e-4."""
+import json
+import os
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MATCH_KEYS = ["found", "score", "scan_index", "ox", "oy", "oz", "low_resolution_score", "rotational_score"]
+
+
+@pytest.fixture(scope="module")
+def hg():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    import hectorgrapher_b200 as hg
+    hg.lib()
+    return hg
+
+
+@pytest.fixture(scope="module")
+def bench_world(oracle, hg):
+    import bench
+    w = bench.build_workload(num_scans=1, points_per_scan=1000)
+    o_hi = oracle.Grid.tsdf(bench.HI_RES, bench.REL_TRUNC, bench.MAX_WEIGHT)
+    o_hi.set_raw(*w["hi"])
+    o_lo = oracle.Grid.tsdf(bench.LO_RES, bench.REL_TRUNC, bench.MAX_WEIGHT)
+    o_lo.set_raw(*w["lo"])
+    g_hi = hg.Grid.tsdf(bench.HI_RES, bench.REL_TRUNC, bench.MAX_WEIGHT, *w["hi"], grid_size=o_hi.grid_size)
+    g_lo = hg.Grid.tsdf(bench.LO_RES, bench.REL_TRUNC, bench.MAX_WEIGHT, *w["lo"], grid_size=o_lo.grid_size)
+    with open(os.path.join(ROOT, "tests", "golden", "c4_golden.json")) as f:
+        golden = json.load(f)
+    return dict(bench=bench, w=w, o_hi=o_hi, o_lo=o_lo, g_hi=g_hi, g_lo=g_lo, golden=golden)
+
+
+def same(r, want, keys=MATCH_KEYS):
+    for k in keys:
+        assert np.float32(r[k]) == np.float32(want[k]), (k, r[k], want[k])
+
+
+def test_c4_full_sweep_as_benchmarked(oracle, hg, bench_world):
+    """bench.correlative_inputs exactly as timed (N = 2048, 1633 discrete scans, 8.02 M lowest-resolution
+    candidates): (1) every lattice sum of the GPU equals the oracle's ScoreCandidates (all host threads);
+    (2) the residue-row lattice kernel equals the brick-table kernel on every sum (HG_LATTICE_CHECK in the
+    host-replay search); (3) device-resident search = host replay = the oracle's MatchFullSubmap (frozen);
+    (4) sharded over 2 and 8 with the bound exchange and the best-record reduce: same answer."""
+    b, w = bench_world["bench"], bench_world["w"]
+    ci = b.correlative_inputs(w, rotational=False)
+    gm = hg.Fcsm(bench_world["g_hi"], bench_world["g_lo"], ci["submap_hist"], **ci["opts"])
+    om = oracle.Fcsm(bench_world["o_hi"], bench_world["o_lo"], ci["submap_hist"], **ci["opts"])
+    want = bench_world["golden"]["full_sweep"]
+    r = gm.match(ci["node"], ci["submap"], ci["high"], ci["low"], ci["hist"], min_score=ci["min_score"], full=True)
+    same(r, want)
+    assert r["num_scans"] == want["num_scans"] and r["num_lattice"] == 8022929
+    # (1) the whole lattice, generation order: scan, z, y, x with step 64
+    wxy = (bench_world["o_hi"].grid_size + 1) // 2 + int(np.floor(np.linalg.norm(ci["high"], axis=1).max() / b.HI_RES + 0.5 + 0.5))
+    step, S = 64, int(r["num_scans"])
+    n1 = (2 * wxy + step) // step
+    assert S * n1 ** 3 == r["num_lattice"]
+    axis = -wxy + step * np.arange(n1)
+    zz, yy, xx = np.meshgrid(axis, axis, axis, indexing="ij")
+    per_scan = np.stack([xx.ravel(), yy.ravel(), zz.ravel()], 1)
+    threads = os.cpu_count() or 8
+    rng = np.random.RandomState(5)
+    scans = sorted(set([0, S - 1, int(want["scan_index"])] + list(rng.choice(S, 160, replace=False))))
+    for chunk in np.array_split(np.array(scans), 8):
+        cand = np.concatenate([np.concatenate([np.full((len(per_scan), 1), s), per_scan], 1) for s in chunk]).astype(np.int32)
+        gs, _, _ = gm.score_candidates(wxy, wxy, np.pi, ci["node"], ci["submap"], ci["high"], ci["hist"], 6, cand)
+        os_, _, _ = om.score_candidates(wxy, wxy, np.pi, ci["node"], ci["submap"], ci["high"], ci["hist"], 6, cand,
+                                        threads=threads)
+        assert (np.asarray(gs) == np.asarray(os_)).all()
+    # (2) + (3)
+    os.environ["HG_SEARCH_HOST_REPLAY"] = "1"
+    os.environ["HG_LATTICE_CHECK"] = "1"
+    try:
+        rh = gm.match(ci["node"], ci["submap"], ci["high"], ci["low"], ci["hist"], min_score=ci["min_score"], full=True)
+    finally:
+        os.environ.pop("HG_SEARCH_HOST_REPLAY", None)
+        os.environ.pop("HG_LATTICE_CHECK", None)
+    same(rh, want)
+    # (4)
+    from hectorgrapher_b200 import capi
+    for shards in (2, 8):
+        # the two phases of one shard must be adjacent on a thread: run the shards one after the other,
+        # first collecting the bounds (begin + finish under the own bound), then again under the common bound
+        bounds = []
+        for k in range(shards):
+            h, bound = gm.full_submap_begin(ci["node"][3:], ci["submap"][3:], ci["high"], ci["low"], ci["hist"],
+                                            min_score=ci["min_score"], shard_index=k, num_shards=shards)
+            gm.full_submap_finish(h, bound)
+            bounds.append(bound)
+        common = max(bounds)
+        assert common > ci["min_score"]
+        records = []
+        for k in range(shards):
+            h, _ = gm.full_submap_begin(ci["node"][3:], ci["submap"][3:], ci["high"], ci["low"], ci["hist"],
+                                        min_score=ci["min_score"], shard_index=k, num_shards=shards)
+            records.append(capi.pack_best_record(gm.full_submap_finish(h, common)))
+        best, unresolved = capi.select_best_record(np.stack(records))
+        assert not unresolved
+        same(best, want, ["found", "score", "scan_index", "ox", "oy", "oz", "low_resolution_score"])
+
+
+def test_c4_configured_as_benchmarked(oracle, hg, bench_world):
+    """C4 with the rotational prefilter at min_rotational_score 0.77: same discrete scans kept, same candidate."""
+    b, w = bench_world["bench"], bench_world["w"]
+    ci = b.correlative_inputs(w, rotational=True)
+    gm = hg.Fcsm(bench_world["g_hi"], bench_world["g_lo"], ci["submap_hist"], **ci["opts"])
+    want = bench_world["golden"]["configured"]
+    r = gm.match(ci["node"], ci["submap"], ci["high"], ci["low"], ci["hist"], min_score=ci["min_score"], full=True)
+    same(r, want)
+    assert r["num_scans"] == want["num_scans"]
+
+
+def test_c3_as_benchmarked(oracle, hg, bench_world):
+    """C3 as SURVEY 8(d) writes it (pose_graph.lua:20, 40-49 thresholds): 100 seeded offsets at N = 2048 against
+    the oracle's frozen answers, single searches and the batched search; 10 offsets at N = 20480 (the lattice
+    kernel's N > 8192 variant, full window) against the oracle run here."""
+    b, w = bench_world["bench"], bench_world["w"]
+    ci = b.correlative_inputs(w, rotational=True)
+    gm = hg.Fcsm(bench_world["g_hi"], bench_world["g_lo"], ci["submap_hist"], **ci["opts"])
+    offsets = b.local_search_offsets(ci, 100)
+    rows = bench_world["golden"]["c3"]["rows"]
+    keys = bench_world["golden"]["c3"]["keys"]
+    nodes = [(ci["high"], ci["low"], ci["hist"])] * len(offsets)
+    batch = gm.match_batch(offsets, [ci["submap"]] * len(offsets), nodes, min_score=ci["min_score"])
+    found = 0
+    for k, (node, row) in enumerate(zip(offsets, rows)):
+        want = dict(zip(keys, row))
+        assert batch[k]["found"] == want["found"]
+        if want["found"]:
+            same(batch[k], want)
+            found += 1
+        if k % 10 == 0:
+            single = gm.match(node, ci["submap"], ci["high"], ci["low"], ci["hist"], min_score=ci["min_score"])
+            assert single["found"] == want["found"]
+            if want["found"]:
+                same(single, want)
+    assert found >= 90
+    big = b.correlative_inputs(w, rotational=True, num_points=20480)
+    assert len(big["high"]) == 20480
+    gm2 = hg.Fcsm(bench_world["g_hi"], bench_world["g_lo"], big["submap_hist"], **big["opts"])
+    om2 = oracle.Fcsm(bench_world["o_hi"], bench_world["o_lo"], big["submap_hist"], **big["opts"])
+    offs = b.local_search_offsets(big, 10)
+    got = gm2.match_batch(offs, [big["submap"]] * 10, [(big["high"], big["low"], big["hist"])] * 10,
+                          min_score=big["min_score"])
+    with ThreadPoolExecutor(10) as ex:
+        exp = list(ex.map(lambda nd: om2.match(nd, big["submap"], big["high"], big["low"], big["hist"],
+                                               min_score=big["min_score"]), offs))
+    hits = 0
+    for r, want in zip(got, exp):
+        assert r["found"] == want["found"]
+        if want["found"]:
+            same(r, want)
+            hits += 1
+    assert hits >= 8
+    # a full-submap search at N = 20480 exercises the residue-row kernel's 32-bit accumulator variant
+    os.environ["HG_LATTICE_CHECK"] = "1"
+    os.environ["HG_SEARCH_HOST_REPLAY"] = "1"
+    try:
+        sweep = dict(big["opts"])
+        sweep["angular_search_window"] = 0.05
+        gm3 = hg.Fcsm(bench_world["g_hi"], bench_world["g_lo"], big["submap_hist"], **sweep)
+        r = gm3.match(offs[0], big["submap"], big["high"], big["low"], big["hist"], min_score=big["min_score"])
+        assert np.isfinite(r["score"])
+    finally:
+        os.environ.pop("HG_LATTICE_CHECK", None)
+        os.environ.pop("HG_SEARCH_HOST_REPLAY", None)
+
+
+def test_c5_constraints_against_the_oracle(oracle, hg, bench_world):
+    """C5 as benchmarked, 8 submaps x 26 nodes = 208 pairs: every constraint of the grouped device path (one
+    search + one refine launch per group) equals the oracle's Match followed by the oracle's refine — same
+    candidate score, pose within 1e-4 — and equals the pair-at-a-time path bit for bit."""
+    b = bench_world["bench"]
+    synth, sph = bench_world["w"]["synth"], bench_world["w"]["sph"]
+    hist = np.zeros(8, np.float32)
+    empty = np.zeros((0, 3), np.int32)
+    num_submaps, nodes = 8, 26
+    matchers, g_his, g_los, jobs, oracles = [], [], [], [], []
+    for s in range(num_submaps):
+        origin, yaw, scans, high, low = b.c5_submap_inputs(synth, sph, s, num_submaps)
+        g_hi = hg.Grid.tsdf(b.HI_RES, b.REL_TRUNC, b.MAX_WEIGHT, empty, [], [])
+        g_lo = hg.Grid.tsdf(b.LO_RES, b.REL_TRUNC, b.MAX_WEIGHT, empty, [], [])
+        o_hi = oracle.Grid.tsdf(b.HI_RES, b.REL_TRUNC, b.MAX_WEIGHT)
+        o_lo = oracle.Grid.tsdf(b.LO_RES, b.REL_TRUNC, b.MAX_WEIGHT)
+        for o, pts in scans:
+            for g in (g_hi, g_lo, o_hi, o_lo):
+                g.insert_tsdf(o, pts, **b.C5_INSERTER)
+        g_his.append(g_hi)
+        g_los.append(g_lo)
+        matchers.append(hg.Fcsm(g_hi, g_lo, hist, **b.C5_FCSM_OPTIONS))
+        oracles.append((oracle.Fcsm(o_hi, o_lo, hist, **b.C5_FCSM_OPTIONS), o_hi, o_lo))
+        jobs += b.c5_jobs(synth, s, s, origin, yaw, high, low, hist, nodes)
+    res = hg.constraints_run_batch(matchers, g_his, g_los, jobs, b.C5_OPTIONS)
+    # the pair-at-a-time path, reached through single-pair batches
+    singles = [hg.constraints_run_batch(matchers, g_his, g_los, [jobs[j]], b.C5_OPTIONS)[0] for j in range(0, len(jobs), 13)]
+    for k, j in enumerate(range(0, len(jobs), 13)):
+        assert singles[k]["found"] == res[j]["found"] and singles[k]["score"] == res[j]["score"]
+        assert np.abs(singles[k]["pose"] - res[j]["pose"]).max() < 1e-9
+
+    def reference(j):
+        job = jobs[j]
+        om, o_hi, o_lo = oracles[job["submap_index"]]
+        r0 = om.match(job["node_pose"], job["submap_pose"], job["high"], job["low"], hist,
+                      min_score=b.C5_OPTIONS["min_score"])
+        if not r0["found"]:
+            return r0, None
+        init = np.array([r0[k] for k in ["tx", "ty", "tz", "qw", "qx", "qy", "qz"]])
+        pose, _, _ = oracle.scan_match([job["high"], job["low"]], [o_hi, o_lo], b.C5_OPTIONS["occupied_space_weights"],
+                                       b.C5_OPTIONS["translation_weight"], b.C5_OPTIONS["rotation_weight"], init,
+                                       max_num_iterations=b.C5_OPTIONS["max_num_iterations"],
+                                       use_nonmonotonic_steps=False)
+        return r0, pose
+
+    with ThreadPoolExecutor(os.cpu_count() or 8) as ex:
+        refs = list(ex.map(reference, range(len(jobs))))
+    found = 0
+    for j, (r0, pose) in enumerate(refs):
+        assert res[j]["found"] == int(r0["found"]), j
+        if not r0["found"]:
+            continue
+        found += 1
+        assert res[j]["score"] == np.float32(r0["score"])
+        assert np.abs(res[j]["pose"][:3] - pose[:3]).max() < 1e-4
+        assert min(np.abs(res[j]["pose"][3:] - pose[3:]).max(), np.abs(res[j]["pose"][3:] + pose[3:]).max()) < 1e-4
+    assert found >= 200
+
+
+def test_equal_scores_across_shards_follow_the_reference_order(oracle, hg):
+    """Scores are sums / N quantised, so two discrete scans in different shards can hold leaves of exactly the
+    same score. The reference keeps the first one its search meets, i.e. the one below the higher-scoring
+    lowest-resolution candidate (fast_correlative_scan_matcher_3d.cc:384, 437-440, 465-466). Small seeded worlds
+    with few points and few distinct voxel values make such ties common; wherever the rule decides (different
+    ancestor scores) the sharded search + hg_select_best_record must return the unsharded oracle's candidate."""
+    from hectorgrapher_b200 import capi
+    opts = dict(branch_and_bound_depth=2, full_resolution_depth=2, use_rotational_scan_matcher=False,
+                min_low_resolution_score=0.0, linear_xy_search_window=2.0, linear_z_search_window=1.0,
+                angular_search_window=0.3)
+    ident = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    hist = np.zeros(4, np.float32)
+    decided = undecided = no_tie = 0
+    for seed in range(60):
+        rng = np.random.RandomState(1000 + seed)
+        cells = np.stack(np.meshgrid(np.arange(-10, 11), np.arange(-10, 11), np.arange(-2, 3), indexing="ij"), -1).reshape(-1, 3)
+        probs = rng.choice([0.15, 0.3, 0.45, 0.6, 0.75, 0.9], size=len(cells), p=[0.6, 0.2, 0.1, 0.06, 0.03, 0.01])
+        og = oracle.Grid.prob(0.5)
+        og.set_probability(cells.astype(np.int32), probs)
+        ex, ev = og.export()
+        gg = hg.Grid.prob(0.5, ex, ev, grid_size=og.grid_size)
+        cloud = (rng.uniform(-1, 1, (3, 3)) * np.array([3.0, 3.0, 0.6])).astype(np.float32)
+        om = oracle.Fcsm(og, og, hist, **opts)
+        gm = hg.Fcsm(gg, gg, hist, **opts)
+        r0 = om.match(ident, ident, cloud, cloud, hist, min_score=0.15, full=True)
+        whole = gm.match(ident, ident, cloud, cloud, hist, min_score=0.15, full=True)
+        for k in ["found", "score", "scan_index", "ox", "oy", "oz"]:
+            assert np.float32(whole[k]) == np.float32(r0[k]), (seed, k, whole[k], r0[k])
+        if not r0["found"]:
+            continue
+        shard_results = []
+        for k in range(2):
+            h, bound = gm.full_submap_begin(ident[3:], ident[3:], cloud, cloud, hist, min_score=0.15, shard_index=k,
+                                            num_shards=2)
+            shard_results.append(gm.full_submap_finish(h, bound))
+        best, unresolved = capi.select_best_record(np.stack([capi.pack_best_record(r) for r in shard_results]))
+        assert best is not None and np.float32(best["score"]) == np.float32(r0["score"])
+        tie = all(r["found"] for r in shard_results) and shard_results[0]["score"] == shard_results[1]["score"]
+        if unresolved:
+            # equal leaves below equal-scoring lowest-resolution candidates (across the shards, or inside the
+            # winning shard): only std::sort over the unsharded list orders those; flagged, not asserted
+            undecided += 1
+            continue
+        if tie:
+            decided += 1
+        else:
+            no_tie += 1
+        for k in ["scan_index", "ox", "oy", "oz"]:
+            assert np.float32(best[k]) == np.float32(r0[k]), (seed, k, best, r0)
+    assert decided >= 3, (decided, undecided, no_tie)
