@@ -9,5 +9,5 @@ present, calls fail loudly.
 from . import capi  # noqa: F401
 from .capi import (  # noqa: F401
     Batch, ConstraintBatch, Cost, Fcsm, Grid, HgError, PbStream, Stack, build, grid_proto_decode, constraints_run_batch, get_cell_index,
-    adaptive_voxel_filter, kernel_launch_count, lib, low_resolution_scores, scan_match, set_device, voxel_filter,
+    adaptive_voxel_filter, kernel_launch_count, lib, low_resolution_scores, scan_match, scan_match_evaluate, set_device, voxel_filter,
 )

@@ -120,6 +120,7 @@ SYMBOLS = {
     "hg_batch_evaluate": (c_i, [vp, vp, c_i, vp, vp, c_i, vp, vp, vp, vp, vp, vp]),
     "hg_batch_normal_equations": (c_i, [vp, vp, c_i, vp, vp, vp, vp, vp]),
     "hg_batch_level_usage": (c_i, [vp, vp, c_i, vp, vp, vp]),
+    "hg_scan_match_evaluate": (c_i, [c_i, vp, vp, vp, vp, c_d, c_d, c_i, vp, vp, vp, vp, vp]),
     "hg_scan_match": (c_i, [c_i, vp, vp, vp, vp, c_d, c_d, c_i, c_i, c_i, vp, vp, vp, vp]),
     "hg_stack_build": (c_i, [vp, c_i, c_i, vp]),
     "hg_stack_destroy": (None, [vp]),
@@ -520,6 +521,24 @@ def scan_match(clouds, grids, weights, translation_weight, rotation_weight, init
                                max_num_iterations, int(use_nonmonotonic_steps), _p(target), _p(initial_pose),
                                _p(pose), _p(summary)))
     return pose, summary
+
+
+def scan_match_evaluate(clouds, grids, weights, translation_weight, rotation_weight, pose, target_translation=None,
+                        only_optimize_yaw=False):
+    """hg_scan_match_evaluate (CeresScanMatcher3D::Evaluate): (cost, residuals, gradient in the tangent space)."""
+    clouds = [_f32(c).reshape(-1, 3) for c in clouds]
+    carr = (vp * len(clouds))(*[c.ctypes.data for c in clouds])
+    sizes = _i32([len(c) for c in clouds])
+    weights = _f64(weights)
+    pose = _f64(pose)
+    target = _f64(pose[:3] if target_translation is None else target_translation)
+    cost = np.zeros(1)
+    r = np.zeros(int(sizes.sum()) + 6)
+    g = np.zeros(4 if only_optimize_yaw else 6)
+    _check(lib().hg_scan_match_evaluate(len(clouds), carr, _p(sizes), _grid_array(grids), _p(weights),
+                                        translation_weight, rotation_weight, int(only_optimize_yaw), _p(target),
+                                        _p(pose), _p(cost), _p(r), _p(g)))
+    return float(cost[0]), r, g
 
 
 class Stack:

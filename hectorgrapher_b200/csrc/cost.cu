@@ -1137,6 +1137,59 @@ extern "C" int hg_scan_match(int num_clouds, const float* const* clouds, const i
   return HG_OK;
 }
 
+// CeresScanMatcher3D::Evaluate (ceres_scan_matcher_3d.cc:97-118): the same problem as Match,
+// evaluated once at the initial pose — cost, all residuals (clouds in order, then the translation
+// and rotation deltas), and what the reference asks ceres::Problem::Evaluate for in its fourth
+// argument, which is the GRADIENT of the cost in the tangent space of the pose.
+extern "C" int hg_scan_match_evaluate(int num_clouds, const float* const* clouds, const int32_t* cloud_sizes,
+                                      const hg_grid* const* grids, const double* occupied_space_weights,
+                                      double translation_weight, double rotation_weight, int only_optimize_yaw,
+                                      const double* target_translation, const double* initial_pose, double* cost,
+                                      double* residuals, double* gradient) {
+  HG_REQUIRE(num_clouds >= 1 && clouds && cloud_sizes && grids && occupied_space_weights && initial_pose &&
+                 target_translation,
+             "hg_scan_match_evaluate: bad arguments");
+  double t[3] = {initial_pose[0], initial_pose[1], initial_pose[2]};
+  double q[4] = {initial_pose[3], initial_pose[4], initial_pose[5], initial_pose[6]};
+  hg::DenseLmProblem<LmCost> problem;
+  const int tb = problem.AddParameterBlock(t, 3, hg::LocalParameterization::kIdentity);
+  const int qb = problem.AddParameterBlock(q, 4, only_optimize_yaw ? hg::LocalParameterization::kYawOnlyQuaternion
+                                                                   : hg::LocalParameterization::kQuaternion);
+  std::vector<std::unique_ptr<LmCost>> owned;
+  for (int i = 0; i < num_clouds; ++i) {
+    HG_REQUIRE(occupied_space_weights[i] > 0., "hg_scan_match_evaluate: occupied_space_weight must be > 0");
+    HG_REQUIRE(cloud_sizes[i] > 0 && clouds[i] != nullptr && grids[i] != nullptr,
+               "hg_scan_match_evaluate: empty point cloud");
+    const double scaling = occupied_space_weights[i] / std::sqrt(static_cast<double>(cloud_sizes[i]));
+    hg_cost* c = nullptr;
+    const int kind = grids[i]->dev.kind == kGridProb ? HG_COST_OCCUPIED_SPACE : HG_COST_TSDF_SPACE;
+    const int rc = hg_cost_create(kind, scaling, clouds[i], 3, cloud_sizes[i], &grids[i], 1, 0.0, &c);
+    if (rc != HG_OK) return rc;
+    c->batch->stream = ThreadStream();
+    owned.emplace_back(new GpuScanCost(c));
+    problem.AddResidualBlock(owned.back().get(), {tb, qb});
+  }
+  owned.emplace_back(new TranslationDelta(translation_weight, target_translation));
+  problem.AddResidualBlock(owned.back().get(), {tb});
+  owned.emplace_back(new RotationDelta(rotation_weight, initial_pose + 3));
+  problem.AddResidualBlock(owned.back().get(), {qb});
+  double c = 0.0;
+  std::vector<double> r, J;
+  if (!problem.Evaluate(&c, &r, &J)) {
+    SetError(std::string("hg_scan_match_evaluate: evaluation failed: ") + hg_last_error());
+    return HG_ERR_CUDA;
+  }
+  if (cost != nullptr) *cost = c;
+  if (residuals != nullptr) std::copy(r.begin(), r.end(), residuals);
+  if (gradient != nullptr) {
+    const int n = problem.NumLocalParameters();
+    for (int k = 0; k < n; ++k) gradient[k] = 0.0;
+    for (size_t i = 0; i < r.size(); ++i)
+      for (int k = 0; k < n; ++k) gradient[k] += J[i * n + k] * r[i];
+  }
+  return HG_OK;
+}
+
 // ---------------------------------------------------------------------------
 // hg_cost_normal_equations_static — the Gauss-Newton terms of one residual
 // block computed with NO allocation of any kind at call time.

@@ -19,6 +19,8 @@
 #pragma once
 
 #include <array>
+#include <cmath>
+#include <cstdint>
 #include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
@@ -384,6 +386,42 @@ class CeresScanMatcher3D {
     }
   }
 
+  // ceres_scan_matcher_3d.cc:97-118: the assembled problem evaluated at the initial pose. The reference
+  // hands its 'jacobians' vector to ceres::Problem::Evaluate as the GRADIENT argument: it receives the
+  // gradient of the cost in the tangent space of the pose (3 translation + 3 rotation entries, or 3 + 1
+  // with only_optimize_yaw), not a Jacobian. 'residuals': every cloud's residuals, then the translation
+  // and rotation deltas (3 + 3).
+  void Evaluate(const std::array<double, 3>& target_translation, const Rigid3d& initial_pose_estimate,
+                const std::vector<PointCloudAndHybridGridPointers>& point_clouds_and_hybrid_grids, double* cost,
+                std::vector<double>* residuals, std::vector<double>* jacobians) const {
+    const int n = static_cast<int>(point_clouds_and_hybrid_grids.size());
+    if (static_cast<int>(options_.occupied_space_weight.size()) != n) {
+      std::fprintf(stderr, "[hg_b200] occupied_space_weight count != number of point clouds\n");
+      std::abort();
+    }
+    std::vector<const float*> clouds;
+    std::vector<int32_t> sizes;
+    std::vector<const hg_grid*> grids;
+    size_t num_residuals = 6;
+    for (const auto& p : point_clouds_and_hybrid_grids) {
+      clouds.push_back(p.first.data);
+      sizes.push_back(p.first.size);
+      grids.push_back(p.second->get());
+      num_residuals += static_cast<size_t>(p.first.size);
+    }
+    double init[7], c = 0.;
+    initial_pose_estimate.ToArray(init);
+    std::vector<double> r(num_residuals), g(options_.only_optimize_yaw ? 4 : 6);
+    CheckOk(hg_scan_match_evaluate(n, clouds.data(), sizes.data(), grids.data(), options_.occupied_space_weight.data(),
+                                   options_.translation_weight, options_.rotation_weight,
+                                   options_.only_optimize_yaw ? 1 : 0, target_translation.data(), init, &c, r.data(),
+                                   g.data()),
+            "hg_scan_match_evaluate");
+    if (cost != nullptr) *cost = c;
+    if (residuals != nullptr) *residuals = r;
+    if (jacobians != nullptr) *jacobians = g;
+  }
+
  private:
   const CeresScanMatcherOptions3D options_;
 };
@@ -474,8 +512,34 @@ class FastCorrelativeScanMatcher3D {
 // ConstraintBuilder3D (constraint_builder_3d.h:51-114), compute side. Pairs are queued by
 // MaybeAddConstraint / MaybeAddGlobalConstraint and computed by a background worker in batches
 // through hg_constraints_run_batch; WhenDone's callback receives the non-null constraints, like
-// RunWhenDoneCallback (constraint_builder_3d.cc:297-323). The distance gate and the sampler of
-// MaybeAddConstraint (:82-86) are the caller's (they need no GPU).
+// RunWhenDoneCallback (constraint_builder_3d.cc:297-323). MaybeAddConstraint applies the distance
+// gate and the sampler of the reference (:82-86) before anything is queued.
+
+// common::FixedRatioSampler (common/fixed_ratio_sampler.cc:23-43).
+class FixedRatioSampler {
+ public:
+  explicit FixedRatioSampler(double ratio) : ratio_(ratio) {
+    if (!(ratio >= 0.) || !(ratio <= 1.)) {
+      std::fprintf(stderr, "[hg_b200] FixedRatioSampler: ratio must be in [0, 1]\n");  // CHECK_GE / CHECK_LE
+      std::abort();
+    }
+    if (ratio == 0.) std::fprintf(stderr, "[hg_b200] FixedRatioSampler is dropping all data.\n");
+  }
+  bool Pulse() {
+    ++num_pulses_;
+    if (static_cast<double>(num_samples_) / num_pulses_ < ratio_) {
+      ++num_samples_;
+      return true;
+    }
+    return false;
+  }
+
+ private:
+  const double ratio_;
+  int64_t num_pulses_ = 0;
+  int64_t num_samples_ = 0;
+};
+
 class ConstraintBuilder3D {
  public:
   struct SubmapId { int trajectory_id; int submap_index; };
@@ -494,9 +558,18 @@ class ConstraintBuilder3D {
     hg_fcsm_options fast_correlative_scan_matcher_options_3d;
     double loop_closure_translation_weight = 1.1e4;
     double loop_closure_rotation_weight = 1e5;
+    // constraint_builder options (configuration_files/pose_graph.lua:18-19)
+    double max_constraint_distance = 15.;
+    double sampling_ratio = 0.3;
+    // One process per GPU, every rank receiving the same sequence of MaybeAdd(Global)Constraint calls: this
+    // builder computes the accepted pairs number shard_index, shard_index + num_shards, ... of that sequence
+    // (0 / 1 = all); the ranks gather their constraints at WhenDone (fixed-size records).
+    int shard_index = 0;
+    int num_shards = 1;
   };
 
-  explicit ConstraintBuilder3D(const Options& options) : options_(options), worker_([this] { Work(); }) {}
+  explicit ConstraintBuilder3D(const Options& options)
+      : options_(options), sampler_(options.sampling_ratio), worker_([this] { Work(); }) {}
   ~ConstraintBuilder3D() {
     {
       std::unique_lock<std::mutex> lock(mu_);
@@ -533,6 +606,17 @@ class ConstraintBuilder3D {
   void MaybeAddConstraint(const SubmapId& submap_id, const NodeId& node_id,
                           const TrajectoryNodeData* constant_data, const Rigid3d& global_node_pose,
                           const Rigid3d& global_submap_pose) {
+    // constraint_builder_3d.cc:82-86
+    double d2 = 0.;
+    for (int k = 0; k < 3; ++k) {
+      const double d = global_node_pose.translation[k] - global_submap_pose.translation[k];
+      d2 += d * d;
+    }
+    if (std::sqrt(d2) > options_.max_constraint_distance) return;
+    {
+      std::unique_lock<std::mutex> lock(sampler_mu_);
+      if (!sampler_.Pulse()) return;
+    }
     Enqueue(submap_id, node_id, constant_data, global_node_pose, global_submap_pose, false);
   }
   void MaybeAddGlobalConstraint(const SubmapId& submap_id, const NodeId& node_id,
@@ -580,10 +664,11 @@ class ConstraintBuilder3D {
                const Rigid3d& sp, bool full) {
     {
       std::unique_lock<std::mutex> lock(mu_);
-      if (when_done_) {
-        std::fprintf(stderr, "[hg_b200] MaybeAddConstraint after WhenDone\n");  // :88-91
-        std::abort();
+      if (when_done_) {  // :88-91, :119-122: a warning, the constraint is still computed
+        std::fprintf(stderr, "[hg_b200] MaybeAddConstraint was called while WhenDone was scheduled.\n");
       }
+      const int64_t sequence = next_sequence_++;
+      if (sequence % options_.num_shards != options_.shard_index) return;  // another rank computes this pair
       pending_.push_back(Pending{s, n, d, np, sp, full});
     }
     cv_.notify_all();
@@ -670,6 +755,8 @@ class ConstraintBuilder3D {
   }
 
   const Options options_;
+  std::mutex sampler_mu_;
+  FixedRatioSampler sampler_;
   std::mutex mu_;
   std::condition_variable cv_;
   std::deque<Pending> pending_;
@@ -677,6 +764,7 @@ class ConstraintBuilder3D {
   Result constraints_;
   std::unique_ptr<std::function<void(const Result&)>> when_done_;
   int num_finished_nodes_ = 0;
+  int64_t next_sequence_ = 0;
   bool busy_ = false;
   bool stop_ = false;
   std::thread worker_;  // last member: starts after everything above is constructed

@@ -333,6 +333,18 @@ int hg_scan_match(int num_clouds, const float* const* clouds, const int32_t* clo
                   const double* target_translation, const double* initial_pose, double* pose_out,
                   double* summary_out);
 
+/* CeresScanMatcher3D::Evaluate (ceres_scan_matcher_3d.cc:97-118): the problem of hg_scan_match
+ * evaluated once at 'initial_pose'. cost = 1/2 |r|^2; residuals (may be NULL): sum of the cloud
+ * sizes + 6 doubles — every cloud's residuals in order, then the translation and the rotation
+ * delta; gradient (may be NULL): 6 doubles (4 with only_optimize_yaw), the gradient of the cost in
+ * the tangent space of (translation, rotation) — what the reference's call receives, because it
+ * passes its 'jacobians' vector as ceres::Problem::Evaluate's gradient argument. */
+int hg_scan_match_evaluate(int num_clouds, const float* const* clouds, const int32_t* cloud_sizes,
+                           const hg_grid* const* grids, const double* occupied_space_weights,
+                           double translation_weight, double rotation_weight, int only_optimize_yaw,
+                           const double* target_translation, const double* initial_pose, double* cost,
+                           double* residuals, double* gradient);
+
 /* ------------------------------------------------ precomputation grids -- */
 
 /* PrecomputationGridStack3D(grid, options)

@@ -371,6 +371,49 @@ int orc_scan_match_trace(int num_clouds, const float* const* clouds, const int* 
   return s.termination;
 }
 
+// ---- CeresScanMatcher3D::Evaluate (ceres_scan_matcher_3d.cc:97-118): cost, residuals and the gradient
+// in the tangent space (the reference passes its 'jacobians' vector as Problem::Evaluate's gradient).
+int orc_scan_match_evaluate(int num_clouds, const float* const* clouds, const int* cloud_sizes, void* const* grids,
+                            const double* occupied_space_weights, double translation_weight, double rotation_weight,
+                            int only_optimize_yaw, const double* target_translation, const double* initial_pose,
+                            double* cost, double* residuals, double* gradient) {
+  double t[3] = {initial_pose[0], initial_pose[1], initial_pose[2]};
+  double q[4] = {initial_pose[3], initial_pose[4], initial_pose[5], initial_pose[6]};
+  hg::DenseLmProblem<CostFunction> problem;
+  const int tb = problem.AddParameterBlock(t, 3, hg::LocalParameterization::kIdentity);
+  const int qb = problem.AddParameterBlock(
+      q, 4, only_optimize_yaw ? hg::LocalParameterization::kYawOnlyQuaternion : hg::LocalParameterization::kQuaternion);
+  std::vector<std::unique_ptr<CostFunction>> owned;
+  for (int i = 0; i < num_clouds; ++i) {
+    auto* h = static_cast<GridHandle*>(grids[i]);
+    CloudView cloud;
+    cloud.data = clouds[i];
+    cloud.n = cloud_sizes[i];
+    cloud.stride = 3;
+    const double scaling = occupied_space_weights[i] / std::sqrt(static_cast<double>(cloud.n));
+    if (h->prob) {
+      owned.emplace_back(new ScanCostFunction(kOccupiedSpace, scaling, cloud, h->prob.get(), {}, 0.));
+    } else {
+      owned.emplace_back(new ScanCostFunction(kTSDFSpace, scaling, cloud, nullptr, {h->tsdf.get()}, 0.));
+    }
+    problem.AddResidualBlock(owned.back().get(), {tb, qb});
+  }
+  owned.emplace_back(new TranslationDeltaCostFunction(translation_weight, target_translation));
+  problem.AddResidualBlock(owned.back().get(), {tb});
+  owned.emplace_back(new RotationDeltaCostFunction(rotation_weight, initial_pose + 3));
+  problem.AddResidualBlock(owned.back().get(), {qb});
+  double c = 0.0;
+  std::vector<double> r, J;
+  if (!problem.Evaluate(&c, &r, &J)) return 1;
+  *cost = c;
+  std::copy(r.begin(), r.end(), residuals);
+  const int n = problem.NumLocalParameters();
+  for (int k = 0; k < n; ++k) gradient[k] = 0.0;
+  for (size_t i = 0; i < r.size(); ++i)
+    for (int k = 0; k < n; ++k) gradient[k] += J[i * n + k] * r[i];
+  return 0;
+}
+
 // ---- precomputation stack ---------------------------------------------------
 void* orc_stack_new(void* grid, int branch_and_bound_depth, int full_resolution_depth) {
   auto* h = static_cast<GridHandle*>(grid);

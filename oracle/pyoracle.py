@@ -349,6 +349,27 @@ def scan_match(clouds, grids, weights, translation_weight, rotation_weight, init
     return pose, summary, term
 
 
+def scan_match_evaluate(clouds, grids, weights, translation_weight, rotation_weight, pose, target_translation=None,
+                        only_optimize_yaw=False):
+    """CeresScanMatcher3D::Evaluate: (cost, residuals, gradient in the tangent space)."""
+    clouds = [_f32(c).reshape(-1, 3) for c in clouds]
+    carr = (vp * len(clouds))(*[c.ctypes.data for c in clouds])
+    sizes = _i32([len(c) for c in clouds])
+    garr = (vp * len(grids))(*[g.h for g in grids])
+    weights = _f64(weights)
+    pose = _f64(pose)
+    target = _f64(pose[:3] if target_translation is None else target_translation)
+    cost = np.zeros(1)
+    r = np.zeros(int(sizes.sum()) + 6)
+    g = np.zeros(4 if only_optimize_yaw else 6)
+    f = lib().orc_scan_match_evaluate
+    f.argtypes = [c_i, vp, vp, vp, vp, c_d, c_d, c_i, vp, vp, vp, vp, vp]
+    rc = f(len(clouds), carr, _p(sizes), garr, _p(weights), translation_weight, rotation_weight,
+           int(only_optimize_yaw), _p(target), _p(pose), _p(cost), _p(r), _p(g))
+    assert rc == 0
+    return float(cost[0]), r, g
+
+
 class Stack:
     def __init__(self, grid, depth, full_resolution_depth):
         self.grid = grid

@@ -123,6 +123,7 @@ int main(int argc, char** argv) {
     co.compute.rotation_weight = 1.;
     co.compute.max_num_iterations = 10;
     co.fast_correlative_scan_matcher_options_3d = fo;
+    co.sampling_ratio = 1.0;
     hg::ConstraintBuilder3D builder(co);
     if (builder.GetNumFinishedNodes() != 0) return Fail("GetNumFinishedNodes");
     builder.AddSubmap({0, 0}, wall, wall, submap_histogram);
@@ -141,6 +142,88 @@ int main(int argc, char** argv) {
     std::promise<size_t> again;
     builder.WhenDone([&again](const hg::ConstraintBuilder3D::Result& r) { again.set_value(r.size()); });
     if (again.get_future().get() != 0) return Fail("empty WhenDone");
+  }
+  // --- MaybeAddConstraint's distance gate and sampler (constraint_builder_3d.cc:82-86) ------------
+  {
+    hg::FixedRatioSampler sampler(0.3);  // common/fixed_ratio_sampler.cc:33-40: 1, 0, 0, 1, 0, 0, 1, 0, 0, 0
+    int taken = 0;
+    const bool expect[10] = {true, false, false, true, false, false, true, false, false, false};
+    for (int k = 0; k < 10; ++k) {
+      const bool got = sampler.Pulse();
+      if (got != expect[k]) return Fail("FixedRatioSampler sequence");
+      taken += got ? 1 : 0;
+    }
+    if (taken != 3) return Fail("FixedRatioSampler count");
+    hg::ConstraintBuilder3D::Options co;
+    std::memset(&co.compute, 0, sizeof(co.compute));
+    co.compute.min_score = 0.3f;
+    co.compute.global_localization_min_score = 0.4f;
+    co.compute.occupied_space_weights[0] = 5.;
+    co.compute.occupied_space_weights[1] = 30.;
+    co.compute.translation_weight = 10.;
+    co.compute.rotation_weight = 1.;
+    co.compute.max_num_iterations = 10;
+    co.fast_correlative_scan_matcher_options_3d = fo;
+    co.sampling_ratio = 0.5;
+    co.max_constraint_distance = 15.;
+    hg::ConstraintBuilder3D builder(co);
+    builder.AddSubmap({0, 0}, wall, wall, submap_histogram);
+    hg::Rigid3d identity, far_node;
+    far_node.translation = {{16., 0., 0.}};
+    // six near nodes at ratio 0.5 -> three are sampled; the far ones never reach the sampler
+    for (int n = 0; n < 6; ++n) {
+      builder.MaybeAddConstraint({0, 0}, {0, 100 + n}, &data, far_node, identity);
+      builder.MaybeAddConstraint({0, 0}, {0, n}, &data, identity, identity);
+      builder.NotifyEndOfNode();
+    }
+    std::promise<hg::ConstraintBuilder3D::Result> done;
+    builder.WhenDone([&done](const hg::ConstraintBuilder3D::Result& r) { done.set_value(r); });
+    const hg::ConstraintBuilder3D::Result constraints = done.get_future().get();
+    if (constraints.size() != 3) return Fail("distance gate / sampler: expected 3 constraints");
+    for (const auto& c : constraints)
+      if (c.node_id.node_index >= 100) return Fail("a constraint beyond max_constraint_distance was computed");
+  }
+  // --- CeresScanMatcher3D::Evaluate (ceres_scan_matcher_3d.cc:97-118) ------------------------------
+  {
+    hg::CeresScanMatcherOptions3D so;
+    so.occupied_space_weight = {1.0};
+    so.translation_weight = 0.5;
+    so.rotation_weight = 0.1;
+    hg::CeresScanMatcher3D matcher(so);
+    hg::Rigid3d pose;
+    pose.translation = {{0.1, -0.05, 0.02}};
+    hg::PointCloudView view;
+    view.data = data.high_resolution_point_cloud.data();
+    view.size = static_cast<int32_t>(data.high_resolution_point_cloud.size() / 3);
+    double cost = -1.;
+    std::vector<double> residuals, gradient;
+    matcher.Evaluate({{0., 0., 0.}}, pose, {{view, wall.get()}}, &cost, &residuals, &gradient);
+    if (residuals.size() != static_cast<size_t>(view.size) + 6 || gradient.size() != 6) return Fail("Evaluate sizes");
+    double half = 0.;
+    for (double r : residuals) half += 0.5 * r * r;
+    if (std::fabs(half - cost) > 1e-12 * (1. + cost)) return Fail("Evaluate cost != 1/2 |r|^2");
+    if (std::fabs(residuals[view.size] - 0.5 * 0.1) > 1e-12) return Fail("Evaluate translation delta");
+  }
+  // --- best-record exchange of a sharded search (hg_pack / select) ------------------------------------
+  {
+    hg_match_result a, b;
+    std::memset(&a, 0, sizeof(a));
+    std::memset(&b, 0, sizeof(b));
+    a.found = b.found = 1;
+    a.score = b.score = 0.8f;
+    a.best_ancestor_score = 0.9f;
+    b.best_ancestor_score = 0.95f;
+    a.best_scan_index = 3;
+    b.best_scan_index = 40;
+    double records[2 * HG_BEST_RECORD_DOUBLES];
+    if (hg_pack_best_record(&a, records) != HG_OK || hg_pack_best_record(&b, records + HG_BEST_RECORD_DOUBLES) != HG_OK)
+      return Fail("hg_pack_best_record");
+    int winner = -1, unresolved = -1;
+    if (hg_select_best_record(records, 2, &winner, &unresolved) != HG_OK || winner != 1 || unresolved != 0)
+      return Fail("hg_select_best_record: the leaf below the higher-scoring ancestor is met first");
+    hg_match_result back;
+    if (hg_unpack_best_record(records + HG_BEST_RECORD_DOUBLES, &back) != HG_OK || back.best_scan_index != 40)
+      return Fail("hg_unpack_best_record");
   }
   // --- range-data inserters (range_data_inserter_3d_test.cc:43-98) ---------------------------
   {

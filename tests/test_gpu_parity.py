@@ -1033,3 +1033,25 @@ def test_chunked_host_evaluate_after_update_points(oracle, hg, world, pinned):
                          [world["o_tsdf_hi"], world["o_tsdf_lo"]], ratios[b])
         ro, Jo = oc.evaluate(np.concatenate([poses[i0[b]], poses[i1[b]]]))
         assert_close(r[offsets[b]:offsets[b + 1]], ro, "residuals of block 7")
+
+
+@pytest.mark.parametrize("grids", [("g_tsdf_hi", "g_tsdf_lo", "o_tsdf_hi", "o_tsdf_lo"), ("g_prob", "g_prob_lo", "o_prob", "o_prob_lo")])
+def test_scan_matcher_evaluate(oracle, hg, world, grids):
+    """CeresScanMatcher3D::Evaluate (ceres_scan_matcher_3d.cc:97-118): cost, residual vector (clouds, then the
+    translation and rotation deltas) and the tangent-space gradient of the assembled problem at a pose."""
+    rng = np.random.RandomState(55)
+    cloud = world["cloud"]
+    low = cloud[::9]
+    for yaw_only in (False, True):
+        pose = perturbed(world["truth"], rng, 0.1, 0.04)
+        target = pose[:3] + rng.uniform(-0.05, 0.05, 3)
+        c1, r1, g1 = hg.scan_match_evaluate([cloud, low], [world[grids[0]], world[grids[1]]], [5.0, 30.0], 10.0, 1.0,
+                                            pose, target_translation=target, only_optimize_yaw=yaw_only)
+        c0, r0, g0 = oracle.scan_match_evaluate([cloud, low], [world[grids[2]], world[grids[3]]], [5.0, 30.0], 10.0,
+                                                1.0, pose, target_translation=target, only_optimize_yaw=yaw_only)
+        assert len(r1) == len(cloud) + len(low) + 6 and len(g1) == (4 if yaw_only else 6)
+        assert_close(r1, r0, "residuals")
+        assert abs(c1 - c0) <= 1e-9 * max(1.0, abs(c0))
+        assert np.abs(g1 - g0).max() <= 1e-7 * max(1.0, np.abs(g0).max())
+        assert abs(c1 - 0.5 * float(r1 @ r1)) <= 1e-12 * max(1.0, c1)
+        assert np.abs(r1[-3:]).max() < 1e-15  # the rotation delta vanishes at the pose it is anchored to
