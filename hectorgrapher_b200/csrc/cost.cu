@@ -453,8 +453,14 @@ int LaunchCost(const hg_batch* B, const CostArgs& args, int num_tiles, cudaStrea
 #define HG_LAUNCH(L, T)                                                                         \
   do {                                                                                          \
     if (NE && smem > 48 * 1024) {                                                               \
-      HG_CUDA(cudaFuncSetAttribute(CostKernel<L, T, NE>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                   static_cast<int>(smem)));                                    \
+      /* once per device and kernel: the attribute sticks */                                    \
+      static std::atomic<unsigned long long> configured{0};                                     \
+      const unsigned long long bit = 1ull << (B->device & 63);                                  \
+      if ((configured.load(std::memory_order_acquire) & bit) == 0) {                            \
+        HG_CUDA(cudaFuncSetAttribute(CostKernel<L, T, NE>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                     static_cast<int>(smem)));                                  \
+        configured.fetch_or(bit, std::memory_order_release);                                    \
+      }                                                                                         \
     }                                                                                           \
     CostKernel<L, T, NE><<<num_tiles, kThreads, smem, stream>>>(args);                          \
   } while (0)

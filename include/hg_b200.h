@@ -262,7 +262,12 @@ int hg_cost_normal_equations(const hg_cost* cost, const double* const* parameter
  * function's device must be the current device. The first call on a device looks up
  * the array's address (make that call before starting any stream capture). All calls
  * share the one array per GPU and take a process-wide lock; the function returns
- * after the device has finished. Host outputs, any may be NULL. */
+ * after the device has finished. Two calls that overlapped on the GPU (which the lock
+ * prevents inside one process) would race on the array. The call does NOT take the
+ * cost function's own lock: do not run it concurrently with hg_batch_update_points,
+ * hg_cost_evaluate or hg_cost_normal_equations on the SAME cost function from another
+ * thread (points queued by an earlier hg_batch_update_points are waited for on the
+ * stream). Host outputs, any may be NULL. */
 int hg_cost_normal_equations_static(const hg_cost* cost, const double* const* parameters,
                                     double* JtJ, double* Jtr, double* cost_out);
 

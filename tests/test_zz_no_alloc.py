@@ -83,3 +83,23 @@ def test_static_scratch_rejects_blocks_beyond_its_limit(setup):
     a = at_limit.normal_equations(truth, static_scratch=True)
     b = at_limit.normal_equations(truth)
     assert _close(a[0], b[0]) and _close(a[2], b[2])
+
+
+def test_static_scratch_calls_leave_device_memory_alone(setup):
+    """The reason this entry point exists: after its first call on a device (which looks up the address of
+    the static array) a call must not take or return device memory. cudaMemGetInfo's free byte count stays
+    where it was over 100 calls — an allocation by the library or by the CUDA runtime would move it."""
+    import torch
+    hg, synth, g_hi, g_lo, cloud, truth = setup
+    c = hg.Cost("interpolated_multires_tsdf", 0.05, cloud, [g_hi, g_lo], 0.35)
+    rng = np.random.RandomState(23)
+    p = _params(synth, truth, rng, True)
+    first = c.normal_equations(p, static_scratch=True)  # set-up call
+    torch.cuda.synchronize()
+    free_before, _ = torch.cuda.mem_get_info()
+    for _ in range(100):
+        got = c.normal_equations(p, static_scratch=True)
+    torch.cuda.synchronize()
+    free_after, _ = torch.cuda.mem_get_info()
+    assert free_after == free_before
+    assert (got[0] == first[0]).all() and got[2] == first[2]
