@@ -60,7 +60,7 @@ def measured_peak():
 def measured_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu capture, or None."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
             return int(json.load(f)[kernel]["dram_bytes_per_launch"])
     except Exception:
         return None
@@ -286,9 +286,11 @@ def golden():
         return {}
 
 
-# ncu (profiles/r2_ncu_summary.md): global-load sectors of ScoreLatticePackedKernel<5,1> per (candidate, point)
-# gather; the level it reads is L1-resident, so the kernel is bound by the L1 data path, not by HBM.
-LATTICE_L1_SECTORS_PER_GATHER = 0.1224
+# ncu (profiles/r2_ncu_summary.md) of ScoreLatticePackedKernel<5,1> on the full sweep: the level it gathers from
+# is L1-resident, and of the L1 sub-units the LSU data pipe is the busiest (l1tex__data_pipe_lsu_wavefronts 63.5 %
+# of its peak of one wavefront = one 128-byte pass per clock and SM; issue slots 69 %). 342.5 M wavefronts for
+# 8 022 929 x 2 048 gathers.
+LATTICE_L1_WAVEFRONTS_PER_GATHER = 342.5e6 / (8022929 * 2048)
 L1_BYTES_PER_CLK_PER_SM = 128
 NUM_SMS = 148
 
@@ -374,7 +376,7 @@ def correlative_bench(hg, torch, w, rank, world, dist, clocks_mhz=None):
     lat = sweep["lowest_resolution_kernel"]
     sm_mhz = clocks_mhz or 1965.0
     l1_peak = NUM_SMS * L1_BYTES_PER_CLK_PER_SM * sm_mhz * 1e6 / 1e9  # GB/s
-    l1_achieved = lat["candidates_per_s_per_gpu"] * n_pts * LATTICE_L1_SECTORS_PER_GATHER * 32 / 1e9
+    l1_achieved = lat["candidates_per_s_per_gpu"] * n_pts * LATTICE_L1_WAVEFRONTS_PER_GATHER * L1_BYTES_PER_CLK_PER_SM / 1e9
     cpu_rate, cpu_desc, cpu_threads = cpu_baseline_candidates(w)
     return {
         "metric": "correlative candidates scored/s", "value": sweep["candidates_per_s"], "unit": "candidates/s",
@@ -391,12 +393,13 @@ def correlative_bench(hg, torch, w, rank, world, dist, clocks_mhz=None):
                      "achieved": l1_achieved, "peak": l1_peak, "frac": l1_achieved / l1_peak,
                      "traffic": measured_traffic("ScoreLatticePackedKernel<5>"),
                      "note": "per GPU, lowest-resolution lattice kernel of the full sweep. The level it gathers "
-                             "from is a few hundred KB and L1-resident (ncu: 47 MB of DRAM traffic per 8 M-candidate "
-                             "launch), so HBM is not the bound; the bound is the L1 data path: achieved = global-load "
-                             "sectors (ncu: %.4f per gather, four voxels per 32-bit load) x 32 B x gathers/s; peak = "
-                             "%d SMs x %d B/clk x %.0f MHz. SURVEY 8(d)'s byte model (N + 24 B per candidate against "
-                             "HBM) would read %.2f of the HBM peak." % (
-                                 LATTICE_L1_SECTORS_PER_GATHER, NUM_SMS, L1_BYTES_PER_CLK_PER_SM, sm_mhz,
+                             "from is a few hundred KB and L1-resident (ncu: 46 MB of DRAM traffic per 8 M-candidate "
+                             "launch, L1 hit rate 96 %%), so HBM is not the bound; the busiest unit is the L1 LSU data "
+                             "pipe: achieved = wavefronts (ncu: %.5f per gather; a lane reads four voxels per 32-bit "
+                             "load) x 128 B x gathers/s; peak = %d SMs x %d B/clk x %.0f MHz (one wavefront per clock "
+                             "and SM). SURVEY 8(d)'s byte model (N + 24 B per candidate against HBM) would read %.2f of "
+                             "the HBM peak." % (
+                                 LATTICE_L1_WAVEFRONTS_PER_GATHER, NUM_SMS, L1_BYTES_PER_CLK_PER_SM, sm_mhz,
                                  lat["candidates_per_s_per_gpu"] * (n_pts + 24) / 1e9 / measured_peak()[0])},
         "cpu_baseline": {"value": cpu_rate, "unit": "candidates/s", "cores": cpu_threads, "kind": "port",
                          "sample": cpu_desc},
@@ -588,8 +591,7 @@ def constraint_bench(hg, torch, w, rank, world, dist, num_submaps=100, nodes_per
            "ms_per_pair_per_gpu": 1e3 * float(dt.item()) * world / max(n_jobs, 1),
            "constraints_found": int(stats[0].item()), "candidates_scored": float(stats[1].item()),
            "candidates_per_s": float(stats[1].item()) / float(dt.item()),
-           "pairs_in_flight_per_gpu": int(os.environ.get(
-               "HG_CONSTRAINT_THREADS", max(4, min(16, (os.cpu_count() or 8) // max(1, world)))))}
+           "group_workers_per_gpu": int(os.environ.get("HG_CONSTRAINT_THREADS", 3))}
     if cpu:
         try:
             rate, threads, desc = cpu_baseline_pairs(synth, sph, num_submaps)
@@ -895,7 +897,7 @@ def run_ours(args, rank, world, local_rank):
                        "l2": "256 MiB flush write between timed steps; working set per step ~0.9 GB"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": measured_traffic("CostKernel<2,true,false>"),
-                         "traffic_note": "bytes per launch (ncu, profiles/r1_ncu_summary.md); algorithmic bytes per "
+                         "traffic_note": "bytes per launch (ncu, profiles/r2_ncu_summary.md); algorithmic bytes per "
                                          "launch = %d" % (ALG_BYTES_PER_POINT * N),
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_point": ALG_BYTES_PER_POINT, "kernel": "CostKernel<2,true,false>"},

@@ -28,8 +28,7 @@ namespace {
 // flight (each search on its own non-blocking stream with its own thread-local scratch,
 // see fcsm.cu) fill it. The workers live as long as the process so that their scratch
 // (pinned buffers in particular) is allocated once. HG_CONSTRAINT_THREADS sets the number
-// of pairs in flight (default: host cores per rank, clamped to 4..16; 1 = compute on the
-// calling thread).
+// of workers (default 3; 1 = compute on the calling thread).
 class WorkerPool {
  public:
   static WorkerPool& Get() {
@@ -65,13 +64,15 @@ class WorkerPool {
 
  private:
   WorkerPool() {
-    // Default: the host cores this process can count on (one process per GPU: the cores are
-    // shared by LOCAL_WORLD_SIZE ranks), between 4 and 16 — the workers mostly wait on their
-    // streams, and 16 in flight is where a B200 stops gaining on the C5 workload.
+    // Default: three workers (two when the rank has fewer than three cores). A unit of work is a
+    // whole group of pairs — one device-resident search and one refine launch — so a worker's host
+    // time is small and a second and third one only have to cover its synchronisation gaps; more
+    // concurrent groups make the GPU slower, not faster (measured on C5, 2 000 pairs: 1 worker 61 us
+    // per pair, 2-3 workers 51-52, 4: 67, 8: 81, 16: 87).
     int ranks = 1;
     if (const char* env = std::getenv("LOCAL_WORLD_SIZE")) ranks = std::max(1, std::atoi(env));
     int n = static_cast<int>(std::thread::hardware_concurrency()) / ranks;
-    n = n < 4 ? 4 : (n > 16 ? 16 : n);
+    n = n < 3 ? 2 : 3;
     if (const char* env = std::getenv("HG_CONSTRAINT_THREADS")) n = std::atoi(env);
     n = n < 1 ? 1 : (n > 64 ? 64 : n);
     for (int i = 0; i < n; ++i) {

@@ -1849,6 +1849,7 @@ struct SearchDev {
   const int* lattice;  // [total_scans * per_scan]
   int4* starts;        // [total_scans] dive state
   int* start_sums;     // -1 = the scan's best lattice candidate does not beat min_score
+  int* start_dead;     // 1 = not among the scans the dive starts from
   int* bound_bits;     // [P] score bits of the best valid dive leaf, 0 = none
   int* thresh_bits;    // [P] phase B keeps score bits >= this
   int* best_bits;      // [P] best valid leaf of phase B
@@ -1959,21 +1960,25 @@ __global__ void __launch_bounds__(256) LatticeBatchKernel(const SearchDev s, con
   }
 }
 
-// Keeps the dive starts of the 'keep' best-scoring scans of every problem (a CTA per problem,
-// rank by counting); the others are marked dead. The dive only has to produce a good bound.
+// Keeps the dive starts of the 'keep' best-scoring scans of every problem (rank by counting:
+// blockIdx.x = problem, blockIdx.y = chunk of 256 of its scans); the others are marked in
+// start_dead. The dive only has to produce a good bound.
 __global__ void __launch_bounds__(256) SelectStartsKernel(const SearchDev s, const int keep) {
   const ProblemDev& P = s.problems[blockIdx.x];
-  if (P.S <= keep || P.S > 2048) return;
-  int* sums = s.start_sums + P.scan_begin;
-  __shared__ int snapshot[2048];
-  for (int t = threadIdx.x; t < P.S; t += 256) snapshot[t] = sums[t];
-  __syncthreads();
-  for (int t = threadIdx.x; t < P.S; t += 256) {
-    const int mine = snapshot[t];
+  const int t = blockIdx.y * 256 + threadIdx.x;
+  if (t >= P.S) return;
+  const int* sums = s.start_sums + P.scan_begin;
+  int dead = 0;
+  if (P.S > keep) {
+    const int mine = sums[t];
     int rank = 0;
-    for (int j = 0; j < P.S; ++j) rank += (snapshot[j] > mine || (snapshot[j] == mine && j < t)) ? 1 : 0;
-    if (rank >= keep) sums[t] = -1;
+    for (int j = 0; j < P.S; ++j) {
+      const int other = __ldg(sums + j);
+      rank += (other > mine || (other == mine && j < t)) ? 1 : 0;
+    }
+    dead = rank >= keep ? 1 : 0;
   }
+  s.start_dead[P.scan_begin + t] = dead;
 }
 
 // Dive start of every discrete scan: its best lattice candidate (first one on equal sums).
@@ -2092,7 +2097,7 @@ __global__ void __launch_bounds__(256) DiveLevelKernel(const SearchDev s, const 
   __shared__ int warp_sums[8][8];
   __shared__ int totals[8];
   const int sg = blockIdx.x;
-  if (s.start_sums[sg] < 0) return;  // CTA-uniform
+  if (s.start_sums[sg] < 0 || s.start_dead[sg]) return;  // CTA-uniform
   const int4 p = s.starts[sg];
   const ProblemDev& P = s.problems[s.scans[sg].problem];
   const int half = 1 << child_depth;
@@ -2133,7 +2138,7 @@ __global__ void __launch_bounds__(128) GateKernel(const SearchDev s, const GateA
   for (int item = blockIdx.x * 4 + warp; item < count; item += gridDim.x * 4) {
     const int4 c = DIVE ? s.starts[item] : s.list[0][item];
     const int sum = DIVE ? s.start_sums[item] : s.list_sum[0][item];
-    if (sum < 0) continue;  // warp-uniform
+    if (sum < 0 || (DIVE && s.start_dead[item])) continue;  // warp-uniform
     const ScanDev sc = s.scans[c.x];
     const ProblemDev& P = s.problems[sc.problem];
     const float score_value = DeviceScore(sum, P.N);
@@ -2215,17 +2220,16 @@ __device__ __forceinline__ int WarpAppend(int* counter, const bool keep) {
 // Lattice candidates that reach their problem's threshold -> the frontier of the lowest
 // resolution.
 __global__ void __launch_bounds__(256) SeedKernel(const SearchDev s) {
-  const long long n = static_cast<long long>(s.total_scans) * s.per_scan;
+  const int n = s.total_scans * s.per_scan;  // < 2^31 (checked on the host)
   const int d = s.max_depth;
-  for (long long base = static_cast<long long>(blockIdx.x) * blockDim.x; base < n;
-       base += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long i = base + threadIdx.x;
+  for (int base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+    const int i = base + threadIdx.x;
     bool keep = false;
     int sg = 0, at = 0, sum = 0;
     if (i < n) {
-      sg = static_cast<int>(i / s.per_scan);
-      at = static_cast<int>(i - static_cast<long long>(sg) * s.per_scan);
-      sum = s.lattice[i];
+      sg = i / s.per_scan;
+      at = i - sg * s.per_scan;
+      sum = __ldg(s.lattice + i);
       const int p = s.scans[sg].problem;
       keep = __float_as_int(DeviceScore(sum, s.problems[p].N)) >= s.thresh_bits[p];
     }
@@ -2452,7 +2456,7 @@ class DeviceSearch {
     winners_cap_ = std::max(256, 4 * P);
     if ((rc = ws_->d_cells.Reserve(cell_ints * sizeof(int))) != HG_OK) return rc;
     if ((rc = ws_->d_lattice.Reserve(lattice_n * sizeof(int))) != HG_OK) return rc;
-    if ((rc = ws_->d_starts.Reserve(n_scans * (sizeof(int4) + sizeof(int)))) != HG_OK) return rc;
+    if ((rc = ws_->d_starts.Reserve(n_scans * (sizeof(int4) + 2 * sizeof(int)))) != HG_OK) return rc;
     if ((rc = ws_->d_lists.Reserve(static_cast<size_t>(list_cap_) * (2 * sizeof(int4) + 2 * sizeof(int) + sizeof(float)))) != HG_OK)
       return rc;
     // control block: CtrlDev | per problem: bound, thresh, best, win_count (ints) | scored (u64) | winners
@@ -2475,6 +2479,7 @@ class DeviceSearch {
     s.lattice = ws_->d_lattice.as<int>();
     s.starts = ws_->d_starts.as<int4>();
     s.start_sums = reinterpret_cast<int*>(ws_->d_starts.as<int4>() + n_scans);
+    s.start_dead = s.start_sums + n_scans;
     int* pp = reinterpret_cast<int*>(c + off_pp);
     s.bound_bits = pp;
     s.thresh_bits = pp + P;
@@ -2556,8 +2561,13 @@ class DeviceSearch {
     ArgmaxPerScanKernel<<<(total_scans_ * 32 + 255) / 256, 256, 0, stream_>>>(s);
     CountLaunch();
     ++launches_;
-    if (P > 1) {  // a batch of local searches: a few dozen starts per problem give the bound
-      SelectStartsKernel<<<P, 256, 0, stream_>>>(s, kDiveStartsPerProblem);
+    {
+      // The dive only has to produce a good bound: a few dozen starts per problem of a batch of local
+      // searches, a few hundred for a single (full-submap) search — neighbouring yaws are near copies.
+      int max_s = 1;
+      for (int p = 0; p < P; ++p) max_s = std::max(max_s, problems_[p].scans.S);
+      SelectStartsKernel<<<dim3(P, (max_s + 255) / 256), 256, 0, stream_>>>(
+          s, P > 1 ? kDiveStartsPerProblem : kDiveStartsSingle);
       CountLaunch();
       ++launches_;
     }
@@ -2834,6 +2844,7 @@ class DeviceSearch {
  private:
   static constexpr int kListCapacity = 1 << 20;
   static constexpr int kDiveStartsPerProblem = 32;
+  static constexpr int kDiveStartsSingle = 256;
   struct Problem {
     SearchParameters sp;
     const hg_node_data* data = nullptr;
