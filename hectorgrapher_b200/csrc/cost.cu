@@ -693,6 +693,7 @@ int64_t hg_batch_num_residuals(const hg_batch* B) { return B ? B->num_points : 0
 int hg_batch_update_points(hg_batch* B, const float* points, int stride_floats) {
   HG_REQUIRE(B != nullptr && points != nullptr && stride_floats == B->stride,
              "hg_batch_update_points: bad arguments");
+  HG_ON_DEVICE(B->device);
   std::lock_guard<std::mutex> lock(B->mu);
   // Evaluations that returned early (device outputs) may still be reading the old points.
   int rc = WaitForSlots(B);
@@ -721,6 +722,7 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
                       const int32_t* pose_index1, int device_outputs, double* residuals, double* jt0,
                       double* jq0, double* jt1, double* jq1, void* cuda_stream) {
   HG_REQUIRE(B != nullptr && poses != nullptr && num_poses >= 1, "hg_batch_evaluate: bad arguments");
+  HG_ON_DEVICE(B->device);
   cudaStream_t stream = cuda_stream != nullptr ? static_cast<cudaStream_t>(cuda_stream) : B->stream;
   std::lock_guard<std::mutex> lock(B->mu);
   int slot = 0;
@@ -835,6 +837,7 @@ int hg_batch_normal_equations(const hg_batch* B, const double* poses, int num_po
                               const int32_t* pose_index0, const int32_t* pose_index1, double* JtJ,
                               double* Jtr, double* cost_out) {
   HG_REQUIRE(B != nullptr && poses != nullptr && num_poses >= 1, "hg_batch_normal_equations: bad arguments");
+  HG_ON_DEVICE(B->device);
   std::lock_guard<std::mutex> lock(B->mu);
   cudaStream_t stream = B->stream;
   int slot = 0;
@@ -882,6 +885,7 @@ int hg_batch_level_usage(const hg_batch* B, const double* poses, int num_poses, 
   HG_REQUIRE(B != nullptr && poses != nullptr && num_poses >= 1 && counts != nullptr,
              "hg_batch_level_usage: bad arguments");
   HG_REQUIRE(B->lookup == 2, "hg_batch_level_usage: only multi-resolution TSDF cost functions have levels");
+  HG_ON_DEVICE(B->device);
   std::lock_guard<std::mutex> lock(B->mu);
   cudaStream_t stream = B->stream;
   int slot = 0;

@@ -1727,7 +1727,7 @@ int HostReplayMatch(const hg_fcsm* m, const SearchParameters& sp, const Rigid& n
                               int shard_index, int num_shards, hg_match_result* result) {
   std::memset(result, 0, sizeof(*result));
   result->pose_rotation[0] = 1.0;
-  HG_CUDA(cudaSetDevice(m->device));
+  HG_ON_DEVICE(m->device);
   // The calling host thread's own non-blocking stream: searches driven by different host
   // threads overlap on the device.
   cudaStream_t stream = ThreadStream();
@@ -2926,7 +2926,7 @@ int MatchWithSearchParameters(const hg_fcsm* m, const SearchParameters& sp, cons
   if (m->options.strict_visit_order != 0 || ForceHostReplay()) {
     return HostReplayMatch(m, sp, node_pose, submap_pose, data, min_score, shard_index, num_shards, result);
   }
-  HG_CUDA(cudaSetDevice(m->device));
+  HG_ON_DEVICE(m->device);
   cudaStream_t stream = ThreadStream();
   HG_REQUIRE(stream != nullptr, "hg_fcsm: cannot create a stream");
   PhaseTimer pt;
@@ -3085,7 +3085,7 @@ int hg_fcsm_match_batch(const hg_fcsm* m, int num_problems, const double* global
     }
     return HG_OK;
   }
-  HG_CUDA(cudaSetDevice(m->device));
+  HG_ON_DEVICE(m->device);
   cudaStream_t stream = ThreadStream();
   HG_REQUIRE(stream != nullptr, "hg_fcsm: cannot create a stream");
   // Sub-batches bounded by the memory of the discretised scans (12 bytes per scan point and level).
@@ -3166,7 +3166,7 @@ int hg_fcsm_full_submap_begin(const hg_fcsm* m, const double* global_node_rotati
   h->shard_index = shard_index;
   h->num_shards = num_shards;
   if (m->options.strict_visit_order == 0 && !ForceHostReplay()) {
-    HG_CUDA(cudaSetDevice(m->device));
+    HG_ON_DEVICE(m->device);
     cudaStream_t stream = ThreadStream();
     HG_REQUIRE(stream != nullptr, "hg_fcsm: cannot create a stream");
     h->search.reset(new DeviceSearch(m, stream));
@@ -3186,6 +3186,7 @@ int hg_fcsm_full_submap_begin(const hg_fcsm* m, const double* global_node_rotati
 int hg_fcsm_full_submap_finish(hg_fcsm_search* search, float bound, hg_match_result* result) {
   HG_REQUIRE(search != nullptr && result != nullptr, "hg_fcsm_full_submap_finish: bad arguments");
   std::unique_ptr<hg_fcsm_search> h(search);
+  HG_ON_DEVICE(h->m->device);
   if (h->search) {
     std::vector<DeviceSearch::Outcome> outcomes;
     const int rc = h->search->RunPhaseB(bound, &outcomes);
@@ -3289,7 +3290,7 @@ int hg_fcsm_discrete_scans(const hg_fcsm* m, int wxy, int wz, double angular_sea
   HG_REQUIRE(m && global_node_pose && global_submap_pose && num_scans, "hg_fcsm_discrete_scans: bad arguments");
   int rc = CheckNodeData(data);
   if (rc != HG_OK) return rc;
-  HG_CUDA(cudaSetDevice(m->device));
+  HG_ON_DEVICE(m->device);
   ScanSet scans;
   const SearchParameters sp{wxy, wz, angular_search_window};
   rc = GenerateDiscreteScans(m, sp, data, ToRigidF(global_node_pose, global_node_pose + 3),
@@ -3328,7 +3329,7 @@ int hg_fcsm_score_candidates(const hg_fcsm* m, int wxy, int wz, double angular_s
   HG_REQUIRE(depth >= 0 && depth < m->options.branch_and_bound_depth, "hg_fcsm_score_candidates: bad depth");
   int rc = CheckNodeData(data);
   if (rc != HG_OK) return rc;
-  HG_CUDA(cudaSetDevice(m->device));
+  HG_ON_DEVICE(m->device);
   ScanSet scans;
   const SearchParameters sp{wxy, wz, angular_search_window};
   rc = GenerateDiscreteScans(m, sp, data, ToRigidF(global_node_pose, global_node_pose + 3),

@@ -320,6 +320,7 @@ int hg_grid_lookup(const hg_grid* grid, int what, int64_t n, const int32_t* xyz,
   HG_REQUIRE(grid != nullptr && n >= 0 && what >= 0 && what <= 2, "hg_grid_lookup: bad arguments");
   HG_REQUIRE((grid->dev.kind == kGridProb) == (what == 0), "hg_grid_lookup: 'what' does not match the grid type");
   if (n == 0) return HG_OK;
+  HG_ON_DEVICE(grid->device);
   int32_t* d_xyz = nullptr;
   float* d_out = nullptr;
   HG_CUDA(cudaMalloc(&d_xyz, n * 3 * sizeof(int32_t)));

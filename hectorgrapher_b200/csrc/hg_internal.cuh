@@ -36,6 +36,39 @@ inline void CountLaunch(uint64_t n = 1) { g_kernel_launches.fetch_add(n, std::me
     }                                  \
   } while (0)
 
+// ---------------------------------------------------------------- devices --
+// One policy for every entry point that takes a handle: the call runs on the handle's device and
+// the caller's current device is what it was when the call returns.
+class DeviceGuard {
+ public:
+  explicit DeviceGuard(const int device) {
+    if (cudaGetDevice(&previous_) != cudaSuccess) previous_ = -1;
+    if (previous_ != device) {
+      ok_ = cudaSetDevice(device) == cudaSuccess;
+      switched_ = ok_;
+    }
+  }
+  ~DeviceGuard() {
+    if (switched_ && previous_ >= 0) cudaSetDevice(previous_);
+  }
+  bool ok() const { return ok_; }
+  DeviceGuard(const DeviceGuard&) = delete;
+  DeviceGuard& operator=(const DeviceGuard&) = delete;
+
+ private:
+  int previous_ = -1;
+  bool switched_ = false;
+  bool ok_ = true;
+};
+#define HG_ON_DEVICE(device)                                             \
+  ::hg::DeviceGuard _hg_device_guard(device);                            \
+  do {                                                                   \
+    if (!_hg_device_guard.ok()) {                                        \
+      ::hg::SetError("cannot switch to the handle's CUDA device");      \
+      return HG_ERR_CUDA;                                                \
+    }                                                                    \
+  } while (0)
+
 // ------------------------------------------------------------ allocation --
 // alloc.cu: blocks released by a host thread are cached by that thread and reused (no
 // cudaFree on the per-pair path); a block may be released by another thread than the

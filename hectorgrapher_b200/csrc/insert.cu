@@ -29,6 +29,7 @@
 // the same sort, keyed (cell, hit-or-miss), and one table lookup per touched cell.
 #include <cub/cub.cuh>
 #include <thrust/iterator/counting_iterator.h>
+#include <thrust/iterator/transform_iterator.h>
 
 #include <algorithm>
 #include <chrono>
@@ -686,6 +687,10 @@ int UploadReturns(GridMutable* m, const float* returns, const int stride, const 
   return HG_OK;
 }
 
+struct WidenCount {
+  __host__ __device__ unsigned long long operator()(const int v) const { return static_cast<unsigned long long>(v); }
+};
+
 // Exclusive scan of counts[0..n) into offsets[0..n]; returns the total.
 int ScanCounts(GridMutable* m, const int64_t n, int* total) {
   // counts has n + 1 entries with counts[n] = 0, so that offsets[n] is the total.
@@ -697,6 +702,22 @@ int ScanCounts(GridMutable* m, const int64_t n, int* total) {
                                         static_cast<int>(n + 1)));
   CountLaunch();
   HG_CUDA(cudaMemcpy(total, m->offsets.as<int>() + n, sizeof(int), cudaMemcpyDeviceToHost));
+  // The offsets are 32-bit: a scan whose updates do not fit is refused instead of wrapping around
+  // (the sum is taken again in 64 bits).
+  if (m->num.Ensure(sizeof(unsigned long long)) != HG_OK) return HG_ERR_CUDA;
+  thrust::transform_iterator<WidenCount, const int*> wide(m->counts.as<int>(), WidenCount());
+  unsigned long long* d_sum = reinterpret_cast<unsigned long long*>(m->num.p);
+  bytes = 0;
+  cub::DeviceReduce::Sum(nullptr, bytes, wide, d_sum, static_cast<int>(n));
+  if (m->temp.Ensure(bytes) != HG_OK) return HG_ERR_CUDA;
+  HG_CUDA(cub::DeviceReduce::Sum(m->temp.p, bytes, wide, d_sum, static_cast<int>(n)));
+  CountLaunch();
+  unsigned long long sum = 0;
+  HG_CUDA(cudaMemcpy(&sum, d_sum, sizeof(sum), cudaMemcpyDeviceToHost));
+  if (sum >= (1ull << 31)) {
+    SetError("range-data insertion: " + std::to_string(sum) + " cell updates in one scan exceed the 2^31 - 1 this path indexes");
+    return HG_ERR_LIMIT;
+  }
   return HG_OK;
 }
 
@@ -770,7 +791,7 @@ int hg_grid_insert_tsdf(hg_grid* grid, const hg_tsdf_inserter_options* options, 
   HG_REQUIRE(num_returns < (int64_t(1) << 27), "hg_grid_insert_tsdf: too many returns for one call");
   if (num_updates) *num_updates = 0;
   if (num_returns == 0) return HG_OK;
-  HG_CUDA(cudaSetDevice(grid->device));
+  HG_ON_DEVICE(grid->device);
   int rc = MakeMutable(grid);
   if (rc != HG_OK) return rc;
   GridMutable* m = grid->mut;
@@ -895,7 +916,7 @@ int hg_grid_insert_occupancy(hg_grid* grid, const hg_occupancy_inserter_options*
                  options->hit_probability < 1.0 && options->miss_probability > 0.0,
              "hg_grid_insert_occupancy: need miss_probability < 0.5 < hit_probability");
   if (num_returns == 0) return HG_OK;
-  HG_CUDA(cudaSetDevice(grid->device));
+  HG_ON_DEVICE(grid->device);
   int rc = MakeMutable(grid);
   if (rc != HG_OK) return rc;
   GridMutable* m = grid->mut;
@@ -986,7 +1007,7 @@ int hg_grid_insert_occupancy(hg_grid* grid, const hg_occupancy_inserter_options*
 int hg_grid_export(const hg_grid* grid, int64_t max_voxels, int64_t* num_voxels, int32_t* xyz,
                    uint16_t* values_a, uint16_t* values_b) {
   HG_REQUIRE(grid != nullptr && num_voxels != nullptr && max_voxels >= 0, "hg_grid_export: bad arguments");
-  HG_CUDA(cudaSetDevice(grid->device));
+  HG_ON_DEVICE(grid->device);
   const bool tsdf = grid->dev.kind == kGridTsdf;
   const size_t vb = tsdf ? sizeof(ushort2) : sizeof(uint16_t);
   const int64_t nb = grid->num_bricks;

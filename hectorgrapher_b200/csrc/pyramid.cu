@@ -155,6 +155,7 @@ extern "C" {
 int hg_stack_build(const hg_grid* grid, int branch_and_bound_depth, int full_resolution_depth,
                    hg_stack** out) {
   HG_REQUIRE(grid != nullptr && out != nullptr, "hg_stack_build: bad arguments");
+  HG_ON_DEVICE(grid->device);
   // fast_correlative_scan_matcher_3d.cc:63-64 CHECK_GE(..., 1)
   HG_REQUIRE(branch_and_bound_depth >= 1 && full_resolution_depth >= 1,
              "hg_stack_build: branch_and_bound_depth and full_resolution_depth must be >= 1");
@@ -286,6 +287,7 @@ int hg_stack_lookup(const hg_stack* stack, int depth, int64_t n, const int32_t* 
   HG_REQUIRE(stack != nullptr && depth >= 0 && depth < static_cast<int>(stack->levels.size()) && n >= 0,
              "hg_stack_lookup: bad arguments");
   if (n == 0) return HG_OK;
+  HG_ON_DEVICE(stack->device);
   int32_t* d_xyz = nullptr;
   unsigned char* d_out = nullptr;
   HG_CUDA(cudaMalloc(&d_xyz, n * 3 * sizeof(int32_t)));
