@@ -212,6 +212,13 @@ __global__ void __launch_bounds__(256) ScoreLatticeDenseKernel(const DenseLevel 
 // voxels of consecutive x-candidates become CONSECUTIVE BYTES, four per 32-bit load. Rows
 // carry kLatticePadLeft zero bytes before and kLatticePadRight after their payload, so that any
 // window of up to 32 candidates that touches the payload can be read without bounds checks.
+// One pyramid level as the kernels read it; the matcher keeps an array of them on the device so that
+// one launch can walk several levels.
+struct LevelDev {
+  BrickTable table;
+  DenseLevel dense;
+};
+
 struct LatticeRows {
   const unsigned* data = nullptr;  // [(z * dim1 + y) * cs + r][row_words]
   int min[3] = {0, 0, 0};
@@ -670,6 +677,7 @@ struct hg_fcsm {
   // Residue-row copy of the lowest-resolution level for the lattice kernel (see LatticeRows).
   LatticeRows lattice_rows;
   void* d_lattice_rows = nullptr;
+  LevelDev* d_levels = nullptr;  // [branch_and_bound_depth]
 };
 
 namespace {
@@ -2090,34 +2098,42 @@ __device__ __forceinline__ unsigned ValidChildren(const int px, const int py, co
   return valid;
 }
 
-// One level of the dive: a CTA per start scores its eight children and the best one (the first
-// on equal sums) replaces the start.
-__global__ void __launch_bounds__(256) DiveLevelKernel(const SearchDev s, const BrickTable level,
-                                                       const DenseLevel dense, const int child_depth) {
+// The greedy dive: a CTA per start walks from the lowest resolution to a leaf; at every level it
+// scores the eight children and the best one (the first on equal sums) becomes the next parent.
+__global__ void __launch_bounds__(256) DiveKernel(const SearchDev s, const LevelDev* __restrict__ levels) {
   __shared__ int warp_sums[8][8];
   __shared__ int totals[8];
   const int sg = blockIdx.x;
   if (s.start_sums[sg] < 0 || s.start_dead[sg]) return;  // CTA-uniform
-  const int4 p = s.starts[sg];
+  int4 p = s.starts[sg];
   const ProblemDev& P = s.problems[s.scans[sg].problem];
-  const int half = 1 << child_depth;
-  const int e = max(0, child_depth - s.frd + 1);
-  const unsigned valid = ValidChildren(p.y, p.z, p.w, half, P.wxy, P.wz);
-  BlockChildrenSums(level, dense, CellsOf(s, P, sg - P.scan_begin, child_depth), P.N, p.y, p.z, p.w, half, e, valid,
-                    warp_sums, totals);
-  if (threadIdx.x != 0) return;
-  int best = 0, best_sum = -1;
+  const int* cells0 = CellsOf(s, P, sg - P.scan_begin, 0);
+  int best_sum = s.start_sums[sg];
+  unsigned long long scored = 0;
+  for (int child_depth = s.max_depth - 1; child_depth >= 0; --child_depth) {
+    const int half = 1 << child_depth;
+    const int e = max(0, child_depth - s.frd + 1);
+    const unsigned valid = ValidChildren(p.y, p.z, p.w, half, P.wxy, P.wz);
+    const LevelDev& L = levels[child_depth];
+    BlockChildrenSums(L.table, L.dense, cells0 + e * P.level_stride, P.N, p.y, p.z, p.w, half, e, valid, warp_sums,
+                      totals);
+    int best = 0;
+    best_sum = -1;
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    if (((valid >> k) & 1u) && totals[k] > best_sum) {
-      best_sum = totals[k];
-      best = k;
+    for (int k = 0; k < 8; ++k) {
+      if (((valid >> k) & 1u) && totals[k] > best_sum) {
+        best_sum = totals[k];
+        best = k;
+      }
     }
+    p = make_int4(sg, p.y + ((best & 1) ? half : 0), p.z + ((best & 2) ? half : 0), p.w + ((best & 4) ? half : 0));
+    scored += __popc(valid);
+    __syncthreads();  // 'totals' is rewritten by the next level
   }
-  s.starts[sg] = make_int4(sg, p.y + ((best & 1) ? half : 0), p.z + ((best & 2) ? half : 0),
-                           p.w + ((best & 4) ? half : 0));
+  if (threadIdx.x != 0) return;
+  s.starts[sg] = p;
   s.start_sums[sg] = best_sum;
-  atomicAdd(&s.scored[s.scans[sg].problem], static_cast<unsigned long long>(__popc(valid)));
+  atomicAdd(&s.scored[s.scans[sg].problem], scored);
 }
 
 // LowResolutionMatcher closure (low_resolution_matcher.cc:24-69) for candidates: a warp per
@@ -2453,7 +2469,7 @@ class DeviceSearch {
     // ---- device state
     const size_t lattice_n = n_scans * per_scan_;
     list_cap_ = kListCapacity;
-    winners_cap_ = std::max(256, 4 * P);
+    winners_cap_ = std::max(4096, 8 * P);
     if ((rc = ws_->d_cells.Reserve(cell_ints * sizeof(int))) != HG_OK) return rc;
     if ((rc = ws_->d_lattice.Reserve(lattice_n * sizeof(int))) != HG_OK) return rc;
     if ((rc = ws_->d_starts.Reserve(n_scans * (sizeof(int4) + 2 * sizeof(int)))) != HG_OK) return rc;
@@ -2571,9 +2587,8 @@ class DeviceSearch {
       CountLaunch();
       ++launches_;
     }
-    for (int depth = max_depth_; depth >= 1; --depth) {
-      const hg_stack_level& L = m_->stack->levels[depth - 1];
-      DiveLevelKernel<<<total_scans_, 256, 0, stream_>>>(s, L.table, L.dense, depth - 1);
+    if (max_depth_ >= 1) {
+      DiveKernel<<<total_scans_, 256, 0, stream_>>>(s, m_->d_levels);
       CountLaunch();
       ++launches_;
     }
@@ -2999,6 +3014,12 @@ int hg_fcsm_create(const hg_grid* grid, const hg_grid* low_resolution_grid,
     m->histogram.assign(rotational_scan_matcher_histogram, rotational_scan_matcher_histogram + histogram_size);
   const int rc = hg_stack_build(grid, options->branch_and_bound_depth, options->full_resolution_depth, &m->stack);
   if (rc != HG_OK) return rc;
+  {
+    std::vector<LevelDev> levels;
+    for (const hg_stack_level& L : m->stack->levels) levels.push_back(LevelDev{L.table, L.dense});
+    HG_CUDA(cudaMalloc(&m->d_levels, levels.size() * sizeof(LevelDev)));
+    HG_CUDA(cudaMemcpy(m->d_levels, levels.data(), levels.size() * sizeof(LevelDev), cudaMemcpyHostToDevice));
+  }
   // Residue rows of the lowest-resolution level for the lattice kernel.
   const int depth = static_cast<int>(m->stack->levels.size()) - 1;
   const hg_stack_level& L = m->stack->levels[depth];
@@ -3034,6 +3055,7 @@ int hg_fcsm_create(const hg_grid* grid, const hg_grid* low_resolution_grid,
 void hg_fcsm_destroy(hg_fcsm* m) {
   if (m == nullptr) return;
   if (m->d_lattice_rows) cudaFree(m->d_lattice_rows);
+  if (m->d_levels) cudaFree(m->d_levels);
   hg_stack_destroy(m->stack);
   delete m;
 }

@@ -12,14 +12,40 @@ def shard_indices(n, rank, world):
     return np.arange(rank, n, world, dtype=np.int64)
 
 
+_BUFFERS = {}
+
+
+def _buffers(dist, device):
+    """Persistent staging for the two small exchanges of a sharded search: the collectives run on
+    preallocated device tensors fed from / drained into pinned host tensors, so that an exchange is two
+    tiny copies and one collective instead of fresh allocations, list-of-tensor gathers and pageable copies."""
+    world = dist.get_world_size()
+    key = (str(device), world)
+    if key not in _BUFFERS:
+        from . import capi
+        n = capi.BEST_RECORD_DOUBLES
+        pin = str(device) != "cpu" and torch.cuda.is_available()
+        host = lambda shape, dtype: (torch.zeros(shape, dtype=dtype).pin_memory() if pin else torch.zeros(shape, dtype=dtype))
+        _BUFFERS[key] = dict(
+            bound_d=torch.zeros(1, dtype=torch.float32, device=device), bound_h=host(1, torch.float32),
+            rec_d=torch.zeros(n, dtype=torch.float64, device=device), rec_h=host(n, torch.float64),
+            all_d=torch.zeros(world * n, dtype=torch.float64, device=device), all_h=host(world * n, torch.float64))
+    return _BUFFERS[key]
+
+
 def all_reduce_max_bound(bound, dist, device="cuda"):
     """The optional mid-search exchange of a sharded MatchFullSubmap: the largest dive bound
     any shard found (hg_fcsm_full_submap_begin), one 4-byte all-reduce-max."""
     if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
         return float(bound)
-    t = torch.tensor([float(bound)], dtype=torch.float32, device=device)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+    b = _buffers(dist, device)
+    b["bound_h"][0] = float(bound)
+    b["bound_d"].copy_(b["bound_h"], non_blocking=True)
+    dist.all_reduce(b["bound_d"], op=dist.ReduceOp.MAX)
+    b["bound_h"].copy_(b["bound_d"], non_blocking=True)
+    if str(device) != "cpu":
+        torch.cuda.current_stream().synchronize()
+    return float(b["bound_h"][0])
 
 
 def reduce_best_candidate(result, dist, device="cuda"):
@@ -31,13 +57,15 @@ def reduce_best_candidate(result, dist, device="cuda"):
     from . import capi
     mine = capi.pack_best_record(result) if result is not None else np.zeros(capi.BEST_RECORD_DOUBLES)
     if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
-        allrec = mine[None]
-    else:
-        t = torch.as_tensor(mine, dtype=torch.float64, device=device)
-        bufs = [torch.zeros_like(t) for _ in range(dist.get_world_size())]
-        dist.all_gather(bufs, t)
-        allrec = torch.stack(bufs).cpu().numpy()
-    return capi.select_best_record(allrec)
+        return capi.select_best_record(mine[None])
+    b = _buffers(dist, device)
+    b["rec_h"].copy_(torch.from_numpy(mine))
+    b["rec_d"].copy_(b["rec_h"], non_blocking=True)
+    dist.all_gather_into_tensor(b["all_d"], b["rec_d"])
+    b["all_h"].copy_(b["all_d"], non_blocking=True)
+    if str(device) != "cpu":
+        torch.cuda.current_stream().synchronize()
+    return capi.select_best_record(b["all_h"].numpy().reshape(dist.get_world_size(), -1))
 
 
 def gather_job_results(local, owned, dist, device="cuda"):
