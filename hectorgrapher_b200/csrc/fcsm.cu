@@ -2573,6 +2573,34 @@ class DeviceSearch {
       }
     }
     if (time_lattice) HG_CUDA(cudaEventRecord(e1_, stream_));
+    if (std::getenv("HG_LATTICE_CHECK") != nullptr) {
+      // Development / test aid: whatever kernel scored the lattice, against the brick-table kernel, every sum.
+      const hg_stack_level& L = m_->stack->levels[max_depth_];
+      for (int p = 0; p < P; ++p) {
+        const ScanSet& sc = problems_[p].scans;
+        const size_t n = static_cast<size_t>(sc.S) * per_scan_;
+        if (n == 0) continue;
+        DeviceBuffer check;
+        if ((rc = check.Reserve(n * sizeof(int))) != HG_OK) return rc;
+        const int* cells = ws_->d_cells.as<int>() + pd[p].cells_offset + lattice_level * pd[p].level_stride;
+        ScoreLatticeKernel<<<static_cast<unsigned>((n * 32 + 255) / 256), 256, 0, stream_>>>(
+            L.table, cells, sc.N, ReduceExponentOf(m_, max_depth_), nxy_, nz_, sp.wxy, sp.wz, 1 << max_depth_,
+            static_cast<int64_t>(n), check.as<int>());
+        CountLaunch();
+        std::vector<int> got(n), want(n);
+        HG_CUDA(cudaMemcpyAsync(got.data(), ws_->d_lattice.as<int>() + static_cast<size_t>(pd[p].scan_begin) * per_scan_,
+                                n * sizeof(int), cudaMemcpyDeviceToHost, stream_));
+        HG_CUDA(cudaMemcpyAsync(want.data(), check.p, n * sizeof(int), cudaMemcpyDeviceToHost, stream_));
+        HG_CUDA(cudaStreamSynchronize(stream_));
+        for (size_t i = 0; i < n; ++i) {
+          if (got[i] != want[i]) {
+            SetError("HG_LATTICE_CHECK: lattice sum " + std::to_string(i) + " of problem " + std::to_string(p) + " is " +
+                     std::to_string(got[i]) + ", the brick-table kernel gives " + std::to_string(want[i]));
+            return HG_ERR_CUDA;
+          }
+        }
+      }
+    }
     // ---- dive
     ArgmaxPerScanKernel<<<(total_scans_ * 32 + 255) / 256, 256, 0, stream_>>>(s);
     CountLaunch();

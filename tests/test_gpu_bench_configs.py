@@ -160,18 +160,15 @@ def test_c3_as_benchmarked(oracle, hg, bench_world):
             same(r, want)
             hits += 1
     assert hits >= 8
-    # a full-submap search at N = 20480 exercises the residue-row kernel's 32-bit accumulator variant
+    # a full-submap search at N = 20480 runs the residue-row kernel's 32-bit accumulator variant over the full
+    # window (17^3 lattice candidates per kept scan x 20480 points): every sum against the brick-table kernel
     os.environ["HG_LATTICE_CHECK"] = "1"
-    os.environ["HG_SEARCH_HOST_REPLAY"] = "1"
     try:
-        sweep = dict(big["opts"])
-        sweep["angular_search_window"] = 0.05
-        gm3 = hg.Fcsm(bench_world["g_hi"], bench_world["g_lo"], big["submap_hist"], **sweep)
-        r = gm3.match(offs[0], big["submap"], big["high"], big["low"], big["hist"], min_score=big["min_score"])
-        assert np.isfinite(r["score"])
+        r = gm2.match(big["node"], big["submap"], big["high"], big["low"], big["hist"], min_score=big["min_score"],
+                      full=True)
     finally:
         os.environ.pop("HG_LATTICE_CHECK", None)
-        os.environ.pop("HG_SEARCH_HOST_REPLAY", None)
+    assert r["found"] == 1.0 and r["num_lattice"] > 100000 and abs(r["tx"] - big["origin"][0]) < 0.3
 
 
 def test_c5_constraints_against_the_oracle(oracle, hg, bench_world):
