@@ -6,8 +6,12 @@ Metric M1 (headline `value`): scan-to-TSDF residual + Jacobian points/s on confi
 one step = one Evaluate of 64 two-pose interpolated multi-resolution TSDF residual blocks
 (InterpolatedMultiResolutionTSDFSpaceCostFunction3D) over 8 control poses, 6.4 M points,
 residuals + all four Jacobian blocks written in Ceres' layout.
-Metric M2 (reported in `correlative`): correlative candidates scored/s on config C4
-(MatchFullSubmap, lowest-resolution level), sharded by discrete scan over the ranks.
+Metric M2 (reported in `correlative`): correlative candidates scored/s on config C4 (MatchFullSubmap at
+pose_graph.lua's thresholds, discrete scans dealt over the ranks; the timed region includes the NCCL exchange of
+the dive bound and of the best records) in two variants, rotational prefilter on ("configured") and off ("full
+sweep", the ~8 M-candidate stress case the value and the roofline are quoted on); `local_search` = C3 (batched local
+Match, 100 node poses at N = 2048 and 10 at N = 20480); `constraint_batch` = C5 (10 000 pairs). Selected candidates
+are asserted against the CPU oracle's frozen answers (tests/golden/c4_golden.json).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
