@@ -25,7 +25,9 @@ def main():
     N = int(w["offsets"][-1])
     g_hi = hg.Grid.tsdf(bench.HI_RES, bench.REL_TRUNC, bench.MAX_WEIGHT, *w["hi"])
     g_lo = hg.Grid.tsdf(bench.LO_RES, bench.REL_TRUNC, bench.MAX_WEIGHT, *w["lo"])
-    batch = hg.Batch("interpolated_multires_tsdf", w["points"], w["offsets"], w["scales"], [g_hi, g_lo], w["ratios"])
+    make_batch = lambda: hg.Batch("interpolated_multires_tsdf", w["points"], w["offsets"], w["scales"], [g_hi, g_lo],
+                                  w["ratios"])
+    batch = make_batch()
     dev = torch.device("cuda", 0)
     outs = [torch.empty(N * k, dtype=torch.float64, device=dev) for k in (1, 3, 4, 3, 4)]
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
@@ -34,6 +36,7 @@ def main():
     stream = torch.cuda.current_stream()
 
     def step():
+        nonlocal batch
         batch.evaluate_raw(poses.ctypes.data, len(poses), i0.ctypes.data, i1.ctypes.data, True,
                            *[o.data_ptr() for o in outs], stream.cuda_stream)
 
@@ -47,7 +50,8 @@ def main():
         for cfg in configs:
             for kv in cfg.split():
                 k, v = kv.split("=")
-                os.environ[k] = v  # note: HG_TILE_OUT is read when the batch is created, not per call
+                os.environ[k] = v
+            batch = make_batch()  # HG_TILE_OUT is read when the batch is created
             for o in outs:
                 o.zero_()
             for _ in range(1 if once else 3):
