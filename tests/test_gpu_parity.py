@@ -1055,3 +1055,36 @@ def test_scan_matcher_evaluate(oracle, hg, world, grids):
         assert np.abs(g1 - g0).max() <= 1e-7 * max(1.0, np.abs(g0).max())
         assert abs(c1 - 0.5 * float(r1 @ r1)) <= 1e-12 * max(1.0, c1)
         assert np.abs(r1[-3:]).max() < 1e-15  # the rotation delta vanishes at the pose it is anchored to
+
+
+def test_device_search_equals_oracle_across_pyramid_shapes(oracle, hg, world):
+    """The device-resident search prunes every subtree that scores below the greedy dive's bound, which is only
+    right if a parent's score bounds its children's at every pyramid shape (half-resolution levels included;
+    the fold ((c + start) >> e) - (start >> e) is designed, not proven, to keep that). Randomised check over
+    depths, full-resolution depths, windows and node poses: the selected candidate equals the oracle's depth-first
+    search, which does not prune that way; the host replay in strict order agrees too."""
+    rng = np.random.RandomState(77)
+    hi, lo, hist = node_inputs(world, n_high=400, n_low=100)
+    submap = np.array([0, 0, 0, 1, 0, 0, 0], float)
+    truth_yaw = 2 * np.arctan2(world["truth"][6], world["truth"][3])
+    submap_hist = oracle.rotate_histogram(hist, np.float32(truth_yaw))
+    checked = found = 0
+    for depth, frd in [(3, 1), (4, 1), (4, 2), (5, 2), (5, 3), (6, 2), (6, 4), (7, 3), (5, 5)]:
+        for grids in (("tsdf_hi", "tsdf_lo"), ("prob", "prob_lo")):
+            opts = dict(branch_and_bound_depth=depth, full_resolution_depth=frd, use_rotational_scan_matcher=False,
+                        min_low_resolution_score=0.25, linear_xy_search_window=float(rng.uniform(0.8, 2.5)),
+                        linear_z_search_window=float(rng.uniform(0.2, 0.7)), angular_search_window=0.1)
+            om = oracle.Fcsm(world["o_" + grids[0]], world["o_" + grids[1]], submap_hist, **opts)
+            gm = hg.Fcsm(world["g_" + grids[0]], world["g_" + grids[1]], submap_hist, **opts)
+            gs = hg.Fcsm(world["g_" + grids[0]], world["g_" + grids[1]], submap_hist, strict_visit_order=1, **opts)
+            for trial in range(2):
+                node = perturbed(world["truth"], rng, 0.6, 0.05)
+                min_score = float(rng.choice([0.15, 0.3]))
+                r0 = om.match(node, submap, hi, lo, hist, min_score=min_score)
+                r1 = gm.match(node, submap, hi, lo, hist, min_score=min_score)
+                r2 = gs.match(node, submap, hi, lo, hist, min_score=min_score)
+                assert_same_match(r0, r1)
+                assert_same_match(r0, r2)
+                checked += 1
+                found += int(r0["found"])
+    assert checked == 36 and found >= 18
