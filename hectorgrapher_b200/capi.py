@@ -104,6 +104,7 @@ SYMBOLS = {
     "hg_grid_size": (c_i, [vp]),
     "hg_grid_num_bricks": (c_i64, [vp]),
     "hg_grid_lookup": (c_i, [vp, c_i, c_i64, vp, vp]),
+    "hg_grid_interpolated_weight": (c_i, [vp, c_i64, vp, vp]),
     "hg_get_cell_index": (c_i, [c_f, c_i64, vp, vp]),
     "hg_cost_create": (c_i, [c_i, c_d, vp, c_i, c_i, vp, c_i, c_d, vp]),
     "hg_cost_destroy": (None, [vp]),
@@ -256,6 +257,13 @@ class Grid:
         out = np.zeros(len(xyz), np.float32)
         code = {"probability": 0, "tsd": 1, "weight": 2}[what]
         _check(lib().hg_grid_lookup(self.h, code, len(xyz), _p(xyz), _p(out)))
+        return out
+
+    def interpolated_weight(self, xyz):
+        """InterpolatedTSDF::GetWeight (interpolated_tsdf.h:129-156) at real-valued points."""
+        xyz = _f64(xyz).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float64)
+        _check(lib().hg_grid_interpolated_weight(self.h, len(xyz), _p(xyz), _p(out)))
         return out
 
     @staticmethod

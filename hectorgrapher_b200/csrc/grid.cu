@@ -11,6 +11,7 @@
 #include <unordered_map>
 
 #include "device_math.cuh"
+#include "interpolation.cuh"
 
 namespace hg {
 
@@ -206,6 +207,40 @@ __global__ void LookupKernel(const GridDev g, const int what, const int64_t n,
   out[i] = v;
 }
 
+// InterpolatedTSDF::GetWeight (interpolated_tsdf.h:129-156): plain trilinear blend of the eight
+// corner weights around the lower voxel, z then y then x, each step (b - a) * n + a in double with
+// no fused multiply-add; the normalised coordinates are true divisions (the reference's double
+// instantiation). InterpolatedMultiResolutionTSDF::GetWeight
+// (interpolated_multi_resolution_tsdf.h:139-171) returns from the first iteration of its loop, so
+// it is this lookup on the finest grid of the pyramid.
+__global__ void InterpolatedWeightKernel(const GridDev g, const int64_t n, const double* __restrict__ p,
+                                         double* __restrict__ out) {
+  const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (i >= n) return;
+  const double x = p[3 * i], y = p[3 * i + 1], z = p[3 * i + 2];
+  double x1, y1, z1, x2, y2, z2;
+  int ix, iy, iz;
+  LowerVoxel(g, x, &x1, &x2, &ix);
+  LowerVoxel(g, y, &y1, &y2, &iy);
+  LowerVoxel(g, z, &z1, &z2, &iz);
+  double q[8];  // corner order 111,112,121,122,211,212,221,222
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const ushort2 t = LoadTsdf(g.table, ix + (k >> 2), iy + ((k >> 1) & 1), iz + (k & 1));
+    q[k] = static_cast<double>(Decode(g.b, t.y));
+  }
+  const double nx = __ddiv_rn(__dsub_rn(x, x1), __dsub_rn(x2, x1));
+  const double ny = __ddiv_rn(__dsub_rn(y, y1), __dsub_rn(y2, y1));
+  const double nz = __ddiv_rn(__dsub_rn(z, z1), __dsub_rn(z2, z1));
+  const double q11 = __dadd_rn(__dmul_rn(__dsub_rn(q[1], q[0]), nz), q[0]);
+  const double q12 = __dadd_rn(__dmul_rn(__dsub_rn(q[3], q[2]), nz), q[2]);
+  const double q21 = __dadd_rn(__dmul_rn(__dsub_rn(q[5], q[4]), nz), q[4]);
+  const double q22 = __dadd_rn(__dmul_rn(__dsub_rn(q[7], q[6]), nz), q[6]);
+  const double q1 = __dadd_rn(__dmul_rn(__dsub_rn(q12, q11), ny), q11);
+  const double q2 = __dadd_rn(__dmul_rn(__dsub_rn(q22, q21), ny), q21);
+  out[i] = __dadd_rn(__dmul_rn(__dsub_rn(q2, q1), nx), q1);
+}
+
 __global__ void CellIndexKernel(const float resolution, const float inv_resolution, const int64_t n,
                                 const float* __restrict__ p, int32_t* __restrict__ out) {
   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
@@ -331,6 +366,26 @@ int hg_grid_lookup(const hg_grid* grid, int what, int64_t n, const int32_t* xyz,
   HG_CUDA(cudaGetLastError());
   HG_CUDA(cudaMemcpy(out, d_out, n * sizeof(float), cudaMemcpyDeviceToHost));
   cudaFree(d_xyz);
+  cudaFree(d_out);
+  return HG_OK;
+}
+
+int hg_grid_interpolated_weight(const hg_grid* grid, int64_t n, const double* points_xyz, double* out) {
+  HG_REQUIRE(grid != nullptr && n >= 0, "hg_grid_interpolated_weight: bad arguments");
+  HG_REQUIRE(grid->dev.kind != kGridProb, "hg_grid_interpolated_weight: needs a TSDF grid");
+  if (n == 0) return HG_OK;
+  HG_REQUIRE(points_xyz != nullptr && out != nullptr, "hg_grid_interpolated_weight: null buffer");
+  HG_ON_DEVICE(grid->device);
+  double* d_p = nullptr;
+  double* d_out = nullptr;
+  HG_CUDA(cudaMalloc(&d_p, n * 3 * sizeof(double)));
+  HG_CUDA(cudaMalloc(&d_out, n * sizeof(double)));
+  HG_CUDA(cudaMemcpy(d_p, points_xyz, n * 3 * sizeof(double), cudaMemcpyHostToDevice));
+  InterpolatedWeightKernel<<<static_cast<unsigned>((n + 255) / 256), 256>>>(grid->dev, n, d_p, d_out);
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  HG_CUDA(cudaMemcpy(out, d_out, n * sizeof(double), cudaMemcpyDeviceToHost));
+  cudaFree(d_p);
   cudaFree(d_out);
   return HG_OK;
 }

@@ -77,6 +77,14 @@ int64_t hg_grid_num_bricks(const hg_grid* grid);
  * device. what: 0 probability, 1 tsd, 2 weight. Host pointers. */
 int hg_grid_lookup(const hg_grid* grid, int what, int64_t n, const int32_t* xyz, float* out);
 
+/* InterpolatedTSDF::GetWeight (interpolated_tsdf.h:129-156) at real-valued
+ * points (world frame of the grid, doubles), on the device: the trilinear blend
+ * of the eight corner weights around the lower voxel. The multi-resolution
+ * variant (interpolated_multi_resolution_tsdf.h:139-171) returns from the first
+ * iteration of its loop, i.e. it is this call on the pyramid's finest grid.
+ * TSDF grids only. Host pointers. */
+int hg_grid_interpolated_weight(const hg_grid* grid, int64_t n, const double* points_xyz, double* out);
+
 /* HybridGridBase::GetCellIndex (hybrid_grid_base.h:428-433) on the device. */
 int hg_get_cell_index(float resolution, int64_t n, const float* points_xyz, int32_t* out_xyz);
 

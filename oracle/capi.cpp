@@ -241,6 +241,12 @@ void orc_interpolate(void* g, int n, const double* xyz, double* out) {
   }
 }
 
+void orc_interpolate_weight(void* g, int n, const double* xyz, double* out) {
+  auto* h = static_cast<GridHandle*>(g);
+  InterpolatedTSDF it(*h->tsdf);
+  for (int i = 0; i < n; ++i) out[i] = it.GetWeight(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+}
+
 // ---- cost functions ---------------------------------------------------------
 void* orc_cost_new(int kind, double scaling_factor, const float* pts, int n, int stride,
                    void* const* grids, int num_grids, double interpolation_ratio) {

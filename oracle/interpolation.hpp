@@ -170,6 +170,30 @@ class InterpolatedTSDF {
     return BlendTsd(-0.3, w, q, nx, ny, nz);
   }
 
+  // interpolated_tsdf.h:129-156: trilinear blend of the corner weights, z then
+  // y then x. interpolated_multi_resolution_tsdf.h:139-171 is the same lookup
+  // on the finest grid (its loop returns in the first iteration).
+  template <typename T>
+  T GetWeight(const T& x, const T& y, const T& z) const {
+    double x1, y1, z1, x2, y2, z2;
+    InterpolationDataPoints(tsdf_, ScalarPart(x), ScalarPart(y), ScalarPart(z), &x1, &y1, &z1,
+                            &x2, &y2, &z2);
+    const Array3i i1 = tsdf_.GetCellIndex(
+        Vector3f(static_cast<float>(x1), static_cast<float>(y1), static_cast<float>(z1)));
+    double w[8];
+    FetchWeights(tsdf_, i1, w);
+    const T nx = (x - x1) / (x2 - x1);
+    const T ny = (y - y1) / (y2 - y1);
+    const T nz = (z - z1) / (z2 - z1);
+    const T q11 = (w[1] - w[0]) * nz + w[0];
+    const T q12 = (w[3] - w[2]) * nz + w[2];
+    const T q21 = (w[5] - w[4]) * nz + w[4];
+    const T q22 = (w[7] - w[6]) * nz + w[6];
+    const T q1 = (q12 - q11) * ny + q11;
+    const T q2 = (q22 - q21) * ny + q21;
+    return (q2 - q1) * nx + q1;
+  }
+
  private:
   const HybridGridTSDF& tsdf_;
 };

@@ -64,6 +64,7 @@ def lib():
         L.orc_insert_occupancy.argtypes = [vp, vp, c_i, vp, c_f, c_f, c_i]
         L.orc_insert_tsdf.argtypes = [vp, vp, c_i, vp, c_d, c_d, c_i, c_d, c_d, c_d, c_d, c_d]
         L.orc_interpolate.argtypes = [vp, c_i, vp, vp]
+        L.orc_interpolate_weight.argtypes = [vp, c_i, vp, vp]
         L.orc_cost_new.restype = vp
         L.orc_cost_new.argtypes = [c_i, c_d, vp, c_i, c_i, vp, c_i, c_d]
         L.orc_cost_free.argtypes = [vp]
@@ -220,6 +221,12 @@ class Grid:
         xyz = _f64(xyz).reshape(-1, 3)
         out = np.zeros(len(xyz), np.float64)
         lib().orc_interpolate(self.h, len(xyz), _p(xyz), _p(out))
+        return out
+
+    def interpolate_weight(self, xyz):
+        xyz = _f64(xyz).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float64)
+        lib().orc_interpolate_weight(self.h, len(xyz), _p(xyz), _p(out))
         return out
 
 

@@ -102,6 +102,28 @@ def test_grid_lookup_bit_exact(oracle, hg, world):
             assert (a.view(np.uint32) == b.view(np.uint32)).all(), (name, what)
 
 
+def test_interpolated_weight_bit_exact(oracle, hg, world):
+    # InterpolatedTSDF::GetWeight (interpolated_tsdf.h:129-156; the multi-resolution
+    # variant, interpolated_multi_resolution_tsdf.h:139-171, is this on the finest grid).
+    rng = np.random.RandomState(11)
+    for name in ["tsdf_hi", "tsdf_lo"]:
+        og, gg = world["o_" + name], world["g_" + name]
+        res = 0.10 if name == "tsdf_hi" else 0.45
+        ex = og.export()[0]
+        centres = ex[rng.randint(0, len(ex), 20000)].astype(np.float64) * np.float32(res)
+        near = centres + rng.uniform(-1.5 * res, 1.5 * res, size=centres.shape)
+        on_centre = centres[:2000]                     # exactly on a cell centre (n = 0 or 1)
+        on_face = centres[2000:4000] + 0.5 * np.float32(res)   # cell boundary: lround ties
+        far = rng.uniform(-900, 900, size=(1000, 3))   # no brick: all weights 0
+        q = np.concatenate([near, on_centre, on_face, far])
+        a, b = gg.interpolated_weight(q), og.interpolate_weight(q)
+        assert (a.view(np.uint64) == b.view(np.uint64)).all(), name
+        assert (a[:20000] > 0).mean() > 0.5 and (a[-1000:] == 0).all()
+    with pytest.raises(Exception):
+        world["g_prob"].interpolated_weight([[0.0, 0.0, 0.0]])
+    assert len(world["g_tsdf_hi"].interpolated_weight(np.zeros((0, 3)))) == 0
+
+
 def test_grid_edge_cases(oracle, hg):
     # empty grid: everything reads the default
     g = hg.Grid.prob(0.1, np.zeros((0, 3), np.int32), np.zeros(0, np.uint16))

@@ -128,6 +128,21 @@ def _interp_fixture(oracle):
     return g
 
 
+def test_interpolated_tsdf_weight(oracle):
+    """interpolated_tsdf.h:129-156: at a cell centre the blend is that voxel's weight,
+    halfway between two centres it is their mean, far from every voxel it is 0.
+    (The reference has no test of its own for GetWeight; these are the properties
+    of the trilinear formula.)"""
+    g = oracle.Grid.tsdf(1.0, 0.5, 100.0)
+    g.set_cell([[1, 0, 1], [2, 0, 1]], [0.1, 0.2], [8.0, 24.0])
+    w = g.lookup("weight", [[1, 0, 1], [2, 0, 1]]).astype(np.float64)
+    got = g.interpolate_weight([[1.0, 0.0, 1.0], [2.0, 0.0, 1.0], [1.5, 0.0, 1.0], [1.0, 0.5, 1.0], [40., 40., 40.]])
+    assert got[0] == w[0] and got[1] == w[1]
+    assert abs(got[2] - 0.5 * (w[0] + w[1])) < 1e-12
+    assert abs(got[3] - 0.5 * w[0]) < 1e-12
+    assert got[4] == 0.0
+
+
 def test_interpolated_grid_at_grid_points(oracle):
     """internal/3d/scan_matching/interpolated_grid_test.cc:52-61."""
     g = _interp_fixture(oracle)
