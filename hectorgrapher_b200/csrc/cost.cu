@@ -44,6 +44,9 @@ struct BlockDev {
   double ct0, ct1;
   double m0[16];
   double m1[16];
+  double s0, s1;  // m0 = s0 I + c q1', m1 = s1 I + c q0' (pose_prep.h)
+  double c[4];
+  double q0[4], q1[4];
   double scale;
   long long point_offset;  // first point of the block in the concatenated cloud / outputs
   int n;
@@ -74,7 +77,7 @@ struct CostArgs {
 
 constexpr int kThreads = 256;
 
-template <int LOOKUP>
+template <int LOOKUP, int LEAN = 0>
 __device__ __forceinline__ ValueGrad Residual(const CostArgs& a, const double scale, const double x,
                                               const double y, const double z) {
   ValueGrad r;
@@ -93,7 +96,10 @@ __device__ __forceinline__ ValueGrad Residual(const CostArgs& a, const double sc
     bool found = false;
 #pragma unroll
     for (int l = 0; l < HG_MAX_PYRAMID_LEVELS; ++l) {
-      if (l < a.num_grids && !found) found = LookupTsdfLevel<true>(a.grids[l], x, y, z, &t);
+      if (l < a.num_grids && !found) {
+        found = LEAN ? LookupTsdfLevelAllObserved(a.grids[l], x, y, z, &t)
+                     : LookupTsdfLevel<true>(a.grids[l], x, y, z, &t);
+      }
     }
     if (!found) {  // interpolated_multi_resolution_tsdf.h:136
       t.v = static_cast<double>(a.grids[0].min_tsd);
@@ -113,8 +119,8 @@ __host__ __device__ constexpr int NumNormalTerms(int n) { return n * (n + 1) / 2
 // Terms the kernel accumulates per tile: those of the 7-vector u (see CostKernel).
 constexpr int kNormalTermsU = NumNormalTerms(7);
 
-template <int LOOKUP, bool TWO_POSE, bool NORMAL_EQ>
-__global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const CostArgs a) {
+template <int LOOKUP, bool TWO_POSE, bool NORMAL_EQ, int LEAN = 0>
+__global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : (LEAN == 2 ? 3 : (LEAN == 3 ? 2 : 4))) CostKernel(const CostArgs a) {
   constexpr int NC = TWO_POSE ? 14 : 7;
   __shared__ BlockDev sb;
   extern __shared__ double red[];  // NORMAL_EQ only: kNormalTermsU x kThreads
@@ -168,10 +174,14 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
       const long long gi = sb.point_offset + i;
       const double qw = sb.q[0], qx = sb.q[1], qy = sb.q[2], qz = sb.q[3];
       const WorldPoint wp = TransformPoint(qw, qx, qy, qz, sb.t[0], sb.t[1], sb.t[2], px, py, pz);
-      const ValueGrad v = Residual<LOOKUP>(a, sb.scale, wp.x, wp.y, wp.z);
+      const ValueGrad v = Residual<LOOKUP, LEAN>(a, sb.scale, wp.x, wp.y, wp.z);
       res = v.v;
       double aw, ax, ay, az;
-      RotationTerms(qw, qx, qy, qz, px, py, pz, wp, v, &aw, &ax, &ay, &az);
+      if (LEAN) {
+        RotationTermsClosedForm(qw, qx, qy, qz, px, py, pz, wp, v, &aw, &ax, &ay, &az);
+      } else {
+        RotationTerms(qw, qx, qy, qz, px, py, pz, wp, v, &aw, &ax, &ay, &az);
+      }
 
       if (NORMAL_EQ) {
         const double u[7] = {v.gx, v.gy, v.gz, aw, ax, ay, az};
@@ -189,10 +199,21 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : 4) CostKernel(const 
       } else {
         J[0] = v.gx * sb.ct0; J[1] = v.gy * sb.ct0; J[2] = v.gz * sb.ct0;
         J[7] = v.gx * sb.ct1; J[8] = v.gy * sb.ct1; J[9] = v.gz * sb.ct1;
+        if (LEAN) {
+          // (aw ax ay az) m0 and m1 with m0 = s0 I + c q1', m1 = s1 I + c q0' (pose_prep.h)
+          const double ac = aw * sb.c[0] + ax * sb.c[1] + ay * sb.c[2] + az * sb.c[3];
+          const double A[4] = {aw, ax, ay, az};
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          J[3 + j] = aw * sb.m0[j] + ax * sb.m0[4 + j] + ay * sb.m0[8 + j] + az * sb.m0[12 + j];
-          J[10 + j] = aw * sb.m1[j] + ax * sb.m1[4 + j] + ay * sb.m1[8 + j] + az * sb.m1[12 + j];
+          for (int j = 0; j < 4; ++j) {
+            J[3 + j] = sb.s0 * A[j] + ac * sb.q1[j];
+            J[10 + j] = sb.s1 * A[j] + ac * sb.q0[j];
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            J[3 + j] = aw * sb.m0[j] + ax * sb.m0[4 + j] + ay * sb.m0[8 + j] + az * sb.m0[12 + j];
+            J[10 + j] = aw * sb.m1[j] + ax * sb.m1[4 + j] + ay * sb.m1[8 + j] + az * sb.m1[12 + j];
+          }
         }
       }
 
@@ -464,7 +485,15 @@ int LaunchCost(const hg_batch* B, const CostArgs& args, int num_tiles, cudaStrea
     }                                                                                           \
     CostKernel<L, T, NE><<<num_tiles, kThreads, smem, stream>>>(args);                          \
   } while (0)
-  if (B->lookup == 0) {
+  const char* lean_env = std::getenv("HG_COST_LEAN");
+  const int lean = lean_env == nullptr ? 1 : std::atoi(lean_env);
+  if (lean == 1 && !NE && B->lookup == 2 && B->two_pose) {
+    CostKernel<2, true, false, 1><<<num_tiles, kThreads, smem, stream>>>(args);
+  } else if (lean == 2 && !NE && B->lookup == 2 && B->two_pose) {
+    CostKernel<2, true, false, 2><<<num_tiles, kThreads, smem, stream>>>(args);
+  } else if (lean == 3 && !NE && B->lookup == 2 && B->two_pose) {
+    CostKernel<2, true, false, 3><<<num_tiles, kThreads, smem, stream>>>(args);
+  } else if (B->lookup == 0) {
     if (B->two_pose) HG_LAUNCH(0, true); else HG_LAUNCH(0, false);
   } else if (B->lookup == 1) {
     if (B->two_pose) HG_LAUNCH(1, true); else HG_LAUNCH(1, false);
@@ -528,6 +557,11 @@ int PrepareBlocks(const hg_batch* B, const double* poses, int num_poses, const i
     d.ct1 = p.ct1;
     std::memcpy(d.m0, p.m0, sizeof(d.m0));
     std::memcpy(d.m1, p.m1, sizeof(d.m1));
+    d.s0 = p.s0;
+    d.s1 = p.s1;
+    std::memcpy(d.c, p.c, sizeof(d.c));
+    std::memcpy(d.q0, p.q0, sizeof(d.q0));
+    std::memcpy(d.q1, p.q1, sizeof(d.q1));
     d.scale = B->scales[b];
     d.point_offset = B->offsets[b];
     d.n = static_cast<int>(B->offsets[b + 1] - B->offsets[b]);
@@ -551,7 +585,13 @@ int WaitForAllPoints(const hg_batch* B, cudaStream_t stream) {
 CostArgs BaseArgs(const hg_batch* B) {
   CostArgs a;
   std::memset(&a, 0, sizeof(a));
-  for (int i = 0; i < B->num_grids; ++i) a.grids[i] = B->grids[i]->dev;
+  for (int i = 0; i < B->num_grids; ++i) {
+    const char* env = std::getenv("HG_NO_STENCILS");
+    const bool off = env != nullptr && std::atoi(env) != 0;
+    if (B->lookup == 2 && B->two_pose && !off) EnsureStencils(B->grids[i]);
+    a.grids[i] = B->grids[i]->dev;
+    if (off) a.grids[i].stencils = nullptr;
+  }
   a.num_grids = B->num_grids;
   a.points = B->d_points;
   a.stride = B->stride;
@@ -1290,6 +1330,11 @@ extern "C" int hg_cost_normal_equations_static(const hg_cost* cost, const double
   block.ct1 = p.ct1;
   std::memcpy(block.m0, p.m0, sizeof(block.m0));
   std::memcpy(block.m1, p.m1, sizeof(block.m1));
+  block.s0 = p.s0;
+  block.s1 = p.s1;
+  std::memcpy(block.c, p.c, sizeof(block.c));
+  std::memcpy(block.q0, p.q0, sizeof(block.q0));
+  std::memcpy(block.q1, p.q1, sizeof(block.q1));
   block.scale = B->scales[0];
   block.point_offset = 0;
   block.n = static_cast<int>(B->num_points);

@@ -8,6 +8,7 @@
 //   mapping/value_conversion_tables.cc:29-51, 2d/tsd_value_converter.cc:22-32  decoding constants
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 #include <unordered_map>
 
 #include "device_math.cuh"
@@ -241,6 +242,15 @@ __global__ void InterpolatedWeightKernel(const GridDev g, const int64_t n, const
   out[i] = __dadd_rn(__dmul_rn(__dsub_rn(q2, q1), nx), q1);
 }
 
+__global__ void PackStencilsKernel(const float* __restrict__ decoded, const int64_t n, float4* __restrict__ out) {
+  const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (i >= n) return;
+  const int v = static_cast<int>(i & 511);
+  const float* base = decoded + (i >> 9) * kApronBrickVoxels + (((v >> 6) * 9 + ((v >> 3) & 7)) * 9 + (v & 7));
+  out[2 * i] = make_float4(base[0], base[81], base[9], base[90]);
+  out[2 * i + 1] = make_float4(base[1], base[82], base[10], base[91]);
+}
+
 __global__ void CellIndexKernel(const float resolution, const float inv_resolution, const int64_t n,
                                 const float* __restrict__ p, int32_t* __restrict__ out) {
   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
@@ -265,6 +275,35 @@ static int BuildDecodedBricks(hg_grid* g) {
 }
 
 
+namespace hg {
+
+static std::mutex g_stencil_mutex;
+
+int EnsureStencils(const hg_grid* grid_const) {
+  hg_grid* g = const_cast<hg_grid*>(grid_const);
+  std::lock_guard<std::mutex> lock(g_stencil_mutex);
+  if (g->dev.stencils != nullptr || g->num_all_bricks == 0 || g->d_decoded == nullptr) return HG_OK;
+  HG_ON_DEVICE(g->device);
+  const int64_t n = g->num_all_bricks * 512;
+  HG_CUDA(cudaMalloc(&g->d_stencils, static_cast<size_t>(n) * 32));
+  PackStencilsKernel<<<static_cast<unsigned>((n + 255) / 256), 256>>>(static_cast<const float*>(g->d_decoded), n,
+                                                                    static_cast<float4*>(g->d_stencils));
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
+  HG_CUDA(cudaDeviceSynchronize());
+  g->dev.stencils = static_cast<const float4*>(g->d_stencils);
+  return HG_OK;
+}
+
+void DropStencils(hg_grid* g) {
+  std::lock_guard<std::mutex> lock(g_stencil_mutex);
+  if (g->d_stencils) cudaFree(g->d_stencils);
+  g->d_stencils = nullptr;
+  g->dev.stencils = nullptr;
+}
+
+}  // namespace hg
+
 extern "C" {
 
 const char* hg_last_error(void) { return hg::t_error.c_str(); }
@@ -280,7 +319,7 @@ int hg_grid_upload_prob(float resolution, int grid_size, int64_t num_voxels, con
                         const uint16_t* values, hg_grid** out) {
   HG_REQUIRE(out != nullptr && resolution > 0.f && num_voxels >= 0, "hg_grid_upload_prob: bad arguments");
   HG_REQUIRE(num_voxels == 0 || (xyz != nullptr && values != nullptr), "hg_grid_upload_prob: null voxel arrays");
-  hg_grid* g = new hg_grid;
+  hg_grid* g = new hg_grid();
   HG_CUDA(cudaGetDevice(&g->device));
   g->dev.kind = kGridProb;
   g->dev.resolution = resolution;
@@ -311,7 +350,7 @@ int hg_grid_upload_tsdf(float resolution, float relative_truncation_distance, fl
              "hg_grid_upload_tsdf: bad arguments");
   HG_REQUIRE(num_voxels == 0 || (xyz != nullptr && tsd_values != nullptr && weight_values != nullptr),
              "hg_grid_upload_tsdf: null voxel arrays");
-  hg_grid* g = new hg_grid;
+  hg_grid* g = new hg_grid();
   HG_CUDA(cudaGetDevice(&g->device));
   g->dev.kind = kGridTsdf;
   g->dev.resolution = resolution;
@@ -344,6 +383,7 @@ void hg_grid_destroy(hg_grid* grid) {
   if (grid->d_index) cudaFree(grid->d_index);
   if (grid->d_bricks) cudaFree(grid->d_bricks);
   if (grid->d_decoded) cudaFree(grid->d_decoded);
+  if (grid->d_stencils) cudaFree(grid->d_stencils);
   DestroyGridMutable(grid);
   delete grid;
 }

@@ -142,6 +142,12 @@ struct GridDev {
   // TSD of an observed voxel, NaN for an unobserved one (weight value 0 or 1) —
   // the cost functors never read the TSD of an unobserved voxel.
   const float* decoded;
+  // Optional third copy for the Jacobian kernels (EnsureStencils, grid.cu): for every voxel of
+  // every brick the 2x2x2 stencil whose lower corner it is, eight decoded floats in the
+  // reference's corner order (111,112,121,122,211,212,221,222) = one 32-byte sector, so an
+  // interpolated lookup is two 16-byte loads from one sector instead of eight 4-byte loads from
+  // four to eight. Null until a cost function asks for it; dropped when the grid is written.
+  const float4* stencils;
   float resolution;
   float inv_resolution;     // fl(1 / resolution): fast path of the exact cell-index computation
   double inv_resolution_d;  // 1.0 / double(resolution): seed for the reciprocal of the cell width
@@ -169,6 +175,7 @@ struct hg_grid {
   void* d_index = nullptr;
   void* d_bricks = nullptr;
   void* d_decoded = nullptr;
+  void* d_stencils = nullptr;
   // Host copy of the brick coordinates (brick id -> brick coords), used to
   // derive the precomputation levels' brick sets.
   std::vector<int32_t> brick_coords;
@@ -177,6 +184,10 @@ struct hg_grid {
 
 namespace hg {
 void DestroyGridMutable(hg_grid* grid);  // insert.cu
+// grid.cu: builds GridDev::stencils if it is missing (thread-safe; the grid is logically const).
+int EnsureStencils(const hg_grid* grid);
+// Frees GridDev::stencils (the grid's voxels are about to change).
+void DropStencils(hg_grid* grid);
 
 // scan_match.cu: CeresScanMatcher3D::Match solved entirely on the device (arguments of
 // hg_scan_match). HG_ERR_LIMIT when the problem does not fit the kernel.

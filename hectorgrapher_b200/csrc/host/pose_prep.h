@@ -86,6 +86,13 @@ struct BlockPose {
   double ct0, ct1;   // d t / d t0 = ct0 I,  d t / d t1 = ct1 I
   double m0[16];     // d q_i / d q0_j, row-major [i][j]
   double m1[16];     // d q_i / d q1_j
+  // The same two matrices in the form slerp gives them: q = s0 q0 + s1 q1 with s0, s1 functions
+  // of d = q0 . q1 only, so m0 = s0 I + c q1', m1 = s1 I + c q0' with c = s0'(d) q0 + s1'(d) q1.
+  // A row vector a times them is s0 a + (a . c) q1' and s1 a + (a . c) q0': 20 multiply-adds per
+  // point in the Jacobian kernel instead of 32.
+  double s0, s1;
+  double c[4];
+  double q0[4], q1[4];
 };
 
 inline BlockPose OnePose(const double* t, const double* q) {
@@ -97,6 +104,13 @@ inline BlockPose OnePose(const double* t, const double* q) {
   for (int i = 0; i < 16; ++i) {
     p.m0[i] = (i % 5 == 0) ? 1.0 : 0.0;
     p.m1[i] = 0.0;
+  }
+  p.s0 = 1.0;
+  p.s1 = 0.0;
+  for (int i = 0; i < 4; ++i) {
+    p.c[i] = 0.0;
+    p.q0[i] = q[i];
+    p.q1[i] = 0.0;
   }
   return p;
 }
@@ -136,6 +150,21 @@ inline BlockPose TwoPose(const double* t0, const double* q0, const double* t1, c
       p.m0[i * 4 + j] = qi.v[j];
       p.m1[i * 4 + j] = qi.v[4 + j];
     }
+  }
+  // d s / d q0_j = s'(d) q1_j: read s'(d) off the largest component of q1 (a quaternion is never
+  // all zero; in the lerp branch the derivatives are zero).
+  int js = 0;
+  for (int j = 1; j < 4; ++j) {
+    if (std::abs(q1[j]) > std::abs(q1[js])) js = j;
+  }
+  const double ds0 = q1[js] != 0.0 ? s0.v[js] / q1[js] : 0.0;
+  const double ds1 = q1[js] != 0.0 ? s1.v[js] / q1[js] : 0.0;
+  p.s0 = s0.a;
+  p.s1 = s1.a;
+  for (int i = 0; i < 4; ++i) {
+    p.c[i] = ds0 * q0[i] + ds1 * q1[i];
+    p.q0[i] = q0[i];
+    p.q1[i] = q1[i];
   }
   return p;
 }

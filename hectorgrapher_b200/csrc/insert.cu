@@ -656,6 +656,7 @@ int AddBricks(hg_grid* g, const std::vector<uint64_t>& keys, int64_t* added) {
 }
 
 int RebuildReadCopies(hg_grid* g) {
+  DropStencils(g);  // rebuilt from the new decoded bricks by the next cost function that wants them
   GridMutable* m = g->mut;
   if (g->num_all_bricks == 0) return HG_OK;
   if (m->coords.cap == 0) {  // an uploaded grid written to without any new brick

@@ -34,6 +34,42 @@ __device__ __forceinline__ void LowerVoxel(const GridDev& g, const double x, dou
   *index = i;
 }
 
+// The same selection without a branch per axis: q = fl(xf * fl(1/res)) rounded to the nearest
+// integer decides the cell whenever q's fraction is outside the band around one half in which
+// the product and the IEEE quotient can round differently (CellIndexFast, device_math.cuh);
+// there |q - i| < 0.5 strictly, so nearest-even and half-away-from-zero agree. Returns true
+// when the axis needs the exact path (LowerVoxel) instead — the caller takes one branch for
+// all three axes.
+__device__ __forceinline__ bool LowerVoxelNoBranch(const GridDev& g, const double x, double* x1, double* x2,
+                                                   int* index) {
+  const float xf = __double2float_rn(x);
+  const float q = __fmul_rn(xf, g.inv_resolution);
+  const int i = __float2int_rn(q);
+  const float fi = __int2float_rn(i);
+  const float d = __fsub_rn(q, fi);
+  const bool exact_path = !(__fsub_rn(0.5f, fabsf(d)) > __fmul_rn(fabsf(q), 4.8e-7f));
+  const float c = __fmul_rn(fi, g.resolution);
+  const bool above = static_cast<double>(c) > x;
+  const float lower = above ? __fsub_rn(c, g.resolution) : c;
+  *x1 = static_cast<double>(lower);
+  *x2 = static_cast<double>(__fadd_rn(lower, g.resolution));
+  *index = above ? i - 1 : i;
+  return exact_path;
+}
+
+__device__ __forceinline__ void LowerVoxel3(const GridDev& g, const double x, const double y, const double z,
+                                            double* x1, double* y1, double* z1, double* x2, double* y2,
+                                            double* z2, int* ix, int* iy, int* iz) {
+  const bool ex = LowerVoxelNoBranch(g, x, x1, x2, ix);
+  const bool ey = LowerVoxelNoBranch(g, y, y1, y2, iy);
+  const bool ez = LowerVoxelNoBranch(g, z, z1, z2, iz);
+  if (ex | ey | ez) {  // rare: a coordinate within ~5e-7 relative of a cell boundary, or NaN / huge
+    LowerVoxel(g, x, x1, x2, ix);
+    LowerVoxel(g, y, y1, y2, iy);
+    LowerVoxel(g, z, z1, z2, iz);
+  }
+}
+
 // 1 / d for d = x2 - x1, which equals the resolution up to float rounding of the
 // cell centres: two Newton steps from 1 / double(resolution) converge to full
 // double precision (the seed is already within ~1e-7 relative).
@@ -173,6 +209,49 @@ __device__ __forceinline__ ValueGrad BlendTsdf(const double unknown, const bool*
   return r;
 }
 
+// One level of the multi-resolution lookup, the form the Jacobian kernels run: a level is used
+// only when all eight corners are observed (interpolated_multi_resolution_tsdf.h:99-106), i.e.
+// when none of the eight pre-decoded floats is the NaN marker — which is what the sum of the
+// eight says (decoded TSDs are finite, |tsd| <= truncation distance) — and a missing brick
+// is eight unobserved corners. Then all seven blends take the lerp branch: plain trilinear.
+__device__ __forceinline__ bool LookupTsdfLevelAllObserved(const GridDev& g, const double x, const double y,
+                                                           const double z, ValueGrad* out) {
+  double x1, y1, z1, x2, y2, z2;
+  int ix, iy, iz;
+  LowerVoxel3(g, x, y, z, &x1, &y1, &z1, &x2, &y2, &z2, &ix, &iy, &iz);
+  const int id = BrickId(g.table, ix, iy, iz);
+  if (id < 0) return false;
+  float r0, r1, r2, r3, r4, r5, r6, r7;
+  if (g.stencils != nullptr) {
+    const float4* s = g.stencils + 2 * (id * 512 + InBrick(ix, iy, iz));
+    const float4 lo = __ldg(s), hi = __ldg(s + 1);
+    r0 = lo.x; r1 = lo.y; r2 = lo.z; r3 = lo.w;
+    r4 = hi.x; r5 = hi.y; r6 = hi.z; r7 = hi.w;
+  } else {
+    const float* base = g.decoded + (id * kApronBrickVoxels + InApronBrick(ix, iy, iz));
+    r0 = __ldg(base); r1 = __ldg(base + 81); r2 = __ldg(base + 9); r3 = __ldg(base + 90);
+    r4 = __ldg(base + 1); r5 = __ldg(base + 82); r6 = __ldg(base + 10); r7 = __ldg(base + 91);
+  }
+  const float all = ((r0 + r1) + (r2 + r3)) + ((r4 + r5) + (r6 + r7));
+  if (all != all) return false;
+  const double q0 = r0, q1 = r1, q2 = r2, q3 = r3, q4 = r4, q5 = r5, q6 = r6, q7 = r7;
+  const double sx = CellWidthReciprocal(g.inv_resolution_d, x2 - x1);
+  const double sy = CellWidthReciprocal(g.inv_resolution_d, y2 - y1);
+  const double sz = CellWidthReciprocal(g.inv_resolution_d, z2 - z1);
+  const double nx = (x - x1) * sx, ny = (y - y1) * sy, nz = (z - z1) * sz;
+  const double d0 = q1 - q0, d1 = q3 - q2, d2 = q5 - q4, d3 = q7 - q6;
+  const double a0 = d0 * nz + q0, a1 = d1 * nz + q2, a2 = d2 * nz + q4, a3 = d3 * nz + q6;
+  const double b0y = a1 - a0, b1y = a3 - a2;
+  const double b0 = b0y * ny + a0, b0z = (d1 - d0) * ny + d0;
+  const double b1 = b1y * ny + a2, b1z = (d3 - d2) * ny + d2;
+  const double cx = b1 - b0;
+  out->v = cx * nx + b0;
+  out->gx = cx * sx;
+  out->gy = ((b1y - b0y) * nx + b0y) * sy;
+  out->gz = ((b1z - b0z) * nx + b0z) * sz;
+  return true;
+}
+
 // One pyramid level. Returns false when the level must be skipped
 // (multi-resolution rule: any unobserved corner), true otherwise.
 template <bool MULTI>
@@ -275,6 +354,29 @@ __device__ __forceinline__ void RotationTerms(const double qw, const double qx, 
   const double dzy_ = qw * ez1 + uvx + (qz * ez0 - qx * ez2);
   const double dzz_ = qw * ez2 + 0.0 + (qx * ez1 - qy * ez0);
   *az = v.gx * dzx_ + v.gy * dzy_ + v.gz * dzz_;
+}
+
+// The same four numbers in closed form. With u = (qx, qy, qz), w = qw and world = p + w uv +
+// u x uv + t, uv = 2 u x p:
+//   a_w = g . uv
+//   a_u = 2 w (p x g) + 2 [(u . p) g + (g . u) p - 2 (g . p) u]
+// (from g . (e x p) = e . (p x g), (u x p) x g = p (u . g) - u (p . g), p x (g x u) =
+// g (p . u) - u (p . g)); equal to RotationTerms up to rounding, 37 FP64 operations instead of ~50.
+__device__ __forceinline__ void RotationTermsClosedForm(const double qw, const double qx, const double qy,
+                                                        const double qz, const double px, const double py,
+                                                        const double pz, const WorldPoint& w, const ValueGrad& v,
+                                                        double* aw, double* ax, double* ay, double* az) {
+  *aw = v.gx * w.uvx + v.gy * w.uvy + v.gz * w.uvz;
+  const double cx = py * v.gz - pz * v.gy, cy = pz * v.gx - px * v.gz, cz = px * v.gy - py * v.gx;
+  const double up = qx * px + qy * py + qz * pz;
+  const double gu = v.gx * qx + v.gy * qy + v.gz * qz;
+  const double gp2 = -2.0 * (v.gx * px + v.gy * py + v.gz * pz);
+  const double tx = qw * cx + (up * v.gx + gu * px + gp2 * qx);
+  const double ty = qw * cy + (up * v.gy + gu * py + gp2 * qy);
+  const double tz = qw * cz + (up * v.gz + gu * pz + gp2 * qz);
+  *ax = tx + tx;
+  *ay = ty + ty;
+  *az = tz + tz;
 }
 
 }  // namespace hg
