@@ -53,9 +53,13 @@ struct BlockDev {
   int pad;
 };
 
-struct TileDev {
+struct alignas(16) TileDev {
   int block;
-  int start;  // first point of the tile inside its block
+  int start;        // first point of the tile inside its block
+  int count;        // points in the tile
+  int pad;
+  long long first;  // the tile's first point in the concatenated cloud / outputs (block offset + start)
+  long long pad2;
 };
 
 struct CostArgs {
@@ -65,7 +69,6 @@ struct CostArgs {
   int stride;
   const BlockDev* blocks;
   const TileDev* tiles;
-  int tile_points;  // points per tile (multiple of 256)
   double* r;
   double* jt0;
   double* jq0;
@@ -77,7 +80,7 @@ struct CostArgs {
 
 constexpr int kThreads = 256;
 
-template <int LOOKUP, int LEAN = 0>
+template <int LOOKUP>
 __device__ __forceinline__ ValueGrad Residual(const CostArgs& a, const double scale, const double x,
                                               const double y, const double z) {
   ValueGrad r;
@@ -96,10 +99,7 @@ __device__ __forceinline__ ValueGrad Residual(const CostArgs& a, const double sc
     bool found = false;
 #pragma unroll
     for (int l = 0; l < HG_MAX_PYRAMID_LEVELS; ++l) {
-      if (l < a.num_grids && !found) {
-        found = LEAN ? LookupTsdfLevelAllObserved(a.grids[l], x, y, z, &t)
-                     : LookupTsdfLevel<true>(a.grids[l], x, y, z, &t);
-      }
+      if (l < a.num_grids && !found) found = LookupTsdfLevelAllObserved(a.grids[l], x, y, z, &t);
     }
     if (!found) {  // interpolated_multi_resolution_tsdf.h:136
       t.v = static_cast<double>(a.grids[0].min_tsd);
@@ -119,15 +119,152 @@ __host__ __device__ constexpr int NumNormalTerms(int n) { return n * (n + 1) / 2
 // Terms the kernel accumulates per tile: those of the 7-vector u (see CostKernel).
 constexpr int kNormalTermsU = NumNormalTerms(7);
 
-template <int LOOKUP, bool TWO_POSE, bool NORMAL_EQ, int LEAN = 0>
-__global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : (LEAN == 2 ? 3 : (LEAN == 3 ? 2 : 4))) CostKernel(const CostArgs a) {
-  constexpr int NC = TWO_POSE ? 14 : 7;
+// One point of a residual block: residual and Jacobian row, written straight to the outputs.
+// (aw ax ay az) = grad . d world / d q of the block's effective pose; for two poses the row of
+// pose k is that times d q / d q_k = s_k I + c q_other' (pose_prep.h).
+template <int LOOKUP, bool TWO_POSE>
+__device__ __forceinline__ void PointJacobian(const CostArgs& a, const BlockDev& sb, const double px,
+                                              const double py, const double pz, const long long gi) {
+  const double qw = sb.q[0], qx = sb.q[1], qy = sb.q[2], qz = sb.q[3];
+  const WorldPoint wp = TransformPoint(qw, qx, qy, qz, sb.t[0], sb.t[1], sb.t[2], px, py, pz);
+  const ValueGrad v = Residual<LOOKUP>(a, sb.scale, wp.x, wp.y, wp.z);
+  double A[4];
+  RotationTerms(qw, qx, qy, qz, px, py, pz, wp, v, &A[0], &A[1], &A[2], &A[3]);
+  // Outputs are written once and never re-read by the kernel: streaming stores keep them from
+  // evicting the voxel bricks out of L2.
+  if (a.r) __stcs(a.r + gi, v.v);
+  if (!TWO_POSE) {
+    if (a.jt0) {
+      double* o = a.jt0 + gi * 3;
+      __stcs(o, v.gx); __stcs(o + 1, v.gy); __stcs(o + 2, v.gz);
+    }
+    if (a.jq0) {
+      if (a.vec_store) {
+        double2* o = reinterpret_cast<double2*>(a.jq0 + gi * 4);
+        __stcs(o, make_double2(A[0], A[1]));
+        __stcs(o + 1, make_double2(A[2], A[3]));
+      } else {
+        double* o = a.jq0 + gi * 4;
+        o[0] = A[0]; o[1] = A[1]; o[2] = A[2]; o[3] = A[3];
+      }
+    }
+    return;
+  }
+  const double ac = A[0] * sb.c[0] + A[1] * sb.c[1] + A[2] * sb.c[2] + A[3] * sb.c[3];
+  if (a.jt0) {
+    double* o = a.jt0 + gi * 3;
+    __stcs(o, v.gx * sb.ct0); __stcs(o + 1, v.gy * sb.ct0); __stcs(o + 2, v.gz * sb.ct0);
+  }
+  if (a.jq0) {
+    double J[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) J[j] = sb.s0 * A[j] + ac * sb.q1[j];
+    if (a.vec_store) {
+      double2* o = reinterpret_cast<double2*>(a.jq0 + gi * 4);
+      __stcs(o, make_double2(J[0], J[1]));
+      __stcs(o + 1, make_double2(J[2], J[3]));
+    } else {
+      double* o = a.jq0 + gi * 4;
+      o[0] = J[0]; o[1] = J[1]; o[2] = J[2]; o[3] = J[3];
+    }
+  }
+  if (a.jt1) {
+    double* o = a.jt1 + gi * 3;
+    __stcs(o, v.gx * sb.ct1); __stcs(o + 1, v.gy * sb.ct1); __stcs(o + 2, v.gz * sb.ct1);
+  }
+  if (a.jq1) {
+    double J[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) J[j] = sb.s1 * A[j] + ac * sb.q0[j];
+    if (a.vec_store) {
+      double2* o = reinterpret_cast<double2*>(a.jq1 + gi * 4);
+      __stcs(o, make_double2(J[0], J[1]));
+      __stcs(o + 1, make_double2(J[2], J[3]));
+    } else {
+      double* o = a.jq1 + gi * 4;
+      o[0] = J[0]; o[1] = J[1]; o[2] = J[2]; o[3] = J[3];
+    }
+  }
+}
+
+__device__ __forceinline__ void LoadPoint(const CostArgs& a, const long long index, float* x, float* y, float* z) {
+  const float* pp = a.points + index * a.stride;
+  *x = __ldcs(pp); *y = __ldcs(pp + 1); *z = __ldcs(pp + 2);
+}
+
+// Residuals and Jacobians of a whole batch: persistent CTAs (4 per SM), CTA c takes tiles c,
+// c + gridDim.x, ... A CTA that starts a tile waits ~1.5 us on the chain tile -> block descriptor
+// -> first points before it has anything to compute (measured: 256 / 512 / 1024-point tiles of
+// one-tile CTAs ran the C2 batch in 0.243 / 0.214 / 0.199 ms); here that chain runs one tile
+// ahead: the next tile's block descriptor is copied into the other half of a double buffer with
+// cp.async (no registers, no stall) during the first round of this tile, and the next tile's
+// first points are the prefetch of this tile's last round.
+template <int LOOKUP, bool TWO_POSE>
+__global__ void __launch_bounds__(kThreads, 4) CostKernelPersistent(const CostArgs a, const int num_tiles) {
+  constexpr int kWords = sizeof(BlockDev) / 8;
+  __shared__ BlockDev descriptors[2];
+  const int lane = static_cast<int>(threadIdx.x);
+  const int stride = gridDim.x;
+  int t = blockIdx.x;
+  if (t >= num_tiles) return;
+  int count = a.tiles[t].count;
+  long long first = a.tiles[t].first;
+  {
+    const double* src = reinterpret_cast<const double*>(a.blocks + a.tiles[t].block);
+    double* dst = reinterpret_cast<double*>(&descriptors[0]);
+    for (int w = lane; w < kWords; w += kThreads) dst[w] = src[w];
+  }
+  float nx = 0.f, ny = 0.f, nz = 0.f;
+  if (lane < count) LoadPoint(a, first + lane, &nx, &ny, &nz);
+  __syncthreads();
+  int cur = 0;
+  for (;;) {
+    const int t_next = t + stride;
+    const bool has_next = t_next < num_tiles;
+    const BlockDev& sb = descriptors[cur];
+    int next_count = 0;
+    long long next_first = 0;
+    for (int base = 0; base < count; base += kThreads) {
+      const int i = base + lane;
+      const double px = static_cast<double>(nx), py = static_cast<double>(ny), pz = static_cast<double>(nz);
+      if (base == 0 && has_next) {
+        const double* src = reinterpret_cast<const double*>(a.blocks + __ldg(&a.tiles[t_next].block));
+        double* dst = reinterpret_cast<double*>(&descriptors[cur ^ 1]);
+        for (int w = lane; w < kWords; w += kThreads) {
+          const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(dst + w));
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(src + w) : "memory");
+        }
+      }
+      // The next round's point is loaded while this round's stencil gathers are in flight.
+      if (base + kThreads < count) {
+        if (i + kThreads < count) LoadPoint(a, first + i + kThreads, &nx, &ny, &nz);
+      } else if (has_next) {
+        next_count = __ldg(&a.tiles[t_next].count);
+        next_first = __ldg(&a.tiles[t_next].first);
+        if (lane < next_count) LoadPoint(a, next_first + lane, &nx, &ny, &nz);
+      }
+      if (i < count) PointJacobian<LOOKUP, TWO_POSE>(a, sb, px, py, pz, first + i);
+    }
+    if (!has_next) break;
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();
+    t = t_next;
+    count = next_count;
+    first = next_first;
+    cur ^= 1;
+  }
+}
+
+// Gauss-Newton sums of a batch (NORMAL_EQ), one CTA per tile.
+template <int LOOKUP, bool TWO_POSE, bool NORMAL_EQ>
+__global__ void __launch_bounds__(kThreads, 2) CostKernel(const CostArgs a) {
+  static_assert(NORMAL_EQ, "the Jacobian outputs are CostKernelPersistent's");
   __shared__ BlockDev sb;
-  extern __shared__ double red[];  // NORMAL_EQ only: kNormalTermsU x kThreads
+  extern __shared__ double red[];  // kNormalTermsU x kThreads
 
   const TileDev tile = a.tiles[blockIdx.x];
   {
-    // Cooperative copy of the block descriptor (352 bytes).
+    // Cooperative copy of the block descriptor.
     const int words = sizeof(BlockDev) / 8;
     const double* src = reinterpret_cast<const double*>(a.blocks + tile.block);
     double* dst = reinterpret_cast<double*>(&sb);
@@ -135,123 +272,36 @@ __global__ void __launch_bounds__(kThreads, NORMAL_EQ ? 2 : (LEAN == 2 ? 3 : (LE
   }
   __syncthreads();
 
-  // NORMAL_EQ: every row of [J | r] is u M with u = (grad value, grad . d world / d q) — 7 numbers
-  // per point — and a block-constant 7 x NC matrix M (identity for one pose; the interpolation
-  // weights and d q / d q0, d q / d q1 for two). So J'J = M' (sum u u') M: the kernel only sums
-  // the 36 terms of u and r (upper triangle of u u', u r, r r) per thread in registers, and
+  // Every row of [J | r] is u M with u = (grad value, grad . d world / d q) — 7 numbers per point
+  // — and a block-constant 7 x NC matrix M (identity for one pose; the interpolation weights and
+  // d q / d q0, d q / d q1 for two). So J'J = M' (sum u u') M: the kernel only sums the 36 terms
+  // of u and r (upper triangle of u u', u r, r r) per thread in registers, and
   // ReducePartialsKernel applies M once per block.
   double S[kNormalTermsU];
-  if (NORMAL_EQ) {
 #pragma unroll
-    for (int e = 0; e < kNormalTermsU; ++e) S[e] = 0.0;
-  }
+  for (int e = 0; e < kNormalTermsU; ++e) S[e] = 0.0;
 
-  const int tile_end = min(sb.n, tile.start + a.tile_points);
-  // The point of the NEXT round is loaded while this round's stencil gathers are in flight.
-  // (Not in the normal-equation variant, which has no registers to spare.)
-  float nx = 0.f, ny = 0.f, nz = 0.f;
-  if (!NORMAL_EQ && tile.start + static_cast<int>(threadIdx.x) < tile_end) {
-    const float* pp = a.points + (sb.point_offset + tile.start + threadIdx.x) * a.stride;
-    nx = __ldcs(pp); ny = __ldcs(pp + 1); nz = __ldcs(pp + 2);
-  }
+  const int tile_end = tile.start + tile.count;
   for (int base = tile.start; base < tile_end; base += kThreads) {
     const int i = base + threadIdx.x;
-    const bool active = i < tile_end;
-    double res = 0.0;
-    double J[NC];
-#pragma unroll
-    for (int c = 0; c < NC; ++c) J[c] = 0.0;
-    if (NORMAL_EQ && active) {
-      const float* pp = a.points + (sb.point_offset + i) * a.stride;
-      nx = __ldcs(pp); ny = __ldcs(pp + 1); nz = __ldcs(pp + 2);
-    }
-    const double px = static_cast<double>(nx), py = static_cast<double>(ny), pz = static_cast<double>(nz);
-    if (!NORMAL_EQ && i + kThreads < tile_end) {
-      const float* pp = a.points + (sb.point_offset + i + kThreads) * a.stride;
-      nx = __ldcs(pp); ny = __ldcs(pp + 1); nz = __ldcs(pp + 2);
-    }
-    if (active) {
-      const long long gi = sb.point_offset + i;
+    if (i < tile_end) {
+      float fx, fy, fz;
+      LoadPoint(a, sb.point_offset + i, &fx, &fy, &fz);
+      const double px = static_cast<double>(fx), py = static_cast<double>(fy), pz = static_cast<double>(fz);
       const double qw = sb.q[0], qx = sb.q[1], qy = sb.q[2], qz = sb.q[3];
       const WorldPoint wp = TransformPoint(qw, qx, qy, qz, sb.t[0], sb.t[1], sb.t[2], px, py, pz);
-      const ValueGrad v = Residual<LOOKUP, LEAN>(a, sb.scale, wp.x, wp.y, wp.z);
-      res = v.v;
+      const ValueGrad v = Residual<LOOKUP>(a, sb.scale, wp.x, wp.y, wp.z);
       double aw, ax, ay, az;
-      if (LEAN) {
-        RotationTermsClosedForm(qw, qx, qy, qz, px, py, pz, wp, v, &aw, &ax, &ay, &az);
-      } else {
-        RotationTerms(qw, qx, qy, qz, px, py, pz, wp, v, &aw, &ax, &ay, &az);
-      }
-
-      if (NORMAL_EQ) {
-        const double u[7] = {v.gx, v.gy, v.gz, aw, ax, ay, az};
-        int e = 0;
+      RotationTerms(qw, qx, qy, qz, px, py, pz, wp, v, &aw, &ax, &ay, &az);
+      const double u[7] = {v.gx, v.gy, v.gz, aw, ax, ay, az};
+      int e = 0;
 #pragma unroll
-        for (int ca = 0; ca < 7; ++ca)
+      for (int ca = 0; ca < 7; ++ca)
 #pragma unroll
-          for (int cb = ca; cb < 7; ++cb) S[e++] += u[ca] * u[cb];
+        for (int cb = ca; cb < 7; ++cb) S[e++] += u[ca] * u[cb];
 #pragma unroll
-        for (int ca = 0; ca < 7; ++ca) S[28 + ca] += u[ca] * res;
-        S[35] += res * res;
-      } else if (!TWO_POSE) {
-        J[0] = v.gx; J[1] = v.gy; J[2] = v.gz;
-        J[3] = aw; J[4] = ax; J[5] = ay; J[6] = az;
-      } else {
-        J[0] = v.gx * sb.ct0; J[1] = v.gy * sb.ct0; J[2] = v.gz * sb.ct0;
-        J[7] = v.gx * sb.ct1; J[8] = v.gy * sb.ct1; J[9] = v.gz * sb.ct1;
-        if (LEAN) {
-          // (aw ax ay az) m0 and m1 with m0 = s0 I + c q1', m1 = s1 I + c q0' (pose_prep.h)
-          const double ac = aw * sb.c[0] + ax * sb.c[1] + ay * sb.c[2] + az * sb.c[3];
-          const double A[4] = {aw, ax, ay, az};
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            J[3 + j] = sb.s0 * A[j] + ac * sb.q1[j];
-            J[10 + j] = sb.s1 * A[j] + ac * sb.q0[j];
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            J[3 + j] = aw * sb.m0[j] + ax * sb.m0[4 + j] + ay * sb.m0[8 + j] + az * sb.m0[12 + j];
-            J[10 + j] = aw * sb.m1[j] + ax * sb.m1[4 + j] + ay * sb.m1[8 + j] + az * sb.m1[12 + j];
-          }
-        }
-      }
-
-      if (!NORMAL_EQ) {
-        // Outputs are written once and never re-read by the kernel: streaming
-        // stores keep them from evicting the voxel bricks out of L2.
-        if (a.r) __stcs(a.r + gi, res);
-        if (a.jt0) {
-          double* o = a.jt0 + gi * 3;
-          __stcs(o, J[0]); __stcs(o + 1, J[1]); __stcs(o + 2, J[2]);
-        }
-        if (a.jq0) {
-          if (a.vec_store) {
-            double2* o = reinterpret_cast<double2*>(a.jq0 + gi * 4);
-            __stcs(o, make_double2(J[3], J[4]));
-            __stcs(o + 1, make_double2(J[5], J[6]));
-          } else {
-            double* o = a.jq0 + gi * 4;
-            o[0] = J[3]; o[1] = J[4]; o[2] = J[5]; o[3] = J[6];
-          }
-        }
-        if (TWO_POSE) {
-          if (a.jt1) {
-            double* o = a.jt1 + gi * 3;
-            __stcs(o, J[7]); __stcs(o + 1, J[8]); __stcs(o + 2, J[9]);
-          }
-          if (a.jq1) {
-            if (a.vec_store) {
-              double2* o = reinterpret_cast<double2*>(a.jq1 + gi * 4);
-              __stcs(o, make_double2(J[10], J[11]));
-              __stcs(o + 1, make_double2(J[12], J[13]));
-            } else {
-              double* o = a.jq1 + gi * 4;
-              o[0] = J[10]; o[1] = J[11]; o[2] = J[12]; o[3] = J[13];
-            }
-          }
-        }
-      }
+      for (int ca = 0; ca < 7; ++ca) S[28 + ca] += u[ca] * v.v;
+      S[35] += v.v * v.v;
     }
   }
   if (NORMAL_EQ) {
@@ -354,7 +404,7 @@ __global__ void __launch_bounds__(kThreads) LevelUsageKernel(const CostArgs a, u
     if (threadIdx.x < words) dst[threadIdx.x] = src[threadIdx.x];
   }
   __syncthreads();
-  const int tile_end = min(sb.n, tile.start + a.tile_points);
+  const int tile_end = tile.start + tile.count;
   for (int i = tile.start + threadIdx.x; i < tile_end; i += kThreads) {
     const float* pp = a.points + (sb.point_offset + i) * a.stride;
     const WorldPoint wp = TransformPoint(sb.q[0], sb.q[1], sb.q[2], sb.q[3], sb.t[0], sb.t[1], sb.t[2],
@@ -363,7 +413,7 @@ __global__ void __launch_bounds__(kThreads) LevelUsageKernel(const CostArgs a, u
     int level = a.num_grids;
     ValueGrad t;
     for (int l = a.num_grids - 1; l >= 0; --l)
-      if (LookupTsdfLevel<true>(a.grids[l], wp.x, wp.y, wp.z, &t)) level = l;
+      if (LookupTsdfLevelAllObserved(a.grids[l], wp.x, wp.y, wp.z, &t)) level = l;
     atomicAdd(&counts[level], 1ull);
   }
 }
@@ -462,38 +512,58 @@ void BuildTiles(const std::vector<int64_t>& offsets, int tile_points, std::vecto
   for (size_t b = 0; b + 1 < offsets.size(); ++b) {
     if (tile_begin) tile_begin->push_back(static_cast<int>(tiles->size()));
     const int64_t n = offsets[b + 1] - offsets[b];
-    for (int64_t s = 0; s < n; s += tile_points) tiles->push_back(TileDev{static_cast<int>(b), static_cast<int>(s)});
+    for (int64_t s = 0; s < n; s += tile_points) {
+      TileDev t;
+      t.block = static_cast<int>(b);
+      t.start = static_cast<int>(s);
+      t.count = static_cast<int>(std::min<int64_t>(tile_points, n - s));
+      t.pad = 0;
+      t.first = offsets[b] + s;
+      t.pad2 = 0;
+      tiles->push_back(t);
+    }
   }
   if (tile_begin) tile_begin->push_back(static_cast<int>(tiles->size()));
+}
+
+// Persistent grid of the Jacobian kernel: 4 CTAs per SM (its launch bound), never more than tiles.
+int PersistentGrid(const int device, const int num_tiles) {
+  static std::atomic<int> sms[64];
+  const int slot = device & 63;
+  int n = sms[slot].load(std::memory_order_acquire);
+  if (n == 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || n <= 0) n = 148;
+    sms[slot].store(n, std::memory_order_release);
+  }
+  int per_sm = 4;
+  if (const char* env = std::getenv("HG_COST_CTAS_PER_SM")) per_sm = std::max(1, std::atoi(env));
+  return std::min(num_tiles, n * per_sm);
 }
 
 template <bool NE>
 int LaunchCost(const hg_batch* B, const CostArgs& args, int num_tiles, cudaStream_t stream) {
   if (num_tiles == 0) return HG_OK;
   const size_t smem = NE ? static_cast<size_t>(kThreads) * kNormalTermsU * sizeof(double) : 0;
+  const int grid = PersistentGrid(B->device, num_tiles);
 #define HG_LAUNCH(L, T)                                                                         \
   do {                                                                                          \
-    if (NE && smem > 48 * 1024) {                                                               \
+    if (!NE) {                                                                                  \
+      CostKernelPersistent<L, T><<<grid, kThreads, 0, stream>>>(args, num_tiles);              \
+      break;                                                                                    \
+    }                                                                                           \
+    if (smem > 48 * 1024) {                                                                     \
       /* once per device and kernel: the attribute sticks */                                    \
       static std::atomic<unsigned long long> configured{0};                                     \
       const unsigned long long bit = 1ull << (B->device & 63);                                  \
       if ((configured.load(std::memory_order_acquire) & bit) == 0) {                            \
-        HG_CUDA(cudaFuncSetAttribute(CostKernel<L, T, NE>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+        HG_CUDA(cudaFuncSetAttribute(CostKernel<L, T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                      static_cast<int>(smem)));                                  \
         configured.fetch_or(bit, std::memory_order_release);                                    \
       }                                                                                         \
     }                                                                                           \
-    CostKernel<L, T, NE><<<num_tiles, kThreads, smem, stream>>>(args);                          \
+    CostKernel<L, T, true><<<num_tiles, kThreads, smem, stream>>>(args);                        \
   } while (0)
-  const char* lean_env = std::getenv("HG_COST_LEAN");
-  const int lean = lean_env == nullptr ? 1 : std::atoi(lean_env);
-  if (lean == 1 && !NE && B->lookup == 2 && B->two_pose) {
-    CostKernel<2, true, false, 1><<<num_tiles, kThreads, smem, stream>>>(args);
-  } else if (lean == 2 && !NE && B->lookup == 2 && B->two_pose) {
-    CostKernel<2, true, false, 2><<<num_tiles, kThreads, smem, stream>>>(args);
-  } else if (lean == 3 && !NE && B->lookup == 2 && B->two_pose) {
-    CostKernel<2, true, false, 3><<<num_tiles, kThreads, smem, stream>>>(args);
-  } else if (B->lookup == 0) {
+  if (B->lookup == 0) {
     if (B->two_pose) HG_LAUNCH(0, true); else HG_LAUNCH(0, false);
   } else if (B->lookup == 1) {
     if (B->two_pose) HG_LAUNCH(1, true); else HG_LAUNCH(1, false);
@@ -585,12 +655,12 @@ int WaitForAllPoints(const hg_batch* B, cudaStream_t stream) {
 CostArgs BaseArgs(const hg_batch* B) {
   CostArgs a;
   std::memset(&a, 0, sizeof(a));
+  const char* env = std::getenv("HG_NO_STENCILS");  // diagnostic: gather from the apron bricks instead
+  const bool packed = env == nullptr || std::atoi(env) == 0;
   for (int i = 0; i < B->num_grids; ++i) {
-    const char* env = std::getenv("HG_NO_STENCILS");
-    const bool off = env != nullptr && std::atoi(env) != 0;
-    if (B->lookup == 2 && B->two_pose && !off) EnsureStencils(B->grids[i]);
+    if (packed) EnsureStencils(B->grids[i]);  // no-op once built; rebuilt after the grid was written
     a.grids[i] = B->grids[i]->dev;
-    if (off) a.grids[i].stencils = nullptr;
+    if (!packed) a.grids[i].stencils = nullptr;
   }
   a.num_grids = B->num_grids;
   a.points = B->d_points;
@@ -771,7 +841,6 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
   CostArgs a = BaseArgs(B);
   a.blocks = B->d_blocks[slot];
   a.tiles = B->d_tiles_out;
-  a.tile_points = B->tile_out;
   const int64_t N = B->num_points;
   if (!B->two_pose) {
     jt1 = nullptr;
@@ -886,7 +955,6 @@ int hg_batch_normal_equations(const hg_batch* B, const double* poses, int num_po
   CostArgs a = BaseArgs(B);
   a.blocks = B->d_blocks[slot];
   a.tiles = B->d_tiles_ne;
-  a.tile_points = kTileNe;
   a.partials = B->d_partials;
   rc = WaitForAllPoints(B, stream);
   if (rc != HG_OK) return rc;
@@ -934,7 +1002,6 @@ int hg_batch_level_usage(const hg_batch* B, const double* poses, int num_poses, 
   CostArgs a = BaseArgs(B);
   a.blocks = B->d_blocks[slot];
   a.tiles = B->d_tiles_out;
-  a.tile_points = B->tile_out;
   rc = WaitForAllPoints(B, stream);
   if (rc != HG_OK) return rc;
   unsigned long long* d_counts = static_cast<unsigned long long*>(
@@ -1345,7 +1412,6 @@ extern "C" int hg_cost_normal_equations_static(const hg_cost* cost, const double
   CostArgs a = BaseArgs(B);
   a.blocks = d_block;
   a.tiles = B->d_tiles_ne;
-  a.tile_points = kTileNe;
   a.partials = d_partials;
   rc = WaitForAllPoints(B, stream);  // points queued by hg_batch_update_points (an event wait: no allocation)
   if (rc != HG_OK) return rc;

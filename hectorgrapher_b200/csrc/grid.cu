@@ -281,6 +281,7 @@ static std::mutex g_stencil_mutex;
 
 int EnsureStencils(const hg_grid* grid_const) {
   hg_grid* g = const_cast<hg_grid*>(grid_const);
+  if (__atomic_load_n(&g->dev.stencils, __ATOMIC_ACQUIRE) != nullptr) return HG_OK;
   std::lock_guard<std::mutex> lock(g_stencil_mutex);
   if (g->dev.stencils != nullptr || g->num_all_bricks == 0 || g->d_decoded == nullptr) return HG_OK;
   HG_ON_DEVICE(g->device);
@@ -291,7 +292,7 @@ int EnsureStencils(const hg_grid* grid_const) {
   CountLaunch();
   HG_CUDA(cudaGetLastError());
   HG_CUDA(cudaDeviceSynchronize());
-  g->dev.stencils = static_cast<const float4*>(g->d_stencils);
+  __atomic_store_n(&g->dev.stencils, static_cast<const float4*>(g->d_stencils), __ATOMIC_RELEASE);
   return HG_OK;
 }
 

@@ -86,12 +86,13 @@ __device__ __forceinline__ double CellWidthReciprocal(const double seed, const d
 // fixed offsets, no branches on the brick faces.
 // The voxels are the pre-decoded floats (GridDev::decoded); 'absent' is what a
 // voxel of a missing brick reads.
-__device__ __forceinline__ void FetchStencil(const GridDev& g, const int ix, const int iy, const int iz,
-                                             const float absent, float* v) {
-  const int id = BrickId(g.table, ix, iy, iz);
-  if (id < 0) {
-#pragma unroll
-    for (int k = 0; k < 8; ++k) v[k] = absent;
+__device__ __forceinline__ void FetchStencilOfBrick(const GridDev& g, const int id, const int ix, const int iy,
+                                                    const int iz, float* v) {
+  if (g.stencils != nullptr) {  // packed copy: the whole stencil is one 32-byte sector
+    const float4* s = g.stencils + 2 * (id * 512 + InBrick(ix, iy, iz));
+    const float4 lo = __ldg(s), hi = __ldg(s + 1);
+    v[0] = lo.x; v[1] = lo.y; v[2] = lo.z; v[3] = lo.w;
+    v[4] = hi.x; v[5] = hi.y; v[6] = hi.z; v[7] = hi.w;
     return;
   }
   const float* base = g.decoded + (id * kApronBrickVoxels + InApronBrick(ix, iy, iz));
@@ -104,6 +105,16 @@ __device__ __forceinline__ void FetchStencil(const GridDev& g, const int ix, con
   v[6] = __ldg(base + 10);
   v[7] = __ldg(base + 91);
 }
+__device__ __forceinline__ void FetchStencil(const GridDev& g, const int ix, const int iy, const int iz,
+                                             const float absent, float* v) {
+  const int id = BrickId(g.table, ix, iy, iz);
+  if (id < 0) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = absent;
+    return;
+  }
+  FetchStencilOfBrick(g, id, ix, iy, iz, v);
+}
 
 struct ValueGrad {
   double v, gx, gy, gz;  // value and gradient w.r.t. the world point
@@ -114,9 +125,7 @@ __device__ __forceinline__ ValueGrad LookupOccupancy(const GridDev& g, const dou
                                                      const double z) {
   double x1, y1, z1, x2, y2, z2;
   int ix, iy, iz;
-  LowerVoxel(g, x, &x1, &x2, &ix);
-  LowerVoxel(g, y, &y1, &y2, &iy);
-  LowerVoxel(g, z, &z1, &z2, &iz);
+  LowerVoxel3(g, x, y, z, &x1, &y1, &z1, &x2, &y2, &z2, &ix, &iy, &iz);
   float raw[8];
   FetchStencil(g, ix, iy, iz, g.a.unknown, raw);
   double q[8];
@@ -221,17 +230,9 @@ __device__ __forceinline__ bool LookupTsdfLevelAllObserved(const GridDev& g, con
   LowerVoxel3(g, x, y, z, &x1, &y1, &z1, &x2, &y2, &z2, &ix, &iy, &iz);
   const int id = BrickId(g.table, ix, iy, iz);
   if (id < 0) return false;
-  float r0, r1, r2, r3, r4, r5, r6, r7;
-  if (g.stencils != nullptr) {
-    const float4* s = g.stencils + 2 * (id * 512 + InBrick(ix, iy, iz));
-    const float4 lo = __ldg(s), hi = __ldg(s + 1);
-    r0 = lo.x; r1 = lo.y; r2 = lo.z; r3 = lo.w;
-    r4 = hi.x; r5 = hi.y; r6 = hi.z; r7 = hi.w;
-  } else {
-    const float* base = g.decoded + (id * kApronBrickVoxels + InApronBrick(ix, iy, iz));
-    r0 = __ldg(base); r1 = __ldg(base + 81); r2 = __ldg(base + 9); r3 = __ldg(base + 90);
-    r4 = __ldg(base + 1); r5 = __ldg(base + 82); r6 = __ldg(base + 10); r7 = __ldg(base + 91);
-  }
+  float r[8];
+  FetchStencilOfBrick(g, id, ix, iy, iz, r);
+  const float r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3], r4 = r[4], r5 = r[5], r6 = r[6], r7 = r[7];
   const float all = ((r0 + r1) + (r2 + r3)) + ((r4 + r5) + (r6 + r7));
   if (all != all) return false;
   const double q0 = r0, q1 = r1, q2 = r2, q3 = r3, q4 = r4, q5 = r5, q6 = r6, q7 = r7;
@@ -259,9 +260,7 @@ __device__ __forceinline__ bool LookupTsdfLevel(const GridDev& g, const double x
                                                 const double z, ValueGrad* out) {
   double x1, y1, z1, x2, y2, z2;
   int ix, iy, iz;
-  LowerVoxel(g, x, &x1, &x2, &ix);
-  LowerVoxel(g, y, &y1, &y2, &iy);
-  LowerVoxel(g, z, &z1, &z2, &iz);
+  LowerVoxel3(g, x, y, z, &x1, &y1, &z1, &x2, &y2, &z2, &ix, &iy, &iz);
   float raw[8];
   FetchStencil(g, ix, iy, iz, __int_as_float(0x7fc00000), raw);
   bool o[8];
@@ -327,45 +326,17 @@ __device__ __forceinline__ WorldPoint TransformPoint(const double qw, const doub
   return w;
 }
 
-// a_k = grad . d world / d q_k for k = w, x, y, z (closed form of the formula above).
+// a_k = grad . d world / d q_k for k = w, x, y, z, g = grad. With u = (qx, qy, qz), w = qw and
+// world = p + w uv + u x uv + t, uv = 2 u x p:
+//   a_w = g . uv
+//   a_u = 2 w (p x g) + 2 [(u . p) g + (g . u) p - 2 (g . p) u]
+// (from g . (e x p) = e . (p x g), (u x p) x g = p (u . g) - u (p . g), p x (g x u) =
+// g (p . u) - u (p . g)): 37 FP64 operations, where differentiating the formula term by term
+// takes ~50.
 __device__ __forceinline__ void RotationTerms(const double qw, const double qx, const double qy, const double qz,
                                               const double px, const double py, const double pz,
                                               const WorldPoint& w, const ValueGrad& v, double* aw, double* ax,
                                               double* ay, double* az) {
-  const double uvx = w.uvx, uvy = w.uvy, uvz = w.uvz;
-  // d/dw = uv
-  *aw = v.gx * uvx + v.gy * uvy + v.gz * uvz;
-  // d/du_k = w (2 e_k x p) + e_k x uv + u x (2 e_k x p)
-  // k = x: 2 e_x x p = (0, -2pz, 2py)
-  const double ex0 = 0.0, ex1 = -2.0 * pz, ex2 = 2.0 * py;
-  const double dxx_ = qw * ex0 + 0.0 + (qy * ex2 - qz * ex1);
-  const double dxy_ = qw * ex1 - uvz + (qz * ex0 - qx * ex2);
-  const double dxz_ = qw * ex2 + uvy + (qx * ex1 - qy * ex0);
-  *ax = v.gx * dxx_ + v.gy * dxy_ + v.gz * dxz_;
-  // k = y: 2 e_y x p = (2pz, 0, -2px);  e_y x uv = (uvz, 0, -uvx)
-  const double ey0 = 2.0 * pz, ey1 = 0.0, ey2 = -2.0 * px;
-  const double dyx_ = qw * ey0 + uvz + (qy * ey2 - qz * ey1);
-  const double dyy_ = qw * ey1 + 0.0 + (qz * ey0 - qx * ey2);
-  const double dyz_ = qw * ey2 - uvx + (qx * ey1 - qy * ey0);
-  *ay = v.gx * dyx_ + v.gy * dyy_ + v.gz * dyz_;
-  // k = z: 2 e_z x p = (-2py, 2px, 0);  e_z x uv = (-uvy, uvx, 0)
-  const double ez0 = -2.0 * py, ez1 = 2.0 * px, ez2 = 0.0;
-  const double dzx_ = qw * ez0 - uvy + (qy * ez2 - qz * ez1);
-  const double dzy_ = qw * ez1 + uvx + (qz * ez0 - qx * ez2);
-  const double dzz_ = qw * ez2 + 0.0 + (qx * ez1 - qy * ez0);
-  *az = v.gx * dzx_ + v.gy * dzy_ + v.gz * dzz_;
-}
-
-// The same four numbers in closed form. With u = (qx, qy, qz), w = qw and world = p + w uv +
-// u x uv + t, uv = 2 u x p:
-//   a_w = g . uv
-//   a_u = 2 w (p x g) + 2 [(u . p) g + (g . u) p - 2 (g . p) u]
-// (from g . (e x p) = e . (p x g), (u x p) x g = p (u . g) - u (p . g), p x (g x u) =
-// g (p . u) - u (p . g)); equal to RotationTerms up to rounding, 37 FP64 operations instead of ~50.
-__device__ __forceinline__ void RotationTermsClosedForm(const double qw, const double qx, const double qy,
-                                                        const double qz, const double px, const double py,
-                                                        const double pz, const WorldPoint& w, const ValueGrad& v,
-                                                        double* aw, double* ax, double* ay, double* az) {
   *aw = v.gx * w.uvx + v.gy * w.uvy + v.gz * w.uvz;
   const double cx = py * v.gz - pz * v.gy, cy = pz * v.gx - px * v.gz, cz = px * v.gy - py * v.gx;
   const double up = qx * px + qy * py + qz * pz;
