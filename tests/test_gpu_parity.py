@@ -190,6 +190,60 @@ def test_cost_function_parity(oracle, hg, world, kind):
         assert (J3[1] == 0).all()
 
 
+@pytest.mark.parametrize("kind", list(KIND_GRIDS.keys()))
+def test_packed_stencils_equal_apron_gather(oracle, hg, world, kind, monkeypatch):
+    """The packed 2x2x2 stencil copy of a grid (GridDev::stencils) holds the same floats as the
+    apron bricks: every cost kind gives bit-identical outputs with and without it."""
+    rng = np.random.RandomState(5)
+    cloud = world["cloud"]
+    gg = [world["g_" + n] for n in KIND_GRIDS[kind]]
+    two = kind.startswith("interpolated")
+    gc = hg.Cost(kind, 0.01, cloud, gg, 0.6 if two else 0.0)
+    p = perturbed(world["truth"], rng)
+    if two:
+        p = np.concatenate([p, perturbed(world["truth"], rng, 0.3, 0.15)])
+    r1, J1 = gc.evaluate(p)
+    monkeypatch.setenv("HG_NO_STENCILS", "1")
+    r0, J0 = gc.evaluate(p)
+    monkeypatch.delenv("HG_NO_STENCILS")
+    assert (r0 == r1).all() and np.abs(r0).max() > 0
+    for a, b in zip(J0, J1):
+        assert (a == b).all()
+
+
+def test_packed_stencils_follow_insertions(oracle, hg):
+    """A grid written after a cost function was built on it: the packed stencils are dropped with
+    the old voxels and rebuilt, so the next evaluation sees the new map."""
+    from hectorgrapher_b200 import synth
+    sph = synth.spheres()
+    rng = np.random.RandomState(2)
+    g = hg.Grid.tsdf(0.10, 2.5, 1000.0, np.zeros((0, 3), np.int32), [], [])
+    o = oracle.Grid.tsdf(0.10, 2.5, 1000.0)
+    clouds = []
+    for k in range(3):
+        origin, yaw = synth.corkscrew_pose(k, 4)
+        pts = synth.scan(origin, yaw, 16, 180, sph, rng)
+        world_pts = (synth.quat_rotate(synth.quat_from_yaw(yaw), pts.astype(np.float64)) + origin).astype(np.float32)
+        clouds.append((np.asarray(origin, np.float32), world_pts))
+    origin, yaw = synth.corkscrew_pose(1, 4)
+    local = synth.scan(origin, yaw, 8, 128, sph, rng)
+    pose = np.concatenate([origin, synth.quat_from_yaw(yaw)])
+    g.insert_tsdf(*clouds[0])
+    o.insert_tsdf(*clouds[0])
+    gc = hg.Cost("tsdf", 0.05, local, [g], 0.0)
+    oc = oracle.Cost("tsdf", 0.05, local, [o], 0.0)
+    assert_close(gc.evaluate(pose)[0], oc.evaluate(pose)[0], "before the second insertion")
+    before = gc.evaluate(pose)[0]
+    for c in clouds[1:]:
+        g.insert_tsdf(*c)
+        o.insert_tsdf(*c)
+    r1, J1 = gc.evaluate(pose)
+    r0, J0 = oc.evaluate(pose)
+    assert_close(r1, r0, "after the insertions")
+    assert_close(J1[1], J0[1], "after the insertions, rotation block")
+    assert np.abs(r1 - before).max() > 1e-6  # the map did change under the cost function
+
+
 def test_cost_function_slerp_branches(oracle, hg, world):
     """Two-pose functors: lerp branch (identical rotations) and the d < 0 sign flip."""
     cloud = world["cloud"][:500]
