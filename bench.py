@@ -925,11 +925,11 @@ def run_ours(args, rank, world, local_rank):
                        "points_per_step_per_gpu": N, "multi_gpu": "replicas only (one window per GPU)",
                        "l2": "256 MiB flush write between timed steps; working set per step ~0.9 GB"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": measured_traffic("CostKernel<2,true,false>"),
+                         "frac": achieved / peak, "traffic": measured_traffic("CostKernelPersistent<2,true>"),
                          "traffic_note": "bytes per launch (ncu, profiles/r2_ncu_summary.md); algorithmic bytes per "
                                          "launch = %d" % (ALG_BYTES_PER_POINT * N),
                          "peak_source": peak_src,
-                         "algorithmic_bytes_per_point": ALG_BYTES_PER_POINT, "kernel": "CostKernel<2,true,false>"},
+                         "algorithmic_bytes_per_point": ALG_BYTES_PER_POINT, "kernel": "CostKernelPersistent<2,true>"},
             "cpu_baseline": {"value": cpu_rate, "unit": "points/s", "cores": cpu_threads, "kind": "port",
                              "sample": cpu_desc},
             "e2e": {"value": world * N * e2e_steps / e2e_s, "unit": "points/s",

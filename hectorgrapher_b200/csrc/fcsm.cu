@@ -2375,6 +2375,7 @@ class DeviceSearch {
   ~DeviceSearch() {
     if (e0_) cudaEventDestroy(e0_);
     if (e1_) cudaEventDestroy(e1_);
+    for (auto& m : marks_) cudaEventDestroy(m.second);
   }
 
   int AddProblem(const SearchParameters& sp, const Rigid& node_pose, const Rigid& submap_pose,
@@ -2464,7 +2465,9 @@ class DeviceSearch {
       }
     }
     std::memcpy(h + off_problems, pd.data(), P * sizeof(ProblemDev));
+    Mark("start");
     HG_CUDA(cudaMemcpyAsync(ws_->d_upload.p, h, upload_bytes, cudaMemcpyHostToDevice, stream_));
+    Mark("upload");
     char* d = ws_->d_upload.as<char>();
     // ---- device state
     const size_t lattice_n = n_scans * per_scan_;
@@ -2547,6 +2550,7 @@ class DeviceSearch {
       }
     }
     HG_CUDA(cudaGetLastError());
+    Mark("discretise");
     if (time_lattice) {
       HG_CUDA(cudaEventCreate(&e0_));
       HG_CUDA(cudaEventCreate(&e1_));
@@ -2573,6 +2577,7 @@ class DeviceSearch {
       }
     }
     if (time_lattice) HG_CUDA(cudaEventRecord(e1_, stream_));
+    Mark("lattice");
     if (std::getenv("HG_LATTICE_CHECK") != nullptr) {
       // Development / test aid: whatever kernel scored the lattice, against the brick-table kernel, every sum.
       const hg_stack_level& L = m_->stack->levels[max_depth_];
@@ -2615,14 +2620,17 @@ class DeviceSearch {
       CountLaunch();
       ++launches_;
     }
+    Mark("argmax+starts");
     if (max_depth_ >= 1) {
       DiveKernel<<<total_scans_, 256, 0, stream_>>>(s, m_->d_levels);
       CountLaunch();
       ++launches_;
     }
+    Mark("dive");
     GateKernel<true><<<std::min(PersistentBlocks(16), (total_scans_ + 3) / 4), 128, 0, stream_>>>(s, GateGrid());
     CountLaunch();
     ++launches_;
+    Mark("dive-gate");
     HG_CUDA(cudaGetLastError());
     phase_a_done_ = true;
     return HG_OK;
@@ -2648,23 +2656,30 @@ class DeviceSearch {
     outcomes->assign(P, Outcome());
     if (total_scans_ == 0) return HG_OK;
     const SearchDev& s = dev_;
+    Mark("(host: bound exchange)");
     ThresholdKernel<<<(P + 127) / 128, 128, 0, stream_>>>(s, P, external_bound);
     SeedKernel<<<PersistentBlocks(8), 256, 0, stream_>>>(s);
     CountLaunch(2);
     launches_ += 2;
+    Mark("threshold+seed");
     for (int depth = max_depth_; depth >= 1; --depth) {
       const hg_stack_level& L = m_->stack->levels[depth - 1];
       ExpandKernel<<<PersistentBlocks(8), 256, 0, stream_>>>(s, L.table, L.dense, depth - 1);
       CountLaunch();
       ++launches_;
+      Mark("expand");
     }
     GateKernel<false><<<PersistentBlocks(16), 128, 0, stream_>>>(s, GateGrid());
+    Mark("gate");
     WinnersKernel<<<PersistentBlocks(4), 256, 0, stream_>>>(s);
     CountLaunch(2);
     launches_ += 2;
+    Mark("winners");
     HG_CUDA(cudaGetLastError());
     HG_CUDA(cudaMemcpyAsync(ws_->h_ctrl.p, ws_->d_ctrl.p, ctrl_bytes_, cudaMemcpyDeviceToHost, stream_));
+    Mark("readback");
     HG_CUDA(cudaStreamSynchronize(stream_));
+    PrintMarks();
     if (e0_ != nullptr) HG_CUDA(cudaEventElapsedTime(&lattice_ms_, e0_, e1_));
     const char* h = ws_->h_ctrl.as<char>();
     const CtrlDev* ctrl = reinterpret_cast<const CtrlDev*>(h);
@@ -2920,6 +2935,30 @@ class DeviceSearch {
   int list_cap_ = 0, winners_cap_ = 0;
   size_t ctrl_bytes_ = 0, off_pp_ = 0, off_scored_ = 0, off_win_ = 0;
   cudaEvent_t e0_ = nullptr, e1_ = nullptr;
+  // HG_TRACE: events between the phases of a search, printed by RunPhaseB.
+  std::vector<std::pair<const char*, cudaEvent_t>> marks_;
+  void Mark(const char* label) {
+    if (!TraceEnabled()) return;
+    cudaEvent_t e = nullptr;
+    if (cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, stream_);
+    marks_.emplace_back(label, e);
+  }
+  void PrintMarks() {
+    if (marks_.size() > 1) {
+      std::fprintf(stderr, "[hg trace] device phases (us):");
+      for (size_t i = 1; i < marks_.size(); ++i) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, marks_[i - 1].second, marks_[i].second);
+        std::fprintf(stderr, " %s %.0f", marks_[i].first, 1e3f * ms);
+      }
+      float total = 0.f;
+      cudaEventElapsedTime(&total, marks_.front().second, marks_.back().second);
+      std::fprintf(stderr, " | first to last mark %.0f (includes the host's wait between the phases)\n", 1e3f * total);
+    }
+    for (auto& m : marks_) cudaEventDestroy(m.second);
+    marks_.clear();
+  }
   float lattice_ms_ = 0.f;
   int launches_ = 0;
   bool phase_a_done_ = false;

@@ -6,7 +6,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-fi
     python bench.py --steps 2 --warmup 3 --c5-small > gpurun_out/r2_ncu_list.log 2>&1
 HG_CONSTRAINT_THREADS=1 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r2_c5_launches.csv \
     python tools/trace_c5.py 2 100 > gpurun_out/r2_c5_ncu.log 2>&1
-ncu --set full --import-source on --clock-control none -k regex:CostKernel --launch-skip 1 --launch-count 1 \
+ncu --set full --import-source on --clock-control none -k regex:CostKernelPersistent --launch-skip 1 --launch-count 1 \
     -o gpurun_out/r2_cost_kernel -f python tools/ab_cost.py --once "HG_TILE_OUT=1024" > gpurun_out/r2_ncu_cost.log 2>&1
 ncu --set full --import-source on --clock-control none -k regex:ScoreLatticePackedKernel --launch-skip 1 --launch-count 1 \
     -o gpurun_out/r2_lattice_kernel -f python tools/trace_c4.py > gpurun_out/r2_ncu_lattice.log 2>&1

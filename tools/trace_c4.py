@@ -13,7 +13,7 @@ g_lo = hg.Grid.tsdf(bench.LO_RES, bench.REL_TRUNC, bench.MAX_WEIGHT, *w["lo"])
 ci = bench.correlative_inputs(w, rotational="--configured" in sys.argv)
 high, low, hist, node, submap = ci["high"], ci["low"], ci["hist"], ci["node"], ci["submap"]
 m = hg.Fcsm(g_hi, g_lo, ci["submap_hist"], **ci["opts"])
-for mode in ("device", "host"):
+for mode in (("device",) if "--device-only" in sys.argv else ("device", "host")):
     if mode == "host":
         os.environ["HG_SEARCH_HOST_REPLAY"] = "1"
     else:
