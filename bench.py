@@ -326,13 +326,14 @@ NUM_SMS = 148
 
 def sharded_full_submap(m, ci, rank, world, dist):
     """One MatchFullSubmap over all ranks: phase A on this rank's discrete scans, one all-reduce-max of the
-    dive bound, phase B under the common bound, all-gather of the best records and selection — all of it
+    dive bound (in device memory, on the search's stream), phase B under the common bound, all-gather of the best records and selection — all of it
     inside the caller's timed region. Returns (winner dict or None, order_unresolved, this rank's result)."""
     from hectorgrapher_b200 import dist as hgdist
-    handle, bound = m.full_submap_begin(ci["node"][3:], ci["submap"][3:], ci["high"], ci["low"], ci["hist"],
-                                        min_score=ci["min_score"], shard_index=rank, num_shards=world)
-    bound = hgdist.all_reduce_max_bound(bound, dist)
-    mine = m.full_submap_finish(handle, bound)
+    handle, d_bound, stream = m.full_submap_begin_async(ci["node"][3:], ci["submap"][3:], ci["high"], ci["low"],
+                                                        ci["hist"], min_score=ci["min_score"], shard_index=rank,
+                                                        num_shards=world)
+    hgdist.all_reduce_max_device_bound(d_bound, stream, dist)  # queued behind phase A: no host wait
+    mine = m.full_submap_finish(handle, 0.0)
     best, unresolved = hgdist.reduce_best_candidate(mine, dist)
     return best, unresolved, mine
 

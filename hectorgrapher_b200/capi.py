@@ -136,6 +136,7 @@ SYMBOLS = {
     "hg_fcsm_match_full_submap": (c_i, [vp, vp, vp, vp, c_f, c_i, c_i, vp]),
     "hg_fcsm_match_batch": (c_i, [vp, c_i, vp, vp, vp, c_f, vp]),
     "hg_fcsm_full_submap_begin": (c_i, [vp, vp, vp, vp, c_f, c_i, c_i, vp, vp]),
+    "hg_fcsm_full_submap_begin_async": (c_i, [vp, vp, vp, vp, c_f, c_i, c_i, vp, vp, vp]),
     "hg_fcsm_full_submap_finish": (c_i, [vp, c_f, vp]),
     "hg_fcsm_search_abandon": (None, [vp]),
     "hg_pack_best_record": (c_i, [vp, vp]),
@@ -742,6 +743,18 @@ class Fcsm:
         _check(lib().hg_fcsm_full_submap_begin(self.h, _p(nq), _p(sq), C.byref(data), min_score, shard_index,
                                                num_shards, C.byref(out), C.byref(bound)))
         return (out, data, keep), float(bound.value)
+
+    def full_submap_begin_async(self, node_rotation, submap_rotation, high, low, hist, gravity=(1, 0, 0, 0),
+                                min_score=0.55, shard_index=0, num_shards=1):
+        """First half without a host round trip (hg_fcsm_full_submap_begin_async): returns (handle,
+        device address of the float holding the dive bound or 0, cudaStream_t the work is queued on or 0).
+        All-reduce-max the float in place on that stream, then full_submap_finish(handle, 0.0)."""
+        nq, sq = _f64(node_rotation), _f64(submap_rotation)
+        data, keep = make_node_data(high, low, hist, gravity)
+        out, d_bound, stream = vp(), vp(), vp()
+        _check(lib().hg_fcsm_full_submap_begin_async(self.h, _p(nq), _p(sq), C.byref(data), min_score, shard_index,
+                                                     num_shards, C.byref(out), C.byref(d_bound), C.byref(stream)))
+        return (out, data, keep), int(d_bound.value or 0), int(stream.value or 0)
 
     def full_submap_finish(self, handle, bound):
         res = MatchResult()

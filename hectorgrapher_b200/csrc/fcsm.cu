@@ -651,6 +651,7 @@ struct Workspace {
   PinnedBuffer h_cand, h_sums, h_kept, h_poses, h_low, h_count;
   // device-resident search (DeviceSearch)
   DeviceBuffer d_upload, d_starts, d_lists, d_ctrl;
+  DeviceBuffer d_exchange;  // dive bounds offered to / received from the other shards of a search
   PinnedBuffer h_upload, h_ctrl;
 };
 Workspace& GetWorkspace(int device) {
@@ -2211,7 +2212,9 @@ __global__ void __launch_bounds__(128) GateKernel(const SearchDev s, const GateA
 // its own dive's and, for a sharded search, the one the other shards found), or the smallest
 // score above min_score when there is none. Scores are >= 0.1, so their bit patterns order like
 // the floats.
-__global__ void ThresholdKernel(const SearchDev s, const int num_problems, const float external_bound) {
+// exchange_bits: null, or one float per problem that the caller's collective left in device memory.
+__global__ void ThresholdKernel(const SearchDev s, const int num_problems, const float external_bound,
+                                const int* __restrict__ exchange_bits) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= num_problems) return;
   float t = nextafterf(s.problems[p].min_score, __int_as_float(0x7f800000));
@@ -2219,6 +2222,10 @@ __global__ void ThresholdKernel(const SearchDev s, const int num_problems, const
   int bits = __float_as_int(t);
   bits = max(bits, s.bound_bits[p]);
   if (external_bound > 0.f) bits = max(bits, __float_as_int(external_bound));
+  if (exchange_bits != nullptr) {
+    const float e = __int_as_float(exchange_bits[p]);
+    if (e > 0.f && e <= 1.f) bits = max(bits, exchange_bits[p]);  // a score; anything else is ignored
+  }
   s.thresh_bits[p] = bits;
 }
 
@@ -2636,6 +2643,24 @@ class DeviceSearch {
     return HG_OK;
   }
 
+  // Queues a copy of every problem's dive bound into a separate device array and returns it: the
+  // caller's collective (an all-reduce-max over the shards of the search) works on that array in
+  // place, on this search's stream or one ordered after it, and RunPhaseB reads it — no host round
+  // trip between the phases. The problem's own bound stays where it is (phase B must meet that leaf again).
+  int OfferBounds(float** exchange) {
+    const int P = num_problems();
+    int rc;
+    if ((rc = ws_->d_exchange.Reserve(std::max(P, 1) * sizeof(int))) != HG_OK) return rc;
+    exchange_ = ws_->d_exchange.as<int>();
+    if (total_scans_ == 0) {
+      HG_CUDA(cudaMemsetAsync(exchange_, 0, std::max(P, 1) * sizeof(int), stream_));
+    } else {
+      HG_CUDA(cudaMemcpyAsync(exchange_, dev_.bound_bits, P * sizeof(int), cudaMemcpyDeviceToDevice, stream_));
+    }
+    *exchange = reinterpret_cast<float*>(exchange_);
+    return HG_OK;
+  }
+
   // Synchronises and returns every problem's own dive bound (0 = none).
   int ReadBounds(std::vector<float>* bounds) {
     const int P = num_problems();
@@ -2657,7 +2682,7 @@ class DeviceSearch {
     if (total_scans_ == 0) return HG_OK;
     const SearchDev& s = dev_;
     Mark("(host: bound exchange)");
-    ThresholdKernel<<<(P + 127) / 128, 128, 0, stream_>>>(s, P, external_bound);
+    ThresholdKernel<<<(P + 127) / 128, 128, 0, stream_>>>(s, P, external_bound, exchange_);
     SeedKernel<<<PersistentBlocks(8), 256, 0, stream_>>>(s);
     CountLaunch(2);
     launches_ += 2;
@@ -2935,6 +2960,7 @@ class DeviceSearch {
   int list_cap_ = 0, winners_cap_ = 0;
   size_t ctrl_bytes_ = 0, off_pp_ = 0, off_scored_ = 0, off_win_ = 0;
   cudaEvent_t e0_ = nullptr, e1_ = nullptr;
+  int* exchange_ = nullptr;
   // HG_TRACE: events between the phases of a search, printed by RunPhaseB.
   std::vector<std::pair<const char*, cudaEvent_t>> marks_;
   void Mark(const char* label) {
@@ -3267,6 +3293,45 @@ int hg_fcsm_full_submap_begin(const hg_fcsm* m, const double* global_node_rotati
     rc = h->search->ReadBounds(&bounds);
     if (rc != HG_OK) return rc;
     *dive_bound = bounds[0];
+  }
+  *search_out = h.release();
+  return HG_OK;
+}
+
+int hg_fcsm_full_submap_begin_async(const hg_fcsm* m, const double* global_node_rotation,
+                                    const double* global_submap_rotation, const hg_node_data* data, float min_score,
+                                    int shard_index, int num_shards, hg_fcsm_search** search_out, float** d_bound,
+                                    void** stream_out) {
+  HG_REQUIRE(m && global_node_rotation && global_submap_rotation && search_out && d_bound && stream_out,
+             "hg_fcsm_full_submap_begin_async: bad arguments");
+  HG_REQUIRE(num_shards >= 1 && shard_index >= 0 && shard_index < num_shards,
+             "hg_fcsm_full_submap_begin_async: bad shard");
+  int rc = CheckNodeData(data);
+  if (rc != HG_OK) return rc;
+  *d_bound = nullptr;
+  *stream_out = nullptr;
+  std::unique_ptr<hg_fcsm_search> h(new hg_fcsm_search);
+  h->m = m;
+  h->sp = FullSubmapWindow(m, data);
+  const double zero[3] = {0., 0., 0.};
+  h->node_pose = ToRigidF(zero, global_node_rotation);
+  h->submap_pose = ToRigidF(zero, global_submap_rotation);
+  h->data = data;
+  h->min_score = min_score;
+  h->shard_index = shard_index;
+  h->num_shards = num_shards;
+  if (m->options.strict_visit_order == 0 && !ForceHostReplay()) {
+    HG_ON_DEVICE(m->device);
+    cudaStream_t stream = ThreadStream();
+    HG_REQUIRE(stream != nullptr, "hg_fcsm: cannot create a stream");
+    h->search.reset(new DeviceSearch(m, stream));
+    rc = h->search->AddProblem(h->sp, h->node_pose, h->submap_pose, data, min_score, shard_index, num_shards);
+    if (rc != HG_OK) return rc;
+    rc = h->search->RunPhaseA(true);
+    if (rc != HG_OK) return rc;
+    rc = h->search->OfferBounds(d_bound);
+    if (rc != HG_OK) return rc;
+    *stream_out = static_cast<void*>(stream);
   }
   *search_out = h.release();
   return HG_OK;

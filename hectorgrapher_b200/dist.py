@@ -48,6 +48,25 @@ def all_reduce_max_bound(bound, dist, device="cuda"):
     return float(b["bound_h"][0])
 
 
+class _DeviceFloat:
+    """A float in device memory that somebody else owns, as seen by torch (zero copy)."""
+
+    def __init__(self, address):
+        self.__cuda_array_interface__ = {"shape": (1,), "typestr": "<f4", "data": (int(address), False),
+                                         "version": 2, "strides": None}
+
+
+def all_reduce_max_device_bound(d_bound, stream, dist):
+    """The same exchange with the bound left where hg_fcsm_full_submap_begin_async put it: the
+    all-reduce-max is queued behind phase A on the search's own stream and phase B is queued behind it,
+    so the host never waits between the two halves of a sharded search."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return
+    t = torch.as_tensor(_DeviceFloat(d_bound), device=torch.device("cuda", torch.cuda.current_device()))
+    with torch.cuda.stream(torch.cuda.ExternalStream(stream)):
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+
+
 def reduce_best_candidate(result, dist, device="cuda"):
     """result: this rank's match result (dict of hectorgrapher_b200.capi, or None). All-gathers one
     fixed-size record per rank (hg_pack_best_record) and selects the winner with the library's rule

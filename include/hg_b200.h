@@ -486,6 +486,21 @@ int hg_fcsm_full_submap_begin(const hg_fcsm* matcher, const double* global_node_
                               float min_score, int shard_index, int num_shards,
                               hg_fcsm_search** search, float* dive_bound);
 int hg_fcsm_full_submap_finish(hg_fcsm_search* search, float bound, hg_match_result* result);
+
+/* The first half without a host round trip: phase A is only queued — on *stream, a cudaStream_t of
+ * the matcher's device that belongs to the calling thread — and *d_bound is the device address of a
+ * float that holds this shard's dive bound (0 = none) once the queued work has run. The caller
+ * all-reduces (max) that float in place over the shards with its own collective on *stream or on
+ * a stream ordered after it (ncclAllReduce(d_bound, d_bound, 1, ncclFloat, ncclMax, comm, stream)),
+ * then calls hg_fcsm_full_submap_finish(search, 0, result) from the same thread: phase B reads the
+ * exchanged bound from device memory. *d_bound is null when the matcher searches on the host
+ * (strict_visit_order): use hg_fcsm_full_submap_begin then. The float lives in the thread's
+ * workspace: no other search of this thread may run between the two halves.
+ * Same reference step as hg_fcsm_full_submap_begin (fast_correlative_scan_matcher_3d.cc:215-238, 384). */
+int hg_fcsm_full_submap_begin_async(const hg_fcsm* matcher, const double* global_node_rotation,
+                                    const double* global_submap_rotation, const hg_node_data* data,
+                                    float min_score, int shard_index, int num_shards, hg_fcsm_search** search,
+                                    float** d_bound, void** stream);
 /* Drops a search that will not be finished. */
 void hg_fcsm_search_abandon(hg_fcsm_search* search);
 

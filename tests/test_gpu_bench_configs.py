@@ -105,6 +105,26 @@ def test_c4_full_sweep_as_benchmarked(oracle, hg, bench_world):
         best, unresolved = capi.select_best_record(np.stack(records))
         assert not unresolved
         same(best, want, ["found", "score", "scan_index", "ox", "oy", "oz", "low_resolution_score"])
+    # (5) the same exchange with the bound left in device memory (hg_fcsm_full_submap_begin_async):
+    # what the other shards would have all-reduced into the float is written there through torch
+    import torch
+    from hectorgrapher_b200.dist import _DeviceFloat
+    shards = 8
+    records = []
+    for k in range(shards):
+        h, d_bound, stream = gm.full_submap_begin_async(ci["node"][3:], ci["submap"][3:], ci["high"], ci["low"],
+                                                        ci["hist"], min_score=ci["min_score"], shard_index=k,
+                                                        num_shards=shards)
+        assert d_bound != 0 and stream != 0
+        t = torch.as_tensor(_DeviceFloat(d_bound), device="cuda")
+        with torch.cuda.stream(torch.cuda.ExternalStream(stream)):
+            own = float(t.cpu()[0])        # ordered behind phase A on the search's stream
+            assert own == np.float32(bounds[k])
+            t.fill_(float(common))         # the all-reduce-max, in place
+        records.append(capi.pack_best_record(gm.full_submap_finish(h, 0.0)))
+    best, unresolved = capi.select_best_record(np.stack(records))
+    assert not unresolved
+    same(best, want, ["found", "score", "scan_index", "ox", "oy", "oz", "low_resolution_score"])
 
 
 def test_c4_configured_as_benchmarked(oracle, hg, bench_world):
