@@ -6,7 +6,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhg_b200.so")
+LIB_PATH = os.environ.get("HG_LIB_PATH") or os.path.join(_HERE, "libhg_b200.so")  # HG_LIB_PATH: A/B of two builds
 _LIB = None
 
 vp = C.c_void_p
@@ -178,6 +178,8 @@ def lib():
                           "__graft_entry__.build(); there is no CPU fallback")
         L = C.CDLL(LIB_PATH)
         for name, (res, args) in SYMBOLS.items():
+            if "HG_LIB_PATH" in os.environ and not hasattr(L, name):
+                continue  # an older build under A/B: calling what it lacks fails loudly at the call
             fn = getattr(L, name)
             fn.restype = res
             fn.argtypes = args

@@ -394,6 +394,11 @@ __global__ void __launch_bounds__(128) ReducePartialsKernel(const double* __rest
   out[static_cast<size_t>(b) * P + e] = value;
 }
 
+// Copies 8-byte words from pinned host memory (read over PCIe in place) to device memory.
+__global__ void UploadWordsKernel(const double* __restrict__ src, double* __restrict__ dst, const int n) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
 // Which pyramid level answers each point of a multi-resolution TSDF batch
 // (interpolated_multi_resolution_tsdf.h:82-137: the first level whose eight corners are all
 // observed): counts[l] for level l, counts[num_grids] for "none". Settles how many stencil
@@ -641,8 +646,15 @@ int PrepareBlocks(const hg_batch* B, const double* poses, int num_poses, const i
     d.n = static_cast<int>(B->offsets[b + 1] - B->offsets[b]);
     d.pad = 0;
   }
-  HG_CUDA(cudaMemcpyAsync(B->d_blocks[slot], B->h_blocks[slot], sizeof(BlockDev) * B->num_blocks,
-                          cudaMemcpyHostToDevice, stream));
+  // The descriptors travel by a kernel that reads the pinned array in place (unified addressing),
+  // not by a copy: a cudaMemcpyAsync would queue on the host-to-device copy engine behind the
+  // point chunks hg_batch_update_points has just queued (77 MB on C2), and the first chunk's
+  // kernel would wait ~1.4 ms for 30 KB.
+  const int words = static_cast<int>(sizeof(BlockDev) / 8) * B->num_blocks;
+  UploadWordsKernel<<<std::min((words + 255) / 256, 64), 256, 0, stream>>>(
+      reinterpret_cast<const double*>(B->h_blocks[slot]), reinterpret_cast<double*>(B->d_blocks[slot]), words);
+  CountLaunch();
+  HG_CUDA(cudaGetLastError());
   return HG_OK;
 }
 
@@ -927,6 +939,13 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
   // at once, so the step costs about what the device-to-host copies alone cost.
   if (B->copy_out == nullptr) HG_CUDA(cudaStreamCreateWithFlags(&B->copy_out, cudaStreamNonBlocking));
   const int num_chunks = static_cast<int>(B->chunk_block_begin.size()) - 1;
+  const bool trace = std::getenv("HG_TRACE_E2E") != nullptr;
+  std::vector<cudaEvent_t> tk, td;
+  cudaEvent_t t_begin = nullptr;
+  if (trace) {
+    cudaEventCreate(&t_begin);
+    cudaEventRecord(t_begin, stream);
+  }
   for (int c = 0; c < num_chunks; ++c) {
     const int b0 = B->chunk_block_begin[c], b1 = B->chunk_block_begin[c + 1];
     const int t0 = B->out_tile_begin[b0], t1 = B->out_tile_begin[b1];
@@ -939,6 +958,12 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
     rc = LazyEvent(&B->chunk_done[c]);
     if (rc != HG_OK) return rc;
     HG_CUDA(cudaEventRecord(B->chunk_done[c], stream));
+    if (trace) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      cudaEventRecord(e, stream);
+      tk.push_back(e);
+    }
     HG_CUDA(cudaStreamWaitEvent(B->copy_out, B->chunk_done[c], 0));
     if (n == 0) continue;
     if (residuals)
@@ -951,10 +976,34 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
       HG_CUDA(cudaMemcpyAsync(jt1 + 3 * p0, a.jt1 + 3 * p0, sizeof(double) * n * 3, cudaMemcpyDeviceToHost, B->copy_out));
     if (jq1)
       HG_CUDA(cudaMemcpyAsync(jq1 + 4 * p0, a.jq1 + 4 * p0, sizeof(double) * n * 4, cudaMemcpyDeviceToHost, B->copy_out));
+    if (trace) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      cudaEventRecord(e, B->copy_out);
+      td.push_back(e);
+    }
   }
   HG_CUDA(cudaEventRecord(B->slot_done[slot], stream));
   HG_CUDA(cudaStreamSynchronize(B->copy_out));
   HG_CUDA(cudaStreamSynchronize(stream));
+  if (trace) {
+    std::fprintf(stderr, "[hg trace] host-pointer Evaluate, ms after the first launch was queued: kernels done");
+    for (cudaEvent_t e : tk) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, t_begin, e);
+      std::fprintf(stderr, " %.2f", ms);
+      cudaEventDestroy(e);
+    }
+    std::fprintf(stderr, "; copies out done");
+    for (cudaEvent_t e : td) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, t_begin, e);
+      std::fprintf(stderr, " %.2f", ms);
+      cudaEventDestroy(e);
+    }
+    std::fprintf(stderr, "\n");
+    cudaEventDestroy(t_begin);
+  }
   B->points_pending = false;
   return HG_OK;
 }
