@@ -104,6 +104,7 @@ SYMBOLS = {
     "hg_grid_size": (c_i, [vp]),
     "hg_grid_num_bricks": (c_i64, [vp]),
     "hg_grid_lookup": (c_i, [vp, c_i, c_i64, vp, vp]),
+    "hg_grid_stencil_bytes": (c_i64, [vp]),
     "hg_grid_interpolated_weight": (c_i, [vp, c_i64, vp, vp]),
     "hg_get_cell_index": (c_i, [c_f, c_i64, vp, vp]),
     "hg_cost_create": (c_i, [c_i, c_d, vp, c_i, c_i, vp, c_i, c_d, vp]),
@@ -254,6 +255,10 @@ class Grid:
     @property
     def num_bricks(self):
         return lib().hg_grid_num_bricks(self.h)
+
+    @property
+    def stencil_bytes(self):
+        return lib().hg_grid_stencil_bytes(self.h)
 
     def lookup(self, what, xyz):
         xyz = _i32(xyz).reshape(-1, 3)

@@ -454,6 +454,7 @@ struct hg_batch {
   TileDev* d_tiles_out = nullptr;
   int num_tiles_out = 0;
   int tile_out = 256;
+  bool wants_stencils = false;  // large batch: keep the grids' packed stencil copies built
   TileDev* d_tiles_ne = nullptr;
   int num_tiles_ne = 0;
   int* d_ne_tile_begin = nullptr;  // num_blocks + 1
@@ -677,7 +678,7 @@ CostArgs BaseArgs(const hg_batch* B, const bool build_stencils = true) {
   const char* env = std::getenv("HG_NO_STENCILS");  // diagnostic: gather from the apron bricks instead
   const bool packed = env == nullptr || std::atoi(env) == 0;
   for (int i = 0; i < B->num_grids; ++i) {
-    if (packed && build_stencils) EnsureStencils(B->grids[i]);  // no-op once built
+    if (packed && build_stencils && B->wants_stencils) EnsureStencils(B->grids[i]);  // no-op once built
     a.grids[i] = B->grids[i]->dev;
     if (!packed) a.grids[i].stencils = nullptr;
   }
@@ -740,9 +741,14 @@ int hg_batch_create(int kind, int num_blocks, const float* points, int stride_fl
   for (int i = 0; i < num_grids; ++i) B->grids[i] = grids[i];
   B->num_grids = num_grids;
   {
-    // Packed stencil copies of the grids (GridDev::stencils), built once per grid.
-    const char* env = std::getenv("HG_NO_STENCILS");
-    if (env == nullptr || std::atoi(env) == 0) {
+    // Packed stencil copies of the grids (GridDev::stencils), built once per grid — for batches large
+    // enough to gain from them: a scan matcher's few thousand points against the submap that is being
+    // written every scan would pay a rebuild per scan for a kernel that is latency-bound anyway.
+    int64_t min_points = 32768;
+    if (const char* env = std::getenv("HG_STENCIL_MIN_POINTS")) min_points = std::atoll(env);
+    const char* off = std::getenv("HG_NO_STENCILS");
+    B->wants_stencils = B->num_points >= min_points;
+    if (B->wants_stencils && (off == nullptr || std::atoi(off) == 0)) {
       for (int i = 0; i < num_grids; ++i) {
         const int rc = EnsureStencils(grids[i]);
         if (rc != HG_OK) return rc;

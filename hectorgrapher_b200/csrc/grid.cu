@@ -286,20 +286,31 @@ int EnsureStencils(const hg_grid* grid_const) {
   if (g->dev.stencils != nullptr || g->num_all_bricks == 0 || g->d_decoded == nullptr) return HG_OK;
   HG_ON_DEVICE(g->device);
   const int64_t n = g->num_all_bricks * 512;
-  HG_CUDA(cudaMalloc(&g->d_stencils, static_cast<size_t>(n) * 32));
-  PackStencilsKernel<<<static_cast<unsigned>((n + 255) / 256), 256>>>(static_cast<const float*>(g->d_decoded), n,
-                                                                    static_cast<float4*>(g->d_stencils));
+  if (g->stencil_capacity < n) {  // grow-only: a grid that is written between uses keeps its buffer
+    if (g->d_stencils) cudaFree(g->d_stencils);
+    g->d_stencils = nullptr;
+    g->stencil_capacity = 0;
+    const int64_t cap = n + n / 2;
+    HG_CUDA(cudaMalloc(&g->d_stencils, static_cast<size_t>(cap) * 32));
+    g->stencil_capacity = cap;
+  }
+  cudaStream_t stream = ThreadStream();
+  HG_REQUIRE(stream != nullptr, "EnsureStencils: cannot create a stream");
+  // the decoded bricks were written on the legacy default stream (upload / insertion), which a
+  // non-blocking stream does not wait for
+  HG_CUDA(cudaStreamSynchronize(nullptr));
+  PackStencilsKernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(
+      static_cast<const float*>(g->d_decoded), n, static_cast<float4*>(g->d_stencils));
   CountLaunch();
   HG_CUDA(cudaGetLastError());
-  HG_CUDA(cudaDeviceSynchronize());
+  HG_CUDA(cudaStreamSynchronize(stream));
   __atomic_store_n(&g->dev.stencils, static_cast<const float4*>(g->d_stencils), __ATOMIC_RELEASE);
   return HG_OK;
 }
 
+// The grid's voxels are about to change: the packed copy is stale (its buffer is kept).
 void DropStencils(hg_grid* g) {
   std::lock_guard<std::mutex> lock(g_stencil_mutex);
-  if (g->d_stencils) cudaFree(g->d_stencils);
-  g->d_stencils = nullptr;
   g->dev.stencils = nullptr;
 }
 
@@ -387,6 +398,11 @@ void hg_grid_destroy(hg_grid* grid) {
   if (grid->d_stencils) cudaFree(grid->d_stencils);
   DestroyGridMutable(grid);
   delete grid;
+}
+
+int64_t hg_grid_stencil_bytes(const hg_grid* grid) {
+  if (grid == nullptr || grid->dev.stencils == nullptr) return 0;
+  return grid->num_all_bricks * 512 * 32;
 }
 
 int hg_grid_size(const hg_grid* grid) { return grid ? grid->grid_size : 0; }

@@ -176,6 +176,7 @@ struct hg_grid {
   void* d_bricks = nullptr;
   void* d_decoded = nullptr;
   void* d_stencils = nullptr;
+  int64_t stencil_capacity = 0;  // voxels d_stencils has room for (32 bytes each)
   // Host copy of the brick coordinates (brick id -> brick coords), used to
   // derive the precomputation levels' brick sets.
   std::vector<int32_t> brick_coords;
@@ -186,7 +187,7 @@ namespace hg {
 void DestroyGridMutable(hg_grid* grid);  // insert.cu
 // grid.cu: builds GridDev::stencils if it is missing (thread-safe; the grid is logically const).
 int EnsureStencils(const hg_grid* grid);
-// Frees GridDev::stencils (the grid's voxels are about to change).
+// Marks GridDev::stencils stale (the grid's voxels are about to change); the buffer is kept.
 void DropStencils(hg_grid* grid);
 
 // scan_match.cu: CeresScanMatcher3D::Match solved entirely on the device (arguments of

@@ -71,6 +71,13 @@ int hg_grid_upload_tsdf(float resolution, float relative_truncation_distance, fl
 void hg_grid_destroy(hg_grid* grid);
 int hg_grid_size(const hg_grid* grid);
 int64_t hg_grid_num_bricks(const hg_grid* grid);
+/* Bytes of the grid's packed 2x2x2 stencil copy that is valid right now, 0 if there is none. The
+ * copy (32 bytes per voxel of every brick; no reference counterpart: a read-side layout of the
+ * same values HybridGridTSDF::GetTSD / HybridGrid::GetProbability return, hybrid_grid_tsdf.h:105-113)
+ * is built when a cost function over >= 32768 points is created on the grid (hg_batch_create,
+ * hg_cost_create), marked stale when the grid is written and rebuilt by that cost function's next
+ * evaluation. */
+int64_t hg_grid_stencil_bytes(const hg_grid* grid);
 
 /* HybridGrid::GetProbability / HybridGridTSDF::GetTSD / GetWeight at integer
  * cells (hybrid_grid.h:133-135, hybrid_grid_tsdf.h:105-113), evaluated on the

@@ -198,7 +198,9 @@ def test_packed_stencils_equal_apron_gather(oracle, hg, world, kind, monkeypatch
     cloud = world["cloud"]
     gg = [world["g_" + n] for n in KIND_GRIDS[kind]]
     two = kind.startswith("interpolated")
+    monkeypatch.setenv("HG_STENCIL_MIN_POINTS", "0")  # by default only batches of >= 32768 points build them
     gc = hg.Cost(kind, 0.01, cloud, gg, 0.6 if two else 0.0)
+    assert all(g.stencil_bytes > 0 for g in gg)
     p = perturbed(world["truth"], rng)
     if two:
         p = np.concatenate([p, perturbed(world["truth"], rng, 0.3, 0.15)])
@@ -211,7 +213,7 @@ def test_packed_stencils_equal_apron_gather(oracle, hg, world, kind, monkeypatch
         assert (a == b).all()
 
 
-def test_packed_stencils_follow_insertions(oracle, hg):
+def test_packed_stencils_follow_insertions(oracle, hg, monkeypatch):
     """A grid written after a cost function was built on it: the packed stencils are dropped with
     the old voxels and rebuilt, so the next evaluation sees the new map."""
     from hectorgrapher_b200 import synth
@@ -230,14 +232,19 @@ def test_packed_stencils_follow_insertions(oracle, hg):
     pose = np.concatenate([origin, synth.quat_from_yaw(yaw)])
     g.insert_tsdf(*clouds[0])
     o.insert_tsdf(*clouds[0])
+    monkeypatch.setenv("HG_STENCIL_MIN_POINTS", "0")
+    assert g.stencil_bytes == 0
     gc = hg.Cost("tsdf", 0.05, local, [g], 0.0)
+    assert g.stencil_bytes > 0
     oc = oracle.Cost("tsdf", 0.05, local, [o], 0.0)
     assert_close(gc.evaluate(pose)[0], oc.evaluate(pose)[0], "before the second insertion")
     before = gc.evaluate(pose)[0]
     for c in clouds[1:]:
         g.insert_tsdf(*c)
         o.insert_tsdf(*c)
+        assert g.stencil_bytes == 0  # stale
     r1, J1 = gc.evaluate(pose)
+    assert g.stencil_bytes > 0       # rebuilt by the evaluation
     r0, J0 = oc.evaluate(pose)
     assert_close(r1, r0, "after the insertions")
     assert_close(J1[1], J0[1], "after the insertions, rotation block")
