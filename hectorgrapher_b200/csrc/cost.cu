@@ -75,7 +75,7 @@ struct CostArgs {
   double* jt1;
   double* jq1;
   double* partials;  // normal-equation mode: [tile][P]
-  int vec_store;     // jq0 / jq1 are 16-byte aligned: use 16-byte stores
+  int vec_store;     // jq0 / jq1 rows: 2 = 32-byte aligned (one 256-bit store), 1 = 16-byte aligned, 0 = neither
 };
 
 constexpr int kThreads = 256;
@@ -119,6 +119,21 @@ __host__ __device__ constexpr int NumNormalTerms(int n) { return n * (n + 1) / 2
 // Terms the kernel accumulates per tile: those of the 7-vector u (see CostKernel).
 constexpr int kNormalTermsU = NumNormalTerms(7);
 
+// One 4-wide Jacobian row. vec: 2 = one 256-bit streaming store (32-byte aligned rows), 1 = two
+// 128-bit ones, 0 = scalar stores.
+__device__ __forceinline__ void StoreRow4(double* base, const long long gi, const int vec, const double j0,
+                                          const double j1, const double j2, const double j3) {
+  double* o = base + gi * 4;
+  if (vec == 2) {
+    asm volatile("st.global.cs.v4.b64 [%0], {%1, %2, %3, %4};" ::"l"(o), "d"(j0), "d"(j1), "d"(j2), "d"(j3) : "memory");
+  } else if (vec == 1) {
+    __stcs(reinterpret_cast<double2*>(o), make_double2(j0, j1));
+    __stcs(reinterpret_cast<double2*>(o) + 1, make_double2(j2, j3));
+  } else {
+    o[0] = j0; o[1] = j1; o[2] = j2; o[3] = j3;
+  }
+}
+
 // One point of a residual block: residual and Jacobian row, written straight to the outputs.
 // (aw ax ay az) = grad . d world / d q of the block's effective pose; for two poses the row of
 // pose k is that times d q / d q_k = s_k I + c q_other' (pose_prep.h).
@@ -138,16 +153,7 @@ __device__ __forceinline__ void PointJacobian(const CostArgs& a, const BlockDev&
       double* o = a.jt0 + gi * 3;
       __stcs(o, v.gx); __stcs(o + 1, v.gy); __stcs(o + 2, v.gz);
     }
-    if (a.jq0) {
-      if (a.vec_store) {
-        double2* o = reinterpret_cast<double2*>(a.jq0 + gi * 4);
-        __stcs(o, make_double2(A[0], A[1]));
-        __stcs(o + 1, make_double2(A[2], A[3]));
-      } else {
-        double* o = a.jq0 + gi * 4;
-        o[0] = A[0]; o[1] = A[1]; o[2] = A[2]; o[3] = A[3];
-      }
-    }
+    if (a.jq0) StoreRow4(a.jq0, gi, a.vec_store, A[0], A[1], A[2], A[3]);
     return;
   }
   const double ac = A[0] * sb.c[0] + A[1] * sb.c[1] + A[2] * sb.c[2] + A[3] * sb.c[3];
@@ -159,14 +165,7 @@ __device__ __forceinline__ void PointJacobian(const CostArgs& a, const BlockDev&
     double J[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) J[j] = sb.s0 * A[j] + ac * sb.q1[j];
-    if (a.vec_store) {
-      double2* o = reinterpret_cast<double2*>(a.jq0 + gi * 4);
-      __stcs(o, make_double2(J[0], J[1]));
-      __stcs(o + 1, make_double2(J[2], J[3]));
-    } else {
-      double* o = a.jq0 + gi * 4;
-      o[0] = J[0]; o[1] = J[1]; o[2] = J[2]; o[3] = J[3];
-    }
+    StoreRow4(a.jq0, gi, a.vec_store, J[0], J[1], J[2], J[3]);
   }
   if (a.jt1) {
     double* o = a.jt1 + gi * 3;
@@ -176,14 +175,7 @@ __device__ __forceinline__ void PointJacobian(const CostArgs& a, const BlockDev&
     double J[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) J[j] = sb.s1 * A[j] + ac * sb.q0[j];
-    if (a.vec_store) {
-      double2* o = reinterpret_cast<double2*>(a.jq1 + gi * 4);
-      __stcs(o, make_double2(J[0], J[1]));
-      __stcs(o + 1, make_double2(J[2], J[3]));
-    } else {
-      double* o = a.jq1 + gi * 4;
-      o[0] = J[0]; o[1] = J[1]; o[2] = J[2]; o[3] = J[3];
-    }
+    StoreRow4(a.jq1, gi, a.vec_store, J[0], J[1], J[2], J[3]);
   }
 }
 
@@ -885,7 +877,9 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
     rc = WaitForAllPoints(B, stream);
     if (rc != HG_OK) return rc;
     a.r = residuals; a.jt0 = jt0; a.jq0 = jq0; a.jt1 = jt1; a.jq1 = jq1;
-    a.vec_store = ((reinterpret_cast<uintptr_t>(jq0) | reinterpret_cast<uintptr_t>(jq1)) % 16 == 0) ? 1 : 0;
+    const uintptr_t rows = reinterpret_cast<uintptr_t>(jq0) | reinterpret_cast<uintptr_t>(jq1);
+    a.vec_store = rows % 32 == 0 ? 2 : (rows % 16 == 0 ? 1 : 0);
+    if (const char* env = std::getenv("HG_VEC_STORE_MAX")) a.vec_store = std::min(a.vec_store, std::atoi(env));
     rc = LaunchCost<false>(B, a, B->num_tiles_out, stream);
     if (rc != HG_OK) return rc;
     HG_CUDA(cudaEventRecord(B->slot_done[slot], stream));  // returns without waiting: see the slot ring
@@ -910,7 +904,7 @@ int hg_batch_evaluate(const hg_batch* B, const double* poses, int num_poses, con
   a.jt0 = jt0 ? d + 8 * N : nullptr;
   a.jt1 = jt1 ? d + 11 * N : nullptr;
   a.r = residuals ? d + 14 * N : nullptr;
-  a.vec_store = 1;
+  a.vec_store = 2;  // the staging area is 256-byte aligned and the 4-wide arrays come first
   // Small blocks (a scan matcher's Evaluate: ~1 MB into Ceres' pageable arrays): one DMA of the
   // whole staging area into pinned memory and host copies from there cost less than up to five
   // separate pageable device-to-host copies.
