@@ -1973,32 +1973,50 @@ __global__ void __launch_bounds__(256) LatticeBatchKernel(const SearchDev s, con
 // blockIdx.x = problem, blockIdx.y = chunk of 256 of its scans); the others are marked in
 // start_dead. The dive only has to produce a good bound.
 __global__ void __launch_bounds__(256) SelectStartsKernel(const SearchDev s, const int keep) {
+  __shared__ int tile[1024];
   const ProblemDev& P = s.problems[blockIdx.x];
   const int t = blockIdx.y * 256 + threadIdx.x;
-  if (t >= P.S) return;
+  if (blockIdx.y * 256 >= P.S) return;  // whole CTAs leave; the others stay together for the barriers
   const int* sums = s.start_sums + P.scan_begin;
+  const bool active = t < P.S;
   int dead = 0;
   if (P.S > keep) {
-    const int mine = sums[t];
+    const int mine = active ? sums[t] : 0;
     int rank = 0;
-    for (int j = 0; j < P.S; ++j) {
-      const int other = __ldg(sums + j);
-      rank += (other > mine || (other == mine && j < t)) ? 1 : 0;
+    // the problem's sums pass through shared memory 1 024 at a time: every thread compares its own
+    // with all of them (read straight from global memory this loop was 100 us for 1 633 scans)
+    for (int base = 0; base < P.S; base += 1024) {
+      const int n = min(1024, P.S - base);
+      __syncthreads();
+      for (int j = threadIdx.x; j < n; j += 256) tile[j] = __ldg(sums + base + j);
+      __syncthreads();
+#pragma unroll 8
+      for (int j = 0; j < n; ++j) {
+        const int other = tile[j];
+        rank += (other > mine || (other == mine && base + j < t)) ? 1 : 0;
+      }
     }
     dead = rank >= keep ? 1 : 0;
   }
-  s.start_dead[P.scan_begin + t] = dead;
+  if (active) s.start_dead[P.scan_begin + t] = dead;
 }
 
 // Dive start of every discrete scan: its best lattice candidate (first one on equal sums).
+// WARPS warps per scan: one for the small lattices of local windows, eight for a full-submap
+// lattice (4 913 sums per scan: a single warp walks them in 154 dependent rounds, ~100 us for the
+// whole launch however many scans there are).
+template <int WARPS>
 __global__ void __launch_bounds__(256) ArgmaxPerScanKernel(const SearchDev s) {
-  const int sg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (sg >= s.total_scans) return;
+  __shared__ int s_best[8], s_at[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sg = WARPS == 8 ? static_cast<int>(blockIdx.x) : static_cast<int>((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  if (sg >= s.total_scans) return;  // whole warps (WARPS == 1) or whole CTAs (WARPS == 8)
   const int* sums = s.lattice + static_cast<long long>(sg) * s.per_scan;
   int best = -1, at = 0x7fffffff;
-  for (int i = lane; i < s.per_scan; i += 32) {
-    const int v = sums[i];
+  const int first = WARPS == 8 ? static_cast<int>(threadIdx.x) : lane;
+#pragma unroll 4
+  for (int i = first; i < s.per_scan; i += 32 * WARPS) {
+    const int v = __ldg(sums + i);
     if (v > best) {
       best = v;
       at = i;
@@ -2012,7 +2030,22 @@ __global__ void __launch_bounds__(256) ArgmaxPerScanKernel(const SearchDev s) {
       at = oa;
     }
   }
-  if (lane != 0) return;
+  if (WARPS == 8) {
+    if (lane == 0) {
+      s_best[warp] = best;
+      s_at[warp] = at;
+    }
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    for (int w = 1; w < 8; ++w) {
+      if (s_best[w] > best || (s_best[w] == best && s_at[w] < at)) {
+        best = s_best[w];
+        at = s_at[w];
+      }
+    }
+  } else if (lane != 0) {
+    return;
+  }
   const ProblemDev& P = s.problems[s.scans[sg].problem];
   const int iz = at / (s.nxy * s.nxy), rem = at - iz * s.nxy * s.nxy, iy = rem / s.nxy, ix = rem - iy * s.nxy;
   s.starts[sg] = make_int4(sg, -P.wxy + ix * s.step, -P.wxy + iy * s.step, -P.wz + iz * s.step);
@@ -2614,7 +2647,11 @@ class DeviceSearch {
       }
     }
     // ---- dive
-    ArgmaxPerScanKernel<<<(total_scans_ * 32 + 255) / 256, 256, 0, stream_>>>(s);
+    if (per_scan_ >= 1024) {
+      ArgmaxPerScanKernel<8><<<total_scans_, 256, 0, stream_>>>(s);
+    } else {
+      ArgmaxPerScanKernel<1><<<(total_scans_ * 32 + 255) / 256, 256, 0, stream_>>>(s);
+    }
     CountLaunch();
     ++launches_;
     {
