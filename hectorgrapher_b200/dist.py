@@ -62,6 +62,10 @@ def all_reduce_max_device_bound(d_bound, stream, dist):
     so the host never waits between the two halves of a sharded search."""
     if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
         return
+    if not d_bound:
+        # the matcher searches on the host (strict_visit_order / HG_SEARCH_HOST_REPLAY): there is no
+        # device-resident bound, every rank's finish() searches under its own — nothing to exchange
+        return
     t = torch.as_tensor(_DeviceFloat(d_bound), device=torch.device("cuda", torch.cuda.current_device()))
     with torch.cuda.stream(torch.cuda.ExternalStream(stream)):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
