@@ -94,7 +94,7 @@ __device__ __forceinline__ ValueGrad Residual(const CostArgs& a, const double sc
   }
   ValueGrad t;
   if (LOOKUP == 1) {
-    LookupTsdfLevel<false>(a.grids[0], x, y, z, &t);
+    LookupTsdf(a.grids[0], x, y, z, &t);
   } else {
     bool found = false;
 #pragma unroll

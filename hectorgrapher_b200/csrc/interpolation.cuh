@@ -263,11 +263,10 @@ __device__ __forceinline__ bool LookupTsdfLevelAllObserved(const GridDev& g, con
   return true;
 }
 
-// One pyramid level. Returns false when the level must be skipped
-// (multi-resolution rule: any unobserved corner), true otherwise.
-template <bool MULTI>
-__device__ __forceinline__ bool LookupTsdfLevel(const GridDev& g, const double x, const double y,
-                                                const double z, ValueGrad* out) {
+// InterpolatedTSDF::GetTSD (interpolated_tsdf.h:71-116): the single-grid lookup with its
+// weight-aware blends. (The multi-resolution lookup runs LookupTsdfLevelAllObserved per level.)
+__device__ __forceinline__ void LookupTsdf(const GridDev& g, const double x, const double y, const double z,
+                                           ValueGrad* out) {
   double x1, y1, z1, x2, y2, z2;
   int ix, iy, iz;
   LowerVoxel3(g, x, y, z, &x1, &y1, &z1, &x2, &y2, &z2, &ix, &iy, &iz);
@@ -280,12 +279,10 @@ __device__ __forceinline__ bool LookupTsdfLevel(const GridDev& g, const double x
     o[k] = raw[k] == raw[k];  // NaN marks an unobserved voxel
     observed += o[k] ? 1 : 0;
   }
-  if (MULTI) {
-    if (observed < 8) return false;  // interpolated_multi_resolution_tsdf.h:99-106
-  } else if (observed == 0) {        // interpolated_tsdf.h:87-90
+  if (observed == 0) {  // interpolated_tsdf.h:87-90
     out->v = static_cast<double>(g.min_tsd);
     out->gx = out->gy = out->gz = 0.0;
-    return true;
+    return;
   }
   double q[8];
 #pragma unroll
@@ -294,23 +291,8 @@ __device__ __forceinline__ bool LookupTsdfLevel(const GridDev& g, const double x
   const double sy = CellWidthReciprocal(g.inv_resolution_d, y2 - y1);
   const double sz = CellWidthReciprocal(g.inv_resolution_d, z2 - z1);
   const double nx = (x - x1) * sx, ny = (y - y1) * sy, nz = (z - z1) * sz;
-  if (MULTI) {
-    // every corner observed: plain trilinear blend (all seven blends take the lerp branch)
-    const double a0 = (q[1] - q[0]) * nz + q[0], d0 = q[1] - q[0];
-    const double a1 = (q[3] - q[2]) * nz + q[2], d1 = q[3] - q[2];
-    const double a2 = (q[5] - q[4]) * nz + q[4], d2 = q[5] - q[4];
-    const double a3 = (q[7] - q[6]) * nz + q[6], d3 = q[7] - q[6];
-    const double b0 = (a1 - a0) * ny + a0, b0y = a1 - a0, b0z = (d1 - d0) * ny + d0;
-    const double b1 = (a3 - a2) * ny + a2, b1y = a3 - a2, b1z = (d3 - d2) * ny + d2;
-    out->v = (b1 - b0) * nx + b0;
-    out->gx = (b1 - b0) * sx;
-    out->gy = ((b1y - b0y) * nx + b0y) * sy;
-    out->gz = ((b1z - b0z) * nx + b0z) * sz;
-    return true;
-  }
   // interpolated_tsdf.h:34 hard-codes -0.3 for a pair of unobserved voxels.
   *out = BlendTsdf(-0.3, o, q, nx, ny, nz, sx, sy, sz);
-  return true;
 }
 
 // LOOKUP: 0 occupancy, 1 TSDF, 2 multi-resolution TSDF. Returns the residual

@@ -296,7 +296,7 @@ __device__ __forceinline__ void ScanMatchBody(const ScanMatchArgs& a) {
           v.gz = -scale * p.gz;
         } else {
           ValueGrad t;
-          LookupTsdfLevel<false>(grid, wp.x, wp.y, wp.z, &t);
+          LookupTsdf(grid, wp.x, wp.y, wp.z, &t);
           v.v = scale * t.v;  // tsdf_space_cost_function_3d.h:76
           v.gx = scale * t.gx;
           v.gy = scale * t.gy;
