@@ -60,6 +60,8 @@ def _worker(rank, world, port, out_dir):
         none, _ = hgdist.reduce_best_candidate(rec(0, 0.0, 0, (0, 0, 0)), dist, device="cpu")
         assert none is None
         assert hgdist.all_reduce_max_bound(0.25 + 0.5 * rank, dist, device="cpu") == 0.75
+        # a matcher that searches on the host has no device-resident bound: nothing is exchanged, nobody waits
+        assert hgdist.all_reduce_max_device_bound(0, 0, dist) is None
         # 3. constraint jobs: partition by index, gather fixed-size records, identical to the serial list
         jobs = np.arange(9)
         serial = np.stack([jobs, jobs * 0.5 + 1.0], 1)
