@@ -41,3 +41,14 @@ def test_host_pose_preparation():
     out = subprocess.run([exe], text=True, capture_output=True)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "POSE PREP OK" in out.stdout
+
+
+def test_branch_free_lower_voxel_selection():
+    """tests/cpp/test_lower_voxel.cpp: the arithmetic of the cost kernels' branch-free lower-voxel
+    selection against the reference's division + lround, 20 M values incl. cell boundaries (CPU only)."""
+    exe = os.path.join(ROOT, "tests", "cpp", "test_lower_voxel.bin")
+    subprocess.check_call(["g++", "-std=c++11", "-O2", "-ffp-contract=off", "-o", exe,
+                           os.path.join(ROOT, "tests", "cpp", "test_lower_voxel.cpp")])
+    out = subprocess.run([exe], text=True, capture_output=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "LOWER VOXEL OK" in out.stdout
