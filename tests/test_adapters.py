@@ -52,3 +52,14 @@ def test_branch_free_lower_voxel_selection():
     out = subprocess.run([exe], text=True, capture_output=True)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "LOWER VOXEL OK" in out.stdout
+
+
+def test_closed_form_rotation_terms():
+    """tests/cpp/test_rotation_terms.cpp: the closed form of grad . d world / d q the kernels use,
+    against central differences of Eigen's quaternion * vector formula (CPU only)."""
+    exe = os.path.join(ROOT, "tests", "cpp", "test_rotation_terms.bin")
+    subprocess.check_call(["g++", "-std=c++11", "-O2", "-ffp-contract=off", "-o", exe,
+                           os.path.join(ROOT, "tests", "cpp", "test_rotation_terms.cpp")])
+    out = subprocess.run([exe], text=True, capture_output=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "ROTATION TERMS OK" in out.stdout
