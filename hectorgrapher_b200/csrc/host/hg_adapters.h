@@ -493,6 +493,46 @@ class FastCorrelativeScanMatcher3D {
             "hg_fcsm_match_full_submap");
     return ToResult(r);
   }
+  // MatchFullSubmap spread over num_shards processes, one GPU each (the matcher's discrete scans are
+  // dealt round-robin; every process holds the same submap and node). The two collectives are the
+  // caller's:
+  //   all_reduce_max(float* device_value, void* cuda_stream) — all-reduce (max) of ONE float in device
+  //     memory, in place, queued on cuda_stream, e.g. ncclAllReduce(p, p, 1, ncclFloat, ncclMax, comm,
+  //     (cudaStream_t)cuda_stream); it is not called when the matcher searches on the host
+  //     (strict_visit_order), where every shard searches under its own bound;
+  //   all_gather(const double* mine, double* all, int doubles_per_rank) — all-gather of one host record
+  //     per shard into all[num_shards * doubles_per_rank], in shard order.
+  // Every process returns the same result: the reference's answer (fast_correlative_scan_matcher_3d.cc:
+  // 176-200, 384, 437-468), equal leaves ordered the way its search meets them. *order_unresolved (may
+  // be null) is set in the one case only an unsharded search in strict order can settle.
+  template <typename AllReduceMax, typename AllGather>
+  std::unique_ptr<Result> MatchFullSubmapSharded(const std::array<double, 4>& global_node_rotation,
+                                                 const std::array<double, 4>& global_submap_rotation,
+                                                 const TrajectoryNodeData& constant_data, float min_score,
+                                                 int shard_index, int num_shards, AllReduceMax&& all_reduce_max,
+                                                 AllGather&& all_gather, bool* order_unresolved = nullptr) const {
+    const hg_node_data d = constant_data.View();
+    hg_fcsm_search* search = nullptr;
+    float* d_bound = nullptr;
+    void* stream = nullptr;
+    CheckOk(hg_fcsm_full_submap_begin_async(matcher_, global_node_rotation.data(), global_submap_rotation.data(), &d,
+                                            min_score, shard_index, num_shards, &search, &d_bound, &stream),
+            "hg_fcsm_full_submap_begin_async");
+    if (d_bound != nullptr) all_reduce_max(d_bound, stream);
+    hg_match_result mine;
+    CheckOk(hg_fcsm_full_submap_finish(search, 0.f, &mine), "hg_fcsm_full_submap_finish");
+    std::vector<double> record(HG_BEST_RECORD_DOUBLES), all(static_cast<size_t>(num_shards) * HG_BEST_RECORD_DOUBLES);
+    CheckOk(hg_pack_best_record(&mine, record.data()), "hg_pack_best_record");
+    all_gather(record.data(), all.data(), HG_BEST_RECORD_DOUBLES);
+    int winner = -1, unresolved = 0;
+    CheckOk(hg_select_best_record(all.data(), num_shards, &winner, &unresolved), "hg_select_best_record");
+    if (order_unresolved != nullptr) *order_unresolved = unresolved != 0;
+    if (winner < 0) return nullptr;
+    hg_match_result best;
+    CheckOk(hg_unpack_best_record(all.data() + static_cast<size_t>(winner) * HG_BEST_RECORD_DOUBLES, &best),
+            "hg_unpack_best_record");
+    return ToResult(best);
+  }
   const hg_fcsm* handle() const { return matcher_; }
 
  private:

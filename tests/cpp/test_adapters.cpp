@@ -6,6 +6,7 @@
 //   range_data_inserter_3d_test.cc:43-98      (hit / miss probabilities after one insertion)
 // Prints "ADAPTERS OK" and exits 0 on success. With argument "compile-only" it exits before
 // touching the GPU (used by the CPU-side test to check that the header compiles and links).
+#include <array>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -109,6 +110,30 @@ int main(int argc, char** argv) {
     hg::TrajectoryNodeData far = data;
     far.low_resolution_point_cloud = {42.f, 42.f, 42.f};
     if (fcsm.Match(identity, identity, far, 0.3f)) return Fail("low resolution gate");
+    // The sharded form with one shard and pass-through collectives is the unsharded call.
+    const std::array<double, 4> no_rotation = {{1.0, 0.0, 0.0, 0.0}};
+    auto whole = fcsm.MatchFullSubmap(no_rotation, no_rotation, data, 0.3f);
+    int reduces = 0, gathers = 0;
+    bool unresolved = true;
+    auto sharded = fcsm.MatchFullSubmapSharded(
+        no_rotation, no_rotation, data, 0.3f, 0, 1,
+        [&reduces](float* device_value, void* stream) { reduces += device_value != nullptr && stream != nullptr; },
+        [&gathers](const double* mine, double* all, int n) {
+          ++gathers;
+          std::memcpy(all, mine, sizeof(double) * n);
+        },
+        &unresolved);
+    if (reduces != 1 || gathers != 1) return Fail("MatchFullSubmapSharded: collectives not called once each");
+    if (static_cast<bool>(whole) != static_cast<bool>(sharded)) return Fail("MatchFullSubmapSharded: found differs");
+    if (whole) {
+      if (whole->score != sharded->score) return Fail("MatchFullSubmapSharded: score");
+      for (int i = 0; i < 3; ++i)
+        if (whole->pose_estimate.translation[i] != sharded->pose_estimate.translation[i])
+          return Fail("MatchFullSubmapSharded: translation");
+      for (int i = 0; i < 4; ++i)
+        if (whole->pose_estimate.rotation[i] != sharded->pose_estimate.rotation[i])
+          return Fail("MatchFullSubmapSharded: rotation");
+    }
   }
 
   // --- ConstraintBuilder3D: CallsBack + finds the constraint ------------------------------
